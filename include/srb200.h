@@ -1,0 +1,81 @@
+/*
+ * srb200.h -- C ABI of libsrb200.so: the B200 (sm_100a) GMM-HMM scoring / alignment / EM hot path.
+ *
+ * Drop-in boundary for the path SURVEY.md section 8 names.  The reference (tjysdsg/speech-recognition) has
+ * no FFI: its boundary is the Python module API of sr/recognition (sr/recognition/__init__.py:1-5).  The
+ * host-side mirror of that API lives in speech-recognition_b200/sr/recognition and calls THIS library
+ * through ctypes (speech-recognition_b200/srb200/lib.py); INTEGRATION.md shows the stub.
+ *
+ * Conventions (all entry points):
+ *   - plain C types, DEVICE pointers unless the name says host; the caller owns every allocation;
+ *   - `stream` is a cudaStream_t passed as void*; calls are asynchronous on it, re-entrant per stream;
+ *   - return 0 on success, a negative SRB_E* code otherwise; srb_last_error_string() explains (thread local);
+ *   - costs are NEGATIVE log-likelihoods, smaller is better (decode.py:86-87); +inf = impossible;
+ *   - ragged batches are CSR: frames of utterance u are rows utt_off[u] .. utt_off[u+1]-1 of X[N,D] (fp32);
+ *   - a packed model (see srb_pack_model) holds R tied states x Mp Gaussians (Mp = M rounded up to 4).
+ */
+#ifndef SRB200_H
+#define SRB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SRB_OK 0
+#define SRB_EINVAL (-1)      /* bad argument (null pointer, size out of range) */
+#define SRB_EUNSUPPORTED (-2) /* shape outside what the kernels are built for */
+#define SRB_ECUDA (-3)       /* a CUDA runtime call failed */
+#define SRB_ENODEVICE (-4)   /* no sm_100 device */
+
+#define SRB_MAX_DIM 64       /* feature dimension limit of the register-resident scorer */
+#define SRB_DP_MAX_STATES 8  /* per-word state limit of the fused classify / train kernels */
+
+int srb_version(void);
+const char *srb_last_error_string(void);
+/* multiprocessor count and max opt-in shared memory of the current device */
+int srb_device_info(int *sm_count, int *smem_optin_bytes, int *cc_major, int *cc_minor);
+
+/* ---- packed model ------------------------------------------------------------------------------
+ * Replaces MultivariateNormal.__init__/cov setter/pdf and GMM.evaluate's per-call arithmetic
+ * (hmm_state.py:10-45,114-120): for Gaussian g, dim d (x' = x - shift[d]):
+ *     log2 N_g(x) w_g = sum_d ( x'^2 * A[g,d] + x' * B[g,d] ) + C[g]
+ *     A = -0.5/var * log2(e),  B = (mu-shift)/var * log2(e),
+ *     C = (log w - 0.5*(D log 2pi + sum log var) - 0.5*sum (mu-shift)^2/var) * log2(e)
+ * Layout: ab = float2[G4/4][D][4] (A,B pairs of 4 consecutive Gaussians per dim), c = float[G4],
+ * G4 = R*Mp.  Padding Gaussians carry C = -inf.  Weights are NOT normalised.
+ * Inputs are float64 device arrays mu[R*M,D], var[R*M,D], w[R*M], shift[D]. */
+int64_t srb_packed_ab_floats(int R, int M, int D);
+int64_t srb_packed_c_floats(int R, int M);
+int srb_pack_model(const double *mu, const double *var, const double *w, const double *shift, int R, int M, int D,
+                   float *ab, float *c, float *shift_f32, void *stream);
+
+/* ---- K1: GMM scoring (GMM.evaluate, hmm_state.py:114-120, batched over frames and states) -------
+ * E[n, r] = -log sum_m w_rm N_rm(X[n])  for r in [0,R).  Any output may be NULL:
+ *   E        float[N, ldE]   costs
+ *   best_cost/best_state     per-frame min over r (first minimum) -- the streaming reduction used for
+ *                            the large sweep where E must not be materialised
+ *   comp     float[N, R*Mp]  per-Gaussian natural-log  log(w_m N_m(x))  (GMM.evaluate(..., False), log domain) */
+int srb_gmm_score(const float *X, int64_t N, int D, const float *ab, const float *c, const float *shift, int R,
+                  int Mp, float *E, int64_t ldE, float *best_cost, int32_t *best_state, float *comp, void *stream);
+
+/* ---- fused isolated-word classifier (core.py:79-87 over hmm.py:126-135 over decode.py:80-146) ----
+ * W word models of S states each (packed model has R = W*S states, word-major); trans float[W,S,S] with
+ * trans[w,i,j] = cost j -> i, +inf = none (decode.py:86-87).  Start in state 0 at frame 0
+ * (decode.py:99-100), end in state S-1 at the last frame (decode.py:126-127).
+ *   final float[B,W]  = costs[-1,-1] per word (hmm.py:135);   label int32[B] = first argmin (core.py:85)
+ * Utterances need >= 2 frames (decode.py reads column -1 at c == 0). */
+int srb_classify(const float *X, const int32_t *utt_off, int32_t B, int64_t N, int D, const float *ab,
+                 const float *c, const float *shift, int W, int S, int Mp, const float *trans, float *final,
+                 int32_t *label, void *stream);
+
+/* ---- FP32 FMA peak probe (roofline denominator for K1; not part of the reference path) ----------
+ * Runs `iters` dependent-chain-free FMA rounds per thread on every SM and returns elapsed ms through
+ * *ms_out (host pointer) plus the FMA count (host pointer).  packed != 0 uses fma.rn.f32x2. */
+int srb_fma_peak(int packed, int iters, float *ms_out, double *fma_count_out, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SRB200_H */

@@ -1,0 +1,114 @@
+"""Batched device-side operators over libsrb200 (torch is used for memory and streams only)."""
+import numpy as np
+import torch
+
+from . import lib as _l
+
+
+def device():
+    if not torch.cuda.is_available():
+        raise RuntimeError("srb200 needs a CUDA device (B200, sm_100a); there is no CPU path")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def fma_peak(packed=True, iters=4096):
+    """Measured FP32 FMA rate (FMA/s) of the current device with plain FFMA or packed fma.rn.f32x2."""
+    import ctypes
+    ms, n = ctypes.c_float(), ctypes.c_double()
+    _l.check(_l.load().srb_fma_peak(int(packed), iters, ctypes.byref(ms), ctypes.byref(n), _l.stream_ptr()))
+    return n.value / (ms.value * 1e-3)
+
+
+class PackedModel:
+    """R tied states x M diagonal Gaussians in the scorer's layout (see include/srb200.h, srb_pack_model).
+
+    Keeps the float64 parameters (mu, var, w: [R, M, D] / [R, M]) on the device next to the packed fp32 copy;
+    `repack()` refreshes the latter after an M-step wrote the former."""
+
+    def __init__(self, mu, var, w, shift=None):
+        dev = device()
+        mu = torch.as_tensor(np.asarray(mu, np.float64)) if not torch.is_tensor(mu) else mu
+        var = torch.as_tensor(np.asarray(var, np.float64)) if not torch.is_tensor(var) else var
+        w = torch.as_tensor(np.asarray(w, np.float64)) if not torch.is_tensor(w) else w
+        assert mu.dim() == 3 and var.shape == mu.shape and w.shape == mu.shape[:2]
+        self.R, self.M, self.D = (int(v) for v in mu.shape)
+        self.Mp = (self.M + 3) // 4 * 4
+        self.mu = mu.to(dev, torch.float64).contiguous()
+        self.var = var.to(dev, torch.float64).contiguous()
+        self.w = w.to(dev, torch.float64).contiguous()
+        if shift is None:
+            shift = self.mu.reshape(-1, self.D).mean(dim=0)
+        self.shift64 = torch.as_tensor(shift).to(dev, torch.float64).contiguous()
+        L = _l.load()
+        self.ab = torch.empty(L.srb_packed_ab_floats(self.R, self.M, self.D), dtype=torch.float32, device=dev)
+        self.c = torch.empty(L.srb_packed_c_floats(self.R, self.M), dtype=torch.float32, device=dev)
+        self.shift = torch.empty(self.D, dtype=torch.float32, device=dev)
+        self.repack()
+
+    def repack(self):
+        _l.check(_l.load().srb_pack_model(_l.ptr(self.mu), _l.ptr(self.var), _l.ptr(self.w), _l.ptr(self.shift64),
+                                          self.R, self.M, self.D, _l.ptr(self.ab), _l.ptr(self.c),
+                                          _l.ptr(self.shift), _l.stream_ptr()))
+        return self
+
+    @classmethod
+    def from_words(cls, word_models, shift=None):
+        """word_models: list of (mu[S,M,D], cov[S,M,D], w[S,M], trans[S,S]) -> (PackedModel, trans[W,S,S] fp32)."""
+        mu = np.concatenate([np.asarray(m[0], np.float64) for m in word_models], axis=0)
+        var = np.concatenate([np.asarray(m[1], np.float64) for m in word_models], axis=0)
+        w = np.concatenate([np.asarray(m[2], np.float64) for m in word_models], axis=0)
+        pm = cls(mu, var, w, shift)
+        trans = torch.as_tensor(np.stack([np.asarray(m[3], np.float64) for m in word_models])).to(pm.ab.device,
+                                                                                               torch.float32)
+        return pm, trans.contiguous()
+
+
+def as_frames(X):
+    """[N, D] float32 contiguous CUDA tensor (16-byte aligned by the torch allocator)."""
+    if not torch.is_tensor(X):
+        X = torch.as_tensor(np.ascontiguousarray(X, dtype=np.float32))
+    return X.to(device(), torch.float32).contiguous()
+
+
+def as_offsets(off):
+    if not torch.is_tensor(off):
+        off = torch.as_tensor(np.ascontiguousarray(off, dtype=np.int32))
+    return off.to(device(), torch.int32).contiguous()
+
+
+def gmm_score(X, pm, want_E=True, want_best=False, want_comp=False):
+    """K1.  -> dict(E[N,R], best_cost[N], best_state[N], comp[N,R,Mp]) for the requested outputs."""
+    X = as_frames(X)
+    N = X.shape[0]
+    assert X.shape[1] == pm.D
+    dev = X.device
+    out = {}
+    E = torch.empty((N, pm.R), dtype=torch.float32, device=dev) if want_E else None
+    bc = torch.empty(N, dtype=torch.float32, device=dev) if want_best else None
+    bs = torch.empty(N, dtype=torch.int32, device=dev) if want_best else None
+    comp = torch.empty((N, pm.R, pm.Mp), dtype=torch.float32, device=dev) if want_comp else None
+    _l.check(_l.load().srb_gmm_score(_l.ptr(X), N, pm.D, _l.ptr(pm.ab), _l.ptr(pm.c), _l.ptr(pm.shift), pm.R, pm.Mp,
+                                     _l.ptr(E), pm.R, _l.ptr(bc), _l.ptr(bs), _l.ptr(comp), _l.stream_ptr()))
+    if want_E:
+        out["E"] = E
+    if want_best:
+        out["best_cost"], out["best_state"] = bc, bs
+    if want_comp:
+        out["comp"] = comp
+    return out
+
+
+def classify(X, off, pm, trans, W, S, final=None, label=None):
+    """Fused score + Viterbi over W isolated-word models (core.py:79-87).  -> (final[B,W] f32, label[B] i32)."""
+    X = as_frames(X)
+    off = as_offsets(off)
+    B = off.numel() - 1
+    assert pm.R == W * S and tuple(trans.shape) == (W, S, S)
+    if final is None:
+        final = torch.empty((B, W), dtype=torch.float32, device=X.device)
+    if label is None:
+        label = torch.empty(B, dtype=torch.int32, device=X.device)
+    _l.check(_l.load().srb_classify(_l.ptr(X), _l.ptr(off), B, X.shape[0], pm.D, _l.ptr(pm.ab), _l.ptr(pm.c),
+                                    _l.ptr(pm.shift), W, S, pm.Mp, _l.ptr(trans), _l.ptr(final), _l.ptr(label),
+                                    _l.stream_ptr()))
+    return final, label

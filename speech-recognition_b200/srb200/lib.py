@@ -1,0 +1,65 @@
+"""ctypes binding of libsrb200.so (include/srb200.h).  No CPU fallback: a missing library is an error."""
+import ctypes
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(HERE, "libsrb200.so")
+
+c_void_p, c_int, c_i32, c_i64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_int32, ctypes.c_int64
+
+# name -> (restype, argtypes); one entry per symbol declared in include/srb200.h
+SIGNATURES = {
+    "srb_version": (c_int, []),
+    "srb_last_error_string": (ctypes.c_char_p, []),
+    "srb_device_info": (c_int, [ctypes.POINTER(c_int)] * 4),
+    "srb_packed_ab_floats": (c_i64, [c_int, c_int, c_int]),
+    "srb_packed_c_floats": (c_i64, [c_int, c_int]),
+    "srb_pack_model": (c_int, [c_void_p] * 4 + [c_int] * 3 + [c_void_p] * 4),
+    "srb_gmm_score": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_i64,
+                              c_void_p, c_void_p, c_void_p, c_void_p]),
+    "srb_classify": (c_int, [c_void_p, c_void_p, c_i32, c_i64, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                             c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "srb_fma_peak": (c_int, [c_int, c_int, ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_double), c_void_p]),
+}
+
+
+class SrbError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"libsrb200 error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def load():
+    """Load the library (built by srb200/build.py).  Raises if it is absent -- there is no other path."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise ImportError(f"{SO_PATH} not built: run `python __graft_entry__.py build` (nvcc, sm_100a)")
+        lib = ctypes.CDLL(SO_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        raise SrbError(rc, load().srb_last_error_string().decode())
+
+
+def ptr(t):
+    """device pointer of a torch tensor (or None)"""
+    if t is None:
+        return None
+    assert t.is_cuda and t.is_contiguous(), "libsrb200 takes contiguous CUDA tensors"
+    return t.data_ptr()
+
+
+def stream_ptr():
+    import torch
+    return torch.cuda.current_stream().cuda_stream

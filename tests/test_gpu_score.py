@@ -1,0 +1,126 @@
+"""GPU parity: K1 scoring and the fused classifier against the float64 oracle (through the C ABI)."""
+import numpy as np
+import pytest
+
+from oracle import oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-4          # north_star: log-likelihoods within 1e-4 relative (FP32)
+
+
+@pytest.fixture(scope="module")
+def eng():
+    from srb200 import engine
+    return engine
+
+
+def _models(seed=1, **kw):
+    from srb200 import synth
+    return synth.make_models(seed, **kw)
+
+
+def test_gmm_score_matches_oracle(eng):
+    from srb200 import synth
+    models, base = _models(3, W=11, S=5, M=4)
+    X, off, _ = synth.make_utterances(4, base, 13, T=97)          # N = 1261: ragged last tile
+    pm, _ = eng.PackedModel.from_words(models)
+    out = eng.gmm_score(X, pm, want_E=True, want_best=True, want_comp=True)
+    E = out["E"].cpu().numpy()
+    comp = out["comp"].cpu().numpy()
+    emit = np.arange(55)
+    Eo = orc.emissions(X.astype(np.float64), models, emit, log_domain=True)
+    np.testing.assert_allclose(E, Eo, rtol=RTOL)
+    # per-Gaussian log(w N(x)) of state (word 2, state 3)
+    mu, var, w, _ = models[2]
+    _, co = orc.gmm_evaluate(X.astype(np.float64), mu[3], var[3], w[3], log_domain=True)
+    np.testing.assert_allclose(comp[:, 13, :4], co, rtol=RTOL, atol=1e-3)
+    bs = out["best_state"].cpu().numpy()
+    bc = out["best_cost"].cpu().numpy()
+    assert np.array_equal(bc, E.min(axis=1)) and np.array_equal(bs, E.argmin(axis=1))
+
+
+def test_gmm_score_reference_linear_domain_and_unnormalised_weights(eng, golden):
+    """Against the frozen outputs of the reference's own GMM.evaluate (hmm_state.py:114-120)."""
+    g = golden["emission"]
+    X = g["em_X"]
+    pm = eng.PackedModel(g["em_mu"][None], g["em_cov"][None], g["em_w"][None])     # one state, weights sum != 1
+    out = eng.gmm_score(X.astype(np.float32), pm, want_comp=True)
+    E = out["E"].cpu().numpy()[:, 0]
+    ref = g["em_cost"]
+    f = np.isfinite(ref)
+    assert f.any()
+    np.testing.assert_allclose(E[f], ref[f], rtol=RTOL)
+    comps = g["em_comps"]                                         # linear-domain w_m N_m(x)
+    ok = comps > 1e-300
+    np.testing.assert_allclose(out["comp"].cpu().numpy()[:, 0, :4][ok], np.log(comps[ok]), rtol=RTOL, atol=1e-3)
+
+
+@pytest.mark.parametrize("M,S,W", [(4, 5, 11), (16, 8, 3), (2, 3, 4)])
+def test_gmm_score_multi_block_states(eng, M, S, W):
+    from srb200 import synth
+    models, base = _models(5, W=W, S=S, M=M)
+    X, off, _ = synth.make_utterances(6, base, 7, T=50)
+    pm, _ = eng.PackedModel.from_words(models)
+    E = eng.gmm_score(X, pm)["E"].cpu().numpy()
+    Eo = orc.emissions(X.astype(np.float64), models, np.arange(W * S), log_domain=True)
+    np.testing.assert_allclose(E, Eo, rtol=RTOL)
+
+
+def test_gmm_score_param_groups(eng):
+    """More Gaussians than fit shared memory at once: the kernel sweeps parameter groups."""
+    from srb200 import synth
+    models, base = _models(7, W=40, S=5, M=8)                     # 1600 Gaussians ~ 500 KB of parameters
+    X, off, _ = synth.make_utterances(8, base, 6, T=100)
+    pm, _ = eng.PackedModel.from_words(models)
+    out = eng.gmm_score(X, pm, want_best=True)
+    E = out["E"].cpu().numpy()
+    Eo = orc.emissions(X.astype(np.float64), models, np.arange(200), log_domain=True)
+    np.testing.assert_allclose(E, Eo, rtol=RTOL)
+    assert np.array_equal(out["best_state"].cpu().numpy(), E.argmin(axis=1))
+
+
+@pytest.mark.parametrize("ragged", [None, (2, 40), (300, 1300)])
+def test_classify_matches_oracle(eng, ragged):
+    from srb200 import synth
+    models, base = _models(11, W=11, S=5, M=4)
+    X, off, words = synth.make_utterances(12, base, 64 if ragged != (300, 1300) else 9, T=100, ragged=ragged)
+    pm, trans = eng.PackedModel.from_words(models)
+    final, label = eng.classify(X, off, pm, trans, 11, 5)
+    final, label = final.cpu().numpy(), label.cpu().numpy()
+    fo, lo = orc.classify(X.astype(np.float64), off.astype(np.int64), models, log_domain=True)
+    fin = np.isfinite(fo)
+    assert np.array_equal(np.isfinite(final), fin)
+    np.testing.assert_allclose(final[fin], fo[fin], rtol=RTOL)
+    # labels exact wherever the oracle's decision margin exceeds the tolerance
+    so = np.sort(fo, axis=1)
+    decided = (so[:, 1] - so[:, 0]) > RTOL * np.abs(so[:, 0])
+    assert decided.mean() > 0.9
+    assert np.array_equal(label[decided], lo[decided])
+    if ragged is None:
+        assert (label == words).mean() > 0.95
+
+
+def test_classify_golden_reference(eng, golden):
+    """Frozen HMM.evaluate outputs of the reference (hmm.py:126-135) for 3 isolated models."""
+    g = golden["decode"]
+    models = [(g["iso_mu"][i], g["iso_cov"][i], g["iso_w"][i], g["iso_trans"][i]) for i in range(len(g["iso_mu"]))]
+    pm, trans = eng.PackedModel.from_words(models)
+    W, S = len(models), models[0][0].shape[0]
+    final, label = eng.classify(g["iso_X"].astype(np.float32), g["iso_off"].astype(np.int32), pm, trans, W, S)
+    ref = g["iso_final"]                                          # [B, W]
+    f = np.isfinite(ref)
+    np.testing.assert_allclose(final.cpu().numpy()[f], ref[f], rtol=RTOL)
+
+
+def test_classify_dense_transitions(eng):
+    """Non left-to-right (ergodic) transitions take the dense DP branch."""
+    from srb200 import synth
+    rng = np.random.default_rng(5)
+    models, base = _models(21, W=4, S=4, M=4)
+    models = [(m[0], m[1], m[2], rng.uniform(0.5, 3.0, size=(4, 4))) for m in models]
+    X, off, _ = synth.make_utterances(22, base, 10, T=30)
+    pm, trans = eng.PackedModel.from_words(models)
+    final, _ = eng.classify(X, off, pm, trans, 4, 4)
+    fo, _ = orc.classify(X.astype(np.float64), off.astype(np.int64), models, log_domain=True)
+    np.testing.assert_allclose(final.cpu().numpy(), fo, rtol=RTOL)
