@@ -112,3 +112,74 @@ def classify(X, off, pm, trans, W, S, final=None, label=None):
                                     _l.ptr(pm.shift), W, S, pm.Mp, _l.ptr(trans), _l.ptr(final), _l.ptr(label),
                                     _l.stream_ptr()))
     return final, label
+
+
+class HostClassifier:
+    """Host-facing isolated-word classifier (core.py:63-94's inner loop): numpy / pinned host frames in, labels out.
+
+    The batch is cut into chunks of whole utterances; chunk k+1 is copied host->device on one stream while chunk k
+    is scored and decoded on the other (two device staging buffers), and the labels come back with one D2H copy
+    per chunk.  All device work goes through srb_classify."""
+
+    def __init__(self, pm, trans, W, S, max_utts=8192, max_frames=8192 * 100):
+        dev = device()
+        self.pm, self.trans, self.W, self.S = pm, trans, W, S
+        self.max_utts, self.max_frames = int(max_utts), int(max_frames)
+        self.streams = [torch.cuda.Stream(dev) for _ in range(2)]
+        self.xbuf = [torch.empty((self.max_frames, pm.D), dtype=torch.float32, device=dev) for _ in range(2)]
+        self.obuf = [torch.empty(self.max_utts + 1, dtype=torch.int32, device=dev) for _ in range(2)]
+        self.final = [torch.empty((self.max_utts, W), dtype=torch.float32, device=dev) for _ in range(2)]
+        self.label = [torch.empty(self.max_utts, dtype=torch.int32, device=dev) for _ in range(2)]
+        self.off_pin = [torch.empty(self.max_utts + 1, dtype=torch.int32).pin_memory() for _ in range(2)]
+        self.done = [None, None]
+
+    def _chunks(self, off):
+        """Greedy split of utterances into chunks bounded by max_utts / max_frames."""
+        B = len(off) - 1
+        u = 0
+        while u < B:
+            ue = min(B, u + self.max_utts)
+            lim = int(off[u]) + self.max_frames
+            if int(off[ue]) > lim:
+                ue = int(np.searchsorted(off, lim, side="right")) - 1
+                if ue <= u:
+                    raise ValueError(f"utterance {u} has more than max_frames={self.max_frames} frames")
+            yield u, ue
+            u = ue
+
+    def run(self, X, off, labels_out=None, final_out=None):
+        """X: [N, D] float32 host tensor/array (pinned for full speed); off: [B+1] int32 -> labels [B] int32 (host)."""
+        Xt = X if torch.is_tensor(X) else torch.from_numpy(np.ascontiguousarray(X, dtype=np.float32))
+        offn = off.numpy() if torch.is_tensor(off) else np.asarray(off)
+        B = len(offn) - 1
+        if labels_out is None:
+            labels_out = torch.empty(B, dtype=torch.int32).pin_memory()
+        cur = torch.cuda.current_stream()
+        start = torch.cuda.Event()
+        start.record(cur)
+        L = _l.load()
+        for k, (u0, u1) in enumerate(self._chunks(offn)):
+            s = k & 1
+            st = self.streams[s]
+            nb, f0, f1 = u1 - u0, int(offn[u0]), int(offn[u1])
+            if self.done[s] is not None:
+                self.done[s].synchronize()          # pinned offsets / staging buffers of slot s are free again
+            np.subtract(offn[u0:u1 + 1], f0, out=self.off_pin[s].numpy()[:nb + 1])
+            with torch.cuda.stream(st):
+                st.wait_event(start)
+                self.xbuf[s][:f1 - f0].copy_(Xt[f0:f1], non_blocking=True)
+                self.obuf[s][:nb + 1].copy_(self.off_pin[s][:nb + 1], non_blocking=True)
+                _l.check(L.srb_classify(self.xbuf[s].data_ptr(), self.obuf[s].data_ptr(), nb, f1 - f0, self.pm.D,
+                                        _l.ptr(self.pm.ab), _l.ptr(self.pm.c), _l.ptr(self.pm.shift), self.W, self.S,
+                                        self.pm.Mp, _l.ptr(self.trans), self.final[s].data_ptr(),
+                                        self.label[s].data_ptr(), st.cuda_stream))
+                labels_out[u0:u1].copy_(self.label[s][:nb], non_blocking=True)
+                if final_out is not None:
+                    final_out[u0:u1].copy_(self.final[s][:nb], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(st)
+                self.done[s] = ev
+        for s in range(2):
+            if self.done[s] is not None:
+                cur.wait_event(self.done[s])
+        return labels_out
