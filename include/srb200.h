@@ -70,6 +70,45 @@ int srb_classify(const float *X, const int32_t *utt_off, int32_t B, int64_t N, i
                  const float *c, const float *shift, int W, int S, int Mp, const float *trans, float *final,
                  int32_t *label, void *stream);
 
+
+/* ---- K2: batched Viterbi over state graphs with non-emitting states ------------------------------
+ * Replaces decode_hmm_states (decode.py:80-146) and, with E = local distances, dtw (decode.py:7-77).
+ * One or more graphs are packed back to back (graph g owns states g_state_off[g] .. g_state_off[g+1]-1);
+ * utterance u runs on graph utt_graph[u] (NULL: graph 0).  Per graph-local state r:
+ *   emit[r]      column of E holding states[r].evaluate(x), or -1 for a NES (hmm_state.py:90-91, cost 0)
+ *   pred_ptr     CSR (absolute offsets) over the finite entries of transitions[r, :] in ascending origin order
+ *                (decode.py:104-107), pred_idx = origin (graph local), pred_cost = transitions[r, origin]
+ *   nes_idx      ascending local indices of the NES (they split a column into runs, see viterbi.cu)
+ *   end_state    candidate end states in caller order; the end frame is always the last frame (callers pass
+ *                -1 or T-1: main.py:60, continuous_speech.py:89, decode.py:126-127)
+ * At most 255 predecessors per state.  Start: only (state 0, frame 0) is seeded (decode.py:99-100).
+ * Outputs: best_cost[B], best_end[B] (last minimum wins, decode.py:131-134; +inf / -1 when no path),
+ *   bp[bp_off[u] + c*R + r] = position of the winning origin in r's predecessor list (first minimum wins),
+ *   costs_out (optional) same indexing, float: costs[r, c] (decode.py returns it),
+ *   path_state/path_frame[path_off[u] ...] the reversed path of decode.py:142-146 (end cell excluded,
+ *   stops at frame 0), path_len[u] its length (0 when no path, -1 when the capacity path_off[u+1]-path_off[u]
+ *   was too small; T + 2 * number of NES + 1 always suffices). */
+int srb_viterbi_graph(const float *E, int64_t ldE, const int32_t *utt_off, int32_t B, const int32_t *utt_graph,
+                      const int32_t *g_state_off, const int32_t *g_nes_off, const int32_t *g_end_off,
+                      const int32_t *emit, const int32_t *pred_ptr, const int32_t *pred_idx, const float *pred_cost,
+                      const int32_t *nes_idx, const int32_t *end_state, int32_t Rmax, const int64_t *bp_off,
+                      uint8_t *bp, float *costs_out, float *best_cost, int32_t *best_end, const int64_t *path_off,
+                      int32_t *path_state, int32_t *path_frame, int32_t *path_len, void *stream);
+
+/* ---- K4: batched forward-backward (Baum-Welch E-step) for NES-free graphs -------------------------
+ * The reference has NO forward-backward; semantics are defined to be consistent with
+ * srb_viterbi_graph: same graph packing, start in state 0 at frame 0, end in any end_state at the last frame;
+ * min instead of log-sum-exp gives the Viterbi costs.  succ_* is the successor CSR of the same edges
+ * (succ_ptr absolute, per origin), pred_tgt[j] the target of predecessor edge j.
+ *   gamma[ws_off[u] + c*R + r]  state posterior (sums to 1 over r);  neg_log_z[u] = -log P(x) (double)
+ *   xi_sum[j] += sum_c posterior of edge j (double, indexed like pred_idx; caller zeroes it; optional). */
+int srb_forward_backward(const float *E, int64_t ldE, const int32_t *utt_off, int32_t B, const int32_t *utt_graph,
+                         const int32_t *g_state_off, const int32_t *g_end_off, const int32_t *emit,
+                         const int32_t *pred_ptr, const int32_t *pred_idx, const float *pred_cost,
+                         const int32_t *pred_tgt, const int32_t *succ_ptr, const int32_t *succ_idx,
+                         const float *succ_cost, const int32_t *end_state, int32_t Rmax, int32_t NNZmax,
+                         const int64_t *ws_off, float *gamma, double *neg_log_z, double *xi_sum, void *stream);
+
 /* ---- FP32 FMA peak probe (roofline denominator for K1; not part of the reference path) ----------
  * Runs `iters` dependent-chain-free FMA rounds per thread on every SM and returns elapsed ms through
  * *ms_out (host pointer) plus the FMA count (host pointer).  packed != 0 uses fma.rn.f32x2. */

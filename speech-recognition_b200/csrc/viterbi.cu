@@ -1,0 +1,410 @@
+// viterbi.cu -- K2: batched Viterbi over arbitrary state graphs with non-emitting states (decode.py:80-146),
+// back-pointers + traceback, and K4: batched log-domain forward-backward (no reference counterpart).
+//
+// One warp per utterance, states strided over the lanes, the two live cost columns in shared memory.
+// The reference sweeps states in index order inside a column and lets a transition that touches a
+// non-emitting state (NES) read the SAME column (decode.py:109-111); a same-column read of a state with a
+// higher index sees +inf (not yet written).  That order is reproduced by cutting a column into the runs of
+// emitting states between consecutive NES: run k is relaxed in parallel, then NES k is reduced over its
+// predecessors, then run k+1 ...  Ties: the first minimum in origin order wins (np.argmin, decode.py:118).
+#include "common.cuh"
+
+namespace srb {
+
+constexpr int VW = 4;   // warps (utterances in flight) per CTA
+
+struct GraphBatch {
+    const int32_t *utt_graph;     // [B] graph of each utterance, or null (all use graph 0)
+    const int32_t *g_state_off;   // [ng+1] first global state index of each graph
+    const int32_t *g_nes_off;     // [ng+1] range of nes_idx
+    const int32_t *g_end_off;     // [ng+1] range of end_state
+    const int32_t *emit;          // [sum R] column of E, or -1 for a NES (hmm_state.py:90-91: evaluate -> 0)
+    const int32_t *pred_ptr;      // [sum R + 1] absolute CSR offsets into pred_idx / pred_cost
+    const int32_t *pred_idx;      // origin state (graph local), ascending per target
+    const float *pred_cost;       // transitions[target, origin]
+    const int32_t *nes_idx;       // ascending local indices of the NES of each graph
+    const int32_t *end_state;     // candidate end states (local), frame = last (main.py:60 passes -1)
+};
+
+__device__ __forceinline__ void lexmin(float &v, int &p, float ov, int op) {
+    if (ov < v || (ov == v && op < p)) {
+        v = ov;
+        p = op;
+    }
+}
+
+__global__ void __launch_bounds__(VW * 32)
+viterbi_graph_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *__restrict__ off, int B, GraphBatch G,
+                     int Rmax, const int64_t *__restrict__ bp_off, uint8_t *__restrict__ bp,
+                     float *__restrict__ costs_out, float *__restrict__ best_cost, int32_t *__restrict__ best_end,
+                     const int64_t *__restrict__ path_off, int32_t *__restrict__ path_state,
+                     int32_t *__restrict__ path_frame, int32_t *__restrict__ path_len) {
+    extern __shared__ float vsm[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float *prev = vsm + (size_t)warp * 2 * Rmax, *cur = prev + Rmax;
+    const float INF = CUDART_INF_F;
+
+    for (int u = blockIdx.x * VW + warp; u < B; u += gridDim.x * VW) {
+        const int g = G.utt_graph ? G.utt_graph[u] : 0;
+        const int s0 = G.g_state_off[g], R = G.g_state_off[g + 1] - s0;
+        const int n0 = G.g_nes_off[g], K = G.g_nes_off[g + 1] - n0;
+        const int64_t f0 = off[u];
+        const int T = (int)(off[u + 1] - f0);
+        uint8_t *bpu = bp + bp_off[u];
+        float *cu = costs_out ? costs_out + bp_off[u] : nullptr;
+        const int32_t *emit = G.emit + s0, *pptr = G.pred_ptr + s0;
+        if (T <= 0) {
+            if (lane == 0) {
+                best_cost[u] = INF;
+                best_end[u] = -1;
+                path_len[u] = 0;
+            }
+            continue;
+        }
+        for (int r = lane; r < R; r += 32) prev[r] = INF;   // column -1 == the still-untouched last column (A8)
+        __syncwarp();
+        for (int c = 0; c < T; ++c) {
+            const float *Erow = E + (f0 + c) * ldE;
+            uint8_t *bpc = bpu + (size_t)c * R;
+            int lo = 0;
+            for (int k = 0; k <= K; ++k) {
+                const int hi = (k < K) ? G.nes_idx[n0 + k] : R;
+                for (int r = lo + lane; r < hi; r += 32) {        // emitting states of run k
+                    float out;
+                    if (c == 0 && r == 0) {
+                        out = Erow[emit[0]];                       // decode.py:99-100
+                    } else {
+                        const int p0 = pptr[r], p1 = pptr[r + 1];
+                        float best = INF;
+                        int bj = 0;
+                        for (int j = p0; j < p1; ++j) {
+                            const int o = G.pred_idx[j];
+                            const float v = (emit[o] < 0) ? (o < r ? cur[o] : INF) : prev[o];
+                            const float cand = G.pred_cost[j] + v;
+                            if (cand < best) {
+                                best = cand;
+                                bj = j - p0;
+                            }
+                        }
+                        out = (p1 > p0) ? best + Erow[emit[r]] : INF;
+                        bpc[r] = (uint8_t)bj;
+                    }
+                    cur[r] = out;
+                }
+                __syncwarp();
+                if (k < K) {                                       // the NES closing run k: same-column reduce
+                    const int n = hi;
+                    const int p0 = pptr[n], p1 = pptr[n + 1];
+                    if (c == 0 && n == 0) {
+                        if (lane == 0) cur[0] = 0.f;
+                    } else {
+                        float best = INF;
+                        int bj = 0x7fffffff;
+                        for (int j = p0 + lane; j < p1; j += 32) {
+                            const int o = G.pred_idx[j];
+                            const float cand = G.pred_cost[j] + (o < n ? cur[o] : INF);
+                            lexmin(best, bj, cand, j - p0);
+                        }
+#pragma unroll
+                        for (int d = 16; d; d >>= 1) {
+                            const float ov = __shfl_xor_sync(0xffffffffu, best, d);
+                            const int op = __shfl_xor_sync(0xffffffffu, bj, d);
+                            lexmin(best, bj, ov, op);
+                        }
+                        if (lane == 0) {
+                            cur[n] = (p1 > p0) ? best : INF;
+                            bpc[n] = (uint8_t)(p1 > p0 ? bj : 0);
+                        }
+                    }
+                    __syncwarp();
+                    lo = hi + 1;
+                }
+            }
+            if (cu)
+                for (int r = lane; r < R; r += 32) cu[(size_t)c * R + r] = cur[r];
+            float *t = prev;
+            prev = cur;
+            cur = t;
+            __syncwarp();
+        }
+        // ---- best end point: '>=' -> the last listed minimum wins (decode.py:131-134); traceback :142-146
+        if (lane == 0) {
+            float bc = INF;
+            int bi = -1;
+            for (int e = G.g_end_off[g]; e < G.g_end_off[g + 1]; ++e) {
+                const int s = G.end_state[e];
+                if (bc >= prev[s]) {
+                    bc = prev[s];
+                    bi = s;
+                }
+            }
+            best_cost[u] = bc;
+            best_end[u] = bi;
+            int len = 0;
+            if (bc < INF && path_state) {
+                int32_t *ps = path_state + path_off[u], *pf = path_frame + path_off[u];
+                const int cap = (int)(path_off[u + 1] - path_off[u]);
+                int i = bi, j = T - 1;
+                while (j > 0 && len < cap) {
+                    const int code = bpu[(size_t)j * R + i];
+                    const int o = G.pred_idx[pptr[i] + code];
+                    if (!(emit[o] < 0 || emit[i] < 0)) --j;
+                    i = o;
+                    ps[len] = i;
+                    pf[len] = j;
+                    ++len;
+                }
+                if (j > 0) len = -1;   // capacity exhausted
+            }
+            if (path_len) path_len[u] = len;
+        }
+        __syncwarp();
+    }
+}
+
+
+// ------------------------------------------------------------------------------------------------ K4
+// Scaled log-domain forward-backward for NES-free graphs.  Boundary conditions are those of the Viterbi
+// above (start in state 0 at frame 0, end in one of the graph's end states at the last frame); replacing the
+// log-sum-exp by min gives exactly the Viterbi costs (tests tie the two).  Every column is renormalised by
+// its minimum (alpha_hat = alpha - min), the offsets summed in double, so posteriors keep FP32 relative
+// accuracy for paths whose cumulative cost reaches 1e4:
+//     gamma_c(r) = exp(-(alpha_hat_c(r) + beta_hat_c(r))) / sum_r(...)
+//     xi_c(o->r) = exp(-(alpha_hat_{c-1}(o) + tr + E_c(r) + beta_hat_c(r))) / sum_edges(...)
+struct OnlineNegLse {   // accumulates -log(sum exp(-x_i))
+    float m, s;
+    __device__ __forceinline__ void reset() { m = __int_as_float(0x7f800000); s = 0.f; }
+    __device__ __forceinline__ void add(float x) {
+        if (x == CUDART_INF_F) return;
+        if (x < m) {
+            s = s * __expf(x - m) + 1.f;   // m == inf: s == 0 and exp(-inf) == 0
+            m = x;
+        } else {
+            s += __expf(m - x);
+        }
+    }
+    __device__ __forceinline__ float value() const { return s > 0.f ? m - __logf(s) : CUDART_INF_F; }
+};
+
+__device__ __forceinline__ float warp_min(float v) {
+#pragma unroll
+    for (int d = 16; d; d >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, d));
+    return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    return v;
+}
+
+__global__ void __launch_bounds__(VW * 32)
+forward_backward_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *__restrict__ off, int B,
+                        GraphBatch G, const int32_t *__restrict__ succ_ptr, const int32_t *__restrict__ succ_idx,
+                        const float *__restrict__ succ_cost, const int32_t *__restrict__ pred_tgt, int Rmax,
+                        int NNZmax, const int64_t *__restrict__ ws_off, float *__restrict__ gamma,
+                        double *__restrict__ neg_log_z, double *__restrict__ xi_sum) {
+    extern __shared__ float vsm[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float *colA = vsm + (size_t)warp * (2 * Rmax + NNZmax), *colB = colA + Rmax, *xi = colB + Rmax;
+    const float INF = CUDART_INF_F;
+
+    for (int u = blockIdx.x * VW + warp; u < B; u += gridDim.x * VW) {
+        const int g = G.utt_graph ? G.utt_graph[u] : 0;
+        const int s0 = G.g_state_off[g], R = G.g_state_off[g + 1] - s0;
+        const int64_t f0 = off[u];
+        const int T = (int)(off[u + 1] - f0);
+        const int32_t *emit = G.emit + s0, *pptr = G.pred_ptr + s0, *sptr = succ_ptr + s0;
+        const int e0 = pptr[0], nnz = pptr[R] - e0;
+        float *gu = gamma + ws_off[u];
+        if (T <= 0) {
+            if (lane == 0 && neg_log_z) neg_log_z[u] = (double)INF;
+            continue;
+        }
+        // ---- forward
+        float *prev = colA, *cur = colB;
+        double scale = 0.0;
+        for (int c = 0; c < T; ++c) {
+            const float *Erow = E + (f0 + c) * ldE;
+            float mymin = INF;
+            for (int r = lane; r < R; r += 32) {
+                float a;
+                if (c == 0) {
+                    a = (r == 0) ? Erow[emit[0]] : INF;
+                } else {
+                    OnlineNegLse acc; acc.reset();
+                    for (int j = pptr[r]; j < pptr[r + 1]; ++j) acc.add(G.pred_cost[j] + prev[G.pred_idx[j]]);
+                    a = acc.value() + Erow[emit[r]];
+                }
+                cur[r] = a;
+                mymin = fminf(mymin, a);
+            }
+            const float m = warp_min(mymin);
+            const float sub = (m < INF) ? m : 0.f;
+            scale += (double)sub;
+            __syncwarp();
+            for (int r = lane; r < R; r += 32) {
+                const float a = cur[r] - sub;
+                cur[r] = a;
+                gu[(size_t)c * R + r] = a;           // alpha_hat, overwritten by gamma in the backward sweep
+            }
+            __syncwarp();
+            float *t = prev;
+            prev = cur;
+            cur = t;
+        }
+        // log Z over the end states at the last column (prev = alpha_hat_{T-1})
+        OnlineNegLse zacc; zacc.reset();
+        for (int e = G.g_end_off[g] + lane; e < G.g_end_off[g + 1]; e += 32) zacc.add(prev[G.end_state[e]]);
+        float zl = zacc.value();
+        {   // merge the per-lane partial sums: -lse over lanes
+            const float zm = warp_min(zl);
+            const float zs = warp_sum(zl < INF ? __expf(zm - zl) : 0.f);
+            zl = (zm < INF) ? zm - __logf(zs) : INF;
+        }
+        if (lane == 0 && neg_log_z) neg_log_z[u] = (zl < INF) ? scale + (double)zl : (double)INF;
+        // ---- backward; colA/colB now hold beta_hat columns
+        float *bnext = colA, *bcur = colB;
+        for (int j = lane; j < nnz; j += 32) xi[j] = 0.f;
+        for (int r = lane; r < R; r += 32) bnext[r] = INF;
+        __syncwarp();
+        for (int e = G.g_end_off[g] + lane; e < G.g_end_off[g + 1]; e += 32) bnext[G.end_state[e]] = 0.f;
+        __syncwarp();
+        for (int c = T - 1; c >= 0; --c) {
+            // gamma of column c from alpha_hat_c (global) and beta_hat_c (bnext)
+            float gs = 0.f;
+            for (int r = lane; r < R; r += 32) {
+                const float v = gu[(size_t)c * R + r] + bnext[r];
+                const float p = (v < INF) ? __expf(-v) : 0.f;
+                bcur[r] = p;                          // scratch
+                gs += p;
+            }
+            gs = warp_sum(gs);
+            const float inv = gs > 0.f ? 1.f / gs : 0.f;
+            __syncwarp();
+            if (c > 0) {
+                // xi of the transitions into column c (needs alpha_hat_{c-1}, still in global)
+                const float *Erow = E + (f0 + c) * ldE;
+                float xs = 0.f;
+                for (int j = lane; j < nnz; j += 32) {
+                    const int r = pred_tgt[e0 + j];
+                    const int o = G.pred_idx[e0 + j];
+                    const float v = gu[(size_t)(c - 1) * R + o] + G.pred_cost[e0 + j] + Erow[emit[r]] + bnext[r];
+                    const float p = (v < INF) ? __expf(-v) : 0.f;
+                    xs += p;
+                    xi[j] = p;                         // unnormalised, this column only (added below)
+                }
+                xs = warp_sum(xs);
+                const float xinv = xs > 0.f ? 1.f / xs : 0.f;
+                if (xi_sum)
+                    for (int j = lane; j < nnz; j += 32) atomicAdd(xi_sum + e0 + j, (double)(xi[j] * xinv));
+            }
+            for (int r = lane; r < R; r += 32) gu[(size_t)c * R + r] = bcur[r] * inv;
+            __syncwarp();
+            if (c == 0) break;
+            // beta_hat_{c-1}(o) = -lse over successors r of (tr + E_c(r) + beta_hat_c(r)), renormalised
+            const float *Erow = E + (f0 + c) * ldE;
+            float mymin = INF;
+            for (int o = lane; o < R; o += 32) {
+                OnlineNegLse acc; acc.reset();
+                for (int j = sptr[o]; j < sptr[o + 1]; ++j) {
+                    const int r = succ_idx[j];
+                    acc.add(succ_cost[j] + Erow[emit[r]] + bnext[r]);
+                }
+                const float b = acc.value();
+                bcur[o] = b;
+                mymin = fminf(mymin, b);
+            }
+            const float m = warp_min(mymin);
+            const float sub = (m < INF) ? m : 0.f;
+            __syncwarp();
+            for (int o = lane; o < R; o += 32) bcur[o] -= sub;
+            __syncwarp();
+            float *t = bnext;
+            bnext = bcur;
+            bcur = t;
+        }
+        __syncwarp();
+    }
+}
+
+}  // namespace srb
+
+using namespace srb;
+
+extern "C" {
+
+static GraphBatch make_graph(const int32_t *utt_graph, const int32_t *g_state_off, const int32_t *g_nes_off,
+                             const int32_t *g_end_off, const int32_t *emit, const int32_t *pred_ptr,
+                             const int32_t *pred_idx, const float *pred_cost, const int32_t *nes_idx,
+                             const int32_t *end_state) {
+    GraphBatch G;
+    G.utt_graph = utt_graph;
+    G.g_state_off = g_state_off;
+    G.g_nes_off = g_nes_off;
+    G.g_end_off = g_end_off;
+    G.emit = emit;
+    G.pred_ptr = pred_ptr;
+    G.pred_idx = pred_idx;
+    G.pred_cost = pred_cost;
+    G.nes_idx = nes_idx;
+    G.end_state = end_state;
+    return G;
+}
+
+int srb_viterbi_graph(const float *E, int64_t ldE, const int32_t *utt_off, int32_t B, const int32_t *utt_graph,
+                      const int32_t *g_state_off, const int32_t *g_nes_off, const int32_t *g_end_off,
+                      const int32_t *emit, const int32_t *pred_ptr, const int32_t *pred_idx, const float *pred_cost,
+                      const int32_t *nes_idx, const int32_t *end_state, int32_t Rmax, const int64_t *bp_off,
+                      uint8_t *bp, float *costs_out, float *best_cost, int32_t *best_end, const int64_t *path_off,
+                      int32_t *path_state, int32_t *path_frame, int32_t *path_len, void *stream) {
+    SRB_REQUIRE(E && utt_off && g_state_off && g_nes_off && g_end_off && emit && pred_ptr && pred_idx && pred_cost &&
+                    end_state && bp_off && bp && best_cost && best_end,
+                SRB_EINVAL, "srb_viterbi_graph: null pointer");
+    SRB_REQUIRE(!path_state || (path_off && path_frame && path_len), SRB_EINVAL,
+                "srb_viterbi_graph: path_state needs path_off, path_frame and path_len");
+    SRB_REQUIRE(B >= 0 && Rmax > 0 && ldE > 0, SRB_EINVAL, "srb_viterbi_graph: bad sizes");
+    if (B == 0) return SRB_OK;
+    const size_t bytes = (size_t)VW * 2 * Rmax * sizeof(float);
+    SRB_REQUIRE(bytes <= (size_t)smem_optin(), SRB_EUNSUPPORTED, "srb_viterbi_graph: %d states do not fit shared memory",
+                Rmax);
+    SRB_CUDA(cudaFuncSetAttribute(viterbi_graph_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    const int sms = sm_count();
+    int64_t grid = ((int64_t)B + VW - 1) / VW;
+    const int64_t cap = (int64_t)sms * 16;
+    if (grid > cap) grid = cap;
+    GraphBatch G = make_graph(utt_graph, g_state_off, g_nes_off, g_end_off, emit, pred_ptr, pred_idx, pred_cost, nes_idx,
+                              end_state);
+    viterbi_graph_kernel<<<(int)grid, VW * 32, bytes, (cudaStream_t)stream>>>(
+        E, ldE, utt_off, B, G, Rmax, bp_off, bp, costs_out, best_cost, best_end, path_off, path_state, path_frame,
+        path_len);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+int srb_forward_backward(const float *E, int64_t ldE, const int32_t *utt_off, int32_t B, const int32_t *utt_graph,
+                         const int32_t *g_state_off, const int32_t *g_end_off, const int32_t *emit,
+                         const int32_t *pred_ptr, const int32_t *pred_idx, const float *pred_cost,
+                         const int32_t *pred_tgt, const int32_t *succ_ptr, const int32_t *succ_idx,
+                         const float *succ_cost, const int32_t *end_state, int32_t Rmax, int32_t NNZmax,
+                         const int64_t *ws_off, float *gamma, double *neg_log_z, double *xi_sum, void *stream) {
+    SRB_REQUIRE(E && utt_off && g_state_off && g_end_off && emit && pred_ptr && pred_idx && pred_cost && pred_tgt &&
+                    succ_ptr && succ_idx && succ_cost && end_state && ws_off && gamma,
+                SRB_EINVAL, "srb_forward_backward: null pointer");
+    SRB_REQUIRE(B >= 0 && Rmax > 0 && NNZmax >= 0 && ldE > 0, SRB_EINVAL, "srb_forward_backward: bad sizes");
+    if (B == 0) return SRB_OK;
+    const size_t bytes = (size_t)VW * (2 * Rmax + NNZmax) * sizeof(float);
+    SRB_REQUIRE(bytes <= (size_t)smem_optin(), SRB_EUNSUPPORTED, "srb_forward_backward: graph too large for shared memory");
+    SRB_CUDA(cudaFuncSetAttribute(forward_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    const int sms = sm_count();
+    int64_t grid = ((int64_t)B + VW - 1) / VW;
+    const int64_t cap = (int64_t)sms * 16;
+    if (grid > cap) grid = cap;
+    GraphBatch G = make_graph(utt_graph, g_state_off, g_state_off, g_end_off, emit, pred_ptr, pred_idx, pred_cost, nullptr,
+                              end_state);
+    forward_backward_kernel<<<(int)grid, VW * 32, bytes, (cudaStream_t)stream>>>(
+        E, ldE, utt_off, B, G, succ_ptr, succ_idx, succ_cost, pred_tgt, Rmax, NNZmax, ws_off, gamma, neg_log_z, xi_sum);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+}  // extern "C"

@@ -183,3 +183,92 @@ class HostClassifier:
             if self.done[s] is not None:
                 cur.wait_event(self.done[s])
         return labels_out
+
+
+# ------------------------------------------------------------------------------------------------ K2 / K4
+from .graph import GraphBatch, StateGraph  # noqa: E402
+
+
+def _utt_layout(off, gb, utt_graph):
+    """Per-utterance workspace offsets: ws_off[u] = sum_{v<u} T_v * R_{graph(v)} (int64), path capacity offsets."""
+    offn = off.cpu().numpy().astype(np.int64) if torch.is_tensor(off) else np.asarray(off, np.int64)
+    T = np.diff(offn)
+    R = np.diff(gb.state_off.astype(np.int64))
+    nn = np.diff(gb.host["g_nes_off"].astype(np.int64))
+    if utt_graph is None:
+        Ru, Nu = np.full(len(T), R[0]), np.full(len(T), nn[0])
+    else:
+        ug = np.asarray(utt_graph)
+        Ru, Nu = R[ug], nn[ug]
+    ws = np.zeros(len(T) + 1, np.int64)
+    np.cumsum(T * Ru, out=ws[1:])
+    po = np.zeros(len(T) + 1, np.int64)
+    np.cumsum(T + 2 * Nu + 2, out=po[1:])
+    return ws, po
+
+
+class ViterbiResult:
+    """Device outputs of srb_viterbi_graph plus host-side views in the reference's formats."""
+
+    def __init__(self, best_cost, best_end, path_state, path_frame, path_len, path_off, costs, ws_off, bp):
+        self.best_cost, self.best_end = best_cost, best_end
+        self.path_state, self.path_frame, self.path_len, self.path_off = path_state, path_frame, path_len, path_off
+        self.costs, self.ws_off, self.bp = costs, ws_off, bp
+
+    def paths(self):
+        """list of reversed [[state, frame], ...] int64 arrays (decode.py:142-146 format)."""
+        ps, pf = self.path_state.cpu().numpy(), self.path_frame.cpu().numpy()
+        ln = self.path_len.cpu().numpy()
+        out = []
+        for u, n in enumerate(ln):
+            if n < 0:
+                raise RuntimeError("path capacity exhausted")
+            o = self.path_off[u]
+            out.append(np.stack([ps[o:o + n], pf[o:o + n]], axis=1).astype(np.int64))
+        return out
+
+
+def viterbi(E, off, gb, utt_graph=None, want_costs=False, want_path=True):
+    """K2.  E: [N, ldE] float32 CUDA emission costs; off: [B+1] int32; gb: GraphBatch."""
+    dev = E.device
+    offd = as_offsets(off)
+    B = offd.numel() - 1
+    ws, po = _utt_layout(off, gb, utt_graph)
+    ws_d = torch.from_numpy(ws).to(dev)
+    po_d = torch.from_numpy(po).to(dev)
+    ug = None if utt_graph is None else torch.as_tensor(np.asarray(utt_graph, np.int32)).to(dev)
+    bp = torch.empty(max(int(ws[-1]), 1), dtype=torch.uint8, device=dev)
+    costs = torch.empty(max(int(ws[-1]), 1), dtype=torch.float32, device=dev) if want_costs else None
+    bc = torch.empty(B, dtype=torch.float32, device=dev)
+    be = torch.empty(B, dtype=torch.int32, device=dev)
+    ps = torch.empty(max(int(po[-1]), 1), dtype=torch.int32, device=dev) if want_path else None
+    pf = torch.empty(max(int(po[-1]), 1), dtype=torch.int32, device=dev) if want_path else None
+    pl = torch.zeros(B, dtype=torch.int32, device=dev)
+    _l.check(_l.load().srb_viterbi_graph(
+        _l.ptr(E), E.stride(0), _l.ptr(offd), B, _l.ptr(ug), _l.ptr(gb["g_state_off"]), _l.ptr(gb["g_nes_off"]),
+        _l.ptr(gb["g_end_off"]), _l.ptr(gb["emit"]), _l.ptr(gb["pred_ptr"]), _l.ptr(gb["pred_idx"]),
+        _l.ptr(gb["pred_cost"]), _l.ptr(gb["nes_idx"]), _l.ptr(gb["end_state"]), gb.Rmax, _l.ptr(ws_d), _l.ptr(bp),
+        _l.ptr(costs), _l.ptr(bc), _l.ptr(be), _l.ptr(po_d), _l.ptr(ps), _l.ptr(pf), _l.ptr(pl), _l.stream_ptr()))
+    return ViterbiResult(bc, be, ps, pf, pl, po, costs, ws, bp)
+
+
+def forward_backward(E, off, gb, utt_graph=None, want_xi=False):
+    """K4.  -> (gamma flat float32 [sum T*R], ws_off, neg_log_z[B] float64, xi_sum[nnz] float64 or None)."""
+    dev = E.device
+    offd = as_offsets(off)
+    B = offd.numel() - 1
+    if gb.n_nes_max:
+        raise ValueError("forward_backward is defined for NES-free graphs only")
+    ws, _ = _utt_layout(off, gb, utt_graph)
+    ws_d = torch.from_numpy(ws).to(dev)
+    ug = None if utt_graph is None else torch.as_tensor(np.asarray(utt_graph, np.int32)).to(dev)
+    gamma = torch.empty(max(int(ws[-1]), 1), dtype=torch.float32, device=dev)
+    nlz = torch.empty(B, dtype=torch.float64, device=dev)
+    xi = torch.zeros(max(int(gb.edge_off[-1]), 1), dtype=torch.float64, device=dev) if want_xi else None
+    _l.check(_l.load().srb_forward_backward(
+        _l.ptr(E), E.stride(0), _l.ptr(offd), B, _l.ptr(ug), _l.ptr(gb["g_state_off"]), _l.ptr(gb["g_end_off"]),
+        _l.ptr(gb["emit"]), _l.ptr(gb["pred_ptr"]), _l.ptr(gb["pred_idx"]), _l.ptr(gb["pred_cost"]),
+        _l.ptr(gb["pred_tgt"]), _l.ptr(gb["succ_ptr"]), _l.ptr(gb["succ_idx"]), _l.ptr(gb["succ_cost"]),
+        _l.ptr(gb["end_state"]), gb.Rmax, gb.NNZmax, _l.ptr(ws_d), _l.ptr(gamma), _l.ptr(nlz), _l.ptr(xi),
+        _l.stream_ptr()))
+    return gamma, ws, nlz, xi

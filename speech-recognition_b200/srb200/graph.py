@@ -1,0 +1,97 @@
+"""State graphs in the packed CSR form srb_viterbi_graph / srb_forward_backward take (include/srb200.h).
+
+Host-side (numpy) packing of what the reference passes around as a dense `transitions[R, R]` matrix
+(`transitions[i, j]` = cost j -> i, inf = none, decode.py:86-87) plus a list of state objects.
+"""
+import numpy as np
+import torch
+
+
+class StateGraph:
+    """One graph: emit[r] (column of the emission matrix, -1 = NES), CSR predecessors in ascending origin order
+    (decode.py:104-107 iterates origins ascending, so 'first minimum' is preserved), end states."""
+
+    def __init__(self, transitions, emit, end_states=None, keep_inf=False):
+        tr = np.asarray(transitions, dtype=np.float64)
+        R = tr.shape[0]
+        assert tr.shape == (R, R)
+        self.R = R
+        self.emit = np.asarray(emit, dtype=np.int32).reshape(R)
+        # dtw (decode.py:44-51) keeps inf entries as candidates; decode_hmm_states (:106) skips them
+        fin = np.ones_like(tr, dtype=bool) if keep_inf else ~np.isposinf(tr)
+        tgt, org = np.nonzero(fin)                      # row-major: targets ascending, origins ascending within
+        self.pred_ptr = np.zeros(R + 1, np.int32)
+        np.cumsum(np.bincount(tgt, minlength=R), out=self.pred_ptr[1:])
+        self.pred_idx = org.astype(np.int32)
+        self.pred_tgt = tgt.astype(np.int32)
+        self.pred_cost = tr[tgt, org].astype(np.float32)
+        if (np.diff(self.pred_ptr) > 255).any():
+            raise ValueError("a state has more than 255 predecessors (back-pointer codes are 8 bit)")
+        self.nes_idx = np.nonzero(self.emit < 0)[0].astype(np.int32)
+        if end_states is None:
+            end_states = [R - 1]                         # decode.py:126-127
+        self.end_states = np.asarray(end_states, dtype=np.int32).reshape(-1)
+        # successor CSR of the same edges (forward-backward's beta recursion)
+        order = np.lexsort((tgt, org))
+        self.succ_ptr = np.zeros(R + 1, np.int32)
+        np.cumsum(np.bincount(org, minlength=R), out=self.succ_ptr[1:])
+        self.succ_idx = tgt[order].astype(np.int32)
+        self.succ_cost = self.pred_cost[order]
+        self.has_nes_self_loop = bool(any(np.isfinite(tr[n, n]) for n in self.nes_idx))
+
+    @property
+    def nnz(self):
+        return int(self.pred_idx.shape[0])
+
+
+class GraphBatch:
+    """Several StateGraphs packed back to back on the device."""
+
+    def __init__(self, graphs, device):
+        self.graphs = graphs
+        R = [g.R for g in graphs]
+        self.Rmax = max(R)
+        self.NNZmax = max(g.nnz for g in graphs)
+        self.n_nes_max = max(len(g.nes_idx) for g in graphs)
+        self.state_off = np.zeros(len(graphs) + 1, np.int32)
+        np.cumsum(R, out=self.state_off[1:])
+        edge_off = np.zeros(len(graphs) + 1, np.int64)
+        np.cumsum([g.nnz for g in graphs], out=edge_off[1:])
+        self.edge_off = edge_off
+
+        def cat(parts, dtype):
+            return np.concatenate(parts).astype(dtype) if parts else np.zeros(0, dtype)
+
+        def offs(lens):
+            o = np.zeros(len(lens) + 1, np.int32)
+            np.cumsum(lens, out=o[1:])
+            return o
+
+        pred_ptr = cat([g.pred_ptr[:-1].astype(np.int64) + edge_off[i] for i, g in enumerate(graphs)] +
+                       [np.array([edge_off[-1]])], np.int32)
+        succ_ptr = cat([g.succ_ptr[:-1].astype(np.int64) + edge_off[i] for i, g in enumerate(graphs)] +
+                       [np.array([edge_off[-1]])], np.int32)
+        host = {
+            "g_state_off": self.state_off,
+            "g_nes_off": offs([len(g.nes_idx) for g in graphs]),
+            "g_end_off": offs([len(g.end_states) for g in graphs]),
+            "emit": cat([g.emit for g in graphs], np.int32),
+            "pred_ptr": pred_ptr,
+            "pred_idx": cat([g.pred_idx for g in graphs], np.int32),
+            "pred_tgt": cat([g.pred_tgt for g in graphs], np.int32),
+            "pred_cost": cat([g.pred_cost for g in graphs], np.float32),
+            "nes_idx": cat([g.nes_idx for g in graphs], np.int32),
+            "end_state": cat([g.end_states for g in graphs], np.int32),
+            "succ_ptr": succ_ptr,
+            "succ_idx": cat([g.succ_idx for g in graphs], np.int32),
+            "succ_cost": cat([g.succ_cost for g in graphs], np.float32),
+        }
+        self.host = host
+        self.dev = {}
+        for k, v in host.items():
+            if v.size == 0:                              # keep a valid pointer for empty arrays
+                v = np.zeros(1, v.dtype)
+            self.dev[k] = torch.from_numpy(v).to(device)
+
+    def __getitem__(self, k):
+        return self.dev[k]

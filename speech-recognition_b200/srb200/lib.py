@@ -19,6 +19,9 @@ SIGNATURES = {
                               c_void_p, c_void_p, c_void_p, c_void_p]),
     "srb_classify": (c_int, [c_void_p, c_void_p, c_i32, c_i64, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int,
                              c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "srb_viterbi_graph": (c_int, [c_void_p, c_i64, c_void_p, c_i32] + [c_void_p] * 10 + [c_i32] + [c_void_p] * 10),
+    "srb_forward_backward": (c_int, [c_void_p, c_i64, c_void_p, c_i32] + [c_void_p] * 12 + [c_i32, c_i32] +
+                             [c_void_p] * 5),
     "srb_fma_peak": (c_int, [c_int, c_int, ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_double), c_void_p]),
 }
 

@@ -1,0 +1,155 @@
+"""GPU parity: K2 graph Viterbi (decode_hmm_states / dtw) and K4 forward-backward against the oracle and the
+frozen reference outputs, through the C ABI."""
+import numpy as np
+import pytest
+
+from conftest import unragged
+from oracle import oracle as orc
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-4
+
+
+@pytest.fixture(scope="module")
+def eng():
+    from srb200 import engine
+    return engine
+
+
+def models_from(mu, cov, w, tr):
+    return [(mu[i], cov[i], w[i], tr[i]) for i in range(mu.shape[0])]
+
+
+def dev_E(eng, X, models):
+    pm, _ = eng.PackedModel.from_words(models)
+    return eng.gmm_score(X.astype(np.float32), pm)["E"]
+
+
+def check_costs(costs_flat, ws, off, R, ref_list):
+    c = costs_flat.cpu().numpy()
+    for u, ref in enumerate(ref_list):                     # ref: [T, R]
+        got = c[ws[u]:ws[u + 1]].reshape(-1, R)
+        f = np.isfinite(ref)
+        assert np.array_equal(np.isfinite(got), f)
+        np.testing.assert_allclose(got[f], ref[f], rtol=RTOL)
+
+
+def test_isolated_decode_golden(eng, golden):
+    """decode_hmm_states on 5 utterances x 3 isolated models: costs and paths frozen from the reference."""
+    from srb200.graph import GraphBatch, StateGraph
+    g = golden["decode"]
+    models = models_from(g["iso_mu"], g["iso_cov"], g["iso_w"], g["iso_trans"])
+    E = dev_E(eng, g["iso_X"], models)                     # [N, 15]
+    rc = unragged(g["iso_costs"], g["iso_costs_off"])
+    rp = unragged(g["iso_paths"], g["iso_paths_off"])
+    B = len(g["iso_off"]) - 1
+    for w, m in enumerate(models):
+        gb = GraphBatch([StateGraph(m[3], np.arange(5) + 5 * w)], E.device)
+        res = eng.viterbi(E, g["iso_off"].astype(np.int32), gb, want_costs=True)
+        check_costs(res.costs, res.ws_off, g["iso_off"], 5, [rc[u * 3 + w] for u in range(B)])
+        for u, p in enumerate(res.paths()):
+            assert np.array_equal(p, rp[u * 3 + w])
+        np.testing.assert_allclose(res.best_cost.cpu().numpy(), g["iso_final"][:, w], rtol=RTOL)
+
+
+def test_graph_decode_golden(eng, golden):
+    """Word-loop graph with NES (build_state_sequences) and per-utterance forced-alignment chains."""
+    from srb200.graph import GraphBatch, StateGraph
+    g = golden["decode"]
+    models = models_from(g["iso_mu"], g["iso_cov"], g["iso_w"], g["iso_trans"])
+    E = dev_E(eng, g["gr_X"], models)
+    off = g["gr_off"].astype(np.int32)
+    gb = GraphBatch([StateGraph(g["gr_trans"], g["gr_emit"], g["gr_ends"])], E.device)
+    res = eng.viterbi(E, off, gb, want_costs=True)
+    check_costs(res.costs, res.ws_off, off, 49, unragged(g["gr_costs"], g["gr_costs_off"]))
+    rp = unragged(g["gr_paths"], g["gr_paths_off"])
+    for u, p in enumerate(res.paths()):
+        assert np.array_equal(p, rp[u])
+        assert orc.path_to_words(p, g["gr_emit"], 5) == list(g["gr_strings"][u])
+    # forced alignment: one chain graph per utterance (continuous_speech.py:80,89)
+    graphs = [StateGraph(g["fa_trans"][i], g["fa_emit"][i], g["fa_ends"][i]) for i in range(2)]
+    gb = GraphBatch(graphs, E.device)
+    res = eng.viterbi(E, off, gb, utt_graph=[0, 1], want_costs=True)
+    check_costs(res.costs, res.ws_off, off, 19, unragged(g["fa_costs"], g["fa_costs_off"]))
+    fp = unragged(g["fa_paths"], g["fa_paths_off"])
+    for u, p in enumerate(res.paths()):
+        assert np.array_equal(p, fp[u])
+
+
+def test_digit_loop_graph_vs_oracle(eng):
+    """Config-4 shape: 7 layers x 11 words x 5 states = 393 states, ragged utterances."""
+    from srb200 import synth
+    from srb200.graph import GraphBatch, StateGraph
+    models, base = synth.make_models(31, W=11, S=5, M=4)
+    rng = np.random.default_rng(7)
+    utts = []
+    for _ in range(4):
+        digits = rng.integers(0, 11, size=7)
+        parts = [synth.make_utterances(int(rng.integers(1 << 30)), base[d:d + 1], 1, T=int(rng.integers(12, 25)))[0]
+                 for d in digits]
+        utts.append(np.concatenate(parts))
+    X = np.concatenate(utts)
+    off = np.concatenate([[0], np.cumsum([len(u) for u in utts])]).astype(np.int32)
+    emit, trans, ends = orc.build_state_sequences(5, [m[3] for m in models], [list(range(11))] * 7)
+    assert len(emit) == 393
+    E = dev_E(eng, X, models)
+    gb = GraphBatch([StateGraph(trans, emit, ends)], E.device)
+    res = eng.viterbi(E, off, gb)
+    paths = res.paths()
+    bc = res.best_cost.cpu().numpy()
+    for u, x in enumerate(utts):
+        Eo = orc.emissions(x, models, emit, log_domain=True)
+        costs, path, best = orc.decode_hmm_states(Eo, trans, emit < 0, [[e, -1] for e in ends])
+        ref = costs[best[0], best[1]]
+        np.testing.assert_allclose(bc[u], ref, rtol=RTOL)
+        if not np.array_equal(paths[u], path):             # only inside the decision margin
+            assert abs(bc[u] - ref) <= 1e-5 * abs(ref)
+        assert orc.path_to_words(paths[u], emit, 5) == orc.path_to_words(path, emit, 5)
+
+
+def test_dtw_golden(eng, golden):
+    """dtw (decode.py:7-77) == the same kernel on local distances with inf transitions kept as candidates."""
+    import torch
+    from srb200.graph import GraphBatch, StateGraph
+    g = golden["dtw_helpers"]
+    xs = unragged(g["dtw_X"], g["dtw_off"])
+    off = g["dtw_off"].astype(np.int32)
+    for nm, var in (("dtw_e", None), ("dtw_m", g["dtw_var"])):
+        Dl = np.concatenate([orc.local_dist(x, g["dtw_y"], var) for x in xs]).astype(np.float32)
+        E = torch.from_numpy(Dl).cuda()
+        gb = GraphBatch([StateGraph(g["dtw_trans"], np.arange(5), keep_inf=True)], E.device)
+        res = eng.viterbi(E, off, gb, want_costs=True)
+        check_costs(res.costs, res.ws_off, off, 5, unragged(g[nm + "_costs"], g[nm + "_costs_off"]))
+        rp = unragged(g[nm + "_paths"], g[nm + "_paths_off"])
+        for u, p in enumerate(res.paths()):
+            assert np.array_equal(p, rp[u])
+
+
+@pytest.mark.parametrize("S,M", [(5, 4), (8, 16)])
+def test_forward_backward_vs_oracle(eng, S, M):
+    from srb200 import synth
+    from srb200.graph import GraphBatch, StateGraph
+    models, base = synth.make_models(41, W=3, S=S, M=M)
+    X, off, words = synth.make_utterances(42, base, 12, ragged=(S + 3, 90))
+    E = dev_E(eng, X, models)
+    graphs = [StateGraph(m[3], np.arange(S) + S * w) for w, m in enumerate(models)]
+    gb = GraphBatch(graphs, E.device)
+    gamma, ws, nlz, xi = eng.forward_backward(E, off, gb, utt_graph=words.astype(np.int32), want_xi=True)
+    gamma, nlz, xi = gamma.cpu().numpy(), nlz.cpu().numpy(), xi.cpu().numpy()
+    xi_ref = np.zeros_like(xi)
+    for u in range(len(off) - 1):
+        x = X[off[u]:off[u + 1]].astype(np.float64)
+        m = models[words[u]]
+        Eo = orc.emissions(x, [m], np.arange(S), log_domain=True)
+        z, a, b, go = orc.forward_backward(Eo, m[3])
+        np.testing.assert_allclose(nlz[u], z, rtol=1e-5)
+        got = gamma[ws[u]:ws[u + 1]].reshape(-1, S)
+        np.testing.assert_allclose(got, go, rtol=2e-3, atol=2e-5)
+        np.testing.assert_allclose(got.sum(axis=1), 1.0, rtol=1e-5)
+        sg = graphs[words[u]]
+        e0 = gb.edge_off[words[u]]
+        for j in range(sg.nnz):
+            o, r = sg.pred_idx[j], sg.pred_tgt[j]
+            v = a[:-1, o] + m[3][r, o] + Eo[1:, r] + b[1:, r] - z
+            xi_ref[e0 + j] += np.exp(-v).sum()
+    np.testing.assert_allclose(xi, xi_ref, rtol=2e-3, atol=1e-4)
