@@ -109,6 +109,44 @@ int srb_forward_backward(const float *E, int64_t ldE, const int32_t *utt_off, in
                          const float *succ_cost, const int32_t *end_state, int32_t Rmax, int32_t NNZmax,
                          const int64_t *ws_off, float *gamma, double *neg_log_z, double *xi_sum, void *stream);
 
+
+/* ---- K5 / K6: sufficient statistics, K-means assignment, M-step ---------------------------------
+ * Statistics row of one group (Gaussian / segment / cluster), srb_stats_row(D) = 2*D + 3 doubles:
+ *   [S0, S1[0..D), S2[0..D), count, loglik]   S1, S2 = first / second moments about the group's shift vector.
+ * `partial` is caller-owned scratch of srb_stats_parts() * groups * srb_stats_row(D) floats (one private slice
+ * per accumulating warp: no atomics); the slices are summed in a fixed order in double into `out`
+ * (accumulate != 0 adds to `out`), so the result does not depend on scheduling and can be allreduced as is. */
+int srb_stats_row(int D);
+int srb_stats_parts(void);
+
+/* moments of the frames of each group: label[n] in [0,K) or < 0 to skip; shift double[K,D].
+ * Replaces segment_data/combine_templates (kmeans.py:15-50), calc_variance (kmeans.py:6-12: unbiased variance
+ * = (S2 - S1^2/S0)/(S0-1)), cluster_centroids and the centroid update (kmeans.py:158-164,187). */
+int srb_group_stats(const float *X, int64_t N, int D, const int32_t *label, int K, const double *shift,
+                    float *partial, double *out, int accumulate, void *stream);
+
+/* E-step of GMM.em (hmm_state.py:122-136) for frames hard-aligned to tied states: label[n] = state in [0,R)
+ * (< 0: skip); posteriors over the FIRST ncomp components of the state (hmm.py:104-124 trains 2^i of them),
+ * computed in the log domain (no underflow rows); shift = the component's current mean.
+ * mu/var double[R*M,D], lc double[R*M] from srb_gauss_consts.  ncomp <= 8.  out: double[R*M, row]. */
+int srb_gmm_stats(const float *X, int64_t N, int D, const int32_t *label, int R, int M, int ncomp, const double *mu,
+                  const double *var, const double *lc, float *partial, double *out, int accumulate, void *stream);
+
+/* local distances to S templates Y double[S,D]: kind 0 = Euclidean norm (kmeans.py:111), kind 1 =
+ * mahalanobis(x, y_s, var_s) (hmm_state.py:48-58) with var double[S, var_stride>=D or 0 for one shared row]
+ * (kmeans.py:183 uses cov[0] for every centroid -> var_stride 0).  out float[N,ldo] and/or argmin_out int32[N]
+ * (first minimum, kmeans.py:185). */
+int srb_local_dist(const float *X, int64_t N, int D, const double *Y, const double *var, int S, int kind,
+                   int var_stride, float *out, int64_t ldo, int32_t *argmin_out, void *stream);
+
+/* M-step of GMM.em (hmm_state.py:138-148) in place on mu/var/w double (first ncomp components per state):
+ * mu += S1/S0, var = S2/S0 - (S1/S0)^2 (floored at var_floor), w = S0/count. */
+int srb_mstep(const double *stats, int R, int M, int ncomp, int D, double *mu, double *var, double *w,
+              double var_floor, void *stream);
+
+/* lc[g] = log w_g - 0.5*(D log 2pi + sum_d log var[g,d])  (natural log) */
+int srb_gauss_consts(const double *var, const double *w, int G, int D, double *lc, void *stream);
+
 /* ---- FP32 FMA peak probe (roofline denominator for K1; not part of the reference path) ----------
  * Runs `iters` dependent-chain-free FMA rounds per thread on every SM and returns elapsed ms through
  * *ms_out (host pointer) plus the FMA count (host pointer).  packed != 0 uses fma.rn.f32x2. */

@@ -1,0 +1,357 @@
+// stats.cu -- K5: sufficient-statistic accumulation (hard alignment + within-state posteriors, GMM.em
+// hmm_state.py:122-148; segment / cluster moments, kmeans.py:6-30,173-187), K6: K-means assignment,
+// the deterministic partial-sum reduction and the M-step.
+//
+// Accumulation layout: one warp walks a contiguous chunk of frames with the LANES OVER THE FEATURE DIMENSIONS
+// (d = lane and lane + 32, D <= 64).  Frames aligned to the same group (tied state / segment / cluster) form
+// runs; the moments of the current run live in registers and are flushed to the warp's PRIVATE slice of a
+// partial buffer when the group changes -- no atomics anywhere.  A second kernel adds the slices in a fixed
+// order in double, which makes the result independent of scheduling (and ready for the NCCL allreduce).
+//
+// Moments are taken about a per-group shift vector (the Gaussian's current mean / the current centroid) so
+// that  var = S2/S0 - (S1/S0)^2  does not cancel in FP32:  S0 = sum g, S1 = sum g (x - shift), S2 = sum g (x - shift)^2.
+// Row layout of one group in every buffer:  [S0, S1[0..D), S2[0..D), count, loglik]  = 2*D + 3 values
+// (count / loglik: frames and summed log-likelihood of the state, kept on its component 0 only).
+#include "common.cuh"
+
+namespace srb {
+
+constexpr int SW = 8;          // warps per CTA
+constexpr int SCH = 128;       // frames per warp chunk
+constexpr int MAXC = 8;        // components per state handled in registers by the GMM mode
+
+__device__ __forceinline__ float wsum(float v) {
+#pragma unroll
+    for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    return v;
+}
+
+// ---- group moments: label[n] in [0, K) (or < 0: skip), weight 1
+__global__ void __launch_bounds__(SW * 32)
+group_stats_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t *__restrict__ label, int K,
+                   const double *__restrict__ shift, float *__restrict__ partial) {
+    const int lane = threadIdx.x & 31;
+    const int64_t wg = (int64_t)blockIdx.x * SW + (threadIdx.x >> 5), nw = (int64_t)gridDim.x * SW;
+    const int row = 2 * D + 3;
+    float *mine = partial + (size_t)wg * K * row;
+    const int d0 = lane, d1 = lane + 32;
+    const bool h0 = d0 < D, h1 = d1 < D;
+    for (int64_t c0 = wg * SCH; c0 < N; c0 += nw * SCH) {
+        const int64_t c1 = min(N, c0 + SCH);
+        int curg = -1;
+        float s0 = 0.f, a0 = 0.f, a1 = 0.f, q0 = 0.f, q1 = 0.f, sh0 = 0.f, sh1 = 0.f;
+        for (int64_t n = c0; n <= c1; ++n) {
+            const int g = (n < c1) ? label[n] : -2;
+            if (g != curg) {
+                if (curg >= 0) {   // flush the run
+                    float *r = mine + (size_t)curg * row;
+                    if (lane == 0) r[0] += s0;
+                    if (h0) {
+                        r[1 + d0] += a0;
+                        r[1 + D + d0] += q0;
+                    }
+                    if (h1) {
+                        r[1 + d1] += a1;
+                        r[1 + D + d1] += q1;
+                    }
+                }
+                curg = g;
+                s0 = a0 = a1 = q0 = q1 = 0.f;
+                if (g >= 0) {
+                    sh0 = h0 ? (float)shift[(size_t)g * D + d0] : 0.f;
+                    sh1 = h1 ? (float)shift[(size_t)g * D + d1] : 0.f;
+                }
+            }
+            if (g >= 0) {
+                const float *x = X + n * D;
+                const float x0 = h0 ? x[d0] - sh0 : 0.f, x1 = h1 ? x[d1] - sh1 : 0.f;
+                s0 += 1.f;
+                a0 += x0;
+                a1 += x1;
+                q0 = fmaf(x0, x0, q0);
+                q1 = fmaf(x1, x1, q1);
+            }
+        }
+    }
+}
+
+// ---- GMM mode: label[n] = tied state s; groups are the first ncomp components of s, weights are the
+// within-state posteriors  p_m = w_m N_m(x) / sum_{m' < ncomp} w_m' N_m'(x)  (hmm_state.py:126-136, log domain).
+__global__ void __launch_bounds__(SW * 32)
+gmm_stats_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t *__restrict__ label, int M, int ncomp,
+                 const double *__restrict__ mu, const double *__restrict__ var, const double *__restrict__ lc,
+                 float *__restrict__ partial, int G) {
+    const int lane = threadIdx.x & 31;
+    const int64_t wg = (int64_t)blockIdx.x * SW + (threadIdx.x >> 5), nw = (int64_t)gridDim.x * SW;
+    const int row = 2 * D + 3;
+    float *mine = partial + (size_t)wg * G * row;
+    const int d0 = lane, d1 = lane + 32;
+    const bool h0 = d0 < D, h1 = d1 < D;
+    float m0[MAXC], m1[MAXC], v0[MAXC], v1[MAXC], cst[MAXC];
+    float s0[MAXC], a0[MAXC], a1[MAXC], q0[MAXC], q1[MAXC];
+    for (int64_t c0 = wg * SCH; c0 < N; c0 += nw * SCH) {
+        const int64_t c1 = min(N, c0 + SCH);
+        int curs = -1;
+        float cnt = 0.f, llsum = 0.f;
+        for (int64_t n = c0; n <= c1; ++n) {
+            const int s = (n < c1) ? label[n] : -2;
+            if (s != curs) {
+                if (curs >= 0) {
+#pragma unroll
+                    for (int m = 0; m < MAXC; ++m) {
+                        if (m < ncomp) {
+                            float *r = mine + ((size_t)curs * M + m) * row;
+                            if (lane == 0) {
+                                r[0] += s0[m];
+                                if (m == 0) {
+                                    r[2 * D + 1] += cnt;
+                                    r[2 * D + 2] += llsum;
+                                }
+                            }
+                            if (h0) {
+                                r[1 + d0] += a0[m];
+                                r[1 + D + d0] += q0[m];
+                            }
+                            if (h1) {
+                                r[1 + d1] += a1[m];
+                                r[1 + D + d1] += q1[m];
+                            }
+                        }
+                    }
+                }
+                curs = s;
+                cnt = llsum = 0.f;
+                if (s >= 0) {
+#pragma unroll
+                    for (int m = 0; m < MAXC; ++m) {
+                        s0[m] = a0[m] = a1[m] = q0[m] = q1[m] = 0.f;
+                        if (m < ncomp) {
+                            const size_t g = (size_t)s * M + m;
+                            m0[m] = h0 ? (float)mu[g * D + d0] : 0.f;
+                            m1[m] = h1 ? (float)mu[g * D + d1] : 0.f;
+                            v0[m] = h0 ? (float)(-0.5 / var[g * D + d0]) : 0.f;
+                            v1[m] = h1 ? (float)(-0.5 / var[g * D + d1]) : 0.f;
+                            cst[m] = (float)lc[g];
+                        }
+                    }
+                }
+            }
+            if (s >= 0) {
+                const float *x = X + n * D;
+                const float xa = h0 ? x[d0] : 0.f, xb = h1 ? x[d1] : 0.f;
+                float ll[MAXC], e0[MAXC], e1[MAXC];
+                float mx = -CUDART_INF_F;
+#pragma unroll
+                for (int m = 0; m < MAXC; ++m) {
+                    if (m < ncomp) {
+                        e0[m] = xa - m0[m];
+                        e1[m] = xb - m1[m];
+                        const float part = e0[m] * e0[m] * v0[m] + e1[m] * e1[m] * v1[m];
+                        ll[m] = wsum(part) + cst[m];
+                        mx = fmaxf(mx, ll[m]);
+                    }
+                }
+                float den = 0.f;
+#pragma unroll
+                for (int m = 0; m < MAXC; ++m)
+                    if (m < ncomp) {
+                        ll[m] = __expf(ll[m] - mx);
+                        den += ll[m];
+                    }
+                const float inv = 1.f / den;
+                cnt += 1.f;
+                llsum += mx + __logf(den);
+#pragma unroll
+                for (int m = 0; m < MAXC; ++m)
+                    if (m < ncomp) {
+                        const float p = ll[m] * inv;
+                        s0[m] += p;
+                        a0[m] = fmaf(p, e0[m], a0[m]);
+                        a1[m] = fmaf(p, e1[m], a1[m]);
+                        q0[m] = fmaf(p * e0[m], e0[m], q0[m]);
+                        q1[m] = fmaf(p * e1[m], e1[m], q1[m]);
+                    }
+            }
+        }
+    }
+}
+
+// out[i] (+)= sum_p partial[p][i]  in double, fixed order
+__global__ void reduce_partials_kernel(const float *__restrict__ partial, int64_t nparts, int64_t len,
+                                       double *__restrict__ out, int accumulate) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= len) return;
+    double s = accumulate ? out[i] : 0.0;
+    for (int64_t p = 0; p < nparts; ++p) s += (double)partial[p * len + i];
+    out[i] = s;
+}
+
+
+// ---- local distances of every frame to S templates (dtw's dist_fun, kmeans' mahalanobis):
+// kind 0: ||x - y_s||_2 (kmeans.py:111 default np.linalg.norm)
+// kind 1: mahalanobis(x, y_s, var_s) = 0.5*log((2 pi)^D prod var) + 0.5*sum (x-y)^2/var  (hmm_state.py:48-58)
+// One warp per frame group, lanes over dims, templates in shared memory (double -> float once per CTA).
+__global__ void __launch_bounds__(SW * 32)
+local_dist_kernel(const float *__restrict__ X, int64_t N, int D, const double *__restrict__ Y,
+                  const double *__restrict__ var, int S, int kind, int var_stride, float *__restrict__ out,
+                  int64_t ldo, int32_t *__restrict__ argmin_out) {
+    extern __shared__ float lsm[];
+    float *ys = lsm, *iv = ys + (size_t)S * D, *cs = iv + (size_t)S * D;   // S*D, S*D, S
+    for (int i = threadIdx.x; i < S * D; i += blockDim.x) {
+        ys[i] = (float)Y[i];
+        iv[i] = (kind == 1) ? (float)(0.5 / var[(size_t)(i / D) * var_stride + (i % D)]) : 1.f;
+    }
+    for (int s = threadIdx.x; s < S; s += blockDim.x) {
+        double c = 0.0;
+        if (kind == 1) {
+            for (int d = 0; d < D; ++d) c += log(var[(size_t)s * var_stride + d]);
+            c = 0.5 * (c + (double)D * 1.8378770664093454836);
+        }
+        cs[s] = (float)c;
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int64_t wg = (int64_t)blockIdx.x * SW + (threadIdx.x >> 5), nw = (int64_t)gridDim.x * SW;
+    const int d0 = lane, d1 = lane + 32;
+    const bool h0 = d0 < D, h1 = d1 < D;
+    for (int64_t n = wg; n < N; n += nw) {
+        const float xa = h0 ? X[n * D + d0] : 0.f, xb = h1 ? X[n * D + d1] : 0.f;
+        float best = CUDART_INF_F;
+        int bi = 0;
+        for (int s = 0; s < S; ++s) {
+            float p = 0.f;
+            if (h0) {
+                const float e = xa - ys[s * D + d0];
+                p = e * e * iv[s * D + d0];
+            }
+            if (h1) {
+                const float e = xb - ys[s * D + d1];
+                p = fmaf(e * e, iv[s * D + d1], p);
+            }
+            p = wsum(p);
+            const float dist = (kind == 1) ? p + cs[s] : sqrtf(p);
+            if (out && lane == 0) out[n * ldo + s] = dist;
+            if (dist < best) {             // np.argmin: first minimum (kmeans.py:185)
+                best = dist;
+                bi = s;
+            }
+        }
+        if (argmin_out && lane == 0) argmin_out[n] = bi;
+    }
+}
+
+// ---- M-step of GMM.em (hmm_state.py:138-148) from the reduced moments, for the first ncomp components of
+// every state:  mu' = mu + S1/S0;  var' = S2/S0 - (S1/S0)^2  (== sum p (x-mu')^2 / sum p);  w' = S0 / count.
+// Components with S0 == 0 are left untouched (the reference would divide by zero there).
+__global__ void mstep_kernel(const double *__restrict__ stats, int R, int M, int ncomp, int D, double *__restrict__ mu,
+                             double *__restrict__ var, double *__restrict__ w, double var_floor) {
+    const int row = 2 * D + 3;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;   // (state, comp, d)
+    if (idx >= R * ncomp * D) return;
+    const int d = idx % D, m = (idx / D) % ncomp, s = idx / (D * ncomp);
+    const size_t g = (size_t)s * M + m;
+    const double *r = stats + g * row;
+    const double S0 = r[0];
+    if (!(S0 > 0.0)) return;
+    const double m1 = r[1 + d] / S0;
+    double v = r[1 + D + d] / S0 - m1 * m1;
+    if (v < var_floor) v = var_floor;
+    mu[g * D + d] += m1;
+    var[g * D + d] = v;
+    if (d == 0) {
+        const double cnt = stats[((size_t)s * M) * row + 2 * D + 1];
+        if (cnt > 0.0) w[g] = S0 / cnt;
+    }
+}
+
+// natural-log constants  lc[g] = log w - 0.5*(D log 2pi + sum log var)  (hmm_state.py:39-40 in the log domain)
+__global__ void gauss_consts_kernel(const double *__restrict__ var, const double *__restrict__ w, int G, int D,
+                                    double *__restrict__ lc) {
+    const int g = blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= G) return;
+    double ld = 0.0;
+    for (int d = 0; d < D; ++d) ld += log(var[(size_t)g * D + d]);
+    lc[g] = (w[g] > 0.0 ? log(w[g]) : -CUDART_INF) - 0.5 * ((double)D * 1.8378770664093454836 + ld);
+}
+
+}  // namespace srb
+
+using namespace srb;
+
+extern "C" {
+
+int srb_stats_row(int D) { return 2 * D + 3; }
+
+int srb_stats_parts(void) { return sm_count() * 2 * SW; }   // private slices (one per accumulating warp)
+
+static int stats_grid() { return sm_count() * 2; }
+
+int srb_group_stats(const float *X, int64_t N, int D, const int32_t *label, int K, const double *shift,
+                    float *partial, double *out, int accumulate, void *stream) {
+    SRB_REQUIRE(X && label && shift && partial && out, SRB_EINVAL, "srb_group_stats: null pointer");
+    SRB_REQUIRE(N >= 0 && D > 0 && D <= 64 && K > 0, SRB_EINVAL, "srb_group_stats: bad N/D/K");
+    const int grid = stats_grid();
+    SRB_REQUIRE(grid > 0, SRB_ENODEVICE, "no CUDA device");
+    const int64_t len = (int64_t)K * (2 * D + 3), parts = (int64_t)grid * SW;
+    cudaStream_t st = (cudaStream_t)stream;
+    SRB_CUDA(cudaMemsetAsync(partial, 0, sizeof(float) * len * parts, st));
+    if (N > 0) group_stats_kernel<<<grid, SW * 32, 0, st>>>(X, N, D, label, K, shift, partial);
+    reduce_partials_kernel<<<(int)((len + 255) / 256), 256, 0, st>>>(partial, parts, len, out, accumulate);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+int srb_gmm_stats(const float *X, int64_t N, int D, const int32_t *label, int R, int M, int ncomp, const double *mu,
+                  const double *var, const double *lc, float *partial, double *out, int accumulate, void *stream) {
+    SRB_REQUIRE(X && label && mu && var && lc && partial && out, SRB_EINVAL, "srb_gmm_stats: null pointer");
+    SRB_REQUIRE(N >= 0 && D > 0 && D <= 64 && R > 0 && M > 0, SRB_EINVAL, "srb_gmm_stats: bad N/D/R/M");
+    SRB_REQUIRE(ncomp >= 1 && ncomp <= M && ncomp <= MAXC, SRB_EUNSUPPORTED,
+                "srb_gmm_stats: ncomp=%d outside 1..min(M,%d)", ncomp, MAXC);
+    const int grid = stats_grid();
+    SRB_REQUIRE(grid > 0, SRB_ENODEVICE, "no CUDA device");
+    const int G = R * M;
+    const int64_t len = (int64_t)G * (2 * D + 3), parts = (int64_t)grid * SW;
+    cudaStream_t st = (cudaStream_t)stream;
+    SRB_CUDA(cudaMemsetAsync(partial, 0, sizeof(float) * len * parts, st));
+    if (N > 0) gmm_stats_kernel<<<grid, SW * 32, 0, st>>>(X, N, D, label, M, ncomp, mu, var, lc, partial, G);
+    reduce_partials_kernel<<<(int)((len + 255) / 256), 256, 0, st>>>(partial, parts, len, out, accumulate);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+int srb_local_dist(const float *X, int64_t N, int D, const double *Y, const double *var, int S, int kind,
+                   int var_stride, float *out, int64_t ldo, int32_t *argmin_out, void *stream) {
+    SRB_REQUIRE(X && Y && (out || argmin_out), SRB_EINVAL, "srb_local_dist: null pointer");
+    SRB_REQUIRE(kind == 0 || (kind == 1 && var), SRB_EINVAL, "srb_local_dist: kind 1 needs var");
+    SRB_REQUIRE(N >= 0 && D > 0 && D <= 64 && S > 0 && (!out || ldo >= S), SRB_EINVAL, "srb_local_dist: bad sizes");
+    if (N == 0) return SRB_OK;
+    const size_t bytes = sizeof(float) * ((size_t)2 * S * D + S);
+    SRB_REQUIRE(bytes <= (size_t)smem_optin(), SRB_EUNSUPPORTED, "srb_local_dist: %d templates do not fit shared memory", S);
+    SRB_CUDA(cudaFuncSetAttribute(local_dist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    int64_t grid = (N + SW - 1) / SW;
+    const int64_t cap = (int64_t)sm_count() * 8;
+    if (grid > cap) grid = cap;
+    local_dist_kernel<<<(int)grid, SW * 32, bytes, (cudaStream_t)stream>>>(X, N, D, Y, var, S, kind, var_stride, out,
+                                                                          ldo, argmin_out);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+int srb_mstep(const double *stats, int R, int M, int ncomp, int D, double *mu, double *var, double *w,
+              double var_floor, void *stream) {
+    SRB_REQUIRE(stats && mu && var && w, SRB_EINVAL, "srb_mstep: null pointer");
+    SRB_REQUIRE(R > 0 && M > 0 && ncomp >= 1 && ncomp <= M && D > 0, SRB_EINVAL, "srb_mstep: bad sizes");
+    const int n = R * ncomp * D;
+    mstep_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(stats, R, M, ncomp, D, mu, var, w, var_floor);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+int srb_gauss_consts(const double *var, const double *w, int G, int D, double *lc, void *stream) {
+    SRB_REQUIRE(var && w && lc && G > 0 && D > 0, SRB_EINVAL, "srb_gauss_consts: bad argument");
+    gauss_consts_kernel<<<(G + 127) / 128, 128, 0, (cudaStream_t)stream>>>(var, w, G, D, lc);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+}  // extern "C"

@@ -272,3 +272,99 @@ def forward_backward(E, off, gb, utt_graph=None, want_xi=False):
         _l.ptr(gb["end_state"]), gb.Rmax, gb.NNZmax, _l.ptr(ws_d), _l.ptr(gamma), _l.ptr(nlz), _l.ptr(xi),
         _l.stream_ptr()))
     return gamma, ws, nlz, xi
+
+
+# ------------------------------------------------------------------------------------------------ K5 / K6
+_scratch = {}
+
+
+def _partial(groups, D, dev):
+    """Caller-owned scratch for the per-warp private slices (grown on demand, reused across calls)."""
+    L = _l.load()
+    need = L.srb_stats_parts() * groups * L.srb_stats_row(D)
+    key = (dev.index, "partial")
+    buf = _scratch.get(key)
+    if buf is None or buf.numel() < need:
+        buf = torch.empty(need, dtype=torch.float32, device=dev)
+        _scratch[key] = buf
+    return buf
+
+
+def _f64(a, dev):
+    if torch.is_tensor(a):
+        return a.to(dev, torch.float64).contiguous()
+    return torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(dev)
+
+
+def _i32(a, dev):
+    if torch.is_tensor(a):
+        return a.to(dev, torch.int32).contiguous()
+    return torch.from_numpy(np.ascontiguousarray(a, dtype=np.int32)).to(dev)
+
+
+def group_stats(X, label, K, shift, out=None, accumulate=False):
+    """-> double [K, 2D+3] rows [S0, S1, S2, -, -] about shift[K, D]."""
+    X = as_frames(X)
+    dev, D = X.device, X.shape[1]
+    label, shift = _i32(label, dev), _f64(shift, dev)
+    assert shift.shape == (K, D)
+    L = _l.load()
+    if out is None:
+        out = torch.zeros((K, L.srb_stats_row(D)), dtype=torch.float64, device=dev)
+    _l.check(L.srb_group_stats(_l.ptr(X), X.shape[0], D, _l.ptr(label), K, _l.ptr(shift), _l.ptr(_partial(K, D, dev)),
+                               _l.ptr(out), int(accumulate), _l.stream_ptr()))
+    return out
+
+
+def moments_from_stats(stats, shift, D, unbiased=True):
+    """(count[K], mean[K,D], var[K,D]) from group_stats rows (calc_variance: unbiased, kmeans.py:12)."""
+    S0 = stats[:, 0]
+    S1, S2 = stats[:, 1:1 + D], stats[:, 1 + D:1 + 2 * D]
+    m1 = S1 / S0[:, None]
+    mean = shift + m1
+    den = (S0 - 1.0) if unbiased else S0
+    var = (S2 - S1 * m1) / den[:, None]
+    return S0, mean, var
+
+
+def gauss_consts(var, w):
+    G, D = var.reshape(-1, var.shape[-1]).shape
+    lc = torch.empty(G, dtype=torch.float64, device=var.device)
+    _l.check(_l.load().srb_gauss_consts(_l.ptr(var), _l.ptr(w), G, D, _l.ptr(lc), _l.stream_ptr()))
+    return lc
+
+
+def gmm_stats(X, label, pm, ncomp, out=None, accumulate=False):
+    """E-step statistics of frames hard-aligned to tied states of PackedModel pm -> double [R*M, 2D+3]."""
+    X = as_frames(X)
+    dev = X.device
+    label = _i32(label, dev)
+    L = _l.load()
+    lc = gauss_consts(pm.var, pm.w)
+    if out is None:
+        out = torch.zeros((pm.R * pm.M, L.srb_stats_row(pm.D)), dtype=torch.float64, device=dev)
+    _l.check(L.srb_gmm_stats(_l.ptr(X), X.shape[0], pm.D, _l.ptr(label), pm.R, pm.M, ncomp, _l.ptr(pm.mu),
+                             _l.ptr(pm.var), _l.ptr(lc), _l.ptr(_partial(pm.R * pm.M, pm.D, dev)), _l.ptr(out),
+                             int(accumulate), _l.stream_ptr()))
+    return out
+
+
+def mstep(stats, pm, ncomp, var_floor=0.0):
+    """In-place M-step on pm.mu / pm.var / pm.w (double), then refresh the packed fp32 copy."""
+    _l.check(_l.load().srb_mstep(_l.ptr(stats), pm.R, pm.M, ncomp, pm.D, _l.ptr(pm.mu), _l.ptr(pm.var), _l.ptr(pm.w),
+                                 float(var_floor), _l.stream_ptr()))
+    return pm.repack()
+
+
+def local_dist(X, Y, var=None, shared_var=False, want_dist=True, want_argmin=False):
+    """kind 0 (var None): Euclidean norm; kind 1: mahalanobis with var[S,D] (or one shared row, kmeans.py:183)."""
+    X = as_frames(X)
+    dev, D = X.device, X.shape[1]
+    Y = _f64(Y, dev)
+    S = Y.shape[0]
+    v = None if var is None else _f64(var, dev)
+    out = torch.empty((X.shape[0], S), dtype=torch.float32, device=dev) if want_dist else None
+    am = torch.empty(X.shape[0], dtype=torch.int32, device=dev) if want_argmin else None
+    _l.check(_l.load().srb_local_dist(_l.ptr(X), X.shape[0], D, _l.ptr(Y), _l.ptr(v), S, 0 if var is None else 1,
+                                      0 if shared_var else D, _l.ptr(out), S, _l.ptr(am), _l.stream_ptr()))
+    return out, am

@@ -22,6 +22,16 @@ SIGNATURES = {
     "srb_viterbi_graph": (c_int, [c_void_p, c_i64, c_void_p, c_i32] + [c_void_p] * 10 + [c_i32] + [c_void_p] * 10),
     "srb_forward_backward": (c_int, [c_void_p, c_i64, c_void_p, c_i32] + [c_void_p] * 12 + [c_i32, c_i32] +
                              [c_void_p] * 5),
+    "srb_stats_row": (c_int, [c_int]),
+    "srb_stats_parts": (c_int, []),
+    "srb_group_stats": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "srb_gmm_stats": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                              c_void_p, c_void_p, c_int, c_void_p]),
+    "srb_local_dist": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_i64,
+                               c_void_p, c_void_p]),
+    "srb_mstep": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, ctypes.c_double,
+                          c_void_p]),
+    "srb_gauss_consts": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "srb_fma_peak": (c_int, [c_int, c_int, ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_double), c_void_p]),
 }
 

@@ -1,0 +1,126 @@
+"""GPU parity: K5/K6 statistics kernels (local distances, group moments, GMM E-step + M-step) against the
+frozen reference outputs and the oracle, through the C ABI."""
+import numpy as np
+import pytest
+
+from conftest import unragged
+from oracle import oracle as orc
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-4
+
+
+@pytest.fixture(scope="module")
+def eng():
+    from srb200 import engine
+    return engine
+
+
+def test_local_dist_golden(eng, golden):
+    g = golden["dtw_helpers"]
+    X = g["dtw_X"]
+    for var in (None, g["dtw_var"]):
+        ref = orc.local_dist(X, g["dtw_y"], var)
+        out, am = eng.local_dist(X.astype(np.float32), g["dtw_y"], var, want_argmin=True)
+        np.testing.assert_allclose(out.cpu().numpy(), ref, rtol=RTOL)
+        assert np.array_equal(am.cpu().numpy(), ref.argmin(axis=1))
+    e = golden["emission"]                                  # mahalanobis() of the reference itself
+    for v1, v2, var, ref in zip(e["mh_v1"], e["mh_v2"], e["mh_var"], e["mh_out"]):
+        out, _ = eng.local_dist(v1[None].astype(np.float32), v2[None], var[None])
+        np.testing.assert_allclose(out.cpu().numpy()[0, 0], ref, rtol=RTOL)
+
+
+def test_group_stats_combine_templates_golden(eng, golden):
+    """segment means / unbiased variances of combine_templates (kmeans.py:15-30)."""
+    g = golden["dtw_helpers"]
+    xs = unragged(g["dtw_X"], g["dtw_off"])
+    starts = g["sd_seg_starts"]
+    labels = []
+    for r, x in enumerate(xs):
+        b = list(starts[r]) + [len(x)]
+        labels.append(np.repeat(np.arange(5), np.diff(b)))
+    labels = np.concatenate(labels).astype(np.int32)
+    X = g["dtw_X"].astype(np.float32)
+    shift = np.tile(X.mean(axis=0), (5, 1))
+    st = eng.group_stats(X, labels, 5, shift).cpu().numpy()
+    n, mean, var = eng.moments_from_stats(st, shift, 39)
+    assert np.array_equal(n, np.bincount(labels, minlength=5))
+    np.testing.assert_allclose(mean, g["ct_res"], rtol=RTOL, atol=1e-5)
+    np.testing.assert_allclose(var, g["ct_vars"], rtol=RTOL)
+
+
+def test_group_stats_large_random(eng):
+    rng = np.random.default_rng(0)
+    N, K, D = 200_003, 7, 39
+    X = (rng.normal(size=(N, D)) * 2 + 5).astype(np.float32)
+    lab = rng.integers(-1, K, size=N).astype(np.int32)
+    lab[1000:1400] = 3                                     # long runs too
+    shift = rng.normal(size=(K, D)) + 5
+    st = eng.group_stats(X, lab, K, shift).cpu().numpy()
+    n, mean, var = eng.moments_from_stats(st, shift, D)
+    for k in range(K):
+        xk = X[lab == k].astype(np.float64)
+        assert n[k] == len(xk)
+        np.testing.assert_allclose(mean[k], xk.mean(axis=0), rtol=1e-5)
+        np.testing.assert_allclose(var[k], xk.var(axis=0, ddof=1), rtol=RTOL)
+
+
+@pytest.mark.parametrize("k", [2, 4])
+def test_kmeans_pieces_golden(eng, golden, k):
+    """The three device pieces of kmeans (kmeans.py:167-193): partition variances, assignment with cov[0],
+    centroid update -- against the frozen reference run."""
+    g = golden["kmeans_em"]
+    data = g["km_data"]
+    X = data.astype(np.float32)
+    shift = np.tile(data.mean(axis=0), (k, 1))
+    st = eng.group_stats(X, g[f"km{k}_partition"].astype(np.int32), k, shift).cpu().numpy()
+    _, _, cov = eng.moments_from_stats(st, shift, 39)
+    np.testing.assert_allclose(cov, g[f"km{k}_cov"], rtol=RTOL)
+    # assignment of the converged centroids reproduces the converged clusters (fixed point)
+    _, am = eng.local_dist(X, g[f"km{k}_cent"], g[f"km{k}_cov"][:1], shared_var=True, want_dist=False,
+                           want_argmin=True)
+    assert np.array_equal(am.cpu().numpy(), g[f"km{k}_clusters"])
+    st = eng.group_stats(X, am, k, g[f"km{k}_cent"]).cpu().numpy()
+    _, cent, _ = eng.moments_from_stats(st, g[f"km{k}_cent"], 39)
+    np.testing.assert_allclose(cent, g[f"km{k}_cent"], rtol=RTOL, atol=1e-6)
+
+
+@pytest.mark.parametrize("k", [2, 4])
+def test_em_iteration_golden(eng, golden, k):
+    """One and three GMM.em iterations (hmm_state.py:122-159) on the first k of 4 components."""
+    g = golden["kmeans_em"]
+    X = g["km_data"].astype(np.float32)
+    lab = np.zeros(len(X), np.int32)
+    pm = eng.PackedModel(g[f"em{k}_mu_in"][None], g[f"em{k}_cov_in"][None], g[f"em{k}_w_in"][None])
+    for it in range(1, 4):
+        st = eng.gmm_stats(X, lab, pm, k)
+        eng.mstep(st, pm, k)
+        if it in (1, 3):
+            np.testing.assert_allclose(pm.w.cpu().numpy()[0], g[f"em{k}_it{it}_w"], rtol=RTOL)
+            np.testing.assert_allclose(pm.mu.cpu().numpy()[0], g[f"em{k}_it{it}_mu"], rtol=RTOL, atol=1e-5)
+            np.testing.assert_allclose(pm.var.cpu().numpy()[0], g[f"em{k}_it{it}_cov"], rtol=RTOL)
+
+
+def test_gmm_stats_multi_state_vs_oracle(eng):
+    """Frames hard-aligned to 55 tied states, ragged runs, skipped frames; statistics per state == oracle EM pass."""
+    from srb200 import synth
+    models, base = synth.make_models(51, W=11, S=5, M=4)
+    X, off, words = synth.make_utterances(52, base, 300, T=60)
+    rng = np.random.default_rng(3)
+    N = X.shape[0]
+    t_in = np.arange(N) - np.repeat(off[:-1], np.diff(off))
+    lab = (np.repeat(words, np.diff(off)) * 5 + np.minimum(t_in // 12, 4)).astype(np.int32)
+    lab[rng.random(N) < 0.05] = -1
+    pm, _ = eng.PackedModel.from_words(models)
+    st = eng.gmm_stats(X, lab, pm, 2)
+    eng.mstep(st, pm, 2)
+    mu, var, w = pm.mu.cpu().numpy(), pm.var.cpu().numpy(), pm.w.cpu().numpy()
+    for s in (0, 7, 23, 54):
+        m = models[s // 5]
+        data = X[lab == s].astype(np.float64)
+        gs = orc.GMMState(m[0][s % 5, 0], m[1][s % 5, 0], 4)
+        gs.mu, gs.cov, gs.w = m[0][s % 5].copy(), m[1][s % 5].copy(), m[2][s % 5].copy()
+        gs.em(data, 2, 1)
+        np.testing.assert_allclose(mu[s], gs.mu, rtol=RTOL, atol=1e-5)
+        np.testing.assert_allclose(var[s], gs.cov, rtol=RTOL)
+        np.testing.assert_allclose(w[s], gs.w, rtol=RTOL)
