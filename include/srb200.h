@@ -60,6 +60,12 @@ int srb_pack_model(const double *mu, const double *var, const double *w, const d
 int srb_gmm_score(const float *X, int64_t N, int D, const float *ab, const float *c, const float *shift, int R,
                   int Mp, float *E, int64_t ldE, float *best_cost, int32_t *best_state, float *comp, void *stream);
 
+/* Same on rows [row0, row0+nrows) of X only (outputs stay indexed by absolute row): lets a caller score each
+ * word's contiguous block of a word-sorted corpus against that word's states (HMM.fit works per word, hmm.py:57). */
+int srb_gmm_score_rows(const float *X, int64_t N, int64_t row0, int64_t nrows, int D, const float *ab, const float *c,
+                       const float *shift, int R, int Mp, float *E, int64_t ldE, float *best_cost, int32_t *best_state,
+                       float *comp, void *stream);
+
 /* ---- fused isolated-word classifier (core.py:79-87 over hmm.py:126-135 over decode.py:80-146) ----
  * W word models of S states each (packed model has R = W*S states, word-major); trans float[W,S,S] with
  * trans[w,i,j] = cost j -> i, +inf = none (decode.py:86-87).  Start in state 0 at frame 0
@@ -87,13 +93,16 @@ int srb_classify(const float *X, const int32_t *utt_off, int32_t B, int64_t N, i
  *   costs_out (optional) same indexing, float: costs[r, c] (decode.py returns it),
  *   path_state/path_frame[path_off[u] ...] the reversed path of decode.py:142-146 (end cell excluded,
  *   stops at frame 0), path_len[u] its length (0 when no path, -1 when the capacity path_off[u+1]-path_off[u]
- *   was too small; T + 2 * number of NES + 1 always suffices). */
+ *   was too small; T + 2 * number of NES + 1 always suffices),
+ *   frame_label[N] (optional) = g_state_off[graph] + state of the emitting state aligned to each frame (the
+ *   hard alignment kmeans.py:196-205 / continuous_speech.py:83-106 pool by; -1 for utterances without a path;
+ *   a frame emitted twice around a NES keeps the EARLIER state). */
 int srb_viterbi_graph(const float *E, int64_t ldE, const int32_t *utt_off, int32_t B, const int32_t *utt_graph,
                       const int32_t *g_state_off, const int32_t *g_nes_off, const int32_t *g_end_off,
                       const int32_t *emit, const int32_t *pred_ptr, const int32_t *pred_idx, const float *pred_cost,
                       const int32_t *nes_idx, const int32_t *end_state, int32_t Rmax, const int64_t *bp_off,
                       uint8_t *bp, float *costs_out, float *best_cost, int32_t *best_end, const int64_t *path_off,
-                      int32_t *path_state, int32_t *path_frame, int32_t *path_len, void *stream);
+                      int32_t *path_state, int32_t *path_frame, int32_t *path_len, int32_t *frame_label, void *stream);
 
 /* ---- K4: batched forward-backward (Baum-Welch E-step) for NES-free graphs -------------------------
  * The reference has NO forward-backward; semantics are defined to be consistent with

@@ -10,7 +10,7 @@ constexpr int SMAX = SRB_DP_MAX_STATES;
 // states (all of them when the model fits, as in the 220-Gaussian digit model).
 template <int D>
 __global__ void __launch_bounds__(NT, 1)
-score_kernel(const float *__restrict__ X, int64_t N, const float *__restrict__ ab, const float *__restrict__ c,
+score_kernel(const float *__restrict__ X, int64_t N, int64_t row0, int64_t nrows, const float *__restrict__ ab, const float *__restrict__ c,
              const float *__restrict__ shift, int R, int Mp, int SG, float *__restrict__ E, int64_t ldE,
              float *__restrict__ best_cost, int32_t *__restrict__ best_state, float *__restrict__ comp) {
     extern __shared__ __align__(16) float smem[];
@@ -21,14 +21,14 @@ score_kernel(const float *__restrict__ X, int64_t N, const float *__restrict__ a
     const int ES = SG | 1;
     const int nblk = Mp >> 2;
     const int ngroups = (R + SG - 1) / SG;
-    const int64_t ntiles = (N + TF - 1) / TF;
+    const int64_t ntiles = (nrows + TF - 1) / TF;
 
     if (threadIdx.x < D) shift_s[threadIdx.x] = shift[threadIdx.x];
     bool params_loaded = false;
 
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const int64_t f0 = tile * TF;
-        const int nf = (int)min((int64_t)TF, N - f0);
+        const int64_t f0 = row0 + tile * TF;
+        const int nf = (int)min((int64_t)TF, row0 + nrows - f0);
         __syncthreads();
         const int xoff = stage_frames<D>(xs, X, N, f0, nf);
         __syncthreads();
@@ -284,14 +284,16 @@ using namespace srb;
 
 extern "C" {
 
-int srb_gmm_score(const float *X, int64_t N, int D, const float *ab, const float *c, const float *shift, int R,
-                  int Mp, float *E, int64_t ldE, float *best_cost, int32_t *best_state, float *comp, void *stream) {
+int srb_gmm_score_rows(const float *X, int64_t N, int64_t row0, int64_t nrows, int D, const float *ab, const float *c,
+                       const float *shift, int R, int Mp, float *E, int64_t ldE, float *best_cost, int32_t *best_state,
+                       float *comp, void *stream) {
     SRB_REQUIRE(X && ab && c && shift, SRB_EINVAL, "srb_gmm_score: null pointer");
     SRB_REQUIRE(N >= 0 && R > 0 && Mp > 0 && (Mp & 3) == 0, SRB_EINVAL, "srb_gmm_score: bad N/R/Mp");
+    SRB_REQUIRE(row0 >= 0 && nrows >= 0 && row0 + nrows <= N, SRB_EINVAL, "srb_gmm_score: rows outside X");
     SRB_REQUIRE(!E || ldE >= R, SRB_EINVAL, "srb_gmm_score: ldE < R");
     SRB_REQUIRE(((uintptr_t)X & 15) == 0 && ((uintptr_t)ab & 15) == 0 && ((uintptr_t)c & 15) == 0, SRB_EINVAL,
                 "srb_gmm_score: X, ab, c must be 16-byte aligned");
-    if (N == 0) return SRB_OK;
+    if (nrows == 0) return SRB_OK;
     const int sms = sm_count(), cap = smem_optin();
     SRB_REQUIRE(sms > 0, SRB_ENODEVICE, "no CUDA device");
     int SG = R;
@@ -299,16 +301,21 @@ int srb_gmm_score(const float *X, int64_t N, int D, const float *ab, const float
     SRB_REQUIRE(score_smem_bytes(SG, Mp, D) <= (size_t)cap, SRB_EUNSUPPORTED,
                 "srb_gmm_score: one state of %d Gaussians x %d dims does not fit shared memory", Mp, D);
     const size_t bytes = score_smem_bytes(SG, Mp, D);
-    const int64_t ntiles = (N + TF - 1) / TF;
+    const int64_t ntiles = (nrows + TF - 1) / TF;
     const int grid = (int)(ntiles < sms ? ntiles : sms);
     SRB_DISPATCH_D(D, {
         int rc = set_smem(score_kernel<kD>, bytes);
         if (rc) return rc;
-        score_kernel<kD><<<grid, NT, bytes, (cudaStream_t)stream>>>(X, N, ab, c, shift, R, Mp, SG, E, ldE, best_cost,
-                                                                    best_state, comp);
+        score_kernel<kD><<<grid, NT, bytes, (cudaStream_t)stream>>>(X, N, row0, nrows, ab, c, shift, R, Mp, SG, E, ldE,
+                                                                    best_cost, best_state, comp);
     });
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
+}
+
+int srb_gmm_score(const float *X, int64_t N, int D, const float *ab, const float *c, const float *shift, int R,
+                  int Mp, float *E, int64_t ldE, float *best_cost, int32_t *best_state, float *comp, void *stream) {
+    return srb_gmm_score_rows(X, N, 0, N, D, ab, c, shift, R, Mp, E, ldE, best_cost, best_state, comp, stream);
 }
 
 int srb_classify(const float *X, const int32_t *utt_off, int32_t B, int64_t N, int D, const float *ab,

@@ -38,7 +38,8 @@ viterbi_graph_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *__
                      int Rmax, const int64_t *__restrict__ bp_off, uint8_t *__restrict__ bp,
                      float *__restrict__ costs_out, float *__restrict__ best_cost, int32_t *__restrict__ best_end,
                      const int64_t *__restrict__ path_off, int32_t *__restrict__ path_state,
-                     int32_t *__restrict__ path_frame, int32_t *__restrict__ path_len) {
+                     int32_t *__restrict__ path_frame, int32_t *__restrict__ path_len,
+                     int32_t *__restrict__ frame_label) {
     extern __shared__ float vsm[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float *prev = vsm + (size_t)warp * 2 * Rmax, *cur = prev + Rmax;
@@ -57,7 +58,7 @@ viterbi_graph_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *__
             if (lane == 0) {
                 best_cost[u] = INF;
                 best_end[u] = -1;
-                path_len[u] = 0;
+                if (path_len) path_len[u] = 0;
             }
             continue;
         }
@@ -141,20 +142,27 @@ viterbi_graph_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *__
             best_cost[u] = bc;
             best_end[u] = bi;
             int len = 0;
-            if (bc < INF && path_state) {
-                int32_t *ps = path_state + path_off[u], *pf = path_frame + path_off[u];
-                const int cap = (int)(path_off[u + 1] - path_off[u]);
+            if (bc < INF && (path_state || frame_label)) {
+                int32_t *ps = path_state ? path_state + path_off[u] : nullptr;
+                int32_t *pf = path_state ? path_frame + path_off[u] : nullptr;
+                const int cap = path_state ? (int)(path_off[u + 1] - path_off[u]) : 0x7fffffff;
                 int i = bi, j = T - 1;
+                if (frame_label && emit[i] >= 0) frame_label[f0 + j] = s0 + i;
                 while (j > 0 && len < cap) {
                     const int code = bpu[(size_t)j * R + i];
                     const int o = G.pred_idx[pptr[i] + code];
                     if (!(emit[o] < 0 || emit[i] < 0)) --j;
                     i = o;
-                    ps[len] = i;
-                    pf[len] = j;
+                    if (ps) {
+                        ps[len] = i;
+                        pf[len] = j;
+                    }
+                    if (frame_label && emit[i] >= 0) frame_label[f0 + j] = s0 + i;
                     ++len;
                 }
                 if (j > 0) len = -1;   // capacity exhausted
+            } else if (frame_label) {
+                for (int c = 0; c < T; ++c) frame_label[f0 + c] = -1;   // no path: frames are skipped downstream
             }
             if (path_len) path_len[u] = len;
         }
@@ -356,7 +364,7 @@ int srb_viterbi_graph(const float *E, int64_t ldE, const int32_t *utt_off, int32
                       const int32_t *emit, const int32_t *pred_ptr, const int32_t *pred_idx, const float *pred_cost,
                       const int32_t *nes_idx, const int32_t *end_state, int32_t Rmax, const int64_t *bp_off,
                       uint8_t *bp, float *costs_out, float *best_cost, int32_t *best_end, const int64_t *path_off,
-                      int32_t *path_state, int32_t *path_frame, int32_t *path_len, void *stream) {
+                      int32_t *path_state, int32_t *path_frame, int32_t *path_len, int32_t *frame_label, void *stream) {
     SRB_REQUIRE(E && utt_off && g_state_off && g_nes_off && g_end_off && emit && pred_ptr && pred_idx && pred_cost &&
                     end_state && bp_off && bp && best_cost && best_end,
                 SRB_EINVAL, "srb_viterbi_graph: null pointer");
@@ -376,7 +384,7 @@ int srb_viterbi_graph(const float *E, int64_t ldE, const int32_t *utt_off, int32
                               end_state);
     viterbi_graph_kernel<<<(int)grid, VW * 32, bytes, (cudaStream_t)stream>>>(
         E, ldE, utt_off, B, G, Rmax, bp_off, bp, costs_out, best_cost, best_end, path_off, path_state, path_frame,
-        path_len);
+        path_len, frame_label);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }

@@ -228,7 +228,7 @@ class ViterbiResult:
         return out
 
 
-def viterbi(E, off, gb, utt_graph=None, want_costs=False, want_path=True):
+def viterbi(E, off, gb, utt_graph=None, want_costs=False, want_path=True, frame_label=None):
     """K2.  E: [N, ldE] float32 CUDA emission costs; off: [B+1] int32; gb: GraphBatch."""
     dev = E.device
     offd = as_offsets(off)
@@ -248,8 +248,11 @@ def viterbi(E, off, gb, utt_graph=None, want_costs=False, want_path=True):
         _l.ptr(E), E.stride(0), _l.ptr(offd), B, _l.ptr(ug), _l.ptr(gb["g_state_off"]), _l.ptr(gb["g_nes_off"]),
         _l.ptr(gb["g_end_off"]), _l.ptr(gb["emit"]), _l.ptr(gb["pred_ptr"]), _l.ptr(gb["pred_idx"]),
         _l.ptr(gb["pred_cost"]), _l.ptr(gb["nes_idx"]), _l.ptr(gb["end_state"]), gb.Rmax, _l.ptr(ws_d), _l.ptr(bp),
-        _l.ptr(costs), _l.ptr(bc), _l.ptr(be), _l.ptr(po_d), _l.ptr(ps), _l.ptr(pf), _l.ptr(pl), _l.stream_ptr()))
-    return ViterbiResult(bc, be, ps, pf, pl, po, costs, ws, bp)
+        _l.ptr(costs), _l.ptr(bc), _l.ptr(be), _l.ptr(po_d), _l.ptr(ps), _l.ptr(pf), _l.ptr(pl), _l.ptr(frame_label),
+        _l.stream_ptr()))
+    res = ViterbiResult(bc, be, ps, pf, pl, po, costs, ws, bp)
+    res.frame_label = frame_label
+    return res
 
 
 def forward_backward(E, off, gb, utt_graph=None, want_xi=False):

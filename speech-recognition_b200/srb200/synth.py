@@ -1,6 +1,6 @@
 """Seeded synthetic models and utterances of the shapes BASELINE.json names.
 
-Pure numpy; shared by tests/ and bench.py so that the CUDA path and the oracle see identical inputs."""
+Pure numpy; shared by tests/ and bench.py so that the CUDA path and its CPU checker see identical inputs."""
 import numpy as np
 
 D = 39

@@ -1,0 +1,151 @@
+"""Device-resident batched training of isolated-word GMM-HMMs (BASELINE config 2).
+
+The reference trains one word at a time (`HMM.fit(ys)`, hmm.py:57-95): Viterbi re-alignment of every utterance
+with the current GMM states (align_gmm_states, kmeans.py:196-205), pooled frames per state, per-state EM
+(GMM.em, hmm_state.py:122-159).  Here all words are trained together from one word-sorted corpus that stays in
+HBM; one `em_iteration()` is
+
+    score (K1, each word's block against its own S states) -> Viterbi + traceback (K2, frame labels)
+    -> E-step statistics (K5) -> [allreduce over GPUs] -> M-step -> repack
+
+Utterances are sharded over ranks; the only collective is one allreduce of the float64 statistics buffer
+(`[W*S*M, 2D+3]` + total cost) per iteration, after which every rank applies the same M-step.
+"""
+import numpy as np
+import torch
+
+from . import engine
+from . import lib as _l
+from .graph import GraphBatch, StateGraph
+
+
+def shard_range(n_items, rank, world):
+    """Contiguous, balanced [lo, hi) of items for `rank` (utterance sharding)."""
+    base, rem = divmod(n_items, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def sort_by_word(X, off, words):
+    """Reorder utterances so that each word's frames are contiguous.  -> (X, off, words, order)"""
+    words = np.asarray(words)
+    order = np.argsort(words, kind="stable")
+    lens = np.diff(off)
+    if np.array_equal(order, np.arange(len(order))):
+        return X, np.asarray(off), words, order
+    new_off = np.zeros(len(off), np.int64)
+    np.cumsum(lens[order], out=new_off[1:])
+    idx = np.concatenate([np.arange(off[u], off[u + 1]) for u in order]) if len(order) else np.zeros(0, np.int64)
+    return X[idx], new_off.astype(off.dtype), words[order], order
+
+
+class ViterbiPlan:
+    """Pre-planned K2 launch for a fixed batch (offsets, graphs): all buffers allocated once."""
+
+    def __init__(self, off, gb, utt_graph=None, want_path=False, want_label=True):
+        dev = gb["emit"].device
+        self.gb = gb
+        self.off = engine.as_offsets(off)
+        self.B = self.off.numel() - 1
+        offn = np.asarray(off.cpu() if torch.is_tensor(off) else off, dtype=np.int64)
+        ws, po = engine._utt_layout(offn, gb, utt_graph)
+        self.ws, self.po = ws, po
+        self.ws_d = torch.from_numpy(ws).to(dev)
+        self.ug = None if utt_graph is None else torch.as_tensor(np.asarray(utt_graph, np.int32)).to(dev)
+        self.bp = torch.empty(max(int(ws[-1]), 1), dtype=torch.uint8, device=dev)
+        self.best_cost = torch.empty(self.B, dtype=torch.float32, device=dev)
+        self.best_end = torch.empty(self.B, dtype=torch.int32, device=dev)
+        self.N = int(offn[-1])
+        self.label = torch.empty(max(self.N, 1), dtype=torch.int32, device=dev) if want_label else None
+        self.po_d = self.ps = self.pf = self.pl = None
+        if want_path:
+            self.po_d = torch.from_numpy(po).to(dev)
+            self.ps = torch.empty(max(int(po[-1]), 1), dtype=torch.int32, device=dev)
+            self.pf = torch.empty(max(int(po[-1]), 1), dtype=torch.int32, device=dev)
+            self.pl = torch.zeros(self.B, dtype=torch.int32, device=dev)
+
+    def run(self, E):
+        gb, p = self.gb, _l.ptr
+        _l.check(_l.load().srb_viterbi_graph(
+            p(E), E.stride(0), p(self.off), self.B, p(self.ug), p(gb["g_state_off"]), p(gb["g_nes_off"]),
+            p(gb["g_end_off"]), p(gb["emit"]), p(gb["pred_ptr"]), p(gb["pred_idx"]), p(gb["pred_cost"]),
+            p(gb["nes_idx"]), p(gb["end_state"]), gb.Rmax, p(self.ws_d), p(self.bp), None, p(self.best_cost),
+            p(self.best_end), p(self.po_d), p(self.ps), p(self.pf), p(self.pl), p(self.label), _l.stream_ptr()))
+        return self
+
+
+class IsolatedTrainer:
+    """All W word models trained together on this rank's shard of a word-sorted corpus."""
+
+    def __init__(self, X, off, words, pm, trans, S, ncomp, group=None, var_floor=1e-6):
+        """X [N,D] float32, off [B+1], words [B] (numpy, this rank's shard); pm: PackedModel with W*S states;
+        trans: [W,S,S] float64 numpy (decode.py:86-87 convention)."""
+        X, off, words, self.order = sort_by_word(np.asarray(X), np.asarray(off), words)
+        self.dev = engine.device()
+        self.X = engine.as_frames(X)
+        self.pm, self.S, self.ncomp, self.group, self.var_floor = pm, S, ncomp, group, var_floor
+        self.W = pm.R // S
+        self.words = words
+        off = np.asarray(off, np.int64)
+        self.N, self.B = int(off[-1]), len(off) - 1
+        uptr = np.searchsorted(words, np.arange(self.W + 1), side="left")
+        self.word_rows = [(int(off[uptr[w]]), int(off[uptr[w + 1]])) for w in range(self.W)]
+        graphs = [StateGraph(trans[w], np.arange(S)) for w in range(self.W)]
+        self.gb = GraphBatch(graphs, self.dev)
+        self.plan = ViterbiPlan(off.astype(np.int32), self.gb, utt_graph=words.astype(np.int32))
+        self.E = torch.empty((max(self.N, 1), S), dtype=torch.float32, device=self.dev)
+        L = _l.load()
+        self.row = L.srb_stats_row(pm.D)
+        self.G = pm.R * pm.M
+        self.stats = torch.zeros(self.G * self.row + 2, dtype=torch.float64, device=self.dev)   # + cost, utterances
+        self.partial = torch.empty(L.srb_stats_parts() * self.G * self.row, dtype=torch.float32, device=self.dev)
+        self.lc = torch.empty(self.G, dtype=torch.float64, device=self.dev)
+        self.launches_per_iteration = self.W + 1 + 1 + 3 + 2 + 1 + 1
+
+    def align(self):
+        """K1 per word block + K2: frame labels (tied state per frame) and per-utterance best cost."""
+        pm, S, L, p = self.pm, self.S, _l.load(), _l.ptr
+        st = _l.stream_ptr()
+        blk = S * pm.Mp * pm.D * 2
+        for w, (r0, r1) in enumerate(self.word_rows):
+            if r1 > r0:
+                _l.check(L.srb_gmm_score_rows(p(self.X), self.N, r0, r1 - r0, pm.D, pm.ab[w * blk:].data_ptr(),
+                                              pm.c[w * S * pm.Mp:].data_ptr(), p(pm.shift), S, pm.Mp, p(self.E), S,
+                                              None, None, None, st))
+        self.plan.run(self.E)
+        return self.plan.label
+
+    def accumulate(self):
+        pm, L, p = self.pm, _l.load(), _l.ptr
+        st = _l.stream_ptr()
+        _l.check(L.srb_gauss_consts(p(pm.var), p(pm.w), self.G, pm.D, p(self.lc), st))
+        body = self.stats[:self.G * self.row]
+        _l.check(L.srb_gmm_stats(p(self.X), self.N, pm.D, p(self.plan.label), pm.R, pm.M, self.ncomp, p(pm.mu),
+                                 p(pm.var), p(self.lc), p(self.partial), p(body), 0, st))
+        self.stats[self.G * self.row] = self.plan.best_cost.sum(dtype=torch.float64)
+        self.stats[self.G * self.row + 1] = float(self.B)
+        return self.stats
+
+    def reduce(self):
+        """The one collective of an iteration: sum of the statistics buffer over ranks (NCCL over NVLink)."""
+        if self.group is not None or (torch.distributed.is_initialized() and torch.distributed.get_world_size() > 1):
+            torch.distributed.all_reduce(self.stats, group=self.group)
+        return self.stats
+
+    def update(self):
+        pm = self.pm
+        _l.check(_l.load().srb_mstep(_l.ptr(self.stats), pm.R, pm.M, self.ncomp, pm.D, _l.ptr(pm.mu), _l.ptr(pm.var),
+                                     _l.ptr(pm.w), float(self.var_floor), _l.stream_ptr()))
+        pm.repack()
+
+    def em_iteration(self):
+        """One segmental-K-means + EM pass.  Returns the device statistics buffer (last two entries: summed
+        Viterbi cost and utterance count over all ranks) without synchronising."""
+        self.align()
+        self.accumulate()
+        self.reduce()
+        self.update()
+        return self.stats
+
+    def mean_cost(self):
+        return float(self.stats[-2] / self.stats[-1])
