@@ -30,6 +30,7 @@ for p in (ROOT, PKG):
 import numpy as np  # noqa: E402
 
 W_, S_, M_, D_ = 11, 5, 4, 39
+NCOMP = int(np.log(M_)) and 2 ** int(np.log(M_))   # hmm.py:104: n_splits = int(np.log(4)) = 1 -> 2 trained components
 FMA_PER_FRAME_DECODE = W_ * S_ * M_ * 2 * D_          # 17 160 FMA per frame (all 11 words scored)
 
 
@@ -38,11 +39,12 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--workload", default=os.environ.get("SRB_WORKLOAD", "decode"), choices=["decode", "em"])
+    ap.add_argument("--workload", default=os.environ.get("SRB_WORKLOAD", "em"), choices=["decode", "em"])
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--utts", type=int, default=100_000, help="utterances per GPU (100 frames each)")
     ap.add_argument("--frames", type=int, default=100)
     ap.add_argument("--cpu-utts", type=int, default=0, help="utterances of the CPU sample (0 = auto)")
+    ap.add_argument("--no-decode", action="store_true", help="skip the decode sub-benchmark of the em line")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     return ap.parse_args()
 
@@ -111,6 +113,24 @@ def cpu_decode(models, base, n_utts, frames, steps=1, warmup=0):
     return X.shape[0] / dt, orc.num_threads(), dt * 1e3
 
 
+def cpu_em(models, base, n_utts, frames, steps=1, warmup=0):
+    """Times the CPU restatement of one training pass (oracle.train_iteration: align_gmm_states for every utterance,
+    OpenMP over utterances, then one GMM.em iteration per tied state) on a bounded sample."""
+    from oracle import oracle as orc
+    from srb200 import synth
+    X, off, words = synth.make_utterances(2, base, n_utts, T=frames)
+    X64, off64 = X.astype(np.float64), off.astype(np.int64)
+    for _ in range(warmup):
+        orc.train_iteration(X64, off64, words, models, NCOMP)
+    ts = []
+    for _ in range(max(steps, 1)):
+        t0 = time.perf_counter()
+        orc.train_iteration(X64, off64, words, models, NCOMP)
+        ts.append(time.perf_counter() - t0)
+    dt = float(np.mean(ts))
+    return X.shape[0] / dt, orc.num_threads(), dt * 1e3
+
+
 # ------------------------------------------------------------------------------------------ distributed plumbing
 def dist_env():
     return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
@@ -142,6 +162,120 @@ def timed_steps(fn, steps, warmup, torch, dist, world):
     return total, per
 
 
+def bench_decode(args, ctx):
+    """Config-1 shape: every utterance scored against all 11 word models + Viterbi (fused classify kernel)."""
+    torch, dist, engine = ctx["torch"], ctx["dist"], ctx["engine"]
+    X, off, words, pm, trans, world = ctx["X"], ctx["off"], ctx["words"], ctx["pm"], ctx["trans"], ctx["world"]
+    N, B = int(X.shape[0]), len(off) - 1
+    Xd, offd = engine.as_frames(X), engine.as_offsets(off)
+    final = torch.empty((B, W_), dtype=torch.float32, device="cuda")
+    label = torch.empty(B, dtype=torch.int32, device="cuda")
+
+    def step():
+        engine.classify(Xd, offd, pm, trans, W_, S_, final, label)
+
+    sampler = ClockSampler(ctx["local"])
+    sampler.start()
+    total_ms, per = timed_steps(step, args.steps, args.warmup, torch, dist, world)
+    clocks = sampler.stop()
+    acc = float((label.cpu().numpy() == words).mean())
+    kern_ms = float(np.mean(per))
+    flops = 2.0 * FMA_PER_FRAME_DECODE * N / (kern_ms * 1e-3)
+    peak_fma = ctx["peak_fma"]
+    out = {
+        "metric": "decoded frames/s (GMM scoring of all 11 word models + Viterbi)",
+        "value": world * N * args.steps / (total_ms * 1e-3), "unit": "frames/s", "ms_per_step": total_ms / args.steps,
+        "gpu_launches": args.steps,          # one fused classify_kernel launch per step
+        "roofline": {"bound": "fp32_fma", "achieved": flops / 1e12, "peak": 2 * peak_fma / 1e12,
+                     "unit": "TFLOP/s", "frac": flops / (2 * peak_fma), "traffic": None,
+                     "kernel": "classify_kernel<39>", "kernel_ms": kern_ms,
+                     "peak_source": "srb_fma_peak (FFMA2 probe) measured in this run",
+                     "algorithmic": "17160 FMA/frame = 220 Gaussians x 2*39 (SURVEY 8d)",
+                     "hbm": {"achieved_gbs": (N * D_ * 4 + B * (W_ + 1) * 4) / (kern_ms * 1e-3) / 1e9,
+                             "peak_gbs": peaks().get("hbm_gbs")}},
+        "accuracy": acc, "clocks": clocks,
+    }
+    # ---- end to end: pinned host buffers -> chunked H2D on two streams -> classify -> D2H labels
+    Xh = torch.from_numpy(X).pin_memory()
+    offh = torch.from_numpy(off.astype(np.int32))
+    runner = engine.HostClassifier(pm, trans, W_, S_, max_utts=8192, max_frames=8192 * args.frames)
+    out_labels = torch.empty(B, dtype=torch.int32).pin_memory()
+    e2e_ms, _ = timed_steps(lambda: runner.run(Xh, offh, out_labels), args.steps, args.warmup, torch, dist, world)
+    assert np.array_equal(out_labels.numpy(), label.cpu().numpy()), "e2e labels differ from the resident run"
+    out["e2e"] = {"value": world * N * args.steps / (e2e_ms * 1e-3), "unit": "frames/s",
+                  "h2d_bytes_per_step": int(X.nbytes + off.nbytes), "d2h_bytes_per_step": int(B * 4),
+                  "api": "srb200.engine.HostClassifier.run (host numpy/pinned buffers in, labels out)"}
+    del Xd, Xh
+    return out
+
+
+def bench_em(args, ctx):
+    """Config 2: one segmental-K-means + EM iteration over the rank's shard (align -> stats -> allreduce -> M-step)."""
+    torch, dist, engine = ctx["torch"], ctx["dist"], ctx["engine"]
+    from srb200.trainer import IsolatedTrainer
+    X, off, words, world = ctx["X"], ctx["off"], ctx["words"], ctx["world"]
+    N, B = int(X.shape[0]), len(off) - 1
+    pm, _ = engine.PackedModel.from_words(ctx["models"])       # private copy: training moves it
+    trans_np = np.stack([m[3] for m in ctx["models"]])
+    tr = IsolatedTrainer(X, off, words, pm, trans_np, S_, NCOMP)
+    sampler = ClockSampler(ctx["local"])
+    sampler.start()
+    total_ms, per = timed_steps(tr.em_iteration, args.steps, args.warmup, torch, dist, world)
+    clocks = sampler.stop()
+    mean_cost = tr.mean_cost()
+    # phase breakdown (outside the timed region): CUDA events between the phases of a few more iterations
+    names = ["score", "viterbi", "stats", "allreduce", "mstep"]
+    acc = dict.fromkeys(names, 0.0)
+    reps = 3
+    for _ in range(reps):
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
+        ev[0].record()
+        tr.score()
+        ev[1].record()
+        tr.plan.run(tr.E)
+        ev[2].record()
+        tr.accumulate()
+        ev[3].record()
+        tr.reduce()
+        ev[4].record()
+        tr.update()
+        ev[5].record()
+        torch.cuda.synchronize()
+        for i, k in enumerate(names):
+            acc[k] += ev[i].elapsed_time(ev[i + 1]) / reps
+    # algorithmic HBM bytes per frame of each phase (DESIGN.md): X = 156 B, E = 4*S, labels 4, back-pointers S
+    bytes_pf = {"score": D_ * 4 + 4 * S_, "viterbi": 4 * S_ + 2 * S_ + 4, "stats": D_ * 4 + 4}
+    dom = max(("score", "viterbi", "stats"), key=lambda k: acc[k])
+    gbs = bytes_pf[dom] * N / (acc[dom] * 1e-3) / 1e9
+    pk = peaks()
+    out = {
+        "metric": "EM-iteration frames/s (segmental K-means alignment + GMM EM statistics + M-step)",
+        "value": world * N * args.steps / (total_ms * 1e-3), "unit": "frames/s", "ms_per_step": total_ms / args.steps,
+        "gpu_launches": args.steps * (W_ + 6),   # 11 score + viterbi + consts + stats + reduce + mstep + pack
+        "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk.get("hbm_gbs"), "unit": "GB/s",
+                     "frac": gbs / pk.get("hbm_gbs"), "traffic": None, "kernel": dom, "kernel_ms": acc[dom],
+                     "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "source" not in pk else "fallback",
+                     "algorithmic": f"{bytes_pf[dom]} B/frame for the {dom} phase", "phase_ms": acc,
+                     "step_bytes_per_frame": sum(bytes_pf.values()),
+                     "step_hbm_frac": sum(bytes_pf.values()) * N / (float(np.mean(per)) * 1e-3) / 1e9 / pk.get("hbm_gbs")},
+        "mean_viterbi_cost": mean_cost, "clocks": clocks,
+    }
+    # ---- end to end: the shard comes from pinned host memory every step, the updated model goes back
+    Xh = torch.from_numpy(np.ascontiguousarray(tr.X.cpu().numpy())).pin_memory()
+    host_model = torch.empty(tr.stats.numel(), dtype=torch.float64).pin_memory()
+
+    def e2e_step():
+        tr.X.copy_(Xh, non_blocking=True)
+        tr.em_iteration()
+        host_model.copy_(tr.stats, non_blocking=True)
+
+    e2e_ms, _ = timed_steps(e2e_step, args.steps, args.warmup, torch, dist, world)
+    out["e2e"] = {"value": world * N * args.steps / (e2e_ms * 1e-3), "unit": "frames/s",
+                  "h2d_bytes_per_step": int(Xh.numel() * 4), "d2h_bytes_per_step": int(host_model.numel() * 8),
+                  "api": "srb200.trainer.IsolatedTrainer (pinned host shard in, statistics/model out)"}
+    return out
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -152,74 +286,37 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from srb200 import engine, synth
+    from srb200.trainer import sort_by_word
 
     models, base = synth.make_models(1, W=W_, S=S_, M=M_)
     X, off, words = synth.make_utterances(100 + rank, base, args.utts, T=args.frames)
+    X, off, words, _ = sort_by_word(X, off, words)
     N, B = int(X.shape[0]), args.utts
     pm, trans = engine.PackedModel.from_words(models)
-    sampler = ClockSampler(local)
-    line = {}
-
-    if args.workload == "decode":
-        Xd, offd = engine.as_frames(X), engine.as_offsets(off)
-        final = torch.empty((B, W_), dtype=torch.float32, device="cuda")
-        label = torch.empty(B, dtype=torch.int32, device="cuda")
-
-        def step():
-            engine.classify(Xd, offd, pm, trans, W_, S_, final, label)
-
-        peak_fma = max(engine.fma_peak(True, 8192) for _ in range(3))      # FMA/s, measured now on this GPU
-        sampler.start()
-        total_ms, per = timed_steps(step, args.steps, args.warmup, torch, dist, world)
-        clocks = sampler.stop()
-        acc = float((label.cpu().numpy() == words).mean())
-        kern_ms = float(np.mean(per))
-        flops = 2.0 * FMA_PER_FRAME_DECODE * N / (kern_ms * 1e-3)
-        line.update({
-            "metric": "decoded frames/s (GMM scoring of all 11 word models + Viterbi, 1 GPU shard each)",
-            "value": world * N * args.steps / (total_ms * 1e-3), "unit": "frames/s",
-            "gpu_launches": args.steps,          # one fused classify_kernel launch per step
-            "roofline": {"bound": "fp32_fma", "achieved": flops / 1e12, "peak": 2 * peak_fma / 1e12,
-                         "unit": "TFLOP/s", "frac": flops / (2 * peak_fma), "traffic": None,
-                         "kernel": "classify_kernel<39>", "kernel_ms": kern_ms,
-                         "peak_source": "srb_fma_peak (fma.rn.f32x2 probe) measured in this run",
-                         "algorithmic": "17160 FMA/frame = 220 Gaussians x 2*39 (SURVEY 8d)",
-                         "hbm": {"achieved_gbs": (N * D_ * 4 + B * (W_ + 1) * 4) / (kern_ms * 1e-3) / 1e9,
-                                 "peak_gbs": peaks().get("hbm_gbs")}},
-            "accuracy": acc,
-        })
-        # ---- end to end: pinned host buffers -> chunked H2D on two streams -> classify -> D2H labels
-        Xh = torch.from_numpy(X).pin_memory()
-        offh = torch.from_numpy(off.astype(np.int32))
-        runner = engine.HostClassifier(pm, trans, W_, S_, max_utts=8192, max_frames=8192 * args.frames)
-        out_labels = torch.empty(B, dtype=torch.int32).pin_memory()
-
-        def e2e_step():
-            runner.run(Xh, offh, out_labels)
-
-        e2e_ms, _ = timed_steps(e2e_step, args.steps, args.warmup, torch, dist, world)
-        assert np.array_equal(out_labels.numpy(), label.cpu().numpy()), "e2e labels differ from the resident run"
-        line["e2e"] = {"value": world * N * args.steps / (e2e_ms * 1e-3), "unit": "frames/s",
-                       "h2d_bytes_per_step": int(X.nbytes + off.nbytes), "d2h_bytes_per_step": int(B * 4),
-                       "api": "srb200.engine.HostClassifier.run (host numpy/pinned buffers in, labels out)"}
-    else:
-        raise SystemExit("workload 'em' is not built yet")
-
+    peak_fma = max(engine.fma_peak(True, 8192) for _ in range(3))      # FMA/s, measured now on this GPU
+    ctx = {"torch": torch, "dist": dist, "engine": engine, "X": X, "off": off, "words": words, "pm": pm,
+           "trans": trans, "models": models, "world": world, "local": local, "peak_fma": peak_fma}
+    line = (bench_em if args.workload == "em" else bench_decode)(args, ctx)
+    if args.workload == "em" and world == 1 and not args.no_decode:
+        d = bench_decode(args, ctx)
+        line["decode"] = {k: d[k] for k in ("metric", "value", "unit", "ms_per_step", "roofline", "e2e", "accuracy")}
     line.update({
-        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {W_} words x {S_} states x {M_} diag Gaussians, D={D_}, "
-                               f"{B} utterances x {args.frames} frames per GPU",
+                               f"{B} utterances x {args.frames} frames per GPU"
+                               + (f", EM over the first {NCOMP} components (hmm.py:104)" if args.workload == "em" else ""),
                    "utterances_per_gpu": B, "frames_per_gpu": N, "l2": "shard (%.2f GB) larger than L2" % (X.nbytes / 1e9),
-                   "parallelism": f"utterance-sharded x{world}, no data-path collective"},
-        "clocks": clocks,
+                   "parallelism": f"utterance-sharded x{world}" + (", one fp64 allreduce of the statistics per step"
+                                                                   if args.workload == "em" else ", no collective")},
     })
     if rank == 0 and not args.no_cpu:
-        n_cpu = args.cpu_utts or 512
-        v, cores, ms = cpu_decode(models, base, n_cpu, args.frames)
+        n_cpu = args.cpu_utts or (2048 if args.workload == "em" else 512)
+        fn = cpu_em if args.workload == "em" else cpu_decode
+        v, cores, ms = fn(models, base, n_cpu, args.frames)
         line["cpu_baseline"] = {"value": v, "unit": "frames/s", "cores": cores, "kind": "port",
-                                "sample": f"{n_cpu} utterances x {args.frames} frames, oracle/sr_oracle.c orc_classify "
-                                          f"(float64, OpenMP), {ms:.0f} ms"}
+                                "sample": f"{n_cpu} utterances x {args.frames} frames, oracle/ float64 C restatement "
+                                          f"(OpenMP), {ms:.0f} ms"}
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -241,13 +338,15 @@ def run_reference(args):
         return
     from srb200 import synth
     models, base = synth.make_models(1, W=W_, S=S_, M=M_)
-    n_cpu = args.cpu_utts or 512
-    if args.workload != "decode":
-        raise SystemExit("workload 'em' is not built yet")
-    v, cores, ms = cpu_decode(models, base, n_cpu, args.frames, steps=args.steps, warmup=min(args.warmup, 1))
+    em = args.workload == "em"
+    n_cpu = args.cpu_utts or (2048 if em else 512)
+    fn = cpu_em if em else cpu_decode
+    v, cores, ms = fn(models, base, n_cpu, args.frames, steps=args.steps, warmup=min(args.warmup, 1))
+    metric = ("EM-iteration frames/s (segmental K-means alignment + GMM EM statistics + M-step)" if em else
+              "decoded frames/s (GMM scoring of all 11 word models + Viterbi)")
     line = {
         "impl": "reference",
-        "metric": "decoded frames/s (GMM scoring of all 11 word models + Viterbi, 1 GPU shard each)",
+        "metric": metric,
         "value": v, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",

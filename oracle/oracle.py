@@ -497,3 +497,45 @@ def continuous_train_iteration(data, word_models, label_seqs, n_gaussians=4, n_s
                     tr[si + 1, si] = -np.log(p_jump)
                 tr[si, si] = -np.log(1 - p_jump)
     return new
+
+
+# ------------------------------------------------------------------------------------ batched training pass (CPU baseline)
+def align_labels(X, off, words, word_models, log_domain=False):
+    """kmeans.py:196-205 for a labelled batch -> (labels[N] tied state per frame, cost[B]).  OpenMP over utterances."""
+    X, Xp = _d(X)
+    off, op = _i(off)
+    words, wp_ = _i(words)
+    S, M, D = word_models[0][0].shape
+    mu, mp = _d(np.array([m[0] for m in word_models]))
+    cov, cp = _d(np.array([m[1] for m in word_models]))
+    w, wp = _d(np.array([m[2] for m in word_models]))
+    tr, tp = _d(np.array([m[3] for m in word_models]))
+    B = len(off) - 1
+    labels = np.empty(X.shape[0], np.int64)
+    cost = np.empty(B)
+    lib().orc_align_labels(Xp, op, ctypes.c_int64(B), D, wp_, mp, cp, wp, tp, S, M, int(log_domain),
+                           labels.ctypes.data_as(c_ip), cost.ctypes.data_as(c_dp))
+    return labels, cost
+
+
+def train_iteration(X, off, words, word_models, ncomp, log_domain=False):
+    """One segmental-K-means + EM pass over all words: Viterbi re-alignment (align_gmm_states) then ONE GMM.em
+    iteration (hmm_state.py:124-148) per tied state on its pooled frames.  -> (new models, mean cost)."""
+    X = np.ascontiguousarray(X, dtype=np.float64)
+    labels, cost = align_labels(X, off, words, word_models, log_domain)
+    S, M, D = word_models[0][0].shape
+    order = np.argsort(labels, kind="stable")
+    bounds = np.searchsorted(labels[order], np.arange(len(word_models) * S + 1))
+    new = []
+    for wd, m in enumerate(word_models):
+        mu, cov, w = m[0].copy(), m[1].copy(), m[2].copy()
+        for s in range(S):
+            t = wd * S + s
+            idx = np.sort(order[bounds[t]:bounds[t + 1]])
+            if len(idx) == 0:
+                continue
+            st = GMMState(mu[s, 0], cov[s, 0], M)
+            st.mu, st.cov, st.w = mu[s], cov[s], w[s]
+            st.em(X[idx], ncomp, 1)
+        new.append((mu, cov, w, m[3]))
+    return new, float(cost.mean())

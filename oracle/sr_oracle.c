@@ -424,6 +424,46 @@ double orc_forward_backward(const double *E, int64_t T, int R, const double *tra
     return nlz;
 }
 
+
+/* ---- align_gmm_states (kmeans.py:196-205) for a labelled batch: every utterance is Viterbi-aligned to the S
+ * states of its own word (decode_hmm_states with the word's GMM states), OpenMP over utterances.
+ * labels[N] = tied state (word*S + state) of every frame, cost[B] = costs[-1,-1].  This is the alignment half of
+ * the CPU baseline of the EM workload; the E/M half is orc_em_iteration per tied state. */
+void orc_align_labels(const double *X, const int64_t *off, int64_t B, int D, const int64_t *word, const double *mu,
+                      const double *cov, const double *w, const double *trans, int S, int M, int log_domain,
+                      int64_t *labels, double *cost) {
+#pragma omp parallel for schedule(dynamic, 4)
+    for (int64_t u = 0; u < B; ++u) {
+        int64_t T = off[u + 1] - off[u];
+        int wd = (int)word[u];
+        double *E = (double *)malloc(sizeof(double) * T * S);
+        double *costs = (double *)malloc(sizeof(double) * T * S);
+        int64_t *pm = (int64_t *)malloc(sizeof(int64_t) * T * S * 2);
+        int64_t *path = (int64_t *)malloc(sizeof(int64_t) * (T + 2) * 2);
+        double *col = (double *)malloc(sizeof(double) * T);
+        uint8_t nes[64] = {0};
+        for (int s = 0; s < S; ++s) {
+            size_t g = ((size_t)wd * S + s) * M;
+            orc_gmm_evaluate(X + off[u] * D, T, D, mu + g * D, cov + g * D, w + g, M, log_domain, col, NULL);
+            for (int64_t t = 0; t < T; ++t) E[t * S + s] = col[t];
+        }
+        int64_t ends[2] = {S - 1, T - 1};
+        int64_t n = orc_decode(E, T, S, trans + (size_t)wd * S * S, nes, ends, 1, costs, pm, path, T + 2, NULL);
+        cost[u] = costs[(int64_t)(S - 1) * T + (T - 1)];
+        int64_t *lab = labels + off[u];
+        for (int64_t t = 0; t < T; ++t) lab[t] = -1;
+        if (n >= 0 && !isinf(cost[u])) {
+            lab[T - 1] = (int64_t)wd * S + (S - 1);
+            for (int64_t k = 0; k < n; ++k) lab[path[2 * k + 1]] = (int64_t)wd * S + path[2 * k];
+        }
+        free(E);
+        free(costs);
+        free(pm);
+        free(path);
+        free(col);
+    }
+}
+
 int orc_num_threads(void) {
 #ifdef _OPENMP
     extern int omp_get_max_threads(void);

@@ -102,8 +102,8 @@ class IsolatedTrainer:
         self.lc = torch.empty(self.G, dtype=torch.float64, device=self.dev)
         self.launches_per_iteration = self.W + 1 + 1 + 3 + 2 + 1 + 1
 
-    def align(self):
-        """K1 per word block + K2: frame labels (tied state per frame) and per-utterance best cost."""
+    def score(self):
+        """K1: each word's contiguous block of frames against that word's S states -> E[N, S]."""
         pm, S, L, p = self.pm, self.S, _l.load(), _l.ptr
         st = _l.stream_ptr()
         blk = S * pm.Mp * pm.D * 2
@@ -112,6 +112,11 @@ class IsolatedTrainer:
                 _l.check(L.srb_gmm_score_rows(p(self.X), self.N, r0, r1 - r0, pm.D, pm.ab[w * blk:].data_ptr(),
                                               pm.c[w * S * pm.Mp:].data_ptr(), p(pm.shift), S, pm.Mp, p(self.E), S,
                                               None, None, None, st))
+        return self.E
+
+    def align(self):
+        """K1 per word block + K2: frame labels (tied state per frame) and per-utterance best cost."""
+        self.score()
         self.plan.run(self.E)
         return self.plan.label
 
