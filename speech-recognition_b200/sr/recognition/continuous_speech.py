@@ -1,0 +1,147 @@
+"""Connected-word layer of the sr.recognition mirror (reference: sr/recognition/continuous_speech.py:13-179).
+
+`build_state_sequences` builds the same flat state list / dense transition matrix / end indices.
+`continuous_train` runs the embedded Viterbi training loop with ONE batched scoring launch and ONE batched
+graph-Viterbi launch per outer iteration for all utterances (one forced-alignment chain graph per distinct label
+sequence), then the per-state split / K-means / EM of the reference on device-resident pools.
+"""
+import copy
+import os
+import pickle
+import warnings
+
+import numpy as np
+import torch
+
+from . import _ops
+from .decode import decode_batch
+from .hmm_state import NES, mahalanobis
+from .kmeans import _kmeans_device
+
+
+def build_state_sequences(hmms, label_matrix):
+    """Flat graph [NES, layer 0 words, NES, layer 1 words, NES, ...] (continuous_speech.py:13-53).
+    Every word of layer k is entered from NES k (cost 0) and leaves to NES k+1 (cost 0); inside a word block the
+    word's own transitions apply.  -> (states, transitions [R, R], end-state indices of the last layer)"""
+    S = len(hmms[0].gmm_states)                       # all models share the state count (asserted below)
+    R = 1 + sum(len(hmms[l].gmm_states) for labels in label_matrix for l in labels) + len(label_matrix)
+    trans = np.full((R, R), np.inf)
+    seq = [NES()]
+    entry = 0                                          # index of the NES feeding the current layer
+    last_ends = []
+    for labels in label_matrix:
+        starts, ends = [], []
+        for l in labels:
+            o = len(seq)
+            assert S == len(hmms[l].gmm_states)
+            seq += hmms[l].gmm_states
+            trans[o:o + S, o:o + S] = hmms[l].transitions
+            starts.append(o)
+            ends.append(o + S - 1)
+        seq.append(NES())
+        exit_ = len(seq) - 1
+        trans[starts, entry] = 0
+        trans[exit_, ends] = 0
+        entry, last_ends = exit_, ends
+    return seq, trans, last_ends
+
+
+def _pool_segments(path, is_nes):
+    """The reference's pooling state machine (continuous_speech.py:90-106, quirks A12) on one forward path:
+    -> list of (state_row, start_frame, end_frame).  A segment opens at the first point whose state emits, closes
+    at the first later point with a different row (that point's frame is excluded and does not open a segment
+    itself); the last open segment is never flushed."""
+    r, c = path[:, 0], path[:, 1]
+    n = len(r)
+    if n == 0:
+        return []
+    # only the first two points of every run of equal rows can change the machine's state
+    run_first = np.flatnonzero(np.concatenate([[True], r[1:] != r[:-1]]))
+    cand = np.unique(np.concatenate([run_first, np.minimum(run_first + 1, n - 1)]))
+    out = []
+    start = cur = None
+    for i in cand:
+        ri, ci = int(r[i]), int(c[i])
+        if start is None and not is_nes[ri]:
+            start, cur = ci, ri
+        if ri != cur and start is not None and start < ci:
+            out.append((cur, start, ci))
+            start = cur = None
+    return out
+
+
+def continuous_train(data, models, label_seqs, output_path, n_gaussians=4, n_segments=5, max_iteration=1000):
+    """Embedded training on connected utterances (continuous_speech.py:56-179)."""
+    old_models = models
+    new_models = copy.deepcopy(models)
+    X, off = _ops.cat_frames(data)
+    Xd = _ops.to_device(X)
+    off64 = off.astype(np.int64)
+    for it in range(max_iteration):
+        print('=' * 25)
+        print('Continuous training iteration:', it)
+        # ---- alignment: one chain graph per distinct label sequence, all utterances in one launch
+        keys, graphs, utt_graph = {}, [], []
+        for labels in label_seqs:
+            k = tuple(labels)
+            if k not in keys:
+                keys[k] = len(graphs)
+                seq, trans, ends = build_state_sequences(new_models, [[l] for l in labels])
+                graphs.append((seq, trans, ends))
+            utt_graph.append(keys[k])
+        res = decode_batch(data, graphs, utt_graph=utt_graph, want_path=True)
+        paths = res.paths()
+        # ---- pooling per tied state (dict order = first appearance, it fixes the RNG stream of kmeans)
+        pools, order = {}, []
+        for u, path in enumerate(paths):
+            seq = graphs[utt_graph[u]][0]
+            is_nes = np.array([type(s) is NES for s in seq])
+            for row, a, b in _pool_segments(path[::-1], is_nes):
+                st = seq[row]
+                if id(st) not in pools:
+                    pools[id(st)] = (st, [])
+                    order.append(id(st))
+                pools[id(st)][1].append((int(off64[u]) + a, int(off64[u]) + b))
+        # ---- per-state split / K-means / EM (continuous_speech.py:110-142)
+        for sid in order:
+            state, spans = pools[sid]
+            assert type(state) is not NES
+            idx = torch.from_numpy(np.concatenate([np.arange(a, b) for a, b in spans])).to(Xd.device)
+            seg_d = Xd.index_select(0, idx)
+            seg_h = X[idx.cpu().numpy()]
+            n_splits = int(np.log(n_gaussians))
+            assert n_splits > 0
+            centroids = seg_d.double().mean(dim=0).cpu().numpy().reshape(1, -1)
+            weights = np.full(n_gaussians, 1 / n_segments)
+            for i in range(n_splits):
+                k = 2 ** (i + 1)
+                centroids = np.concatenate([centroids * 0.9, centroids * 1.1], axis=0)
+                clusters, centroids, variance = _kmeans_device(seg_d, seg_h, k, centroids, mahalanobis, 1000)
+                cs, c_counts = np.unique(clusters, return_counts=True)
+                for c in cs:
+                    weights[c] = c_counts[c] / n_segments       # continuous_speech.py:135-137 (sic)
+                state.update_models(centroids, variance, weights[:k])
+                state._em_device(seg_d, k, 10000)
+        # ---- transitions from segment counts (continuous_speech.py:144-164)
+        for m in new_models:
+            states = m.gmm_states
+            for si, st in enumerate(states):
+                if id(st) not in pools:
+                    warnings.warn("No MFCC data for state", UserWarning)
+                    continue
+                spans = pools[id(st)][1]
+                p_jump = len(spans) / sum(b - a for a, b in spans)
+                if si < len(states) - 1:
+                    m.transitions[si + 1, si] = -np.log(p_jump)
+                m.transitions[si, si] = -np.log(1 - p_jump)
+        for i, m in enumerate(new_models):
+            with open(os.path.join(output_path, str(i) + '.pkl'), 'wb') as f:
+                pickle.dump(m, f)
+        if all(nm == om for nm, om in zip(new_models, old_models)):
+            print('Continuous training converged')
+            break
+        old_models = new_models
+        new_models = copy.deepcopy(old_models)
+
+
+__all__ = ["build_state_sequences", "continuous_train"]

@@ -1,0 +1,127 @@
+"""Model layer of the sr.recognition mirror (reference: sr/recognition/hmm.py:8-135).
+
+`HMM` keeps the reference's attributes (`mu`, `sigma`, `transitions`, `segments`, `gmm_states`, `use_gmm`,
+`use_em`) and methods; fitting and evaluation are batched device operations (skmeans / kmeans / GMM.em /
+Viterbi re-alignment from .kmeans and .hmm_state, the fused score+Viterbi classifier for `evaluate`).
+"""
+import numpy as np
+import torch
+
+from . import _ops
+from ._ops import engine
+from .decode import decode_hmm_states, dtw
+from .hmm_state import GMM, mahalanobis
+from .kmeans import _kmeans_device, align_gmm_states, skmeans
+
+
+class HMM:
+    """Left-to-right word model of `n_segments` states (hmm.py:8-55)."""
+
+    def __init__(self, n_segments):
+        self.n_segments = n_segments
+        self.mu = None
+        self.sigma = None
+        self.transitions = None
+        self.segments = []
+        self.gmm_states = None
+        self.use_gmm = True
+        self.use_em = True
+
+    def __eq__(self, other):
+        if not self.use_gmm:
+            return np.allclose(self.mu, other.mu) and np.allclose(self.sigma, other.sigma)
+        if not other.use_gmm or self.n_segments != other.n_segments:
+            return False
+        return all(self.gmm_states[i] == other.gmm_states[i] for i in range(self.n_segments))
+
+    def reset(self):
+        self.mu = self.sigma = self.transitions = self.gmm_states = None
+        self.segments = []
+
+    def __getitem__(self, item):
+        assert self.use_gmm == True  # noqa: E712 (hmm.py:51)
+        if type(item) is int or type(item) is slice:
+            return self.gmm_states[item]
+        raise TypeError('The type of index is not supported')
+
+    def fit(self, ys, n_gaussians, use_gmm=True, use_em=True):
+        """Fit from a list of [T, D] utterances (hmm.py:57-78).  use_gmm=False: one Gaussian per state from
+        segmental K-means; otherwise binary-split K-means (+ EM when use_em) per state."""
+        self.use_em = use_em
+        self.use_gmm = use_gmm
+        if use_gmm:
+            self.fit_GMM(ys, n_gaussians)
+        else:
+            self.mu, self.sigma, self.transitions, self.segments = skmeans(ys, self.n_segments,
+                                                                           return_segmented_data=True)
+        return self
+
+    def _init_gmm(self, n_gaussians):
+        self.gmm_states = [GMM(self.mu[i, :], self.sigma[i, :], n_gaussians) for i in range(self.n_segments)]
+
+    def fit_GMM(self, ys, n_gaussians):
+        """skmeans -> per-state split / K-means / EM -> Viterbi re-alignment (hmm.py:83-95)."""
+        self.mu, self.sigma, self.transitions, self.segments = skmeans(ys, self.n_segments,
+                                                                       return_segmented_data=True)
+        self._init_gmm(n_gaussians)
+        for i in range(len(self.segments)):
+            self._fit_GMM(self.segments[i], n_gaussians, i)
+        self.segments = align_gmm_states(ys, self.gmm_states, self.transitions, self.n_segments)
+
+    def _fit_GMM(self, data, n_gaussians, seg_i):
+        """One state (hmm.py:97-124): int(log(n)) binary splits (natural log, A1); after each split K-means on the
+        x0.9 / x1.1 centroids, weights from cluster counts, then EM over the 2^(i+1) trained components."""
+        n_splits = int(np.log(n_gaussians))
+        assert n_splits > 0
+        Xd = _ops.to_device(data)
+        n = data.shape[0]
+        state = self.gmm_states[seg_i]
+        centroids = np.array([self.mu[seg_i, :]])
+        weights = np.full(n_gaussians, 1 / n)
+        for i in range(n_splits):
+            k = 2 ** (i + 1)
+            centroids = np.concatenate([centroids * 0.9, centroids * 1.1], axis=0)
+            clusters, centroids, variance = _kmeans_device(Xd, data, k, centroids, mahalanobis, 1000)
+            cs, c_counts = np.unique(clusters, return_counts=True)
+            for c in cs:
+                weights[c] = c_counts[c] / n              # indexed by label as in hmm.py:116-118 (A4)
+            state.update_models(centroids, variance, weights[:k])
+            if self.use_em:
+                state._em_device(Xd, k, 10000)
+
+    def evaluate(self, x):
+        """Cost of the best path ending in the last state at the last frame, costs[-1, -1] (hmm.py:126-135)."""
+        if self.use_gmm:
+            return float(self.evaluate_batch([x])[0])
+        costs, _ = dtw(x, self.mu, mahalanobis, self.transitions, self.sigma)
+        return costs[-1, -1]
+
+    def evaluate_batch(self, xs):
+        """evaluate() of many utterances in one launch -> float64 [B]."""
+        return classify([self], xs)[0][:, 0]
+
+
+def classify(models, xs):
+    """The isolated-word test loop (core.py:79-87) for many utterances: every x against every model.
+    -> (costs [B, W] float64, labels [B] int64 = first argmin, strict '<').  Models of up to
+    SRB_DP_MAX_STATES equal-sized GMM states go through the fused score+Viterbi kernel; others through K1 + K2."""
+    S = models[0].n_segments
+    fused = all(m.use_gmm and m.n_segments == S for m in models) and S <= 8 and all(len(x) >= 2 for x in xs)
+    if fused:
+        X, off = _ops.cat_frames(xs)
+        pm = _ops.pack_gmms([s for m in models for s in m.gmm_states])
+        trans = torch.as_tensor(np.stack([np.asarray(m.transitions, np.float64) for m in models])) \
+            .to(pm.ab.device, torch.float32).contiguous()
+        final, label = engine.classify(X, off, pm, trans, len(models), S)
+        return final.double().cpu().numpy(), label.cpu().numpy().astype(np.int64)
+    costs = np.empty((len(xs), len(models)))
+    for w, m in enumerate(models):
+        for u, x in enumerate(xs):
+            if m.use_gmm:
+                costs[u, w] = decode_hmm_states(x, m.gmm_states, m.transitions)[0][-1, -1]
+            else:
+                costs[u, w] = m.evaluate(x)
+    return costs, np.argmin(costs, axis=1)
+
+
+__all__ = ["HMM", "classify"]
