@@ -46,6 +46,7 @@ def parse():
     ap.add_argument("--cpu-utts", type=int, default=0, help="utterances of the CPU sample (0 = auto)")
     ap.add_argument("--no-decode", action="store_true", help="skip the decode sub-benchmark of the em line")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--unfused", action="store_true", help="em: use the separate K1/K2/K5 kernels instead of the fused pass")
     return ap.parse_args()
 
 
@@ -217,48 +218,78 @@ def bench_em(args, ctx):
     N, B = int(X.shape[0]), len(off) - 1
     pm, _ = engine.PackedModel.from_words(ctx["models"])       # private copy: training moves it
     trans_np = np.stack([m[3] for m in ctx["models"]])
-    tr = IsolatedTrainer(X, off, words, pm, trans_np, S_, NCOMP)
+    tr = IsolatedTrainer(X, off, words, pm, trans_np, S_, NCOMP, fused=None if not args.unfused else False)
     sampler = ClockSampler(ctx["local"])
     sampler.start()
     total_ms, per = timed_steps(tr.em_iteration, args.steps, args.warmup, torch, dist, world)
     clocks = sampler.stop()
     mean_cost = tr.mean_cost()
-    # phase breakdown (outside the timed region): CUDA events between the phases of a few more iterations
-    names = ["score", "viterbi", "stats", "allreduce", "mstep"]
-    acc = dict.fromkeys(names, 0.0)
-    reps = 3
-    for _ in range(reps):
-        ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
-        ev[0].record()
-        tr.score()
-        ev[1].record()
-        tr.plan.run(tr.E)
-        ev[2].record()
-        tr.accumulate()
-        ev[3].record()
-        tr.reduce()
-        ev[4].record()
-        tr.update()
-        ev[5].record()
-        torch.cuda.synchronize()
-        for i, k in enumerate(names):
-            acc[k] += ev[i].elapsed_time(ev[i + 1]) / reps
-    # algorithmic HBM bytes per frame of each phase: X = 156 B, E = 4*S, labels 4, back-pointers S
-    bytes_pf = {"score": D_ * 4 + 4 * S_, "viterbi": 4 * S_ + 2 * S_ + 4, "stats": D_ * 4 + 4}
-    dom = max(("score", "viterbi", "stats"), key=lambda k: acc[k])
-    gbs = bytes_pf[dom] * N / (acc[dom] * 1e-3) / 1e9
     pk = peaks()
+    peak_fma = ctx["peak_fma"]
+    if tr.fused:
+        # phase breakdown (outside the timed region): CUDA events around the fused kernel call and the rest
+        names = ["em_fused", "allreduce", "mstep"]
+        acc = dict.fromkeys(names, 0.0)
+        reps = 5
+        for _ in range(reps):
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+            ev[0].record()
+            tr.fused_pass()
+            ev[1].record()
+            tr.reduce()
+            ev[2].record()
+            tr.update()
+            ev[3].record()
+            torch.cuda.synchronize()
+            for i, k in enumerate(names):
+                acc[k] += ev[i].elapsed_time(ev[i + 1]) / reps
+        # algorithmic work of the fused kernel per frame: scoring of the word's S*M Gaussians
+        # (2*D FMA each) + accumulation of the ncomp trained components (2*D FMA each); 156 B of X read once
+        fma_pf = S_ * M_ * 2 * D_ + NCOMP * 2 * D_
+        kern_ms = acc["em_fused"]
+        flops = 2.0 * fma_pf * N / (kern_ms * 1e-3)
+        gbs = (D_ * 4) * N / (kern_ms * 1e-3) / 1e9
+        roof = {"bound": "fp32_fma", "achieved": flops / 1e12, "peak": 2 * peak_fma / 1e12, "unit": "TFLOP/s",
+                "frac": flops / (2 * peak_fma), "traffic": None, "kernel": "em_isolated_kernel<39,5>",
+                "kernel_ms": kern_ms, "peak_source": "srb_fma_peak (FFMA2 probe) measured in this run",
+                "algorithmic": f"{fma_pf} FMA/frame = {S_ * M_} Gaussians x 2*39 scoring + {NCOMP} x 2*39 accumulation; "
+                               f"{D_ * 4} B/frame of X read once",
+                "hbm": {"achieved_gbs": gbs, "peak_gbs": pk.get("hbm_gbs"), "frac": gbs / pk.get("hbm_gbs")},
+                "phase_ms": acc}
+        launches = 6          # em_isolated, reduce_slices, cost sum (torch, 1-2), mstep, pack
+    else:
+        names = ["score", "viterbi", "stats", "allreduce", "mstep"]
+        acc = dict.fromkeys(names, 0.0)
+        reps = 3
+        for _ in range(reps):
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
+            ev[0].record()
+            tr.score()
+            ev[1].record()
+            tr.plan.run(tr.E)
+            ev[2].record()
+            tr.accumulate()
+            ev[3].record()
+            tr.reduce()
+            ev[4].record()
+            tr.update()
+            ev[5].record()
+            torch.cuda.synchronize()
+            for i, k in enumerate(names):
+                acc[k] += ev[i].elapsed_time(ev[i + 1]) / reps
+        bytes_pf = {"score": D_ * 4 + 4 * S_, "viterbi": 4 * S_ + 2 * S_ + 4, "stats": D_ * 4 + 4}
+        dom = max(("score", "viterbi", "stats"), key=lambda k: acc[k])
+        gbs = bytes_pf[dom] * N / (acc[dom] * 1e-3) / 1e9
+        roof = {"bound": "hbm", "achieved": gbs, "peak": pk.get("hbm_gbs"), "unit": "GB/s",
+                "frac": gbs / pk.get("hbm_gbs"), "traffic": None, "kernel": dom, "kernel_ms": acc[dom],
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "source" not in pk else "fallback",
+                "algorithmic": f"{bytes_pf[dom]} B/frame for the {dom} phase", "phase_ms": acc}
+        launches = W_ + 6
     out = {
         "metric": "EM-iteration frames/s (segmental K-means alignment + GMM EM statistics + M-step)",
         "value": world * N * args.steps / (total_ms * 1e-3), "unit": "frames/s", "ms_per_step": total_ms / args.steps,
-        "gpu_launches": args.steps * (W_ + 6),   # 11 score + viterbi + consts + stats + reduce + mstep + pack
-        "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk.get("hbm_gbs"), "unit": "GB/s",
-                     "frac": gbs / pk.get("hbm_gbs"), "traffic": None, "kernel": dom, "kernel_ms": acc[dom],
-                     "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "source" not in pk else "fallback",
-                     "algorithmic": f"{bytes_pf[dom]} B/frame for the {dom} phase", "phase_ms": acc,
-                     "step_bytes_per_frame": sum(bytes_pf.values()),
-                     "step_hbm_frac": sum(bytes_pf.values()) * N / (float(np.mean(per)) * 1e-3) / 1e9 / pk.get("hbm_gbs")},
-        "mean_viterbi_cost": mean_cost, "clocks": clocks,
+        "gpu_launches": args.steps * launches, "roofline": roof,
+        "mean_viterbi_cost": mean_cost, "clocks": clocks, "fused": bool(tr.fused),
     }
     # ---- end to end: the shard comes from pinned host memory every step, the updated model goes back
     Xh = torch.from_numpy(np.ascontiguousarray(tr.X.cpu().numpy())).pin_memory()

@@ -156,6 +156,31 @@ int srb_mstep(const double *stats, int R, int M, int ncomp, int D, double *mu, d
 /* lc[g] = log w_g - 0.5*(D log 2pi + sum_d log var[g,d])  (natural log) */
 int srb_gauss_consts(const double *var, const double *w, int G, int D, double *lc, void *stream);
 
+/* ---- fused isolated-word training pass (BASELINE config 2) ----------------------------------------
+ * One kernel per iteration replaces align_gmm_states (kmeans.py:196-205: decode_hmm_states per utterance,
+ * get_segments_from_path, segment_data) followed by the E-step of GMM.em on every state's pool
+ * (hmm_state.py:122-136): each utterance is scored against the S states of ITS word (packed model, word-major,
+ * R = W*S), Viterbi-aligned (left-to-right transitions with skips of at most 2 states, kmeans.py:53-95; start in
+ * state 0, end in state S-1 at the last frame), and the posterior-weighted moments of the first ncomp components
+ * are accumulated.  X is read from HBM once.
+ *   srb_em_plan   (HOST arrays) groups consecutive utterances of one word into tiles of <= srb_em_tile_frames()
+ *                 frames: tile t = utterances tile_first_utt[t] .. tile_first_utt[t+1]-1 (capacity B+1 ints).
+ *                 utt_word must be non-decreasing; an utterance longer than a tile gives SRB_EUNSUPPORTED (use
+ *                 srb_gmm_score_rows + srb_viterbi_graph + srb_gmm_stats instead).
+ *   srb_em_isolated  partial: caller scratch of srb_em_parts() * W*S*M * srb_stats_row(D) floats, or NULL for an
+ *                 alignment-only call; stats_out double[W*S*M, row] as srb_gmm_stats; optional outputs
+ *                 best_cost[B] (costs[-1,-1] of hmm.py:135, +inf when no path), seg_start int32[B,S] (segment start
+ *                 frames = seg_starts of kmeans.py:200-204), frame_label int32[N] (w*S+s, -1 without a path). */
+int srb_em_tile_frames(void);
+int srb_em_parts(void);
+int srb_em_plan(const int32_t *utt_off_host, const int32_t *utt_word_host, int32_t B, int32_t *tile_first_utt_host,
+                int32_t *ntiles);
+int srb_em_isolated(const float *X, int64_t N, int D, const int32_t *utt_off, const int32_t *utt_word, int32_t B,
+                    const int32_t *tile_first_utt, int32_t ntiles, const float *ab, const float *c, const float *shift,
+                    int W, int S, int M, int Mp, const float *trans, int ncomp, const double *mu, float *partial,
+                    double *stats_out, int accumulate, float *best_cost, int32_t *seg_start, int32_t *frame_label,
+                    void *stream);
+
 /* ---- FP32 FMA peak probe (roofline denominator for K1; not part of the reference path) ----------
  * Runs `iters` dependent-chain-free FMA rounds per thread on every SM and returns elapsed ms through
  * *ms_out (host pointer) plus the FMA count (host pointer).  packed != 0 uses fma.rn.f32x2. */

@@ -20,14 +20,14 @@ struct Frames {
 
 // Stage rows [f0, f0+nf) of X[N,D] into shared memory with 128-bit loads.  Returns the offset (0..3 floats)
 // of row f0 inside xs.  xs must hold TF*D + 4 floats.
-template <int D>
+template <int D, int NTH = NT>
 __device__ __forceinline__ int stage_frames(float *xs, const float *__restrict__ X, int64_t N, int64_t f0, int nf) {
     const int64_t g0 = f0 * D, g1 = (f0 + nf) * D, gend = N * D;
     const int64_t ga = g0 & ~(int64_t)3;
     const int nvec = (int)((g1 - ga + 3) >> 2);
     const float4 *src = reinterpret_cast<const float4 *>(X + ga);
     float4 *dst = reinterpret_cast<float4 *>(xs);
-    for (int i = threadIdx.x; i < nvec; i += NT) {
+    for (int i = threadIdx.x; i < nvec; i += NTH) {
         const int64_t g = ga + 4 * (int64_t)i;
         float4 v;
         if (g + 4 <= gend) {
@@ -45,11 +45,11 @@ __device__ __forceinline__ int stage_frames(float *xs, const float *__restrict__
 
 // shared tile -> registers.  Frame slot k of this thread is local frame threadIdx.x + k*NT; frames past nf
 // read frame 0 (their results are discarded by the caller).
-template <int D>
+template <int D, int NTH = NT>
 __device__ __forceinline__ void load_frames(Frames<D> &fr, const float *xs, int xoff, int nf, const float *shift_s) {
 #pragma unroll
     for (int k = 0; k < FR; ++k) {
-        int lf = threadIdx.x + k * NT;
+        int lf = threadIdx.x + k * NTH;
         if (lf >= nf) lf = 0;
         const float *row = xs + xoff + lf * D;   // stride D words: odd D -> conflict free
 #pragma unroll

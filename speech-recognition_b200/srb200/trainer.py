@@ -77,7 +77,7 @@ class ViterbiPlan:
 class IsolatedTrainer:
     """All W word models trained together on this rank's shard of a word-sorted corpus."""
 
-    def __init__(self, X, off, words, pm, trans, S, ncomp, group=None, var_floor=1e-6):
+    def __init__(self, X, off, words, pm, trans, S, ncomp, group=None, var_floor=1e-6, fused=None):
         """X [N,D] float32, off [B+1], words [B] (numpy, this rank's shard); pm: PackedModel with W*S states;
         trans: [W,S,S] float64 numpy (decode.py:86-87 convention)."""
         X, off, words, self.order = sort_by_word(np.asarray(X), np.asarray(off), words)
@@ -101,6 +101,53 @@ class IsolatedTrainer:
         self.partial = torch.empty(L.srb_stats_parts() * self.G * self.row, dtype=torch.float32, device=self.dev)
         self.lc = torch.empty(self.G, dtype=torch.float64, device=self.dev)
         self.launches_per_iteration = self.W + 1 + 1 + 3 + 2 + 1 + 1
+        # ---- fused pass (srb_em_isolated): one kernel scores, aligns and accumulates; needs left-to-right models
+        # with skips <= 2 (what calc_transition_costs produces, kmeans.py:53-95) and utterances that fit a tile
+        self.fused = False
+        if fused is not False:
+            self.fused = self._plan_fused(off.astype(np.int32), words.astype(np.int32), np.asarray(trans, np.float64))
+            if fused is True and not self.fused:
+                raise ValueError("fused training pass not applicable: " + self.fused_why)
+        if self.fused:
+            self.launches_per_iteration = 1 + 1 + 1 + 2 + 1 + 1   # memset+em+reduce, cost sum (2), mstep, pack
+
+    def _plan_fused(self, off32, words32, trans):
+        import ctypes
+        L = _l.load()
+        S, W = self.S, self.W
+        r, o = np.indices((S, S))
+        if S > 8 or self.ncomp > 8 or np.isfinite(trans[:, (o > r) | (r - o > 2)]).any():
+            self.fused_why = "transitions are not left-to-right with skips <= 2 (or S, ncomp > 8)"
+            return False
+        tiles = np.empty(self.B + 1, np.int32)
+        nt = ctypes.c_int32(0)
+        off32, words32 = np.ascontiguousarray(off32), np.ascontiguousarray(words32)
+        rc = L.srb_em_plan(off32.ctypes.data, words32.ctypes.data, self.B, tiles.ctypes.data, ctypes.byref(nt))
+        if rc != 0:
+            self.fused_why = L.srb_last_error_string().decode()
+            return False
+        self.ntiles = int(nt.value)
+        self.tiles = torch.from_numpy(tiles[:self.ntiles + 1].copy()).to(self.dev)
+        self.words_d = torch.from_numpy(words32).to(self.dev)
+        self.off_d = torch.from_numpy(off32).to(self.dev)
+        self.trans_d = torch.from_numpy(trans.astype(np.float32)).to(self.dev).contiguous()
+        self.em_partial = torch.empty(L.srb_em_parts() * self.G * self.row, dtype=torch.float32, device=self.dev)
+        self.best_cost = torch.empty(max(self.B, 1), dtype=torch.float32, device=self.dev)
+        return True
+
+    def fused_pass(self, seg_start=None, frame_label=None, stats=True):
+        """srb_em_isolated over the shard: statistics body of self.stats (+ best_cost, optional boundaries/labels)."""
+        pm, p = self.pm, _l.ptr
+        body = self.stats[:self.G * self.row]
+        _l.check(_l.load().srb_em_isolated(
+            p(self.X), self.N, pm.D, p(self.off_d), p(self.words_d), self.B, p(self.tiles), self.ntiles, p(pm.ab),
+            p(pm.c), p(pm.shift), self.W, self.S, pm.M, pm.Mp, p(self.trans_d), self.ncomp, p(pm.mu),
+            p(self.em_partial) if stats else None, p(body) if stats else None, 0, p(self.best_cost), p(seg_start),
+            p(frame_label), _l.stream_ptr()))
+        if stats:
+            self.stats[self.G * self.row] = self.best_cost[:self.B].sum(dtype=torch.float64)
+            self.stats[self.G * self.row + 1] = float(self.B)
+        return self.stats
 
     def score(self):
         """K1: each word's contiguous block of frames against that word's S states -> E[N, S]."""
@@ -146,8 +193,11 @@ class IsolatedTrainer:
     def em_iteration(self):
         """One segmental-K-means + EM pass.  Returns the device statistics buffer (last two entries: summed
         Viterbi cost and utterance count over all ranks) without synchronising."""
-        self.align()
-        self.accumulate()
+        if self.fused:
+            self.fused_pass()
+        else:
+            self.align()
+            self.accumulate()
         self.reduce()
         self.update()
         return self.stats

@@ -2,6 +2,8 @@
 import os
 import re
 
+import numpy as np
+
 from conftest import ROOT
 
 
@@ -27,3 +29,23 @@ def test_no_oracle_import_in_product():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dp, f)).read()
                 assert "oracle" not in src, f"{f} mentions the oracle: the product must never route through it"
+
+
+def test_em_plan_rejects_long_and_unsorted():
+    """host-side tile planner of the fused training pass (no CUDA call)"""
+    import ctypes
+    from srb200 import lib
+    L = lib.load()
+    tile = L.srb_em_tile_frames()
+    off = np.array([0, 10, 10 + tile + 1], np.int32)
+    w = np.zeros(2, np.int32)
+    tiles = np.empty(3, np.int32)
+    nt = ctypes.c_int32()
+    assert L.srb_em_plan(off.ctypes.data, w.ctypes.data, 2, tiles.ctypes.data, ctypes.byref(nt)) == -2
+    off = np.array([0, 10, 20, 30], np.int32)
+    w = np.array([1, 0, 0], np.int32)
+    tiles = np.empty(4, np.int32)
+    assert L.srb_em_plan(off.ctypes.data, w.ctypes.data, 3, tiles.ctypes.data, ctypes.byref(nt)) == -1
+    w = np.array([0, 0, 1], np.int32)
+    assert L.srb_em_plan(off.ctypes.data, w.ctypes.data, 3, tiles.ctypes.data, ctypes.byref(nt)) == 0
+    assert nt.value == 2 and list(tiles[:3]) == [0, 2, 3]

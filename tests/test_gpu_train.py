@@ -35,8 +35,9 @@ def oracle_iteration(X, off, words, models, S, ncomp):
     return new, total / len(words)
 
 
+@pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("shuffle", [False, True])
-def test_em_iteration_matches_oracle(shuffle):
+def test_em_iteration_matches_oracle(shuffle, fused):
     from srb200 import engine, synth
     from srb200.trainer import IsolatedTrainer
     W, S, M, ncomp = 4, 5, 4, 2
@@ -47,7 +48,8 @@ def test_em_iteration_matches_oracle(shuffle):
         X, off, words, _ = sort_by_word(X, off, words)
     pm, _ = engine.PackedModel.from_words(models)
     trans = np.stack([m[3] for m in models])
-    tr = IsolatedTrainer(X, off, words, pm, trans, S, ncomp)
+    tr = IsolatedTrainer(X, off, words, pm, trans, S, ncomp, fused=fused)
+    assert tr.fused == fused
     tr.em_iteration()
     ref, mean_cost = oracle_iteration(X, off, words, models, S, ncomp)
     np.testing.assert_allclose(tr.mean_cost(), mean_cost, rtol=RTOL)
@@ -60,3 +62,52 @@ def test_em_iteration_matches_oracle(shuffle):
     c1 = tr.mean_cost()
     tr.em_iteration()
     assert tr.mean_cost() <= c1 + 1e-3
+
+
+@pytest.mark.parametrize("W,S,M,ncomp,skip", [(3, 5, 4, 2, False), (2, 3, 4, 1, False), (2, 8, 8, 4, True),
+                                              (1, 5, 4, 4, True), (2, 6, 4, 2, False)])
+def test_fused_pass_equals_unfused_kernels(W, S, M, ncomp, skip):
+    """srb_em_isolated against the K1 + K2 + K5 kernels it fuses: identical alignments (labels, boundaries),
+    statistics within FP32 accumulation noise; ragged lengths incl. utterances too short to reach the last state."""
+    import torch
+    from srb200 import engine, synth
+    from srb200.trainer import IsolatedTrainer, sort_by_word
+    models, base = synth.make_models(71 + S, W=W, S=S, M=M)
+    if skip:                                   # skip arcs of calc_transition_costs (kmeans.py:85-94, jump 2)
+        models = [(m[0], m[1], m[2], m[3].copy()) for m in models]
+        for m in models:
+            m[3][2, 0] = 1.3
+            m[3][S - 1, S - 3] = 0.7
+    X, off, words = synth.make_utterances(72, base, 90, ragged=(2, 120), noise=0.9)
+    X, off, words, _ = sort_by_word(X, off, words)
+    trans = np.stack([m[3] for m in models])
+    pm_a, _ = engine.PackedModel.from_words(models)
+    pm_b, _ = engine.PackedModel.from_words(models)
+    a = IsolatedTrainer(X, off, words, pm_a, trans, S, ncomp, fused=True)
+    b = IsolatedTrainer(X, off, words, pm_b, trans, S, ncomp, fused=False)
+    seg = torch.zeros((a.B, S), dtype=torch.int32, device="cuda")
+    lab = torch.full((a.N,), -7, dtype=torch.int32, device="cuda")
+    a.fused_pass(seg_start=seg, frame_label=lab)
+    b.align()
+    b.accumulate()
+    la, lb = lab.cpu().numpy(), b.plan.label.cpu().numpy()
+    ca, cb = a.best_cost.cpu().numpy(), b.plan.best_cost.cpu().numpy()
+    assert np.array_equal(np.isfinite(ca), np.isfinite(cb))
+    fin = np.isfinite(cb)
+    assert fin.sum() > 40 and (~fin).sum() > 0
+    np.testing.assert_allclose(ca[fin], cb[fin], rtol=1e-6)
+    # labels: state index within the word in the fused kernel's global numbering w*S+s == graph offset + s
+    assert np.array_equal(la, lb)
+    # boundaries == get_segments_from_path of the K2 labels
+    offn = np.asarray(off, np.int64)
+    sg = seg.cpu().numpy()
+    for u in np.nonzero(fin)[0]:
+        l = lb[offn[u]:offn[u + 1]] - words[u] * S
+        cnt = np.bincount(l, minlength=S)
+        assert np.array_equal(sg[u, 1:], np.cumsum(cnt)[:-1]) and sg[u, 0] == 0
+    G, row = a.G, a.row
+    sa, sb = a.stats[:G * row].cpu().numpy().reshape(G, row), b.stats[:G * row].cpu().numpy().reshape(G, row)
+    scale = np.abs(sb).max(axis=1, keepdims=True) + 1e-30
+    assert np.max(np.abs(sa - sb) / scale) < 2e-5
+    np.testing.assert_allclose(sa[:, 0], sb[:, 0], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(a.stats[-2:].cpu().numpy(), b.stats[-2:].cpu().numpy(), rtol=1e-6)
