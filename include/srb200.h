@@ -164,7 +164,8 @@ int srb_gauss_consts(const double *var, const double *w, int G, int D, double *l
  * state 0, end in state S-1 at the last frame), and the posterior-weighted moments of the first ncomp components
  * are accumulated.  X is read from HBM once.
  *   srb_em_plan   (HOST arrays) groups consecutive utterances of one word into tiles of <= srb_em_tile_frames()
- *                 frames: tile t = utterances tile_first_utt[t] .. tile_first_utt[t+1]-1 (capacity B+1 ints).
+ *                 frames and writes one 16-byte descriptor per tile, int32 {first utterance, first frame, frames,
+ *                 word << 8 | utterances} (capacity 4*B ints; copy it to 16-byte aligned device memory).
  *                 utt_word must be non-decreasing; an utterance longer than a tile gives SRB_EUNSUPPORTED (use
  *                 srb_gmm_score_rows + srb_viterbi_graph + srb_gmm_stats instead).
  *   srb_em_isolated  partial: caller scratch of srb_em_parts() * W*S*M * srb_stats_row(D) floats, or NULL for an
@@ -173,10 +174,10 @@ int srb_gauss_consts(const double *var, const double *w, int G, int D, double *l
  *                 frames = seg_starts of kmeans.py:200-204), frame_label int32[N] (w*S+s, -1 without a path). */
 int srb_em_tile_frames(void);
 int srb_em_parts(void);
-int srb_em_plan(const int32_t *utt_off_host, const int32_t *utt_word_host, int32_t B, int32_t *tile_first_utt_host,
+int srb_em_plan(const int32_t *utt_off_host, const int32_t *utt_word_host, int32_t B, int32_t *tile_desc_host,
                 int32_t *ntiles);
-int srb_em_isolated(const float *X, int64_t N, int D, const int32_t *utt_off, const int32_t *utt_word, int32_t B,
-                    const int32_t *tile_first_utt, int32_t ntiles, const float *ab, const float *c, const float *shift,
+int srb_em_isolated(const float *X, int64_t N, int D, const int32_t *utt_off, int32_t B, const int32_t *tile_desc,
+                    int32_t ntiles, const float *ab, const float *c, const float *shift,
                     int W, int S, int M, int Mp, const float *trans, int ncomp, const double *mu, float *partial,
                     double *stats_out, int accumulate, float *best_cost, int32_t *seg_start, int32_t *frame_label,
                     void *stream);

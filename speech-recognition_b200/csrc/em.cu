@@ -18,6 +18,8 @@
 //      each component's mean, like stats.cu) into per-warp shared partials, flushed to the CTA's private global
 //      slice when the word changes.  No atomics; reduce_partials adds the slices in a fixed order in double.
 // Two CTAs are resident per SM so that one CTA's serial Viterbi phase overlaps the other's FMA-bound scoring.
+#include <type_traits>
+
 #include "score_core.cuh"
 
 namespace srb {
@@ -51,16 +53,43 @@ __host__ __device__ inline EmSmem em_layout(int S, int Mp, int ncomp, int D, boo
     return L;
 }
 
-template <int D, int ST>
+// 16-byte async copies global -> shared (LDGSTS): all of a tile's loads are in flight at once
+__device__ __forceinline__ void cp_async16(void *dst, const void *src) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src));
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory"); }
+
+template <int D, int NTH>
+__device__ __forceinline__ int stage_frames_async(float *xs, const float *__restrict__ X, int64_t N, int64_t f0, int nf) {
+    const int64_t g0 = f0 * D, g1 = (f0 + nf) * D, gend = N * D;
+    const int64_t ga = g0 & ~(int64_t)3;
+    const int nvec = (int)((g1 - ga + 3) >> 2);
+    for (int i = threadIdx.x; i < nvec; i += NTH) {
+        const int64_t g = ga + 4 * (int64_t)i;
+        if (g + 4 <= gend) {
+            cp_async16(xs + 4 * i, X + g);
+        } else {   // last vector of the whole array: do not read past X
+            xs[4 * i + 0] = g + 0 < gend ? X[g + 0] : 0.f;
+            xs[4 * i + 1] = g + 1 < gend ? X[g + 1] : 0.f;
+            xs[4 * i + 2] = g + 2 < gend ? X[g + 2] : 0.f;
+            xs[4 * i + 3] = 0.f;
+        }
+    }
+    return (int)(g0 - ga);
+}
+
+template <int D, int ST, int NC>
 __global__ void __launch_bounds__(ENT, 2)
 em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__restrict__ off,
-                   const int32_t *__restrict__ word, const int32_t *__restrict__ tile_u, int ntiles,
+                   const int4 *__restrict__ tile_desc, int ntiles,
                    const float *__restrict__ ab, const float *__restrict__ c, const float *__restrict__ shift, int S_rt,
-                   int M, int Mp, const float *__restrict__ trans, int ncomp, const double *__restrict__ mu,
+                   int M, int Mp, const float *__restrict__ trans, int ncomp_rt, const double *__restrict__ mu,
                    float *__restrict__ partial, int G, float *__restrict__ best_cost, int32_t *__restrict__ seg_start,
                    int32_t *__restrict__ frame_label) {
     extern __shared__ __align__(16) float smem[];
     const int S = ST ? ST : S_rt;
+    const int ncomp = NC ? NC : ncomp_rt;
     const bool stats = partial != nullptr;
     const EmSmem L = em_layout(S, Mp, ncomp, D, stats);
     float *shift_s = smem, *tr_s = smem + L.tr, *pc = smem + L.pc, *pab = smem + L.pab, *mean_s = smem + L.mean;
@@ -79,11 +108,12 @@ em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__rest
     float *slice = stats ? partial + (size_t)blockIdx.x * G * row : nullptr;
     int cur_w = -1;
 
+    int4 desc = t_lo < t_hi ? __ldg(tile_desc + t_lo) : make_int4(0, 0, 0, 0);
     for (int t = t_lo; t < t_hi; ++t) {
-        const int u0 = tile_u[t], u1 = tile_u[t + 1], nutt = u1 - u0;
-        const int64_t f0 = off[u0];
-        const int nf = (int)(off[u1] - f0);
-        const int w = word[u0];
+        // descriptor {first utterance, first frame, frames, word << 8 | utterances}; the next one is fetched now
+        const int u0 = desc.x, nf = desc.z, nutt = desc.w & 0xff, w = desc.w >> 8;
+        const int64_t f0 = desc.y;
+        if (t + 1 < t_hi) desc = __ldg(tile_desc + t + 1);
         __syncthreads();                                   // previous tile fully consumed
         if (w != cur_w) {
             if (stats && cur_w >= 0) {                     // flush the finished word's statistics (fixed order)
@@ -111,7 +141,8 @@ em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__rest
             cur_w = w;
         }
         for (int i = tid; i <= nutt; i += ENT) uoff[i] = (int)(off[u0 + i] - f0);
-        const int xoff = stage_frames<D, ENT>(xs, X, N, f0, nf);
+        const int xoff = stage_frames_async<D, ENT>(xs, X, N, f0, nf);
+        cp_async_wait_all();
         __syncthreads();
 
         // ---- 1. scoring: E[f][s], natural-log component scores Ps[f][s*Mp + m]
@@ -148,70 +179,65 @@ em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__rest
         }
         __syncthreads();
 
-        // ---- 2. Viterbi, one thread per utterance, threads spread over the warps (decode.py:97-134 for a
-        //         left-to-right model; ties: lowest origin wins like np.argmin)
-        for (int p = (tid & 31) * EWARPS + wq; p < nutt; p += ENT) {
-            const int ts = uoff[p], T = uoff[p + 1] - ts;
-            float cost[ESMAX], a0[ESMAX], a1[ESMAX], a2[ESMAX];
-            int bd[ESMAX][ESMAX];
+        // ---- 2. Viterbi (decode.py:97-134 for a left-to-right model; ties: lowest origin wins like np.argmin).
+        //         8 lanes per utterance (lane = state), 4 utterances per warp, utterances dealt round-robin to the
+        //         warps.  Lane r keeps cost[r] and the boundaries of the best path into r packed one byte each
+        //         (frame index inside the utterance < ETILE = 256); the 1- and 2-state-back candidates come by
+        //         __shfl_up inside the 8-lane group.
+        {
+            using BT = typename std::conditional<(ST > 0 && ST <= 5), uint32_t, uint64_t>::type;
+            const int grp = lane >> 3, r = lane & 7;
+            const float a0 = tr_s[r * ESMAX + r];
+            const float a1 = r >= 1 ? tr_s[r * ESMAX + r - 1] : INF;
+            const float a2 = r >= 2 ? tr_s[r * ESMAX + r - 2] : INF;
+            const BT ones = (BT)0x0101010101010101ull;
+            // byte k-1 holds boundary k; an origin o keeps the bytes < o
+            const BT keep1 = r >= 2 ? (((BT)1 << (8 * (r - 1))) - 1) : (BT)0;
+            const BT keep2 = r >= 3 ? (((BT)1 << (8 * (r - 2))) - 1) : (BT)0;
+            for (int pb = 0; pb < nutt; pb += EWARPS * 4) {
+                const int p = pb + grp * EWARPS + wq;
+                const bool act = p < nutt;
+                const int ts = act ? uoff[p] : 0;
+                const int T = act ? uoff[p + 1] - ts : 0;
+                int Tmax = T;
 #pragma unroll
-            for (int r = 0; r < ESMAX; ++r) {
-                cost[r] = INF;
-                a0[r] = tr_s[r * ESMAX + r];
-                a1[r] = r >= 1 ? tr_s[r * ESMAX + r - 1] : INF;
-                a2[r] = r >= 2 ? tr_s[r * ESMAX + r - 2] : INF;
-#pragma unroll
-                for (int k = 0; k < ESMAX; ++k) bd[r][k] = 0;
-            }
-            const float *Erow = Es + (size_t)ts * ES;
-            if (T > 0) cost[0] = Erow[0];
-            for (int tt = 1; tt < T; ++tt) {
-                Erow += ES;
-#pragma unroll
-                for (int r = ESMAX - 1; r >= 0; --r) {
-                    if (r < S) {
-                        float best;
-                        int src;
-                        if (r >= 2) {
-                            best = cost[r - 2] + a2[r];
-                            src = 2;
-                            const float c1 = cost[r - 1] + a1[r];
-                            if (c1 < best) { best = c1; src = 1; }
-                        } else if (r == 1) {
-                            best = cost[0] + a1[1];
-                            src = 1;
-                        } else {
-                            best = INF;
-                            src = 0;
-                        }
-                        const float c0 = cost[r] + a0[r];
-                        if (r == 0 || c0 < best) { best = c0; src = 0; }
-                        cost[r] = best + Erow[r];
-#pragma unroll
-                        for (int k = 1; k < ESMAX; ++k) {
-                            if (k <= r) {
-                                int v = bd[r][k];
-                                if (src == 1) v = (k <= r - 1) ? bd[r >= 1 ? r - 1 : 0][k] : tt;
-                                if (src == 2) v = (k <= r - 2) ? bd[r >= 2 ? r - 2 : 0][k] : tt;
-                                bd[r][k] = v;
-                            }
-                        }
+                for (int d = 16; d >= 8; d >>= 1) Tmax = max(Tmax, __shfl_xor_sync(0xffffffffu, Tmax, d));
+                const int rr = r < S ? r : 0;
+                const float *Ep = Es + (size_t)ts * ES + rr;
+                float cost = (T > 0 && r == 0) ? Ep[0] : INF;
+                BT bd = 0, rep = 0;
+                float e_next = (T > 1 && r < S) ? Ep[ES] : INF;
+                for (int tt = 1; tt < Tmax; ++tt) {
+                    const float e = e_next;
+                    if (tt + 1 < T && r < S) e_next = Ep[(size_t)(tt + 1) * ES];
+                    const float c1 = __shfl_up_sync(0xffffffffu, cost, 1, 8);
+                    const float c2 = __shfl_up_sync(0xffffffffu, cost, 2, 8);
+                    const BT b1 = __shfl_up_sync(0xffffffffu, bd, 1, 8);
+                    const BT b2 = __shfl_up_sync(0xffffffffu, bd, 2, 8);
+                    // candidates in ascending origin order, strict '<': the lowest origin wins ties (np.argmin)
+                    const float t2 = c2 + a2, t1 = c1 + a1, t0 = cost + a0;
+                    const bool p1 = t1 < t2;
+                    const float b12 = p1 ? t1 : t2;
+                    const bool p0 = t0 < b12;
+                    const float best = p0 ? t0 : b12;
+                    rep += ones;                                       // tt in every byte
+                    const BT inh = p1 ? b1 : b2;                       // boundaries k <= origin are inherited,
+                    const BT keep = p1 ? keep1 : keep2;                // the later ones become tt
+                    const BT nb = p0 ? bd : ((inh & keep) | (rep & ~keep));
+                    if (tt < T) {
+                        cost = best + e;
+                        bd = nb;
                     }
                 }
-            }
-            float fc = INF;
-#pragma unroll
-            for (int r = 0; r < ESMAX; ++r)
-                if (r == S - 1) {
-                    fc = cost[r];
-#pragma unroll
-                    for (int k = 1; k < ESMAX; ++k)
-                        if (k <= r) bnd[p * ESMAX + k] = bd[r][k];
+                if (act && r == S - 1) {
+                    const float fc = cost;
+                    bnd[p * ESMAX] = (fc < INF) ? 0 : -1;      // -1: no path, the utterance's frames are skipped
+                    for (int k = 1; k < S; ++k) bnd[p * ESMAX + k] = (int)((bd >> (8 * (k - 1))) & 0xff);
+                    if (best_cost) best_cost[u0 + p] = fc;
+                    if (seg_start)
+                        for (int k = 0; k < S; ++k)
+                            seg_start[(size_t)(u0 + p) * S + k] = (fc < INF && k) ? (int)((bd >> (8 * (k - 1))) & 0xff) : 0;
                 }
-            bnd[p * ESMAX] = (fc < INF) ? 0 : -1;          // -1: no path, the utterance's frames are skipped
-            if (best_cost) best_cost[u0 + p] = fc;
-            if (seg_start) {
-                for (int k = 0; k < S; ++k) seg_start[(size_t)(u0 + p) * S + k] = (fc < INF && k) ? bnd[p * ESMAX + k] : 0;
             }
         }
         __syncthreads();
@@ -250,7 +276,7 @@ em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__rest
                 if (s != curs) {
                     if (curs >= 0) {
 #pragma unroll
-                        for (int m = 0; m < EMAXC; ++m) {
+                        for (int m = 0; m < (NC ? NC : EMAXC); ++m) {
                             if (m < ncomp) {
                                 float *r = mine + (size_t)(curs * ncomp + m) * row;
                                 if (lane == 0) {
@@ -275,7 +301,7 @@ em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__rest
                     cnt = llsum = 0.f;
                     if (s >= 0) {
 #pragma unroll
-                        for (int m = 0; m < EMAXC; ++m) {
+                        for (int m = 0; m < (NC ? NC : EMAXC); ++m) {
                             s0[m] = a0[m] = a1[m] = q0[m] = q1[m] = 0.f;
                             if (m < ncomp) {
                                 m0[m] = h0 ? mean_s[(s * ncomp + m) * D + d0] : 0.f;
@@ -291,7 +317,7 @@ em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__rest
                     cnt += 1.f;
                     llsum += LLs[f * ES + s];
 #pragma unroll
-                    for (int m = 0; m < EMAXC; ++m)
+                    for (int m = 0; m < (NC ? NC : EMAXC); ++m)
                         if (m < ncomp) {
                             const float p = prow[m];
                             const float e0 = xa - m0[m], e1 = xb - m1[m];
@@ -337,14 +363,14 @@ int srb_em_tile_frames(void) { return ETILE; }
 
 int srb_em_parts(void) { return sm_count() * 2; }
 
-int srb_em_plan(const int32_t *utt_off, const int32_t *utt_word, int32_t B, int32_t *tile_first_utt, int32_t *ntiles) {
-    SRB_REQUIRE(utt_off && utt_word && tile_first_utt && ntiles && B >= 0, SRB_EINVAL, "srb_em_plan: bad argument");
+int srb_em_plan(const int32_t *utt_off, const int32_t *utt_word, int32_t B, int32_t *tile_desc, int32_t *ntiles) {
+    SRB_REQUIRE(utt_off && utt_word && tile_desc && ntiles && B >= 0, SRB_EINVAL, "srb_em_plan: bad argument");
     int nt = 0;
     int32_t u = 0;
     while (u < B) {
         SRB_REQUIRE(u == 0 || utt_word[u] >= utt_word[u - 1], SRB_EINVAL,
                     "srb_em_plan: utterances must be sorted by word (utterance %d)", u);
-        tile_first_utt[nt++] = u;
+        SRB_REQUIRE(utt_word[u] >= 0 && utt_word[u] < (1 << 22), SRB_EINVAL, "srb_em_plan: bad word id");
         const int64_t start = utt_off[u];
         int32_t v = u;
         while (v < B && utt_word[v] == utt_word[u] && (int64_t)utt_off[v + 1] - start <= ETILE && v - u < ENT) {
@@ -352,19 +378,23 @@ int srb_em_plan(const int32_t *utt_off, const int32_t *utt_word, int32_t B, int3
             ++v;
         }
         SRB_REQUIRE(v > u, SRB_EUNSUPPORTED, "srb_em_plan: utterance %d has more than %d frames", u, ETILE);
+        int32_t *d = tile_desc + 4 * (size_t)nt++;
+        d[0] = u;
+        d[1] = utt_off[u];
+        d[2] = utt_off[v] - utt_off[u];
+        d[3] = (utt_word[u] << 8) | (v - u);
         u = v;
     }
-    tile_first_utt[nt] = B;
     *ntiles = nt;
     return SRB_OK;
 }
 
-int srb_em_isolated(const float *X, int64_t N, int D, const int32_t *utt_off, const int32_t *utt_word, int32_t B,
-                    const int32_t *tile_first_utt, int32_t ntiles, const float *ab, const float *c, const float *shift,
+int srb_em_isolated(const float *X, int64_t N, int D, const int32_t *utt_off, int32_t B, const int32_t *tile_desc,
+                    int32_t ntiles, const float *ab, const float *c, const float *shift,
                     int W, int S, int M, int Mp, const float *trans, int ncomp, const double *mu, float *partial,
                     double *stats_out, int accumulate, float *best_cost, int32_t *seg_start, int32_t *frame_label,
                     void *stream) {
-    SRB_REQUIRE(X && utt_off && utt_word && tile_first_utt && ab && c && shift && trans, SRB_EINVAL,
+    SRB_REQUIRE(X && utt_off && tile_desc && ab && c && shift && trans && ((uintptr_t)tile_desc & 15) == 0, SRB_EINVAL,
                 "srb_em_isolated: null pointer");
     SRB_REQUIRE(!partial || (stats_out && mu), SRB_EINVAL, "srb_em_isolated: statistics need stats_out and mu");
     SRB_REQUIRE(W > 0 && S > 0 && S <= ESMAX && M > 0 && Mp >= M && (Mp & 3) == 0, SRB_EUNSUPPORTED,
@@ -382,20 +412,22 @@ int srb_em_isolated(const float *X, int64_t N, int D, const int32_t *utt_off, co
         const size_t bytes = sizeof(float) * (size_t)L.total;
         SRB_REQUIRE(bytes <= (size_t)smem_optin(), SRB_EUNSUPPORTED, "srb_em_isolated: %zu B shared memory needed", bytes);
         const int grid = ntiles < nparts ? ntiles : nparts;
-#define SRB_EM_LAUNCH(kD, kS)                                                                                      \
+#define SRB_EM_LAUNCH(kD, kS, kC)                                                                                  \
     {                                                                                                              \
-        SRB_CUDA(cudaFuncSetAttribute(em_isolated_kernel<kD, kS>, cudaFuncAttributeMaxDynamicSharedMemorySize,     \
+        SRB_CUDA(cudaFuncSetAttribute(em_isolated_kernel<kD, kS, kC>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
                                       (int)bytes));                                                                \
-        em_isolated_kernel<kD, kS><<<grid, ENT, bytes, st>>>(X, N, utt_off, utt_word, tile_first_utt, ntiles, ab,  \
-                                                             c, shift, S, M, Mp, trans, ncomp, mu, partial, G,     \
-                                                             best_cost, seg_start, frame_label);                   \
+        em_isolated_kernel<kD, kS, kC><<<grid, ENT, bytes, st>>>(                                                  \
+            X, N, utt_off, reinterpret_cast<const int4 *>(tile_desc), ntiles, ab, c, shift, S, M, Mp, trans, ncomp, mu, \
+            partial, G, best_cost, seg_start, frame_label);                                                        \
     }
-        // the 5-state model of the reference's scripts (config.py, core.py:48) gets a fully static instantiation
-        if (D == 39 && S == 5) SRB_EM_LAUNCH(39, 5)
-        else if (D == 39 && S == 8) SRB_EM_LAUNCH(39, 8)
-        else if (D == 39) SRB_EM_LAUNCH(39, 0)
-        else if (D == 26) SRB_EM_LAUNCH(26, 0)
-        else if (D == 13) SRB_EM_LAUNCH(13, 0)
+        // the 5-state / 4-Gaussian model of the reference's scripts (config.py, core.py:48; hmm.py:104 trains 2
+        // components) gets a fully static instantiation
+        if (D == 39 && S == 5 && ncomp == 2) SRB_EM_LAUNCH(39, 5, 2)
+        else if (D == 39 && S == 5) SRB_EM_LAUNCH(39, 5, 0)
+        else if (D == 39 && S == 8) SRB_EM_LAUNCH(39, 8, 0)
+        else if (D == 39) SRB_EM_LAUNCH(39, 0, 0)
+        else if (D == 26) SRB_EM_LAUNCH(26, 0, 0)
+        else if (D == 13) SRB_EM_LAUNCH(13, 0, 0)
         else {
             set_error("feature dimension %d not built (13, 26, 39)", D);
             return SRB_EUNSUPPORTED;

@@ -119,7 +119,7 @@ class IsolatedTrainer:
         if S > 8 or self.ncomp > 8 or np.isfinite(trans[:, (o > r) | (r - o > 2)]).any():
             self.fused_why = "transitions are not left-to-right with skips <= 2 (or S, ncomp > 8)"
             return False
-        tiles = np.empty(self.B + 1, np.int32)
+        tiles = np.empty((max(self.B, 1), 4), np.int32)
         nt = ctypes.c_int32(0)
         off32, words32 = np.ascontiguousarray(off32), np.ascontiguousarray(words32)
         rc = L.srb_em_plan(off32.ctypes.data, words32.ctypes.data, self.B, tiles.ctypes.data, ctypes.byref(nt))
@@ -127,8 +127,7 @@ class IsolatedTrainer:
             self.fused_why = L.srb_last_error_string().decode()
             return False
         self.ntiles = int(nt.value)
-        self.tiles = torch.from_numpy(tiles[:self.ntiles + 1].copy()).to(self.dev)
-        self.words_d = torch.from_numpy(words32).to(self.dev)
+        self.tiles = torch.from_numpy(tiles[:max(self.ntiles, 1)].copy()).to(self.dev)
         self.off_d = torch.from_numpy(off32).to(self.dev)
         self.trans_d = torch.from_numpy(trans.astype(np.float32)).to(self.dev).contiguous()
         self.em_partial = torch.empty(L.srb_em_parts() * self.G * self.row, dtype=torch.float32, device=self.dev)
@@ -140,7 +139,7 @@ class IsolatedTrainer:
         pm, p = self.pm, _l.ptr
         body = self.stats[:self.G * self.row]
         _l.check(_l.load().srb_em_isolated(
-            p(self.X), self.N, pm.D, p(self.off_d), p(self.words_d), self.B, p(self.tiles), self.ntiles, p(pm.ab),
+            p(self.X), self.N, pm.D, p(self.off_d), self.B, p(self.tiles), self.ntiles, p(pm.ab),
             p(pm.c), p(pm.shift), self.W, self.S, pm.M, pm.Mp, p(self.trans_d), self.ncomp, p(pm.mu),
             p(self.em_partial) if stats else None, p(body) if stats else None, 0, p(self.best_cost), p(seg_start),
             p(frame_label), _l.stream_ptr()))

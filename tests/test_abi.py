@@ -39,13 +39,12 @@ def test_em_plan_rejects_long_and_unsorted():
     tile = L.srb_em_tile_frames()
     off = np.array([0, 10, 10 + tile + 1], np.int32)
     w = np.zeros(2, np.int32)
-    tiles = np.empty(3, np.int32)
+    tiles = np.empty(12, np.int32)
     nt = ctypes.c_int32()
     assert L.srb_em_plan(off.ctypes.data, w.ctypes.data, 2, tiles.ctypes.data, ctypes.byref(nt)) == -2
     off = np.array([0, 10, 20, 30], np.int32)
     w = np.array([1, 0, 0], np.int32)
-    tiles = np.empty(4, np.int32)
     assert L.srb_em_plan(off.ctypes.data, w.ctypes.data, 3, tiles.ctypes.data, ctypes.byref(nt)) == -1
     w = np.array([0, 0, 1], np.int32)
     assert L.srb_em_plan(off.ctypes.data, w.ctypes.data, 3, tiles.ctypes.data, ctypes.byref(nt)) == 0
-    assert nt.value == 2 and list(tiles[:3]) == [0, 2, 3]
+    assert nt.value == 2 and list(tiles[:8]) == [0, 0, 20, 2, 2, 20, 10, (1 << 8) | 1]
