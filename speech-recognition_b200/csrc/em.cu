@@ -261,72 +261,78 @@ em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__rest
         if (!stats) continue;                              // uniform per CTA: alignment-only call
         __syncthreads();
 
-        // ---- 4. statistics: warp = 64-frame chunk, lanes over dims, runs of equal state in registers
+        // ---- 4. statistics: each warp takes a quarter of the tile's frames and walks it RUN by RUN (a run = the
+        //         frames of one utterance aligned to one state, known from the boundaries), lanes over the feature
+        //         dimensions, the run's moments in registers, one flush per run into the warp's shared partials.
         {
             const int d0 = lane, d1 = lane + 32;
             const bool h0 = d0 < D, h1 = d1 < D;
-            const int c0 = wq * (ETILE / EWARPS), c1 = min(nf, c0 + ETILE / EWARPS);
+            const int chunk = (nf + EWARPS - 1) / EWARPS;
+            const int c0 = wq * chunk, c1 = min(nf, c0 + chunk);
             float *mine = part + (size_t)wq * GW * row;
-            float m0[EMAXC], m1[EMAXC], s0[EMAXC], a0[EMAXC], a1[EMAXC], q0[EMAXC], q1[EMAXC];
-            int curs = -1;
-            float cnt = 0.f, llsum = 0.f;
-            for (int f = c0; f <= c1 && c0 < c1; ++f) {
-                int s = (f < c1) ? (int)lab[f] : -2;
-                if (s == 255) s = -1;
-                if (s != curs) {
-                    if (curs >= 0) {
-#pragma unroll
-                        for (int m = 0; m < (NC ? NC : EMAXC); ++m) {
-                            if (m < ncomp) {
-                                float *r = mine + (size_t)(curs * ncomp + m) * row;
-                                if (lane == 0) {
-                                    r[0] += s0[m];
-                                    if (m == 0) {
-                                        r[2 * D + 1] += cnt;
-                                        r[2 * D + 2] += llsum;
-                                    }
-                                }
-                                if (h0) {
-                                    r[1 + d0] += a0[m];
-                                    r[1 + D + d0] += q0[m];
-                                }
-                                if (h1) {
-                                    r[1 + d1] += a1[m];
-                                    r[1 + D + d1] += q1[m];
-                                }
-                            }
-                        }
-                    }
-                    curs = s;
-                    cnt = llsum = 0.f;
-                    if (s >= 0) {
-#pragma unroll
-                        for (int m = 0; m < (NC ? NC : EMAXC); ++m) {
-                            s0[m] = a0[m] = a1[m] = q0[m] = q1[m] = 0.f;
-                            if (m < ncomp) {
-                                m0[m] = h0 ? mean_s[(s * ncomp + m) * D + d0] : 0.f;
-                                m1[m] = h1 ? mean_s[(s * ncomp + m) * D + d1] : 0.f;
-                            }
-                        }
-                    }
+            constexpr int NCC = NC ? NC : EMAXC;
+            int f = c0;
+            while (f < c1) {
+                int lo = 0, hi = nutt;                         // utterance of frame f (warp uniform)
+                while (hi - lo > 1) {
+                    const int mid = (lo + hi) >> 1;
+                    if (uoff[mid] <= f) lo = mid; else hi = mid;
                 }
-                if (s >= 0) {
-                    const float *x = xs + xoff + f * D;
-                    const float xa = h0 ? x[d0] : 0.f, xb = h1 ? x[d1] : 0.f;
-                    const float *prow = Ps + (size_t)f * PS + s * Mp;
-                    cnt += 1.f;
-                    llsum += LLs[f * ES + s];
+                const int us = uoff[lo], ue = uoff[lo + 1];
+                const int st = lab[f];
+                if (st == 255) {                               // utterance without a path: skipped
+                    f = ue;
+                    continue;
+                }
+                const int rend = (st + 1 < S) ? us + bnd[lo * ESMAX + st + 1] : ue;
+                const int e = min(c1, rend);
+                float m0[NCC], m1[NCC], s0[NCC], a0[NCC], a1[NCC], q0[NCC], q1[NCC];
 #pragma unroll
-                    for (int m = 0; m < (NC ? NC : EMAXC); ++m)
+                for (int m = 0; m < NCC; ++m) {
+                    s0[m] = a0[m] = a1[m] = q0[m] = q1[m] = 0.f;
+                    m0[m] = (m < ncomp && h0) ? mean_s[(st * ncomp + m) * D + d0] : 0.f;
+                    m1[m] = (m < ncomp && h1) ? mean_s[(st * ncomp + m) * D + d1] : 0.f;
+                }
+                float llsum = 0.f;
+                const float cnt = (float)(e - f);
+                const float *xp = xs + xoff + f * D;
+                const float *pp = Ps + (size_t)f * PS + st * Mp;
+                const float *lp = LLs + f * ES + st;
+                for (; f < e; ++f, xp += D, pp += PS, lp += ES) {
+                    const float xa = h0 ? xp[d0] : 0.f, xb = h1 ? xp[d1] : 0.f;
+                    llsum += lp[0];
+#pragma unroll
+                    for (int m = 0; m < NCC; ++m)
                         if (m < ncomp) {
-                            const float p = prow[m];
+                            const float pw = pp[m];
                             const float e0 = xa - m0[m], e1 = xb - m1[m];
-                            s0[m] += p;
-                            a0[m] = fmaf(p, e0, a0[m]);
-                            a1[m] = fmaf(p, e1, a1[m]);
-                            q0[m] = fmaf(p * e0, e0, q0[m]);
-                            q1[m] = fmaf(p * e1, e1, q1[m]);
+                            s0[m] += pw;
+                            a0[m] = fmaf(pw, e0, a0[m]);
+                            a1[m] = fmaf(pw, e1, a1[m]);
+                            q0[m] = fmaf(pw * e0, e0, q0[m]);
+                            q1[m] = fmaf(pw * e1, e1, q1[m]);
                         }
+                }
+#pragma unroll
+                for (int m = 0; m < NCC; ++m) {
+                    if (m < ncomp) {
+                        float *r = mine + (size_t)(st * ncomp + m) * row;
+                        if (lane == 0) {
+                            r[0] += s0[m];
+                            if (m == 0) {
+                                r[2 * D + 1] += cnt;
+                                r[2 * D + 2] += llsum;
+                            }
+                        }
+                        if (h0) {
+                            r[1 + d0] += a0[m];
+                            r[1 + D + d0] += q0[m];
+                        }
+                        if (h1) {
+                            r[1 + d1] += a1[m];
+                            r[1 + D + d1] += q1[m];
+                        }
+                    }
                 }
             }
         }
