@@ -39,7 +39,7 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--workload", default=os.environ.get("SRB_WORKLOAD", "em"), choices=["decode", "em"])
+    ap.add_argument("--workload", default=os.environ.get("SRB_WORKLOAD", "em"), choices=["decode", "em", "connected", "stress", "fb"])
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--utts", type=int, default=100_000, help="utterances per GPU (100 frames each)")
     ap.add_argument("--frames", type=int, default=100)
@@ -307,6 +307,145 @@ def bench_em(args, ctx):
     return out
 
 
+def _roof_fma(fma_pf, N, ms, peak_fma, kernel, note):
+    flops = 2.0 * fma_pf * N / (ms * 1e-3)
+    return {"bound": "fp32_fma", "achieved": flops / 1e12, "peak": 2 * peak_fma / 1e12, "unit": "TFLOP/s",
+            "frac": flops / (2 * peak_fma), "traffic": None, "kernel": kernel, "kernel_ms": ms,
+            "peak_source": "srb_fma_peak (FFMA2 probe) measured in this run", "algorithmic": note}
+
+
+def bench_connected(args, ctx):
+    """Config 4: connected-digit decoding, 7 layers x 11 words (393 states, 847 arcs), 500-frame utterances:
+    K1 scoring of the 55 tied states + K2 graph Viterbi with back-pointers, traceback and paths."""
+    torch, dist, engine = ctx["torch"], ctx["dist"], ctx["engine"]
+    from srb200 import synth
+    from srb200.graph import GraphBatch, word_loop_graph
+    from srb200.trainer import ViterbiPlan
+    B, T, L = args.utts if args.utts != 100_000 else 4096, 500, 7
+    X, off, strings = synth.make_strings(300 + ctx["rank"], ctx["base"], B, L, T)
+    g, word_of = word_loop_graph(np.stack([m[3] for m in ctx["models"]]), L)
+    gb = GraphBatch([g], engine.device())
+    Xd = engine.as_frames(X)
+    N = Xd.shape[0]
+    plan = ViterbiPlan(off, gb, want_path=True, want_label=True)
+    pm = ctx["pm"]
+    E = torch.empty((N, pm.R), dtype=torch.float32, device="cuda")
+    L_ = ctx["lib"]
+
+    def step():
+        L_.check(L_.load().srb_gmm_score(L_.ptr(Xd), N, pm.D, L_.ptr(pm.ab), L_.ptr(pm.c), L_.ptr(pm.shift), pm.R,
+                                         pm.Mp, L_.ptr(E), pm.R, None, None, None, L_.stream_ptr()))
+        plan.run(E)
+
+    sampler = ClockSampler(ctx["local"])
+    sampler.start()
+    total_ms, per = timed_steps(step, args.steps, args.warmup, torch, dist, ctx["world"])
+    clocks = sampler.stop()
+    # decoded strings from the frame labels (main.py:61-67 equivalent): word of the state at each word-slot centre
+    lab = plan.label.cpu().numpy().reshape(B, T)
+    centres = ((np.arange(L) + 0.5) * T / L).astype(int)
+    acc = float((word_of[lab[:, centres]] == strings).mean())
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    ev[0].record()
+    L_.check(L_.load().srb_gmm_score(L_.ptr(Xd), N, pm.D, L_.ptr(pm.ab), L_.ptr(pm.c), L_.ptr(pm.shift), pm.R, pm.Mp,
+                                     L_.ptr(E), pm.R, None, None, None, L_.stream_ptr()))
+    ev[1].record()
+    plan.run(E)
+    ev[2].record()
+    torch.cuda.synchronize()
+    ms = float(np.mean(per))
+    roof = _roof_fma(FMA_PER_FRAME_DECODE, N, ms, ctx["peak_fma"], "score_kernel<39> + viterbi_graph_kernel",
+                     "17160 FMA/frame scoring (55 tied states x 4 x 2*39); DP 847 arcs + 393 states per frame; "
+                     "393 B/frame back-pointers")
+    roof["phase_ms"] = {"score": ev[0].elapsed_time(ev[1]), "viterbi": ev[1].elapsed_time(ev[2])}
+    return {"metric": "decoded frames/s (connected-digit grammar, GMM scoring + graph Viterbi with back-pointers)",
+            "value": ctx["world"] * N * args.steps / (total_ms * 1e-3), "unit": "frames/s",
+            "ms_per_step": total_ms / args.steps, "gpu_launches": 2 * args.steps, "roofline": roof,
+            "digit_accuracy": acc, "clocks": clocks,
+            "_workload": f"connected: 7 layers x 11 words (393 states), {B} utterances x {T} frames per GPU",
+            "_frames": N}
+
+
+def bench_stress(args, ctx):
+    """Config 5: likelihood-only sweep, 2000 tied states x 32 Gaussians x 39 dims; per-frame best state streamed out
+    (the 8 kB/frame cost matrix is never materialised)."""
+    torch, dist, engine = ctx["torch"], ctx["dist"], ctx["engine"]
+    R, M = 2000, 32
+    rng = np.random.default_rng(7)
+    mu = rng.normal(size=(R, 1, D_)) + 0.5 * rng.normal(size=(R, M, D_))
+    var = rng.uniform(0.5, 1.5, size=(R, M, D_))
+    w = rng.dirichlet(np.ones(M), size=R)
+    pm = engine.PackedModel(mu, var, w)
+    N = args.utts * args.frames
+    Xd = torch.randn((N, D_), dtype=torch.float32, device="cuda", generator=torch.Generator("cuda").manual_seed(9))
+    bc = torch.empty(N, dtype=torch.float32, device="cuda")
+    bs = torch.empty(N, dtype=torch.int32, device="cuda")
+    L_ = ctx["lib"]
+
+    def step():
+        L_.check(L_.load().srb_gmm_score(L_.ptr(Xd), N, D_, L_.ptr(pm.ab), L_.ptr(pm.c), L_.ptr(pm.shift), R, pm.Mp,
+                                         None, R, L_.ptr(bc), L_.ptr(bs), None, L_.stream_ptr()))
+
+    sampler = ClockSampler(ctx["local"])
+    sampler.start()
+    total_ms, per = timed_steps(step, args.steps, args.warmup, torch, dist, ctx["world"])
+    clocks = sampler.stop()
+    ms = float(np.mean(per))
+    roof = _roof_fma(R * M * 2 * D_, N, ms, ctx["peak_fma"], "score_kernel<39>", "4.992 M FMA/frame = 64000 Gaussians x 2*39")
+    return {"metric": "GMM-scored frames/s (2000 states x 32 Gaussians, best state per frame)",
+            "value": ctx["world"] * N * args.steps / (total_ms * 1e-3), "unit": "frames/s",
+            "ms_per_step": total_ms / args.steps, "gpu_launches": args.steps, "roofline": roof, "clocks": clocks,
+            "_workload": f"stress: 2000 states x 32 Gaussians, {N} frames per GPU", "_frames": N}
+
+
+def bench_fb(args, ctx):
+    """Config 3 E-step: 8 states x 16 Gaussians per word, ragged 50-300 frame utterances: per-word K1 scoring + K4
+    forward-backward (state posteriors, log-likelihood).  No reference counterpart (parity unpinned)."""
+    torch, dist, engine = ctx["torch"], ctx["dist"], ctx["engine"]
+    from srb200 import synth
+    from srb200.graph import GraphBatch, StateGraph
+    from srb200.trainer import sort_by_word
+    S, M = 8, 16
+    models, base = synth.make_models(11, W=W_, S=S, M=M)
+    B = args.utts if args.utts != 100_000 else 50_000
+    X, off, words = synth.make_utterances(400 + ctx["rank"], base, B, ragged=(50, 300))
+    X, off, words, _ = sort_by_word(X, off, words)
+    pm, _ = engine.PackedModel.from_words(models)
+    Xd = engine.as_frames(X)
+    N = Xd.shape[0]
+    gb = GraphBatch([StateGraph(m[3], np.arange(S)) for m in models], engine.device())
+    E = torch.empty((N, S), dtype=torch.float32, device="cuda")
+    uptr = np.searchsorted(words, np.arange(W_ + 1))
+    rows = [(int(off[uptr[w]]), int(off[uptr[w + 1]])) for w in range(W_)]
+    L_ = ctx["lib"]
+    blk = S * pm.Mp * pm.D * 2
+    offd = engine.as_offsets(off)
+    out = {}
+
+    def step():
+        for w, (r0, r1) in enumerate(rows):
+            if r1 > r0:
+                L_.check(L_.load().srb_gmm_score_rows(L_.ptr(Xd), N, r0, r1 - r0, pm.D, pm.ab[w * blk:].data_ptr(),
+                                                      pm.c[w * S * pm.Mp:].data_ptr(), L_.ptr(pm.shift), S, pm.Mp,
+                                                      L_.ptr(E), S, None, None, None, L_.stream_ptr()))
+        out["fb"] = engine.forward_backward(E, offd, gb, utt_graph=words.astype(np.int32))
+
+    sampler = ClockSampler(ctx["local"])
+    sampler.start()
+    total_ms, per = timed_steps(step, args.steps, args.warmup, torch, dist, ctx["world"])
+    clocks = sampler.stop()
+    gamma, ws, nlz, _ = out["fb"]
+    ms = float(np.mean(per))
+    roof = _roof_fma(S * M * 2 * D_, N, ms, ctx["peak_fma"], "score_kernel<39> x11 + forward_backward_kernel",
+                     "9984 FMA/frame scoring (8 states x 16 x 2*39); 22 log-add arcs per frame, twice")
+    return {"metric": "forward-backward E-step frames/s (8 states x 16 Gaussians, ragged 50-300 frames)",
+            "value": ctx["world"] * N * args.steps / (total_ms * 1e-3), "unit": "frames/s",
+            "ms_per_step": total_ms / args.steps, "gpu_launches": (W_ + 1) * args.steps, "roofline": roof,
+            "mean_neg_log_z_per_frame": float(nlz.sum().item() / N), "clocks": clocks,
+            "_workload": f"fb: 11 words x 8 states x 16 Gaussians, {B} utterances of 50-300 frames per GPU",
+            "_frames": N}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -319,14 +458,30 @@ def run_ours(args):
     from srb200 import engine, synth
     from srb200.trainer import sort_by_word
 
+    from srb200 import lib as lib_
     models, base = synth.make_models(1, W=W_, S=S_, M=M_)
+    pm, trans = engine.PackedModel.from_words(models)
+    peak_fma = max(engine.fma_peak(True, 8192) for _ in range(3))      # FMA/s, measured now on this GPU
+    ctx = {"torch": torch, "dist": dist, "engine": engine, "pm": pm, "trans": trans, "models": models, "base": base,
+           "world": world, "local": local, "rank": rank, "peak_fma": peak_fma, "lib": lib_}
+    extra = {"connected": bench_connected, "stress": bench_stress, "fb": bench_fb}
+    if args.workload in extra:
+        # parity-test configurations of BASELINE.json (configs[2..4]) as optional device-resident sub-benchmarks
+        line = extra[args.workload](args, ctx)
+        wl, N = line.pop("_workload"), line.pop("_frames")
+        line.update({"n_gpus": world, "steps": args.steps, "warmup": args.warmup, "higher_is_better": True,
+                     "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                     "config": {"workload": wl, "frames_per_gpu": N, "l2": "inputs larger than L2",
+                                "parallelism": f"utterance-sharded x{world}, no collective"}})
+        if rank == 0:
+            print(json.dumps(line), flush=True)
+        if world > 1:
+            dist.destroy_process_group()
+        return
     X, off, words = synth.make_utterances(100 + rank, base, args.utts, T=args.frames)
     X, off, words, _ = sort_by_word(X, off, words)
     N, B = int(X.shape[0]), args.utts
-    pm, trans = engine.PackedModel.from_words(models)
-    peak_fma = max(engine.fma_peak(True, 8192) for _ in range(3))      # FMA/s, measured now on this GPU
-    ctx = {"torch": torch, "dist": dist, "engine": engine, "X": X, "off": off, "words": words, "pm": pm,
-           "trans": trans, "models": models, "world": world, "local": local, "peak_fma": peak_fma}
+    ctx.update({"X": X, "off": off, "words": words})
     line = (bench_em if args.workload == "em" else bench_decode)(args, ctx)
     if args.workload == "em" and world == 1 and not args.no_decode:
         d = bench_decode(args, ctx)

@@ -53,32 +53,6 @@ __host__ __device__ inline EmSmem em_layout(int S, int Mp, int ncomp, int D, boo
     return L;
 }
 
-// 16-byte async copies global -> shared (LDGSTS): all of a tile's loads are in flight at once
-__device__ __forceinline__ void cp_async16(void *dst, const void *src) {
-    const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src));
-}
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory"); }
-
-template <int D, int NTH>
-__device__ __forceinline__ int stage_frames_async(float *xs, const float *__restrict__ X, int64_t N, int64_t f0, int nf) {
-    const int64_t g0 = f0 * D, g1 = (f0 + nf) * D, gend = N * D;
-    const int64_t ga = g0 & ~(int64_t)3;
-    const int nvec = (int)((g1 - ga + 3) >> 2);
-    for (int i = threadIdx.x; i < nvec; i += NTH) {
-        const int64_t g = ga + 4 * (int64_t)i;
-        if (g + 4 <= gend) {
-            cp_async16(xs + 4 * i, X + g);
-        } else {   // last vector of the whole array: do not read past X
-            xs[4 * i + 0] = g + 0 < gend ? X[g + 0] : 0.f;
-            xs[4 * i + 1] = g + 1 < gend ? X[g + 1] : 0.f;
-            xs[4 * i + 2] = g + 2 < gend ? X[g + 2] : 0.f;
-            xs[4 * i + 3] = 0.f;
-        }
-    }
-    return (int)(g0 - ga);
-}
-
 template <int D, int ST, int NC>
 __global__ void __launch_bounds__(ENT, 2)
 em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__restrict__ off,

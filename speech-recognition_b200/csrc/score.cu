@@ -30,7 +30,8 @@ score_kernel(const float *__restrict__ X, int64_t N, int64_t row0, int64_t nrows
         const int64_t f0 = row0 + tile * TF;
         const int nf = (int)min((int64_t)TF, row0 + nrows - f0);
         __syncthreads();
-        const int xoff = stage_frames<D>(xs, X, N, f0, nf);
+        const int xoff = stage_frames_async<D, NT>(xs, X, N, f0, nf);
+        cp_async_wait_all();
         __syncthreads();
         Frames<D> fr;
         load_frames<D>(fr, xs, xoff, nf, shift_s);
@@ -145,7 +146,8 @@ classify_kernel(const float *__restrict__ X, const int32_t *__restrict__ off, in
         const int nf = (int)min((int64_t)TF, fend - cf0);
         const int64_t cf1 = cf0 + nf;
         __syncthreads();
-        const int xoff = stage_frames<D>(xs, X, N, cf0, nf);
+        const int xoff = stage_frames_async<D, NT>(xs, X, N, cf0, nf);
+        cp_async_wait_all();
         __syncthreads();
         Frames<D> fr;
         load_frames<D>(fr, xs, xoff, nf, shift_s);

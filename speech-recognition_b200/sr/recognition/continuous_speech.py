@@ -144,4 +144,29 @@ def continuous_train(data, models, label_seqs, output_path, n_gaussians=4, n_seg
         new_models = copy.deepcopy(old_models)
 
 
-__all__ = ["build_state_sequences", "continuous_train"]
+def path_to_models(path, seq):
+    """main.py:61-67: reversed path -> forward state rows, consecutive duplicates removed, split at the
+    non-emitting states, first state of every piece mapped to the index of the model that owns it
+    (`state.parent`, set by core.py:107-109, else looked up by position in `seq`)."""
+    rows = np.asarray(path)[:, 0][::-1]
+    if rows.size == 0:
+        return []
+    rows = rows[np.concatenate([[True], rows[1:] != rows[:-1]])]
+    nes = np.array([type(seq[r]) is NES for r in rows])
+    first = ~nes & np.concatenate([[True], nes[:-1]])           # first emitting state after a NES (or at the start)
+    return [seq[r].parent for r in rows[first]]
+
+
+def recognize_strings(xs, models, n_layers=7):
+    """Connected-word recognition of many utterances (main.py:35,59-67): every model allowed in each of
+    `n_layers` layers, one batched scoring + graph-Viterbi launch, word strings from the paths."""
+    for i, m in enumerate(models):
+        for s in m.gmm_states:
+            if s.parent is None:
+                s.parent = i
+    seq, trans, ends = build_state_sequences(models, [list(range(len(models)))] * n_layers)
+    res = decode_batch(xs, [(seq, trans, ends)], want_path=True)
+    return [path_to_models(p, seq) for p in res.paths()]
+
+
+__all__ = ["build_state_sequences", "continuous_train", "path_to_models", "recognize_strings"]

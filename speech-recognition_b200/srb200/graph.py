@@ -95,3 +95,30 @@ class GraphBatch:
 
     def __getitem__(self, k):
         return self.dev[k]
+
+
+def word_loop_graph(word_trans, n_layers):
+    """The connected-word grammar of main.py:35 / continuous_speech.py:13-53 as a StateGraph: layers of all W words
+    between non-emitting states; emit[r] = w*S + s (column of the tied state), -1 for the NES.
+    -> (StateGraph, word_of_state[R] with -1 at the NES)"""
+    word_trans = np.asarray(word_trans, np.float64)
+    W, S, _ = word_trans.shape
+    R = 1 + n_layers * (W * S + 1)
+    tr = np.full((R, R), np.inf)
+    emit = np.full(R, -1, np.int32)
+    word_of = np.full(R, -1, np.int32)
+    entry, ends = 0, []
+    for layer in range(n_layers):
+        base = 1 + layer * (W * S + 1)
+        exit_ = base + W * S
+        ends = []
+        for w in range(W):
+            o = base + w * S
+            tr[o:o + S, o:o + S] = word_trans[w]
+            emit[o:o + S] = w * S + np.arange(S)
+            word_of[o:o + S] = w
+            tr[o, entry] = 0.0
+            tr[exit_, o + S - 1] = 0.0
+            ends.append(o + S - 1)
+        entry = exit_
+    return StateGraph(tr, emit, end_states=ends), word_of

@@ -57,3 +57,22 @@ def make_utterances(seed, base, n_utts, T=100, noise=0.7, ragged=None, dtype=np.
 
 def split_utts(X, off):
     return [X[off[i]:off[i + 1]] for i in range(len(off) - 1)]
+
+
+def make_strings(seed, base, n_utts, n_words=7, T=500, noise=0.7):
+    """Connected utterances (BASELINE config 4): n_words random words back to back, T frames in total, each word
+    walking left-to-right through its state means.  -> (X[N,dim] float32, off[B+1] int32, strings[B,n_words])"""
+    rng = np.random.default_rng(seed)
+    W, S, dim = base.shape
+    strings = rng.integers(0, W, size=(n_utts, n_words))
+    t = np.arange(T)
+    word_pos = np.minimum(t * n_words // T, n_words - 1)                 # word slot of every frame
+    w_start = (np.arange(n_words) * T + n_words - 1) // n_words
+    w_len = np.diff(np.append(w_start, T))
+    seg = np.minimum((t - w_start[word_pos]) * S // w_len[word_pos], S - 1)
+    X = base[strings[:, word_pos], seg[None, :]].reshape(n_utts * T, dim).astype(np.float32)
+    step = 1 << 20
+    for i in range(0, X.shape[0], step):
+        X[i:i + step] += noise * rng.standard_normal(size=(min(step, X.shape[0] - i), dim), dtype=np.float32)
+    off = (np.arange(n_utts + 1) * T).astype(np.int32)
+    return X, off, strings

@@ -101,6 +101,14 @@ def case_graph_decode(rec, G):
         assert np.array_equal(np.isfinite(costs), f)
         close(costs[f], ref[f])
         assert np.array_equal(path, z["gr_paths"][z["gr_paths_off"][u]:z["gr_paths_off"][u + 1]])
+    # main.py:61-67 post-processing: the decoded word strings (the synthetic strings are recognised correctly)
+    for i, m in enumerate(models):
+        for s in m.gmm_states:
+            s.parent = i
+    ref_strings = [rec.path_to_models(z["gr_paths"][z["gr_paths_off"][u]:z["gr_paths_off"][u + 1]], seq)
+                   for u in range(len(xs))]
+    assert rec.recognize_strings(xs, models, n_layers=3) == ref_strings
+    assert ref_strings == [list(s) for s in z["gr_strings"]]
 
 
 def case_dtw_helpers(rec, G):
