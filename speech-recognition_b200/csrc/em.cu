@@ -44,7 +44,7 @@ __host__ __device__ inline EmSmem em_layout(int S, int Mp, int ncomp, int D, boo
     L.xs = o;   o += ETILE * D + 4;
     L.es = o;   o += ETILE * (S | 1);
     L.ps = o;   o += ETILE * ((S * Mp) | 1);
-    L.ll = o;   o += ETILE * (S | 1);
+    L.ll = o;   o += ETILE;
     L.part = o; o += stats ? EWARPS * S * ncomp * (2 * D + 3) : 0;
     L.bnd = o;  o += ENT * ESMAX;
     L.uoff = o; o += ENT + 4;
@@ -132,24 +132,6 @@ em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__rest
 #pragma unroll
                 for (int k = 0; k < FR; ++k) Es[(tid + k * ENT) * ES + s] = cost[k];
             }
-            // posteriors over the first ncomp components (hmm_state.py:126-136, log domain); thread-private rows
-#pragma unroll
-            for (int k = 0; k < FR; ++k) {
-                float *prow = Ps + (size_t)(tid + k * ENT) * PS;
-                for (int s = 0; s < S; ++s) {
-                    float mx = -INF;
-                    for (int m = 0; m < ncomp; ++m) mx = fmaxf(mx, prow[s * Mp + m]);
-                    float den = 0.f;
-                    for (int m = 0; m < ncomp; ++m) {
-                        const float e = (mx > -INF) ? __expf(prow[s * Mp + m] - mx) : 0.f;
-                        prow[s * Mp + m] = e;
-                        den += e;
-                    }
-                    const float inv = den > 0.f ? 1.f / den : 0.f;
-                    for (int m = 0; m < ncomp; ++m) prow[s * Mp + m] *= inv;
-                    LLs[(tid + k * ENT) * ES + s] = den > 0.f ? mx + __logf(den) : 0.f;
-                }
-            }
         }
         __syncthreads();
 
@@ -169,7 +151,8 @@ em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__rest
             const BT keep1 = r >= 2 ? (((BT)1 << (8 * (r - 1))) - 1) : (BT)0;
             const BT keep2 = r >= 3 ? (((BT)1 << (8 * (r - 2))) - 1) : (BT)0;
             for (int pb = 0; pb < nutt; pb += EWARPS * 4) {
-                const int p = pb + grp * EWARPS + wq;
+                if (pb + wq * 4 >= nutt) break;                       // warp uniform: nothing left for this warp
+                const int p = pb + wq * 4 + grp;
                 const bool act = p < nutt;
                 const int ts = act ? uoff[p] : 0;
                 const int T = act ? uoff[p + 1] - ts : 0;
@@ -231,6 +214,21 @@ em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__rest
             }
             lab[f] = (unsigned char)s;
             if (frame_label) frame_label[f0 + f] = (s == 255) ? -1 : w * S + s;
+            if (stats && s != 255) {
+                // posteriors over the first ncomp components of the ALIGNED state (hmm_state.py:126-136, log domain)
+                float *prow = Ps + (size_t)f * PS + s * Mp;
+                float mx = -INF;
+                for (int m = 0; m < ncomp; ++m) mx = fmaxf(mx, prow[m]);
+                float den = 0.f;
+                for (int m = 0; m < ncomp; ++m) {
+                    const float e = (mx > -INF) ? __expf(prow[m] - mx) : 0.f;
+                    prow[m] = e;
+                    den += e;
+                }
+                const float inv = den > 0.f ? 1.f / den : 0.f;
+                for (int m = 0; m < ncomp; ++m) prow[m] *= inv;
+                LLs[f] = den > 0.f ? mx + __logf(den) : 0.f;
+            }
         }
         if (!stats) continue;                              // uniform per CTA: alignment-only call
         __syncthreads();
@@ -271,8 +269,8 @@ em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__rest
                 const float cnt = (float)(e - f);
                 const float *xp = xs + xoff + f * D;
                 const float *pp = Ps + (size_t)f * PS + st * Mp;
-                const float *lp = LLs + f * ES + st;
-                for (; f < e; ++f, xp += D, pp += PS, lp += ES) {
+                const float *lp = LLs + f;
+                for (; f < e; ++f, xp += D, pp += PS, ++lp) {
                     const float xa = h0 ? xp[d0] : 0.f, xb = h1 ? xp[d1] : 0.f;
                     llsum += lp[0];
 #pragma unroll
