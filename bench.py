@@ -32,6 +32,15 @@ import numpy as np  # noqa: E402
 W_, S_, M_, D_ = 11, 5, 4, 39
 NCOMP = int(np.log(M_)) and 2 ** int(np.log(M_))   # hmm.py:104: n_splits = int(np.log(4)) = 1 -> 2 trained components
 FMA_PER_FRAME_DECODE = W_ * S_ * M_ * 2 * D_          # 17 160 FMA per frame (all 11 words scored)
+# DRAM bytes per frame of the two headline kernels, from the committed `ncu --set full` captures
+# (dram__bytes_read.sum + dram__bytes_write.sum over a 2 M-frame launch; algorithmic: 156 B/frame of X + outputs)
+NCU_TRAFFIC_PER_FRAME = {"classify_kernel<39>": (318.694e6 / 2e6, "profiles/r01_ncu_classify_v3_raw.csv"),
+                         "em_isolated_kernel<39,5,2>": (317.632e6 / 2e6, "profiles/r01_ncu_emfused_v3_raw.csv")}
+
+
+def ncu_traffic(kernel, frames):
+    per, src = NCU_TRAFFIC_PER_FRAME[kernel]
+    return {"traffic": per * frames, "traffic_source": f"{per:.1f} B/frame x frames per launch, {src}"}
 
 
 def parse():
@@ -188,7 +197,7 @@ def bench_decode(args, ctx):
         "value": world * N * args.steps / (total_ms * 1e-3), "unit": "frames/s", "ms_per_step": total_ms / args.steps,
         "gpu_launches": args.steps,          # one fused classify_kernel launch per step
         "roofline": {"bound": "fp32_fma", "achieved": flops / 1e12, "peak": 2 * peak_fma / 1e12,
-                     "unit": "TFLOP/s", "frac": flops / (2 * peak_fma), "traffic": None,
+                     "unit": "TFLOP/s", "frac": flops / (2 * peak_fma), **ncu_traffic("classify_kernel<39>", N),
                      "kernel": "classify_kernel<39>", "kernel_ms": kern_ms,
                      "peak_source": "srb_fma_peak (FFMA2 probe) measured in this run",
                      "algorithmic": "17160 FMA/frame = 220 Gaussians x 2*39 (SURVEY 8d)",
@@ -250,7 +259,8 @@ def bench_em(args, ctx):
         flops = 2.0 * fma_pf * N / (kern_ms * 1e-3)
         gbs = (D_ * 4) * N / (kern_ms * 1e-3) / 1e9
         roof = {"bound": "fp32_fma", "achieved": flops / 1e12, "peak": 2 * peak_fma / 1e12, "unit": "TFLOP/s",
-                "frac": flops / (2 * peak_fma), "traffic": None, "kernel": "em_isolated_kernel<39,5>",
+                "frac": flops / (2 * peak_fma), **ncu_traffic("em_isolated_kernel<39,5,2>", N),
+                "kernel": "em_isolated_kernel<39,5,2>",
                 "kernel_ms": kern_ms, "peak_source": "srb_fma_peak (FFMA2 probe) measured in this run",
                 "algorithmic": f"{fma_pf} FMA/frame = {S_ * M_} Gaussians x 2*39 scoring + {NCOMP} x 2*39 accumulation; "
                                f"{D_ * 4} B/frame of X read once",
