@@ -110,6 +110,7 @@ def cpu_decode(models, base, n_utts, frames, steps=1, warmup=0):
     utterances, linear-domain emissions like hmm_state.py:36-45) on a bounded sample.  -> (frames/s, cores, ms)"""
     from oracle import oracle as orc
     from srb200 import synth
+    orc.set_num_threads()
     X, off, _ = synth.make_utterances(2, base, n_utts, T=frames)
     X64, off64 = X.astype(np.float64), off.astype(np.int64)
     for _ in range(warmup):
@@ -128,6 +129,7 @@ def cpu_em(models, base, n_utts, frames, steps=1, warmup=0):
     OpenMP over utterances, then one GMM.em iteration per tied state) on a bounded sample."""
     from oracle import oracle as orc
     from srb200 import synth
+    orc.set_num_threads()
     X, off, words = synth.make_utterances(2, base, n_utts, T=frames)
     X64, off64 = X.astype(np.float64), off.astype(np.int64)
     for _ in range(warmup):

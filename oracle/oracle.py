@@ -64,6 +64,13 @@ def num_threads():
     return int(lib().orc_num_threads())
 
 
+def set_num_threads(n=None):
+    """Use n (default: all host cores) OpenMP threads regardless of OMP_NUM_THREADS (torchrun sets it to 1)."""
+    import os
+    lib().orc_set_num_threads(int(n or os.cpu_count() or 1))
+    return num_threads()
+
+
 # ------------------------------------------------------------------------------------ emission (a2,a3,a6)
 def gmm_evaluate(X, mu, cov, w, log_domain=False):
     """hmm_state.py:114-120 for a batch of frames -> (cost[N], comps[N,M]).

@@ -472,3 +472,13 @@ int orc_num_threads(void) {
     return 1;
 #endif
 }
+
+/* thread count of the OpenMP loops (torchrun exports OMP_NUM_THREADS=1; the CPU baseline wants all host cores) */
+void orc_set_num_threads(int n) {
+#ifdef _OPENMP
+    extern void omp_set_num_threads(int);
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
