@@ -163,8 +163,8 @@ int srb_gauss_consts(const double *var, const double *w, int G, int D, double *l
  * R = W*S), Viterbi-aligned (left-to-right transitions with skips of at most 2 states, kmeans.py:53-95; start in
  * state 0, end in state S-1 at the last frame), and the posterior-weighted moments of the first ncomp components
  * are accumulated.  X is read from HBM once.
- *   srb_em_plan   (HOST arrays) groups consecutive utterances of one word into tiles of <= srb_em_tile_frames()
- *                 frames and writes one 16-byte descriptor per tile, int32 {first utterance, first frame, frames,
+ *   srb_em_plan   (HOST arrays) groups consecutive utterances of one word into tiles of *tile_frames frames
+ *                 (128 when no utterance is longer, else srb_em_tile_frames() = 256; pass it on to srb_em_isolated) and writes one 16-byte descriptor per tile, int32 {first utterance, first frame, frames,
  *                 word << 8 | utterances} (capacity 4*B ints; copy it to 16-byte aligned device memory).
  *                 utt_word must be non-decreasing; an utterance longer than a tile gives SRB_EUNSUPPORTED (use
  *                 srb_gmm_score_rows + srb_viterbi_graph + srb_gmm_stats instead).
@@ -175,9 +175,9 @@ int srb_gauss_consts(const double *var, const double *w, int G, int D, double *l
 int srb_em_tile_frames(void);
 int srb_em_parts(void);
 int srb_em_plan(const int32_t *utt_off_host, const int32_t *utt_word_host, int32_t B, int32_t *tile_desc_host,
-                int32_t *ntiles);
+                int32_t *ntiles, int32_t *tile_frames);
 int srb_em_isolated(const float *X, int64_t N, int D, const int32_t *utt_off, int32_t B, const int32_t *tile_desc,
-                    int32_t ntiles, const float *ab, const float *c, const float *shift,
+                    int32_t ntiles, int32_t tile_frames, const float *ab, const float *c, const float *shift,
                     int W, int S, int M, int Mp, const float *trans, int ncomp, const double *mu, float *partial,
                     double *stats_out, int accumulate, float *best_cost, int32_t *seg_start, int32_t *frame_label,
                     void *stream);

@@ -17,16 +17,20 @@
 //   4. accumulates [S0, S1, S2, count, loglik] rows with the lanes over the feature dimensions (moments about
 //      each component's mean, like stats.cu) into per-warp shared partials, flushed to the CTA's private global
 //      slice when the word changes.  No atomics; reduce_partials adds the slices in a fixed order in double.
-// Two CTAs are resident per SM so that one CTA's serial Viterbi phase overlaps the other's FMA-bound scoring.
+// The scorer runs at ONE frame per thread here (~128 registers): 16 warps are resident per SM (4 CTAs of 128
+// threads, or 2 of 256 when an utterance is longer than 128 frames), so one CTA's serial Viterbi phase overlaps the
+// others' scoring and statistics.
+#include <algorithm>
 #include <type_traits>
 
 #include "score_core.cuh"
 
 namespace srb {
 
-constexpr int ENT = 128;             // threads per CTA
-constexpr int ETILE = ENT * FR;      // frames per tile
-constexpr int EWARPS = ENT / 32;
+constexpr int EFR = 1;               // frames per thread (1: ~128 registers -> 16 warps per SM)
+constexpr int ETILE_MAX = 256;       // threads per CTA = frames per tile: 128 (4 CTAs/SM) or 256 (2 CTAs/SM)
+constexpr int EUTT = 32;             // utterances per tile
+constexpr int EPARTS = 4;            // private statistics slices per SM (= CTAs per SM at the small tile)
 constexpr int ESMAX = SRB_DP_MAX_STATES;
 constexpr int EMAXC = 8;             // trained components per state handled in registers
 
@@ -34,7 +38,8 @@ struct EmSmem {                      // offsets in floats into the dynamic share
     int tr, pc, pab, mean, xs, es, ps, ll, part, bnd, uoff, lab, total;
 };
 
-__host__ __device__ inline EmSmem em_layout(int S, int Mp, int ncomp, int D, bool stats) {
+__host__ __device__ inline EmSmem em_layout(int S, int Mp, int ncomp, int D, bool stats, int ETILE) {
+    const int EWARPS = ETILE / 32;
     EmSmem L;
     int o = 64;                                           // shift_s
     L.tr = o;   o += ESMAX * ESMAX;
@@ -43,18 +48,18 @@ __host__ __device__ inline EmSmem em_layout(int S, int Mp, int ncomp, int D, boo
     L.mean = o; o += (S * ncomp * D + 3) & ~3;
     L.xs = o;   o += ETILE * D + 4;
     L.es = o;   o += ETILE * (S | 1);
-    L.ps = o;   o += ETILE * ((S * Mp) | 1);
+    L.ps = o;   o += ETILE * ((S * ncomp) | 1);
     L.ll = o;   o += ETILE;
     L.part = o; o += stats ? EWARPS * S * ncomp * (2 * D + 3) : 0;
-    L.bnd = o;  o += ENT * ESMAX;
-    L.uoff = o; o += ENT + 4;
+    L.bnd = o;  o += EUTT * ESMAX;
+    L.uoff = o; o += EUTT + 4;
     L.lab = o;  o += ETILE / 4;
     L.total = o;
     return L;
 }
 
-template <int D, int ST, int NC>
-__global__ void __launch_bounds__(ENT, 2)
+template <int D, int ST, int NC, int ENT>
+__global__ void __launch_bounds__(ENT, 512 / ENT)
 em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__restrict__ off,
                    const int4 *__restrict__ tile_desc, int ntiles,
                    const float *__restrict__ ab, const float *__restrict__ c, const float *__restrict__ shift, int S_rt,
@@ -65,12 +70,13 @@ em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__rest
     const int S = ST ? ST : S_rt;
     const int ncomp = NC ? NC : ncomp_rt;
     const bool stats = partial != nullptr;
-    const EmSmem L = em_layout(S, Mp, ncomp, D, stats);
+    constexpr int ETILE = ENT * EFR, EWARPS = ENT / 32;
+    const EmSmem L = em_layout(S, Mp, ncomp, D, stats, ETILE);
     float *shift_s = smem, *tr_s = smem + L.tr, *pc = smem + L.pc, *pab = smem + L.pab, *mean_s = smem + L.mean;
     float *xs = smem + L.xs, *Es = smem + L.es, *Ps = smem + L.ps, *LLs = smem + L.ll, *part = smem + L.part;
     int *bnd = reinterpret_cast<int *>(smem + L.bnd), *uoff = reinterpret_cast<int *>(smem + L.uoff);
     unsigned char *lab = reinterpret_cast<unsigned char *>(smem + L.lab);
-    const int ES = S | 1, PS = (S * Mp) | 1, row = 2 * D + 3, GW = S * ncomp;
+    const int ES = S | 1, PS = (S * ncomp) | 1, row = 2 * D + 3, GW = S * ncomp;
     const int tid = threadIdx.x, lane = tid & 31, wq = tid >> 5;
     const int nblk = Mp >> 2;
     const float INF = CUDART_INF_F;
@@ -121,16 +127,16 @@ em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__rest
 
         // ---- 1. scoring: E[f][s], natural-log component scores Ps[f][s*Mp + m]
         {
-            Frames<D> fr;
-            load_frames<D, ENT>(fr, xs, xoff, nf, shift_s);
+            Frames<D, EFR> fr;
+            load_frames<D, ENT, EFR>(fr, xs, xoff, nf, shift_s);
             for (int s = 0; s < S; ++s) {
-                float cost[FR];
-                float *crow[FR];
+                float cost[EFR];
+                float *crow[EFR];
 #pragma unroll
-                for (int k = 0; k < FR; ++k) crow[k] = Ps + (size_t)(tid + k * ENT) * PS + s * Mp;
-                score_state<D>(fr, pab + (size_t)s * Mp * D * 2, pc + s * Mp, nblk, cost, crow, true);
+                for (int k = 0; k < EFR; ++k) crow[k] = Ps + (size_t)(tid + k * ENT) * PS + s * ncomp;
+                score_state<D, EFR>(fr, pab + (size_t)s * Mp * D * 2, pc + s * Mp, nblk, cost, crow, true, ncomp);
 #pragma unroll
-                for (int k = 0; k < FR; ++k) Es[(tid + k * ENT) * ES + s] = cost[k];
+                for (int k = 0; k < EFR; ++k) Es[(tid + k * ENT) * ES + s] = cost[k];
             }
         }
         __syncthreads();
@@ -216,7 +222,7 @@ em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__rest
             if (frame_label) frame_label[f0 + f] = (s == 255) ? -1 : w * S + s;
             if (stats && s != 255) {
                 // posteriors over the first ncomp components of the ALIGNED state (hmm_state.py:126-136, log domain)
-                float *prow = Ps + (size_t)f * PS + s * Mp;
+                float *prow = Ps + (size_t)f * PS + s * ncomp;
                 float mx = -INF;
                 for (int m = 0; m < ncomp; ++m) mx = fmaxf(mx, prow[m]);
                 float den = 0.f;
@@ -268,7 +274,7 @@ em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__rest
                 float llsum = 0.f;
                 const float cnt = (float)(e - f);
                 const float *xp = xs + xoff + f * D;
-                const float *pp = Ps + (size_t)f * PS + st * Mp;
+                const float *pp = Ps + (size_t)f * PS + st * ncomp;
                 const float *lp = LLs + f;
                 for (; f < e; ++f, xp += D, pp += PS, ++lp) {
                     const float xa = h0 ? xp[d0] : 0.f, xb = h1 ? xp[d1] : 0.f;
@@ -337,12 +343,18 @@ using namespace srb;
 
 extern "C" {
 
-int srb_em_tile_frames(void) { return ETILE; }
+int srb_em_tile_frames(void) { return ETILE_MAX; }
 
-int srb_em_parts(void) { return sm_count() * 2; }
+int srb_em_parts(void) { return sm_count() * EPARTS; }
 
-int srb_em_plan(const int32_t *utt_off, const int32_t *utt_word, int32_t B, int32_t *tile_desc, int32_t *ntiles) {
-    SRB_REQUIRE(utt_off && utt_word && tile_desc && ntiles && B >= 0, SRB_EINVAL, "srb_em_plan: bad argument");
+int srb_em_plan(const int32_t *utt_off, const int32_t *utt_word, int32_t B, int32_t *tile_desc, int32_t *ntiles,
+                int32_t *tile_frames) {
+    SRB_REQUIRE(utt_off && utt_word && tile_desc && ntiles && tile_frames && B >= 0, SRB_EINVAL,
+                "srb_em_plan: bad argument");
+    int64_t longest = 0;
+    for (int32_t u = 0; u < B; ++u) longest = std::max<int64_t>(longest, (int64_t)utt_off[u + 1] - utt_off[u]);
+    const int ETILE = longest <= ETILE_MAX / 2 ? ETILE_MAX / 2 : ETILE_MAX;   // small tiles: 4 CTAs per SM
+    *tile_frames = ETILE;
     int nt = 0;
     int32_t u = 0;
     while (u < B) {
@@ -351,7 +363,7 @@ int srb_em_plan(const int32_t *utt_off, const int32_t *utt_word, int32_t B, int3
         SRB_REQUIRE(utt_word[u] >= 0 && utt_word[u] < (1 << 22), SRB_EINVAL, "srb_em_plan: bad word id");
         const int64_t start = utt_off[u];
         int32_t v = u;
-        while (v < B && utt_word[v] == utt_word[u] && (int64_t)utt_off[v + 1] - start <= ETILE && v - u < ENT) {
+        while (v < B && utt_word[v] == utt_word[u] && (int64_t)utt_off[v + 1] - start <= ETILE && v - u < EUTT) {
             SRB_REQUIRE(utt_off[v + 1] > utt_off[v], SRB_EUNSUPPORTED, "srb_em_plan: empty utterance %d", v);
             ++v;
         }
@@ -368,7 +380,7 @@ int srb_em_plan(const int32_t *utt_off, const int32_t *utt_word, int32_t B, int3
 }
 
 int srb_em_isolated(const float *X, int64_t N, int D, const int32_t *utt_off, int32_t B, const int32_t *tile_desc,
-                    int32_t ntiles, const float *ab, const float *c, const float *shift,
+                    int32_t ntiles, int32_t tile_frames, const float *ab, const float *c, const float *shift,
                     int W, int S, int M, int Mp, const float *trans, int ncomp, const double *mu, float *partial,
                     double *stats_out, int accumulate, float *best_cost, int32_t *seg_start, int32_t *frame_label,
                     void *stream) {
@@ -382,21 +394,28 @@ int srb_em_isolated(const float *X, int64_t N, int D, const int32_t *utt_off, in
     const int sms = sm_count();
     SRB_REQUIRE(sms > 0, SRB_ENODEVICE, "no CUDA device");
     const int G = W * S * M, row = 2 * D + 3;
-    const int nparts = sms * 2;
+    SRB_REQUIRE(tile_frames == ETILE_MAX || tile_frames == ETILE_MAX / 2, SRB_EINVAL,
+                "srb_em_isolated: tile_frames must come from srb_em_plan");
+    const int nparts = sms * EPARTS;
     cudaStream_t st = (cudaStream_t)stream;
     if (partial) SRB_CUDA(cudaMemsetAsync(partial, 0, sizeof(float) * (size_t)nparts * G * row, st));
     if (B > 0 && ntiles > 0) {
-        const EmSmem L = em_layout(S, Mp, ncomp, D, partial != nullptr);
+        const EmSmem L = em_layout(S, Mp, ncomp, D, partial != nullptr, tile_frames);
         const size_t bytes = sizeof(float) * (size_t)L.total;
         SRB_REQUIRE(bytes <= (size_t)smem_optin(), SRB_EUNSUPPORTED, "srb_em_isolated: %zu B shared memory needed", bytes);
-        const int grid = ntiles < nparts ? ntiles : nparts;
-#define SRB_EM_LAUNCH(kD, kS, kC)                                                                                  \
+        const int ctas = sms * (512 / tile_frames);
+        const int grid = ntiles < ctas ? ntiles : ctas;
+#define SRB_EM_LAUNCH_T(kD, kS, kC, kT)                                                                            \
     {                                                                                                              \
-        SRB_CUDA(cudaFuncSetAttribute(em_isolated_kernel<kD, kS, kC>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
-                                      (int)bytes));                                                                \
-        em_isolated_kernel<kD, kS, kC><<<grid, ENT, bytes, st>>>(                                                  \
+        SRB_CUDA(cudaFuncSetAttribute(em_isolated_kernel<kD, kS, kC, kT>,                                          \
+                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));                   \
+        em_isolated_kernel<kD, kS, kC, kT><<<grid, kT, bytes, st>>>(                                               \
             X, N, utt_off, reinterpret_cast<const int4 *>(tile_desc), ntiles, ab, c, shift, S, M, Mp, trans, ncomp, mu, \
             partial, G, best_cost, seg_start, frame_label);                                                        \
+    }
+#define SRB_EM_LAUNCH(kD, kS, kC)                                                                                  \
+    {                                                                                                              \
+        if (tile_frames == 128) SRB_EM_LAUNCH_T(kD, kS, kC, 128) else SRB_EM_LAUNCH_T(kD, kS, kC, 256)             \
     }
         // the 5-state / 4-Gaussian model of the reference's scripts (config.py, core.py:48; hmm.py:104 trains 2
         // components) gets a fully static instantiation
@@ -411,6 +430,7 @@ int srb_em_isolated(const float *X, int64_t N, int D, const int32_t *utt_off, in
             return SRB_EUNSUPPORTED;
         }
 #undef SRB_EM_LAUNCH
+#undef SRB_EM_LAUNCH_T
     }
     if (partial) {
         const int64_t len = (int64_t)G * row;

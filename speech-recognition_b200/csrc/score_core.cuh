@@ -13,9 +13,9 @@ constexpr int NT = 256;        // threads per CTA of the scorer
 constexpr int FR = 2;          // frames per thread
 constexpr int TF = NT * FR;    // frames per tile
 
-template <int D>
+template <int D, int FRN = FR>
 struct Frames {
-    float2 xx[FR][D];          // (x'^2, x')
+    float2 xx[FRN][D];         // (x'^2, x')
 };
 
 // Stage rows [f0, f0+nf) of X[N,D] into shared memory with 128-bit loads.  Returns the offset (0..3 floats)
@@ -71,10 +71,10 @@ __device__ __forceinline__ int stage_frames_async(float *xs, const float *__rest
 
 // shared tile -> registers.  Frame slot k of this thread is local frame threadIdx.x + k*NT; frames past nf
 // read frame 0 (their results are discarded by the caller).
-template <int D, int NTH = NT>
-__device__ __forceinline__ void load_frames(Frames<D> &fr, const float *xs, int xoff, int nf, const float *shift_s) {
+template <int D, int NTH = NT, int FRN = FR>
+__device__ __forceinline__ void load_frames(Frames<D, FRN> &fr, const float *xs, int xoff, int nf, const float *shift_s) {
 #pragma unroll
-    for (int k = 0; k < FR; ++k) {
+    for (int k = 0; k < FRN; ++k) {
         int lf = threadIdx.x + k * NTH;
         if (lf >= nf) lf = 0;
         const float *row = xs + xoff + lf * D;   // stride D words: odd D -> conflict free
@@ -88,19 +88,19 @@ __device__ __forceinline__ void load_frames(Frames<D> &fr, const float *xs, int 
 
 // log2-domain scores of the 4 Gaussians of one packed block for the thread's FR frames.
 // pab: shared, float4[D][2] = (A0,B0,A1,B1),(A2,B2,A3,B3) per dim; pc: shared float[4].
-template <int D>
-__device__ __forceinline__ void score_block4(const Frames<D> &fr, const float4 *__restrict__ pab,
-                                             const float *__restrict__ pc, float (&l)[FR][4]) {
-    float2 acc[FR][4];
+template <int D, int FRN = FR>
+__device__ __forceinline__ void score_block4(const Frames<D, FRN> &fr, const float4 *__restrict__ pab,
+                                             const float *__restrict__ pc, float (&l)[FRN][4]) {
+    float2 acc[FRN][4];
 #pragma unroll
-    for (int k = 0; k < FR; ++k)
+    for (int k = 0; k < FRN; ++k)
 #pragma unroll
         for (int j = 0; j < 4; ++j) acc[k][j] = make_float2(0.f, 0.f);
 #pragma unroll
     for (int d = 0; d < D; ++d) {
         const float4 p01 = pab[2 * d], p23 = pab[2 * d + 1];
 #pragma unroll
-        for (int k = 0; k < FR; ++k) {
+        for (int k = 0; k < FRN; ++k) {
             acc[k][0] = ffma2(fr.xx[k][d], make_float2(p01.x, p01.y), acc[k][0]);
             acc[k][1] = ffma2(fr.xx[k][d], make_float2(p01.z, p01.w), acc[k][1]);
             acc[k][2] = ffma2(fr.xx[k][d], make_float2(p23.x, p23.y), acc[k][2]);
@@ -109,7 +109,7 @@ __device__ __forceinline__ void score_block4(const Frames<D> &fr, const float4 *
     }
     const float4 cc = *reinterpret_cast<const float4 *>(pc);
 #pragma unroll
-    for (int k = 0; k < FR; ++k) {
+    for (int k = 0; k < FRN; ++k) {
         l[k][0] = acc[k][0].x + acc[k][0].y + cc.x;
         l[k][1] = acc[k][1].x + acc[k][1].y + cc.y;
         l[k][2] = acc[k][2].x + acc[k][2].y + cc.z;
@@ -119,24 +119,25 @@ __device__ __forceinline__ void score_block4(const Frames<D> &fr, const float4 *
 
 // cost (natural-log units) of one state = -ln sum_m 2^l_m over its Mp/4 blocks (online log-sum-exp).
 // comp (optional, global) receives ln(w_m N_m(x)) per Gaussian: comp_row[k] points at this state's Mp floats.
-template <int D>
-__device__ __forceinline__ void score_state(const Frames<D> &fr, const float *__restrict__ pab_state,
-                                            const float *__restrict__ pc_state, int nblk, float (&cost)[FR],
-                                            float *const (&comp_row)[FR], bool want_comp) {
-    float mrun[FR], srun[FR];
+template <int D, int FRN = FR>
+__device__ __forceinline__ void score_state(const Frames<D, FRN> &fr, const float *__restrict__ pab_state,
+                                            const float *__restrict__ pc_state, int nblk, float (&cost)[FRN],
+                                            float *const (&comp_row)[FRN], bool want_comp, int nstore = 1 << 30) {
+    float mrun[FRN], srun[FRN];
 #pragma unroll
-    for (int k = 0; k < FR; ++k) {
+    for (int k = 0; k < FRN; ++k) {
         mrun[k] = -CUDART_INF_F;
         srun[k] = 0.f;
     }
     for (int b = 0; b < nblk; ++b) {
-        float l[FR][4];
-        score_block4<D>(fr, reinterpret_cast<const float4 *>(pab_state) + (size_t)b * D * 2, pc_state + 4 * b, l);
+        float l[FRN][4];
+        score_block4<D, FRN>(fr, reinterpret_cast<const float4 *>(pab_state) + (size_t)b * D * 2, pc_state + 4 * b, l);
 #pragma unroll
-        for (int k = 0; k < FR; ++k) {
+        for (int k = 0; k < FRN; ++k) {
             if (want_comp && comp_row[k]) {
 #pragma unroll
-                for (int j = 0; j < 4; ++j) comp_row[k][4 * b + j] = l[k][j] * LN2_F;
+                for (int j = 0; j < 4; ++j)
+                    if (4 * b + j < nstore) comp_row[k][4 * b + j] = l[k][j] * LN2_F;
             }
             const float m4 = fmaxf(fmaxf(l[k][0], l[k][1]), fmaxf(l[k][2], l[k][3]));
             const float mn = fmaxf(mrun[k], m4);
@@ -148,7 +149,7 @@ __device__ __forceinline__ void score_state(const Frames<D> &fr, const float *__
         }
     }
 #pragma unroll
-    for (int k = 0; k < FR; ++k) cost[k] = -LN2_F * (mrun[k] + lg2(srun[k]));   // s == 0 -> +inf like -log(0)
+    for (int k = 0; k < FRN; ++k) cost[k] = -LN2_F * (mrun[k] + lg2(srun[k]));   // s == 0 -> +inf like -log(0)
 }
 
 // cooperative copy of `nfloats` (multiple of 4, 16-byte aligned both sides) global -> shared

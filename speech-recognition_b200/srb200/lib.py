@@ -36,8 +36,8 @@ SIGNATURES = {
     "srb_gauss_consts": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "srb_em_tile_frames": (c_int, []),
     "srb_em_parts": (c_int, []),
-    "srb_em_plan": (c_int, [c_void_p, c_void_p, c_i32, c_void_p, ctypes.POINTER(c_i32)]),
-    "srb_em_isolated": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_i32, c_void_p, c_i32, c_void_p, c_void_p,
+    "srb_em_plan": (c_int, [c_void_p, c_void_p, c_i32, c_void_p, ctypes.POINTER(c_i32), ctypes.POINTER(c_i32)]),
+    "srb_em_isolated": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_i32, c_void_p, c_i32, c_i32, c_void_p, c_void_p,
                                 c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
                                 c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "srb_fma_peak": (c_int, [c_int, c_int, ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_double), c_void_p]),

@@ -120,13 +120,14 @@ class IsolatedTrainer:
             self.fused_why = "transitions are not left-to-right with skips <= 2 (or S, ncomp > 8)"
             return False
         tiles = np.empty((max(self.B, 1), 4), np.int32)
-        nt = ctypes.c_int32(0)
+        nt, tf = ctypes.c_int32(0), ctypes.c_int32(0)
         off32, words32 = np.ascontiguousarray(off32), np.ascontiguousarray(words32)
-        rc = L.srb_em_plan(off32.ctypes.data, words32.ctypes.data, self.B, tiles.ctypes.data, ctypes.byref(nt))
+        rc = L.srb_em_plan(off32.ctypes.data, words32.ctypes.data, self.B, tiles.ctypes.data, ctypes.byref(nt),
+                           ctypes.byref(tf))
         if rc != 0:
             self.fused_why = L.srb_last_error_string().decode()
             return False
-        self.ntiles = int(nt.value)
+        self.ntiles, self.tile_frames = int(nt.value), int(tf.value)
         self.tiles = torch.from_numpy(tiles[:max(self.ntiles, 1)].copy()).to(self.dev)
         self.off_d = torch.from_numpy(off32).to(self.dev)
         self.trans_d = torch.from_numpy(trans.astype(np.float32)).to(self.dev).contiguous()
@@ -139,7 +140,7 @@ class IsolatedTrainer:
         pm, p = self.pm, _l.ptr
         body = self.stats[:self.G * self.row]
         _l.check(_l.load().srb_em_isolated(
-            p(self.X), self.N, pm.D, p(self.off_d), self.B, p(self.tiles), self.ntiles, p(pm.ab),
+            p(self.X), self.N, pm.D, p(self.off_d), self.B, p(self.tiles), self.ntiles, self.tile_frames, p(pm.ab),
             p(pm.c), p(pm.shift), self.W, self.S, pm.M, pm.Mp, p(self.trans_d), self.ncomp, p(pm.mu),
             p(self.em_partial) if stats else None, p(body) if stats else None, 0, p(self.best_cost), p(seg_start),
             p(frame_label), _l.stream_ptr()))

@@ -40,11 +40,11 @@ def test_em_plan_rejects_long_and_unsorted():
     off = np.array([0, 10, 10 + tile + 1], np.int32)
     w = np.zeros(2, np.int32)
     tiles = np.empty(12, np.int32)
-    nt = ctypes.c_int32()
-    assert L.srb_em_plan(off.ctypes.data, w.ctypes.data, 2, tiles.ctypes.data, ctypes.byref(nt)) == -2
+    nt, tf = ctypes.c_int32(), ctypes.c_int32()
+    assert L.srb_em_plan(off.ctypes.data, w.ctypes.data, 2, tiles.ctypes.data, ctypes.byref(nt), ctypes.byref(tf)) == -2
     off = np.array([0, 10, 20, 30], np.int32)
     w = np.array([1, 0, 0], np.int32)
-    assert L.srb_em_plan(off.ctypes.data, w.ctypes.data, 3, tiles.ctypes.data, ctypes.byref(nt)) == -1
+    assert L.srb_em_plan(off.ctypes.data, w.ctypes.data, 3, tiles.ctypes.data, ctypes.byref(nt), ctypes.byref(tf)) == -1
     w = np.array([0, 0, 1], np.int32)
-    assert L.srb_em_plan(off.ctypes.data, w.ctypes.data, 3, tiles.ctypes.data, ctypes.byref(nt)) == 0
-    assert nt.value == 2 and list(tiles[:8]) == [0, 0, 20, 2, 2, 20, 10, (1 << 8) | 1]
+    assert L.srb_em_plan(off.ctypes.data, w.ctypes.data, 3, tiles.ctypes.data, ctypes.byref(nt), ctypes.byref(tf)) == 0
+    assert tf.value == 128 and nt.value == 2 and list(tiles[:8]) == [0, 0, 20, 2, 2, 20, 10, (1 << 8) | 1]

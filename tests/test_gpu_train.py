@@ -64,9 +64,10 @@ def test_em_iteration_matches_oracle(shuffle, fused):
     assert tr.mean_cost() <= c1 + 1e-3
 
 
-@pytest.mark.parametrize("W,S,M,ncomp,skip", [(3, 5, 4, 2, False), (2, 3, 4, 1, False), (2, 8, 8, 4, True),
-                                              (1, 5, 4, 4, True), (2, 6, 4, 2, False)])
-def test_fused_pass_equals_unfused_kernels(W, S, M, ncomp, skip):
+@pytest.mark.parametrize("W,S,M,ncomp,skip,lens", [(3, 5, 4, 2, False, (2, 120)), (2, 3, 4, 1, False, (2, 120)),
+                                                   (2, 8, 8, 4, True, (2, 120)), (1, 5, 4, 4, True, (2, 120)),
+                                                   (2, 6, 4, 2, False, (2, 120)), (3, 5, 4, 2, True, (3, 250))])
+def test_fused_pass_equals_unfused_kernels(W, S, M, ncomp, skip, lens):
     """srb_em_isolated against the K1 + K2 + K5 kernels it fuses: identical alignments (labels, boundaries),
     statistics within FP32 accumulation noise; ragged lengths incl. utterances too short to reach the last state."""
     import torch
@@ -78,12 +79,13 @@ def test_fused_pass_equals_unfused_kernels(W, S, M, ncomp, skip):
         for m in models:
             m[3][2, 0] = 1.3
             m[3][S - 1, S - 3] = 0.7
-    X, off, words = synth.make_utterances(72, base, 90, ragged=(2, 120), noise=0.9)
+    X, off, words = synth.make_utterances(72, base, 90, ragged=lens, noise=0.9)
     X, off, words, _ = sort_by_word(X, off, words)
     trans = np.stack([m[3] for m in models])
     pm_a, _ = engine.PackedModel.from_words(models)
     pm_b, _ = engine.PackedModel.from_words(models)
     a = IsolatedTrainer(X, off, words, pm_a, trans, S, ncomp, fused=True)
+    assert a.tile_frames == (128 if lens[1] <= 128 else 256)
     b = IsolatedTrainer(X, off, words, pm_b, trans, S, ncomp, fused=False)
     seg = torch.zeros((a.B, S), dtype=torch.int32, device="cuda")
     lab = torch.full((a.N,), -7, dtype=torch.int32, device="cuda")
