@@ -129,7 +129,7 @@ em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__rest
         {
             Frames<D, EFR> fr;
             load_frames<D, ENT, EFR>(fr, xs, xoff, nf, shift_s);
-            for (int s = 0; s < S; ++s) {
+            for (int s = 0; s < S && (tid & ~31) < nf; ++s) {          // warps past the tile's last frame skip
                 float cost[EFR];
                 float *crow[EFR];
 #pragma unroll
