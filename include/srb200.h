@@ -141,6 +141,17 @@ int srb_group_stats(const float *X, int64_t N, int D, const int32_t *label, int 
 int srb_gmm_stats(const float *X, int64_t N, int D, const int32_t *label, int R, int M, int ncomp, const double *mu,
                   const double *var, const double *lc, float *partial, double *out, int accumulate, void *stream);
 
+/* Baum-Welch (soft-count) variant for rows [row0, row0+nrows) of X that belong to ONE word model: gamma float[N, S]
+ * state posteriors of that word's S states from srb_forward_backward (ws_off[u] = utt_off[u]*S), mu/var/lc/out
+ * already offset to the word's first state (rows [S*M]).  Group (s, m) gets weight gamma[n,s] * p_m; `count` of a
+ * state = sum of its gamma, so srb_mstep's w = S0/count is the soft update.  States with gamma <= gmin are skipped.
+ * partial: srb_stats_parts()/8 * S*M * srb_stats_row(D) floats suffice (srb_stats_parts() * ... always does).
+ * The reference has no soft counts: parity unpinned, defined to reduce to srb_gmm_stats when gamma
+ * is the 0/1 indicator of the Viterbi alignment. */
+int srb_gmm_stats_soft(const float *X, int64_t N, int64_t row0, int64_t nrows, int D, const float *gamma, int S, int M,
+                       int ncomp, const double *mu, const double *var, const double *lc, double gmin, float *partial,
+                       double *out, int accumulate, void *stream);
+
 /* local distances to S templates Y double[S,D]: kind 0 = Euclidean norm (kmeans.py:111), kind 1 =
  * mahalanobis(x, y_s, var_s) (hmm_state.py:48-58) with var double[S, var_stride>=D or 0 for one shared row]
  * (kmeans.py:183 uses cov[0] for every centroid -> var_stride 0).  out float[N,ldo] and/or argmin_out int32[N]

@@ -176,6 +176,93 @@ gmm_stats_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t *_
     }
 }
 
+// ---- soft mode (Baum-Welch): frames [row0, row0+nrows) belong to ONE word whose S states carry the posteriors
+// gamma[n, s] (K4).  Group (s, m) receives weight gamma[n,s] * p_m with p_m the within-state posterior over the
+// first ncomp components (same log-domain arithmetic as gmm_stats_kernel).  States with gamma below `gmin` are
+// skipped (a left-to-right model puts almost all mass on one or two states per frame).  Each warp owns a private
+// [S*ncomp, row] block of shared memory (plain read-modify-write, no atomics, deterministic); the CTA adds its
+// warps' blocks in a fixed order into its private global slice, laid out [S*M, row] like the final statistics.
+__global__ void __launch_bounds__(SW * 32)
+gmm_stats_soft_kernel(const float *__restrict__ X, int64_t row0, int64_t nrows, int D, const float *__restrict__ gamma,
+                      int S, int M, int ncomp, const double *__restrict__ mu, const double *__restrict__ var,
+                      const double *__restrict__ lc, float gmin, float *__restrict__ partial) {
+    extern __shared__ float ssm[];
+    const int row = 2 * D + 3, GW = S * ncomp;
+    float *mean_s = ssm, *hiv_s = mean_s + GW * D, *lc_s = hiv_s + GW * D, *part = lc_s + ((GW + 3) & ~3);
+    const int lane = threadIdx.x & 31, wq = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < GW * D; i += blockDim.x) {
+        const int s = i / (ncomp * D), m = (i / D) % ncomp, d = i % D;
+        const size_t g = (size_t)s * M + m;
+        mean_s[i] = (float)mu[g * D + d];
+        hiv_s[i] = (float)(-0.5 / var[g * D + d]);
+    }
+    for (int i = threadIdx.x; i < GW; i += blockDim.x) lc_s[i] = (float)lc[(size_t)(i / ncomp) * M + i % ncomp];
+    for (int i = threadIdx.x; i < SW * GW * row; i += blockDim.x) part[i] = 0.f;
+    __syncthreads();
+    float *mine = part + (size_t)wq * GW * row;
+    const int d0 = lane, d1 = lane + 32;
+    const bool h0 = d0 < D, h1 = d1 < D;
+    const int64_t wg = (int64_t)blockIdx.x * SW + wq, nw = (int64_t)gridDim.x * SW;
+    for (int64_t c0 = wg * SCH; c0 < nrows; c0 += nw * SCH) {
+        const int64_t c1 = min(nrows, c0 + SCH);
+        for (int64_t n = row0 + c0; n < row0 + c1; ++n) {
+            const float xa = h0 ? X[n * D + d0] : 0.f, xb = h1 ? X[n * D + d1] : 0.f;
+            for (int s = 0; s < S; ++s) {
+                const float g = gamma[n * S + s];
+                if (!(g > gmin)) continue;                               // warp uniform
+                float ll[MAXC], e0[MAXC], e1[MAXC];
+                float mx = -CUDART_INF_F;
+#pragma unroll
+                for (int m = 0; m < MAXC; ++m) {
+                    if (m < ncomp) {
+                        const int o = (s * ncomp + m) * D;
+                        e0[m] = h0 ? xa - mean_s[o + d0] : 0.f;
+                        e1[m] = h1 ? xb - mean_s[o + d1] : 0.f;
+                        const float part_ll = (h0 ? e0[m] * e0[m] * hiv_s[o + d0] : 0.f) +
+                                              (h1 ? e1[m] * e1[m] * hiv_s[o + d1] : 0.f);
+                        ll[m] = wsum(part_ll) + lc_s[s * ncomp + m];
+                        mx = fmaxf(mx, ll[m]);
+                    }
+                }
+                float den = 0.f;
+#pragma unroll
+                for (int m = 0; m < MAXC; ++m)
+                    if (m < ncomp) {
+                        ll[m] = (mx > -CUDART_INF_F) ? __expf(ll[m] - mx) : 0.f;
+                        den += ll[m];
+                    }
+                const float inv = den > 0.f ? g / den : 0.f;
+#pragma unroll
+                for (int m = 0; m < MAXC; ++m)
+                    if (m < ncomp) {
+                        const float p = ll[m] * inv;
+                        float *r = mine + (size_t)(s * ncomp + m) * row;
+                        if (lane == 0) {
+                            r[0] += p;
+                            if (m == 0) r[2 * D + 1] += g;
+                        }
+                        if (h0) {
+                            r[1 + d0] = fmaf(p, e0[m], r[1 + d0]);
+                            r[1 + D + d0] = fmaf(p * e0[m], e0[m], r[1 + D + d0]);
+                        }
+                        if (h1) {
+                            r[1 + d1] = fmaf(p, e1[m], r[1 + d1]);
+                            r[1 + D + d1] = fmaf(p * e1[m], e1[m], r[1 + D + d1]);
+                        }
+                    }
+            }
+        }
+    }
+    __syncthreads();
+    float *slice = partial + (size_t)blockIdx.x * S * M * row;
+    for (int i = threadIdx.x; i < GW * row; i += blockDim.x) {
+        float t = 0.f;
+        for (int q = 0; q < SW; ++q) t += part[(size_t)q * GW * row + i];
+        const int gi = i / row, j = i - gi * row;
+        slice[(size_t)((gi / ncomp) * M + gi % ncomp) * row + j] = t;
+    }
+}
+
 // out[i] (+)= sum_p partial[p][i]  in double, fixed order
 __global__ void reduce_partials_kernel(const float *__restrict__ partial, int64_t nparts, int64_t len,
                                        double *__restrict__ out, int accumulate) {
@@ -315,6 +402,31 @@ int srb_gmm_stats(const float *X, int64_t N, int D, const int32_t *label, int R,
     SRB_CUDA(cudaMemsetAsync(partial, 0, sizeof(float) * len * parts, st));
     if (N > 0) gmm_stats_kernel<<<grid, SW * 32, 0, st>>>(X, N, D, label, M, ncomp, mu, var, lc, partial, G);
     reduce_partials_kernel<<<(int)((len + 255) / 256), 256, 0, st>>>(partial, parts, len, out, accumulate);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+int srb_gmm_stats_soft(const float *X, int64_t N, int64_t row0, int64_t nrows, int D, const float *gamma, int S, int M,
+                       int ncomp, const double *mu, const double *var, const double *lc, double gmin, float *partial,
+                       double *out, int accumulate, void *stream) {
+    SRB_REQUIRE(X && gamma && mu && var && lc && partial && out, SRB_EINVAL, "srb_gmm_stats_soft: null pointer");
+    SRB_REQUIRE(N >= 0 && row0 >= 0 && nrows >= 0 && row0 + nrows <= N && D > 0 && D <= 64 && S > 0 && M > 0, SRB_EINVAL,
+                "srb_gmm_stats_soft: bad sizes");
+    SRB_REQUIRE(ncomp >= 1 && ncomp <= M && ncomp <= MAXC, SRB_EUNSUPPORTED,
+                "srb_gmm_stats_soft: ncomp=%d outside 1..min(M,%d)", ncomp, MAXC);
+    const int grid = stats_grid();
+    SRB_REQUIRE(grid > 0, SRB_ENODEVICE, "no CUDA device");
+    const int row = 2 * D + 3, GW = S * ncomp;
+    const size_t bytes = sizeof(float) * ((size_t)2 * GW * D + ((GW + 3) & ~3) + (size_t)SW * GW * row);
+    SRB_REQUIRE(bytes <= (size_t)smem_optin(), SRB_EUNSUPPORTED,
+                "srb_gmm_stats_soft: %d states x %d components need %zu B shared memory", S, ncomp, bytes);
+    const int64_t len = (int64_t)S * M * row;
+    cudaStream_t st = (cudaStream_t)stream;
+    SRB_CUDA(cudaMemsetAsync(partial, 0, sizeof(float) * len * grid, st));
+    SRB_CUDA(cudaFuncSetAttribute(gmm_stats_soft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    gmm_stats_soft_kernel<<<grid, SW * 32, bytes, st>>>(X, row0, nrows, D, gamma, S, M, ncomp, mu, var, lc, (float)gmin,
+                                                       partial);
+    reduce_partials_kernel<<<(int)((len + 255) / 256), 256, 0, st>>>(partial, grid, len, out, accumulate);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }

@@ -29,6 +29,8 @@ SIGNATURES = {
     "srb_group_stats": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "srb_gmm_stats": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                               c_void_p, c_void_p, c_int, c_void_p]),
+    "srb_gmm_stats_soft": (c_int, [c_void_p, c_i64, c_i64, c_i64, c_int, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p,
+                                   c_void_p, ctypes.c_double, c_void_p, c_void_p, c_int, c_void_p]),
     "srb_local_dist": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_i64,
                                c_void_p, c_void_p]),
     "srb_mstep": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, ctypes.c_double,

@@ -204,3 +204,110 @@ class IsolatedTrainer:
 
     def mean_cost(self):
         return float(self.stats[-2] / self.stats[-1])
+
+
+class BaumWelchTrainer:
+    """Forward-backward (soft-count) EM over this rank's shard of a word-sorted corpus (BASELINE config 3).
+
+    The reference has no Baum-Welch; the iteration is defined as the soft version of IsolatedTrainer's:
+        score (K1, per word block) -> forward-backward (K4: gamma, xi, log Z) -> soft statistics (srb_gmm_stats_soft)
+        -> [allreduce over GPUs] -> M-step (means / variances / weights of the first ncomp components as in
+        hmm_state.py:138-148 with gamma-weighted posteriors; transitions a[o->r] = xi[o->r] / sum_r' xi[o->r'])
+    All words must share the state count S (continuous_speech.py:27-28 makes the same assumption)."""
+
+    def __init__(self, X, off, words, pm, trans, S, ncomp, group=None, var_floor=1e-6, gmin=1e-7,
+                 update_transitions=True):
+        X, off, words, self.order = sort_by_word(np.asarray(X), np.asarray(off), words)
+        self.dev = engine.device()
+        self.X = engine.as_frames(X)
+        self.pm, self.S, self.ncomp, self.group = pm, S, ncomp, group
+        self.var_floor, self.gmin, self.update_transitions = var_floor, gmin, update_transitions
+        self.W = pm.R // S
+        self.words = np.asarray(words).astype(np.int32)
+        off = np.asarray(off, np.int64)
+        self.off = off.astype(np.int32)
+        self.N, self.B = int(off[-1]), len(off) - 1
+        uptr = np.searchsorted(words, np.arange(self.W + 1), side="left")
+        self.word_rows = [(int(off[uptr[w]]), int(off[uptr[w + 1]])) for w in range(self.W)]
+        self.trans = np.array(trans, dtype=np.float64)
+        self._build_graphs()
+        self.E = torch.empty((max(self.N, 1), S), dtype=torch.float32, device=self.dev)
+        L = _l.load()
+        self.row = L.srb_stats_row(pm.D)
+        self.G = pm.R * pm.M
+        self.nnz = int(self.gb.edge_off[-1])
+        # [statistics | xi per edge | sum of -log Z, utterances]
+        self.stats = torch.zeros(self.G * self.row + self.nnz + 2, dtype=torch.float64, device=self.dev)
+        self.partial = torch.empty(L.srb_stats_parts() * S * pm.M * self.row, dtype=torch.float32, device=self.dev)
+        self.lc = torch.empty(self.G, dtype=torch.float64, device=self.dev)
+
+    def _build_graphs(self):
+        self.graphs = [StateGraph(self.trans[w], np.arange(self.S)) for w in range(self.W)]
+        self.gb = GraphBatch(self.graphs, self.dev)
+
+    def e_step(self):
+        pm, S, L, p = self.pm, self.S, _l.load(), _l.ptr
+        st = _l.stream_ptr()
+        blk = S * pm.Mp * pm.D * 2
+        for w, (r0, r1) in enumerate(self.word_rows):
+            if r1 > r0:
+                _l.check(L.srb_gmm_score_rows(p(self.X), self.N, r0, r1 - r0, pm.D, pm.ab[w * blk:].data_ptr(),
+                                              pm.c[w * S * pm.Mp:].data_ptr(), p(pm.shift), S, pm.Mp, p(self.E), S,
+                                              None, None, None, st))
+        self.gamma, _, self.nlz, self.xi = engine.forward_backward(self.E, self.off, self.gb, utt_graph=self.words,
+                                                                   want_xi=True)
+        return self.gamma
+
+    def accumulate(self):
+        pm, S, L, p = self.pm, self.S, _l.load(), _l.ptr
+        st = _l.stream_ptr()
+        _l.check(L.srb_gauss_consts(p(pm.var), p(pm.w), self.G, pm.D, p(self.lc), st))
+        body = self.stats[:self.G * self.row]
+        body.zero_()
+        mu, var = pm.mu.reshape(-1, pm.D), pm.var.reshape(-1, pm.D)
+        for w, (r0, r1) in enumerate(self.word_rows):
+            if r1 > r0:
+                g0 = w * S * pm.M
+                _l.check(L.srb_gmm_stats_soft(p(self.X), self.N, r0, r1 - r0, pm.D, p(self.gamma), S, pm.M, self.ncomp,
+                                              mu[g0:].data_ptr(), var[g0:].data_ptr(), self.lc[g0:].data_ptr(),
+                                              float(self.gmin), p(self.partial), body[g0 * self.row:].data_ptr(), 0,
+                                              st))
+        o = self.G * self.row
+        self.stats[o:o + self.nnz] = self.xi[:self.nnz]
+        fin = torch.isfinite(self.nlz)
+        self.stats[o + self.nnz] = torch.where(fin, self.nlz, torch.zeros_like(self.nlz)).sum()
+        self.stats[o + self.nnz + 1] = fin.sum().double()
+        return self.stats
+
+    def reduce(self):
+        if self.group is not None or (torch.distributed.is_initialized() and torch.distributed.get_world_size() > 1):
+            torch.distributed.all_reduce(self.stats, group=self.group)
+        return self.stats
+
+    def update(self):
+        pm = self.pm
+        _l.check(_l.load().srb_mstep(_l.ptr(self.stats), pm.R, pm.M, self.ncomp, pm.D, _l.ptr(pm.mu), _l.ptr(pm.var),
+                                     _l.ptr(pm.w), float(self.var_floor), _l.stream_ptr()))
+        pm.repack()
+        if self.update_transitions:
+            o = self.G * self.row
+            xi = self.stats[o:o + self.nnz].cpu().numpy()
+            for w, g in enumerate(self.graphs):
+                e0 = int(self.gb.edge_off[w])
+                x = xi[e0:e0 + g.nnz]
+                out = np.bincount(g.pred_idx, weights=x, minlength=self.S)      # total mass leaving each origin
+                with np.errstate(divide="ignore", invalid="ignore"):
+                    cost = -np.log(x / out[g.pred_idx])
+                keep = (out[g.pred_idx] > 0) & (x > 0)          # arcs never taken keep their cost (and the CSR its shape)
+                self.trans[w][g.pred_tgt[keep], g.pred_idx[keep]] = cost[keep]
+            self._build_graphs()
+
+    def em_iteration(self):
+        self.e_step()
+        self.accumulate()
+        self.reduce()
+        self.update()
+        return self.stats
+
+    def mean_neg_log_z(self):
+        return float(self.stats[-2] / self.stats[-1])
