@@ -292,12 +292,18 @@ forward_backward_kernel(const float *__restrict__ E, int64_t ldE, const int32_t 
             if (c > 0) {
                 // xi of the transitions into column c (needs alpha_hat_{c-1}, still in global)
                 const float *Erow = E + (f0 + c) * ldE;
-                float xs = 0.f;
+                float xs = 0.f, vmin = INF;
                 for (int j = lane; j < nnz; j += 32) {
                     const int r = pred_tgt[e0 + j];
                     const int o = G.pred_idx[e0 + j];
                     const float v = gu[(size_t)(c - 1) * R + o] + G.pred_cost[e0 + j] + Erow[emit[r]] + bnext[r];
-                    const float p = (v < INF) ? __expf(-v) : 0.f;
+                    xi[j] = v;
+                    vmin = fminf(vmin, v);
+                }
+                vmin = warp_min(vmin);                 // E_c is not renormalised: exp(-v) alone would underflow
+                for (int j = lane; j < nnz; j += 32) {
+                    const float v = xi[j];
+                    const float p = (v < INF) ? __expf(vmin - v) : 0.f;
                     xs += p;
                     xi[j] = p;                         // unnormalised, this column only (added below)
                 }
