@@ -411,50 +411,40 @@ def bench_stress(args, ctx):
 
 
 def bench_fb(args, ctx):
-    """Config 3 E-step: 8 states x 16 Gaussians per word, ragged 50-300 frame utterances: per-word K1 scoring + K4
-    forward-backward (state posteriors, log-likelihood).  No reference counterpart (parity unpinned)."""
+    """Config 3: one Baum-Welch iteration, 8 states x 16 Gaussians per word (int(log 16) = 2 splits -> 4 trained
+    components, hmm.py:104), ragged 50-300 frame utterances: per-word K1 scoring + K4 forward-backward + soft-count
+    statistics + allreduce + M-step + transition re-estimation.  No reference counterpart (parity unpinned)."""
     torch, dist, engine = ctx["torch"], ctx["dist"], ctx["engine"]
     from srb200 import synth
-    from srb200.graph import GraphBatch, StateGraph
-    from srb200.trainer import sort_by_word
+    from srb200.trainer import BaumWelchTrainer
     S, M = 8, 16
+    ncomp = 2 ** int(np.log(M))
     models, base = synth.make_models(11, W=W_, S=S, M=M)
     B = args.utts if args.utts != 100_000 else 50_000
     X, off, words = synth.make_utterances(400 + ctx["rank"], base, B, ragged=(50, 300))
-    X, off, words, _ = sort_by_word(X, off, words)
     pm, _ = engine.PackedModel.from_words(models)
-    Xd = engine.as_frames(X)
-    N = Xd.shape[0]
-    gb = GraphBatch([StateGraph(m[3], np.arange(S)) for m in models], engine.device())
-    E = torch.empty((N, S), dtype=torch.float32, device="cuda")
-    uptr = np.searchsorted(words, np.arange(W_ + 1))
-    rows = [(int(off[uptr[w]]), int(off[uptr[w + 1]])) for w in range(W_)]
-    L_ = ctx["lib"]
-    blk = S * pm.Mp * pm.D * 2
-    offd = engine.as_offsets(off)
-    out = {}
-
-    def step():
-        for w, (r0, r1) in enumerate(rows):
-            if r1 > r0:
-                L_.check(L_.load().srb_gmm_score_rows(L_.ptr(Xd), N, r0, r1 - r0, pm.D, pm.ab[w * blk:].data_ptr(),
-                                                      pm.c[w * S * pm.Mp:].data_ptr(), L_.ptr(pm.shift), S, pm.Mp,
-                                                      L_.ptr(E), S, None, None, None, L_.stream_ptr()))
-        out["fb"] = engine.forward_backward(E, offd, gb, utt_graph=words.astype(np.int32))
-
+    tr = BaumWelchTrainer(X, off, words, pm, np.stack([m[3] for m in models]), S, ncomp)
+    N = tr.N
     sampler = ClockSampler(ctx["local"])
     sampler.start()
-    total_ms, per = timed_steps(step, args.steps, args.warmup, torch, dist, ctx["world"])
+    total_ms, per = timed_steps(tr.em_iteration, args.steps, args.warmup, torch, dist, ctx["world"])
     clocks = sampler.stop()
-    gamma, ws, nlz, _ = out["fb"]
+    names = ["score+forward_backward", "soft_stats", "allreduce", "mstep+transitions"]
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+    ev[0].record(); tr.e_step(); ev[1].record(); tr.accumulate(); ev[2].record(); tr.reduce(); ev[3].record()
+    tr.update(); ev[4].record()
+    torch.cuda.synchronize()
     ms = float(np.mean(per))
-    roof = _roof_fma(S * M * 2 * D_, N, ms, ctx["peak_fma"], "score_kernel<39> x11 + forward_backward_kernel",
-                     "9984 FMA/frame scoring (8 states x 16 x 2*39); 22 log-add arcs per frame, twice")
-    return {"metric": "forward-backward E-step frames/s (8 states x 16 Gaussians, ragged 50-300 frames)",
+    roof = _roof_fma(S * M * 2 * D_ + S * ncomp * 2 * D_, N, ms, ctx["peak_fma"],
+                     "score_kernel<39> x11 + forward_backward_kernel + gmm_stats_soft_kernel x11",
+                     "9984 FMA/frame scoring (8 states x 16 x 2*39) + up to 8 x 4 x 2*39 soft accumulation; "
+                     "22 log-add arcs per frame, twice")
+    roof["phase_ms"] = {k: ev[i].elapsed_time(ev[i + 1]) for i, k in enumerate(names)}
+    return {"metric": "Baum-Welch EM-iteration frames/s (8 states x 16 Gaussians, ragged 50-300 frames)",
             "value": ctx["world"] * N * args.steps / (total_ms * 1e-3), "unit": "frames/s",
-            "ms_per_step": total_ms / args.steps, "gpu_launches": (W_ + 1) * args.steps, "roofline": roof,
-            "mean_neg_log_z_per_frame": float(nlz.sum().item() / N), "clocks": clocks,
-            "_workload": f"fb: 11 words x 8 states x 16 Gaussians, {B} utterances of 50-300 frames per GPU",
+            "ms_per_step": total_ms / args.steps, "gpu_launches": (2 * W_ + 10) * args.steps, "roofline": roof,
+            "mean_neg_log_z_per_utt": tr.mean_neg_log_z(), "clocks": clocks,
+            "_workload": f"fb: 11 words x 8 states x 16 Gaussians ({ncomp} trained), {B} utterances of 50-300 frames per GPU",
             "_frames": N}
 
 
