@@ -128,12 +128,45 @@ class IsolatedTrainer:
             self.fused_why = L.srb_last_error_string().decode()
             return False
         self.ntiles, self.tile_frames = int(nt.value), int(tf.value)
-        self.tiles = torch.from_numpy(tiles[:max(self.ntiles, 1)].copy()).to(self.dev)
+        self.tiles_host = tiles[:max(self.ntiles, 1)].copy()
+        self.tiles = torch.from_numpy(self.tiles_host).to(self.dev)
+        self._copy_stream = torch.cuda.Stream(self.dev)
         self.off_d = torch.from_numpy(off32).to(self.dev)
         self.trans_d = torch.from_numpy(trans.astype(np.float32)).to(self.dev).contiguous()
         self.em_partial = torch.empty(L.srb_em_parts() * self.G * self.row, dtype=torch.float32, device=self.dev)
         self.best_cost = torch.empty(max(self.B, 1), dtype=torch.float32, device=self.dev)
         return True
+
+    def em_iteration_from_host(self, Xh, chunks=8):
+        """One iteration with the shard coming from PINNED host memory (the end-to-end path bench.py times): the
+        shard is cut at tile boundaries into `chunks` pieces; piece k+1 is copied host->device on a copy stream
+        while srb_em_isolated runs on piece k (statistics accumulate across the pieces)."""
+        assert self.fused, "pipelined host path needs the fused pass"
+        pm, p, L = self.pm, _l.ptr, _l.load()
+        cur, cp = torch.cuda.current_stream(), self._copy_stream
+        cp.wait_stream(cur)                                   # the previous iteration is done reading self.X
+        body = self.stats[:self.G * self.row]
+        cuts = np.linspace(0, self.ntiles, min(chunks, max(self.ntiles, 1)) + 1).astype(np.int64)
+        for k in range(len(cuts) - 1):
+            t0, t1 = int(cuts[k]), int(cuts[k + 1])
+            if t1 <= t0:
+                continue
+            f0 = int(self.tiles_host[t0, 1])
+            f1 = int(self.tiles_host[t1, 1]) if t1 < self.ntiles else self.N
+            with torch.cuda.stream(cp):
+                self.X[f0:f1].copy_(Xh[f0:f1], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(cp)
+            cur.wait_event(ev)
+            _l.check(L.srb_em_isolated(
+                p(self.X), self.N, pm.D, p(self.off_d), self.B, self.tiles[t0:].data_ptr(), t1 - t0, self.tile_frames,
+                p(pm.ab), p(pm.c), p(pm.shift), self.W, self.S, pm.M, pm.Mp, p(self.trans_d), self.ncomp, p(pm.mu),
+                p(self.em_partial), p(body), int(k > 0), p(self.best_cost), None, None, cur.cuda_stream))
+        self.stats[self.G * self.row] = self.best_cost[:self.B].sum(dtype=torch.float64)
+        self.stats[self.G * self.row + 1] = float(self.B)
+        self.reduce()
+        self.update()
+        return self.stats
 
     def fused_pass(self, seg_start=None, frame_label=None, stats=True):
         """srb_em_isolated over the shard: statistics body of self.stats (+ best_cost, optional boundaries/labels)."""

@@ -113,3 +113,26 @@ def test_fused_pass_equals_unfused_kernels(W, S, M, ncomp, skip, lens):
     assert np.max(np.abs(sa - sb) / scale) < 2e-5
     np.testing.assert_allclose(sa[:, 0], sb[:, 0], rtol=1e-5, atol=1e-6)
     np.testing.assert_allclose(a.stats[-2:].cpu().numpy(), b.stats[-2:].cpu().numpy(), rtol=1e-6)
+
+
+def test_pipelined_host_iteration_equals_resident():
+    """em_iteration_from_host (chunked H2D overlapped with the kernel) == em_iteration on the resident shard."""
+    import torch
+    from srb200 import engine, synth
+    from srb200.trainer import IsolatedTrainer, sort_by_word
+    W, S, M, ncomp = 3, 5, 4, 2
+    models, base = synth.make_models(61, W=W, S=S, M=M)
+    X, off, words = synth.make_utterances(63, base, 300, ragged=(30, 110), noise=0.9)
+    X, off, words, _ = sort_by_word(X, off, words)
+    trans = np.stack([m[3] for m in models])
+    pa, _ = engine.PackedModel.from_words(models)
+    pb, _ = engine.PackedModel.from_words(models)
+    a = IsolatedTrainer(X, off, words, pa, trans, S, ncomp, fused=True)
+    b = IsolatedTrainer(X, off, words, pb, trans, S, ncomp, fused=True)
+    Xh = torch.from_numpy(np.ascontiguousarray(X)).pin_memory()
+    b.X.zero_()
+    a.em_iteration()
+    b.em_iteration_from_host(Xh, chunks=5)
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(b.stats.cpu().numpy(), a.stats.cpu().numpy(), rtol=1e-6, atol=1e-9)
+    np.testing.assert_allclose(pb.mu.cpu().numpy(), pa.mu.cpu().numpy(), rtol=1e-7, atol=1e-9)
