@@ -502,7 +502,7 @@ def run_ours(args):
                                                                    if args.workload == "em" else ", no collective")},
     })
     if rank == 0 and not args.no_cpu:
-        n_cpu = args.cpu_utts or (2048 if args.workload == "em" else 512)
+        n_cpu = args.cpu_utts or min(args.utts, 100_000 if args.workload == "em" else 50_000)
         fn = cpu_em if args.workload == "em" else cpu_decode
         v, cores, ms = fn(models, base, n_cpu, args.frames)
         line["cpu_baseline"] = {"value": v, "unit": "frames/s", "cores": cores, "kind": "port",
@@ -530,7 +530,7 @@ def run_reference(args):
     from srb200 import synth
     models, base = synth.make_models(1, W=W_, S=S_, M=M_)
     em = args.workload == "em"
-    n_cpu = args.cpu_utts or (2048 if em else 512)
+    n_cpu = args.cpu_utts or min(args.utts, 20_000 if em else 10_000)
     fn = cpu_em if em else cpu_decode
     v, cores, ms = fn(models, base, n_cpu, args.frames, steps=args.steps, warmup=min(args.warmup, 1))
     metric = ("EM-iteration frames/s (segmental K-means alignment + GMM EM statistics + M-step)" if em else
