@@ -104,6 +104,23 @@ int srb_viterbi_graph(const float *E, int64_t ldE, const int32_t *utt_off, int32
                       uint8_t *bp, float *costs_out, float *best_cost, int32_t *best_end, const int64_t *path_off,
                       int32_t *path_state, int32_t *path_frame, int32_t *path_len, int32_t *frame_label, void *stream);
 
+/* Same contract and bit-identical outputs as srb_viterbi_graph, for graphs in BANDED FORM (what
+ * build_state_sequences, continuous_speech.py:13-53, and plain left-to-right models produce): the emitting
+ * predecessors of an emitting state r lie in {r-2, r-1, r}; it may have one non-emitting predecessor n < r (its
+ * "entry"); states feeding a NES are emitting and have no entry.  Extra per-state arrays (graph-local, packed like
+ * emit): band float[R,3] = costs of the arcs from r-2, r-1, r (+inf = absent); codes int32[R] = back-pointer codes
+ * (positions in the ascending predecessor list) of those three arcs and of the entry arc, one byte each;
+ * entry_nes int32[R] (-1 = none), entry_cost float[R]; entry_state lists the states with an entry per graph
+ * (g_entry_off).  srb200/graph.py derives them (StateGraph.banded_form) or reports that a graph is not banded. */
+int srb_viterbi_banded(const float *E, int64_t ldE, const int32_t *utt_off, int32_t B, const int32_t *utt_graph,
+                       const int32_t *g_state_off, const int32_t *g_nes_off, const int32_t *g_end_off,
+                       const int32_t *emit, const int32_t *pred_ptr, const int32_t *pred_idx, const float *pred_cost,
+                       const int32_t *nes_idx, const int32_t *end_state, const float *band, const int32_t *codes,
+                       const int32_t *entry_nes, const float *entry_cost, const int32_t *g_entry_off,
+                       const int32_t *entry_state, int32_t Rmax, const int64_t *bp_off, uint8_t *bp, float *costs_out,
+                       float *best_cost, int32_t *best_end, const int64_t *path_off, int32_t *path_state,
+                       int32_t *path_frame, int32_t *path_len, int32_t *frame_label, void *stream);
+
 /* ---- K4: batched forward-backward (Baum-Welch E-step) for NES-free graphs -------------------------
  * The reference has NO forward-backward; semantics are defined to be consistent with
  * srb_viterbi_graph: same graph packing, start in state 0 at frame 0, end in any end_state at the last frame;

@@ -33,6 +33,54 @@ __device__ __forceinline__ void lexmin(float &v, int &p, float ov, int op) {
     }
 }
 
+// Best end point ('>=': the last listed minimum wins, decode.py:131-134), traceback (decode.py:142-146) and frame
+// labels for one utterance whose last cost column is `prev`.  Shared by the generic and the banded kernel.
+__device__ __forceinline__ void finish_utterance(const GraphBatch &G, int g, int s0, int R, int T, int64_t f0, int u,
+                                                 const float *prev, const int32_t *emit, const int32_t *pptr,
+                                                 const uint8_t *bpu, int lane, float *best_cost, int32_t *best_end,
+                                                 const int64_t *path_off, int32_t *path_state, int32_t *path_frame,
+                                                 int32_t *path_len, int32_t *frame_label) {
+    const float INF = CUDART_INF_F;
+    // ---- best end point: '>=' -> the last listed minimum wins (decode.py:131-134); traceback :142-146
+    if (lane == 0) {
+        float bc = INF;
+        int bi = -1;
+        for (int e = G.g_end_off[g]; e < G.g_end_off[g + 1]; ++e) {
+            const int s = G.end_state[e];
+            if (bc >= prev[s]) {
+                bc = prev[s];
+                bi = s;
+            }
+        }
+        best_cost[u] = bc;
+        best_end[u] = bi;
+        int len = 0;
+        if (bc < INF && (path_state || frame_label)) {
+            int32_t *ps = path_state ? path_state + path_off[u] : nullptr;
+            int32_t *pf = path_state ? path_frame + path_off[u] : nullptr;
+            const int cap = path_state ? (int)(path_off[u + 1] - path_off[u]) : 0x7fffffff;
+            int i = bi, j = T - 1;
+            if (frame_label && emit[i] >= 0) frame_label[f0 + j] = s0 + i;
+            while (j > 0 && len < cap) {
+                const int code = bpu[(size_t)j * R + i];
+                const int o = G.pred_idx[pptr[i] + code];
+                if (!(emit[o] < 0 || emit[i] < 0)) --j;
+                i = o;
+                if (ps) {
+                    ps[len] = i;
+                    pf[len] = j;
+                }
+                if (frame_label && emit[i] >= 0) frame_label[f0 + j] = s0 + i;
+                ++len;
+            }
+            if (j > 0) len = -1;   // capacity exhausted
+        } else if (frame_label) {
+            for (int c = 0; c < T; ++c) frame_label[f0 + c] = -1;   // no path: frames are skipped downstream
+        }
+        if (path_len) path_len[u] = len;
+    }
+}
+
 __global__ void __launch_bounds__(VW * 32)
 viterbi_graph_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *__restrict__ off, int B, GraphBatch G,
                      int Rmax, const int64_t *__restrict__ bp_off, uint8_t *__restrict__ bp,
@@ -74,6 +122,7 @@ viterbi_graph_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *__
                     float out;
                     if (c == 0 && r == 0) {
                         out = Erow[emit[0]];                       // decode.py:99-100
+                        bpc[0] = 0;
                     } else {
                         const int p0 = pptr[r], p1 = pptr[r + 1];
                         float best = INF;
@@ -97,7 +146,10 @@ viterbi_graph_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *__
                     const int n = hi;
                     const int p0 = pptr[n], p1 = pptr[n + 1];
                     if (c == 0 && n == 0) {
-                        if (lane == 0) cur[0] = 0.f;
+                        if (lane == 0) {
+                            cur[0] = 0.f;
+                            bpc[0] = 0;
+                        }
                     } else {
                         float best = INF;
                         int bj = 0x7fffffff;
@@ -128,44 +180,139 @@ viterbi_graph_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *__
             cur = t;
             __syncwarp();
         }
-        // ---- best end point: '>=' -> the last listed minimum wins (decode.py:131-134); traceback :142-146
-        if (lane == 0) {
-            float bc = INF;
-            int bi = -1;
-            for (int e = G.g_end_off[g]; e < G.g_end_off[g + 1]; ++e) {
-                const int s = G.end_state[e];
-                if (bc >= prev[s]) {
-                    bc = prev[s];
-                    bi = s;
-                }
+        finish_utterance(G, g, s0, R, T, f0, u, prev, emit, pptr, bpu, lane, best_cost, best_end, path_off, path_state,
+                         path_frame, path_len, frame_label);
+        __syncwarp();
+    }
+}
+
+
+// ------------------------------------------------------------------------------------------------ K2, banded form
+// Fast path for the graphs build_state_sequences produces (continuous_speech.py:13-53) and for plain left-to-right
+// models: every emitting state r has its emitting predecessors inside {r-2, r-1, r} plus at most one non-emitting
+// predecessor n < r ("entry"), and the states feeding a NES are emitting and have no entry themselves.  Then a column
+// needs three data-parallel sweeps instead of one sequential run per NES:
+//   1. all emitting states from the previous column (band costs a2, a1, a0; no predecessor-list walk),
+//   2. all NES from the finished emitting states of this column,
+//   3. the entry states, re-relaxed with their NES of this column.
+// Candidate order, first-minimum ties and the back-pointer codes (position in the ascending predecessor list) are
+// those of the generic kernel, so costs, back-pointers and paths are identical.
+struct BandForm {
+    const float *band;            // [sum R][3] = a2, a1, a0 (+inf when the arc is absent)
+    const int32_t *codes;         // [sum R] bytes: code(r-2) | code(r-1) << 8 | code(r) << 16 | code(entry NES) << 24
+    const int32_t *entry_nes;     // [sum R] local index of the entry NES or -1
+    const float *entry_cost;      // [sum R]
+    const int32_t *g_entry_off;   // [ng+1] range of entry_state
+    const int32_t *entry_state;   // local indices of the states with an entry
+};
+
+__global__ void __launch_bounds__(VW * 32)
+viterbi_banded_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *__restrict__ off, int B, GraphBatch G,
+                      BandForm F, int Rmax, const int64_t *__restrict__ bp_off, uint8_t *__restrict__ bp,
+                      float *__restrict__ costs_out, float *__restrict__ best_cost, int32_t *__restrict__ best_end,
+                      const int64_t *__restrict__ path_off, int32_t *__restrict__ path_state,
+                      int32_t *__restrict__ path_frame, int32_t *__restrict__ path_len,
+                      int32_t *__restrict__ frame_label) {
+    extern __shared__ float vsm[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float *prev = vsm + (size_t)warp * 2 * Rmax, *cur = prev + Rmax;
+    const float INF = CUDART_INF_F;
+
+    for (int u = blockIdx.x * VW + warp; u < B; u += gridDim.x * VW) {
+        const int g = G.utt_graph ? G.utt_graph[u] : 0;
+        const int s0 = G.g_state_off[g], R = G.g_state_off[g + 1] - s0;
+        const int n0 = G.g_nes_off[g], K = G.g_nes_off[g + 1] - n0;
+        const int q0 = F.g_entry_off[g], Q = F.g_entry_off[g + 1] - q0;
+        const int64_t f0 = off[u];
+        const int T = (int)(off[u + 1] - f0);
+        uint8_t *bpu = bp + bp_off[u];
+        float *cu = costs_out ? costs_out + bp_off[u] : nullptr;
+        const int32_t *emit = G.emit + s0, *pptr = G.pred_ptr + s0;
+        const float *band = F.band + (size_t)s0 * 3, *ecost = F.entry_cost + s0;
+        const int32_t *codes = F.codes + s0, *enes = F.entry_nes + s0;
+        if (T <= 0) {
+            if (lane == 0) {
+                best_cost[u] = INF;
+                best_end[u] = -1;
+                if (path_len) path_len[u] = 0;
             }
-            best_cost[u] = bc;
-            best_end[u] = bi;
-            int len = 0;
-            if (bc < INF && (path_state || frame_label)) {
-                int32_t *ps = path_state ? path_state + path_off[u] : nullptr;
-                int32_t *pf = path_state ? path_frame + path_off[u] : nullptr;
-                const int cap = path_state ? (int)(path_off[u + 1] - path_off[u]) : 0x7fffffff;
-                int i = bi, j = T - 1;
-                if (frame_label && emit[i] >= 0) frame_label[f0 + j] = s0 + i;
-                while (j > 0 && len < cap) {
-                    const int code = bpu[(size_t)j * R + i];
-                    const int o = G.pred_idx[pptr[i] + code];
-                    if (!(emit[o] < 0 || emit[i] < 0)) --j;
-                    i = o;
-                    if (ps) {
-                        ps[len] = i;
-                        pf[len] = j;
-                    }
-                    if (frame_label && emit[i] >= 0) frame_label[f0 + j] = s0 + i;
-                    ++len;
-                }
-                if (j > 0) len = -1;   // capacity exhausted
-            } else if (frame_label) {
-                for (int c = 0; c < T; ++c) frame_label[f0 + c] = -1;   // no path: frames are skipped downstream
-            }
-            if (path_len) path_len[u] = len;
+            continue;
         }
+        for (int r = lane; r < R; r += 32) prev[r] = INF;
+        __syncwarp();
+        for (int c = 0; c < T; ++c) {
+            const float *Erow = E + (f0 + c) * ldE;
+            uint8_t *bpc = bpu + (size_t)c * R;
+            // ---- 1. emitting states from the previous column
+            for (int r = lane; r < R; r += 32) {
+                const int em = emit[r];
+                if (em < 0) continue;
+                if (c == 0 && r == 0) {
+                    cur[0] = Erow[em];                               // decode.py:99-100
+                    bpc[0] = 0;
+                    continue;
+                }
+                const int cd = codes[r];
+                float best = INF;
+                int code = 0;
+                const float t2 = (r >= 2 ? prev[r - 2] : INF) + band[r * 3 + 0];
+                const float t1 = (r >= 1 ? prev[r - 1] : INF) + band[r * 3 + 1];
+                const float t0 = prev[r] + band[r * 3 + 2];
+                if (t2 < best) { best = t2; code = cd & 0xff; }
+                if (t1 < best) { best = t1; code = (cd >> 8) & 0xff; }
+                if (t0 < best) { best = t0; code = (cd >> 16) & 0xff; }
+                cur[r] = enes[r] < 0 ? best + Erow[em] : best;       // entry states get their emission in sweep 3
+                bpc[r] = (uint8_t)code;
+            }
+            __syncwarp();
+            // ---- 2. the non-emitting states (same column, first minimum in origin order)
+            for (int k = lane; k < K; k += 32) {
+                const int n = G.nes_idx[n0 + k];
+                if (c == 0 && n == 0) {
+                    cur[0] = 0.f;
+                    bpc[0] = 0;
+                    continue;
+                }
+                const int p0 = pptr[n], p1 = pptr[n + 1];
+                float best = INF;
+                int bj = 0;
+                for (int j = p0; j < p1; ++j) {
+                    const int o = G.pred_idx[j];
+                    const float cand = G.pred_cost[j] + (o < n ? cur[o] : INF);
+                    if (cand < best) {
+                        best = cand;
+                        bj = j - p0;
+                    }
+                }
+                cur[n] = (p1 > p0) ? best : INF;
+                bpc[n] = (uint8_t)bj;
+            }
+            __syncwarp();
+            // ---- 3. entry states: the NES arc competes with the band candidates (lower list position wins ties)
+            for (int i = lane; i < Q; i += 32) {
+                const int r = F.entry_state[q0 + i];
+                if (c == 0 && r == 0) continue;
+                const float cand = ecost[r] + cur[enes[r]];
+                const int cn = (codes[r] >> 24) & 0xff;
+                float best = cur[r];
+                int code = bpc[r];
+                if (cand < best || (cand == best && cand < INF && cn < code)) {
+                    best = cand;
+                    code = cn;
+                }
+                cur[r] = best + Erow[emit[r]];
+                bpc[r] = (uint8_t)code;
+            }
+            __syncwarp();
+            if (cu)
+                for (int r = lane; r < R; r += 32) cu[(size_t)c * R + r] = cur[r];
+            float *t = prev;
+            prev = cur;
+            cur = t;
+            __syncwarp();
+        }
+        finish_utterance(G, g, s0, R, T, f0, u, prev, emit, pptr, bpu, lane, best_cost, best_end, path_off, path_state,
+                         path_frame, path_len, frame_label);
         __syncwarp();
     }
 }
@@ -390,6 +537,45 @@ int srb_viterbi_graph(const float *E, int64_t ldE, const int32_t *utt_off, int32
                               end_state);
     viterbi_graph_kernel<<<(int)grid, VW * 32, bytes, (cudaStream_t)stream>>>(
         E, ldE, utt_off, B, G, Rmax, bp_off, bp, costs_out, best_cost, best_end, path_off, path_state, path_frame,
+        path_len, frame_label);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+int srb_viterbi_banded(const float *E, int64_t ldE, const int32_t *utt_off, int32_t B, const int32_t *utt_graph,
+                       const int32_t *g_state_off, const int32_t *g_nes_off, const int32_t *g_end_off,
+                       const int32_t *emit, const int32_t *pred_ptr, const int32_t *pred_idx, const float *pred_cost,
+                       const int32_t *nes_idx, const int32_t *end_state, const float *band, const int32_t *codes,
+                       const int32_t *entry_nes, const float *entry_cost, const int32_t *g_entry_off,
+                       const int32_t *entry_state, int32_t Rmax, const int64_t *bp_off, uint8_t *bp, float *costs_out,
+                       float *best_cost, int32_t *best_end, const int64_t *path_off, int32_t *path_state,
+                       int32_t *path_frame, int32_t *path_len, int32_t *frame_label, void *stream) {
+    SRB_REQUIRE(E && utt_off && g_state_off && g_nes_off && g_end_off && emit && pred_ptr && pred_idx && pred_cost &&
+                    end_state && bp_off && bp && best_cost && best_end && band && codes && entry_nes && entry_cost &&
+                    g_entry_off && entry_state,
+                SRB_EINVAL, "srb_viterbi_banded: null pointer");
+    SRB_REQUIRE(!path_state || (path_off && path_frame && path_len), SRB_EINVAL,
+                "srb_viterbi_banded: path_state needs path_off, path_frame and path_len");
+    SRB_REQUIRE(B >= 0 && Rmax > 0 && ldE > 0, SRB_EINVAL, "srb_viterbi_banded: bad sizes");
+    if (B == 0) return SRB_OK;
+    const size_t bytes = (size_t)VW * 2 * Rmax * sizeof(float);
+    SRB_REQUIRE(bytes <= (size_t)smem_optin(), SRB_EUNSUPPORTED, "srb_viterbi_banded: %d states do not fit shared memory",
+                Rmax);
+    SRB_CUDA(cudaFuncSetAttribute(viterbi_banded_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    int64_t grid = ((int64_t)B + VW - 1) / VW;
+    const int64_t cap = (int64_t)sm_count() * 16;
+    if (grid > cap) grid = cap;
+    GraphBatch G = make_graph(utt_graph, g_state_off, g_nes_off, g_end_off, emit, pred_ptr, pred_idx, pred_cost, nes_idx,
+                              end_state);
+    BandForm F;
+    F.band = band;
+    F.codes = codes;
+    F.entry_nes = entry_nes;
+    F.entry_cost = entry_cost;
+    F.g_entry_off = g_entry_off;
+    F.entry_state = entry_state;
+    viterbi_banded_kernel<<<(int)grid, VW * 32, bytes, (cudaStream_t)stream>>>(
+        E, ldE, utt_off, B, G, F, Rmax, bp_off, bp, costs_out, best_cost, best_end, path_off, path_state, path_frame,
         path_len, frame_label);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;

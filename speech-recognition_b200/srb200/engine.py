@@ -228,7 +228,24 @@ class ViterbiResult:
         return out
 
 
-def viterbi(E, off, gb, utt_graph=None, want_costs=False, want_path=True, frame_label=None):
+def viterbi_launch(gb, E, offd, B, ug, ws_d, bp, costs, bc, be, po_d, ps, pf, pl, frame_label, banded=None):
+    """srb_viterbi_banded when every graph of the batch is in banded form (banded=False forces the generic kernel;
+    both give identical outputs), else srb_viterbi_graph."""
+    p, L = _l.ptr, _l.load()
+    use_banded = gb.banded if banded is None else (banded and gb.banded)
+    head = (p(E), E.stride(0), p(offd), B, p(ug), p(gb["g_state_off"]), p(gb["g_nes_off"]), p(gb["g_end_off"]),
+            p(gb["emit"]), p(gb["pred_ptr"]), p(gb["pred_idx"]), p(gb["pred_cost"]), p(gb["nes_idx"]), p(gb["end_state"]))
+    tail = (gb.Rmax, p(ws_d), p(bp), p(costs), p(bc), p(be), p(po_d), p(ps), p(pf), p(pl), p(frame_label),
+            _l.stream_ptr())
+    if use_banded:
+        _l.check(L.srb_viterbi_banded(*head, p(gb["band"]), p(gb["codes"]), p(gb["entry_nes"]), p(gb["entry_cost"]),
+                                      p(gb["g_entry_off"]), p(gb["entry_state"]), *tail))
+    else:
+        _l.check(L.srb_viterbi_graph(*head, *tail))
+    return use_banded
+
+
+def viterbi(E, off, gb, utt_graph=None, want_costs=False, want_path=True, frame_label=None, banded=None):
     """K2.  E: [N, ldE] float32 CUDA emission costs; off: [B+1] int32; gb: GraphBatch."""
     dev = E.device
     offd = as_offsets(off)
@@ -244,12 +261,7 @@ def viterbi(E, off, gb, utt_graph=None, want_costs=False, want_path=True, frame_
     ps = torch.empty(max(int(po[-1]), 1), dtype=torch.int32, device=dev) if want_path else None
     pf = torch.empty(max(int(po[-1]), 1), dtype=torch.int32, device=dev) if want_path else None
     pl = torch.zeros(B, dtype=torch.int32, device=dev)
-    _l.check(_l.load().srb_viterbi_graph(
-        _l.ptr(E), E.stride(0), _l.ptr(offd), B, _l.ptr(ug), _l.ptr(gb["g_state_off"]), _l.ptr(gb["g_nes_off"]),
-        _l.ptr(gb["g_end_off"]), _l.ptr(gb["emit"]), _l.ptr(gb["pred_ptr"]), _l.ptr(gb["pred_idx"]),
-        _l.ptr(gb["pred_cost"]), _l.ptr(gb["nes_idx"]), _l.ptr(gb["end_state"]), gb.Rmax, _l.ptr(ws_d), _l.ptr(bp),
-        _l.ptr(costs), _l.ptr(bc), _l.ptr(be), _l.ptr(po_d), _l.ptr(ps), _l.ptr(pf), _l.ptr(pl), _l.ptr(frame_label),
-        _l.stream_ptr()))
+    viterbi_launch(gb, E, offd, B, ug, ws_d, bp, costs, bc, be, po_d, ps, pf, pl, frame_label, banded=banded)
     res = ViterbiResult(bc, be, ps, pf, pl, po, costs, ws, bp)
     res.frame_label = frame_label
     return res

@@ -43,6 +43,40 @@ class StateGraph:
     def nnz(self):
         return int(self.pred_idx.shape[0])
 
+    def banded_form(self):
+        """Arrays of srb_viterbi_banded (include/srb200.h) or None when the graph is not in banded form: emitting
+        predecessors of an emitting state r inside {r-2, r-1, r}, at most one NES predecessor n < r (its entry),
+        NES fed only by emitting states n' < n that have no entry themselves."""
+        R, emit = self.R, self.emit
+        is_nes = emit < 0
+        band = np.full((R, 3), np.inf, np.float32)
+        codes = np.zeros((R, 4), np.int64)
+        entry_nes = np.full(R, -1, np.int32)
+        entry_cost = np.zeros(R, np.float32)
+        feeds_nes = np.zeros(R, bool)
+        for r in range(R):
+            p0, p1 = int(self.pred_ptr[r]), int(self.pred_ptr[r + 1])
+            for pos in range(p1 - p0):
+                o, c = int(self.pred_idx[p0 + pos]), self.pred_cost[p0 + pos]
+                if is_nes[r]:
+                    if is_nes[o] or o >= r:
+                        return None
+                    feeds_nes[o] = True
+                elif is_nes[o]:
+                    if o >= r or entry_nes[r] >= 0:
+                        return None
+                    entry_nes[r], entry_cost[r], codes[r, 3] = o, c, pos
+                else:
+                    k = r - o
+                    if k < 0 or k > 2:
+                        return None
+                    band[r, 2 - k], codes[r, 2 - k] = c, pos
+        if (feeds_nes & (entry_nes >= 0)).any():
+            return None
+        packed = (codes[:, 0] | (codes[:, 1] << 8) | (codes[:, 2] << 16) | (codes[:, 3] << 24)).astype(np.int32)
+        return {"band": band.reshape(-1), "codes": packed, "entry_nes": entry_nes, "entry_cost": entry_cost,
+                "entry_state": np.nonzero(entry_nes >= 0)[0].astype(np.int32)}
+
 
 class GraphBatch:
     """Several StateGraphs packed back to back on the device."""
@@ -86,6 +120,17 @@ class GraphBatch:
             "succ_idx": cat([g.succ_idx for g in graphs], np.int32),
             "succ_cost": cat([g.succ_cost for g in graphs], np.float32),
         }
+        forms = [g.banded_form() for g in graphs]
+        self.banded = all(f is not None for f in forms)
+        if self.banded:
+            host.update({
+                "band": cat([f["band"] for f in forms], np.float32),
+                "codes": cat([f["codes"] for f in forms], np.int32),
+                "entry_nes": cat([f["entry_nes"] for f in forms], np.int32),
+                "entry_cost": cat([f["entry_cost"] for f in forms], np.float32),
+                "g_entry_off": offs([len(f["entry_state"]) for f in forms]),
+                "entry_state": cat([f["entry_state"] for f in forms], np.int32),
+            })
         self.host = host
         self.dev = {}
         for k, v in host.items():

@@ -42,7 +42,8 @@ def sort_by_word(X, off, words):
 class ViterbiPlan:
     """Pre-planned K2 launch for a fixed batch (offsets, graphs): all buffers allocated once."""
 
-    def __init__(self, off, gb, utt_graph=None, want_path=False, want_label=True):
+    def __init__(self, off, gb, utt_graph=None, want_path=False, want_label=True, banded=None):
+        self.banded = banded
         dev = gb["emit"].device
         self.gb = gb
         self.off = engine.as_offsets(off)
@@ -65,12 +66,8 @@ class ViterbiPlan:
             self.pl = torch.zeros(self.B, dtype=torch.int32, device=dev)
 
     def run(self, E):
-        gb, p = self.gb, _l.ptr
-        _l.check(_l.load().srb_viterbi_graph(
-            p(E), E.stride(0), p(self.off), self.B, p(self.ug), p(gb["g_state_off"]), p(gb["g_nes_off"]),
-            p(gb["g_end_off"]), p(gb["emit"]), p(gb["pred_ptr"]), p(gb["pred_idx"]), p(gb["pred_cost"]),
-            p(gb["nes_idx"]), p(gb["end_state"]), gb.Rmax, p(self.ws_d), p(self.bp), None, p(self.best_cost),
-            p(self.best_end), p(self.po_d), p(self.ps), p(self.pf), p(self.pl), p(self.label), _l.stream_ptr()))
+        engine.viterbi_launch(self.gb, E, self.off, self.B, self.ug, self.ws_d, self.bp, None, self.best_cost,
+                              self.best_end, self.po_d, self.ps, self.pf, self.pl, self.label, banded=self.banded)
         return self
 
 

@@ -153,3 +153,40 @@ def test_forward_backward_vs_oracle(eng, S, M):
             v = a[:-1, o] + m[3][r, o] + Eo[1:, r] + b[1:, r] - z
             xi_ref[e0 + j] += np.exp(-v).sum()
     np.testing.assert_allclose(xi, xi_ref, rtol=2e-3, atol=1e-4)
+
+
+@pytest.mark.parametrize("layers", [1, 3])
+def test_banded_kernel_equals_generic_kernel(layers):
+    """srb_viterbi_banded (three data-parallel sweeps per column) against srb_viterbi_graph (one sequential run per
+    NES) on word-loop graphs with skip arcs: cost matrices, back-pointers, best ends and paths must be identical."""
+    import torch
+    from srb200 import engine, synth
+    from srb200.graph import GraphBatch, StateGraph, word_loop_graph
+    W, S = 4, 5
+    models, base = synth.make_models(33, W=W, S=S, M=4)
+    trans = np.stack([m[3] for m in models]).copy()
+    rng = np.random.default_rng(5)
+    for w in range(W):                                   # skip arcs and unequal costs (calc_transition_costs style)
+        trans[w][2, 0] = 1.0 + rng.random()
+        trans[w][S - 1, S - 3] = 0.5 + rng.random()
+        trans[w][1, 1] = 0.2 + rng.random()
+    g, _ = word_loop_graph(trans, layers)
+    iso = StateGraph(trans[1], np.arange(S))             # a NES-free left-to-right graph in the same batch
+    iso.emit = (np.arange(S) + S).astype(np.int32)
+    gb = GraphBatch([g, iso], engine.device())
+    assert gb.banded
+    X, off, strings = synth.make_strings(34, base, 12, n_words=layers, T=40 * layers, noise=1.0)
+    pm, _ = engine.PackedModel.from_words(models)
+    E = engine.gmm_score(X, pm)["E"]
+    ug = (np.arange(12) % 3 == 2).astype(np.int32)       # every third utterance on the isolated graph
+    out = []
+    for banded in (True, False):
+        fl = torch.full((E.shape[0],), -9, dtype=torch.int32, device="cuda")
+        r = engine.viterbi(E, off, gb, utt_graph=ug, want_costs=True, want_path=True, frame_label=fl, banded=banded)
+        out.append((r.costs.cpu().numpy(), r.bp.cpu().numpy(), r.best_cost.cpu().numpy(), r.best_end.cpu().numpy(),
+                    r.paths(), fl.cpu().numpy()))
+    a, b = out
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    assert np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3]) and np.array_equal(a[5], b[5])
+    assert all(np.array_equal(x, y) for x, y in zip(a[4], b[4]))
+    assert np.isfinite(a[2]).all()
