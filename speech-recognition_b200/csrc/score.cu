@@ -289,7 +289,7 @@ extern "C" {
 int srb_gmm_score_rows(const float *X, int64_t N, int64_t row0, int64_t nrows, int D, const float *ab, const float *c,
                        const float *shift, int R, int Mp, float *E, int64_t ldE, float *best_cost, int32_t *best_state,
                        float *comp, void *stream) {
-    SRB_REQUIRE(X && ab && c && shift, SRB_EINVAL, "srb_gmm_score: null pointer");
+    SRB_REQUIRE((X || nrows == 0) && ab && c && shift, SRB_EINVAL, "srb_gmm_score: null pointer");
     SRB_REQUIRE(N >= 0 && R > 0 && Mp > 0 && (Mp & 3) == 0, SRB_EINVAL, "srb_gmm_score: bad N/R/Mp");
     SRB_REQUIRE(row0 >= 0 && nrows >= 0 && row0 + nrows <= N, SRB_EINVAL, "srb_gmm_score: rows outside X");
     SRB_REQUIRE(!E || ldE >= R, SRB_EINVAL, "srb_gmm_score: ldE < R");
@@ -323,7 +323,8 @@ int srb_gmm_score(const float *X, int64_t N, int D, const float *ab, const float
 int srb_classify(const float *X, const int32_t *utt_off, int32_t B, int64_t N, int D, const float *ab,
                  const float *c, const float *shift, int W, int S, int Mp, const float *trans, float *final_cost,
                  int32_t *label, void *stream) {
-    SRB_REQUIRE(X && utt_off && ab && c && shift && trans && final_cost, SRB_EINVAL, "srb_classify: null pointer");
+    SRB_REQUIRE(((X && final_cost) || B == 0 || N == 0) && utt_off && ab && c && shift && trans, SRB_EINVAL,
+                "srb_classify: null pointer");
     SRB_REQUIRE(B >= 0 && N >= 0 && W > 0 && S > 0 && Mp > 0 && (Mp & 3) == 0, SRB_EINVAL, "srb_classify: bad sizes");
     SRB_REQUIRE(S <= SMAX, SRB_EUNSUPPORTED, "srb_classify: S=%d > %d states per word", S, SMAX);
     SRB_REQUIRE(((uintptr_t)X & 15) == 0 && ((uintptr_t)ab & 15) == 0 && ((uintptr_t)c & 15) == 0, SRB_EINVAL,

@@ -375,7 +375,7 @@ static int stats_grid() { return sm_count() * 2; }
 
 int srb_group_stats(const float *X, int64_t N, int D, const int32_t *label, int K, const double *shift,
                     float *partial, double *out, int accumulate, void *stream) {
-    SRB_REQUIRE(X && label && shift && partial && out, SRB_EINVAL, "srb_group_stats: null pointer");
+    SRB_REQUIRE((X || N == 0) && label && shift && partial && out, SRB_EINVAL, "srb_group_stats: null pointer");
     SRB_REQUIRE(N >= 0 && D > 0 && D <= 64 && K > 0, SRB_EINVAL, "srb_group_stats: bad N/D/K");
     const int grid = stats_grid();
     SRB_REQUIRE(grid > 0, SRB_ENODEVICE, "no CUDA device");
@@ -390,7 +390,7 @@ int srb_group_stats(const float *X, int64_t N, int D, const int32_t *label, int 
 
 int srb_gmm_stats(const float *X, int64_t N, int D, const int32_t *label, int R, int M, int ncomp, const double *mu,
                   const double *var, const double *lc, float *partial, double *out, int accumulate, void *stream) {
-    SRB_REQUIRE(X && label && mu && var && lc && partial && out, SRB_EINVAL, "srb_gmm_stats: null pointer");
+    SRB_REQUIRE((X || N == 0) && label && mu && var && lc && partial && out, SRB_EINVAL, "srb_gmm_stats: null pointer");
     SRB_REQUIRE(N >= 0 && D > 0 && D <= 64 && R > 0 && M > 0, SRB_EINVAL, "srb_gmm_stats: bad N/D/R/M");
     SRB_REQUIRE(ncomp >= 1 && ncomp <= M && ncomp <= MAXC, SRB_EUNSUPPORTED,
                 "srb_gmm_stats: ncomp=%d outside 1..min(M,%d)", ncomp, MAXC);
@@ -433,7 +433,7 @@ int srb_gmm_stats_soft(const float *X, int64_t N, int64_t row0, int64_t nrows, i
 
 int srb_local_dist(const float *X, int64_t N, int D, const double *Y, const double *var, int S, int kind,
                    int var_stride, float *out, int64_t ldo, int32_t *argmin_out, void *stream) {
-    SRB_REQUIRE(X && Y && (out || argmin_out), SRB_EINVAL, "srb_local_dist: null pointer");
+    SRB_REQUIRE((X || N == 0) && Y && (out || argmin_out || N == 0), SRB_EINVAL, "srb_local_dist: null pointer");
     SRB_REQUIRE(kind == 0 || (kind == 1 && var), SRB_EINVAL, "srb_local_dist: kind 1 needs var");
     SRB_REQUIRE(N >= 0 && D > 0 && D <= 64 && S > 0 && (!out || ldo >= S), SRB_EINVAL, "srb_local_dist: bad sizes");
     if (N == 0) return SRB_OK;

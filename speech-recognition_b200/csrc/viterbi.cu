@@ -518,6 +518,7 @@ int srb_viterbi_graph(const float *E, int64_t ldE, const int32_t *utt_off, int32
                       const int32_t *nes_idx, const int32_t *end_state, int32_t Rmax, const int64_t *bp_off,
                       uint8_t *bp, float *costs_out, float *best_cost, int32_t *best_end, const int64_t *path_off,
                       int32_t *path_state, int32_t *path_frame, int32_t *path_len, int32_t *frame_label, void *stream) {
+    if (B == 0) return SRB_OK;
     SRB_REQUIRE(E && utt_off && g_state_off && g_nes_off && g_end_off && emit && pred_ptr && pred_idx && pred_cost &&
                     end_state && bp_off && bp && best_cost && best_end,
                 SRB_EINVAL, "srb_viterbi_graph: null pointer");
@@ -550,6 +551,7 @@ int srb_viterbi_banded(const float *E, int64_t ldE, const int32_t *utt_off, int3
                        const int32_t *entry_state, int32_t Rmax, const int64_t *bp_off, uint8_t *bp, float *costs_out,
                        float *best_cost, int32_t *best_end, const int64_t *path_off, int32_t *path_state,
                        int32_t *path_frame, int32_t *path_len, int32_t *frame_label, void *stream) {
+    if (B == 0) return SRB_OK;
     SRB_REQUIRE(E && utt_off && g_state_off && g_nes_off && g_end_off && emit && pred_ptr && pred_idx && pred_cost &&
                     end_state && bp_off && bp && best_cost && best_end && band && codes && entry_nes && entry_cost &&
                     g_entry_off && entry_state,
