@@ -35,7 +35,7 @@ constexpr int ESMAX = SRB_DP_MAX_STATES;
 constexpr int EMAXC = 8;             // trained components per state handled in registers
 
 struct EmSmem {                      // offsets in floats into the dynamic shared memory
-    int tr, pc, pab, mean, xs, es, ps, ll, part, bnd, uoff, lab, total;
+    int tr, pc, pab, mean, xs, es, ps, ll, part, bnd, uoff, lab, seg, total;
 };
 
 __host__ __device__ inline EmSmem em_layout(int S, int Mp, int ncomp, int D, bool stats, int ETILE) {
@@ -54,6 +54,7 @@ __host__ __device__ inline EmSmem em_layout(int S, int Mp, int ncomp, int D, boo
     L.bnd = o;  o += EUTT * ESMAX;
     L.uoff = o; o += EUTT + 4;
     L.lab = o;  o += ETILE / 4;
+    L.seg = o;  o += 2 * 8 * 32;                          // segment transfer costs + boundaries (time-parallel Viterbi)
     L.total = o;
     return L;
 }
@@ -142,10 +143,82 @@ em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__rest
         __syncthreads();
 
         // ---- 2. Viterbi (decode.py:97-134 for a left-to-right model; ties: lowest origin wins like np.argmin).
-        //         8 lanes per utterance (lane = state), 4 utterances per warp, utterances dealt round-robin to the
-        //         warps.  Lane r keeps cost[r] and the boundaries of the best path into r packed one byte each
-        //         (frame index inside the utterance < ETILE = 256); the 1- and 2-state-back candidates come by
-        //         __shfl_up inside the 8-lane group.
+        if constexpr (ST > 0 && ST * ST <= 32) {
+            // TIME-PARALLEL form for S <= 5: the utterance is cut into one segment per warp; warp q computes the
+            // (min,+) transfer matrix of its segment, lane (i, j) = best cost from state i at the segment start to
+            // state j at its end (same banded recursion, 1/EWARPS of the steps), with the boundaries of that
+            // partial path packed one byte each.  Warp 0 then chains the matrices from the start vector and splices
+            // the boundaries.  The dependent chain is T/EWARPS + EWARPS steps instead of T.
+            float *Mc = smem + L.seg;
+            uint32_t *Mb = reinterpret_cast<uint32_t *>(smem + L.seg + 8 * 32);
+            const int i = lane / S, j = lane % S;
+            const bool live = lane < S * S;
+            const float a0 = live ? tr_s[j * ESMAX + j] : INF;
+            const float a1 = (live && j >= 1) ? tr_s[j * ESMAX + j - 1] : INF;
+            const float a2 = (live && j >= 2) ? tr_s[j * ESMAX + j - 2] : INF;
+            const uint32_t ones = 0x01010101u;
+            const uint32_t keep1 = j >= 2 ? ((1u << (8 * (j - 1))) - 1) : 0u;
+            const uint32_t keep2 = j >= 3 ? ((1u << (8 * (j - 2))) - 1) : 0u;
+            for (int p = 0; p < nutt; ++p) {
+                const int ts = uoff[p], T = uoff[p + 1] - ts;
+                const int per = (T - 1 + EWARPS - 1) / EWARPS;
+                const int t_lo = 1 + wq * per, t_hi = min(T, t_lo + per);
+                float m = (live && i == j) ? 0.f : INF;
+                uint32_t bd = 0, rep = ones * (uint32_t)(t_lo - 1);
+                const float *Ep = Es + (size_t)ts * ES + j;
+                float e_next = (t_lo < t_hi) ? Ep[(size_t)t_lo * ES] : INF;
+                for (int tt = t_lo; tt < t_hi; ++tt) {
+                    const float e = e_next;
+                    if (tt + 1 < t_hi) e_next = Ep[(size_t)(tt + 1) * ES];
+                    const float c1 = __shfl_up_sync(0xffffffffu, m, 1);
+                    const float c2 = __shfl_up_sync(0xffffffffu, m, 2);
+                    const uint32_t b1 = __shfl_up_sync(0xffffffffu, bd, 1);
+                    const uint32_t b2 = __shfl_up_sync(0xffffffffu, bd, 2);
+                    const float t2 = c2 + a2, t1 = c1 + a1, t0 = m + a0;       // a1/a2 = inf mask the row wrap-around
+                    const bool p1 = t1 < t2;
+                    const float b12 = p1 ? t1 : t2;
+                    const bool p0 = t0 < b12;
+                    rep += ones;
+                    const uint32_t inh = p1 ? b1 : b2, keep = p1 ? keep1 : keep2;
+                    bd = p0 ? bd : ((inh & keep) | (rep & ~keep));
+                    m = (p0 ? t0 : b12) + e;
+                }
+                Mc[wq * 32 + lane] = m;
+                Mb[wq * 32 + lane] = bd;
+                __syncthreads();
+                if (wq == 0) {
+                    float v = (lane == 0 && T > 0) ? Es[(size_t)ts * ES] : INF;   // alpha at frame 0, lane = state
+                    uint32_t vb = 0;
+                    const int jj = lane < S ? lane : 0;
+                    for (int q = 0; q < EWARPS; ++q) {
+                        float best = INF;
+                        int bi = 0;
+#pragma unroll
+                        for (int ii = 0; ii < ST; ++ii) {
+                            const float cand = __shfl_sync(0xffffffffu, v, ii) + Mc[q * 32 + ii * S + jj];
+                            if (cand < best) {
+                                best = cand;
+                                bi = ii;
+                            }
+                        }
+                        const uint32_t vbi = __shfl_sync(0xffffffffu, vb, bi);
+                        const uint32_t keep = bi > 0 ? ((bi >= 4) ? 0xffffffffu : ((1u << (8 * bi)) - 1)) : 0u;
+                        vb = (vbi & keep) | (Mb[q * 32 + bi * S + jj] & ~keep);
+                        v = lane < S ? best : INF;
+                    }
+                    if (lane == S - 1) {
+                        bnd[p * ESMAX] = (v < INF) ? 0 : -1;       // -1: no path, the utterance's frames are skipped
+                        for (int k = 1; k < S; ++k) bnd[p * ESMAX + k] = (int)((vb >> (8 * (k - 1))) & 0xff);
+                        if (best_cost) best_cost[u0 + p] = v;
+                        if (seg_start)
+                            for (int k = 0; k < S; ++k)
+                                seg_start[(size_t)(u0 + p) * S + k] = (v < INF && k) ? (int)((vb >> (8 * (k - 1))) & 0xff) : 0;
+                    }
+                }
+                __syncthreads();
+            }
+        } else
+        //         Sequential form: 8 lanes per utterance (lane = state), 4 utterances per warp.
         {
             using BT = typename std::conditional<(ST > 0 && ST <= 5), uint32_t, uint64_t>::type;
             const int grp = lane >> 3, r = lane & 7;

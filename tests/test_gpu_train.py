@@ -91,22 +91,44 @@ def test_fused_pass_equals_unfused_kernels(W, S, M, ncomp, skip, lens):
     lab = torch.full((a.N,), -7, dtype=torch.int32, device="cuda")
     a.fused_pass(seg_start=seg, frame_label=lab)
     b.align()
-    b.accumulate()
     la, lb = lab.cpu().numpy(), b.plan.label.cpu().numpy()
     ca, cb = a.best_cost.cpu().numpy(), b.plan.best_cost.cpu().numpy()
     assert np.array_equal(np.isfinite(ca), np.isfinite(cb))
     fin = np.isfinite(cb)
     assert fin.sum() > 40 and ((~fin).sum() > 0 or lens[0] > 2)
-    np.testing.assert_allclose(ca[fin], cb[fin], rtol=1e-6)
-    # labels: state index within the word in the fused kernel's global numbering w*S+s == graph offset + s
-    assert np.array_equal(la, lb)
-    # boundaries == get_segments_from_path of the K2 labels
+    # the fused kernel chains per-warp (min,+) segment matrices, K2 runs frame by frame: the same minimum summed in a
+    # different FP32 order
+    np.testing.assert_allclose(ca[fin], cb[fin], rtol=2e-5)
+    # labels: state index within the word in the fused kernel's global numbering w*S+s == graph offset + s.  Equal
+    # except where two paths tie within the FP32 re-association noise; there the fused path's own cost (FP64, from the
+    # K1 emissions) must equal the optimum within the same tolerance.
     offn = np.asarray(off, np.int64)
+    En = b.E.cpu().numpy().astype(np.float64)
+
+    def path_cost(lbl, u):
+        l = lbl[offn[u]:offn[u + 1]] - words[u] * S
+        e = En[offn[u]:offn[u + 1]]
+        tr = trans[words[u]].astype(np.float64)
+        return e[np.arange(len(l)), l].sum() + tr[l[1:], l[:-1]].sum()
+
+    ties = [u for u in np.nonzero(fin)[0] if not np.array_equal(la[offn[u]:offn[u + 1]], lb[offn[u]:offn[u + 1]])]
+    assert len(ties) <= max(1, fin.sum() // 20)
+    for u in list(np.nonzero(fin)[0][:8]) + ties:
+        assert abs(path_cost(lb, u) - cb[u]) <= 2e-5 * abs(cb[u])
+        assert abs(path_cost(la, u) - cb[u]) <= 2e-5 * abs(cb[u])
+        assert la[offn[u]] == words[u] * S and la[offn[u + 1] - 1] == words[u] * S + S - 1
+    assert np.array_equal(la[np.repeat(~fin, np.diff(offn))], lb[np.repeat(~fin, np.diff(offn))])
+    # boundaries == get_segments_from_path of the fused labels
     sg = seg.cpu().numpy()
     for u in np.nonzero(fin)[0]:
-        l = lb[offn[u]:offn[u + 1]] - words[u] * S
+        l = la[offn[u]:offn[u + 1]] - words[u] * S
+        assert np.all(np.diff(l) >= 0)
         cnt = np.bincount(l, minlength=S)
         assert np.array_equal(sg[u, 1:], np.cumsum(cnt)[:-1]) and sg[u, 0] == 0
+    # statistics: K5 on the fused kernel's alignment
+    b.plan.label.copy_(lab)
+    b.plan.best_cost.copy_(a.best_cost)
+    b.accumulate()
     G, row = a.G, a.row
     sa, sb = a.stats[:G * row].cpu().numpy().reshape(G, row), b.stats[:G * row].cpu().numpy().reshape(G, row)
     scale = np.abs(sb).max(axis=1, keepdims=True) + 1e-30
