@@ -33,9 +33,9 @@ W_, S_, M_, D_ = 11, 5, 4, 39
 NCOMP = int(np.log(M_)) and 2 ** int(np.log(M_))   # hmm.py:104: n_splits = int(np.log(4)) = 1 -> 2 trained components
 FMA_PER_FRAME_DECODE = W_ * S_ * M_ * 2 * D_          # 17 160 FMA per frame (all 11 words scored)
 # DRAM bytes per frame of the two headline kernels, from the committed `ncu --set full` captures
-# (dram__bytes_read.sum + dram__bytes_write.sum over a 2 M-frame launch; algorithmic: 156 B/frame of X + outputs)
+# (dram__bytes_read.sum + dram__bytes_write.sum over one 2 M-frame / 10 M-frame launch; algorithmic: 156 B/frame of X + outputs)
 NCU_TRAFFIC_PER_FRAME = {"classify_kernel<39>": (318.694e6 / 2e6, "profiles/r01_ncu_classify_v3_raw.csv"),
-                         "em_isolated_kernel<39,5,2>": (317.632e6 / 2e6, "profiles/r01_ncu_emfused_v3_raw.csv")}
+                         "em_isolated_kernel<39,5,2>": ((1565.19e6 + 4.78e6) / 1e7, "profiles/r01_ncu_emfused_v6_raw.csv")}
 
 
 def ncu_traffic(kernel, frames):
