@@ -1,0 +1,263 @@
+// score_tc.cu -- fused isolated-word classifier with the GMM contraction on the 5th-generation tensor cores.
+//
+// Same contract as classify_kernel (score.cu; core.py:79-87 over hmm.py:133-135 / decode.py:97-124), different engine
+// for the [x'^2, x'] . [A, B] contraction of GMM.evaluate (hmm_state.py:36-45,114-120):
+//   * a tile is 128 frames = the 128 lanes of tensor memory.  Thread t builds frame t's 2*D features in registers,
+//     splits each into a TF32 pair (hi = rna(x), lo = x - hi, exact) and writes both halves straight into TMEM
+//     (tcgen05.st, thread = lane): the A operand never touches shared memory;
+//   * the model's Gaussians are the N columns (220 -> 224 for the 11-word digit model), split the same way once per
+//     model update (srb_pack_model_tc) and resident in shared memory for the whole kernel;
+//   * one thread issues K/8 x 3 tcgen05.mma.kind::tf32 (lo*hi + hi*lo + hi*hi: the 3xTF32 scheme of the north star;
+//     measured error 4.4e-7 of sum|a*b|, the FP32 FMA chain's is 2.3e-7 -- tools/probe_tc.cu) accumulating the log2
+//     densities of all Gaussians of all words for the 128 frames in TMEM;
+//   * all 8 warps read the accumulators back (tcgen05.ld, thread = frame), add the constants, take the per-state
+//     log-sum-exp and write state costs into a shared 256-frame ring;
+//   * the Viterbi recursions of the previous 256 frames (classify_dp.cuh) run while the tensor core works on the
+//     current tile; X of the next tile streams in with cp.async at the same time.
+// Shared memory: B operand 2 x 70 KB + cost ring 55 KB + frame staging 20 KB; TMEM: 224 accumulator + 160 operand columns.
+#include "classify_dp.cuh"
+#include "score_core.cuh"
+#include "tc05.cuh"
+
+namespace srb {
+
+constexpr int TC_M = 128;              // frames per MMA tile (TMEM lanes)
+constexpr int TC_NT = 256;             // threads per CTA
+constexpr int TC_CHUNK = 2 * TC_M;     // frames per Viterbi chunk (cost ring)
+constexpr int TC_NMAX = 256;           // Gaussian columns of one MMA
+constexpr int TC_COL_A = 256;          // TMEM column of the A operand (accumulators sit in [0, NP))
+constexpr int TC_MP = 4;               // Gaussians per state handled by the epilogue
+
+__host__ __device__ constexpr int tc_kp(int D) { return (2 * D + 7) & ~7; }
+static int tc_np(int R, int Mp) { return (R * Mp + 15) & ~15; }
+
+// Gaussian parameters -> TF32 (hi, lo) pair in the K-major chunk-plane layout of tc05.cuh: tcb[2][KP/4][NP][4].
+// Feature k = 2*d is x'^2 (coefficient A), k = 2*d + 1 is x' (coefficient B); rows past R*Mp and k >= 2*D are zero.
+__global__ void pack_tc_kernel(const float *__restrict__ ab, int R, int Mp, int D, int NP, int KP, uint32_t *__restrict__ tcb) {
+    const int total = KP * NP;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const int kc = i / (NP * 4), n = (i >> 2) % NP, k = kc * 4 + (i & 3);
+        float v = 0.f;
+        if (n < R * Mp && k < 2 * D) {
+            const int r = n / Mp, m = n % Mp;
+            v = ab[(((size_t)r * (Mp >> 2) + (m >> 2)) * D + (k >> 1)) * 8 + 2 * (m & 3) + (k & 1)];
+        }
+        uint32_t h, l;
+        tc::split_tf32(v, h, l);
+        tcb[i] = h;
+        tcb[total + i] = l;
+    }
+}
+
+template <int D>
+__global__ void __launch_bounds__(TC_NT, 1)
+classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off, int B, int64_t N,
+                   const uint32_t *__restrict__ tcb, const float *__restrict__ c, const float *__restrict__ shift, int W,
+                   int S, int NP, const float *__restrict__ trans, float *__restrict__ final_cost,
+                   int32_t *__restrict__ label) {
+    constexpr int KP = tc_kp(D), SMAX = SRB_DP_MAX_STATES;
+    extern __shared__ __align__(128) float smem[];
+    __shared__ uint64_t bar;
+    __shared__ uint32_t tslot;
+    __shared__ int band_flag;
+    const int R = W * S, ES = R | 1;
+    float *shift_s = smem;                                   // 64
+    float *tr_s = shift_s + 64;                              // W*SMAX*SMAX   tr_s[w][i][j] = cost j->i
+    float *carry = tr_s + W * SMAX * SMAX;                   // 2*W*SMAX
+    float *pc = carry + 2 * W * SMAX;                        // NP
+    uint32_t *Bh = reinterpret_cast<uint32_t *>(pc + NP);    // KP*NP, 16-byte aligned
+    uint32_t *Bl = Bh + KP * NP;
+    float *xs = reinterpret_cast<float *>(Bl + KP * NP);     // TC_M*D + 4 (+ pad)
+    float *Es = xs + ((TC_M * D + 4 + 3) & ~3);              // TC_CHUNK * ES
+    const int tid = threadIdx.x, wq = tid >> 5;
+
+    // utterance range of this CTA: boundaries at the first utterance starting at or after b*N/grid
+    const int G = gridDim.x, b = blockIdx.x;
+    const int ub = (b == 0) ? 0 : lower_bound_i32(off, B + 1, (int64_t)b * N / G);
+    const int ue = (b == G - 1) ? B : lower_bound_i32(off, B + 1, (int64_t)(b + 1) * N / G);
+    if (ub >= ue) return;                                    // uniform: before any TMEM allocation
+
+    if (wq == 0) tc::tmem_alloc<512>(&tslot);
+    if (tid == 32) {
+        tc::mbar_init(&bar, 1);
+        tc::mbar_fence_init();
+    }
+    if (tid == 0) band_flag = 1;
+    if (tid < D) shift_s[tid] = shift[tid];
+    __syncthreads();
+    for (int i = tid; i < W * SMAX * SMAX; i += TC_NT) {
+        const int w = i / (SMAX * SMAX), r = (i / SMAX) % SMAX, o = i % SMAX;
+        float v = CUDART_INF_F;
+        if (r < S && o < S) v = trans[((size_t)w * S + r) * S + o];
+        tr_s[i] = v;
+        if (v < CUDART_INF_F && (o > r || r - o > 2)) band_flag = 0;   // benign race: all writers store 0
+    }
+    copy_to_smem(reinterpret_cast<float *>(Bh), reinterpret_cast<const float *>(tcb), (int64_t)2 * KP * NP);
+    for (int i = tid; i < NP; i += TC_NT) pc[i] = i < R * TC_MP ? c[i] : -CUDART_INF_F;
+    tc::fence_async_smem();                                  // B was written through the generic proxy
+    tc::fence_before_sync();
+    __syncthreads();
+    tc::fence_after_sync();
+    const bool banded = band_flag != 0;
+    const uint32_t tb = tslot;
+    const uint32_t lane_base = tb + ((uint32_t)((wq & 3) * 32) << 16);
+    const uint32_t idesc = tc::idesc_tf32(TC_M, NP);
+    const uint32_t bH = tc::smem_u32(Bh), bL = tc::smem_u32(Bl);
+
+    const int64_t fbeg = off[ub], fend = off[ue];
+    const int ntile = (int)((fend - fbeg + TC_M - 1) / TC_M);
+    int ufirst = ub, par = 0;
+    uint32_t phase = 0;
+    int nf = (int)min((int64_t)TC_M, fend - fbeg);
+    int xoff = stage_frames_async<D, TC_NT>(xs, X, N, fbeg, nf);
+
+    for (int j = 0; j < ntile; ++j) {
+        const int64_t cf0 = fbeg + (int64_t)j * TC_M;
+        cp_async_wait_all();
+        __syncthreads();                                     // frames of tile j staged; epilogue j-1 done with TMEM
+        // ---- A operand: thread = frame = TMEM lane
+        if (wq < 4) {
+            const int lf = tid < nf ? tid : nf - 1;          // frames past the end repeat the last one (discarded)
+            const float *row = xs + xoff + lf * D;
+#pragma unroll
+            for (int k0 = 0; k0 < KP; k0 += 8) {
+                uint32_t h[8], l[8];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int d = (k0 >> 1) + q;
+                    const float v = d < D ? row[d] - shift_s[d] : 0.f;
+                    tc::split_tf32(v * v, h[2 * q], l[2 * q]);
+                    tc::split_tf32(v, h[2 * q + 1], l[2 * q + 1]);
+                }
+                tc::tmem_st8(lane_base + TC_COL_A + k0, h);
+                tc::tmem_st8(lane_base + TC_COL_A + KP + k0, l);
+            }
+            tc::tmem_st_wait();
+        }
+        tc::fence_before_sync();
+        __syncthreads();
+        tc::fence_after_sync();
+        // ---- log2 densities of all Gaussians: D[128 x NP] = A_lo B_hi^T + A_hi B_lo^T + A_hi B_hi^T
+        if (tid == 0) {
+#pragma unroll
+            for (int kk = 0; kk < KP / 8; ++kk) {
+                const uint64_t dbh = tc::smem_desc(bH + kk * 2 * NP * 16, NP * 16, 128);
+                const uint64_t dbl = tc::smem_desc(bL + kk * 2 * NP * 16, NP * 16, 128);
+                tc::mma_tf32_ts(tb, tb + TC_COL_A + KP + kk * 8, dbh, idesc, kk > 0);
+                tc::mma_tf32_ts(tb, tb + TC_COL_A + kk * 8, dbl, idesc, true);
+                tc::mma_tf32_ts(tb, tb + TC_COL_A + kk * 8, dbh, idesc, true);
+            }
+            tc::mma_commit(&bar);
+        }
+        // ---- while the tensor core runs: next tile's frames, previous chunk's Viterbi
+        const int nf_next = (j + 1 < ntile) ? (int)min((int64_t)TC_M, fend - (cf0 + TC_M)) : 0;
+        int xoff_next = 0;
+        if (nf_next > 0) xoff_next = stage_frames_async<D, TC_NT>(xs, X, N, cf0 + TC_M, nf_next);
+        if ((j & 1) == 0 && j >= 2) {
+            const int64_t v0 = cf0 - TC_CHUNK;
+            classify_dp_chunk<TC_NT>(Es, ES, off, ue, ufirst, v0, v0 + TC_CHUNK, W, S, tr_s, carry, par, banded,
+                                     final_cost, label);
+            par ^= 1;
+        }
+        tc::mbar_wait(&bar, phase);
+        phase ^= 1;
+        tc::fence_after_sync();
+        // ---- epilogue: state cost = -ln sum_m 2^(D + c)   (warps 0-3: first half of the states, 4-7: second half)
+        {
+            const int sh = (((R + 1) >> 1) + 3) & ~3;
+            const int s_lo = (wq >> 2) * sh, s_hi = min(R, s_lo + sh);
+            float *erow = Es + (size_t)((j & 1) * TC_M + (tid & (TC_M - 1))) * ES;
+            for (int s0 = s_lo; s0 < s_hi; s0 += 4) {
+                float v[16];
+                tc::tmem_ld16(lane_base + s0 * TC_MP, v);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float4 cc = *reinterpret_cast<const float4 *>(pc + (s0 + q) * TC_MP);
+                    const float l0 = v[4 * q] + cc.x, l1 = v[4 * q + 1] + cc.y, l2 = v[4 * q + 2] + cc.z,
+                                l3 = v[4 * q + 3] + cc.w;
+                    const float m = fmaxf(fmaxf(l0, l1), fmaxf(l2, l3));
+                    float cost = CUDART_INF_F;
+                    if (m > -CUDART_INF_F) cost = -LN2_F * (m + lg2(ex2(l0 - m) + ex2(l1 - m) + ex2(l2 - m) + ex2(l3 - m)));
+                    if (s0 + q < s_hi) erow[s0 + q] = cost;
+                }
+            }
+        }
+        tc::fence_before_sync();
+        nf = nf_next;
+        xoff = xoff_next;
+    }
+    __syncthreads();
+    if (ntile > 0) {   // the last one or two tiles
+        const int jl = (ntile - 1) & ~1;
+        const int64_t v0 = fbeg + (int64_t)jl * TC_M;
+        classify_dp_chunk<TC_NT>(Es, ES, off, ue, ufirst, v0, min(fend, v0 + (int64_t)TC_CHUNK), W, S, tr_s, carry, par,
+                                 banded, final_cost, label);
+    }
+    tc::fence_before_sync();
+    __syncthreads();
+    if (wq == 0) tc::tmem_free<512>(tb);
+}
+
+static size_t classify_tc_smem_bytes(int W, int S, int NP, int D) {
+    const int R = W * S, KP = tc_kp(D);
+    return 4 * (64 + (size_t)W * SRB_DP_MAX_STATES * SRB_DP_MAX_STATES + 2 * (size_t)W * SRB_DP_MAX_STATES + NP +
+                2 * (size_t)KP * NP + (((size_t)TC_M * D + 4 + 3) & ~(size_t)3) + (size_t)TC_CHUNK * (R | 1));
+}
+
+}  // namespace srb
+
+using namespace srb;
+
+extern "C" {
+
+int64_t srb_tc_model_floats(int R, int Mp, int D) {
+    if (R <= 0 || Mp <= 0 || (Mp & 3) || D <= 0 || tc_np(R, Mp) > TC_NMAX) return 0;
+    return 2 * (int64_t)tc_kp(D) * tc_np(R, Mp);
+}
+
+int srb_pack_model_tc(const float *ab, int R, int Mp, int D, float *tcb, void *stream) {
+    SRB_REQUIRE(ab && tcb, SRB_EINVAL, "srb_pack_model_tc: null pointer");
+    SRB_REQUIRE(srb_tc_model_floats(R, Mp, D) > 0, SRB_EUNSUPPORTED,
+                "srb_pack_model_tc: %d states x %d Gaussians exceed %d tensor-core columns", R, Mp, TC_NMAX);
+    SRB_REQUIRE(((uintptr_t)tcb & 15) == 0, SRB_EINVAL, "srb_pack_model_tc: tcb must be 16-byte aligned");
+    const int NP = tc_np(R, Mp), KP = tc_kp(D);
+    pack_tc_kernel<<<(KP * NP + 255) / 256, 256, 0, (cudaStream_t)stream>>>(ab, R, Mp, D, NP, KP,
+                                                                              reinterpret_cast<uint32_t *>(tcb));
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+int srb_classify_tc_supported(int D, int W, int S, int Mp) {
+    if (D != 39 || Mp != TC_MP || W <= 0 || S <= 0 || S > SRB_DP_MAX_STATES) return 0;
+    const int NP = tc_np(W * S, Mp);
+    if (NP > TC_NMAX) return 0;
+    const int cap = smem_optin();
+    return cap > 0 && classify_tc_smem_bytes(W, S, NP, D) + 64 <= (size_t)cap;
+}
+
+int srb_classify_tc(const float *X, const int32_t *utt_off, int32_t B, int64_t N, int D, const float *tcb, const float *c,
+                    const float *shift, int W, int S, int Mp, const float *trans, float *final_cost, int32_t *label,
+                    void *stream) {
+    SRB_REQUIRE(((X && final_cost) || B == 0 || N == 0) && utt_off && tcb && c && shift && trans, SRB_EINVAL,
+                "srb_classify_tc: null pointer");
+    SRB_REQUIRE(B >= 0 && N >= 0, SRB_EINVAL, "srb_classify_tc: bad sizes");
+    SRB_REQUIRE(srb_classify_tc_supported(D, W, S, Mp), SRB_EUNSUPPORTED,
+                "srb_classify_tc: D=%d, %d words x %d states x %d Gaussians not covered by the tensor-core classifier "
+                "(D = 39, Mp = 4, at most %d Gaussians); use srb_classify", D, W, S, Mp, TC_NMAX);
+    SRB_REQUIRE(((uintptr_t)X & 15) == 0 && ((uintptr_t)tcb & 15) == 0 && ((uintptr_t)c & 15) == 0, SRB_EINVAL,
+                "srb_classify_tc: X, tcb, c must be 16-byte aligned");
+    if (B == 0 || N == 0) return SRB_OK;
+    const int sms = sm_count();
+    SRB_REQUIRE(sms > 0, SRB_ENODEVICE, "no CUDA device");
+    const int NP = tc_np(W * S, Mp);
+    const size_t bytes = classify_tc_smem_bytes(W, S, NP, D);
+    const int64_t want = (N + TC_CHUNK - 1) / TC_CHUNK;
+    const int grid = (int)(want < sms ? want : sms);
+    SRB_CUDA(cudaFuncSetAttribute(classify_tc_kernel<39>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    classify_tc_kernel<39><<<grid, TC_NT, bytes, (cudaStream_t)stream>>>(
+        X, utt_off, B, N, reinterpret_cast<const uint32_t *>(tcb), c, shift, W, S, NP, trans, final_cost, label);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+}  // extern "C"

@@ -43,13 +43,22 @@ class PackedModel:
         self.ab = torch.empty(L.srb_packed_ab_floats(self.R, self.M, self.D), dtype=torch.float32, device=dev)
         self.c = torch.empty(L.srb_packed_c_floats(self.R, self.M), dtype=torch.float32, device=dev)
         self.shift = torch.empty(self.D, dtype=torch.float32, device=dev)
+        n_tc = int(L.srb_tc_model_floats(self.R, self.Mp, self.D))      # TF32-split copy for the tensor-core classifier
+        self.tcb = torch.empty(n_tc, dtype=torch.float32, device=dev) if n_tc > 0 else None
         self.repack()
 
     def repack(self):
         _l.check(_l.load().srb_pack_model(_l.ptr(self.mu), _l.ptr(self.var), _l.ptr(self.w), _l.ptr(self.shift64),
                                           self.R, self.M, self.D, _l.ptr(self.ab), _l.ptr(self.c),
                                           _l.ptr(self.shift), _l.stream_ptr()))
+        if self.tcb is not None:
+            _l.check(_l.load().srb_pack_model_tc(_l.ptr(self.ab), self.R, self.Mp, self.D, _l.ptr(self.tcb),
+                                                 _l.stream_ptr()))
         return self
+
+    def tensor_core_ok(self, W, S):
+        """True when srb_classify_tc covers this model (D = 39, 4 Gaussians per state, <= 256 Gaussians)."""
+        return self.tcb is not None and bool(_l.load().srb_classify_tc_supported(self.D, W, S, self.Mp))
 
     @classmethod
     def from_words(cls, word_models, shift=None):
@@ -98,8 +107,9 @@ def gmm_score(X, pm, want_E=True, want_best=False, want_comp=False):
     return out
 
 
-def classify(X, off, pm, trans, W, S, final=None, label=None):
-    """Fused score + Viterbi over W isolated-word models (core.py:79-87).  -> (final[B,W] f32, label[B] i32)."""
+def classify(X, off, pm, trans, W, S, final=None, label=None, tensor=None):
+    """Fused score + Viterbi over W isolated-word models (core.py:79-87).  -> (final[B,W] f32, label[B] i32).
+    tensor: None = the tcgen05 (3xTF32) kernel when it covers the model, else the FFMA kernel; True / False force one."""
     X = as_frames(X)
     off = as_offsets(off)
     B = off.numel() - 1
@@ -108,9 +118,16 @@ def classify(X, off, pm, trans, W, S, final=None, label=None):
         final = torch.empty((B, W), dtype=torch.float32, device=X.device)
     if label is None:
         label = torch.empty(B, dtype=torch.int32, device=X.device)
-    _l.check(_l.load().srb_classify(_l.ptr(X), _l.ptr(off), B, X.shape[0], pm.D, _l.ptr(pm.ab), _l.ptr(pm.c),
-                                    _l.ptr(pm.shift), W, S, pm.Mp, _l.ptr(trans), _l.ptr(final), _l.ptr(label),
-                                    _l.stream_ptr()))
+    if tensor is None:
+        tensor = pm.tensor_core_ok(W, S)
+    if tensor:
+        _l.check(_l.load().srb_classify_tc(_l.ptr(X), _l.ptr(off), B, X.shape[0], pm.D, _l.ptr(pm.tcb), _l.ptr(pm.c),
+                                           _l.ptr(pm.shift), W, S, pm.Mp, _l.ptr(trans), _l.ptr(final),
+                                           _l.ptr(label), _l.stream_ptr()))
+    else:
+        _l.check(_l.load().srb_classify(_l.ptr(X), _l.ptr(off), B, X.shape[0], pm.D, _l.ptr(pm.ab), _l.ptr(pm.c),
+                                        _l.ptr(pm.shift), W, S, pm.Mp, _l.ptr(trans), _l.ptr(final), _l.ptr(label),
+                                        _l.stream_ptr()))
     return final, label
 
 
@@ -169,10 +186,12 @@ class HostClassifier:
                 st.wait_event(start)
                 self.xbuf[s][:f1 - f0].copy_(Xt[f0:f1], non_blocking=True)
                 self.obuf[s][:nb + 1].copy_(self.off_pin[s][:nb + 1], non_blocking=True)
-                _l.check(L.srb_classify(self.xbuf[s].data_ptr(), self.obuf[s].data_ptr(), nb, f1 - f0, self.pm.D,
-                                        _l.ptr(self.pm.ab), _l.ptr(self.pm.c), _l.ptr(self.pm.shift), self.W, self.S,
-                                        self.pm.Mp, _l.ptr(self.trans), self.final[s].data_ptr(),
-                                        self.label[s].data_ptr(), st.cuda_stream))
+                tensor = self.pm.tensor_core_ok(self.W, self.S)
+                fn, par = (L.srb_classify_tc, self.pm.tcb) if tensor else (L.srb_classify, self.pm.ab)
+                _l.check(fn(self.xbuf[s].data_ptr(), self.obuf[s].data_ptr(), nb, f1 - f0, self.pm.D,
+                            _l.ptr(par), _l.ptr(self.pm.c), _l.ptr(self.pm.shift), self.W, self.S,
+                            self.pm.Mp, _l.ptr(self.trans), self.final[s].data_ptr(),
+                            self.label[s].data_ptr(), st.cuda_stream))
                 labels_out[u0:u1].copy_(self.label[s][:nb], non_blocking=True)
                 if final_out is not None:
                     final_out[u0:u1].copy_(self.final[s][:nb], non_blocking=True)

@@ -80,13 +80,15 @@ def test_gmm_score_param_groups(eng):
     assert np.array_equal(out["best_state"].cpu().numpy(), E.argmin(axis=1))
 
 
+@pytest.mark.parametrize("tensor", [False, True], ids=["ffma", "tcgen05"])
 @pytest.mark.parametrize("ragged", [None, (2, 40), (300, 1300)])
-def test_classify_matches_oracle(eng, ragged):
+def test_classify_matches_oracle(eng, ragged, tensor):
     from srb200 import synth
     models, base = _models(11, W=11, S=5, M=4)
     X, off, words = synth.make_utterances(12, base, 64 if ragged != (300, 1300) else 9, T=100, ragged=ragged)
     pm, trans = eng.PackedModel.from_words(models)
-    final, label = eng.classify(X, off, pm, trans, 11, 5)
+    assert pm.tensor_core_ok(11, 5)
+    final, label = eng.classify(X, off, pm, trans, 11, 5, tensor=tensor)
     final, label = final.cpu().numpy(), label.cpu().numpy()
     fo, lo = orc.classify(X.astype(np.float64), off.astype(np.int64), models, log_domain=True)
     fin = np.isfinite(fo)
@@ -101,19 +103,24 @@ def test_classify_matches_oracle(eng, ragged):
         assert (label == words).mean() > 0.95
 
 
-def test_classify_golden_reference(eng, golden):
+@pytest.mark.parametrize("tensor", [False, True], ids=["ffma", "tcgen05"])
+def test_classify_golden_reference(eng, golden, tensor):
     """Frozen HMM.evaluate outputs of the reference (hmm.py:126-135) for 3 isolated models."""
     g = golden["decode"]
     models = [(g["iso_mu"][i], g["iso_cov"][i], g["iso_w"][i], g["iso_trans"][i]) for i in range(len(g["iso_mu"]))]
     pm, trans = eng.PackedModel.from_words(models)
     W, S = len(models), models[0][0].shape[0]
-    final, label = eng.classify(g["iso_X"].astype(np.float32), g["iso_off"].astype(np.int32), pm, trans, W, S)
+    if tensor and not pm.tensor_core_ok(W, S):
+        pytest.skip("golden model outside the tensor-core classifier's shapes")
+    final, label = eng.classify(g["iso_X"].astype(np.float32), g["iso_off"].astype(np.int32), pm, trans, W, S,
+                                tensor=tensor)
     ref = g["iso_final"]                                          # [B, W]
     f = np.isfinite(ref)
     np.testing.assert_allclose(final.cpu().numpy()[f], ref[f], rtol=RTOL)
 
 
-def test_classify_dense_transitions(eng):
+@pytest.mark.parametrize("tensor", [False, True], ids=["ffma", "tcgen05"])
+def test_classify_dense_transitions(eng, tensor):
     """Non left-to-right (ergodic) transitions take the dense DP branch."""
     from srb200 import synth
     rng = np.random.default_rng(5)
@@ -121,6 +128,32 @@ def test_classify_dense_transitions(eng):
     models = [(m[0], m[1], m[2], rng.uniform(0.5, 3.0, size=(4, 4))) for m in models]
     X, off, _ = synth.make_utterances(22, base, 10, T=30)
     pm, trans = eng.PackedModel.from_words(models)
-    final, _ = eng.classify(X, off, pm, trans, 4, 4)
+    final, _ = eng.classify(X, off, pm, trans, 4, 4, tensor=tensor)
     fo, _ = orc.classify(X.astype(np.float64), off.astype(np.int64), models, log_domain=True)
     np.testing.assert_allclose(final.cpu().numpy(), fo, rtol=RTOL)
+
+
+@pytest.mark.parametrize("W,S,ragged,n", [(11, 5, (2, 300), 6000), (10, 5, (90, 110), 3000), (3, 8, (5, 700), 800),
+                                          (1, 2, (2, 9), 50)])
+def test_classify_tensor_core_equals_ffma(eng, W, S, ragged, n):
+    """srb_classify_tc (tcgen05 3xTF32, TMEM accumulators) against srb_classify (FFMA2) on corpora that fill the whole
+    grid: costs within FP32 accumulation noise, labels equal wherever the two best words are further apart than
+    that; utterances straddle tiles, chunks and CTA ranges."""
+    from srb200 import synth
+    models, base = _models(31 + W, W=W, S=S, M=4)
+    X, off, words = synth.make_utterances(32, base, n, ragged=ragged, noise=0.9)
+    pm, trans = eng.PackedModel.from_words(models)
+    assert pm.tensor_core_ok(W, S)
+    fa, la = eng.classify(X, off, pm, trans, W, S, tensor=False)
+    fb, lb = eng.classify(X, off, pm, trans, W, S, tensor=True)
+    fa, la, fb, lb = fa.cpu().numpy(), la.cpu().numpy(), fb.cpu().numpy(), lb.cpu().numpy()
+    assert np.array_equal(np.isfinite(fa), np.isfinite(fb))
+    fin = np.isfinite(fa)
+    np.testing.assert_allclose(fb[fin], fa[fin], rtol=2e-5)
+    so = np.sort(np.where(fin, fa, np.inf), axis=1)
+    if W > 1:
+        decided = ~(so[:, 1] - so[:, 0] <= 1e-4 * np.abs(so[:, 0]))
+        assert decided.mean() > 0.9
+        assert np.array_equal(la[decided], lb[decided])
+    else:
+        assert np.array_equal(la, lb)
