@@ -39,6 +39,8 @@ NCU_TRAFFIC_PER_FRAME = {"classify_kernel<39>": (318.694e6 / 2e6, "profiles/r01_
 
 
 def ncu_traffic(kernel, frames):
+    if kernel not in NCU_TRAFFIC_PER_FRAME:
+        return {"traffic": None, "traffic_source": "no ncu --set full capture committed for this kernel yet"}
     per, src = NCU_TRAFFIC_PER_FRAME[kernel]
     return {"traffic": per * frames, "traffic_source": f"{per:.1f} B/frame x frames per launch, {src}"}
 
@@ -55,6 +57,7 @@ def parse():
     ap.add_argument("--cpu-utts", type=int, default=0, help="utterances of the CPU sample (0 = auto)")
     ap.add_argument("--no-decode", action="store_true", help="skip the decode sub-benchmark of the em line")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--ffma", action="store_true", help="decode: force the FP32-FMA classifier instead of the tcgen05 one")
     ap.add_argument("--unfused", action="store_true", help="em: use the separate K1/K2/K5 kernels instead of the fused pass")
     return ap.parse_args()
 
@@ -183,8 +186,10 @@ def bench_decode(args, ctx):
     final = torch.empty((B, W_), dtype=torch.float32, device="cuda")
     label = torch.empty(B, dtype=torch.int32, device="cuda")
 
+    tensor = pm.tensor_core_ok(W_, S_) and not args.ffma
+
     def step():
-        engine.classify(Xd, offd, pm, trans, W_, S_, final, label)
+        engine.classify(Xd, offd, pm, trans, W_, S_, final, label, tensor=tensor)
 
     sampler = ClockSampler(ctx["local"])
     sampler.start()
@@ -194,18 +199,35 @@ def bench_decode(args, ctx):
     kern_ms = float(np.mean(per))
     flops = 2.0 * FMA_PER_FRAME_DECODE * N / (kern_ms * 1e-3)
     peak_fma = ctx["peak_fma"]
+    pk = peaks()
+    hbm = {"achieved_gbs": (N * D_ * 4 + B * (W_ + 1) * 4) / (kern_ms * 1e-3) / 1e9, "peak_gbs": pk.get("hbm_gbs")}
+    if tensor:
+        # tcgen05 classifier: the contraction runs as 3 TF32 products per FP32 product on 128 x 224 x 80 tiles
+        # (N 220 -> 224, K 78 -> 80).  `achieved` stays the ALGORITHMIC rate (17 160 FMA per frame);
+        # `peak` is the measured dense bf16 rate, of which TF32 gets half and the 3-way split a third of that.
+        bf16 = pk.get("bf16_tflops", 2250.0)
+        executed = 3 * 2.0 * 224 * 80 * N / (kern_ms * 1e-3)
+        roof = {"bound": "tensor", "achieved": flops / 1e12, "peak": bf16, "unit": "TFLOP/s", "frac": flops / 1e12 / bf16,
+                **ncu_traffic("classify_tc_kernel<39>", N), "kernel": "classify_tc_kernel<39>", "kernel_ms": kern_ms,
+                "peak_source": "MEASURED_PEAKS.json bf16_tflops (burst)" if "bf16_tflops" in pk else "nominal 2250",
+                "algorithmic": "17160 FMA/frame = 220 Gaussians x 2*39 (SURVEY 8d), FP32-equivalent",
+                "tensor_pipe": {"executed_tflops": executed / 1e12, "tf32_peak_tflops": bf16 / 2,
+                                "frac": executed / 1e12 / (bf16 / 2),
+                                "note": "executed = 3 TF32 MMAs per product on padded 128x224x80 tiles"},
+                "fp32_fma": {"peak_tflops": 2 * peak_fma / 1e12, "frac": flops / (2 * peak_fma),
+                             "note": "algorithmic rate over the measured FFMA2 peak; > 1 = above the CUDA-core roofline"},
+                "hbm": hbm}
+    else:
+        roof = {"bound": "fp32_fma", "achieved": flops / 1e12, "peak": 2 * peak_fma / 1e12,
+                "unit": "TFLOP/s", "frac": flops / (2 * peak_fma), **ncu_traffic("classify_kernel<39>", N),
+                "kernel": "classify_kernel<39>", "kernel_ms": kern_ms,
+                "peak_source": "srb_fma_peak (FFMA2 probe) measured in this run",
+                "algorithmic": "17160 FMA/frame = 220 Gaussians x 2*39 (SURVEY 8d)", "hbm": hbm}
     out = {
         "metric": "decoded frames/s (GMM scoring of all 11 word models + Viterbi)",
         "value": world * N * args.steps / (total_ms * 1e-3), "unit": "frames/s", "ms_per_step": total_ms / args.steps,
-        "gpu_launches": args.steps,          # one fused classify_kernel launch per step
-        "roofline": {"bound": "fp32_fma", "achieved": flops / 1e12, "peak": 2 * peak_fma / 1e12,
-                     "unit": "TFLOP/s", "frac": flops / (2 * peak_fma), **ncu_traffic("classify_kernel<39>", N),
-                     "kernel": "classify_kernel<39>", "kernel_ms": kern_ms,
-                     "peak_source": "srb_fma_peak (FFMA2 probe) measured in this run",
-                     "algorithmic": "17160 FMA/frame = 220 Gaussians x 2*39 (SURVEY 8d)",
-                     "hbm": {"achieved_gbs": (N * D_ * 4 + B * (W_ + 1) * 4) / (kern_ms * 1e-3) / 1e9,
-                             "peak_gbs": peaks().get("hbm_gbs")}},
-        "accuracy": acc, "clocks": clocks,
+        "gpu_launches": args.steps,          # one fused classifier launch per step
+        "roofline": roof, "accuracy": acc, "clocks": clocks,
     }
     # ---- end to end: pinned host buffers -> chunked H2D on two streams -> classify -> D2H labels
     Xh = torch.from_numpy(X).pin_memory()

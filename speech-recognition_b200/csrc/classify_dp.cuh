@@ -3,17 +3,54 @@
 // frames whose state costs E[frame - cf0][w*S + s] sit in shared memory; thread = (piece, word), states in registers.
 // The costs of the utterance that straddles the chunk end are carried in shared memory (carry[par] in, carry[par^1]
 // out).  Finished utterances write costs[-1,-1] per word (hmm.py:135) and, once all words are in, the arg-min label
-// (core.py:82-87: strict '<', first model wins).  Must be called by all NTH threads of the CTA.
+// (core.py:82-87: strict '<', first model wins).  Must be called by the NTH threads (tid = 0 .. NTH-1) that share
+// named barrier BAR_ID: the whole CTA with barrier 0 in score.cu, the four Viterbi warps in score_tc.cu.
 #pragma once
 #include "common.cuh"
 
 namespace srb {
 
-template <int NTH>
+__device__ __forceinline__ void named_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+__device__ __forceinline__ void named_arrive(int id, int count) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+
+// SN live states of a left-to-right model with skips <= 2 (kmeans.py:53-95), nsteps frames; the next frame's costs
+// are loaded while the current one is folded in.
+template <int SN>
+__device__ __forceinline__ void dp_banded_steps(float (&cost)[SRB_DP_MAX_STATES], const float *Erow, int ES, int nsteps,
+                                                const float *trw) {
+    constexpr int SMAX = SRB_DP_MAX_STATES;
+    float a0[SN], a1[SN], a2[SN], e[SN];
+#pragma unroll
+    for (int r = 0; r < SN; ++r) {
+        a0[r] = trw[r * SMAX + r];
+        a1[r] = r >= 1 ? trw[r * SMAX + r - 1] : CUDART_INF_F;
+        a2[r] = r >= 2 ? trw[r * SMAX + r - 2] : CUDART_INF_F;
+        e[r] = nsteps > 0 ? Erow[r] : 0.f;
+    }
+    for (int n = 0; n < nsteps; ++n) {
+        Erow += ES;
+        float en[SN];
+        const bool more = n + 1 < nsteps;
+#pragma unroll
+        for (int r = 0; r < SN; ++r) en[r] = more ? Erow[r] : 0.f;
+#pragma unroll
+        for (int r = SN - 1; r >= 0; --r) {
+            float best = cost[r] + a0[r];
+            if (r >= 1) best = fminf(best, cost[r - 1] + a1[r]);
+            if (r >= 2) best = fminf(best, cost[r - 2] + a2[r]);
+            cost[r] = best + e[r];
+        }
+#pragma unroll
+        for (int r = 0; r < SN; ++r) e[r] = en[r];
+    }
+}
+
+template <int NTH, int BAR_ID = 0>
 __device__ __forceinline__ void classify_dp_chunk(const float *Es, int ES, const int32_t *__restrict__ off, int ue,
                                                   int &ufirst, int64_t cf0, int64_t cf1, int W, int S,
                                                   const float *tr_s, float *carry, int par, bool banded,
-                                                  float *__restrict__ final_cost, int32_t *__restrict__ label) {
+                                                  float *__restrict__ final_cost, int32_t *__restrict__ label,
+                                                  int tid) {
     constexpr int SMAX = SRB_DP_MAX_STATES;
     while (ufirst + 1 < ue && (int64_t)off[ufirst + 1] <= cf0) ++ufirst;   // first utterance with frames >= cf0
     int ulast = ufirst;
@@ -23,7 +60,7 @@ __device__ __forceinline__ void classify_dp_chunk(const float *Es, int ES, const
         if (ulast >= ue) ulast = ue - 1;
     }
     const int npieces = ulast - ufirst + 1;
-    for (int pw = threadIdx.x; pw < npieces * W; pw += NTH) {
+    for (int pw = tid; pw < npieces * W; pw += NTH) {
         const int p = pw / W, w = pw - p * W;
         const int u = ufirst + p;
         const int64_t us = off[u], uend = off[u + 1];
@@ -43,7 +80,9 @@ __device__ __forceinline__ void classify_dp_chunk(const float *Es, int ES, const
             for (int r = 0; r < SMAX; ++r) cost[r] = carry[(par * W + w) * SMAX + r];
         }
         const float *trw = tr_s + w * SMAX * SMAX;
-        if (banded) {
+        if (banded && S == 5) {                   // the reference's 5-state models (config.py), fully static
+            dp_banded_steps<5>(cost, Erow, ES, (int)(t1 - t), trw);
+        } else if (banded) {
             float a0[SMAX], a1[SMAX], a2[SMAX];
 #pragma unroll
             for (int r = 0; r < SMAX; ++r) {
@@ -87,9 +126,9 @@ __device__ __forceinline__ void classify_dp_chunk(const float *Es, int ES, const
             for (int r = 0; r < SMAX; ++r) carry[((par ^ 1) * W + w) * SMAX + r] = cost[r];
         }
     }
-    __syncthreads();
+    named_sync(BAR_ID, NTH);
     if (label) {   // core.py:82-87: strict '<', first model wins
-        for (int p = threadIdx.x; p < npieces; p += NTH) {
+        for (int p = tid; p < npieces; p += NTH) {
             const int u = ufirst + p;
             const int64_t uend = off[u + 1];
             if (uend > cf0 && uend <= cf1) {

@@ -163,7 +163,8 @@ classify_kernel(const float *__restrict__ X, const int32_t *__restrict__ off, in
         }
         __syncthreads();
         // ---- phase 2: Viterbi over the pieces of this chunk (classify_dp.cuh)
-        classify_dp_chunk<NT>(xs, ES, off, ue, ufirst, cf0, cf1, W, S, tr_s, carry, par, banded, final_cost, label);
+        classify_dp_chunk<NT>(xs, ES, off, ue, ufirst, cf0, cf1, W, S, tr_s, carry, par, banded, final_cost, label,
+                              threadIdx.x);
     }
 }
 

@@ -22,8 +22,11 @@
 namespace srb {
 
 constexpr int TC_M = 128;              // frames per MMA tile (TMEM lanes)
-constexpr int TC_NT = 256;             // threads per CTA
-constexpr int TC_CHUNK = 2 * TC_M;     // frames per Viterbi chunk (cost ring)
+constexpr int TC_MAIN = 256;           // threads of the scoring warps (features, MMA issue, epilogue)
+constexpr int TC_DP = 128;             // threads of the Viterbi warps
+constexpr int TC_NT = TC_MAIN + TC_DP; // threads per CTA
+constexpr int TC_CHUNK = 2 * TC_M;     // frames of the cost ring (two tiles)
+constexpr int TC_BAR_MAIN = 1, TC_BAR_DP = 2, TC_BAR_FULL = 3, TC_BAR_FREE = 5;   // named barriers (FULL/FREE: +slot)
 constexpr int TC_NMAX = 256;           // Gaussian columns of one MMA
 constexpr int TC_COL_A = 256;          // TMEM column of the A operand (accumulators sit in [0, NP))
 constexpr int TC_MP = 4;               // Gaussians per state handled by the epilogue
@@ -106,92 +109,98 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
 
     const int64_t fbeg = off[ub], fend = off[ue];
     const int ntile = (int)((fend - fbeg + TC_M - 1) / TC_M);
-    int ufirst = ub, par = 0;
-    uint32_t phase = 0;
-    int nf = (int)min((int64_t)TC_M, fend - fbeg);
-    int xoff = stage_frames_async<D, TC_NT>(xs, X, N, fbeg, nf);
 
-    for (int j = 0; j < ntile; ++j) {
-        const int64_t cf0 = fbeg + (int64_t)j * TC_M;
-        cp_async_wait_all();
-        __syncthreads();                                     // frames of tile j staged; epilogue j-1 done with TMEM
-        // ---- A operand: thread = frame = TMEM lane
-        if (wq < 4) {
-            const int lf = tid < nf ? tid : nf - 1;          // frames past the end repeat the last one (discarded)
-            const float *row = xs + xoff + lf * D;
-#pragma unroll
-            for (int k0 = 0; k0 < KP; k0 += 8) {
-                uint32_t h[8], l[8];
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const int d = (k0 >> 1) + q;
-                    const float v = d < D ? row[d] - shift_s[d] : 0.f;
-                    tc::split_tf32(v * v, h[2 * q], l[2 * q]);
-                    tc::split_tf32(v, h[2 * q + 1], l[2 * q + 1]);
-                }
-                tc::tmem_st8(lane_base + TC_COL_A + k0, h);
-                tc::tmem_st8(lane_base + TC_COL_A + KP + k0, l);
-            }
-            tc::tmem_st_wait();
-        }
-        tc::fence_before_sync();
-        __syncthreads();
-        tc::fence_after_sync();
-        // ---- log2 densities of all Gaussians: D[128 x NP] = A_lo B_hi^T + A_hi B_lo^T + A_hi B_hi^T
-        if (tid == 0) {
-#pragma unroll
-            for (int kk = 0; kk < KP / 8; ++kk) {
-                const uint64_t dbh = tc::smem_desc(bH + kk * 2 * NP * 16, NP * 16, 128);
-                const uint64_t dbl = tc::smem_desc(bL + kk * 2 * NP * 16, NP * 16, 128);
-                tc::mma_tf32_ts(tb, tb + TC_COL_A + KP + kk * 8, dbh, idesc, kk > 0);
-                tc::mma_tf32_ts(tb, tb + TC_COL_A + kk * 8, dbl, idesc, true);
-                tc::mma_tf32_ts(tb, tb + TC_COL_A + kk * 8, dbh, idesc, true);
-            }
-            tc::mma_commit(&bar);
-        }
-        // ---- while the tensor core runs: next tile's frames, previous chunk's Viterbi
-        const int nf_next = (j + 1 < ntile) ? (int)min((int64_t)TC_M, fend - (cf0 + TC_M)) : 0;
-        int xoff_next = 0;
-        if (nf_next > 0) xoff_next = stage_frames_async<D, TC_NT>(xs, X, N, cf0 + TC_M, nf_next);
-        if ((j & 1) == 0 && j >= 2) {
-            const int64_t v0 = cf0 - TC_CHUNK;
-            classify_dp_chunk<TC_NT>(Es, ES, off, ue, ufirst, v0, v0 + TC_CHUNK, W, S, tr_s, carry, par, banded,
-                                     final_cost, label);
+    if (wq >= TC_MAIN / 32) {
+        // ================= Viterbi warps: tile j's recursions while the main warps produce tile j+1's costs
+        int ufirst = ub, par = 0;
+        for (int j = 0; j < ntile; ++j) {
+            const int64_t cf0 = fbeg + (int64_t)j * TC_M;
+            named_sync(TC_BAR_FULL + (j & 1), TC_NT);        // costs of tile j are in ring slot j & 1
+            classify_dp_chunk<TC_DP, TC_BAR_DP>(Es + (size_t)(j & 1) * TC_M * ES, ES, off, ue, ufirst, cf0,
+                                                min(fend, cf0 + (int64_t)TC_M), W, S, tr_s, carry, par, banded,
+                                                final_cost, label, tid - TC_MAIN);
             par ^= 1;
+            __threadfence_block();
+            named_arrive(TC_BAR_FREE + (j & 1), TC_NT);      // slot may be overwritten (tile j + 2)
         }
-        tc::mbar_wait(&bar, phase);
-        phase ^= 1;
-        tc::fence_after_sync();
-        // ---- epilogue: state cost = -ln sum_m 2^(D + c)   (warps 0-3: first half of the states, 4-7: second half)
-        {
-            const int sh = (((R + 1) >> 1) + 3) & ~3;
-            const int s_lo = (wq >> 2) * sh, s_hi = min(R, s_lo + sh);
-            float *erow = Es + (size_t)((j & 1) * TC_M + (tid & (TC_M - 1))) * ES;
-            for (int s0 = s_lo; s0 < s_hi; s0 += 4) {
-                float v[16];
-                tc::tmem_ld16(lane_base + s0 * TC_MP, v);
+    } else {
+        // ================= main warps: features -> TMEM, MMA, epilogue
+        uint32_t phase = 0;
+        int nf = (int)min((int64_t)TC_M, fend - fbeg);
+        int xoff = stage_frames_async<D, TC_MAIN>(xs, X, N, fbeg, nf);
+        for (int j = 0; j < ntile; ++j) {
+            const int64_t cf0 = fbeg + (int64_t)j * TC_M;
+            cp_async_wait_all();
+            named_sync(TC_BAR_MAIN, TC_MAIN);                // frames of tile j staged; epilogue j-1 done with TMEM
+            // ---- A operand: thread = frame = TMEM lane
+            if (wq < 4) {
+                const int lf = tid < nf ? tid : nf - 1;      // frames past the end repeat the last one (discarded)
+                const float *row = xs + xoff + lf * D;
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const float4 cc = *reinterpret_cast<const float4 *>(pc + (s0 + q) * TC_MP);
-                    const float l0 = v[4 * q] + cc.x, l1 = v[4 * q + 1] + cc.y, l2 = v[4 * q + 2] + cc.z,
-                                l3 = v[4 * q + 3] + cc.w;
-                    const float m = fmaxf(fmaxf(l0, l1), fmaxf(l2, l3));
-                    float cost = CUDART_INF_F;
-                    if (m > -CUDART_INF_F) cost = -LN2_F * (m + lg2(ex2(l0 - m) + ex2(l1 - m) + ex2(l2 - m) + ex2(l3 - m)));
-                    if (s0 + q < s_hi) erow[s0 + q] = cost;
+                for (int k0 = 0; k0 < KP; k0 += 8) {
+                    uint32_t h[8], l[8];
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int d = (k0 >> 1) + q;
+                        const float v = d < D ? row[d] - shift_s[d] : 0.f;
+                        tc::split_tf32(v * v, h[2 * q], l[2 * q]);
+                        tc::split_tf32(v, h[2 * q + 1], l[2 * q + 1]);
+                    }
+                    tc::tmem_st8(lane_base + TC_COL_A + k0, h);
+                    tc::tmem_st8(lane_base + TC_COL_A + KP + k0, l);
+                }
+                tc::tmem_st_wait();
+            }
+            tc::fence_before_sync();
+            named_sync(TC_BAR_MAIN, TC_MAIN);
+            tc::fence_after_sync();
+            // ---- log2 densities of all Gaussians: D[128 x NP] = A_lo B_hi^T + A_hi B_lo^T + A_hi B_hi^T
+            if (tid == 0) {
+#pragma unroll
+                for (int kk = 0; kk < KP / 8; ++kk) {
+                    const uint64_t dbh = tc::smem_desc(bH + kk * 2 * NP * 16, NP * 16, 128);
+                    const uint64_t dbl = tc::smem_desc(bL + kk * 2 * NP * 16, NP * 16, 128);
+                    tc::mma_tf32_ts(tb, tb + TC_COL_A + KP + kk * 8, dbh, idesc, kk > 0);
+                    tc::mma_tf32_ts(tb, tb + TC_COL_A + kk * 8, dbl, idesc, true);
+                    tc::mma_tf32_ts(tb, tb + TC_COL_A + kk * 8, dbh, idesc, true);
+                }
+                tc::mma_commit(&bar);
+            }
+            // ---- while the tensor core runs: next tile's frames stream in
+            const int nf_next = (j + 1 < ntile) ? (int)min((int64_t)TC_M, fend - (cf0 + TC_M)) : 0;
+            int xoff_next = 0;
+            if (nf_next > 0) xoff_next = stage_frames_async<D, TC_MAIN>(xs, X, N, cf0 + TC_M, nf_next);
+            if (j >= 2) named_sync(TC_BAR_FREE + (j & 1), TC_NT);   // Viterbi of tile j-2 has left this ring slot
+            tc::mbar_wait(&bar, phase);
+            phase ^= 1;
+            tc::fence_after_sync();
+            // ---- epilogue: state cost = -ln sum_m 2^(D + c)   (warps 0-3: first half of the states, 4-7: second)
+            {
+                const int sh = (((R + 1) >> 1) + 3) & ~3;
+                const int s_lo = (wq >> 2) * sh, s_hi = min(R, s_lo + sh);
+                float *erow = Es + (size_t)((j & 1) * TC_M + (tid & (TC_M - 1))) * ES;
+                for (int s0 = s_lo; s0 < s_hi; s0 += 4) {
+                    float v[16];
+                    tc::tmem_ld16(lane_base + s0 * TC_MP, v);
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const float4 cc = *reinterpret_cast<const float4 *>(pc + (s0 + q) * TC_MP);
+                        const float l0 = v[4 * q] + cc.x, l1 = v[4 * q + 1] + cc.y, l2 = v[4 * q + 2] + cc.z,
+                                    l3 = v[4 * q + 3] + cc.w;
+                        const float m = fmaxf(fmaxf(l0, l1), fmaxf(l2, l3));
+                        float cost = CUDART_INF_F;
+                        if (m > -CUDART_INF_F)
+                            cost = -LN2_F * (m + lg2(ex2(l0 - m) + ex2(l1 - m) + ex2(l2 - m) + ex2(l3 - m)));
+                        if (s0 + q < s_hi) erow[s0 + q] = cost;
+                    }
                 }
             }
+            tc::fence_before_sync();
+            __threadfence_block();
+            named_arrive(TC_BAR_FULL + (j & 1), TC_NT);      // hand tile j's costs to the Viterbi warps
+            nf = nf_next;
+            xoff = xoff_next;
         }
-        tc::fence_before_sync();
-        nf = nf_next;
-        xoff = xoff_next;
-    }
-    __syncthreads();
-    if (ntile > 0) {   // the last one or two tiles
-        const int jl = (ntile - 1) & ~1;
-        const int64_t v0 = fbeg + (int64_t)jl * TC_M;
-        classify_dp_chunk<TC_NT>(Es, ES, off, ue, ufirst, v0, min(fend, v0 + (int64_t)TC_CHUNK), W, S, tr_s, carry, par,
-                                 banded, final_cost, label);
     }
     tc::fence_before_sync();
     __syncthreads();
