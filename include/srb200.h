@@ -79,16 +79,17 @@ int srb_classify(const float *X, const int32_t *utt_off, int32_t B, int64_t N, i
 /* Same classifier with the Gaussian contraction on the tcgen05 tensor cores (3xTF32 split, FP32 accumulation in
  * tensor memory; score_tc.cu).  The packed model is split once per model update:
  *   srb_tc_model_floats(R, Mp, D)   floats of the split operand, 0 when the model does not fit one MMA (R*Mp <= 256)
- *   srb_pack_model_tc(ab, ...)      ab (srb_pack_model) -> tcb[2][K/4][NP][4]: TF32 high and low halves, K-major
+ *   srb_pack_model_tc(ab, c, ...)   ab, c (srb_pack_model) -> tcb[2][K/4][NP][4]: TF32 high and low halves, K-major;
+ *                                   K = 2*D features + the constant 1 (coefficient c), padded to a multiple of 8
  *   srb_classify_tc_supported(...)  1 when srb_classify_tc covers the shape (D = 39, Mp = 4, shared memory fits)
- *   srb_classify_tc(...)            arguments and results as srb_classify, tcb in place of ab
+ *   srb_classify_tc(...)            arguments and results as srb_classify, tcb in place of ab and c
  * Costs agree with srb_classify within FP32 accumulation noise (~1e-6 relative); labels are equal wherever the two
  * best words differ by more than that. */
 int64_t srb_tc_model_floats(int R, int Mp, int D);
-int srb_pack_model_tc(const float *ab, int R, int Mp, int D, float *tcb, void *stream);
+int srb_pack_model_tc(const float *ab, const float *c, int R, int Mp, int D, float *tcb, void *stream);
 int srb_classify_tc_supported(int D, int W, int S, int Mp);
 int srb_classify_tc(const float *X, const int32_t *utt_off, int32_t B, int64_t N, int D, const float *tcb,
-                    const float *c, const float *shift, int W, int S, int Mp, const float *trans, float *final,
+                    const float *shift, int W, int S, int Mp, const float *trans, float *final,
                     int32_t *label, void *stream);
 
 

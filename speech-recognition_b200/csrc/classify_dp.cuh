@@ -4,7 +4,8 @@
 // The costs of the utterance that straddles the chunk end are carried in shared memory (carry[par] in, carry[par^1]
 // out).  Finished utterances write costs[-1,-1] per word (hmm.py:135) and, once all words are in, the arg-min label
 // (core.py:82-87: strict '<', first model wins).  Must be called by the NTH threads (tid = 0 .. NTH-1) that share
-// named barrier BAR_ID: the whole CTA with barrier 0 in score.cu, the four Viterbi warps in score_tc.cu.
+// named barrier BAR_ID (the whole CTA with barrier 0 in score.cu) or, with BAR_ID < 0 and NTH = 32, by one warp (each
+// Viterbi warp of score_tc.cu owns a sub-stream of utterances).
 #pragma once
 #include "common.cuh"
 
@@ -55,7 +56,10 @@ __device__ __forceinline__ void classify_dp_chunk(const float *Es, int ES, const
     while (ufirst + 1 < ue && (int64_t)off[ufirst + 1] <= cf0) ++ufirst;   // first utterance with frames >= cf0
     int ulast = ufirst;
     {
-        const int nb = lower_bound_i32(off + ufirst, ue - ufirst + 1, cf1);   // first u' with off >= cf1
+        // first u' with off >= cf1: utterances are not empty, so it is at most cf1 - cf0 + 1 entries ahead
+        const int nfull = ue - ufirst + 1, nnear = (int)min((int64_t)nfull, cf1 - cf0 + 2);
+        int nb = lower_bound_i32(off + ufirst, nnear, cf1);
+        if (nb == nnear && nnear < nfull) nb = lower_bound_i32(off + ufirst, nfull, cf1);   // empty utterances in between
         ulast = ufirst + nb - 1;
         if (ulast >= ue) ulast = ue - 1;
     }
@@ -126,7 +130,7 @@ __device__ __forceinline__ void classify_dp_chunk(const float *Es, int ES, const
             for (int r = 0; r < SMAX; ++r) carry[((par ^ 1) * W + w) * SMAX + r] = cost[r];
         }
     }
-    named_sync(BAR_ID, NTH);
+    if (BAR_ID < 0) __syncwarp(); else named_sync(BAR_ID, NTH);   // BAR_ID < 0: the callers are one warp
     if (label) {   // core.py:82-87: strict '<', first model wins
         for (int p = tid; p < npieces; p += NTH) {
             const int u = ufirst + p;

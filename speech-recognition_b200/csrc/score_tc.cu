@@ -26,17 +26,24 @@ constexpr int TC_MAIN = 256;           // threads of the scoring warps (features
 constexpr int TC_DP = 128;             // threads of the Viterbi warps
 constexpr int TC_NT = TC_MAIN + TC_DP; // threads per CTA
 constexpr int TC_CHUNK = 2 * TC_M;     // frames of the cost ring (two tiles)
+constexpr int TC_SUB = 4;              // sub-streams of utterances per CTA (one per Viterbi warp)
+constexpr int TC_SF = TC_M / TC_SUB;   // frames of one sub-stream in a tile
+constexpr int TC_XSQ = (TC_SF * 39 + 4 + 3) & ~3;   // staging floats per sub-stream (D = 39)
 constexpr int TC_BAR_MAIN = 1, TC_BAR_DP = 2, TC_BAR_FULL = 3, TC_BAR_FREE = 5;   // named barriers (FULL/FREE: +slot)
 constexpr int TC_NMAX = 256;           // Gaussian columns of one MMA
 constexpr int TC_COL_A = 256;          // TMEM column of the A operand (accumulators sit in [0, NP))
 constexpr int TC_MP = 4;               // Gaussians per state handled by the epilogue
+constexpr float TC_CMIN = -1e30f;      // stands in for log2(0) inside the MMA
 
 __host__ __device__ constexpr int tc_kp(int D) { return (2 * D + 7) & ~7; }
-static int tc_np(int R, int Mp) { return (R * Mp + 15) & ~15; }
+static int tc_np(int R, int Mp) { return (R * Mp + 31) & ~31; }   // two MMA halves of a multiple of 16 columns
 
 // Gaussian parameters -> TF32 (hi, lo) pair in the K-major chunk-plane layout of tc05.cuh: tcb[2][KP/4][NP][4].
-// Feature k = 2*d is x'^2 (coefficient A), k = 2*d + 1 is x' (coefficient B); rows past R*Mp and k >= 2*D are zero.
-__global__ void pack_tc_kernel(const float *__restrict__ ab, int R, int Mp, int D, int NP, int KP, uint32_t *__restrict__ tcb) {
+// Feature k = 2*d is x'^2 (coefficient A), k = 2*d + 1 is x' (coefficient B), k = 2*D is the constant 1 whose
+// coefficient is the Gaussian's log2 constant c (-inf of zero-weight padding is clamped to -1e30: 2^-1e30 == 0 all the
+// same, and 0 * c stays finite in the low-half product); rows past R*Mp and the remaining k are zero.
+__global__ void pack_tc_kernel(const float *__restrict__ ab, const float *__restrict__ c, int R, int Mp, int D, int NP,
+                               int KP, uint32_t *__restrict__ tcb) {
     const int total = KP * NP;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
         const int kc = i / (NP * 4), n = (i >> 2) % NP, k = kc * 4 + (i & 3);
@@ -44,6 +51,8 @@ __global__ void pack_tc_kernel(const float *__restrict__ ab, int R, int Mp, int 
         if (n < R * Mp && k < 2 * D) {
             const int r = n / Mp, m = n % Mp;
             v = ab[(((size_t)r * (Mp >> 2) + (m >> 2)) * D + (k >> 1)) * 8 + 2 * (m & 3) + (k & 1)];
+        } else if (n < R * Mp && k == 2 * D) {
+            v = fmaxf(c[n], TC_CMIN);
         }
         uint32_t h, l;
         tc::split_tf32(v, h, l);
@@ -55,23 +64,23 @@ __global__ void pack_tc_kernel(const float *__restrict__ ab, int R, int Mp, int 
 template <int D>
 __global__ void __launch_bounds__(TC_NT, 1)
 classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off, int B, int64_t N,
-                   const uint32_t *__restrict__ tcb, const float *__restrict__ c, const float *__restrict__ shift, int W,
+                   const uint32_t *__restrict__ tcb, const float *__restrict__ shift, int W,
                    int S, int NP, const float *__restrict__ trans, float *__restrict__ final_cost,
                    int32_t *__restrict__ label) {
     constexpr int KP = tc_kp(D), SMAX = SRB_DP_MAX_STATES;
     extern __shared__ __align__(128) float smem[];
-    __shared__ uint64_t bar;
+    __shared__ uint64_t bar[2];
+    __shared__ int sub_u[8];
     __shared__ uint32_t tslot;
     __shared__ int band_flag;
     const int R = W * S, ES = R | 1;
     float *shift_s = smem;                                   // 64
     float *tr_s = shift_s + 64;                              // W*SMAX*SMAX   tr_s[w][i][j] = cost j->i
-    float *carry = tr_s + W * SMAX * SMAX;                   // 2*W*SMAX
-    float *pc = carry + 2 * W * SMAX;                        // NP
-    uint32_t *Bh = reinterpret_cast<uint32_t *>(pc + NP);    // KP*NP, 16-byte aligned
+    float *carry = tr_s + W * SMAX * SMAX;                   // TC_SUB*2*W*SMAX
+    uint32_t *Bh = reinterpret_cast<uint32_t *>(carry + TC_SUB * 2 * W * SMAX);   // KP*NP, 16-byte aligned
     uint32_t *Bl = Bh + KP * NP;
-    float *xs = reinterpret_cast<float *>(Bl + KP * NP);     // TC_M*D + 4 (+ pad)
-    float *Es = xs + ((TC_M * D + 4 + 3) & ~3);              // TC_CHUNK * ES
+    float *xs = reinterpret_cast<float *>(Bl + KP * NP);     // TC_SUB * TC_XSQ
+    float *Es = xs + TC_SUB * TC_XSQ;                        // TC_CHUNK * ES
     const int tid = threadIdx.x, wq = tid >> 5;
 
     // utterance range of this CTA: boundaries at the first utterance starting at or after b*N/grid
@@ -82,7 +91,8 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
 
     if (wq == 0) tc::tmem_alloc<512>(&tslot);
     if (tid == 32) {
-        tc::mbar_init(&bar, 1);
+        tc::mbar_init(&bar[0], 1);
+        tc::mbar_init(&bar[1], 1);
         tc::mbar_fence_init();
     }
     if (tid == 0) band_flag = 1;
@@ -96,7 +106,6 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
         if (v < CUDART_INF_F && (o > r || r - o > 2)) band_flag = 0;   // benign race: all writers store 0
     }
     copy_to_smem(reinterpret_cast<float *>(Bh), reinterpret_cast<const float *>(tcb), (int64_t)2 * KP * NP);
-    for (int i = tid; i < NP; i += TC_NT) pc[i] = i < R * TC_MP ? c[i] : -CUDART_INF_F;
     tc::fence_async_smem();                                  // B was written through the generic proxy
     tc::fence_before_sync();
     __syncthreads();
@@ -104,49 +113,101 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
     const bool banded = band_flag != 0;
     const uint32_t tb = tslot;
     const uint32_t lane_base = tb + ((uint32_t)((wq & 3) * 32) << 16);
-    const uint32_t idesc = tc::idesc_tf32(TC_M, NP);
+    const int NH = NP >> 1;                                  // the MMA runs as two column halves (see the epilogue)
+    const uint32_t idesc = tc::idesc_tf32(TC_M, NH);
     const uint32_t bH = tc::smem_u32(Bh), bL = tc::smem_u32(Bl);
 
+    // The CTA's utterance range is cut into TC_SUB sub-streams of whole utterances (equal frame counts up to one
+    // utterance).  Tile j = frames [32j, 32j+32) of EVERY sub-stream (TMEM lanes 32q .. 32q+31 = sub-stream q), so a
+    // tile holds TC_SUB independent pieces of utterances and the Viterbi chains are 32 steps long, not 128.
     const int64_t fbeg = off[ub], fend = off[ue];
-    const int ntile = (int)((fend - fbeg + TC_M - 1) / TC_M);
+    if (tid <= TC_SUB) {
+        int u = ub;
+        if (tid == TC_SUB) u = ue;
+        else if (tid > 0) u = ub + lower_bound_i32(off + ub, ue - ub + 1, fbeg + (fend - fbeg) * tid / TC_SUB);
+        sub_u[tid] = u;
+    }
+    __syncthreads();
+    int ntile = 0;
+#pragma unroll
+    for (int q = 0; q < TC_SUB; ++q) ntile = max(ntile, (int)((off[sub_u[q + 1]] - off[sub_u[q]] + TC_SF - 1) / TC_SF));
 
     if (wq >= TC_MAIN / 32) {
-        // ================= Viterbi warps: tile j's recursions while the main warps produce tile j+1's costs
-        int ufirst = ub, par = 0;
+        // ================= Viterbi warps: warp q advances sub-stream q's recursions over tile j while the main warps
+        //                   produce tile j+1's costs
+        const int q = wq - TC_MAIN / 32, lane = tid & 31;
+        const int sue = sub_u[q + 1];
+        const int64_t sbeg = off[sub_u[q]], send = off[sue];
+        int ufirst = sub_u[q], par = 0;
+        float *carry_q = carry + (size_t)q * 2 * W * SMAX;
         for (int j = 0; j < ntile; ++j) {
-            const int64_t cf0 = fbeg + (int64_t)j * TC_M;
+            const int64_t cf0 = sbeg + (int64_t)j * TC_SF;
             named_sync(TC_BAR_FULL + (j & 1), TC_NT);        // costs of tile j are in ring slot j & 1
-            classify_dp_chunk<TC_DP, TC_BAR_DP>(Es + (size_t)(j & 1) * TC_M * ES, ES, off, ue, ufirst, cf0,
-                                                min(fend, cf0 + (int64_t)TC_M), W, S, tr_s, carry, par, banded,
-                                                final_cost, label, tid - TC_MAIN);
-            par ^= 1;
+            if (cf0 < send) {
+                classify_dp_chunk<32, -1>(Es + (size_t)((j & 1) * TC_M + q * TC_SF) * ES, ES, off, sue, ufirst, cf0,
+                                          min(send, cf0 + (int64_t)TC_SF), W, S, tr_s, carry_q, par, banded, final_cost,
+                                          label, lane);
+                par ^= 1;
+            }
             __threadfence_block();
             named_arrive(TC_BAR_FREE + (j & 1), TC_NT);      // slot may be overwritten (tile j + 2)
         }
     } else {
         // ================= main warps: features -> TMEM, MMA, epilogue
         uint32_t phase = 0;
-        int nf = (int)min((int64_t)TC_M, fend - fbeg);
-        int xoff = stage_frames_async<D, TC_MAIN>(xs, X, N, fbeg, nf);
+        const int sq = wq & (TC_SUB - 1);                    // sub-stream whose frames this warp turns into features
+        const int64_t my_beg = off[sub_u[sq]], my_end = off[sub_u[sq + 1]];
+        // staging: thread t copies vectors (t & 63) + 64k of sub-stream t >> 6.  A tile advances every sub-stream by
+        // 32 frames = 312 float4, so the 16-byte phase of a sub-stream's first row never changes.
+        const int stq = tid >> 6, sti = tid & 63;
+        const int64_t st_g0 = (int64_t)off[sub_u[stq]] * D, st_ga = st_g0 & ~(int64_t)3;
+        const int64_t st_end = (int64_t)off[sub_u[stq + 1]] * D, gend = N * D;
+        float *st_dst = xs + stq * TC_XSQ;
+        auto stage_tile = [&](int j) {
+            const int64_t base = st_ga + (int64_t)j * (TC_SF * D);
+            const int64_t lim = min(st_end, st_g0 + (int64_t)(j + 1) * (TC_SF * D));
+#pragma unroll
+            for (int k = 0; k < (TC_SF * D / 4 + 1 + 63) / 64; ++k) {
+                const int i = sti + 64 * k;
+                const int64_t g = base + 4 * (int64_t)i;
+                if (i <= TC_SF * D / 4 && g < lim) {
+                    if (g + 4 <= gend) {
+                        cp_async16(st_dst + 4 * i, X + g);
+                    } else {   // last vector of the whole array: do not read past X
+                        st_dst[4 * i + 0] = g + 0 < gend ? X[g + 0] : 0.f;
+                        st_dst[4 * i + 1] = g + 1 < gend ? X[g + 1] : 0.f;
+                        st_dst[4 * i + 2] = g + 2 < gend ? X[g + 2] : 0.f;
+                        st_dst[4 * i + 3] = 0.f;
+                    }
+                }
+            }
+        };
+        stage_tile(0);
         for (int j = 0; j < ntile; ++j) {
-            const int64_t cf0 = fbeg + (int64_t)j * TC_M;
             cp_async_wait_all();
             named_sync(TC_BAR_MAIN, TC_MAIN);                // frames of tile j staged; epilogue j-1 done with TMEM
             // ---- A operand: thread = frame = TMEM lane
             if (wq < 4) {
-                const int lf = tid < nf ? tid : nf - 1;      // frames past the end repeat the last one (discarded)
-                const float *row = xs + xoff + lf * D;
+                const int64_t f0 = my_beg + (int64_t)j * TC_SF;
+                const int nf = (int)max((int64_t)0, min((int64_t)TC_SF, my_end - f0));
+                const int lf = (tid & 31) < nf ? (tid & 31) : max(nf - 1, 0);   // lanes past the end repeat (discarded)
+                const float *row = xs + sq * TC_XSQ + (int)((f0 * D) & 3) + lf * D;
 #pragma unroll
                 for (int k0 = 0; k0 < KP; k0 += 8) {
                     uint32_t h[8], l[8];
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
                         const int d = (k0 >> 1) + q;
-                        const float v = d < D ? row[d] - shift_s[d] : 0.f;
-                        tc::split_tf32(v * v, h[2 * q], l[2 * q]);
-                        tc::split_tf32(v, h[2 * q + 1], l[2 * q + 1]);
+                        if (d < D) {
+                            const float v = nf > 0 ? row[d] - shift_s[d] : 0.f;
+                            tc::split_tf32(v * v, h[2 * q], l[2 * q]);
+                            tc::split_tf32(v, h[2 * q + 1], l[2 * q + 1]);
+                        } else {                             // k = 2*D: the constant feature, then zero padding
+                            h[2 * q] = d == D ? 0x3f800000u : 0u;
+                            h[2 * q + 1] = l[2 * q] = l[2 * q + 1] = 0u;
+                        }
                     }
-                    tc::tmem_st8(lane_base + TC_COL_A + k0, h);
+                tc::tmem_st8(lane_base + TC_COL_A + k0, h);
                     tc::tmem_st8(lane_base + TC_COL_A + KP + k0, l);
                 }
                 tc::tmem_st_wait();
@@ -156,27 +217,28 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
             tc::fence_after_sync();
             // ---- log2 densities of all Gaussians: D[128 x NP] = A_lo B_hi^T + A_hi B_lo^T + A_hi B_hi^T
             if (tid == 0) {
+#pragma unroll 1
+                for (int hf = 0; hf < 2; ++hf) {             // column half hf -> accumulators [hf*NH, hf*NH + NH), bar[hf]
 #pragma unroll
-                for (int kk = 0; kk < KP / 8; ++kk) {
-                    const uint64_t dbh = tc::smem_desc(bH + kk * 2 * NP * 16, NP * 16, 128);
-                    const uint64_t dbl = tc::smem_desc(bL + kk * 2 * NP * 16, NP * 16, 128);
-                    tc::mma_tf32_ts(tb, tb + TC_COL_A + KP + kk * 8, dbh, idesc, kk > 0);
-                    tc::mma_tf32_ts(tb, tb + TC_COL_A + kk * 8, dbl, idesc, true);
-                    tc::mma_tf32_ts(tb, tb + TC_COL_A + kk * 8, dbh, idesc, true);
+                    for (int kk = 0; kk < KP / 8; ++kk) {
+                        const uint64_t dbh = tc::smem_desc(bH + kk * 2 * NP * 16 + hf * NH * 16, NP * 16, 128);
+                        const uint64_t dbl = tc::smem_desc(bL + kk * 2 * NP * 16 + hf * NH * 16, NP * 16, 128);
+                        tc::mma_tf32_ts(tb + hf * NH, tb + TC_COL_A + KP + kk * 8, dbh, idesc, kk > 0);
+                        tc::mma_tf32_ts(tb + hf * NH, tb + TC_COL_A + kk * 8, dbl, idesc, true);
+                        tc::mma_tf32_ts(tb + hf * NH, tb + TC_COL_A + kk * 8, dbh, idesc, true);
+                    }
+                    tc::mma_commit(&bar[hf]);
                 }
-                tc::mma_commit(&bar);
             }
             // ---- while the tensor core runs: next tile's frames stream in
-            const int nf_next = (j + 1 < ntile) ? (int)min((int64_t)TC_M, fend - (cf0 + TC_M)) : 0;
-            int xoff_next = 0;
-            if (nf_next > 0) xoff_next = stage_frames_async<D, TC_MAIN>(xs, X, N, cf0 + TC_M, nf_next);
+            if (j + 1 < ntile) stage_tile(j + 1);
             if (j >= 2) named_sync(TC_BAR_FREE + (j & 1), TC_NT);   // Viterbi of tile j-2 has left this ring slot
-            tc::mbar_wait(&bar, phase);
+            tc::mbar_wait(&bar[wq >> 2], phase);         // warps 0-3 start on the first half while the second runs
             phase ^= 1;
             tc::fence_after_sync();
             // ---- epilogue: state cost = -ln sum_m 2^(D + c)   (warps 0-3: first half of the states, 4-7: second)
             {
-                const int sh = (((R + 1) >> 1) + 3) & ~3;
+                const int sh = NH / TC_MP;
                 const int s_lo = (wq >> 2) * sh, s_hi = min(R, s_lo + sh);
                 float *erow = Es + (size_t)((j & 1) * TC_M + (tid & (TC_M - 1))) * ES;
                 for (int s0 = s_lo; s0 < s_hi; s0 += 4) {
@@ -184,12 +246,10 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
                     tc::tmem_ld16(lane_base + s0 * TC_MP, v);
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
-                        const float4 cc = *reinterpret_cast<const float4 *>(pc + (s0 + q) * TC_MP);
-                        const float l0 = v[4 * q] + cc.x, l1 = v[4 * q + 1] + cc.y, l2 = v[4 * q + 2] + cc.z,
-                                    l3 = v[4 * q + 3] + cc.w;
+                        const float l0 = v[4 * q], l1 = v[4 * q + 1], l2 = v[4 * q + 2], l3 = v[4 * q + 3];
                         const float m = fmaxf(fmaxf(l0, l1), fmaxf(l2, l3));
-                        float cost = CUDART_INF_F;
-                        if (m > -CUDART_INF_F)
+                        float cost = CUDART_INF_F;           // every Gaussian of the state has zero weight
+                        if (m > 0.5f * TC_CMIN)
                             cost = -LN2_F * (m + lg2(ex2(l0 - m) + ex2(l1 - m) + ex2(l2 - m) + ex2(l3 - m)));
                         if (s0 + q < s_hi) erow[s0 + q] = cost;
                     }
@@ -198,8 +258,6 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
             tc::fence_before_sync();
             __threadfence_block();
             named_arrive(TC_BAR_FULL + (j & 1), TC_NT);      // hand tile j's costs to the Viterbi warps
-            nf = nf_next;
-            xoff = xoff_next;
         }
     }
     tc::fence_before_sync();
@@ -209,8 +267,8 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
 
 static size_t classify_tc_smem_bytes(int W, int S, int NP, int D) {
     const int R = W * S, KP = tc_kp(D);
-    return 4 * (64 + (size_t)W * SRB_DP_MAX_STATES * SRB_DP_MAX_STATES + 2 * (size_t)W * SRB_DP_MAX_STATES + NP +
-                2 * (size_t)KP * NP + (((size_t)TC_M * D + 4 + 3) & ~(size_t)3) + (size_t)TC_CHUNK * (R | 1));
+    return 4 * (64 + (size_t)W * SRB_DP_MAX_STATES * SRB_DP_MAX_STATES + TC_SUB * 2 * (size_t)W * SRB_DP_MAX_STATES +
+                2 * (size_t)KP * NP + (size_t)TC_SUB * TC_XSQ + (size_t)TC_CHUNK * (R | 1));
 }
 
 }  // namespace srb
@@ -224,13 +282,13 @@ int64_t srb_tc_model_floats(int R, int Mp, int D) {
     return 2 * (int64_t)tc_kp(D) * tc_np(R, Mp);
 }
 
-int srb_pack_model_tc(const float *ab, int R, int Mp, int D, float *tcb, void *stream) {
-    SRB_REQUIRE(ab && tcb, SRB_EINVAL, "srb_pack_model_tc: null pointer");
+int srb_pack_model_tc(const float *ab, const float *c, int R, int Mp, int D, float *tcb, void *stream) {
+    SRB_REQUIRE(ab && c && tcb, SRB_EINVAL, "srb_pack_model_tc: null pointer");
     SRB_REQUIRE(srb_tc_model_floats(R, Mp, D) > 0, SRB_EUNSUPPORTED,
                 "srb_pack_model_tc: %d states x %d Gaussians exceed %d tensor-core columns", R, Mp, TC_NMAX);
     SRB_REQUIRE(((uintptr_t)tcb & 15) == 0, SRB_EINVAL, "srb_pack_model_tc: tcb must be 16-byte aligned");
     const int NP = tc_np(R, Mp), KP = tc_kp(D);
-    pack_tc_kernel<<<(KP * NP + 255) / 256, 256, 0, (cudaStream_t)stream>>>(ab, R, Mp, D, NP, KP,
+    pack_tc_kernel<<<(KP * NP + 255) / 256, 256, 0, (cudaStream_t)stream>>>(ab, c, R, Mp, D, NP, KP,
                                                                               reinterpret_cast<uint32_t *>(tcb));
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
@@ -244,17 +302,17 @@ int srb_classify_tc_supported(int D, int W, int S, int Mp) {
     return cap > 0 && classify_tc_smem_bytes(W, S, NP, D) + 64 <= (size_t)cap;
 }
 
-int srb_classify_tc(const float *X, const int32_t *utt_off, int32_t B, int64_t N, int D, const float *tcb, const float *c,
+int srb_classify_tc(const float *X, const int32_t *utt_off, int32_t B, int64_t N, int D, const float *tcb,
                     const float *shift, int W, int S, int Mp, const float *trans, float *final_cost, int32_t *label,
                     void *stream) {
-    SRB_REQUIRE(((X && final_cost) || B == 0 || N == 0) && utt_off && tcb && c && shift && trans, SRB_EINVAL,
+    SRB_REQUIRE(((X && final_cost) || B == 0 || N == 0) && utt_off && tcb && shift && trans, SRB_EINVAL,
                 "srb_classify_tc: null pointer");
     SRB_REQUIRE(B >= 0 && N >= 0, SRB_EINVAL, "srb_classify_tc: bad sizes");
     SRB_REQUIRE(srb_classify_tc_supported(D, W, S, Mp), SRB_EUNSUPPORTED,
                 "srb_classify_tc: D=%d, %d words x %d states x %d Gaussians not covered by the tensor-core classifier "
                 "(D = 39, Mp = 4, at most %d Gaussians); use srb_classify", D, W, S, Mp, TC_NMAX);
-    SRB_REQUIRE(((uintptr_t)X & 15) == 0 && ((uintptr_t)tcb & 15) == 0 && ((uintptr_t)c & 15) == 0, SRB_EINVAL,
-                "srb_classify_tc: X, tcb, c must be 16-byte aligned");
+    SRB_REQUIRE(((uintptr_t)X & 15) == 0 && ((uintptr_t)tcb & 15) == 0, SRB_EINVAL,
+                "srb_classify_tc: X and tcb must be 16-byte aligned");
     if (B == 0 || N == 0) return SRB_OK;
     const int sms = sm_count();
     SRB_REQUIRE(sms > 0, SRB_ENODEVICE, "no CUDA device");
@@ -264,7 +322,7 @@ int srb_classify_tc(const float *X, const int32_t *utt_off, int32_t B, int64_t N
     const int grid = (int)(want < sms ? want : sms);
     SRB_CUDA(cudaFuncSetAttribute(classify_tc_kernel<39>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     classify_tc_kernel<39><<<grid, TC_NT, bytes, (cudaStream_t)stream>>>(
-        X, utt_off, B, N, reinterpret_cast<const uint32_t *>(tcb), c, shift, W, S, NP, trans, final_cost, label);
+        X, utt_off, B, N, reinterpret_cast<const uint32_t *>(tcb), shift, W, S, NP, trans, final_cost, label);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }

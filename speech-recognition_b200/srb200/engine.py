@@ -52,7 +52,7 @@ class PackedModel:
                                           self.R, self.M, self.D, _l.ptr(self.ab), _l.ptr(self.c),
                                           _l.ptr(self.shift), _l.stream_ptr()))
         if self.tcb is not None:
-            _l.check(_l.load().srb_pack_model_tc(_l.ptr(self.ab), self.R, self.Mp, self.D, _l.ptr(self.tcb),
+            _l.check(_l.load().srb_pack_model_tc(_l.ptr(self.ab), _l.ptr(self.c), self.R, self.Mp, self.D, _l.ptr(self.tcb),
                                                  _l.stream_ptr()))
         return self
 
@@ -121,7 +121,7 @@ def classify(X, off, pm, trans, W, S, final=None, label=None, tensor=None):
     if tensor is None:
         tensor = pm.tensor_core_ok(W, S)
     if tensor:
-        _l.check(_l.load().srb_classify_tc(_l.ptr(X), _l.ptr(off), B, X.shape[0], pm.D, _l.ptr(pm.tcb), _l.ptr(pm.c),
+        _l.check(_l.load().srb_classify_tc(_l.ptr(X), _l.ptr(off), B, X.shape[0], pm.D, _l.ptr(pm.tcb),
                                            _l.ptr(pm.shift), W, S, pm.Mp, _l.ptr(trans), _l.ptr(final),
                                            _l.ptr(label), _l.stream_ptr()))
     else:
@@ -186,10 +186,14 @@ class HostClassifier:
                 st.wait_event(start)
                 self.xbuf[s][:f1 - f0].copy_(Xt[f0:f1], non_blocking=True)
                 self.obuf[s][:nb + 1].copy_(self.off_pin[s][:nb + 1], non_blocking=True)
-                tensor = self.pm.tensor_core_ok(self.W, self.S)
-                fn, par = (L.srb_classify_tc, self.pm.tcb) if tensor else (L.srb_classify, self.pm.ab)
+                if self.pm.tensor_core_ok(self.W, self.S):
+                    par = (_l.ptr(self.pm.tcb),)
+                    fn = L.srb_classify_tc
+                else:
+                    par = (_l.ptr(self.pm.ab), _l.ptr(self.pm.c))
+                    fn = L.srb_classify
                 _l.check(fn(self.xbuf[s].data_ptr(), self.obuf[s].data_ptr(), nb, f1 - f0, self.pm.D,
-                            _l.ptr(par), _l.ptr(self.pm.c), _l.ptr(self.pm.shift), self.W, self.S,
+                            *par, _l.ptr(self.pm.shift), self.W, self.S,
                             self.pm.Mp, _l.ptr(self.trans), self.final[s].data_ptr(),
                             self.label[s].data_ptr(), st.cuda_stream))
                 labels_out[u0:u1].copy_(self.label[s][:nb], non_blocking=True)
