@@ -3,7 +3,8 @@
 // frames whose state costs E[frame - cf0][w*S + s] sit in shared memory; thread = (piece, word), states in registers.
 // The costs of the utterance that straddles the chunk end are carried in shared memory (carry[par] in, carry[par^1]
 // out).  Finished utterances write costs[-1,-1] per word (hmm.py:135) and, once all words are in, the arg-min label
-// (core.py:82-87: strict '<', first model wins).  Must be called by the NTH threads (tid = 0 .. NTH-1) that share
+// (core.py:82-87: strict '<', first model wins; fin_s, optional, is shared scratch of fin_cap x W floats that saves the
+// round trip through L2 for the first fin_cap utterances of the chunk).  Must be called by the NTH threads (tid = 0 .. NTH-1) that share
 // named barrier BAR_ID (the whole CTA with barrier 0 in score.cu) or, with BAR_ID < 0 and NTH = 32, by one warp (each
 // Viterbi warp of score_tc.cu owns a sub-stream of utterances).
 #pragma once
@@ -51,7 +52,7 @@ __device__ __forceinline__ void classify_dp_chunk(const float *Es, int ES, const
                                                   int &ufirst, int64_t cf0, int64_t cf1, int W, int S,
                                                   const float *tr_s, float *carry, int par, bool banded,
                                                   float *__restrict__ final_cost, int32_t *__restrict__ label,
-                                                  int tid) {
+                                                  int tid, float *fin_s = nullptr, int fin_cap = 0) {
     constexpr int SMAX = SRB_DP_MAX_STATES;
     while (ufirst + 1 < ue && (int64_t)off[ufirst + 1] <= cf0) ++ufirst;   // first utterance with frames >= cf0
     int ulast = ufirst;
@@ -125,6 +126,7 @@ __device__ __forceinline__ void classify_dp_chunk(const float *Es, int ES, const
             for (int r = 0; r < SMAX; ++r)
                 if (r == S - 1) fc = cost[r];
             final_cost[(size_t)u * W + w] = fc;           // hmm.py:135 costs[-1,-1]
+            if (p < fin_cap) fin_s[p * W + w] = fc;       // shared copy for the arg-min below
         } else {
 #pragma unroll
             for (int r = 0; r < SMAX; ++r) carry[((par ^ 1) * W + w) * SMAX + r] = cost[r];
@@ -139,7 +141,7 @@ __device__ __forceinline__ void classify_dp_chunk(const float *Es, int ES, const
                 float bcst = CUDART_INF_F;
                 int bl = 0;
                 for (int w = 0; w < W; ++w) {
-                    const float v = __ldcg(final_cost + (size_t)u * W + w);
+                    const float v = p < fin_cap ? fin_s[p * W + w] : __ldcg(final_cost + (size_t)u * W + w);
                     if (v < bcst) {
                         bcst = v;
                         bl = w;

@@ -24,12 +24,14 @@ namespace srb {
 constexpr int TC_M = 128;              // frames per MMA tile (TMEM lanes)
 constexpr int TC_MAIN = 256;           // threads of the scoring warps (features, MMA issue, epilogue)
 constexpr int TC_DP = 128;             // threads of the Viterbi warps
-constexpr int TC_NT = TC_MAIN + TC_DP; // threads per CTA
+constexpr int TC_MMA_WARP = (TC_MAIN + TC_DP) / 32;   // the warp whose lane 0 issues the MMAs
+constexpr int TC_NT = TC_MAIN + TC_DP + 32;   // threads per CTA
 constexpr int TC_CHUNK = 2 * TC_M;     // frames of the cost ring (two tiles)
 constexpr int TC_SUB = 4;              // sub-streams of utterances per CTA (one per Viterbi warp)
 constexpr int TC_SF = TC_M / TC_SUB;   // frames of one sub-stream in a tile
 constexpr int TC_XSQ = (TC_SF * 39 + 4 + 3) & ~3;   // staging floats per sub-stream (D = 39)
-constexpr int TC_BAR_MAIN = 1, TC_BAR_DP = 2, TC_BAR_FULL = 3, TC_BAR_FREE = 5;   // named barriers (FULL/FREE: +slot)
+constexpr int TC_FIN = 16;             // utterance ends per sub-stream and tile whose final costs stay in shared memory
+constexpr int TC_BAR_FULL = 1, TC_BAR_FREE_A = 3, TC_BAR_FREE_B = 5;   // named barriers (+ ring slot)
 constexpr int TC_NMAX = 256;           // Gaussian columns of one MMA
 constexpr int TC_COL_A = 256;          // TMEM column of the A operand (accumulators sit in [0, NP))
 constexpr int TC_MP = 4;               // Gaussians per state handled by the epilogue
@@ -69,7 +71,7 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
                    int32_t *__restrict__ label) {
     constexpr int KP = tc_kp(D), SMAX = SRB_DP_MAX_STATES;
     extern __shared__ __align__(128) float smem[];
-    __shared__ uint64_t bar[2];
+    __shared__ uint64_t bar[5];
     __shared__ int sub_u[8];
     __shared__ uint32_t tslot;
     __shared__ int band_flag;
@@ -80,7 +82,8 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
     uint32_t *Bh = reinterpret_cast<uint32_t *>(carry + TC_SUB * 2 * W * SMAX);   // KP*NP, 16-byte aligned
     uint32_t *Bl = Bh + KP * NP;
     float *xs = reinterpret_cast<float *>(Bl + KP * NP);     // TC_SUB * TC_XSQ
-    float *Es = xs + TC_SUB * TC_XSQ;                        // TC_CHUNK * ES
+    float *fin_s = xs + TC_SUB * TC_XSQ;                     // TC_SUB * TC_FIN * W
+    float *Es = fin_s + TC_SUB * TC_FIN * W;                 // TC_CHUNK * ES
     const int tid = threadIdx.x, wq = tid >> 5;
 
     // utterance range of this CTA: boundaries at the first utterance starting at or after b*N/grid
@@ -91,8 +94,11 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
 
     if (wq == 0) tc::tmem_alloc<512>(&tslot);
     if (tid == 32) {
-        tc::mbar_init(&bar[0], 1);
-        tc::mbar_init(&bar[1], 1);
+        tc::mbar_init(&bar[0], TC_M);                        // XR: group B's threads
+        tc::mbar_init(&bar[1], TC_M);                        // AR: group A's threads
+        tc::mbar_init(&bar[2], 1);                           // H0, H1: tcgen05.commit
+        tc::mbar_init(&bar[3], 1);
+        tc::mbar_init(&bar[4], TC_M);                        // D1F: group B's threads
         tc::mbar_fence_init();
     }
     if (tid == 0) band_flag = 1;
@@ -132,8 +138,38 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
 #pragma unroll
     for (int q = 0; q < TC_SUB; ++q) ntile = max(ntile, (int)((off[sub_u[q + 1]] - off[sub_u[q]] + TC_SF - 1) / TC_SF));
 
-    if (wq >= TC_MAIN / 32) {
-        // ================= Viterbi warps: warp q advances sub-stream q's recursions over tile j while the main warps
+    // mbarriers, one completion per tile each (parity of tile j = j & 1):
+    //   XR  frames of the tile staged (group B -> A)          AR  A operand in TMEM, staging buffer consumed (A -> MMA, B)
+    //   H0 / H1  column half 0 / 1 accumulated (MMA -> A, B; H1 also frees the A operand)
+    //   D1F accumulator half 1 read back (B -> MMA)
+    uint64_t *XR = &bar[0], *AR = &bar[1], *H0 = &bar[2], *H1 = &bar[3], *D1F = &bar[4];
+
+    if (wq == TC_MMA_WARP) {
+        // ================= MMA issuer: one thread
+        if ((tid & 31) == 0) {
+            for (int j = 0; j < ntile; ++j) {
+                tc::mbar_wait(AR, j & 1);
+                tc::fence_after_sync();
+#pragma unroll 1
+                for (int hf = 0; hf < 2; ++hf) {             // column half hf -> accumulators [hf*NH, hf*NH + NH)
+                    if (hf == 1 && j > 0) {
+                        tc::mbar_wait(D1F, (j - 1) & 1);     // tile j-1's second half has been read back
+                        tc::fence_after_sync();
+                    }
+#pragma unroll
+                    for (int kk = 0; kk < KP / 8; ++kk) {
+                        const uint64_t dbh = tc::smem_desc(bH + kk * 2 * NP * 16 + hf * NH * 16, NP * 16, 128);
+                        const uint64_t dbl = tc::smem_desc(bL + kk * 2 * NP * 16 + hf * NH * 16, NP * 16, 128);
+                        tc::mma_tf32_ts(tb + hf * NH, tb + TC_COL_A + KP + kk * 8, dbh, idesc, kk > 0);
+                        tc::mma_tf32_ts(tb + hf * NH, tb + TC_COL_A + kk * 8, dbl, idesc, true);
+                        tc::mma_tf32_ts(tb + hf * NH, tb + TC_COL_A + kk * 8, dbh, idesc, true);
+                    }
+                    tc::mma_commit(hf ? H1 : H0);
+                }
+            }
+        }
+    } else if (wq >= TC_MAIN / 32) {
+        // ================= Viterbi warps: warp q advances sub-stream q's recursions over tile j while the scoring warps
         //                   produce tile j+1's costs
         const int q = wq - TC_MAIN / 32, lane = tid & 31;
         const int sue = sub_u[q + 1];
@@ -142,33 +178,34 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
         float *carry_q = carry + (size_t)q * 2 * W * SMAX;
         for (int j = 0; j < ntile; ++j) {
             const int64_t cf0 = sbeg + (int64_t)j * TC_SF;
-            named_sync(TC_BAR_FULL + (j & 1), TC_NT);        // costs of tile j are in ring slot j & 1
+            named_sync(TC_BAR_FULL + (j & 1), TC_MAIN + TC_DP);   // costs of tile j are in ring slot j & 1
             if (cf0 < send) {
                 classify_dp_chunk<32, -1>(Es + (size_t)((j & 1) * TC_M + q * TC_SF) * ES, ES, off, sue, ufirst, cf0,
                                           min(send, cf0 + (int64_t)TC_SF), W, S, tr_s, carry_q, par, banded, final_cost,
-                                          label, lane);
+                                          label, lane, fin_s + (size_t)q * TC_FIN * W, TC_FIN);
                 par ^= 1;
             }
             __threadfence_block();
-            named_arrive(TC_BAR_FREE + (j & 1), TC_NT);      // slot may be overwritten (tile j + 2)
+            named_arrive(TC_BAR_FREE_A + (j & 1), TC_M + TC_DP);  // slot may be overwritten (tile j + 2), told to
+            named_arrive(TC_BAR_FREE_B + (j & 1), TC_M + TC_DP);  // both scoring groups
         }
     } else {
-        // ================= main warps: features -> TMEM, MMA, epilogue
-        uint32_t phase = 0;
-        const int sq = wq & (TC_SUB - 1);                    // sub-stream whose frames this warp turns into features
+        // ================= scoring warps.  Group A (warps 0-3): features of tile j -> TMEM, epilogue of column half 0.
+        //                   Group B (warps 4-7): staging of tile j+1, epilogue of column half 1.
+        const bool grpA = wq < 4;
+        const int sq = wq & (TC_SUB - 1);                    // sub-stream whose frames warp sq of group A turns into features
         const int64_t my_beg = off[sub_u[sq]], my_end = off[sub_u[sq + 1]];
-        // staging: thread t copies vectors (t & 63) + 64k of sub-stream t >> 6.  A tile advances every sub-stream by
-        // 32 frames = 312 float4, so the 16-byte phase of a sub-stream's first row never changes.
-        const int stq = tid >> 6, sti = tid & 63;
-        const int64_t st_g0 = (int64_t)off[sub_u[stq]] * D, st_ga = st_g0 & ~(int64_t)3;
-        const int64_t st_end = (int64_t)off[sub_u[stq + 1]] * D, gend = N * D;
-        float *st_dst = xs + stq * TC_XSQ;
+        // staging (group B): thread t copies vectors (t & 31) + 32k of sub-stream t >> 5.  A tile advances every
+        // sub-stream by 32 frames = 312 float4, so the 16-byte phase of a sub-stream's first row never changes.
+        const int sti = tid & 31;
+        const int64_t st_g0 = my_beg * D, st_ga = st_g0 & ~(int64_t)3, st_end = my_end * D, gend = N * D;
+        float *st_dst = xs + sq * TC_XSQ;
         auto stage_tile = [&](int j) {
             const int64_t base = st_ga + (int64_t)j * (TC_SF * D);
             const int64_t lim = min(st_end, st_g0 + (int64_t)(j + 1) * (TC_SF * D));
 #pragma unroll
-            for (int k = 0; k < (TC_SF * D / 4 + 1 + 63) / 64; ++k) {
-                const int i = sti + 64 * k;
+            for (int k = 0; k < (TC_SF * D / 4 + 1 + 31) / 32; ++k) {
+                const int i = sti + 32 * k;
                 const int64_t g = base + 4 * (int64_t)i;
                 if (i <= TC_SF * D / 4 && g < lim) {
                     if (g + 4 <= gend) {
@@ -181,13 +218,18 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
                     }
                 }
             }
-        };
-        stage_tile(0);
-        for (int j = 0; j < ntile; ++j) {
             cp_async_wait_all();
-            named_sync(TC_BAR_MAIN, TC_MAIN);                // frames of tile j staged; epilogue j-1 done with TMEM
-            // ---- A operand: thread = frame = TMEM lane
-            if (wq < 4) {
+            tc::mbar_arrive(XR);
+        };
+        if (!grpA) stage_tile(0);
+        for (int j = 0; j < ntile; ++j) {
+            if (grpA) {
+                // ---- A operand: thread = frame = TMEM lane
+                tc::mbar_wait(XR, j & 1);                    // frames of tile j are staged
+                if (j > 0) {
+                    tc::mbar_wait(H1, (j - 1) & 1);          // every MMA of tile j-1 is done with the A operand
+                    tc::fence_after_sync();
+                }
                 const int64_t f0 = my_beg + (int64_t)j * TC_SF;
                 const int nf = (int)max((int64_t)0, min((int64_t)TC_SF, my_end - f0));
                 const int lf = (tid & 31) < nf ? (tid & 31) : max(nf - 1, 0);   // lanes past the end repeat (discarded)
@@ -207,36 +249,20 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
                             h[2 * q + 1] = l[2 * q] = l[2 * q + 1] = 0u;
                         }
                     }
-                tc::tmem_st8(lane_base + TC_COL_A + k0, h);
+                    tc::tmem_st8(lane_base + TC_COL_A + k0, h);
                     tc::tmem_st8(lane_base + TC_COL_A + KP + k0, l);
                 }
                 tc::tmem_st_wait();
+                tc::fence_before_sync();
+                tc::mbar_arrive(AR);
+            } else {
+                tc::mbar_wait(AR, j & 1);                    // staging buffer consumed
+                if (j + 1 < ntile) stage_tile(j + 1);
             }
-            tc::fence_before_sync();
-            named_sync(TC_BAR_MAIN, TC_MAIN);
+            // ---- epilogue of this group's column half: state cost = -ln sum_m 2^D  (constants are inside D)
+            tc::mbar_wait(grpA ? H0 : H1, j & 1);
             tc::fence_after_sync();
-            // ---- log2 densities of all Gaussians: D[128 x NP] = A_lo B_hi^T + A_hi B_lo^T + A_hi B_hi^T
-            if (tid == 0) {
-#pragma unroll 1
-                for (int hf = 0; hf < 2; ++hf) {             // column half hf -> accumulators [hf*NH, hf*NH + NH), bar[hf]
-#pragma unroll
-                    for (int kk = 0; kk < KP / 8; ++kk) {
-                        const uint64_t dbh = tc::smem_desc(bH + kk * 2 * NP * 16 + hf * NH * 16, NP * 16, 128);
-                        const uint64_t dbl = tc::smem_desc(bL + kk * 2 * NP * 16 + hf * NH * 16, NP * 16, 128);
-                        tc::mma_tf32_ts(tb + hf * NH, tb + TC_COL_A + KP + kk * 8, dbh, idesc, kk > 0);
-                        tc::mma_tf32_ts(tb + hf * NH, tb + TC_COL_A + kk * 8, dbl, idesc, true);
-                        tc::mma_tf32_ts(tb + hf * NH, tb + TC_COL_A + kk * 8, dbh, idesc, true);
-                    }
-                    tc::mma_commit(&bar[hf]);
-                }
-            }
-            // ---- while the tensor core runs: next tile's frames stream in
-            if (j + 1 < ntile) stage_tile(j + 1);
-            if (j >= 2) named_sync(TC_BAR_FREE + (j & 1), TC_NT);   // Viterbi of tile j-2 has left this ring slot
-            tc::mbar_wait(&bar[wq >> 2], phase);         // warps 0-3 start on the first half while the second runs
-            phase ^= 1;
-            tc::fence_after_sync();
-            // ---- epilogue: state cost = -ln sum_m 2^(D + c)   (warps 0-3: first half of the states, 4-7: second)
+            if (j >= 2) named_sync((grpA ? TC_BAR_FREE_A : TC_BAR_FREE_B) + (j & 1), TC_M + TC_DP);   // ring slot free
             {
                 const int sh = NH / TC_MP;
                 const int s_lo = (wq >> 2) * sh, s_hi = min(R, s_lo + sh);
@@ -256,8 +282,9 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
                 }
             }
             tc::fence_before_sync();
+            if (!grpA) tc::mbar_arrive(D1F);                 // accumulator half 1 may be overwritten
             __threadfence_block();
-            named_arrive(TC_BAR_FULL + (j & 1), TC_NT);      // hand tile j's costs to the Viterbi warps
+            named_arrive(TC_BAR_FULL + (j & 1), TC_MAIN + TC_DP);   // hand this half of tile j's costs to the Viterbi warps
         }
     }
     tc::fence_before_sync();
@@ -268,7 +295,7 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
 static size_t classify_tc_smem_bytes(int W, int S, int NP, int D) {
     const int R = W * S, KP = tc_kp(D);
     return 4 * (64 + (size_t)W * SRB_DP_MAX_STATES * SRB_DP_MAX_STATES + TC_SUB * 2 * (size_t)W * SRB_DP_MAX_STATES +
-                2 * (size_t)KP * NP + (size_t)TC_SUB * TC_XSQ + (size_t)TC_CHUNK * (R | 1));
+                2 * (size_t)KP * NP + (size_t)TC_SUB * TC_XSQ + (size_t)TC_SUB * TC_FIN * W + (size_t)TC_CHUNK * (R | 1));
 }
 
 }  // namespace srb
