@@ -63,6 +63,26 @@ __global__ void pack_tc_kernel(const float *__restrict__ ab, const float *__rest
     }
 }
 
+// state costs of 4 states (16 accumulator columns = log2 weighted densities incl. constants) -> erow[s0 .. s0+3]:
+// cost = -ln sum_m 2^l_m (hmm_state.py:114-120 in the log domain), straight-line so that the four chains interleave.
+__device__ __forceinline__ void tc_state_costs(const uint32_t (&r)[16], float *erow, int s0, int s_hi) {
+    float m[4], sum[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+        m[q] = fmaxf(fmaxf(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1])),
+                     fmaxf(__uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3])));
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+        sum[q] = ex2(__uint_as_float(r[4 * q]) - m[q]) + ex2(__uint_as_float(r[4 * q + 1]) - m[q]) +
+                 ex2(__uint_as_float(r[4 * q + 2]) - m[q]) + ex2(__uint_as_float(r[4 * q + 3]) - m[q]);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        float cost = -LN2_F * (m[q] + lg2(sum[q]));
+        cost = m[q] > 0.5f * TC_CMIN ? cost : CUDART_INF_F;   // every Gaussian of the state has zero weight
+        if (s0 + q < s_hi) erow[s0 + q] = cost;
+    }
+}
+
 template <int D>
 __global__ void __launch_bounds__(TC_NT, 1)
 classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off, int B, int64_t N,
@@ -267,17 +287,18 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
                 const int sh = NH / TC_MP;
                 const int s_lo = (wq >> 2) * sh, s_hi = min(R, s_lo + sh);
                 float *erow = Es + (size_t)((j & 1) * TC_M + (tid & (TC_M - 1))) * ES;
-                for (int s0 = s_lo; s0 < s_hi; s0 += 4) {
-                    float v[16];
-                    tc::tmem_ld16(lane_base + s0 * TC_MP, v);
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        const float l0 = v[4 * q], l1 = v[4 * q + 1], l2 = v[4 * q + 2], l3 = v[4 * q + 3];
-                        const float m = fmaxf(fmaxf(l0, l1), fmaxf(l2, l3));
-                        float cost = CUDART_INF_F;           // every Gaussian of the state has zero weight
-                        if (m > 0.5f * TC_CMIN)
-                            cost = -LN2_F * (m + lg2(ex2(l0 - m) + ex2(l1 - m) + ex2(l2 - m) + ex2(l3 - m)));
-                        if (s0 + q < s_hi) erow[s0 + q] = cost;
+                // four states per TMEM load, the next load in flight while the current one is reduced
+                uint32_t va[16], vb[16];
+                if (s_lo < s_hi) tc::tmem_ld16_issue(lane_base + s_lo * TC_MP, va);
+                for (int s0 = s_lo; s0 < s_hi; s0 += 8) {
+                    tc::tmem_ld16_fence(va);
+                    const bool second = s0 + 4 < s_hi;
+                    if (second) tc::tmem_ld16_issue(lane_base + (s0 + 4) * TC_MP, vb);
+                    tc_state_costs(va, erow, s0, s_hi);
+                    if (second) {
+                        tc::tmem_ld16_fence(vb);
+                        if (s0 + 8 < s_hi) tc::tmem_ld16_issue(lane_base + (s0 + 8) * TC_MP, va);
+                        tc_state_costs(vb, erow, s0 + 4, s_hi);
                     }
                 }
             }
