@@ -86,6 +86,9 @@ int srb_classify(const float *X, const int32_t *utt_off, int32_t B, int64_t N, i
  * Costs agree with srb_classify within FP32 accumulation noise (~1e-6 relative); labels are equal wherever the two
  * best words differ by more than that. */
 int64_t srb_tc_model_floats(int R, int Mp, int D);
+/* diagnostics: with a device buffer of int64[64][10] set, CTA 0 of every following srb_classify_tc launch stamps
+ * clock64 at its pipeline events (score_tc.cu, TC_STAMP) for its first 64 tiles; NULL (the default) turns it off. */
+int srb_tc_set_timeline(int64_t *device_buf);
 int srb_pack_model_tc(const float *ab, const float *c, int R, int Mp, int D, float *tcb, void *stream);
 int srb_classify_tc_supported(int D, int W, int S, int Mp);
 int srb_classify_tc(const float *X, const int32_t *utt_off, int32_t B, int64_t N, int D, const float *tcb,

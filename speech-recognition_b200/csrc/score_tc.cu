@@ -35,10 +35,11 @@ constexpr int TC_BAR_FULL = 1, TC_BAR_FREE_A = 3, TC_BAR_FREE_B = 5;   // named 
 constexpr int TC_NMAX = 256;           // Gaussian columns of one MMA
 constexpr int TC_COL_A = 256;          // TMEM column of the A operand (accumulators sit in [0, NP))
 constexpr int TC_MP = 4;               // Gaussians per state handled by the epilogue
+constexpr int TC_TL_TILES = 64, TC_TL_EVENTS = 10;   // srb_tc_set_timeline buffer: int64[TC_TL_TILES][TC_TL_EVENTS]
 constexpr float TC_CMIN = -1e30f;      // stands in for log2(0) inside the MMA
 
 __host__ __device__ constexpr int tc_kp(int D) { return (2 * D + 7) & ~7; }
-static int tc_np(int R, int Mp) { return (R * Mp + 31) & ~31; }   // two MMA halves of a multiple of 16 columns
+static int tc_np(int R, int Mp) { return (R * Mp + 15) & ~15; }   // M = 128 needs N % 16 == 0
 
 // Gaussian parameters -> TF32 (hi, lo) pair in the K-major chunk-plane layout of tc05.cuh: tcb[2][KP/4][NP][4].
 // Feature k = 2*d is x'^2 (coefficient A), k = 2*d + 1 is x' (coefficient B), k = 2*D is the constant 1 whose
@@ -65,19 +66,23 @@ __global__ void pack_tc_kernel(const float *__restrict__ ab, const float *__rest
 
 // state costs of 4 states (16 accumulator columns = log2 weighted densities incl. constants) -> erow[s0 .. s0+3]:
 // cost = -ln sum_m 2^l_m (hmm_state.py:114-120 in the log domain), straight-line so that the four chains interleave.
+// The largest term is 2^0 = 1: a 4-element min/max network separates it, so a state costs 3 EX2 + 1 LG2.
 __device__ __forceinline__ void tc_state_costs(const uint32_t (&r)[16], float *erow, int s0, int s_hi) {
-    float m[4], sum[4];
-#pragma unroll
-    for (int q = 0; q < 4; ++q)
-        m[q] = fmaxf(fmaxf(__uint_as_float(r[4 * q]), __uint_as_float(r[4 * q + 1])),
-                     fmaxf(__uint_as_float(r[4 * q + 2]), __uint_as_float(r[4 * q + 3])));
-#pragma unroll
-    for (int q = 0; q < 4; ++q)
-        sum[q] = ex2(__uint_as_float(r[4 * q]) - m[q]) + ex2(__uint_as_float(r[4 * q + 1]) - m[q]) +
-                 ex2(__uint_as_float(r[4 * q + 2]) - m[q]) + ex2(__uint_as_float(r[4 * q + 3]) - m[q]);
+    float m[4], x0[4], x1[4], x2[4];
 #pragma unroll
     for (int q = 0; q < 4; ++q) {
-        float cost = -LN2_F * (m[q] + lg2(sum[q]));
+        const float l0 = __uint_as_float(r[4 * q]), l1 = __uint_as_float(r[4 * q + 1]);
+        const float l2 = __uint_as_float(r[4 * q + 2]), l3 = __uint_as_float(r[4 * q + 3]);
+        const float a = fmaxf(l0, l1), b = fminf(l0, l1), c = fmaxf(l2, l3), d = fminf(l2, l3);
+        m[q] = fmaxf(a, c);
+        x0[q] = b - m[q];
+        x1[q] = d - m[q];
+        x2[q] = fminf(a, c) - m[q];
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const float sum = 1.f + ex2(x0[q]) + ex2(x1[q]) + ex2(x2[q]);
+        float cost = -LN2_F * (m[q] + lg2(sum));
         cost = m[q] > 0.5f * TC_CMIN ? cost : CUDART_INF_F;   // every Gaussian of the state has zero weight
         if (s0 + q < s_hi) erow[s0 + q] = cost;
     }
@@ -88,10 +93,10 @@ __global__ void __launch_bounds__(TC_NT, 1)
 classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off, int B, int64_t N,
                    const uint32_t *__restrict__ tcb, const float *__restrict__ shift, int W,
                    int S, int NP, const float *__restrict__ trans, float *__restrict__ final_cost,
-                   int32_t *__restrict__ label) {
+                   int32_t *__restrict__ label, long long *__restrict__ timeline) {
     constexpr int KP = tc_kp(D), SMAX = SRB_DP_MAX_STATES;
     extern __shared__ __align__(128) float smem[];
-    __shared__ uint64_t bar[5];
+    __shared__ uint64_t bar[4];
     __shared__ int sub_u[8];
     __shared__ uint32_t tslot;
     __shared__ int band_flag;
@@ -105,6 +110,9 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
     float *fin_s = xs + TC_SUB * TC_XSQ;                     // TC_SUB * TC_FIN * W
     float *Es = fin_s + TC_SUB * TC_FIN * W;                 // TC_CHUNK * ES
     const int tid = threadIdx.x, wq = tid >> 5;
+    // diagnostics (srb_tc_set_timeline): CTA 0 stamps clock64 at its pipeline events of the first TC_TL_TILES tiles
+    const bool tl_on = timeline != nullptr && blockIdx.x == 0 && (tid & 31) == 0;
+#define TC_STAMP(j, k) do { if (tl_on && (j) < TC_TL_TILES) timeline[(j) * TC_TL_EVENTS + (k)] = clock64(); } while (0)
 
     // utterance range of this CTA: boundaries at the first utterance starting at or after b*N/grid
     const int G = gridDim.x, b = blockIdx.x;
@@ -114,11 +122,10 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
 
     if (wq == 0) tc::tmem_alloc<512>(&tslot);
     if (tid == 32) {
-        tc::mbar_init(&bar[0], TC_M);                        // XR: group B's threads
-        tc::mbar_init(&bar[1], TC_M);                        // AR: group A's threads
-        tc::mbar_init(&bar[2], 1);                           // H0, H1: tcgen05.commit
-        tc::mbar_init(&bar[3], 1);
-        tc::mbar_init(&bar[4], TC_M);                        // D1F: group B's threads
+        tc::mbar_init(&bar[0], TC_M);                        // XR: group A's threads
+        tc::mbar_init(&bar[1], TC_DP);                       // AR: the Viterbi warps' threads
+        tc::mbar_init(&bar[2], 1);                           // HB: tcgen05.commit
+        tc::mbar_init(&bar[3], TC_MAIN);                     // DF: all scoring threads
         tc::mbar_fence_init();
     }
     if (tid == 0) band_flag = 1;
@@ -139,8 +146,7 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
     const bool banded = band_flag != 0;
     const uint32_t tb = tslot;
     const uint32_t lane_base = tb + ((uint32_t)((wq & 3) * 32) << 16);
-    const int NH = NP >> 1;                                  // the MMA runs as two column halves (see the epilogue)
-    const uint32_t idesc = tc::idesc_tf32(TC_M, NH);
+    const uint32_t idesc = tc::idesc_tf32(TC_M, NP);
     const uint32_t bH = tc::smem_u32(Bh), bL = tc::smem_u32(Bl);
 
     // The CTA's utterance range is cut into TC_SUB sub-streams of whole utterances (equal frame counts up to one
@@ -159,10 +165,11 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
     for (int q = 0; q < TC_SUB; ++q) ntile = max(ntile, (int)((off[sub_u[q + 1]] - off[sub_u[q]] + TC_SF - 1) / TC_SF));
 
     // mbarriers, one completion per tile each (parity of tile j = j & 1):
-    //   XR  frames of the tile staged (group B -> A)          AR  A operand in TMEM, staging buffer consumed (A -> MMA, B)
-    //   H0 / H1  column half 0 / 1 accumulated (MMA -> A, B; H1 also frees the A operand)
-    //   D1F accumulator half 1 read back (B -> MMA)
-    uint64_t *XR = &bar[0], *AR = &bar[1], *H0 = &bar[2], *H1 = &bar[3], *D1F = &bar[4];
+    //   XR   frames of the tile staged (scoring group A -> Viterbi warps)
+    //   AR   A operand in TMEM, staging buffer consumed (Viterbi warps -> MMA, group A)
+    //   HB   accumulators complete (MMA -> scoring warps; also frees the A operand for the Viterbi warps)
+    //   DF   accumulators read back (scoring warps -> MMA)
+    uint64_t *XR = &bar[0], *AR = &bar[1], *HB = &bar[2], *DF = &bar[3];
 
     if (wq == TC_MMA_WARP) {
         // ================= MMA issuer: one thread
@@ -170,53 +177,97 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
             for (int j = 0; j < ntile; ++j) {
                 tc::mbar_wait(AR, j & 1);
                 tc::fence_after_sync();
-#pragma unroll 1
-                for (int hf = 0; hf < 2; ++hf) {             // column half hf -> accumulators [hf*NH, hf*NH + NH)
-                    if (hf == 1 && j > 0) {
-                        tc::mbar_wait(D1F, (j - 1) & 1);     // tile j-1's second half has been read back
-                        tc::fence_after_sync();
-                    }
-#pragma unroll
-                    for (int kk = 0; kk < KP / 8; ++kk) {
-                        const uint64_t dbh = tc::smem_desc(bH + kk * 2 * NP * 16 + hf * NH * 16, NP * 16, 128);
-                        const uint64_t dbl = tc::smem_desc(bL + kk * 2 * NP * 16 + hf * NH * 16, NP * 16, 128);
-                        tc::mma_tf32_ts(tb + hf * NH, tb + TC_COL_A + KP + kk * 8, dbh, idesc, kk > 0);
-                        tc::mma_tf32_ts(tb + hf * NH, tb + TC_COL_A + kk * 8, dbl, idesc, true);
-                        tc::mma_tf32_ts(tb + hf * NH, tb + TC_COL_A + kk * 8, dbh, idesc, true);
-                    }
-                    tc::mma_commit(hf ? H1 : H0);
+                TC_STAMP(j, 0);
+                if (j > 0) {
+                    tc::mbar_wait(DF, (j - 1) & 1);          // tile j-1's accumulators have been read back
+                    tc::fence_after_sync();
                 }
+                TC_STAMP(j, 1);
+                // one N = NP MMA per K step and product: 122 cycles each at N = 224, while anything narrower than 160
+                // columns costs a flat 93 (tools/probe_tc.cu), so the accumulator is not split
+#pragma unroll
+                for (int kk = 0; kk < KP / 8; ++kk) {
+                    const uint64_t dbh = tc::smem_desc(bH + kk * 2 * NP * 16, NP * 16, 128);
+                    const uint64_t dbl = tc::smem_desc(bL + kk * 2 * NP * 16, NP * 16, 128);
+                    tc::mma_tf32_ts(tb, tb + TC_COL_A + KP + kk * 8, dbh, idesc, kk > 0);
+                    tc::mma_tf32_ts(tb, tb + TC_COL_A + kk * 8, dbl, idesc, true);
+                    tc::mma_tf32_ts(tb, tb + TC_COL_A + kk * 8, dbh, idesc, true);
+                }
+                tc::mma_commit(HB);
+                TC_STAMP(j, 2);
             }
         }
     } else if (wq >= TC_MAIN / 32) {
-        // ================= Viterbi warps: warp q advances sub-stream q's recursions over tile j while the scoring warps
-        //                   produce tile j+1's costs
+        // ================= Viterbi warps: warp q owns sub-stream q = TMEM lanes 32q .. 32q+31.  Per iteration it turns
+        //                   tile j's frames into the A operand (as soon as tile j-1's MMAs are done), then advances the
+        //                   recursions over tile j-1, whose costs the scoring warps have finished meanwhile.
         const int q = wq - TC_MAIN / 32, lane = tid & 31;
         const int sue = sub_u[q + 1];
         const int64_t sbeg = off[sub_u[q]], send = off[sue];
         int ufirst = sub_u[q], par = 0;
         float *carry_q = carry + (size_t)q * 2 * W * SMAX;
-        for (int j = 0; j < ntile; ++j) {
-            const int64_t cf0 = sbeg + (int64_t)j * TC_SF;
-            named_sync(TC_BAR_FULL + (j & 1), TC_MAIN + TC_DP);   // costs of tile j are in ring slot j & 1
-            if (cf0 < send) {
-                classify_dp_chunk<32, -1>(Es + (size_t)((j & 1) * TC_M + q * TC_SF) * ES, ES, off, sue, ufirst, cf0,
-                                          min(send, cf0 + (int64_t)TC_SF), W, S, tr_s, carry_q, par, banded, final_cost,
-                                          label, lane, fin_s + (size_t)q * TC_FIN * W, TC_FIN);
-                par ^= 1;
+        for (int j = 0; j <= ntile; ++j) {
+            if (j < ntile) {
+                // ---- A operand: thread = frame = TMEM lane
+                tc::mbar_wait(XR, j & 1);                    // frames of tile j are staged
+                if (j > 0) {
+                    tc::mbar_wait(HB, (j - 1) & 1);          // every MMA of tile j-1 is done with the A operand
+                    tc::fence_after_sync();
+                }
+                if (q == 0) TC_STAMP(j, 5);
+                const int64_t f0 = sbeg + (int64_t)j * TC_SF;
+                const int nf = (int)max((int64_t)0, min((int64_t)TC_SF, send - f0));
+                const int lf = lane < nf ? lane : max(nf - 1, 0);   // lanes past the end repeat (discarded)
+                const float *row = xs + q * TC_XSQ + (int)((f0 * D) & 3) + lf * D;
+#pragma unroll
+                for (int k0 = 0; k0 < KP; k0 += 8) {
+                    uint32_t h[8], l[8];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) {
+                        const int d = (k0 >> 1) + i;
+                        if (d < D) {
+                            const float v = nf > 0 ? row[d] - shift_s[d] : 0.f;
+                            tc::split_tf32(v * v, h[2 * i], l[2 * i]);
+                            tc::split_tf32(v, h[2 * i + 1], l[2 * i + 1]);
+                        } else {                             // k = 2*D: the constant feature, then zero padding
+                            h[2 * i] = d == D ? 0x3f800000u : 0u;
+                            h[2 * i + 1] = l[2 * i] = l[2 * i + 1] = 0u;
+                        }
+                    }
+                    tc::tmem_st8(lane_base + TC_COL_A + k0, h);
+                    tc::tmem_st8(lane_base + TC_COL_A + KP + k0, l);
+                }
+                tc::tmem_st_wait();
+                tc::fence_before_sync();
+                tc::mbar_arrive(AR);
+                if (q == 0) TC_STAMP(j, 6);
             }
-            __threadfence_block();
-            named_arrive(TC_BAR_FREE_A + (j & 1), TC_M + TC_DP);  // slot may be overwritten (tile j + 2), told to
-            named_arrive(TC_BAR_FREE_B + (j & 1), TC_M + TC_DP);  // both scoring groups
+            if (j >= 1) {
+                const int t = j - 1;
+                const int64_t cf0 = sbeg + (int64_t)t * TC_SF;
+                named_sync(TC_BAR_FULL + (t & 1), TC_MAIN + TC_DP);   // costs of tile t are in ring slot t & 1
+                if (q == 0) TC_STAMP(t, 7);
+                if (cf0 < send) {
+                    classify_dp_chunk<32, -1>(Es + (size_t)((t & 1) * TC_M + q * TC_SF) * ES, ES, off, sue, ufirst, cf0,
+                                              min(send, cf0 + (int64_t)TC_SF), W, S, tr_s, carry_q, par, banded,
+                                              final_cost, label, lane, fin_s + (size_t)q * TC_FIN * W, TC_FIN);
+                    par ^= 1;
+                }
+                if (q == 0) TC_STAMP(t, 8);
+                __threadfence_block();
+                named_arrive(TC_BAR_FREE_A + (t & 1), TC_M + TC_DP);  // slot may be overwritten (tile t + 2), told to
+                named_arrive(TC_BAR_FREE_B + (t & 1), TC_M + TC_DP);  // both scoring groups
+            }
         }
     } else {
-        // ================= scoring warps.  Group A (warps 0-3): features of tile j -> TMEM, epilogue of column half 0.
-        //                   Group B (warps 4-7): staging of tile j+1, epilogue of column half 1.
+        // ================= scoring warps: epilogue of both column halves, the states of each half split between group A
+        //                   (warps 0-3) and group B (warps 4-7) so that every scheduler has two warps on it.  Group A
+        //                   also stages the next tile's frames.
         const bool grpA = wq < 4;
-        const int sq = wq & (TC_SUB - 1);                    // sub-stream whose frames warp sq of group A turns into features
+        const int sq = wq & (TC_SUB - 1);
         const int64_t my_beg = off[sub_u[sq]], my_end = off[sub_u[sq + 1]];
-        // staging (group B): thread t copies vectors (t & 31) + 32k of sub-stream t >> 5.  A tile advances every
-        // sub-stream by 32 frames = 312 float4, so the 16-byte phase of a sub-stream's first row never changes.
+        // staging: lane i of warp sq copies vectors i + 32k of sub-stream sq.  A tile advances every sub-stream by
+        // 32 frames = 312 float4, so the 16-byte phase of a sub-stream's first row never changes.
         const int sti = tid & 31;
         const int64_t st_g0 = my_beg * D, st_ga = st_g0 & ~(int64_t)3, st_end = my_end * D, gend = N * D;
         float *st_dst = xs + sq * TC_XSQ;
@@ -241,76 +292,57 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
             cp_async_wait_all();
             tc::mbar_arrive(XR);
         };
-        if (!grpA) stage_tile(0);
+        const int sp = (((R + 1) >> 1) + 3) & ~3;            // group A takes states [0, sp), group B the rest
+        const int s_lo = grpA ? 0 : sp, s_hi = grpA ? min(R, sp) : R;
+        float *erow0 = Es + (size_t)(tid & (TC_M - 1)) * ES;
+        if (grpA) stage_tile(0);
         for (int j = 0; j < ntile; ++j) {
-            if (grpA) {
-                // ---- A operand: thread = frame = TMEM lane
-                tc::mbar_wait(XR, j & 1);                    // frames of tile j are staged
-                if (j > 0) {
-                    tc::mbar_wait(H1, (j - 1) & 1);          // every MMA of tile j-1 is done with the A operand
-                    tc::fence_after_sync();
-                }
-                const int64_t f0 = my_beg + (int64_t)j * TC_SF;
-                const int nf = (int)max((int64_t)0, min((int64_t)TC_SF, my_end - f0));
-                const int lf = (tid & 31) < nf ? (tid & 31) : max(nf - 1, 0);   // lanes past the end repeat (discarded)
-                const float *row = xs + sq * TC_XSQ + (int)((f0 * D) & 3) + lf * D;
-#pragma unroll
-                for (int k0 = 0; k0 < KP; k0 += 8) {
-                    uint32_t h[8], l[8];
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        const int d = (k0 >> 1) + q;
-                        if (d < D) {
-                            const float v = nf > 0 ? row[d] - shift_s[d] : 0.f;
-                            tc::split_tf32(v * v, h[2 * q], l[2 * q]);
-                            tc::split_tf32(v, h[2 * q + 1], l[2 * q + 1]);
-                        } else {                             // k = 2*D: the constant feature, then zero padding
-                            h[2 * q] = d == D ? 0x3f800000u : 0u;
-                            h[2 * q + 1] = l[2 * q] = l[2 * q + 1] = 0u;
-                        }
-                    }
-                    tc::tmem_st8(lane_base + TC_COL_A + k0, h);
-                    tc::tmem_st8(lane_base + TC_COL_A + KP + k0, l);
-                }
-                tc::tmem_st_wait();
-                tc::fence_before_sync();
-                tc::mbar_arrive(AR);
-            } else {
+            if (grpA && j + 1 < ntile) {
                 tc::mbar_wait(AR, j & 1);                    // staging buffer consumed
-                if (j + 1 < ntile) stage_tile(j + 1);
+                stage_tile(j + 1);
             }
-            // ---- epilogue of this group's column half: state cost = -ln sum_m 2^D  (constants are inside D)
-            tc::mbar_wait(grpA ? H0 : H1, j & 1);
+            float *erow = erow0 + (size_t)(j & 1) * TC_M * ES;
+            // ---- state cost = -ln sum_m 2^D  (constants are inside D) for this group's states
+            tc::mbar_wait(HB, j & 1);
             tc::fence_after_sync();
+            if (wq == 0) TC_STAMP(j, 3);
             if (j >= 2) named_sync((grpA ? TC_BAR_FREE_A : TC_BAR_FREE_B) + (j & 1), TC_M + TC_DP);   // ring slot free
             {
-                const int sh = NH / TC_MP;
-                const int s_lo = (wq >> 2) * sh, s_hi = min(R, s_lo + sh);
-                float *erow = Es + (size_t)((j & 1) * TC_M + (tid & (TC_M - 1))) * ES;
-                // four states per TMEM load, the next load in flight while the current one is reduced
-                uint32_t va[16], vb[16];
-                if (s_lo < s_hi) tc::tmem_ld16_issue(lane_base + s_lo * TC_MP, va);
-                for (int s0 = s_lo; s0 < s_hi; s0 += 8) {
+                // eight states (two TMEM loads) per round, reduced in one straight-line block so that the chains
+                // interleave; the next round's loads are in flight meanwhile
+                uint32_t va[16], vb[16], vc[16], vd[16];
+                auto issue2 = [&](int s0, uint32_t (&p)[16], uint32_t (&q)[16]) {
+                    if (s0 < s_hi) tc::tmem_ld16_issue(lane_base + s0 * TC_MP, p);
+                    if (s0 + 4 < s_hi) tc::tmem_ld16_issue(lane_base + (s0 + 4) * TC_MP, q);
+                };
+                issue2(s_lo, va, vb);
+                for (int s0 = s_lo; s0 < s_hi; s0 += 16) {
                     tc::tmem_ld16_fence(va);
-                    const bool second = s0 + 4 < s_hi;
-                    if (second) tc::tmem_ld16_issue(lane_base + (s0 + 4) * TC_MP, vb);
+                    tc::tmem_ld16_fence(vb);
+                    issue2(s0 + 8, vc, vd);
                     tc_state_costs(va, erow, s0, s_hi);
-                    if (second) {
-                        tc::tmem_ld16_fence(vb);
-                        if (s0 + 8 < s_hi) tc::tmem_ld16_issue(lane_base + (s0 + 8) * TC_MP, va);
-                        tc_state_costs(vb, erow, s0 + 4, s_hi);
+                    if (s0 + 4 < s_hi) tc_state_costs(vb, erow, s0 + 4, s_hi);
+                    if (s0 + 8 < s_hi) {
+                        tc::tmem_ld16_fence(vc);
+                        tc::tmem_ld16_fence(vd);
+                        issue2(s0 + 16, va, vb);
+                        tc_state_costs(vc, erow, s0 + 8, s_hi);
+                        if (s0 + 12 < s_hi) tc_state_costs(vd, erow, s0 + 12, s_hi);
                     }
                 }
+                if (wq == 0) TC_STAMP(j, 4);
+                if (wq == 4) TC_STAMP(j, 9);
+                tc::fence_before_sync();
+                tc::mbar_arrive(DF);                         // the accumulators may be overwritten
             }
-            tc::fence_before_sync();
-            if (!grpA) tc::mbar_arrive(D1F);                 // accumulator half 1 may be overwritten
             __threadfence_block();
-            named_arrive(TC_BAR_FULL + (j & 1), TC_MAIN + TC_DP);   // hand this half of tile j's costs to the Viterbi warps
+            named_arrive(TC_BAR_FULL + (j & 1), TC_MAIN + TC_DP);   // hand tile j's costs to the Viterbi warps
         }
     }
     tc::fence_before_sync();
     __syncthreads();
     if (wq == 0) tc::tmem_free<512>(tb);
+#undef TC_STAMP
 }
 
 static size_t classify_tc_smem_bytes(int W, int S, int NP, int D) {
@@ -323,7 +355,14 @@ static size_t classify_tc_smem_bytes(int W, int S, int NP, int D) {
 
 using namespace srb;
 
+static long long *g_tc_timeline = nullptr;
+
 extern "C" {
+
+int srb_tc_set_timeline(int64_t *device_buf) {
+    g_tc_timeline = reinterpret_cast<long long *>(device_buf);
+    return SRB_OK;
+}
 
 int64_t srb_tc_model_floats(int R, int Mp, int D) {
     if (R <= 0 || Mp <= 0 || (Mp & 3) || D <= 0 || tc_np(R, Mp) > TC_NMAX) return 0;
@@ -370,7 +409,7 @@ int srb_classify_tc(const float *X, const int32_t *utt_off, int32_t B, int64_t N
     const int grid = (int)(want < sms ? want : sms);
     SRB_CUDA(cudaFuncSetAttribute(classify_tc_kernel<39>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     classify_tc_kernel<39><<<grid, TC_NT, bytes, (cudaStream_t)stream>>>(
-        X, utt_off, B, N, reinterpret_cast<const uint32_t *>(tcb), shift, W, S, NP, trans, final_cost, label);
+        X, utt_off, B, N, reinterpret_cast<const uint32_t *>(tcb), shift, W, S, NP, trans, final_cost, label, g_tc_timeline);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }

@@ -101,9 +101,11 @@ probe(const float *A, const float *B, float *Dss, float *Dts, long long *clk) {
     fence_before_sync();
     __syncthreads();
     fence_after_sync();
-    // ---- (4) cycles: 8 x 30 MMAs back to back, SS then TS
-    for (int mode = 0; mode < 2; ++mode) {
+    // ---- (4) cycles: 8 x 30 MMAs back to back, SS then TS, then TS at narrower N (B rows stay 224 apart)
+    for (int mode = 0; mode < 8; ++mode) {
         long long t0 = 0;
+        const int nn = mode < 2 ? N : (mode == 2 ? 112 : mode == 3 ? 64 : mode == 4 ? 32 : mode == 5 ? 160 : mode == 6 ? 128 : 16);
+        const uint32_t idn = idesc_tf32(M, nn);
         if (t == 0) {
             t0 = clock64();
             for (int rep = 0; rep < 8; ++rep)
@@ -111,8 +113,8 @@ probe(const float *A, const float *B, float *Dss, float *Dts, long long *clk) {
                     const uint64_t dah = smem_desc(aH + kk * 2 * M * 16, M * 16, 128);
                     const uint64_t dbh = smem_desc(bH + kk * 2 * N * 16, N * 16, 128);
                     for (int j = 0; j < 3; ++j) {
-                        if (mode == 0) mma_tf32_ss(tb + TM_D, dah, dbh, idesc, true);
-                        else mma_tf32_ts(tb + TM_D, tb + TM_AH + kk * 8, dbh, idesc, true);
+                        if (mode == 0) mma_tf32_ss(tb + TM_D, dah, dbh, idn, true);
+                        else mma_tf32_ts(tb + TM_D, tb + TM_AH + kk * 8, dbh, idn, true);
                     }
                 }
             mma_commit(&bar);
@@ -135,7 +137,7 @@ static void run(const char *name, const std::vector<float> &A, const std::vector
     cudaMalloc(&dB, B.size() * 4);
     cudaMalloc(&dS, M * N * 4);
     cudaMalloc(&dT, M * N * 4);
-    cudaMalloc(&dC, 16);
+    cudaMalloc(&dC, 64);
     cudaMemcpy(dA, A.data(), A.size() * 4, cudaMemcpyHostToDevice);
     cudaMemcpy(dB, B.data(), B.size() * 4, cudaMemcpyHostToDevice);
     cudaMemset(dS, 0xff, M * N * 4);
@@ -147,10 +149,10 @@ static void run(const char *name, const std::vector<float> &A, const std::vector
     printf("[%s] kernel: %s\n", name, cudaGetErrorString(e));
     if (e != cudaSuccess) exit(1);
     std::vector<float> S(M * N), T(M * N);
-    long long clk[2];
+    long long clk[8];
     cudaMemcpy(S.data(), dS, M * N * 4, cudaMemcpyDeviceToHost);
     cudaMemcpy(T.data(), dT, M * N * 4, cudaMemcpyDeviceToHost);
-    cudaMemcpy(clk, dC, 16, cudaMemcpyDeviceToHost);
+    cudaMemcpy(clk, dC, 64, cudaMemcpyDeviceToHost);
     double es = 0, et = 0, mag = 0, e32 = 0;
     int bad_s = 0, bad_t = 0;
     for (int r = 0; r < M; ++r)
@@ -173,6 +175,8 @@ static void run(const char *name, const std::vector<float> &A, const std::vector
     printf("[%s] max |err| / sum|a*b|:  SS %.3e (bad %d)   TS %.3e (bad %d)   fp32 fmaf chain %.3e\n", name, es, bad_s, et, bad_t, e32);
     printf("[%s] D[5][7] ss=%g ts=%g ; 240 MMAs (M128 N224 K8): SS %lld clk (%.1f/MMA)  TS %lld clk (%.1f/MMA)\n", name,
            S[5 * N + 7], T[5 * N + 7], clk[0], clk[0] / 240.0, clk[1], clk[1] / 240.0);
+    printf("[%s] TS clk/MMA at N=112: %.1f  N=64: %.1f  N=32: %.1f  N=160: %.1f  N=128: %.1f  N=16: %.1f\n", name, clk[2] / 240.0,
+           clk[3] / 240.0, clk[4] / 240.0, clk[5] / 240.0, clk[6] / 240.0, clk[7] / 240.0);
     cudaFree(dA); cudaFree(dB); cudaFree(dS); cudaFree(dT); cudaFree(dC);
 }
 
