@@ -35,6 +35,7 @@ FMA_PER_FRAME_DECODE = W_ * S_ * M_ * 2 * D_          # 17 160 FMA pe
 # DRAM bytes per frame of the two headline kernels, from the committed `ncu --set full` captures
 # (dram__bytes_read.sum + dram__bytes_write.sum over one 2 M-frame / 10 M-frame launch; algorithmic: 156 B/frame of X + outputs)
 NCU_TRAFFIC_PER_FRAME = {"classify_kernel<39>": (318.694e6 / 2e6, "profiles/r01_ncu_classify_v3_raw.csv"),
+                         "classify_tc_kernel<39>": ((312.401e6 + 4.543e6) / 2e6, "profiles/r01_ncu_classify_tc_v10_raw.csv"),
                          "em_isolated_kernel<39,5,2>": ((1565.19e6 + 4.78e6) / 1e7, "profiles/r01_ncu_emfused_v6_raw.csv")}
 
 
@@ -213,7 +214,9 @@ def bench_decode(args, ctx):
                 "algorithmic": "17160 FMA/frame = 220 Gaussians x 2*39 (SURVEY 8d), FP32-equivalent",
                 "tensor_pipe": {"executed_tflops": executed / 1e12, "tf32_peak_tflops": bf16 / 2,
                                 "frac": executed / 1e12 / (bf16 / 2),
-                                "note": "executed = 3 TF32 MMAs per product on padded 128x224x80 tiles"},
+                                "note": "executed = 3 TF32 MMAs per product on padded 128x224x80 tiles; ncu "
+                                        "(profiles/r01_ncu_classify_tc_v10_raw.csv): sm__pipe_tensor_cycles_active "
+                                        "43.4 % of elapsed"},
                 "fp32_fma": {"peak_tflops": 2 * peak_fma / 1e12, "frac": flops / (2 * peak_fma),
                              "note": "algorithmic rate over the measured FFMA2 peak; > 1 = above the CUDA-core roofline"},
                 "hbm": hbm}
