@@ -39,6 +39,16 @@ NCU_TRAFFIC_PER_FRAME = {"classify_kernel<39>": (318.694e6 / 2e6, "profiles/r01_
                          "em_isolated_kernel<39,5,2>": ((1565.19e6 + 4.78e6) / 1e7, "profiles/r01_ncu_emfused_v6_raw.csv")}
 
 
+# stdout carries exactly ONE JSON line: the descriptor is saved here and fd 1 is pointed at stderr for the rest of the
+# run, so that whatever a library prints (NCCL's version banner, for one) cannot land next to it.
+_STDOUT_FD = os.dup(1)
+os.dup2(2, 1)
+
+
+def emit(line):
+    os.write(_STDOUT_FD, (json.dumps(line) + "\n").encode())
+
+
 def ncu_traffic(kernel, frames):
     if kernel not in NCU_TRAFFIC_PER_FRAME:
         return {"traffic": None, "traffic_source": "no ncu --set full capture committed for this kernel yet"}
@@ -504,7 +514,7 @@ def run_ours(args):
                      "config": {"workload": wl, "frames_per_gpu": N, "l2": "inputs larger than L2",
                                 "parallelism": f"utterance-sharded x{world}, no collective"}})
         if rank == 0:
-            print(json.dumps(line), flush=True)
+            emit(line)
         if world > 1:
             dist.destroy_process_group()
         return
@@ -534,7 +544,7 @@ def run_ours(args):
                                 "sample": f"{n_cpu} utterances x {args.frames} frames, oracle/ float64 C restatement "
                                           f"(OpenMP), {ms:.0f} ms"}
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -572,7 +582,7 @@ def run_reference(args):
                          "sample": f"{n_cpu} utterances x {args.frames} frames per step"},
         "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 if __name__ == "__main__":
