@@ -140,6 +140,15 @@ int srb_viterbi_banded(const float *E, int64_t ldE, const int32_t *utt_off, int3
                        float *best_cost, int32_t *best_end, const int64_t *path_off, int32_t *path_state,
                        int32_t *path_frame, int32_t *path_len, int32_t *frame_label, void *stream);
 
+/* ---- decoded path -> word string (main.py:59-67, the step right after decode_hmm_states) ----
+ * path_state/path_off/path_len as written by srb_viterbi_graph / srb_viterbi_banded (reversed paths);
+ * state_word[g_state_off[g] + r] = word of graph g's local state r, or -1 for a non-emitting state.
+ * The path is read forwards, consecutive duplicates removed, split at the NES; the first state of each piece gives
+ * the word.  words int32[B, max_words] receives the first max_words words, nwords[B] the full count. */
+int srb_path_words(const int32_t *path_state, const int64_t *path_off, const int32_t *path_len, int32_t B,
+                   const int32_t *utt_graph, const int32_t *g_state_off, const int32_t *state_word, int32_t max_words,
+                   int32_t *words, int32_t *nwords, void *stream);
+
 /* ---- K4: batched forward-backward (Baum-Welch E-step) for NES-free graphs -------------------------
  * The reference has NO forward-backward; semantics are defined to be consistent with
  * srb_viterbi_graph: same graph packing, start in state 0 at frame 0, end in any end_state at the last frame;

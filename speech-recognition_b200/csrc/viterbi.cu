@@ -488,6 +488,39 @@ forward_backward_kernel(const float *__restrict__ E, int64_t ldE, const int32_t 
     }
 }
 
+// ------------------------------------------------------------------------------------------------ path -> words
+// main.py:59-67 after the decoder: the reversed path read forwards, consecutive duplicate states removed, split at the
+// non-emitting states, the first state of every piece mapped to its word.  One warp per utterance: lane i looks at
+// forward position 32c + i; a word starts where the state changes to an emitting one whose predecessor is a NES (or
+// at position 0); ballot + popc give the output slot, so the words come out in order without a second pass.
+__global__ void path_words_kernel(const int32_t *__restrict__ path_state, const int64_t *__restrict__ path_off,
+                                  const int32_t *__restrict__ path_len, int B, const int32_t *__restrict__ utt_graph,
+                                  const int32_t *__restrict__ g_state_off, const int32_t *__restrict__ state_word,
+                                  int max_words, int32_t *__restrict__ words, int32_t *__restrict__ nwords) {
+    const int lane = threadIdx.x & 31;
+    const int u = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5);
+    if (u >= B) return;
+    const int len = max(path_len[u], 0);
+    const int32_t *ps = path_state + path_off[u];
+    const int32_t *sw = state_word + g_state_off[utt_graph ? utt_graph[u] : 0];
+    int count = 0, carry = -1;
+    for (int c0 = 0; c0 < len; c0 += 32) {
+        const int p = c0 + lane;
+        const int s = p < len ? ps[len - 1 - p] : -1;            // the path is stored reversed (decode.py:142-146)
+        int prev = __shfl_up_sync(0xffffffffu, s, 1);
+        if (lane == 0) prev = carry;
+        const bool start = p < len && s != prev && sw[s] >= 0 && (p == 0 || sw[prev] < 0);
+        const unsigned m = __ballot_sync(0xffffffffu, start);
+        if (start) {
+            const int k = count + __popc(m & ((1u << lane) - 1));
+            if (k < max_words) words[(size_t)u * max_words + k] = sw[s];
+        }
+        count += __popc(m);
+        carry = __shfl_sync(0xffffffffu, s, 31);
+    }
+    if (lane == 0) nwords[u] = count;
+}
+
 }  // namespace srb
 
 using namespace srb;
@@ -605,6 +638,21 @@ int srb_forward_backward(const float *E, int64_t ldE, const int32_t *utt_off, in
                               end_state);
     forward_backward_kernel<<<(int)grid, VW * 32, bytes, (cudaStream_t)stream>>>(
         E, ldE, utt_off, B, G, succ_ptr, succ_idx, succ_cost, pred_tgt, Rmax, NNZmax, ws_off, gamma, neg_log_z, xi_sum);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+int srb_path_words(const int32_t *path_state, const int64_t *path_off, const int32_t *path_len, int32_t B,
+                   const int32_t *utt_graph, const int32_t *g_state_off, const int32_t *state_word, int32_t max_words,
+                   int32_t *words, int32_t *nwords, void *stream) {
+    SRB_REQUIRE(B >= 0 && max_words >= 0, SRB_EINVAL, "srb_path_words: bad sizes");
+    if (B == 0) return SRB_OK;
+    SRB_REQUIRE(path_state && path_off && path_len && g_state_off && state_word && nwords && (words || max_words == 0),
+                SRB_EINVAL, "srb_path_words: null pointer");
+    const int threads = 128;
+    const int64_t grid = ((int64_t)B * 32 + threads - 1) / threads;
+    path_words_kernel<<<(int)grid, threads, 0, (cudaStream_t)stream>>>(path_state, path_off, path_len, B, utt_graph,
+                                                                        g_state_off, state_word, max_words, words, nwords);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }

@@ -166,7 +166,9 @@ def recognize_strings(xs, models, n_layers=7):
                 s.parent = i
     seq, trans, ends = build_state_sequences(models, [list(range(len(models)))] * n_layers)
     res = decode_batch(xs, [(seq, trans, ends)], want_path=True)
-    return [path_to_models(p, seq) for p in res.paths()]
+    # the paths stay on the device: srb_path_words turns them into word strings (path_to_models is the host form)
+    state_word = [-1 if type(s) is NES else int(s.parent) for s in seq]
+    return res.vres.words(state_word, n_layers)
 
 
 __all__ = ["build_state_sequences", "continuous_train", "path_to_models", "recognize_strings"]

@@ -250,6 +250,23 @@ class ViterbiResult:
             out.append(np.stack([ps[o:o + n], pf[o:o + n]], axis=1).astype(np.int64))
         return out
 
+    def words(self, state_word, max_words):
+        """Word strings straight from the device paths (main.py:59-67; srb_path_words).
+        state_word: int32 per packed state (graphs back to back), -1 for a non-emitting state.
+        -> list of int lists.  Raises when a string is longer than max_words."""
+        dev = self.path_len.device
+        B = self.path_len.numel()
+        sw = torch.as_tensor(np.ascontiguousarray(state_word, dtype=np.int32)).to(dev)
+        words = torch.empty((B, max(max_words, 1)), dtype=torch.int32, device=dev)
+        nw = torch.empty(B, dtype=torch.int32, device=dev)
+        _l.check(_l.load().srb_path_words(_l.ptr(self.path_state), _l.ptr(self.path_off_dev), _l.ptr(self.path_len), B,
+                                          _l.ptr(self.utt_graph_dev), _l.ptr(self.gb["g_state_off"]), _l.ptr(sw),
+                                          max_words, _l.ptr(words), _l.ptr(nw), _l.stream_ptr()))
+        wn, nn = words.cpu().numpy(), nw.cpu().numpy()
+        if (nn > max_words).any():
+            raise RuntimeError("srb_path_words: a decoded string has more than max_words words")
+        return [wn[u, :nn[u]].tolist() for u in range(B)]
+
 
 def viterbi_launch(gb, E, offd, B, ug, ws_d, bp, costs, bc, be, po_d, ps, pf, pl, frame_label, banded=None):
     """srb_viterbi_banded when every graph of the batch is in banded form (banded=False forces the generic kernel;
@@ -287,6 +304,7 @@ def viterbi(E, off, gb, utt_graph=None, want_costs=False, want_path=True, frame_
     viterbi_launch(gb, E, offd, B, ug, ws_d, bp, costs, bc, be, po_d, ps, pf, pl, frame_label, banded=banded)
     res = ViterbiResult(bc, be, ps, pf, pl, po, costs, ws, bp)
     res.frame_label = frame_label
+    res.path_off_dev, res.utt_graph_dev, res.gb = po_d, ug, gb
     return res
 
 

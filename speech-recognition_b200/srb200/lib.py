@@ -29,6 +29,8 @@ SIGNATURES = {
                                 c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "srb_viterbi_graph": (c_int, [c_void_p, c_i64, c_void_p, c_i32] + [c_void_p] * 10 + [c_i32] + [c_void_p] * 11),
     "srb_viterbi_banded": (c_int, [c_void_p, c_i64, c_void_p, c_i32] + [c_void_p] * 16 + [c_i32] + [c_void_p] * 11),
+    "srb_path_words": (c_int, [c_void_p, c_void_p, c_void_p, c_i32, c_void_p, c_void_p, c_void_p, c_i32, c_void_p,
+                               c_void_p, c_void_p]),
     "srb_forward_backward": (c_int, [c_void_p, c_i64, c_void_p, c_i32] + [c_void_p] * 12 + [c_i32, c_i32] +
                              [c_void_p] * 5),
     "srb_stats_row": (c_int, [c_int]),

@@ -149,6 +149,26 @@ def viterbi(E, off, gb, utt_graph=None, want_costs=False, want_path=True, frame_
     res.ws_off = ws
     res.costs = torch.from_numpy(np.concatenate(costs_flat).astype(np.float32)) if want_costs else None
     res.paths = lambda: paths
+
+    def words(state_word, max_words):
+        # main.py:59-67 in numpy: forward order, drop consecutive duplicates, split at NES (-1), first state per piece
+        out = []
+        for u, pth in enumerate(paths):
+            gi = 0 if utt_graph is None else int(utt_graph[u])
+            sw = np.asarray(state_word)[int(gb.state_off[gi]):]
+            rows = pth[:, 0][::-1]
+            ws_, prev = [], None
+            for r in rows:
+                if prev is not None and r == prev:
+                    continue
+                if sw[r] >= 0 and (prev is None or sw[prev] < 0):
+                    ws_.append(int(sw[r]))
+                prev = r
+            assert len(ws_) <= max_words
+            out.append(ws_)
+        return out
+
+    res.words = words
     res.frame_label = None
     if frame_label is not None:
         frame_label[:len(fl)] = torch.from_numpy(fl)

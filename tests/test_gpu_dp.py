@@ -190,3 +190,60 @@ def test_banded_kernel_equals_generic_kernel(layers):
     assert np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3]) and np.array_equal(a[5], b[5])
     assert all(np.array_equal(x, y) for x, y in zip(a[4], b[4]))
     assert np.isfinite(a[2]).all()
+
+
+def test_path_words_kernel_matches_main_py_postprocessing():
+    """srb_path_words against the host form of main.py:59-67 (reverse, drop consecutive duplicates, split at the NES,
+    first state of every piece -> word) on random paths: runs longer than a warp, NES runs, paths that start or end in
+    a NES, empty paths, and the count of a string longer than max_words."""
+    import ctypes
+    import torch
+    from srb200 import lib as _l
+    rng = np.random.default_rng(17)
+    R, B, max_words = 23, 300, 6
+    state_word = np.where(rng.random(R) < 0.25, -1, rng.integers(0, 11, size=R)).astype(np.int32)
+    state_word[0] = -1
+    paths = []
+    for u in range(B):
+        n_runs = int(rng.integers(0, 9)) if u % 17 else 0
+        fwd = []
+        for _ in range(n_runs):
+            fwd += [int(rng.integers(0, R))] * int(rng.integers(1, 70))
+        if u == 1:                                                           # 10 words: more than max_words
+            emitting = int(np.nonzero(state_word >= 0)[0][0])
+            fwd = ([0] * 3 + [emitting] * 40) * 10
+        paths.append(np.asarray(fwd[::-1], np.int32))                       # stored reversed, like decode.py:142-146
+    ln = np.array([len(p) for p in paths], np.int32)
+    off = np.zeros(B + 1, np.int64)
+    np.cumsum(ln + 3, out=off[1:])                                          # slack between paths, like the decoder's layout
+    flat = np.full(int(off[-1]), -7, np.int32)
+    for u, p in enumerate(paths):
+        flat[off[u]:off[u] + len(p)] = p
+    want = []
+    for p in paths:
+        rows = p[::-1]
+        if rows.size:
+            rows = rows[np.concatenate([[True], rows[1:] != rows[:-1]])]
+        ws, found = [], False
+        for r in rows:                                                       # split_result of main.py:38-52
+            if state_word[r] >= 0:
+                if not found:
+                    ws.append(int(state_word[r]))
+                    found = True
+            else:
+                found = False
+        want.append(ws)
+    dev = "cuda"
+    t = lambda a: torch.from_numpy(a).to(dev)
+    words = torch.full((B, max_words), -5, dtype=torch.int32, device=dev)
+    nw = torch.empty(B, dtype=torch.int32, device=dev)
+    gso, d_flat, d_off, d_ln, d_sw = t(np.array([0, R], np.int32)), t(flat), t(off), t(ln), t(state_word)   # kept alive
+    _l.check(_l.load().srb_path_words(_l.ptr(d_flat), _l.ptr(d_off), _l.ptr(d_ln), B, None, _l.ptr(gso),
+                                      _l.ptr(d_sw), max_words, _l.ptr(words), _l.ptr(nw), _l.stream_ptr()))
+    wn, nn = words.cpu().numpy(), nw.cpu().numpy()
+    assert any(len(w) > max_words for w in want) and any(len(w) == 0 for w in want)
+    for u in range(B):
+        assert nn[u] == len(want[u])
+        k = min(len(want[u]), max_words)
+        assert wn[u, :k].tolist() == want[u][:k]
+        assert (wn[u, k:] == -5).all()

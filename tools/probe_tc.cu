@@ -101,20 +101,26 @@ probe(const float *A, const float *B, float *Dss, float *Dts, long long *clk) {
     fence_before_sync();
     __syncthreads();
     fence_after_sync();
-    // ---- (4) cycles: 8 x 30 MMAs back to back, SS then TS, then TS at narrower N (B rows stay 224 apart)
-    for (int mode = 0; mode < 8; ++mode) {
+    // ---- (4) cycles per MMA, 240 back to back.  mode: 0 SS N=224, 1 TS N=224, 2-7 TS at narrower N (B rows stay 224
+    //      apart), 8-10 SS at N = 112 / 64 / 32, 11 TS N=32 alternating two accumulators, 12 SS N=32 alternating two
+    for (int mode = 0; mode < 13; ++mode) {
         long long t0 = 0;
-        const int nn = mode < 2 ? N : (mode == 2 ? 112 : mode == 3 ? 64 : mode == 4 ? 32 : mode == 5 ? 160 : mode == 6 ? 128 : 16);
+        const int nn_tab[13] = {N, N, 112, 64, 32, 160, 128, 16, 112, 64, 32, 32, 32};
+        const int nn = nn_tab[mode];
+        const bool ss = mode == 0 || (mode >= 8 && mode <= 10) || mode == 12;
+        const bool two = mode >= 11;
         const uint32_t idn = idesc_tf32(M, nn);
         if (t == 0) {
             t0 = clock64();
+            int flip = 0;
             for (int rep = 0; rep < 8; ++rep)
                 for (int kk = 0; kk < K / 8; ++kk) {
                     const uint64_t dah = smem_desc(aH + kk * 2 * M * 16, M * 16, 128);
                     const uint64_t dbh = smem_desc(bH + kk * 2 * N * 16, N * 16, 128);
                     for (int j = 0; j < 3; ++j) {
-                        if (mode == 0) mma_tf32_ss(tb + TM_D, dah, dbh, idn, true);
-                        else mma_tf32_ts(tb + TM_D, tb + TM_AH + kk * 8, dbh, idn, true);
+                        const uint32_t dcol = tb + TM_D + (two ? 64 * (flip ^= 1) : 0);
+                        if (ss) mma_tf32_ss(dcol, dah, dbh, idn, true);
+                        else mma_tf32_ts(dcol, tb + TM_AH + kk * 8, dbh, idn, true);
                     }
                 }
             mma_commit(&bar);
@@ -137,7 +143,7 @@ static void run(const char *name, const std::vector<float> &A, const std::vector
     cudaMalloc(&dB, B.size() * 4);
     cudaMalloc(&dS, M * N * 4);
     cudaMalloc(&dT, M * N * 4);
-    cudaMalloc(&dC, 64);
+    cudaMalloc(&dC, 128);
     cudaMemcpy(dA, A.data(), A.size() * 4, cudaMemcpyHostToDevice);
     cudaMemcpy(dB, B.data(), B.size() * 4, cudaMemcpyHostToDevice);
     cudaMemset(dS, 0xff, M * N * 4);
@@ -149,10 +155,10 @@ static void run(const char *name, const std::vector<float> &A, const std::vector
     printf("[%s] kernel: %s\n", name, cudaGetErrorString(e));
     if (e != cudaSuccess) exit(1);
     std::vector<float> S(M * N), T(M * N);
-    long long clk[8];
+    long long clk[16];
     cudaMemcpy(S.data(), dS, M * N * 4, cudaMemcpyDeviceToHost);
     cudaMemcpy(T.data(), dT, M * N * 4, cudaMemcpyDeviceToHost);
-    cudaMemcpy(clk, dC, 64, cudaMemcpyDeviceToHost);
+    cudaMemcpy(clk, dC, 104, cudaMemcpyDeviceToHost);
     double es = 0, et = 0, mag = 0, e32 = 0;
     int bad_s = 0, bad_t = 0;
     for (int r = 0; r < M; ++r)
@@ -177,6 +183,8 @@ static void run(const char *name, const std::vector<float> &A, const std::vector
            S[5 * N + 7], T[5 * N + 7], clk[0], clk[0] / 240.0, clk[1], clk[1] / 240.0);
     printf("[%s] TS clk/MMA at N=112: %.1f  N=64: %.1f  N=32: %.1f  N=160: %.1f  N=128: %.1f  N=16: %.1f\n", name, clk[2] / 240.0,
            clk[3] / 240.0, clk[4] / 240.0, clk[5] / 240.0, clk[6] / 240.0, clk[7] / 240.0);
+    printf("[%s] SS clk/MMA at N=112: %.1f  N=64: %.1f  N=32: %.1f ; two accumulators alternating at N=32: TS %.1f  SS %.1f\n", name,
+           clk[8] / 240.0, clk[9] / 240.0, clk[10] / 240.0, clk[11] / 240.0, clk[12] / 240.0);
     cudaFree(dA); cudaFree(dB); cudaFree(dS); cudaFree(dT); cudaFree(dC);
 }
 
