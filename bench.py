@@ -61,7 +61,7 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--workload", default=os.environ.get("SRB_WORKLOAD", "em"), choices=["decode", "em", "connected", "stress", "fb"])
+    ap.add_argument("--workload", default=os.environ.get("SRB_WORKLOAD", "em"), choices=["decode", "em", "connected", "stress", "fb", "frontend"])
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--utts", type=int, default=100_000, help="utterances per GPU (100 frames each)")
     ap.add_argument("--frames", type=int, default=100)
@@ -504,7 +504,7 @@ def run_ours(args):
     peak_fma = max(engine.fma_peak(True, 8192) for _ in range(3))      # FMA/s, measured now on this GPU
     ctx = {"torch": torch, "dist": dist, "engine": engine, "pm": pm, "trans": trans, "models": models, "base": base,
            "world": world, "local": local, "rank": rank, "peak_fma": peak_fma, "lib": lib_}
-    extra = {"connected": bench_connected, "stress": bench_stress, "fb": bench_fb}
+    extra = {"connected": bench_connected, "stress": bench_stress, "fb": bench_fb, "frontend": bench_frontend}
     if args.workload in extra:
         # parity-test configurations of BASELINE.json (configs[2..4]) as optional device-resident sub-benchmarks
         line = extra[args.workload](args, ctx)
@@ -547,6 +547,57 @@ def run_ours(args):
         emit(line)
     if world > 1:
         dist.destroy_process_group()
+
+
+def bench_frontend(args, ctx):
+    """SURVEY 8 f3 ("next" row): MFCC front-end, 1 s utterances at 16 kHz -> standardised [100, 39] features
+    (srb_mfcc + srb_delta_standardize).  value: samples resident in HBM; e2e: host int16 arrays in, features out."""
+    torch, dist, world = ctx["torch"], ctx["dist"], ctx["world"]
+    from srb200.frontend import MfccFrontEnd
+    B = min(args.utts, 5000)
+    rng = np.random.default_rng(7 + ctx["rank"])
+    t = np.arange(16000) / 16000.0
+    sigs = [(8000 * np.sin(2 * np.pi * rng.uniform(100, 400) * t * (1 + 0.3 * t)) + 400 * rng.normal(size=16000)).astype(np.int16)
+            for _ in range(B)]
+    fe = MfccFrontEnd()
+    st = fe.stage(sigs)
+    out = fe.run(st)
+    sampler = ClockSampler(ctx["local"])
+    sampler.start()
+    total_ms, per = timed_steps(lambda: fe.run(st, out=out), args.steps, args.warmup, torch, dist, world)
+    clocks = sampler.stop()
+    F = st["F"]
+    kern_ms = float(np.mean(per))
+    # algorithmic bytes per frame: 160 new samples in, 13 cepstra out and back in, 39 features out, standardisation
+    # re-reads them twice and rewrites once (L2-resident per utterance)
+    bytes_pf = 160 * 4 + 13 * 4 * 2 + 39 * 4
+    gbs = bytes_pf * F / (kern_ms * 1e-3) / 1e9
+    pk = peaks()
+    e2e_ms, _ = timed_steps(lambda: fe.features(sigs)["features"].cpu(), max(1, args.steps // 3), 1, torch, dist, world)
+    from oracle import feature_oracle as fo
+    t0 = time.perf_counter()
+    n_cpu = 200
+    for s in sigs[:n_cpu]:
+        fo.load_features(s)
+    cpu_s = time.perf_counter() - t0
+    return {"metric": "MFCC feature frames/s (pre-emphasis, FFT-512, 40 mel filters, DCT, deltas, standardisation)",
+            "value": world * F * args.steps / (total_ms * 1e-3), "unit": "frames/s", "ms_per_step": total_ms / args.steps,
+            "gpu_launches": 2 * args.steps,
+            "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk.get("hbm_gbs"), "unit": "GB/s",
+                         "frac": gbs / pk.get("hbm_gbs"), "traffic": None, "kernel": "mfcc_kernel", "kernel_ms": kern_ms,
+                         "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "source" not in pk else "fallback",
+                         "algorithmic": f"{bytes_pf} B/frame; the kernel is bound by the shared-memory FFT (one warp "
+                                        f"per frame, 9 radix-2 stages), not by HBM"},
+            "clocks": clocks,
+            "e2e": {"value": world * F * max(1, args.steps // 3) / (e2e_ms * 1e-3), "unit": "frames/s",
+                    "h2d_bytes_per_step": int(st["sig"].numel() * 2), "d2h_bytes_per_step": int(F * 39 * 4),
+                    "api": "srb200.frontend.MfccFrontEnd.features (list of host int16 sample arrays in, features out; "
+                           "includes the host-side concatenation of the arrays)"},
+            "cpu_baseline": {"value": n_cpu * 100 / cpu_s, "unit": "frames/s", "cores": 1, "kind": "port",
+                             "sample": f"{n_cpu} utterances of 1 s, oracle/feature_oracle.py (numpy float64), "
+                                       f"{cpu_s * 1e3:.0f} ms"},
+            "_workload": f"frontend: {B} utterances x 16000 samples (1 s at 16 kHz) per GPU -> 100 frames x 39 each",
+            "_frames": F}
 
 
 def peaks():

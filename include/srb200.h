@@ -243,6 +243,23 @@ int srb_em_isolated(const float *X, int64_t N, int D, const int32_t *utt_off, in
  * *ms_out (host pointer) plus the FMA count (host pointer).  packed != 0 uses fma.rn.f32x2. */
 int srb_fma_peak(int packed, int iters, float *ms_out, double *fma_count_out, void *stream);
 
+/* ---- MFCC front-end: the step right before the scoring path ----------------------------------------
+ * Replaces sr/feature/feature.py:7-88 and core.py:13-31 for a batch of 16 kHz utterances.
+ *   srb_mfcc_num_frames(n, sr)   frames of an n-sample utterance: ceil(n / 160) (feature.py:7-16; 0 for sr != 16000)
+ *   srb_mfcc                     signal float[sum n] (the int16 samples as floats), sig_off int64[B+1], frame_off
+ *                                int64[B+1] (prefix sums of srb_mfcc_num_frames), F = frame_off[B];
+ *                                fb_w float[40,257] + fb_range int32[40,2] = the mel filter bank of feature.py:57-76
+ *                                built by the host (dense weights, [first, last) non-zero bin per filter);
+ *                                fbank float[F,40] (optional, log10 energies), mfcc float[F,13] (DCT-II ortho, c 1..13)
+ *   srb_delta_standardize        mfcc float[F,13] -> features float[F,39] = [c, delta, delta-delta] (core.py:13-22),
+ *                                standardised per utterance and dimension when standardize != 0 (feature.py:85-88);
+ *                                utterances need >= 2 frames (the reference indexes feat[1]) */
+int64_t srb_mfcc_num_frames(int64_t nsamples, int sample_rate);
+int srb_mfcc(const float *signal, const int64_t *sig_off, const int64_t *frame_off, int32_t B, int64_t F, int sample_rate,
+             const float *fb_w, const int32_t *fb_range, float *fbank, float *mfcc, void *stream);
+int srb_delta_standardize(const float *mfcc, const int64_t *frame_off, int32_t B, float *features, int standardize,
+                          void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,2 +1,3 @@
-"""`sr` namespace of the mirror: re-exports what the reference's sr/__init__.py:2 takes from sr.recognition."""
+"""`sr` namespace of the mirror: the re-exports of the reference's sr/__init__.py:1-2."""
+from .core import delta_feature, load_wav_as_mfcc, make_HMM, train, test, aurora_continuous_train  # noqa: F401
 from .recognition import HMMState, HMM, decode_hmm_states, GMM, build_state_sequences, NES  # noqa: F401

@@ -29,6 +29,10 @@ SIGNATURES = {
                                 c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "srb_viterbi_graph": (c_int, [c_void_p, c_i64, c_void_p, c_i32] + [c_void_p] * 10 + [c_i32] + [c_void_p] * 11),
     "srb_viterbi_banded": (c_int, [c_void_p, c_i64, c_void_p, c_i32] + [c_void_p] * 16 + [c_i32] + [c_void_p] * 11),
+    "srb_mfcc_num_frames": (c_i64, [c_i64, c_int]),
+    "srb_mfcc": (c_int, [c_void_p, c_void_p, c_void_p, c_i32, c_i64, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                         c_void_p]),
+    "srb_delta_standardize": (c_int, [c_void_p, c_void_p, c_i32, c_void_p, c_int, c_void_p]),
     "srb_path_words": (c_int, [c_void_p, c_void_p, c_void_p, c_i32, c_void_p, c_void_p, c_void_p, c_i32, c_void_p,
                                c_void_p, c_void_p]),
     "srb_forward_backward": (c_int, [c_void_p, c_i64, c_void_p, c_i32] + [c_void_p] * 12 + [c_i32, c_i32] +

@@ -202,3 +202,25 @@ def test_forward_backward_identities(golden):
         nlz_s, a_s, _, _ = orc.forward_backward(E * s, np.where(np.isinf(m[3]), np.inf, m[3] * s))
         f = np.isfinite(costs.T)
         np.testing.assert_allclose(a_s[f] / s, costs.T[f], rtol=2e-3)
+
+
+def test_feature_oracle_matches_reference_front_end():
+    """oracle/feature_oracle.py against the frozen outputs of the reference's mfcc_features / load_wav_as_mfcc1
+    (tests/golden/make_golden_feature.py), and the product's host-built mel filter bank against the oracle's."""
+    import os
+    import sys
+    from oracle import feature_oracle as fo
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_feature.npz"))
+    for i in range(int(g["n"])):
+        fb, mf = fo.mfcc_features(g[f"sig{i}"])
+        np.testing.assert_allclose(fb, g[f"fbank{i}"], rtol=0, atol=1e-12)
+        np.testing.assert_allclose(mf, g[f"mfcc{i}"], rtol=0, atol=1e-12)
+        np.testing.assert_allclose(fo.load_features(g[f"sig{i}"]), g[f"feat{i}"], rtol=1e-9, atol=1e-9)
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(__file__)), "speech-recognition_b200"))
+    from srb200.frontend import mel_filterbank
+    w, rng = mel_filterbank(16000)
+    ref, _ = fo.mel_filterbank(16000)
+    np.testing.assert_allclose(w, ref.astype(np.float32), rtol=0, atol=0)
+    for m in range(40):
+        nz = np.nonzero(ref[m])[0]
+        assert rng[m, 0] <= nz.min() and nz.max() < rng[m, 1]
