@@ -382,9 +382,17 @@ def bench_connected(args, ctx):
     E = torch.empty((N, pm.R), dtype=torch.float32, device="cuda")
     L_ = ctx["lib"]
 
+    use_tc = pm.scorer_tensor_core_ok() and not args.ffma
+
+    def score():
+        if use_tc:
+            engine.gmm_score_tc(Xd, pm, E)
+        else:
+            L_.check(L_.load().srb_gmm_score(L_.ptr(Xd), N, pm.D, L_.ptr(pm.ab), L_.ptr(pm.c), L_.ptr(pm.shift), pm.R,
+                                             pm.Mp, L_.ptr(E), pm.R, None, None, None, L_.stream_ptr()))
+
     def step():
-        L_.check(L_.load().srb_gmm_score(L_.ptr(Xd), N, pm.D, L_.ptr(pm.ab), L_.ptr(pm.c), L_.ptr(pm.shift), pm.R,
-                                         pm.Mp, L_.ptr(E), pm.R, None, None, None, L_.stream_ptr()))
+        score()
         plan.run(E)
 
     sampler = ClockSampler(ctx["local"])
@@ -397,14 +405,15 @@ def bench_connected(args, ctx):
     acc = float((word_of[lab[:, centres]] == strings).mean())
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
     ev[0].record()
-    L_.check(L_.load().srb_gmm_score(L_.ptr(Xd), N, pm.D, L_.ptr(pm.ab), L_.ptr(pm.c), L_.ptr(pm.shift), pm.R, pm.Mp,
-                                     L_.ptr(E), pm.R, None, None, None, L_.stream_ptr()))
+    score()
     ev[1].record()
     plan.run(E)
     ev[2].record()
     torch.cuda.synchronize()
     ms = float(np.mean(per))
-    roof = _roof_fma(FMA_PER_FRAME_DECODE, N, ms, ctx["peak_fma"], "score_kernel<39> + viterbi_graph_kernel",
+    roof = _roof_fma(FMA_PER_FRAME_DECODE, N, ms, ctx["peak_fma"],
+                     ("classify_tc_kernel<39> (scorer mode, tcgen05 3xTF32)" if use_tc else "score_kernel<39>") +
+                     " + viterbi_graph_kernel",
                      "17160 FMA/frame scoring (55 tied states x 4 x 2*39); DP 847 arcs + 393 states per frame; "
                      "393 B/frame back-pointers")
     roof["phase_ms"] = {"score": ev[0].elapsed_time(ev[1]), "viterbi": ev[1].elapsed_time(ev[2])}

@@ -91,6 +91,12 @@ int64_t srb_tc_model_floats(int R, int Mp, int D);
 int srb_tc_set_timeline(int64_t *device_buf);
 int srb_pack_model_tc(const float *ab, const float *c, int R, int Mp, int D, float *tcb, void *stream);
 int srb_classify_tc_supported(int D, int W, int S, int Mp);
+/* The scorer alone on the same kernel: E[n, r] = states[r].evaluate(X[n]) like srb_gmm_score (E only).  chunk_off
+ * int32[nchunks+1] is any partition of the N frames into chunks of >= 1 frame (e.g. the utterance offsets, or steps of
+ * 32 frames); it only drives the split of the work over CTAs and sub-streams. */
+int srb_gmm_score_tc_supported(int D, int R, int Mp);
+int srb_gmm_score_tc(const float *X, int64_t N, int D, const float *tcb, const float *shift, int R, int Mp,
+                     const int32_t *chunk_off, int32_t nchunks, float *E, int64_t ldE, void *stream);
 int srb_classify_tc(const float *X, const int32_t *utt_off, int32_t B, int64_t N, int D, const float *tcb,
                     const float *shift, int W, int S, int Mp, const float *trans, float *final,
                     int32_t *label, void *stream);

@@ -93,7 +93,8 @@ __global__ void __launch_bounds__(TC_NT, 1)
 classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off, int B, int64_t N,
                    const uint32_t *__restrict__ tcb, const float *__restrict__ shift, int W,
                    int S, int NP, const float *__restrict__ trans, float *__restrict__ final_cost,
-                   int32_t *__restrict__ label, long long *__restrict__ timeline) {
+                   int32_t *__restrict__ label, float *__restrict__ E_out, int64_t ldE,
+                   long long *__restrict__ timeline) {
     constexpr int KP = tc_kp(D), SMAX = SRB_DP_MAX_STATES;
     extern __shared__ __align__(128) float smem[];
     __shared__ uint64_t bar[4];
@@ -101,14 +102,15 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
     __shared__ uint32_t tslot;
     __shared__ int band_flag;
     const int R = W * S, ES = R | 1;
+    const int Wc = E_out ? 0 : W;                            // scorer mode (E_out): no Viterbi tables, the "utterances" are chunks
     float *shift_s = smem;                                   // 64
     float *tr_s = shift_s + 64;                              // W*SMAX*SMAX   tr_s[w][i][j] = cost j->i
-    float *carry = tr_s + W * SMAX * SMAX;                   // TC_SUB*2*W*SMAX
-    uint32_t *Bh = reinterpret_cast<uint32_t *>(carry + TC_SUB * 2 * W * SMAX);   // KP*NP, 16-byte aligned
+    float *carry = tr_s + Wc * SMAX * SMAX;                  // TC_SUB*2*W*SMAX
+    uint32_t *Bh = reinterpret_cast<uint32_t *>(carry + TC_SUB * 2 * Wc * SMAX);   // KP*NP, 16-byte aligned
     uint32_t *Bl = Bh + KP * NP;
     float *xs = reinterpret_cast<float *>(Bl + KP * NP);     // TC_SUB * TC_XSQ
     float *fin_s = xs + TC_SUB * TC_XSQ;                     // TC_SUB * TC_FIN * W
-    float *Es = fin_s + TC_SUB * TC_FIN * W;                 // TC_CHUNK * ES
+    float *Es = fin_s + TC_SUB * TC_FIN * Wc;                // TC_CHUNK * ES
     const int tid = threadIdx.x, wq = tid >> 5;
     // diagnostics (srb_tc_set_timeline): CTA 0 stamps clock64 at its pipeline events of the first TC_TL_TILES tiles
     const bool tl_on = timeline != nullptr && blockIdx.x == 0 && (tid & 31) == 0;
@@ -131,7 +133,7 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
     if (tid == 0) band_flag = 1;
     if (tid < D) shift_s[tid] = shift[tid];
     __syncthreads();
-    for (int i = tid; i < W * SMAX * SMAX; i += TC_NT) {
+    for (int i = tid; i < Wc * SMAX * SMAX; i += TC_NT) {
         const int w = i / (SMAX * SMAX), r = (i / SMAX) % SMAX, o = i % SMAX;
         float v = CUDART_INF_F;
         if (r < S && o < S) v = trans[((size_t)w * S + r) * S + o];
@@ -205,7 +207,7 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
         const int sue = sub_u[q + 1];
         const int64_t sbeg = off[sub_u[q]], send = off[sue];
         int ufirst = sub_u[q], par = 0;
-        float *carry_q = carry + (size_t)q * 2 * W * SMAX;
+        float *carry_q = carry + (size_t)q * 2 * Wc * SMAX;
         for (int j = 0; j <= ntile; ++j) {
             if (j < ntile) {
                 // ---- A operand: thread = frame = TMEM lane
@@ -247,7 +249,15 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
                 const int64_t cf0 = sbeg + (int64_t)t * TC_SF;
                 named_sync(TC_BAR_FULL + (t & 1), TC_MAIN + TC_DP);   // costs of tile t are in ring slot t & 1
                 if (q == 0) TC_STAMP(t, 7);
-                if (cf0 < send) {
+                if (cf0 < send && E_out) {
+                    // scorer mode: the tile's cost rows of this sub-stream go to E[frame, 0..R) (coalesced along a row)
+                    const int rows = (int)min((int64_t)TC_SF, send - cf0);
+                    const float *src = Es + (size_t)((t & 1) * TC_M + q * TC_SF) * ES;
+                    for (int i = lane; i < rows * R; i += 32) {
+                        const int r = i / R, c = i - r * R;
+                        E_out[(cf0 + r) * ldE + c] = src[r * ES + c];
+                    }
+                } else if (cf0 < send) {
                     classify_dp_chunk<32, -1>(Es + (size_t)((t & 1) * TC_M + q * TC_SF) * ES, ES, off, sue, ufirst, cf0,
                                               min(send, cf0 + (int64_t)TC_SF), W, S, tr_s, carry_q, par, banded,
                                               final_cost, label, lane, fin_s + (size_t)q * TC_FIN * W, TC_FIN);
@@ -345,10 +355,10 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
 #undef TC_STAMP
 }
 
-static size_t classify_tc_smem_bytes(int W, int S, int NP, int D) {
-    const int R = W * S, KP = tc_kp(D);
-    return 4 * (64 + (size_t)W * SRB_DP_MAX_STATES * SRB_DP_MAX_STATES + TC_SUB * 2 * (size_t)W * SRB_DP_MAX_STATES +
-                2 * (size_t)KP * NP + (size_t)TC_SUB * TC_XSQ + (size_t)TC_SUB * TC_FIN * W + (size_t)TC_CHUNK * (R | 1));
+static size_t classify_tc_smem_bytes(int W, int S, int NP, int D, bool scorer = false) {
+    const int R = W * S, KP = tc_kp(D), Wc = scorer ? 0 : W;
+    return 4 * (64 + (size_t)Wc * SRB_DP_MAX_STATES * SRB_DP_MAX_STATES + TC_SUB * 2 * (size_t)Wc * SRB_DP_MAX_STATES +
+                2 * (size_t)KP * NP + (size_t)TC_SUB * TC_XSQ + (size_t)TC_SUB * TC_FIN * Wc + (size_t)TC_CHUNK * (R | 1));
 }
 
 }  // namespace srb
@@ -409,7 +419,40 @@ int srb_classify_tc(const float *X, const int32_t *utt_off, int32_t B, int64_t N
     const int grid = (int)(want < sms ? want : sms);
     SRB_CUDA(cudaFuncSetAttribute(classify_tc_kernel<39>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     classify_tc_kernel<39><<<grid, TC_NT, bytes, (cudaStream_t)stream>>>(
-        X, utt_off, B, N, reinterpret_cast<const uint32_t *>(tcb), shift, W, S, NP, trans, final_cost, label, g_tc_timeline);
+        X, utt_off, B, N, reinterpret_cast<const uint32_t *>(tcb), shift, W, S, NP, trans, final_cost, label, nullptr, 0, g_tc_timeline);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+int srb_gmm_score_tc_supported(int D, int R, int Mp) {
+    if (D != 39 || Mp != TC_MP || R <= 0) return 0;
+    const int NP = tc_np(R, Mp);
+    if (NP > TC_NMAX) return 0;
+    const int cap = smem_optin();
+    return cap > 0 && classify_tc_smem_bytes(R, 1, NP, D, true) + 64 <= (size_t)cap;
+}
+
+int srb_gmm_score_tc(const float *X, int64_t N, int D, const float *tcb, const float *shift, int R, int Mp,
+                     const int32_t *chunk_off, int32_t nchunks, float *E, int64_t ldE, void *stream) {
+    SRB_REQUIRE(N >= 0 && nchunks >= 0, SRB_EINVAL, "srb_gmm_score_tc: bad sizes");
+    if (N == 0 || nchunks == 0) return SRB_OK;
+    SRB_REQUIRE(X && tcb && shift && chunk_off && E, SRB_EINVAL, "srb_gmm_score_tc: null pointer");
+    SRB_REQUIRE(ldE >= R, SRB_EINVAL, "srb_gmm_score_tc: ldE < R");
+    SRB_REQUIRE(srb_gmm_score_tc_supported(D, R, Mp), SRB_EUNSUPPORTED,
+                "srb_gmm_score_tc: D=%d, %d states x %d Gaussians not covered by the tensor-core scorer (D = 39, Mp = 4, "
+                "at most 57 states = 228 Gaussians); use srb_gmm_score", D, R, Mp);
+    SRB_REQUIRE(((uintptr_t)X & 15) == 0 && ((uintptr_t)tcb & 15) == 0, SRB_EINVAL,
+                "srb_gmm_score_tc: X and tcb must be 16-byte aligned");
+    const int sms = sm_count();
+    SRB_REQUIRE(sms > 0, SRB_ENODEVICE, "no CUDA device");
+    const int NP = tc_np(R, Mp);
+    const size_t bytes = classify_tc_smem_bytes(R, 1, NP, D, true);
+    const int64_t want = (N + TC_CHUNK - 1) / TC_CHUNK;
+    const int grid = (int)(want < sms ? want : sms);
+    SRB_CUDA(cudaFuncSetAttribute(classify_tc_kernel<39>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    classify_tc_kernel<39><<<grid, TC_NT, bytes, (cudaStream_t)stream>>>(
+        X, chunk_off, nchunks, N, reinterpret_cast<const uint32_t *>(tcb), shift, R, 1, NP, nullptr, nullptr, nullptr, E, ldE,
+        nullptr);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }

@@ -60,6 +60,11 @@ class PackedModel:
         """True when srb_classify_tc covers this model (D = 39, 4 Gaussians per state, <= 256 Gaussians)."""
         return self.tcb is not None and bool(_l.load().srb_classify_tc_supported(self.D, W, S, self.Mp))
 
+    def scorer_tensor_core_ok(self):
+        """True when srb_gmm_score_tc covers this model (D = 39, 4 Gaussians per state, <= 57 states = 228 Gaussians:
+        the packed model and the cost ring share 227 KB of shared memory)."""
+        return self.tcb is not None and bool(_l.load().srb_gmm_score_tc_supported(self.D, self.R, self.Mp))
+
     @classmethod
     def from_words(cls, word_models, shift=None):
         """word_models: list of (mu[S,M,D], cov[S,M,D], w[S,M], trans[S,S]) -> (PackedModel, trans[W,S,S] fp32)."""
@@ -85,13 +90,53 @@ def as_offsets(off):
     return off.to(device(), torch.int32).contiguous()
 
 
-def gmm_score(X, pm, want_E=True, want_best=False, want_comp=False):
-    """K1.  -> dict(E[N,R], best_cost[N], best_state[N], comp[N,R,Mp]) for the requested outputs."""
+TC_SCORE_MIN_FRAMES = 4096      # below this the FFMA scorer's launch is cheaper than staging the packed model per CTA
+_chunk_off_cache = {}
+
+
+def score_chunk_offsets(N, dev):
+    """int32[ceil(N/32)+1] partition of N frames into 32-frame chunks (srb_gmm_score_tc's work split), cached per N."""
+    key = (int(N), str(dev))
+    t = _chunk_off_cache.get(key)
+    if t is None:
+        if len(_chunk_off_cache) > 16:
+            _chunk_off_cache.clear()
+        t = torch.arange(0, N + 32, 32, dtype=torch.int64, device=dev).clamp_(max=N).to(torch.int32)
+        if t.numel() >= 2 and int(t[-1]) == int(t[-2]):
+            t = t[:-1].contiguous()
+        _chunk_off_cache[key] = t
+    return t
+
+
+def gmm_score_tc(X, pm, E=None):
+    """K1 on the tensor cores (3xTF32, srb_gmm_score_tc): E[N,R] only."""
+    X = as_frames(X)
+    N = X.shape[0]
+    if E is None:
+        E = torch.empty((N, pm.R), dtype=torch.float32, device=X.device)
+    assert E.is_cuda and E.dtype == torch.float32 and tuple(E.shape) == (N, pm.R) and (N == 0 or E.stride(1) == 1)
+    co = score_chunk_offsets(N, X.device)
+    _l.check(_l.load().srb_gmm_score_tc(_l.ptr(X), N, pm.D, _l.ptr(pm.tcb), _l.ptr(pm.shift), pm.R, pm.Mp, _l.ptr(co),
+                                        co.numel() - 1, E.data_ptr(), E.stride(0) if N else pm.R, _l.stream_ptr()))
+    return E
+
+
+def gmm_score(X, pm, want_E=True, want_best=False, want_comp=False, tensor=None):
+    """K1.  -> dict(E[N,R], best_cost[N], best_state[N], comp[N,R,Mp]) for the requested outputs.
+    tensor: None = the tcgen05 (3xTF32) scorer for E-only requests of >= TC_SCORE_MIN_FRAMES frames when it covers
+    the model, else the FFMA scorer; True / False force one."""
     X = as_frames(X)
     N = X.shape[0]
     assert X.shape[1] == pm.D
     dev = X.device
     out = {}
+    e_only = want_E and not want_best and not want_comp
+    if tensor is None:
+        tensor = e_only and N >= TC_SCORE_MIN_FRAMES and pm.scorer_tensor_core_ok()
+    if tensor:
+        if not e_only:
+            raise ValueError("the tensor-core scorer returns E only")
+        return {"E": gmm_score_tc(X, pm)}
     E = torch.empty((N, pm.R), dtype=torch.float32, device=dev) if want_E else None
     bc = torch.empty(N, dtype=torch.float32, device=dev) if want_best else None
     bs = torch.empty(N, dtype=torch.int32, device=dev) if want_best else None

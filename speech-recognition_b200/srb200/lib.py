@@ -24,6 +24,9 @@ SIGNATURES = {
     "srb_tc_model_floats": (c_i64, [c_int, c_int, c_int]),
     "srb_tc_set_timeline": (c_int, [c_void_p]),
     "srb_pack_model_tc": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "srb_gmm_score_tc_supported": (c_int, [c_int, c_int, c_int]),
+    "srb_gmm_score_tc": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_void_p, c_int, c_int, c_void_p, c_i32, c_void_p,
+                                 c_i64, c_void_p]),
     "srb_classify_tc_supported": (c_int, [c_int, c_int, c_int, c_int]),
     "srb_classify_tc": (c_int, [c_void_p, c_void_p, c_i32, c_i64, c_int, c_void_p, c_void_p, c_int, c_int,
                                 c_int, c_void_p, c_void_p, c_void_p, c_void_p]),

@@ -56,6 +56,48 @@ def test_gmm_score_reference_linear_domain_and_unnormalised_weights(eng, golden)
     np.testing.assert_allclose(out["comp"].cpu().numpy()[:, 0, :4][ok], np.log(comps[ok]), rtol=RTOL, atol=1e-3)
 
 
+@pytest.mark.parametrize("W,S,B,T", [(11, 5, 13, 97), (3, 7, 300, 41), (1, 1, 1, 5), (57, 1, 9, 33), (11, 5, 700, 100)])
+def test_gmm_score_tensor_core_matches_oracle(eng, W, S, B, T):
+    """srb_gmm_score_tc (the tcgen05 classifier's scorer with the cost rows streamed out) against the oracle and the
+    FFMA scorer: ragged last chunk, one frame per lane quarter, several CTAs, a strided E."""
+    import torch
+    from srb200 import synth
+    models, base = _models(11, W=W, S=S, M=4)
+    X, off, _ = synth.make_utterances(12, base, B, T=T)
+    pm, _ = eng.PackedModel.from_words(models)
+    assert pm.scorer_tensor_core_ok()
+    E = eng.gmm_score(X, pm, tensor=True)["E"].cpu().numpy()
+    Eo = orc.emissions(X.astype(np.float64), models, np.arange(W * S), log_domain=True)
+    np.testing.assert_allclose(E, Eo, rtol=RTOL)
+    Ef = eng.gmm_score(X, pm, tensor=False)["E"].cpu().numpy()
+    np.testing.assert_allclose(E, Ef, rtol=2e-5)
+    # strided output: only the R leading columns of each row are written
+    wide = torch.full((X.shape[0], W * S + 3), -7.0, dtype=torch.float32, device="cuda")
+    eng.gmm_score_tc(X, pm, wide[:, :W * S])
+    wide = wide.cpu().numpy()
+    assert np.array_equal(wide[:, :W * S], E) and np.all(wide[:, W * S:] == -7.0)
+    if X.shape[0] >= eng.TC_SCORE_MIN_FRAMES:     # the default route picks the tensor-core scorer here
+        assert np.array_equal(eng.gmm_score(X, pm)["E"].cpu().numpy(), E)
+    with pytest.raises(ValueError):
+        eng.gmm_score(X, pm, want_best=True, tensor=True)
+
+
+def test_gmm_score_tensor_core_unsupported_is_loud(eng):
+    import torch
+    from srb200 import lib as L
+    models, base = _models(5, W=3, S=4, M=8)                       # 8 Gaussians per state: not covered
+    pm, _ = eng.PackedModel.from_words(models)
+    assert not pm.scorer_tensor_core_ok()
+    assert L.load().srb_gmm_score_tc_supported(39, 58, 4) == 0     # packed model + cost ring > 227 KB of shared memory
+    assert L.load().srb_gmm_score_tc_supported(39, 57, 4) == 1
+    X = torch.zeros((64, 39), device="cuda")
+    co = torch.tensor([0, 32, 64], dtype=torch.int32, device="cuda")
+    E = torch.empty((64, 12), device="cuda")
+    rc = L.load().srb_gmm_score_tc(X.data_ptr(), 64, 39, pm.ab.data_ptr(), pm.shift.data_ptr(), 12, 8, co.data_ptr(), 2,
+                                   E.data_ptr(), 12, None)
+    assert rc != 0 and b"not covered" in L.load().srb_last_error_string()
+
+
 @pytest.mark.parametrize("M,S,W", [(4, 5, 11), (16, 8, 3), (2, 3, 4)])
 def test_gmm_score_multi_block_states(eng, M, S, W):
     from srb200 import synth
