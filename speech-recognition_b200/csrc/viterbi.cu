@@ -318,6 +318,213 @@ viterbi_banded_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *_
 }
 
 
+// ------------------------------------------------------------------------------------------------ K2, banded, one graph
+// The same three sweeps for a batch whose utterances all use ONE graph (connected-digit decoding, main.py:40-60): the
+// graph's tables are packed once per CTA into shared memory -- per state {a2, a1, a0, meta}, meta = the four 2-bit
+// back-pointer codes | entry flag << 8 | (emit + 1) << 9 (0: NES) -- next to the NES predecessor lists and the entry
+// list, so a state update is one 16-byte and three 4-byte shared loads, the emission gather and two stores instead of
+// seven table loads with 64-bit address arithmetic.  The NES sweep gives every NES a group of lanes (first minimum
+// kept across the group by (cost, position) order).  Outputs are bit-identical to viterbi_banded_kernel.
+constexpr int VB_NES_CAP = 64;    // NES whose descriptor sits in shared memory (more fall back to the tables in global)
+
+struct BandState { float a2, a1, a0; uint32_t meta; };
+struct BandEntry { int32_t r, nes; float cost; int32_t pad; };
+struct BandNes { int32_t n, p0, cnt, pad; };
+
+template <bool FIRST>
+__device__ __forceinline__ void banded_column(const BandState *tab, const BandEntry *ent, const BandNes *nes,
+                                              const int32_t *pidx_s, const float *pcost_s, int pcap, const GraphBatch &G,
+                                              int R, int K, int Q, int L, const float *prev, float *cur, uint8_t *code_s,
+                                              const float *__restrict__ Erow, uint8_t *__restrict__ bpc, int lane) {
+    const float INF = CUDART_INF_F;
+    // ---- 1. emitting states from the previous column (prev[-2], prev[-1] are +inf pads)
+#pragma unroll 2
+    for (int r = lane; r < R; r += 32) {
+        const BandState t = tab[r];
+        const uint32_t meta = t.meta;
+        if ((meta >> 9) == 0) continue;                              // NES
+        const float t2 = prev[r - 2] + t.a2, t1 = prev[r - 1] + t.a1, t0 = prev[r] + t.a0;
+        float best = INF;
+        uint32_t code = 0;
+        if (t2 < best) { best = t2; code = meta & 3; }
+        if (t1 < best) { best = t1; code = (meta >> 2) & 3; }
+        if (t0 < best) { best = t0; code = (meta >> 4) & 3; }
+        const bool entry = (meta & 0x100) != 0;
+        float v = entry ? best : best + Erow[(meta >> 9) - 1];       // entry states get their emission in sweep 3
+        if (FIRST && r == 0) {                                       // decode.py:99-100
+            v = Erow[(meta >> 9) - 1];
+            code = 0;
+        }
+        cur[r] = v;
+        bpc[r] = (uint8_t)code;
+        if (entry) code_s[r] = (uint8_t)code;
+    }
+    __syncwarp();
+    // ---- 2. the non-emitting states: L lanes per NES, each scanning every L-th predecessor in list order
+    for (int k0 = 0; k0 < K; k0 += 32 / L) {
+        const int k = k0 + lane / L, sub = lane & (L - 1);
+        float best = INF;
+        int bj = 0x7fffffff, n = 0, cnt = 0;
+        if (k < K) {
+            int p0;
+            if (k < VB_NES_CAP) {
+                const BandNes d = nes[k];
+                n = d.n; p0 = d.p0; cnt = d.cnt;
+            } else {
+                n = G.nes_idx[k];
+                p0 = G.pred_ptr[n];
+                cnt = G.pred_ptr[n + 1] - p0;
+            }
+            for (int j = sub; j < cnt; j += L) {
+                const int jj = p0 + j;
+                const int o = jj < pcap ? pidx_s[jj] : G.pred_idx[jj];
+                const float cand = (jj < pcap ? pcost_s[jj] : G.pred_cost[jj]) + cur[o];
+                if (cand < best) {
+                    best = cand;
+                    bj = j;
+                }
+            }
+        }
+        for (int d = L >> 1; d; d >>= 1) {
+            const float ob = __shfl_xor_sync(0xffffffffu, best, d);
+            const int oj = __shfl_xor_sync(0xffffffffu, bj, d);
+            if (ob < best || (ob == best && oj < bj)) {
+                best = ob;
+                bj = oj;
+            }
+        }
+        if (k < K && sub == 0) {
+            if (FIRST && n == 0) {
+                cur[0] = 0.f;
+                bpc[0] = 0;
+            } else {
+                cur[n] = best;
+                bpc[n] = (uint8_t)(best < INF ? bj : 0);
+            }
+        }
+    }
+    __syncwarp();
+    // ---- 3. entry states: the NES arc competes with the band candidates (lower list position wins ties)
+    for (int i = lane; i < Q; i += 32) {
+        const BandEntry e = ent[i];
+        if (FIRST && e.r == 0) continue;
+        const uint32_t meta = tab[e.r].meta;
+        const float cand = e.cost + cur[e.nes];
+        const uint32_t cn = (meta >> 6) & 3;
+        float best = cur[e.r];
+        uint32_t code = code_s[e.r];
+        if (cand < best || (cand == best && cand < INF && cn < code)) {
+            best = cand;
+            code = cn;
+        }
+        cur[e.r] = best + Erow[(meta >> 9) - 1];
+        bpc[e.r] = (uint8_t)code;
+    }
+    __syncwarp();
+}
+
+__global__ void __launch_bounds__(VW * 32)
+viterbi_banded1_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *__restrict__ off, int B, GraphBatch G,
+                       BandForm F, int Rmax, const int64_t *__restrict__ bp_off, uint8_t *__restrict__ bp,
+                       float *__restrict__ costs_out, float *__restrict__ best_cost, int32_t *__restrict__ best_end,
+                       const int64_t *__restrict__ path_off, int32_t *__restrict__ path_state,
+                       int32_t *__restrict__ path_frame, int32_t *__restrict__ path_len,
+                       int32_t *__restrict__ frame_label) {
+    extern __shared__ __align__(16) unsigned char vb_sm[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, tid = threadIdx.x;
+    const int R = G.g_state_off[1] - G.g_state_off[0], K = G.g_nes_off[1] - G.g_nes_off[0];
+    const int Q = F.g_entry_off[1] - F.g_entry_off[0];
+    const int RP = (Rmax + 3) & ~3, pcap = RP;
+    BandState *tab = reinterpret_cast<BandState *>(vb_sm);                       // RP
+    BandEntry *ent = reinterpret_cast<BandEntry *>(tab + RP);                    // RP
+    BandNes *nes = reinterpret_cast<BandNes *>(ent + RP);                        // VB_NES_CAP
+    int32_t *pidx_s = reinterpret_cast<int32_t *>(nes + VB_NES_CAP);             // pcap
+    float *pcost_s = reinterpret_cast<float *>(pidx_s + pcap);                   // pcap
+    float *colbase = pcost_s + pcap;                                             // VW * 2 * (RP + 4)
+    uint8_t *codebase = reinterpret_cast<uint8_t *>(colbase + (size_t)VW * 2 * (RP + 4));   // VW * RP
+    const float INF = CUDART_INF_F;
+
+    for (int r = tid; r < R; r += VW * 32) {
+        const uint32_t cd = (uint32_t)F.codes[r];
+        const int em = G.emit[r];
+        BandState t;
+        t.a2 = F.band[r * 3 + 0];
+        t.a1 = F.band[r * 3 + 1];
+        t.a0 = F.band[r * 3 + 2];
+        t.meta = (cd & 3) | (((cd >> 8) & 3) << 2) | (((cd >> 16) & 3) << 4) | (((cd >> 24) & 3) << 6) |
+                 (F.entry_nes[r] >= 0 ? 0x100u : 0u) | ((uint32_t)(em + 1) << 9);
+        tab[r] = t;
+    }
+    for (int i = tid; i < Q; i += VW * 32) {
+        const int r = F.entry_state[i];
+        BandEntry e;
+        e.r = r;
+        e.nes = F.entry_nes[r];
+        e.cost = F.entry_cost[r];
+        e.pad = 0;
+        ent[i] = e;
+    }
+    for (int k = tid; k < min(K, VB_NES_CAP); k += VW * 32) {
+        const int n = G.nes_idx[k];
+        BandNes d;
+        d.n = n;
+        d.p0 = G.pred_ptr[n];
+        d.cnt = G.pred_ptr[n + 1] - d.p0;
+        d.pad = 0;
+        nes[k] = d;
+    }
+    for (int j = tid; j < min(G.pred_ptr[R], pcap); j += VW * 32) {
+        pidx_s[j] = G.pred_idx[j];
+        pcost_s[j] = G.pred_cost[j];
+    }
+    __syncthreads();
+    int L = 1;                                                       // lanes per NES in sweep 2
+    while (L < 32 && 2 * L * K <= 32) L <<= 1;
+
+    float *prev = colbase + (size_t)warp * 2 * (RP + 4) + 4, *cur = prev + RP + 4;
+    uint8_t *code_s = codebase + (size_t)warp * RP;
+    for (int u = blockIdx.x * VW + warp; u < B; u += gridDim.x * VW) {
+        const int64_t f0 = off[u];
+        const int T = (int)(off[u + 1] - f0);
+        uint8_t *bpu = bp + bp_off[u];
+        float *cu = costs_out ? costs_out + bp_off[u] : nullptr;
+        if (T <= 0) {
+            if (lane == 0) {
+                best_cost[u] = INF;
+                best_end[u] = -1;
+                if (path_len) path_len[u] = 0;
+            }
+            continue;
+        }
+        for (int r = lane - 4; r < R; r += 32) prev[r] = INF;       // incl. the pads in front of both columns
+        if (lane < 4) cur[lane - 4] = INF;
+        __syncwarp();
+        for (int c = 0; c < T; ++c) {
+            const float *Erow = E + (f0 + c) * ldE;
+            uint8_t *bpc = bpu + (size_t)c * R;
+            if (c == 0)
+                banded_column<true>(tab, ent, nes, pidx_s, pcost_s, pcap, G, R, K, Q, L, prev, cur, code_s, Erow, bpc, lane);
+            else
+                banded_column<false>(tab, ent, nes, pidx_s, pcost_s, pcap, G, R, K, Q, L, prev, cur, code_s, Erow, bpc, lane);
+            if (cu)
+                for (int r = lane; r < R; r += 32) cu[(size_t)c * R + r] = cur[r];
+            float *t = prev;
+            prev = cur;
+            cur = t;
+        }
+        finish_utterance(G, 0, 0, R, T, f0, u, prev, G.emit, G.pred_ptr, bpu, lane, best_cost, best_end, path_off,
+                         path_state, path_frame, path_len, frame_label);
+        __syncwarp();
+    }
+}
+
+static size_t banded1_smem_bytes(int Rmax) {
+    const size_t RP = (size_t)((Rmax + 3) & ~3);
+    return RP * (sizeof(BandState) + sizeof(BandEntry) + 8) + VB_NES_CAP * sizeof(BandNes) + (size_t)VW * 2 * (RP + 4) * 4 +
+           (size_t)VW * RP;
+}
+
+
 // ------------------------------------------------------------------------------------------------ K4
 // Scaled log-domain forward-backward for NES-free graphs.  Boundary conditions are those of the Viterbi
 // above (start in state 0 at frame 0, end in one of the graph's end states at the last frame); replacing the
@@ -609,6 +816,16 @@ int srb_viterbi_banded(const float *E, int64_t ldE, const int32_t *utt_off, int3
     F.entry_cost = entry_cost;
     F.g_entry_off = g_entry_off;
     F.entry_state = entry_state;
+    const size_t bytes1 = banded1_smem_bytes(Rmax);
+    if (!utt_graph && bytes1 <= (size_t)smem_optin() / 2) {
+        // one graph for the whole batch: its tables live in shared memory (viterbi_banded1_kernel)
+        SRB_CUDA(cudaFuncSetAttribute(viterbi_banded1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes1));
+        viterbi_banded1_kernel<<<(int)grid, VW * 32, bytes1, (cudaStream_t)stream>>>(
+            E, ldE, utt_off, B, G, F, Rmax, bp_off, bp, costs_out, best_cost, best_end, path_off, path_state, path_frame,
+            path_len, frame_label);
+        SRB_CUDA(cudaGetLastError());
+        return SRB_OK;
+    }
     viterbi_banded_kernel<<<(int)grid, VW * 32, bytes, (cudaStream_t)stream>>>(
         E, ldE, utt_off, B, G, F, Rmax, bp_off, bp, costs_out, best_cost, best_end, path_off, path_state, path_frame,
         path_len, frame_label);
