@@ -326,23 +326,27 @@ viterbi_banded_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *_
 // seven table loads with 64-bit address arithmetic.  The NES sweep gives every NES a group of lanes (first minimum
 // kept across the group by (cost, position) order).  Outputs are bit-identical to viterbi_banded_kernel.
 constexpr int VB_NES_CAP = 64;    // NES whose descriptor sits in shared memory (more fall back to the tables in global)
+constexpr int VB_ECOLS = 128;     // widest emission row staged in shared memory one frame ahead (else gathered from global)
 
 struct BandState { float a2, a1, a0; uint32_t meta; };
-struct BandEntry { int32_t r, nes; float cost; int32_t pad; };
-struct BandNes { int32_t n, p0, cnt, pad; };
+struct BandEntry { uint32_t rn; float cost; };                    // rn = state | entry NES << 16
+struct BandNes { int32_t n, p0, cnt, q0; };                       // p0: absolute CSR offset; q0: offset in the shared copy or -1
 
+// Erow: the frame's emission row, staged in shared memory by the caller or in global
 template <bool FIRST>
 __device__ __forceinline__ void banded_column(const BandState *tab, const BandEntry *ent, const BandNes *nes,
                                               const int32_t *pidx_s, const float *pcost_s, int pcap, const GraphBatch &G,
                                               int R, int K, int Q, int L, const float *prev, float *cur, uint8_t *code_s,
                                               const float *__restrict__ Erow, uint8_t *__restrict__ bpc, int lane) {
     const float INF = CUDART_INF_F;
-    // ---- 1. emitting states from the previous column (prev[-2], prev[-1] are +inf pads)
-#pragma unroll 2
-    for (int r = lane; r < R; r += 32) {
+    // ---- 1. emitting states from the previous column (prev[-2], prev[-1] are +inf pads).  Straight-line body (the
+    //         tables are padded to a multiple of 32 states with non-emitting dummies) so that unrolled iterations overlap.
+    const int R32 = (R + 31) & ~31;
+#pragma unroll 4
+    for (int r = lane; r < R32; r += 32) {
         const BandState t = tab[r];
         const uint32_t meta = t.meta;
-        if ((meta >> 9) == 0) continue;                              // NES
+        const bool emits = (meta >> 9) != 0;                         // else a NES (sweep 2) or padding
         const float t2 = prev[r - 2] + t.a2, t1 = prev[r - 1] + t.a1, t0 = prev[r] + t.a0;
         float best = INF;
         uint32_t code = 0;
@@ -350,38 +354,48 @@ __device__ __forceinline__ void banded_column(const BandState *tab, const BandEn
         if (t1 < best) { best = t1; code = (meta >> 2) & 3; }
         if (t0 < best) { best = t0; code = (meta >> 4) & 3; }
         const bool entry = (meta & 0x100) != 0;
-        float v = entry ? best : best + Erow[(meta >> 9) - 1];       // entry states get their emission in sweep 3
+        const float e = Erow[emits ? (meta >> 9) - 1 : 0];
+        float v = entry ? best : best + e;                           // entry states get their emission in sweep 3
         if (FIRST && r == 0) {                                       // decode.py:99-100
-            v = Erow[(meta >> 9) - 1];
+            v = e;
             code = 0;
         }
-        cur[r] = v;
-        bpc[r] = (uint8_t)code;
+        if (emits) {
+            cur[r] = v;
+            bpc[r] = (uint8_t)code;
+        }
         if (entry) code_s[r] = (uint8_t)code;
     }
-    __syncwarp();
     // ---- 2. the non-emitting states: L lanes per NES, each scanning every L-th predecessor in list order
     for (int k0 = 0; k0 < K; k0 += 32 / L) {
         const int k = k0 + lane / L, sub = lane & (L - 1);
         float best = INF;
         int bj = 0x7fffffff, n = 0, cnt = 0;
         if (k < K) {
-            int p0;
+            int p0, q0 = -1;
             if (k < VB_NES_CAP) {
                 const BandNes d = nes[k];
-                n = d.n; p0 = d.p0; cnt = d.cnt;
+                n = d.n; p0 = d.p0; cnt = d.cnt; q0 = d.q0;
             } else {
                 n = G.nes_idx[k];
                 p0 = G.pred_ptr[n];
                 cnt = G.pred_ptr[n + 1] - p0;
             }
-            for (int j = sub; j < cnt; j += L) {
-                const int jj = p0 + j;
-                const int o = jj < pcap ? pidx_s[jj] : G.pred_idx[jj];
-                const float cand = (jj < pcap ? pcost_s[jj] : G.pred_cost[jj]) + cur[o];
-                if (cand < best) {
-                    best = cand;
-                    bj = j;
+            if (q0 >= 0) {                                           // predecessor list in shared memory
+                for (int j = sub; j < cnt; j += L) {
+                    const float cand = pcost_s[q0 + j] + cur[pidx_s[q0 + j]];
+                    if (cand < best) {
+                        best = cand;
+                        bj = j;
+                    }
+                }
+            } else {
+                for (int j = sub; j < cnt; j += L) {
+                    const float cand = G.pred_cost[p0 + j] + cur[G.pred_idx[p0 + j]];
+                    if (cand < best) {
+                        best = cand;
+                        bj = j;
+                    }
                 }
             }
         }
@@ -407,20 +421,108 @@ __device__ __forceinline__ void banded_column(const BandState *tab, const BandEn
     // ---- 3. entry states: the NES arc competes with the band candidates (lower list position wins ties)
     for (int i = lane; i < Q; i += 32) {
         const BandEntry e = ent[i];
-        if (FIRST && e.r == 0) continue;
-        const uint32_t meta = tab[e.r].meta;
-        const float cand = e.cost + cur[e.nes];
+        const int r = (int)(e.rn & 0xffffu), en = (int)(e.rn >> 16);
+        if (FIRST && r == 0) continue;
+        const uint32_t meta = tab[r].meta;
+        const float cand = e.cost + cur[en];
         const uint32_t cn = (meta >> 6) & 3;
-        float best = cur[e.r];
-        uint32_t code = code_s[e.r];
+        float best = cur[r];
+        uint32_t code = code_s[r];
         if (cand < best || (cand == best && cand < INF && cn < code)) {
             best = cand;
             code = cn;
         }
-        cur[e.r] = best + Erow[(meta >> 9) - 1];
-        bpc[e.r] = (uint8_t)code;
+        cur[r] = best + Erow[(meta >> 9) - 1];
+        bpc[r] = (uint8_t)code;
     }
     __syncwarp();
+}
+
+// finish_utterance for the one-graph kernel: the walk back (decode.py:142-146) is done by the whole warp on a register
+// window of back-pointers -- 16 frames x 16 states below the current (frame, state), 8 bytes per lane, fetched with one
+// round trip and read with shuffles -- because the serial walk otherwise pays one DRAM latency per frame (an
+// utterance's back-pointers have long left L2 when its last column is done).  A band step is decoded from the packed
+// table (codes -> r-2 / r-1 / r); NES hops (7 per connected-digit string) go through the predecessor lists.
+constexpr int VB_WROWS = 16, VB_WCOLS = 16;
+
+__device__ __forceinline__ void finish_banded1(const GraphBatch &G, const BandState *tab, int R, int T, int64_t f0, int u,
+                                               const float *prev, const uint8_t *bpu, int lane,
+                                               float *best_cost, int32_t *best_end, const int64_t *path_off,
+                                               int32_t *path_state, int32_t *path_frame, int32_t *path_len,
+                                               int32_t *frame_label) {
+    const float INF = CUDART_INF_F;
+    float bc = INF;
+    int bi = -1;
+    for (int e = G.g_end_off[0]; e < G.g_end_off[1]; ++e) {          // '>=': the last listed minimum wins (decode.py:131-134)
+        const int s = G.end_state[e];
+        if (bc >= prev[s]) {
+            bc = prev[s];
+            bi = s;
+        }
+    }
+    if (lane == 0) {
+        best_cost[u] = bc;
+        best_end[u] = bi;
+    }
+    int len = 0;
+    if (bc < INF && (path_state || frame_label)) {
+        int32_t *ps = path_state ? path_state + path_off[u] : nullptr;
+        int32_t *pf = path_state ? path_frame + path_off[u] : nullptr;
+        const int cap = path_state ? (int)(path_off[u + 1] - path_off[u]) : 0x7fffffff;
+        int i = bi, j = T - 1;
+        if (lane == 0 && frame_label && (tab[i].meta >> 9) != 0) frame_label[f0 + j] = i;
+        int ja = -1, ia = 0;                                         // window: frames ja-15 .. ja, states ia-15 .. ia
+        uint32_t w0 = 0, w1 = 0;                                     // lane: frames ja - (lane>>2) [- 8], states ia-15+4*(lane&3) ..+3
+        while (j > 0 && len < cap) {
+            if (j > ja || j <= ja - VB_WROWS || i > ia || i <= ia - VB_WCOLS) {
+                ja = j;
+                ia = i;
+                const int sbase = ia - (VB_WCOLS - 1) + 4 * (lane & 3);
+                uint32_t b[8];
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int row = ja - (lane >> 2) - 8 * h;
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const int st = sbase + q;
+                        b[h * 4 + q] = (row >= 0 && st >= 0) ? (uint32_t)bpu[(size_t)row * R + st] : 0u;
+                    }
+                }
+                w0 = b[0] | (b[1] << 8) | (b[2] << 16) | (b[3] << 24);
+                w1 = b[4] | (b[5] << 8) | (b[6] << 16) | (b[7] << 24);
+                // pull the next window's sectors towards L2 while this one is walked
+                const int prow = ja - VB_WROWS - (lane & 15), pst = ia - ((lane >> 4) ? 0 : 2 * VB_WCOLS - 1);
+                if (prow >= 0 && pst >= 0)
+                    asm volatile("prefetch.global.L2 [%0];" ::"l"(bpu + (size_t)prow * R + pst));
+            }
+            const int dr = ja - j, ds = i - (ia - (VB_WCOLS - 1));
+            const uint32_t wsel = (dr & 8) ? w1 : w0;
+            const uint32_t word = __shfl_sync(0xffffffffu, wsel, ((dr & 7) << 2) | (ds >> 2));
+            const int code = (int)((word >> (8 * (ds & 3))) & 0xffu);
+            const BandState t = tab[i];
+            const bool i_emits = (t.meta >> 9) != 0;
+            int o;
+            if (i_emits && t.a2 < INF && code == (int)(t.meta & 3)) o = i - 2;
+            else if (i_emits && t.a1 < INF && code == (int)((t.meta >> 2) & 3)) o = i - 1;
+            else if (i_emits && t.a0 < INF && code == (int)((t.meta >> 4) & 3)) o = i;
+            else o = G.pred_idx[G.pred_ptr[i] + code];               // entry arc of a word, or i is a NES
+            const bool o_emits = (tab[o].meta >> 9) != 0;
+            if (i_emits && o_emits) --j;
+            i = o;
+            if (lane == 0) {
+                if (ps) {
+                    ps[len] = i;
+                    pf[len] = j;
+                }
+                if (frame_label && o_emits) frame_label[f0 + j] = i;
+            }
+            ++len;
+        }
+        if (j > 0) len = -1;   // capacity exhausted
+    } else if (frame_label) {
+        for (int c = lane; c < T; c += 32) frame_label[f0 + c] = -1;   // no path: frames are skipped downstream
+    }
+    if (lane == 0 && path_len) path_len[u] = len;
 }
 
 __global__ void __launch_bounds__(VW * 32)
@@ -434,19 +536,25 @@ viterbi_banded1_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, tid = threadIdx.x;
     const int R = G.g_state_off[1] - G.g_state_off[0], K = G.g_nes_off[1] - G.g_nes_off[0];
     const int Q = F.g_entry_off[1] - F.g_entry_off[0];
-    const int RP = (Rmax + 3) & ~3, pcap = RP;
+    const int RP = (Rmax + 31) & ~31, pcap = RP;              // tables padded to whole 32-state sweeps
     BandState *tab = reinterpret_cast<BandState *>(vb_sm);                       // RP
-    BandEntry *ent = reinterpret_cast<BandEntry *>(tab + RP);                    // RP
-    BandNes *nes = reinterpret_cast<BandNes *>(ent + RP);                        // VB_NES_CAP
-    int32_t *pidx_s = reinterpret_cast<int32_t *>(nes + VB_NES_CAP);             // pcap
+    BandNes *nes = reinterpret_cast<BandNes *>(tab + RP);                        // VB_NES_CAP
+    BandEntry *ent = reinterpret_cast<BandEntry *>(nes + VB_NES_CAP);            // RP
+    int32_t *pidx_s = reinterpret_cast<int32_t *>(ent + RP);                     // pcap
     float *pcost_s = reinterpret_cast<float *>(pidx_s + pcap);                   // pcap
     float *colbase = pcost_s + pcap;                                             // VW * 2 * (RP + 4)
-    uint8_t *codebase = reinterpret_cast<uint8_t *>(colbase + (size_t)VW * 2 * (RP + 4));   // VW * RP
+    float *erowbase = colbase + (size_t)VW * 2 * (RP + 4);                      // VW * VB_ECOLS
+    uint8_t *codebase = reinterpret_cast<uint8_t *>(erowbase + VW * VB_ECOLS);   // VW * RP
     const float INF = CUDART_INF_F;
+    __shared__ int ecols_s;
+    if (tid == 0) ecols_s = 0;
+    __syncthreads();
 
+    int emax = 0;
     for (int r = tid; r < R; r += VW * 32) {
         const uint32_t cd = (uint32_t)F.codes[r];
         const int em = G.emit[r];
+        emax = max(emax, em + 1);
         BandState t;
         t.a2 = F.band[r * 3 + 0];
         t.a1 = F.band[r * 3 + 1];
@@ -458,26 +566,43 @@ viterbi_banded1_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *
     for (int i = tid; i < Q; i += VW * 32) {
         const int r = F.entry_state[i];
         BandEntry e;
-        e.r = r;
-        e.nes = F.entry_nes[r];
+        e.rn = (uint32_t)r | ((uint32_t)F.entry_nes[r] << 16);
         e.cost = F.entry_cost[r];
-        e.pad = 0;
         ent[i] = e;
     }
-    for (int k = tid; k < min(K, VB_NES_CAP); k += VW * 32) {
-        const int n = G.nes_idx[k];
-        BandNes d;
-        d.n = n;
-        d.p0 = G.pred_ptr[n];
-        d.cnt = G.pred_ptr[n + 1] - d.p0;
-        d.pad = 0;
-        nes[k] = d;
-    }
-    for (int j = tid; j < min(G.pred_ptr[R], pcap); j += VW * 32) {
-        pidx_s[j] = G.pred_idx[j];
-        pcost_s[j] = G.pred_cost[j];
+    if (tid == 0) {                                                  // NES descriptors; their predecessor lists are packed
+        int q = 0;                                                   // back to back into the shared copy while they fit
+        for (int k = 0; k < min(K, VB_NES_CAP); ++k) {
+            const int n = G.nes_idx[k];
+            BandNes d;
+            d.n = n;
+            d.p0 = G.pred_ptr[n];
+            d.cnt = G.pred_ptr[n + 1] - d.p0;
+            d.q0 = q + d.cnt <= pcap ? q : -1;
+            if (d.q0 >= 0) q += d.cnt;
+            nes[k] = d;
+        }
     }
     __syncthreads();
+    for (int k = warp; k < min(K, VB_NES_CAP); k += VW) {
+        const BandNes d = nes[k];
+        if (d.q0 < 0) continue;
+        for (int j = lane; j < d.cnt; j += 32) {
+            pidx_s[d.q0 + j] = G.pred_idx[d.p0 + j];
+            pcost_s[d.q0 + j] = G.pred_cost[d.p0 + j];
+        }
+    }
+    for (int r = R + tid; r < RP; r += VW * 32) {                   // padding: never written, never emitting
+        BandState t;
+        t.a2 = t.a1 = t.a0 = INF;
+        t.meta = 0;
+        tab[r] = t;
+    }
+    atomicMax(&ecols_s, emax);
+    __syncthreads();
+    const int ecols = ecols_s;                                       // columns of E the graph reads
+    const bool staged = ecols <= VB_ECOLS;
+    float *erow_s = erowbase + warp * VB_ECOLS;
     int L = 1;                                                       // lanes per NES in sweep 2
     while (L < 32 && 2 * L * K <= 32) L <<= 1;
 
@@ -496,32 +621,51 @@ viterbi_banded1_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *
             }
             continue;
         }
-        for (int r = lane - 4; r < R; r += 32) prev[r] = INF;       // incl. the pads in front of both columns
-        if (lane < 4) cur[lane - 4] = INF;
+        for (int r = lane - 4; r < RP; r += 32) prev[r] = cur[r] = INF;   // incl. the pads in front of and behind both columns
         __syncwarp();
+        const float *Eg = E + f0 * ldE;                             // row of frame c (global)
+        uint8_t *bpc = bpu;
+        float en[VB_ECOLS / 32];                                     // row c+1 in flight while column c is relaxed
+        if (staged) {
+#pragma unroll
+            for (int i = 0; i < VB_ECOLS / 32; ++i) erow_s[lane + 32 * i] = lane + 32 * i < ecols ? Eg[lane + 32 * i] : 0.f;
+            __syncwarp();
+        }
         for (int c = 0; c < T; ++c) {
-            const float *Erow = E + (f0 + c) * ldE;
-            uint8_t *bpc = bpu + (size_t)c * R;
+            if (staged && c + 1 < T) {
+#pragma unroll
+                for (int i = 0; i < VB_ECOLS / 32; ++i) en[i] = lane + 32 * i < ecols ? Eg[ldE + lane + 32 * i] : 0.f;
+            }
             if (c == 0)
-                banded_column<true>(tab, ent, nes, pidx_s, pcost_s, pcap, G, R, K, Q, L, prev, cur, code_s, Erow, bpc, lane);
+                banded_column<true>(tab, ent, nes, pidx_s, pcost_s, pcap, G, R, K, Q, L, prev, cur, code_s,
+                                    staged ? erow_s : Eg, bpc, lane);
+            else if (staged)
+                banded_column<false>(tab, ent, nes, pidx_s, pcost_s, pcap, G, R, K, Q, L, prev, cur, code_s, erow_s, bpc, lane);
             else
-                banded_column<false>(tab, ent, nes, pidx_s, pcost_s, pcap, G, R, K, Q, L, prev, cur, code_s, Erow, bpc, lane);
+                banded_column<false>(tab, ent, nes, pidx_s, pcost_s, pcap, G, R, K, Q, L, prev, cur, code_s, Eg, bpc, lane);
             if (cu)
                 for (int r = lane; r < R; r += 32) cu[(size_t)c * R + r] = cur[r];
+            if (staged && c + 1 < T) {                               // every lane is past its reads of row c
+#pragma unroll
+                for (int i = 0; i < VB_ECOLS / 32; ++i) erow_s[lane + 32 * i] = en[i];
+                __syncwarp();
+            }
             float *t = prev;
             prev = cur;
             cur = t;
+            Eg += ldE;
+            bpc += R;
         }
-        finish_utterance(G, 0, 0, R, T, f0, u, prev, G.emit, G.pred_ptr, bpu, lane, best_cost, best_end, path_off,
-                         path_state, path_frame, path_len, frame_label);
+        finish_banded1(G, tab, R, T, f0, u, prev, bpu, lane, best_cost, best_end, path_off, path_state, path_frame,
+                       path_len, frame_label);
         __syncwarp();
     }
 }
 
 static size_t banded1_smem_bytes(int Rmax) {
-    const size_t RP = (size_t)((Rmax + 3) & ~3);
+    const size_t RP = (size_t)((Rmax + 31) & ~31);
     return RP * (sizeof(BandState) + sizeof(BandEntry) + 8) + VB_NES_CAP * sizeof(BandNes) + (size_t)VW * 2 * (RP + 4) * 4 +
-           (size_t)VW * RP;
+           (size_t)VW * VB_ECOLS * 4 + (size_t)VW * RP;
 }
 
 
