@@ -332,12 +332,23 @@ struct BandState { float a2, a1, a0; uint32_t meta; };
 struct BandEntry { uint32_t rn; float cost; };                    // rn = state | entry NES << 16
 struct BandNes { int32_t n, p0, cnt, q0; };                       // p0: absolute CSR offset; q0: offset in the shared copy or -1
 
+// What a lane does in sweeps 2 and 3 does not depend on the frame: when every NES fits one pass (K * L <= 32, lists in
+// shared memory) and the entries fit VB_QH per lane, the descriptors are read once into registers (HOIST).
+constexpr int VB_QH = 3;
+struct LaneWork {
+    int n, q0, cnt;                 // this lane group's NES (cnt = 0: none), list at pidx_s / pcost_s + q0
+    uint32_t ern[VB_QH];            // entries lane, lane+32, ..: state | NES << 16, or 0xffffffff
+    float ecost[VB_QH];
+    uint32_t emeta[VB_QH];          // entry code << 16 | emit column
+};
+
 // Erow: the frame's emission row, staged in shared memory by the caller or in global
-template <bool FIRST>
+template <bool FIRST, bool HOIST>
 __device__ __forceinline__ void banded_column(const BandState *tab, const BandEntry *ent, const BandNes *nes,
                                               const int32_t *pidx_s, const float *pcost_s, int pcap, const GraphBatch &G,
                                               int R, int K, int Q, int L, const float *prev, float *cur, uint8_t *code_s,
-                                              const float *__restrict__ Erow, uint8_t *__restrict__ bpc, int lane) {
+                                              const float *__restrict__ Erow, uint8_t *__restrict__ bpc, int lane,
+                                              const LaneWork &lw) {
     const float INF = CUDART_INF_F;
     // ---- 1. emitting states from the previous column (prev[-2], prev[-1] are +inf pads).  Straight-line body (the
     //         tables are padded to a multiple of 32 states with non-emitting dummies) so that unrolled iterations overlap.
@@ -367,6 +378,55 @@ __device__ __forceinline__ void banded_column(const BandState *tab, const BandEn
         if (entry) code_s[r] = (uint8_t)code;
     }
     // ---- 2. the non-emitting states: L lanes per NES, each scanning every L-th predecessor in list order
+    if (HOIST) {
+        const int sub = lane & (L - 1);
+        float best = INF;
+        int bj = 0x7fffffff;
+        for (int j = sub; j < lw.cnt; j += L) {
+            const float cand = pcost_s[lw.q0 + j] + cur[pidx_s[lw.q0 + j]];
+            if (cand < best) {
+                best = cand;
+                bj = j;
+            }
+        }
+        for (int d = L >> 1; d; d >>= 1) {
+            const float ob = __shfl_xor_sync(0xffffffffu, best, d);
+            const int oj = __shfl_xor_sync(0xffffffffu, bj, d);
+            if (ob < best || (ob == best && oj < bj)) {
+                best = ob;
+                bj = oj;
+            }
+        }
+        if (lw.n >= 0 && sub == 0) {
+            if (FIRST && lw.n == 0) {
+                cur[0] = 0.f;
+                bpc[0] = 0;
+            } else {
+                cur[lw.n] = best;
+                bpc[lw.n] = (uint8_t)(best < INF ? bj : 0);
+            }
+        }
+        __syncwarp();
+        // ---- 3. entry states (descriptors in registers)
+#pragma unroll
+        for (int h = 0; h < VB_QH; ++h) {
+            const uint32_t rn = lw.ern[h];
+            const int r = (int)(rn & 0xffffu), en = (int)(rn >> 16);
+            if (rn == 0xffffffffu || (FIRST && r == 0)) continue;
+            const float cand = lw.ecost[h] + cur[en];
+            const uint32_t cn = lw.emeta[h] >> 16;
+            float best3 = cur[r];
+            uint32_t code = code_s[r];
+            if (cand < best3 || (cand == best3 && cand < INF && cn < code)) {
+                best3 = cand;
+                code = cn;
+            }
+            cur[r] = best3 + Erow[lw.emeta[h] & 0xffffu];
+            bpc[r] = (uint8_t)code;
+        }
+        __syncwarp();
+        return;
+    }
     for (int k0 = 0; k0 < K; k0 += 32 / L) {
         const int k = k0 + lane / L, sub = lane & (L - 1);
         float best = INF;
@@ -525,7 +585,54 @@ __device__ __forceinline__ void finish_banded1(const GraphBatch &G, const BandSt
     if (lane == 0 && path_len) path_len[u] = len;
 }
 
-__global__ void __launch_bounds__(VW * 32)
+// All columns of one utterance; leaves the last column in prev (by reference).  FAST: emission rows staged and
+// sweeps 2 / 3 on register descriptors.
+template <bool FAST>
+__device__ __forceinline__ void banded1_forward(const BandState *tab, const BandEntry *ent, const BandNes *nes,
+                                                const int32_t *pidx_s, const float *pcost_s, int pcap, const GraphBatch &G,
+                                                int R, int K, int Q, int L, float *&prev, float *&cur, uint8_t *code_s,
+                                                float *erow_s, int ecols, bool staged, const float *__restrict__ Eg,
+                                                int64_t ldE, int T, uint8_t *__restrict__ bpc, float *cu, int lane,
+                                                const LaneWork &lw) {
+    float en[VB_ECOLS / 32];                                         // row c+1 in flight while column c is relaxed
+    if (staged) {
+#pragma unroll
+        for (int i = 0; i < VB_ECOLS / 32; ++i)
+            if (32 * i < ecols) erow_s[lane + 32 * i] = lane + 32 * i < ecols ? Eg[lane + 32 * i] : 0.f;
+        __syncwarp();
+    }
+    for (int c = 0; c < T; ++c) {
+        if (staged && c + 1 < T) {
+#pragma unroll
+            for (int i = 0; i < VB_ECOLS / 32; ++i)
+                if (32 * i < ecols) en[i] = lane + 32 * i < ecols ? Eg[ldE + lane + 32 * i] : 0.f;
+        }
+        if (c == 0)
+            banded_column<true, false>(tab, ent, nes, pidx_s, pcost_s, pcap, G, R, K, Q, L, prev, cur, code_s,
+                                       staged ? erow_s : Eg, bpc, lane, lw);
+        else if (FAST)
+            banded_column<false, true>(tab, ent, nes, pidx_s, pcost_s, pcap, G, R, K, Q, L, prev, cur, code_s, erow_s, bpc,
+                                       lane, lw);
+        else
+            banded_column<false, false>(tab, ent, nes, pidx_s, pcost_s, pcap, G, R, K, Q, L, prev, cur, code_s,
+                                        staged ? erow_s : Eg, bpc, lane, lw);
+        if (cu)
+            for (int r = lane; r < R; r += 32) cu[(size_t)c * R + r] = cur[r];
+        if (staged && c + 1 < T) {                                   // every lane is past its reads of row c
+#pragma unroll
+            for (int i = 0; i < VB_ECOLS / 32; ++i)
+                if (32 * i < ecols) erow_s[lane + 32 * i] = en[i];
+            __syncwarp();
+        }
+        float *t = prev;
+        prev = cur;
+        cur = t;
+        Eg += ldE;
+        bpc += R;
+    }
+}
+
+__global__ void __launch_bounds__(VW * 32, 7)
 viterbi_banded1_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *__restrict__ off, int B, GraphBatch G,
                        BandForm F, int Rmax, const int64_t *__restrict__ bp_off, uint8_t *__restrict__ bp,
                        float *__restrict__ costs_out, float *__restrict__ best_cost, int32_t *__restrict__ best_end,
@@ -606,6 +713,32 @@ viterbi_banded1_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *
     int L = 1;                                                       // lanes per NES in sweep 2
     while (L < 32 && 2 * L * K <= 32) L <<= 1;
 
+    // frame-invariant work of this lane in sweeps 2 and 3
+    LaneWork lw;
+    bool fast = staged && K * L <= 32 && K <= VB_NES_CAP && Q <= 32 * VB_QH;
+    lw.n = -1;
+    lw.q0 = lw.cnt = 0;
+    if (fast && lane / L < K) {
+        const BandNes d = nes[lane / L];
+        lw.n = d.n;
+        lw.q0 = d.q0;
+        lw.cnt = d.cnt;
+    }
+    fast = fast && __all_sync(0xffffffffu, lw.q0 >= 0);
+#pragma unroll
+    for (int h = 0; h < VB_QH; ++h) {
+        lw.ern[h] = 0xffffffffu;
+        lw.ecost[h] = 0.f;
+        lw.emeta[h] = 0;
+        if (fast && lane + 32 * h < Q) {
+            const BandEntry e = ent[lane + 32 * h];
+            const uint32_t meta = tab[e.rn & 0xffffu].meta;
+            lw.ern[h] = e.rn;
+            lw.ecost[h] = e.cost;
+            lw.emeta[h] = (((meta >> 6) & 3) << 16) | ((meta >> 9) - 1);
+        }
+    }
+
     float *prev = colbase + (size_t)warp * 2 * (RP + 4) + 4, *cur = prev + RP + 4;
     uint8_t *code_s = codebase + (size_t)warp * RP;
     for (int u = blockIdx.x * VW + warp; u < B; u += gridDim.x * VW) {
@@ -623,39 +756,12 @@ viterbi_banded1_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *
         }
         for (int r = lane - 4; r < RP; r += 32) prev[r] = cur[r] = INF;   // incl. the pads in front of and behind both columns
         __syncwarp();
-        const float *Eg = E + f0 * ldE;                             // row of frame c (global)
-        uint8_t *bpc = bpu;
-        float en[VB_ECOLS / 32];                                     // row c+1 in flight while column c is relaxed
-        if (staged) {
-#pragma unroll
-            for (int i = 0; i < VB_ECOLS / 32; ++i) erow_s[lane + 32 * i] = lane + 32 * i < ecols ? Eg[lane + 32 * i] : 0.f;
-            __syncwarp();
-        }
-        for (int c = 0; c < T; ++c) {
-            if (staged && c + 1 < T) {
-#pragma unroll
-                for (int i = 0; i < VB_ECOLS / 32; ++i) en[i] = lane + 32 * i < ecols ? Eg[ldE + lane + 32 * i] : 0.f;
-            }
-            if (c == 0)
-                banded_column<true>(tab, ent, nes, pidx_s, pcost_s, pcap, G, R, K, Q, L, prev, cur, code_s,
-                                    staged ? erow_s : Eg, bpc, lane);
-            else if (staged)
-                banded_column<false>(tab, ent, nes, pidx_s, pcost_s, pcap, G, R, K, Q, L, prev, cur, code_s, erow_s, bpc, lane);
-            else
-                banded_column<false>(tab, ent, nes, pidx_s, pcost_s, pcap, G, R, K, Q, L, prev, cur, code_s, Eg, bpc, lane);
-            if (cu)
-                for (int r = lane; r < R; r += 32) cu[(size_t)c * R + r] = cur[r];
-            if (staged && c + 1 < T) {                               // every lane is past its reads of row c
-#pragma unroll
-                for (int i = 0; i < VB_ECOLS / 32; ++i) erow_s[lane + 32 * i] = en[i];
-                __syncwarp();
-            }
-            float *t = prev;
-            prev = cur;
-            cur = t;
-            Eg += ldE;
-            bpc += R;
-        }
+        if (fast)
+            banded1_forward<true>(tab, ent, nes, pidx_s, pcost_s, pcap, G, R, K, Q, L, prev, cur, code_s, erow_s, ecols, true,
+                                  E + f0 * ldE, ldE, T, bpu, cu, lane, lw);
+        else
+            banded1_forward<false>(tab, ent, nes, pidx_s, pcost_s, pcap, G, R, K, Q, L, prev, cur, code_s, erow_s, ecols,
+                                   staged, E + f0 * ldE, ldE, T, bpu, cu, lane, lw);
         finish_banded1(G, tab, R, T, f0, u, prev, bpu, lane, best_cost, best_end, path_off, path_state, path_frame,
                        path_len, frame_label);
         __syncwarp();
