@@ -192,6 +192,52 @@ def test_banded_kernel_equals_generic_kernel(layers):
     assert np.isfinite(a[2]).all()
 
 
+@pytest.mark.parametrize("W,layers,why", [(4, 3, "register descriptors, staged emission rows"),
+                                          (2, 40, "41 NES: more than one pass of the NES sweep"),
+                                          (11, 10, "110 entry states: descriptors stay in shared memory"),
+                                          (30, 2, "150 emission columns: rows gathered from global")])
+def test_one_graph_banded_kernel_equals_generic_kernel(W, layers, why):
+    """viterbi_banded1_kernel (one graph for the whole batch: tables in shared memory, lane-group NES reduction,
+    windowed warp traceback) against srb_viterbi_graph: cost matrices, back-pointers, ends, paths and frame labels must
+    be identical, including 1-frame utterances, utterances too short for any path, and an empty one."""
+    import torch
+    from srb200 import engine, synth
+    from srb200.graph import GraphBatch, word_loop_graph
+    S = 5
+    models, base = synth.make_models(41, W=W, S=S, M=4)
+    trans = np.stack([m[3] for m in models]).copy()
+    rng = np.random.default_rng(6)
+    for w in range(W):
+        trans[w][2, 0] = 1.0 + rng.random()
+        trans[w][S - 1, S - 3] = 0.5 + rng.random()
+    g, _ = word_loop_graph(trans, layers)
+    gb = GraphBatch([g], engine.device())
+    assert gb.banded
+    B = 40
+    X, off, _ = synth.make_strings(42, base, B, n_words=layers, T=12 * layers + 30, noise=1.0)
+    lens = np.diff(off).copy()
+    lens[3], lens[7], lens[11] = 1, 2, 0                 # too short for a path / empty
+    lens[5:] = np.maximum(1, lens[5:] - rng.integers(0, 25, size=B - 5)) * (lens[5:] > 0)
+    lens[11] = 0
+    off2 = np.zeros(B + 1, np.int32)
+    np.cumsum(lens, out=off2[1:])
+    X = np.ascontiguousarray(X[:off2[-1]])
+    pm, _ = engine.PackedModel.from_words(models)
+    E = engine.gmm_score(X, pm)["E"]
+    out = []
+    for banded in (True, False):
+        fl = torch.full((E.shape[0],), -9, dtype=torch.int32, device="cuda")
+        r = engine.viterbi(E, off2, gb, want_costs=True, want_path=True, frame_label=fl, banded=banded)
+        out.append((r.costs.cpu().numpy(), r.bp.cpu().numpy(), r.best_cost.cpu().numpy(), r.best_end.cpu().numpy(),
+                    r.paths(), fl.cpu().numpy(), r.path_len.cpu().numpy()))
+    a, b = out
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    assert np.array_equal(a[2], b[2]) and np.array_equal(a[3], b[3]) and np.array_equal(a[5], b[5])
+    assert np.array_equal(a[6], b[6])
+    assert all(np.array_equal(x, y) for x, y in zip(a[4], b[4]))
+    assert np.isfinite(a[2]).sum() >= B - 8 and not np.isfinite(a[2][[3, 11]]).any()
+
+
 def test_path_words_kernel_matches_main_py_postprocessing():
     """srb_path_words against the host form of main.py:59-67 (reverse, drop consecutive duplicates, split at the NES,
     first state of every piece -> word) on random paths: runs longer than a warp, NES runs, paths that start or end in
