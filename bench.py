@@ -413,7 +413,7 @@ def bench_connected(args, ctx):
     ms = float(np.mean(per))
     roof = _roof_fma(FMA_PER_FRAME_DECODE, N, ms, ctx["peak_fma"],
                      ("classify_tc_kernel<39> (scorer mode, tcgen05 3xTF32)" if use_tc else "score_kernel<39>") +
-                     " + viterbi_graph_kernel",
+                     " + viterbi_banded1_kernel (one-graph banded form of srb_viterbi_banded)",
                      "17160 FMA/frame scoring (55 tied states x 4 x 2*39); DP 847 arcs + 393 states per frame; "
                      "393 B/frame back-pointers")
     roof["phase_ms"] = {"score": ev[0].elapsed_time(ev[1]), "viterbi": ev[1].elapsed_time(ev[2])}
