@@ -169,6 +169,18 @@ int srb_forward_backward(const float *E, int64_t ldE, const int32_t *utt_off, in
                          const float *succ_cost, const int32_t *end_state, int32_t Rmax, int32_t NNZmax,
                          const int64_t *ws_off, float *gamma, double *neg_log_z, double *xi_sum, void *stream);
 
+/* The same E-step for left-to-right models: every graph NES-free with all predecessors of r inside {r-2, r-1, r}
+ * (what HMM.fit / calc_transition_costs build, kmeans.py:53-95) and Rmax <= 32.  band / codes as in
+ * srb_viterbi_banded (band[r] = costs from r-2, r-1, r; codes[r] = their positions in r's predecessor list, one
+ * byte each); order: optional int32[B] permutation of the utterances (falling length balances the lane groups).
+ * One lane per state, 32 / pow2(Rmax) utterances per warp; outputs as srb_forward_backward (xi_sum to 1e-6 relative:
+ * the per-utterance sums are formed in registers before the atomic). */
+int srb_forward_backward_banded(const float *E, int64_t ldE, const int32_t *utt_off, int32_t B, const int32_t *utt_graph,
+                                const int32_t *g_state_off, const int32_t *g_end_off, const int32_t *emit,
+                                const int32_t *pred_ptr, const int32_t *end_state, const float *band,
+                                const int32_t *codes, const int32_t *order, int32_t Rmax, const int64_t *ws_off,
+                                float *gamma, double *neg_log_z, double *xi_sum, void *stream);
+
 
 /* ---- K5 / K6: sufficient statistics, K-means assignment, M-step ---------------------------------
  * Statistics row of one group (Gaussian / segment / cluster), srb_stats_row(D) = 2*D + 3 doubles:

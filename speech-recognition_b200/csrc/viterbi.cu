@@ -945,6 +945,159 @@ forward_backward_kernel(const float *__restrict__ E, int64_t ldE, const int32_t 
     }
 }
 
+// ------------------------------------------------------------------------------------------------ K4, banded
+// The same recursion for left-to-right models (every predecessor of r inside {r-2, r-1, r}, no NES, at most 32 states:
+// what HMM.fit / calc_transition_costs produce, kmeans.py:53-95).  A group of W = pow2 >= Rmax lanes owns one utterance
+// (32 / W utterances per warp), a lane owns one state: alpha / beta live in a register, the band costs and the CSR
+// positions of the three arcs are read once per utterance, predecessors / successors arrive by width-W shuffles, the
+// emission and alpha_hat loads run one column ahead, and the edge posteriors are summed in registers -- one atomic per
+// arc per UTTERANCE instead of one per frame.  `order` (optional) lists the utterances by falling length so that the
+// groups of a warp finish together.  Same boundary conditions, renormalisation and outputs as forward_backward_kernel.
+template <int W>
+__device__ __forceinline__ float group_min(float v) {
+#pragma unroll
+    for (int d = W >> 1; d; d >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, d));
+    return v;
+}
+template <int W>
+__device__ __forceinline__ float group_sum(float v) {
+#pragma unroll
+    for (int d = W >> 1; d; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    return v;
+}
+// -log(exp(-a) + exp(-b) + exp(-c)), +inf entries ignored
+__device__ __forceinline__ float neg_lse3(float a, float b, float c) {
+    const float m = fminf(a, fminf(b, c));
+    if (!(m < CUDART_INF_F)) return CUDART_INF_F;
+    return m - __logf(__expf(m - a) + __expf(m - b) + __expf(m - c));
+}
+
+template <int W>
+__global__ void __launch_bounds__(VW * 32)
+forward_backward_banded_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *__restrict__ off, int B,
+                               GraphBatch G, const float *__restrict__ band, const int32_t *__restrict__ codes,
+                               const int32_t *__restrict__ order, const int64_t *__restrict__ ws_off,
+                               float *__restrict__ gamma, double *__restrict__ neg_log_z, double *__restrict__ xi_sum) {
+    constexpr int GPW = 32 / W;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, sub = lane & (W - 1), grp = lane / W;
+    const float INF = CUDART_INF_F;
+    const int nslots = (B + GPW - 1) / GPW;
+
+    for (int slot = blockIdx.x * VW + warp; slot < nslots; slot += gridDim.x * VW) {
+        const int idx = slot * GPW + grp;
+        const bool valid = idx < B;
+        const int u = valid ? (order ? order[idx] : idx) : 0;
+        const int g = (valid && G.utt_graph) ? G.utt_graph[u] : 0;
+        const int s0 = G.g_state_off[g], R = G.g_state_off[g + 1] - s0;
+        const int64_t f0 = off[u];
+        const int T = valid ? max((int)(off[u + 1] - f0), 0) : 0;
+        const bool act = valid && sub < R;                           // this lane owns a state
+        float a2 = INF, a1 = INF, a0 = INF;
+        int em = 0, arc2 = 0, arc1 = 0, arc0 = 0;
+        bool is_end = false;
+        if (act) {
+            a2 = band[(size_t)(s0 + sub) * 3 + 0];
+            a1 = band[(size_t)(s0 + sub) * 3 + 1];
+            a0 = band[(size_t)(s0 + sub) * 3 + 2];
+            const uint32_t cd = (uint32_t)codes[s0 + sub];
+            const int p0 = G.pred_ptr[s0 + sub];
+            arc2 = p0 + (int)(cd & 0xffu);
+            arc1 = p0 + (int)((cd >> 8) & 0xffu);
+            arc0 = p0 + (int)((cd >> 16) & 0xffu);
+            em = G.emit[s0 + sub];
+            for (int e = G.g_end_off[g]; e < G.g_end_off[g + 1]; ++e) is_end |= (G.end_state[e] == sub);
+        }
+        if (sub < 2) a2 = INF;                                       // no state r-2 / r-1 in this group
+        if (sub < 1) a1 = INF;
+        int Tmax = T;
+#pragma unroll
+        for (int d = 16; d >= W; d >>= 1) Tmax = max(Tmax, __shfl_xor_sync(0xffffffffu, Tmax, d));
+        if (valid && T == 0 && sub == 0 && neg_log_z) neg_log_z[u] = (double)INF;
+        if (Tmax == 0) continue;
+        const float *Eu = E + f0 * ldE + em;
+        float *gu = gamma + (valid ? ws_off[u] : 0) + sub;
+
+        // ---- forward: alpha_hat columns to gamma
+        float alpha = INF;
+        double scale = 0.0;
+        float e_c = (act && 0 < T) ? Eu[0] : 0.f;
+        for (int c = 0; c < Tmax; ++c) {
+            const bool live = c < T;
+            float e_n = 0.f;
+            if (act && c + 1 < T) e_n = Eu[(int64_t)(c + 1) * ldE];
+            const float p1 = __shfl_up_sync(0xffffffffu, alpha, 1, W), p2 = __shfl_up_sync(0xffffffffu, alpha, 2, W);
+            float a;
+            if (c == 0) a = (sub == 0) ? e_c : INF;
+            else a = neg_lse3(p2 + a2, p1 + a1, alpha + a0) + e_c;
+            if (!act) a = INF;
+            const float m = group_min<W>(a);
+            const float sh = (m < INF) ? m : 0.f;
+            if (live) {
+                scale += (double)sh;
+                alpha = a - sh;
+                if (act) gu[(size_t)c * R] = alpha;
+            }
+            e_c = e_n;
+        }
+        {   // log Z over the end states of the last column
+            const float v = (is_end && T > 0) ? alpha : INF;
+            const float zm = group_min<W>(v);
+            const float zs = group_sum<W>(v < INF ? __expf(zm - v) : 0.f);
+            const float zl = (zm < INF) ? zm - __logf(zs) : INF;
+            if (valid && T > 0 && sub == 0 && neg_log_z) neg_log_z[u] = (zl < INF) ? scale + (double)zl : (double)INF;
+        }
+        // ---- backward: gamma over alpha_hat, edge posteriors into registers
+        float beta = is_end ? 0.f : INF;
+        double x2 = 0.0, x1 = 0.0, x0 = 0.0;
+        int c = Tmax - 1;
+        float al_c = (act && c < T) ? gu[(size_t)c * R] : INF;
+        float al_p = (act && c >= 1 && c - 1 < T) ? gu[(size_t)(c - 1) * R] : INF;
+        e_c = (act && c < T) ? Eu[(int64_t)c * ldE] : 0.f;
+        for (; c >= 0; --c) {
+            const bool live = c < T;
+            float al_n = INF, e_n = 0.f;                             // alpha_hat_{c-2}, E_{c-1}
+            if (act && c >= 2 && c - 2 < T) al_n = gu[(size_t)(c - 2) * R];
+            if (act && c >= 1 && c - 1 < T) e_n = Eu[(int64_t)(c - 1) * ldE];
+            // gamma_c
+            const float v = al_c + beta;
+            const float p = (v < INF) ? __expf(-v) : 0.f;
+            const float gs = group_sum<W>(p);
+            if (live && act) gu[(size_t)c * R] = p * (gs > 0.f ? 1.f / gs : 0.f);
+            // xi of the arcs into column c, beta_hat_{c-1}
+            const float w = e_c + beta;                              // E_c(r) + beta_hat_c(r)
+            const float q1 = __shfl_up_sync(0xffffffffu, al_p, 1, W), q2 = __shfl_up_sync(0xffffffffu, al_p, 2, W);
+            const float y2 = a2 + w, y1 = a1 + w, y0 = a0 + w;
+            const float v2 = q2 + y2, v1 = q1 + y1, v0 = al_p + y0;
+            const float vmin = group_min<W>(fminf(v2, fminf(v1, v0)));
+            const float r2 = (v2 < INF) ? __expf(vmin - v2) : 0.f;
+            const float r1 = (v1 < INF) ? __expf(vmin - v1) : 0.f;
+            const float r0 = (v0 < INF) ? __expf(vmin - v0) : 0.f;
+            const float xs = group_sum<W>(r2 + r1 + r0);
+            const float xinv = xs > 0.f ? 1.f / xs : 0.f;
+            float s1 = __shfl_down_sync(0xffffffffu, y1, 1, W), s2 = __shfl_down_sync(0xffffffffu, y2, 2, W);
+            if (sub + 1 >= W) s1 = INF;
+            if (sub + 2 >= W) s2 = INF;
+            const float b = neg_lse3(y0, s1, s2);
+            const float bm = group_min<W>(b);
+            if (live && c > 0) {
+                x2 += (double)(r2 * xinv);
+                x1 += (double)(r1 * xinv);
+                x0 += (double)(r0 * xinv);
+                beta = b - ((bm < INF) ? bm : 0.f);
+            }
+            al_c = al_p;
+            al_p = al_n;
+            e_c = e_n;
+        }
+        if (xi_sum && act && T > 0) {
+            if (a2 < INF) atomicAdd(xi_sum + arc2, x2);
+            if (a1 < INF) atomicAdd(xi_sum + arc1, x1);
+            if (a0 < INF) atomicAdd(xi_sum + arc0, x0);
+        }
+    }
+}
+
+
 // ------------------------------------------------------------------------------------------------ path -> words
 // main.py:59-67 after the decoder: the reversed path read forwards, consecutive duplicate states removed, split at the
 // non-emitting states, the first state of every piece mapped to its word.  One warp per utterance: lane i looks at
@@ -981,6 +1134,20 @@ __global__ void path_words_kernel(const int32_t *__restrict__ path_state, const 
 }  // namespace srb
 
 using namespace srb;
+
+template <int W>
+static int launch_fb_banded(const float *E, int64_t ldE, const int32_t *utt_off, int32_t B, const GraphBatch &G,
+                            const float *band, const int32_t *codes, const int32_t *order, const int64_t *ws_off,
+                            float *gamma, double *neg_log_z, double *xi_sum, void *stream) {
+    const int64_t slots = ((int64_t)B * W + 31) / 32;
+    int64_t grid = (slots + VW - 1) / VW;
+    const int64_t cap = (int64_t)sm_count() * 16;
+    if (grid > cap) grid = cap;
+    forward_backward_banded_kernel<W><<<(int)grid, VW * 32, 0, (cudaStream_t)stream>>>(
+        E, ldE, utt_off, B, G, band, codes, order, ws_off, gamma, neg_log_z, xi_sum);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
 
 extern "C" {
 
@@ -1107,6 +1274,29 @@ int srb_forward_backward(const float *E, int64_t ldE, const int32_t *utt_off, in
         E, ldE, utt_off, B, G, succ_ptr, succ_idx, succ_cost, pred_tgt, Rmax, NNZmax, ws_off, gamma, neg_log_z, xi_sum);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
+}
+
+int srb_forward_backward_banded(const float *E, int64_t ldE, const int32_t *utt_off, int32_t B, const int32_t *utt_graph,
+                                const int32_t *g_state_off, const int32_t *g_end_off, const int32_t *emit,
+                                const int32_t *pred_ptr, const int32_t *end_state, const float *band,
+                                const int32_t *codes, const int32_t *order, int32_t Rmax, const int64_t *ws_off,
+                                float *gamma, double *neg_log_z, double *xi_sum, void *stream) {
+    SRB_REQUIRE(E && utt_off && g_state_off && g_end_off && emit && pred_ptr && end_state && band && codes && ws_off &&
+                    gamma,
+                SRB_EINVAL, "srb_forward_backward_banded: null pointer");
+    SRB_REQUIRE(B >= 0 && Rmax > 0 && ldE > 0, SRB_EINVAL, "srb_forward_backward_banded: bad sizes");
+    SRB_REQUIRE(Rmax <= 32, SRB_EUNSUPPORTED, "srb_forward_backward_banded: %d states (at most 32: use srb_forward_backward)",
+                Rmax);
+    if (B == 0) return SRB_OK;
+    GraphBatch G = make_graph(utt_graph, g_state_off, g_state_off, g_end_off, emit, pred_ptr, nullptr, nullptr, nullptr,
+                              end_state);
+    if (Rmax <= 4)
+        return launch_fb_banded<4>(E, ldE, utt_off, B, G, band, codes, order, ws_off, gamma, neg_log_z, xi_sum, stream);
+    if (Rmax <= 8)
+        return launch_fb_banded<8>(E, ldE, utt_off, B, G, band, codes, order, ws_off, gamma, neg_log_z, xi_sum, stream);
+    if (Rmax <= 16)
+        return launch_fb_banded<16>(E, ldE, utt_off, B, G, band, codes, order, ws_off, gamma, neg_log_z, xi_sum, stream);
+    return launch_fb_banded<32>(E, ldE, utt_off, B, G, band, codes, order, ws_off, gamma, neg_log_z, xi_sum, stream);
 }
 
 int srb_path_words(const int32_t *path_state, const int64_t *path_off, const int32_t *path_len, int32_t B,

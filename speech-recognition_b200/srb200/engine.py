@@ -353,8 +353,10 @@ def viterbi(E, off, gb, utt_graph=None, want_costs=False, want_path=True, frame_
     return res
 
 
-def forward_backward(E, off, gb, utt_graph=None, want_xi=False):
-    """K4.  -> (gamma flat float32 [sum T*R], ws_off, neg_log_z[B] float64, xi_sum[nnz] float64 or None)."""
+def forward_backward(E, off, gb, utt_graph=None, want_xi=False, banded=None):
+    """K4.  -> (gamma flat float32 [sum T*R], ws_off, neg_log_z[B] float64, xi_sum[nnz] float64 or None).
+    Left-to-right models of at most 32 states (gb.banded) run srb_forward_backward_banded, one lane per state with the
+    utterances ordered by falling length; banded=False forces the generic CSR kernel (same outputs to rounding)."""
     dev = E.device
     offd = as_offsets(off)
     B = offd.numel() - 1
@@ -366,6 +368,16 @@ def forward_backward(E, off, gb, utt_graph=None, want_xi=False):
     gamma = torch.empty(max(int(ws[-1]), 1), dtype=torch.float32, device=dev)
     nlz = torch.empty(B, dtype=torch.float64, device=dev)
     xi = torch.zeros(max(int(gb.edge_off[-1]), 1), dtype=torch.float64, device=dev) if want_xi else None
+    fits = gb.banded and gb.Rmax <= 32
+    if banded and not fits:
+        raise ValueError("forward_backward: banded=True needs left-to-right graphs of at most 32 states")
+    if fits and banded is not False:
+        order = torch.argsort(offd[1:] - offd[:-1], descending=True, stable=True).to(torch.int32) if B > 1 else None
+        _l.check(_l.load().srb_forward_backward_banded(
+            _l.ptr(E), E.stride(0), _l.ptr(offd), B, _l.ptr(ug), _l.ptr(gb["g_state_off"]), _l.ptr(gb["g_end_off"]),
+            _l.ptr(gb["emit"]), _l.ptr(gb["pred_ptr"]), _l.ptr(gb["end_state"]), _l.ptr(gb["band"]), _l.ptr(gb["codes"]),
+            _l.ptr(order), gb.Rmax, _l.ptr(ws_d), _l.ptr(gamma), _l.ptr(nlz), _l.ptr(xi), _l.stream_ptr()))
+        return gamma, ws, nlz, xi
     _l.check(_l.load().srb_forward_backward(
         _l.ptr(E), E.stride(0), _l.ptr(offd), B, _l.ptr(ug), _l.ptr(gb["g_state_off"]), _l.ptr(gb["g_end_off"]),
         _l.ptr(gb["emit"]), _l.ptr(gb["pred_ptr"]), _l.ptr(gb["pred_idx"]), _l.ptr(gb["pred_cost"]),

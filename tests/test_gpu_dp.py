@@ -125,8 +125,11 @@ def test_dtw_golden(eng, golden):
             assert np.array_equal(p, rp[u])
 
 
-@pytest.mark.parametrize("S,M", [(5, 4), (8, 16)])
-def test_forward_backward_vs_oracle(eng, S, M):
+@pytest.mark.parametrize("banded", [False, True])
+@pytest.mark.parametrize("S,M", [(5, 4), (8, 16), (3, 2), (12, 2), (20, 2)])
+def test_forward_backward_vs_oracle(eng, S, M, banded):
+    """Both forward-backward kernels (generic CSR: banded=False; one lane per state, 32 / pow2(S) utterances per warp:
+    banded=True) against the float64 oracle: -log Z, state posteriors, summed edge posteriors."""
     from srb200 import synth
     from srb200.graph import GraphBatch, StateGraph
     models, base = synth.make_models(41, W=3, S=S, M=M)
@@ -134,7 +137,8 @@ def test_forward_backward_vs_oracle(eng, S, M):
     E = dev_E(eng, X, models)
     graphs = [StateGraph(m[3], np.arange(S) + S * w) for w, m in enumerate(models)]
     gb = GraphBatch(graphs, E.device)
-    gamma, ws, nlz, xi = eng.forward_backward(E, off, gb, utt_graph=words.astype(np.int32), want_xi=True)
+    assert gb.banded
+    gamma, ws, nlz, xi = eng.forward_backward(E, off, gb, utt_graph=words.astype(np.int32), want_xi=True, banded=banded)
     gamma, nlz, xi = gamma.cpu().numpy(), nlz.cpu().numpy(), xi.cpu().numpy()
     xi_ref = np.zeros_like(xi)
     for u in range(len(off) - 1):
