@@ -179,88 +179,131 @@ gmm_stats_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t *_
 // ---- soft mode (Baum-Welch): frames [row0, row0+nrows) belong to ONE word whose S states carry the posteriors
 // gamma[n, s] (K4).  Group (s, m) receives weight gamma[n,s] * p_m with p_m the within-state posterior over the
 // first ncomp components (same log-domain arithmetic as gmm_stats_kernel).  States with gamma below `gmin` are
-// skipped (a left-to-right model puts almost all mass on one or two states per frame).  Each warp owns a private
-// [S*ncomp, row] block of shared memory (plain read-modify-write, no atomics, deterministic); the CTA adds its
-// warps' blocks in a fixed order into its private global slice, laid out [S*M, row] like the final statistics.
+// skipped (a left-to-right model puts almost all mass on a few states per frame).
+// A warp walks a chunk of frames.  Its lanes are NCP = pow2(ncomp) groups of LPC = 32 / NCP lanes: group m scores and
+// accumulates component m, lane dl of a group owns the dimensions dl, dl + LPC, ...  (D = 39, ncomp = 4: 5 dimensions
+// per lane, 39 of 40 lane slots used; the former lanes-over-dimensions layout ran 4 components x 2 half-empty passes
+// with a full warp reduction each).  Row strides of the shared tables are = +-LPC mod 32, so the groups hit disjoint
+// banks.  The frame's features and its posterior row are fetched one frame ahead.  Each warp owns a private
+// [S*ncomp, rowp] block of shared memory (plain read-modify-write, no atomics, deterministic); the CTA adds its warps'
+// blocks in a fixed order into its private global slice, laid out [S*M, row] like the final statistics.
+__host__ __device__ inline int soft_stride(int n, int lpc) {       // smallest multiple of lpc >= n that is +-lpc mod 32
+    int v = (n + lpc - 1) / lpc * lpc;
+    while (v % 32 != lpc % 32 && v % 32 != (32 - lpc) % 32) v += lpc;
+    return v;
+}
+
+template <int NCP>
 __global__ void __launch_bounds__(SW * 32)
 gmm_stats_soft_kernel(const float *__restrict__ X, int64_t row0, int64_t nrows, int D, const float *__restrict__ gamma,
                       int S, int M, int ncomp, const double *__restrict__ mu, const double *__restrict__ var,
                       const double *__restrict__ lc, float gmin, float *__restrict__ partial) {
+    constexpr int LPC = 32 / NCP, KMAX = 64 / LPC;
     extern __shared__ float ssm[];
-    const int row = 2 * D + 3, GW = S * ncomp;
-    float *mean_s = ssm, *hiv_s = mean_s + GW * D, *lc_s = hiv_s + GW * D, *part = lc_s + ((GW + 3) & ~3);
+    const int row = 2 * D + 3, GW = S * ncomp, Dp = soft_stride(D, LPC), rowp = soft_stride(row, LPC);
+    float *mean_s = ssm, *hiv_s = mean_s + GW * Dp, *lc_s = hiv_s + GW * Dp, *part = lc_s + ((GW + 3) & ~3);
     const int lane = threadIdx.x & 31, wq = threadIdx.x >> 5;
-    for (int i = threadIdx.x; i < GW * D; i += blockDim.x) {
-        const int s = i / (ncomp * D), m = (i / D) % ncomp, d = i % D;
-        const size_t g = (size_t)s * M + m;
-        mean_s[i] = (float)mu[g * D + d];
-        hiv_s[i] = (float)(-0.5 / var[g * D + d]);
+    for (int i = threadIdx.x; i < GW * Dp; i += blockDim.x) {
+        const int gi = i / Dp, d = i - gi * Dp;
+        const size_t g = (size_t)(gi / ncomp) * M + gi % ncomp;
+        mean_s[i] = d < D ? (float)mu[g * D + d] : 0.f;
+        hiv_s[i] = d < D ? (float)(-0.5 / var[g * D + d]) : 0.f;       // zero beyond D: padded dimensions add nothing
     }
     for (int i = threadIdx.x; i < GW; i += blockDim.x) lc_s[i] = (float)lc[(size_t)(i / ncomp) * M + i % ncomp];
-    for (int i = threadIdx.x; i < SW * GW * row; i += blockDim.x) part[i] = 0.f;
+    for (int i = threadIdx.x; i < SW * GW * rowp; i += blockDim.x) part[i] = 0.f;
     __syncthreads();
-    float *mine = part + (size_t)wq * GW * row;
-    const int d0 = lane, d1 = lane + 32;
-    const bool h0 = d0 < D, h1 = d1 < D;
+    float *mine = part + (size_t)wq * GW * rowp;
+    const int m = lane / LPC, dl = lane % LPC, mm = min(m, ncomp - 1);
+    const bool has = m < ncomp;
     const int64_t wg = (int64_t)blockIdx.x * SW + wq, nw = (int64_t)gridDim.x * SW;
     for (int64_t c0 = wg * SCH; c0 < nrows; c0 += nw * SCH) {
-        const int64_t c1 = min(nrows, c0 + SCH);
-        for (int64_t n = row0 + c0; n < row0 + c1; ++n) {
-            const float xa = h0 ? X[n * D + d0] : 0.f, xb = h1 ? X[n * D + d1] : 0.f;
-            for (int s = 0; s < S; ++s) {
-                const float g = gamma[n * S + s];
-                if (!(g > gmin)) continue;                               // warp uniform
-                float ll[MAXC], e0[MAXC], e1[MAXC];
-                float mx = -CUDART_INF_F;
+        const int64_t nb = row0 + c0, ne = row0 + min(nrows, c0 + SCH);
+        float xn[KMAX], gn = 0.f;
 #pragma unroll
-                for (int m = 0; m < MAXC; ++m) {
-                    if (m < ncomp) {
-                        const int o = (s * ncomp + m) * D;
-                        e0[m] = h0 ? xa - mean_s[o + d0] : 0.f;
-                        e1[m] = h1 ? xb - mean_s[o + d1] : 0.f;
-                        const float part_ll = (h0 ? e0[m] * e0[m] * hiv_s[o + d0] : 0.f) +
-                                              (h1 ? e1[m] * e1[m] * hiv_s[o + d1] : 0.f);
-                        ll[m] = wsum(part_ll) + lc_s[s * ncomp + m];
-                        mx = fmaxf(mx, ll[m]);
+        for (int k = 0; k < KMAX; ++k) {
+            xn[k] = 0.f;
+            if (k * LPC < D && k * LPC + dl < D) xn[k] = X[nb * D + k * LPC + dl];
+        }
+        if (lane < S) gn = gamma[nb * S + lane];
+        for (int64_t n = nb; n < ne; ++n) {
+            float x[KMAX];
+            const float g0 = gn;
+#pragma unroll
+            for (int k = 0; k < KMAX; ++k) x[k] = xn[k];
+            if (n + 1 < ne) {
+#pragma unroll
+                for (int k = 0; k < KMAX; ++k)
+                    if (k * LPC < D && k * LPC + dl < D) xn[k] = X[(n + 1) * D + k * LPC + dl];
+                if (lane < S) gn = gamma[(n + 1) * S + lane];
+            }
+            for (int sb = 0; sb < S; sb += 32) {
+                const float gl = sb == 0 ? g0 : (sb + lane < S ? gamma[n * S + sb + lane] : 0.f);
+                unsigned todo = __ballot_sync(0xffffffffu, sb + lane < S && gl > gmin);
+                while (todo) {                                           // states in ascending order, warp uniform
+                    const int bit = __ffs(todo) - 1;
+                    todo &= todo - 1;
+                    const int s = sb + bit;
+                    const float g = __shfl_sync(0xffffffffu, gl, bit);
+                    const float *mp = mean_s + (size_t)(s * ncomp + mm) * Dp + dl;
+                    const float *hp = hiv_s + (size_t)(s * ncomp + mm) * Dp + dl;
+                    float e[KMAX], acc = 0.f;
+#pragma unroll
+                    for (int k = 0; k < KMAX; ++k) {
+                        e[k] = 0.f;
+                        if (k * LPC < D) {
+                            e[k] = x[k] - mp[k * LPC];                   // 0 - 0 beyond D
+                            acc = fmaf(e[k] * e[k], hp[k * LPC], acc);
+                        }
                     }
-                }
-                float den = 0.f;
 #pragma unroll
-                for (int m = 0; m < MAXC; ++m)
-                    if (m < ncomp) {
-                        ll[m] = (mx > -CUDART_INF_F) ? __expf(ll[m] - mx) : 0.f;
-                        den += ll[m];
-                    }
-                const float inv = den > 0.f ? g / den : 0.f;
+                    for (int d = LPC >> 1; d; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+                    const float ll = has ? acc + lc_s[s * ncomp + mm] : -CUDART_INF_F;
+                    float mx = ll;
 #pragma unroll
-                for (int m = 0; m < MAXC; ++m)
-                    if (m < ncomp) {
-                        const float p = ll[m] * inv;
-                        float *r = mine + (size_t)(s * ncomp + m) * row;
-                        if (lane == 0) {
+                    for (int d = LPC; d < 32; d <<= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+                    const float pe = (mx > -CUDART_INF_F) ? __expf(ll - mx) : 0.f;
+                    float den = pe;
+#pragma unroll
+                    for (int d = LPC; d < 32; d <<= 1) den += __shfl_xor_sync(0xffffffffu, den, d);
+                    const float p = pe * (den > 0.f ? g / den : 0.f);
+                    if (has) {
+                        float *r = mine + (size_t)(s * ncomp + m) * rowp;
+                        if (dl == 0) {
                             r[0] += p;
                             if (m == 0) r[2 * D + 1] += g;
                         }
-                        if (h0) {
-                            r[1 + d0] = fmaf(p, e0[m], r[1 + d0]);
-                            r[1 + D + d0] = fmaf(p * e0[m], e0[m], r[1 + D + d0]);
-                        }
-                        if (h1) {
-                            r[1 + d1] = fmaf(p, e1[m], r[1 + d1]);
-                            r[1 + D + d1] = fmaf(p * e1[m], e1[m], r[1 + D + d1]);
-                        }
+#pragma unroll
+                        for (int k = 0; k < KMAX; ++k)
+                            if (k * LPC < D && k * LPC + dl < D) {
+                                const int d = k * LPC + dl;
+                                r[1 + d] = fmaf(p, e[k], r[1 + d]);
+                                r[1 + D + d] = fmaf(p * e[k], e[k], r[1 + D + d]);
+                            }
                     }
+                }
             }
         }
     }
     __syncthreads();
     float *slice = partial + (size_t)blockIdx.x * S * M * row;
     for (int i = threadIdx.x; i < GW * row; i += blockDim.x) {
-        float t = 0.f;
-        for (int q = 0; q < SW; ++q) t += part[(size_t)q * GW * row + i];
         const int gi = i / row, j = i - gi * row;
+        float t = 0.f;
+        for (int q = 0; q < SW; ++q) t += part[((size_t)q * GW + gi) * rowp + j];
         slice[(size_t)((gi / ncomp) * M + gi % ncomp) * row + j] = t;
     }
+}
+
+template <int NCP>
+static cudaError_t launch_stats_soft(int grid, size_t bytes, cudaStream_t st, const float *X, int64_t row0, int64_t nrows,
+                                     int D, const float *gamma, int S, int M, int ncomp, const double *mu,
+                                     const double *var, const double *lc, float gmin, float *partial) {
+    cudaError_t rc = cudaFuncSetAttribute(gmm_stats_soft_kernel<NCP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)bytes);
+    if (rc != cudaSuccess) return rc;
+    gmm_stats_soft_kernel<NCP><<<grid, SW * 32, bytes, st>>>(X, row0, nrows, D, gamma, S, M, ncomp, mu, var, lc, gmin,
+                                                             partial);
+    return cudaGetLastError();
 }
 
 // out[i] (+)= sum_p partial[p][i]  in double, fixed order
@@ -417,15 +460,23 @@ int srb_gmm_stats_soft(const float *X, int64_t N, int64_t row0, int64_t nrows, i
     const int grid = stats_grid();
     SRB_REQUIRE(grid > 0, SRB_ENODEVICE, "no CUDA device");
     const int row = 2 * D + 3, GW = S * ncomp;
-    const size_t bytes = sizeof(float) * ((size_t)2 * GW * D + ((GW + 3) & ~3) + (size_t)SW * GW * row);
+    const int ncp = ncomp <= 1 ? 1 : ncomp <= 2 ? 2 : ncomp <= 4 ? 4 : 8, lpc = 32 / ncp;
+    const size_t bytes = sizeof(float) * ((size_t)2 * GW * soft_stride(D, lpc) + ((GW + 3) & ~3) +
+                                          (size_t)SW * GW * soft_stride(row, lpc));
     SRB_REQUIRE(bytes <= (size_t)smem_optin(), SRB_EUNSUPPORTED,
                 "srb_gmm_stats_soft: %d states x %d components need %zu B shared memory", S, ncomp, bytes);
     const int64_t len = (int64_t)S * M * row;
     cudaStream_t st = (cudaStream_t)stream;
     SRB_CUDA(cudaMemsetAsync(partial, 0, sizeof(float) * len * grid, st));
-    SRB_CUDA(cudaFuncSetAttribute(gmm_stats_soft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-    gmm_stats_soft_kernel<<<grid, SW * 32, bytes, st>>>(X, row0, nrows, D, gamma, S, M, ncomp, mu, var, lc, (float)gmin,
-                                                       partial);
+    const float gm = (float)gmin;
+    if (ncp == 1)
+        SRB_CUDA(launch_stats_soft<1>(grid, bytes, st, X, row0, nrows, D, gamma, S, M, ncomp, mu, var, lc, gm, partial));
+    else if (ncp == 2)
+        SRB_CUDA(launch_stats_soft<2>(grid, bytes, st, X, row0, nrows, D, gamma, S, M, ncomp, mu, var, lc, gm, partial));
+    else if (ncp == 4)
+        SRB_CUDA(launch_stats_soft<4>(grid, bytes, st, X, row0, nrows, D, gamma, S, M, ncomp, mu, var, lc, gm, partial));
+    else
+        SRB_CUDA(launch_stats_soft<8>(grid, bytes, st, X, row0, nrows, D, gamma, S, M, ncomp, mu, var, lc, gm, partial));
     reduce_partials_kernel<<<(int)((len + 255) / 256), 256, 0, st>>>(partial, grid, len, out, accumulate);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
