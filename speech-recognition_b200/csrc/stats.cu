@@ -18,6 +18,7 @@ namespace srb {
 
 constexpr int SW = 8;          // warps per CTA
 constexpr int SCH = 128;       // frames per warp chunk
+constexpr int SCH_SOFT = 32;   // soft counts: no runs to keep, shorter chunks balance the ~3 chunks a warp gets per word
 constexpr int MAXC = 8;        // components per state handled in registers by the GMM mode
 
 __device__ __forceinline__ float wsum(float v) {
@@ -216,8 +217,8 @@ gmm_stats_soft_kernel(const float *__restrict__ X, int64_t row0, int64_t nrows, 
     const int m = lane / LPC, dl = lane % LPC, mm = min(m, ncomp - 1);
     const bool has = m < ncomp;
     const int64_t wg = (int64_t)blockIdx.x * SW + wq, nw = (int64_t)gridDim.x * SW;
-    for (int64_t c0 = wg * SCH; c0 < nrows; c0 += nw * SCH) {
-        const int64_t nb = row0 + c0, ne = row0 + min(nrows, c0 + SCH);
+    for (int64_t c0 = wg * SCH_SOFT; c0 < nrows; c0 += nw * SCH_SOFT) {
+        const int64_t nb = row0 + c0, ne = row0 + min(nrows, c0 + SCH_SOFT);
         float xn[KMAX], gn = 0.f;
 #pragma unroll
         for (int k = 0; k < KMAX; ++k) {

@@ -62,10 +62,13 @@ def numpy_iteration(X, off, words, models, S, ncomp):
     return mu, var, w, np.stack(trans), nlz_sum / len(words)
 
 
-def test_baum_welch_iteration():
+@pytest.mark.parametrize("S,M,ncomp", [(4, 4, 2), (8, 8, 4), (5, 4, 3), (3, 8, 8), (6, 2, 1)])
+def test_baum_welch_iteration(S, M, ncomp):
+    """ncomp = 1, 2, 3 (padded lane group), 4, 8 cover every lane-group width of the soft-count kernel; S = 3 .. 8 the
+    4- and 8-lane groups of the banded forward-backward kernel."""
     from srb200 import engine, synth
     from srb200.trainer import BaumWelchTrainer, sort_by_word
-    W, S, M, ncomp = 2, 4, 4, 2
+    W = 2
     models, base = synth.make_models(81, W=W, S=S, M=M)
     X, off, words = synth.make_utterances(82, base, 24, ragged=(12, 40), noise=1.1)
     X, off, words, _ = sort_by_word(X, off, words)
@@ -86,11 +89,12 @@ def test_baum_welch_iteration():
     assert tr.mean_neg_log_z() <= c1 + 1e-3
 
 
-def test_soft_stats_reduce_to_hard_counts():
+@pytest.mark.parametrize("M,ncomp", [(4, 2), (4, 4), (4, 1), (4, 3), (8, 8), (8, 5)])
+def test_soft_stats_reduce_to_hard_counts(M, ncomp):
     """gamma = 0/1 indicator of an alignment => srb_gmm_stats_soft == srb_gmm_stats (which is pinned to GMM.em)."""
     import torch
     from srb200 import engine, lib, synth
-    W, S, M, ncomp = 1, 5, 4, 2
+    W, S = 1, 5
     models, base = synth.make_models(91, W=W, S=S, M=M)
     X, off, words = synth.make_utterances(92, base, 10, ragged=(20, 50))
     pm, _ = engine.PackedModel.from_words(models)
