@@ -483,7 +483,7 @@ def bench_fb(args, ctx):
     torch.cuda.synchronize()
     ms = float(np.mean(per))
     roof = _roof_fma(S * M * 2 * D_ + S * ncomp * 2 * D_, N, ms, ctx["peak_fma"],
-                     "score_kernel<39> x11 + forward_backward_banded_kernel<8> + gmm_stats_soft_kernel x11",
+                     "classify_tc_kernel<39> (scorer mode, 32 sub-states x 4) x11 + neg_lse_groups_kernel x11 + forward_backward_banded_kernel<8> + gmm_stats_soft_kernel<4> x11",
                      "9984 FMA/frame scoring (8 states x 16 x 2*39) + up to 8 x 4 x 2*39 soft accumulation; "
                      "22 log-add arcs per frame, twice")
     roof["phase_ms"] = {k: ev[i].elapsed_time(ev[i + 1]) for i, k in enumerate(names)}

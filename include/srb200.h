@@ -66,6 +66,11 @@ int srb_gmm_score_rows(const float *X, int64_t N, int64_t row0, int64_t nrows, i
                        const float *shift, int R, int Mp, float *E, int64_t ldE, float *best_cost, int32_t *best_state,
                        float *comp, void *stream);
 
+/* E[n, r] = -log sum_j exp(-P[n, r*J + j]), P float[N, R*J] dense: merges the costs of J sub-states into their state.
+ * With it srb_gmm_score_tc (4 Gaussians per column group) scores states of 4*J Gaussians: the packed model of R states
+ * x 4*J Gaussians IS the packed model of R*J states x 4 (same ab / c memory), see BaumWelchTrainer.e_step. */
+int srb_neg_lse_groups(const float *P, int64_t N, int R, int J, float *E, int64_t ldE, void *stream);
+
 /* ---- fused isolated-word classifier (core.py:79-87 over hmm.py:126-135 over decode.py:80-146) ----
  * W word models of S states each (packed model has R = W*S states, word-major); trans float[W,S,S] with
  * trans[w,i,j] = cost j -> i, +inf = none (decode.py:86-87).  Start in state 0 at frame 0

@@ -181,6 +181,27 @@ static int set_smem(K kernel, size_t bytes) {
                       "cudaFuncSetAttribute(MaxDynamicSharedMemorySize)");
 }
 
+// E[n, r] = -log sum_j exp(-P[n, r*J + j]): the cost of a state whose Gaussians were scored as J sub-states of 4 (the
+// tensor-core scorer handles 4 Gaussians per column group; a 16-Gaussian state is 4 of them).  One thread per (n, r).
+__global__ void neg_lse_groups_kernel(const float *__restrict__ P, int64_t N, int R, int J, float *__restrict__ E,
+                                      int64_t ldE) {
+    const int64_t total = N * R;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t n = i / R;
+        const int r = (int)(i - n * R);
+        const float *p = P + i * J;
+        float m = CUDART_INF_F;
+        for (int j = 0; j < J; ++j) m = fminf(m, p[j]);
+        float v = m;
+        if (m < CUDART_INF_F) {
+            float sum = 0.f;
+            for (int j = 0; j < J; ++j) sum += __expf(m - p[j]);
+            v = m - __logf(sum);
+        }
+        E[n * ldE + r] = v;
+    }
+}
+
 }  // namespace srb
 
 using namespace srb;
@@ -255,6 +276,18 @@ int srb_classify(const float *X, const int32_t *utt_off, int32_t B, int64_t N, i
         classify_kernel<kD><<<grid, NT, bytes, (cudaStream_t)stream>>>(X, utt_off, B, N, ab, c, shift, W, S, Mp, trans,
                                                                        final_cost, label);
     });
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+int srb_neg_lse_groups(const float *P, int64_t N, int R, int J, float *E, int64_t ldE, void *stream) {
+    SRB_REQUIRE(N >= 0 && R > 0 && J > 0 && ldE >= R, SRB_EINVAL, "srb_neg_lse_groups: bad sizes");
+    if (N == 0) return SRB_OK;
+    SRB_REQUIRE(P && E, SRB_EINVAL, "srb_neg_lse_groups: null pointer");
+    int64_t grid = (N * R + 255) / 256;
+    const int64_t cap = (int64_t)sm_count() * 32;
+    if (grid > cap) grid = cap;
+    neg_lse_groups_kernel<<<(int)grid, 256, 0, (cudaStream_t)stream>>>(P, N, R, J, E, ldE);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }

@@ -246,7 +246,7 @@ class BaumWelchTrainer:
     All words must share the state count S (continuous_speech.py:27-28 makes the same assumption)."""
 
     def __init__(self, X, off, words, pm, trans, S, ncomp, group=None, var_floor=1e-6, gmin=1e-7,
-                 update_transitions=True):
+                 update_transitions=True, tensor=None):
         X, off, words, self.order = sort_by_word(np.asarray(X), np.asarray(off), words)
         self.dev = engine.device()
         self.X = engine.as_frames(X)
@@ -266,6 +266,19 @@ class BaumWelchTrainer:
         self.row = L.srb_stats_row(pm.D)
         self.G = pm.R * pm.M
         self.nnz = int(self.gb.edge_off[-1])
+        # tensor-core scoring (srb_gmm_score_tc, 4 Gaussians per column group): a state of Mp Gaussians is scored as
+        # J = Mp/4 sub-states whose costs srb_neg_lse_groups merges.  tensor: None = when covered and worth the
+        # per-CTA model staging, True = required, False = FFMA scorer.
+        self.J = pm.Mp // 4 if pm.Mp % 4 == 0 else 0
+        ok = self.J > 0 and bool(L.srb_gmm_score_tc_supported(pm.D, S * max(self.J, 1), 4))
+        if tensor and not ok:
+            raise ValueError("BaumWelchTrainer: the tensor-core scorer does not cover this model")
+        self.tensor = bool(ok and (tensor or (tensor is None and self.N >= 8 * engine.TC_SCORE_MIN_FRAMES)))
+        if self.tensor:
+            self.tc_floats = int(L.srb_tc_model_floats(S * self.J, 4, pm.D))
+            self.tcb = torch.empty(self.W * self.tc_floats, dtype=torch.float32, device=self.dev)
+            self.P = self.E if self.J == 1 else torch.empty((max(self.N, 1), S * self.J), dtype=torch.float32,
+                                                            device=self.dev)
         # [statistics | xi per edge | sum of -log Z, utterances]
         self.stats = torch.zeros(self.G * self.row + self.nnz + 2, dtype=torch.float64, device=self.dev)
         self.partial = torch.empty(L.srb_stats_parts() * S * pm.M * self.row, dtype=torch.float32, device=self.dev)
@@ -279,11 +292,24 @@ class BaumWelchTrainer:
         pm, S, L, p = self.pm, self.S, _l.load(), _l.ptr
         st = _l.stream_ptr()
         blk = S * pm.Mp * pm.D * 2
+        RJ = S * self.J if self.tensor else 0
         for w, (r0, r1) in enumerate(self.word_rows):
-            if r1 > r0:
-                _l.check(L.srb_gmm_score_rows(p(self.X), self.N, r0, r1 - r0, pm.D, pm.ab[w * blk:].data_ptr(),
-                                              pm.c[w * S * pm.Mp:].data_ptr(), p(pm.shift), S, pm.Mp, p(self.E), S,
-                                              None, None, None, st))
+            if r1 <= r0:
+                continue
+            ab_w, c_w = pm.ab[w * blk:].data_ptr(), pm.c[w * S * pm.Mp:].data_ptr()
+            ra = min(r1, (r0 + 3) & ~3) if self.tensor else r1        # the tensor-core scorer reads X in 16-byte units
+            if ra > r0:
+                _l.check(L.srb_gmm_score_rows(p(self.X), self.N, r0, ra - r0, pm.D, ab_w, c_w, p(pm.shift), S, pm.Mp,
+                                              p(self.E), S, None, None, None, st))
+            if r1 > ra:
+                tcb_w = self.tcb[w * self.tc_floats:]
+                _l.check(L.srb_pack_model_tc(ab_w, c_w, RJ, 4, pm.D, tcb_w.data_ptr(), st))
+                co = engine.score_chunk_offsets(r1 - ra, self.dev)
+                _l.check(L.srb_gmm_score_tc(self.X[ra:].data_ptr(), r1 - ra, pm.D, tcb_w.data_ptr(), p(pm.shift), RJ, 4,
+                                            p(co), co.numel() - 1, self.P[ra:].data_ptr(), RJ, st))
+                if self.J > 1:
+                    _l.check(L.srb_neg_lse_groups(self.P[ra:].data_ptr(), r1 - ra, S, self.J, self.E[ra:].data_ptr(), S,
+                                                  st))
         self.gamma, _, self.nlz, self.xi = engine.forward_backward(self.E, self.off, self.gb, utt_graph=self.words,
                                                                    want_xi=True)
         return self.gamma

@@ -62,8 +62,9 @@ def numpy_iteration(X, off, words, models, S, ncomp):
     return mu, var, w, np.stack(trans), nlz_sum / len(words)
 
 
-@pytest.mark.parametrize("S,M,ncomp", [(4, 4, 2), (8, 8, 4), (5, 4, 3), (3, 8, 8), (6, 2, 1)])
-def test_baum_welch_iteration(S, M, ncomp):
+@pytest.mark.parametrize("S,M,ncomp,tensor", [(4, 4, 2, False), (8, 8, 4, False), (5, 4, 3, False), (3, 8, 8, False),
+                                               (6, 2, 1, False), (8, 16, 4, True), (5, 4, 2, True), (4, 8, 4, True)])
+def test_baum_welch_iteration(S, M, ncomp, tensor):
     """ncomp = 1, 2, 3 (padded lane group), 4, 8 cover every lane-group width of the soft-count kernel; S = 3 .. 8 the
     4- and 8-lane groups of the banded forward-backward kernel."""
     from srb200 import engine, synth
@@ -73,7 +74,8 @@ def test_baum_welch_iteration(S, M, ncomp):
     X, off, words = synth.make_utterances(82, base, 24, ragged=(12, 40), noise=1.1)
     X, off, words, _ = sort_by_word(X, off, words)
     pm, _ = engine.PackedModel.from_words(models)
-    tr = BaumWelchTrainer(X, off, words, pm, np.stack([m[3] for m in models]), S, ncomp, gmin=0.0)
+    tr = BaumWelchTrainer(X, off, words, pm, np.stack([m[3] for m in models]), S, ncomp, gmin=0.0, tensor=tensor)
+    assert bool(tr.tensor) == tensor           # tensor: states scored as Mp/4 sub-states on the tcgen05 scorer
     tr.em_iteration()
     mu, var, w, trans, nlz = numpy_iteration(X.astype(np.float64), off.astype(np.int64), words, models, S, ncomp)
     np.testing.assert_allclose(tr.mean_neg_log_z(), nlz, rtol=1e-5)
