@@ -321,7 +321,8 @@ viterbi_banded_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *_
 // ------------------------------------------------------------------------------------------------ K2, banded, one graph
 // The same three sweeps for a batch whose utterances all use ONE graph (connected-digit decoding, main.py:40-60): the
 // graph's tables are packed once per CTA into shared memory -- per state {a2, a1, a0, meta}, meta = the four 2-bit
-// back-pointer codes | entry flag << 8 | (emit + 1) << 9 (0: NES) -- next to the NES predecessor lists and the entry
+// back-pointer codes | entry flag << 8 | emits flag << 9 | emit << 14 (bits 12.. = byte offset of the emission in its
+// row; 0 for a NES, so meta >> 9 != 0 iff the state emits) -- next to the NES predecessor lists and the entry
 // list, so a state update is one 16-byte and three 4-byte shared loads, the emission gather and two stores instead of
 // seven table loads with 64-bit address arithmetic.  The NES sweep gives every NES a group of lanes (first minimum
 // kept across the group by (cost, position) order).  Outputs are bit-identical to viterbi_banded_kernel.
@@ -359,13 +360,13 @@ __device__ __forceinline__ void banded_column(const BandState *tab, const BandEn
         const uint32_t meta = t.meta;
         const bool emits = (meta >> 9) != 0;                         // else a NES (sweep 2) or padding
         const float t2 = prev[r - 2] + t.a2, t1 = prev[r - 1] + t.a1, t0 = prev[r] + t.a0;
-        float best = INF;
-        uint32_t code = 0;
-        if (t2 < best) { best = t2; code = meta & 3; }
-        if (t1 < best) { best = t1; code = (meta >> 2) & 3; }
-        if (t0 < best) { best = t0; code = (meta >> 4) & 3; }
+        float best = t2;                                             // first minimum in list order r-2, r-1, r; the
+        uint32_t sh = 0;                                             // code is cut out of meta once, after the choice
+        if (t1 < best) { best = t1; sh = 2; }
+        if (t0 < best) { best = t0; sh = 4; }
+        uint32_t code = best < INF ? (meta >> sh) & 3 : 0;
         const bool entry = (meta & 0x100) != 0;
-        const float e = Erow[emits ? (meta >> 9) - 1 : 0];
+        const float e = *reinterpret_cast<const float *>(reinterpret_cast<const char *>(Erow) + (meta >> 12));
         float v = entry ? best : best + e;                           // entry states get their emission in sweep 3
         if (FIRST && r == 0) {                                       // decode.py:99-100
             v = e;
@@ -492,7 +493,7 @@ __device__ __forceinline__ void banded_column(const BandState *tab, const BandEn
             best = cand;
             code = cn;
         }
-        cur[r] = best + Erow[(meta >> 9) - 1];
+        cur[r] = best + Erow[meta >> 14];
         bpc[r] = (uint8_t)code;
     }
     __syncwarp();
@@ -667,7 +668,7 @@ viterbi_banded1_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *
         t.a1 = F.band[r * 3 + 1];
         t.a0 = F.band[r * 3 + 2];
         t.meta = (cd & 3) | (((cd >> 8) & 3) << 2) | (((cd >> 16) & 3) << 4) | (((cd >> 24) & 3) << 6) |
-                 (F.entry_nes[r] >= 0 ? 0x100u : 0u) | ((uint32_t)(em + 1) << 9);
+                 (F.entry_nes[r] >= 0 ? 0x100u : 0u) | (em >= 0 ? 0x200u | ((uint32_t)em << 14) : 0u);
         tab[r] = t;
     }
     for (int i = tid; i < Q; i += VW * 32) {
@@ -735,7 +736,7 @@ viterbi_banded1_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *
             const uint32_t meta = tab[e.rn & 0xffffu].meta;
             lw.ern[h] = e.rn;
             lw.ecost[h] = e.cost;
-            lw.emeta[h] = (((meta >> 6) & 3) << 16) | ((meta >> 9) - 1);
+            lw.emeta[h] = (((meta >> 6) & 3) << 16) | (meta >> 14);
         }
     }
 
@@ -1234,7 +1235,7 @@ int srb_viterbi_banded(const float *E, int64_t ldE, const int32_t *utt_off, int3
     F.g_entry_off = g_entry_off;
     F.entry_state = entry_state;
     const size_t bytes1 = banded1_smem_bytes(Rmax);
-    if (!utt_graph && bytes1 <= (size_t)smem_optin() / 2) {
+    if (!utt_graph && bytes1 <= (size_t)smem_optin() / 2 && ldE <= (1 << 18)) {   // emission column in 18 bits of meta
         // one graph for the whole batch: its tables live in shared memory (viterbi_banded1_kernel)
         SRB_CUDA(cudaFuncSetAttribute(viterbi_banded1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes1));
         viterbi_banded1_kernel<<<(int)grid, VW * 32, bytes1, (cudaStream_t)stream>>>(
