@@ -194,55 +194,6 @@ __host__ __device__ inline int soft_stride(int n, int lpc) {       // smallest m
     return v;
 }
 
-// posterior weight gamma * p_m of this lane group's component for state s, e[k] = x - mean of the lane's dimensions
-template <int NCP>
-__device__ __forceinline__ float soft_state_posterior(int s, float g, const float (&x)[64 / (32 / NCP)],
-                                                      float (&e)[64 / (32 / NCP)], const float *mean_s,
-                                                      const float *hiv_s, const float *lc_s, int ncomp, int mm, bool has,
-                                                      int dl, int D, int Dp) {
-    constexpr int LPC = 32 / NCP, KMAX = 64 / LPC;
-    const float *mp = mean_s + (size_t)(s * ncomp + mm) * Dp + dl;
-    const float *hp = hiv_s + (size_t)(s * ncomp + mm) * Dp + dl;
-    float acc = 0.f;
-#pragma unroll
-    for (int k = 0; k < KMAX; ++k) {
-        e[k] = 0.f;
-        if (k * LPC < D) {
-            e[k] = x[k] - mp[k * LPC];                                   // 0 - 0 beyond D
-            acc = fmaf(e[k] * e[k], hp[k * LPC], acc);
-        }
-    }
-#pragma unroll
-    for (int d = LPC >> 1; d; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
-    const float ll = has ? acc + lc_s[s * ncomp + mm] : -CUDART_INF_F;
-    float mx = ll;
-#pragma unroll
-    for (int d = LPC; d < 32; d <<= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, d));
-    const float pe = (mx > -CUDART_INF_F) ? __expf(ll - mx) : 0.f;
-    float den = pe;
-#pragma unroll
-    for (int d = LPC; d < 32; d <<= 1) den += __shfl_xor_sync(0xffffffffu, den, d);
-    return pe * (den > 0.f ? g / den : 0.f);
-}
-
-// r: this warp's private statistics row of (state, component m)
-template <int NCP>
-__device__ __forceinline__ void soft_accumulate(float *r, float p, float g, const float (&e)[64 / (32 / NCP)], int m,
-                                                int dl, int D) {
-    constexpr int LPC = 32 / NCP, KMAX = 64 / LPC;
-    if (dl == 0) {
-        r[0] += p;
-        if (m == 0) r[2 * D + 1] += g;
-    }
-#pragma unroll
-    for (int k = 0; k < KMAX; ++k)
-        if (k * LPC < D && k * LPC + dl < D) {
-            const int d = k * LPC + dl;
-            r[1 + d] = fmaf(p, e[k], r[1 + d]);
-            r[1 + D + d] = fmaf(p * e[k], e[k], r[1 + D + d]);
-        }
-}
-
 template <int NCP>
 __global__ void __launch_bounds__(SW * 32)
 gmm_stats_soft_kernel(const float *__restrict__ X, int64_t row0, int64_t nrows, int D, const float *__restrict__ gamma,
@@ -289,26 +240,46 @@ gmm_stats_soft_kernel(const float *__restrict__ X, int64_t row0, int64_t nrows, 
             for (int sb = 0; sb < S; sb += 32) {
                 const float gl = sb == 0 ? g0 : (sb + lane < S ? gamma[n * S + sb + lane] : 0.f);
                 unsigned todo = __ballot_sync(0xffffffffu, sb + lane < S && gl > gmin);
-                // States in ascending order, TWO per round (warp uniform): their scoring chains (shared loads ->
-                // FMA chain -> 7 shuffles -> exp) are independent and interleave; at 16 warps per SM (the private
-                // statistics blocks fill shared memory) one chain at a time left the issue slots 43 % busy.
-                while (todo) {
-                    const int bit_a = __ffs(todo) - 1;
+                while (todo) {                                           // states in ascending order, warp uniform
+                    const int bit = __ffs(todo) - 1;
                     todo &= todo - 1;
-                    const bool two = todo != 0;
-                    const int bit_b = two ? __ffs(todo) - 1 : bit_a;
-                    todo &= todo - 1;                                    // 0 stays 0
-                    const float g_a = __shfl_sync(0xffffffffu, gl, bit_a);
-                    const float g_b = __shfl_sync(0xffffffffu, gl, bit_b);
-                    float e_a[KMAX], e_b[KMAX];
-                    const float p_a = soft_state_posterior<NCP>(sb + bit_a, g_a, x, e_a, mean_s, hiv_s, lc_s, ncomp, mm, has,
-                                                                dl, D, Dp);
-                    const float p_b = soft_state_posterior<NCP>(sb + bit_b, g_b, x, e_b, mean_s, hiv_s, lc_s, ncomp, mm, has,
-                                                                dl, D, Dp);
+                    const int s = sb + bit;
+                    const float g = __shfl_sync(0xffffffffu, gl, bit);
+                    const float *mp = mean_s + (size_t)(s * ncomp + mm) * Dp + dl;
+                    const float *hp = hiv_s + (size_t)(s * ncomp + mm) * Dp + dl;
+                    float e[KMAX], acc = 0.f;
+#pragma unroll
+                    for (int k = 0; k < KMAX; ++k) {
+                        e[k] = 0.f;
+                        if (k * LPC < D) {
+                            e[k] = x[k] - mp[k * LPC];                   // 0 - 0 beyond D
+                            acc = fmaf(e[k] * e[k], hp[k * LPC], acc);
+                        }
+                    }
+#pragma unroll
+                    for (int d = LPC >> 1; d; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+                    const float ll = has ? acc + lc_s[s * ncomp + mm] : -CUDART_INF_F;
+                    float mx = ll;
+#pragma unroll
+                    for (int d = LPC; d < 32; d <<= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+                    const float pe = (mx > -CUDART_INF_F) ? __expf(ll - mx) : 0.f;
+                    float den = pe;
+#pragma unroll
+                    for (int d = LPC; d < 32; d <<= 1) den += __shfl_xor_sync(0xffffffffu, den, d);
+                    const float p = pe * (den > 0.f ? g / den : 0.f);
                     if (has) {
-                        soft_accumulate<NCP>(mine + (size_t)((sb + bit_a) * ncomp + m) * rowp, p_a, g_a, e_a, m, dl, D);
-                        if (two)
-                            soft_accumulate<NCP>(mine + (size_t)((sb + bit_b) * ncomp + m) * rowp, p_b, g_b, e_b, m, dl, D);
+                        float *r = mine + (size_t)(s * ncomp + m) * rowp;
+                        if (dl == 0) {
+                            r[0] += p;
+                            if (m == 0) r[2 * D + 1] += g;
+                        }
+#pragma unroll
+                        for (int k = 0; k < KMAX; ++k)
+                            if (k * LPC < D && k * LPC + dl < D) {
+                                const int d = k * LPC + dl;
+                                r[1 + d] = fmaf(p, e[k], r[1 + d]);
+                                r[1 + D + d] = fmaf(p * e[k], e[k], r[1 + D + d]);
+                            }
                     }
                 }
             }
