@@ -61,9 +61,12 @@ class PackedModel:
         return self.tcb is not None and bool(_l.load().srb_classify_tc_supported(self.D, W, S, self.Mp))
 
     def scorer_tensor_core_ok(self):
-        """True when srb_gmm_score_tc covers this model (D = 39, 4 Gaussians per state, <= 57 states = 228 Gaussians:
-        the packed model and the cost ring share 227 KB of shared memory)."""
-        return self.tcb is not None and bool(_l.load().srb_gmm_score_tc_supported(self.D, self.R, self.Mp))
+        """True when srb_gmm_score_tc covers this model: D = 39, 4*J Gaussians per state (a state is scored as J
+        sub-states of 4 -- the packed model [R, Mp/4, D, 4, 2] IS the packed model of R*J states x 4 -- and
+        srb_neg_lse_groups merges them), at most 57 sub-states = 228 Gaussians (the packed model and the cost ring
+        share 227 KB of shared memory)."""
+        return (self.tcb is not None and self.Mp % 4 == 0 and
+                bool(_l.load().srb_gmm_score_tc_supported(self.D, self.R * (self.Mp // 4), 4)))
 
     @classmethod
     def from_words(cls, word_models, shift=None):
@@ -108,16 +111,31 @@ def score_chunk_offsets(N, dev):
     return t
 
 
+TC_MERGE_ROWS = 1 << 20         # frames per pass when sub-state costs are merged (bounds the scratch to 228 floats x 1 M)
+
+
 def gmm_score_tc(X, pm, E=None):
-    """K1 on the tensor cores (3xTF32, srb_gmm_score_tc): E[N,R] only."""
+    """K1 on the tensor cores (3xTF32, srb_gmm_score_tc): E[N,R] only.  States of 4*J Gaussians go through a scratch
+    P[rows, R*J] of sub-state costs and srb_neg_lse_groups."""
     X = as_frames(X)
     N = X.shape[0]
     if E is None:
         E = torch.empty((N, pm.R), dtype=torch.float32, device=X.device)
     assert E.is_cuda and E.dtype == torch.float32 and tuple(E.shape) == (N, pm.R) and (N == 0 or E.stride(1) == 1)
-    co = score_chunk_offsets(N, X.device)
-    _l.check(_l.load().srb_gmm_score_tc(_l.ptr(X), N, pm.D, _l.ptr(pm.tcb), _l.ptr(pm.shift), pm.R, pm.Mp, _l.ptr(co),
-                                        co.numel() - 1, E.data_ptr(), E.stride(0) if N else pm.R, _l.stream_ptr()))
+    L, J = _l.load(), pm.Mp // 4
+    if J <= 1:
+        co = score_chunk_offsets(N, X.device)
+        _l.check(L.srb_gmm_score_tc(_l.ptr(X), N, pm.D, _l.ptr(pm.tcb), _l.ptr(pm.shift), pm.R, pm.Mp, _l.ptr(co),
+                                    co.numel() - 1, E.data_ptr(), E.stride(0) if N else pm.R, _l.stream_ptr()))
+        return E
+    RJ = pm.R * J
+    P = torch.empty((min(N, TC_MERGE_ROWS), RJ), dtype=torch.float32, device=X.device)
+    for r0 in range(0, N, TC_MERGE_ROWS):                    # r0 % 4 == 0: X[r0:] stays 16-byte aligned
+        n = min(TC_MERGE_ROWS, N - r0)
+        co = score_chunk_offsets(n, X.device)
+        _l.check(L.srb_gmm_score_tc(X[r0:].data_ptr(), n, pm.D, _l.ptr(pm.tcb), _l.ptr(pm.shift), RJ, 4, _l.ptr(co),
+                                    co.numel() - 1, P.data_ptr(), RJ, _l.stream_ptr()))
+        _l.check(L.srb_neg_lse_groups(P.data_ptr(), n, pm.R, J, E[r0:].data_ptr(), E.stride(0), _l.stream_ptr()))
     return E
 
 

@@ -82,12 +82,34 @@ def test_gmm_score_tensor_core_matches_oracle(eng, W, S, B, T):
         eng.gmm_score(X, pm, want_best=True, tensor=True)
 
 
+@pytest.mark.parametrize("W,S,M,B,T", [(3, 4, 8, 40, 37), (1, 8, 16, 25, 90), (2, 7, 16, 9, 33), (4, 3, 12, 300, 41), (2, 5, 6, 20, 50)])
+def test_gmm_score_tensor_core_sub_states(eng, W, S, M, B, T):
+    """States of 4*J Gaussians on the tcgen05 scorer (J sub-states of 4 + srb_neg_lse_groups) against the oracle and
+    the FFMA scorer."""
+    from srb200 import synth
+    models, base = _models(21, W=W, S=S, M=M)
+    X, off, _ = synth.make_utterances(22, base, B, T=T)
+    pm, _ = eng.PackedModel.from_words(models)
+    assert pm.Mp == (M + 3) // 4 * 4 and pm.scorer_tensor_core_ok()
+    E = eng.gmm_score(X, pm, tensor=True)["E"].cpu().numpy()
+    Eo = orc.emissions(X.astype(np.float64), models, np.arange(W * S), log_domain=True)
+    np.testing.assert_allclose(E, Eo, rtol=RTOL)
+    np.testing.assert_allclose(E, eng.gmm_score(X, pm, tensor=False)["E"].cpu().numpy(), rtol=2e-5)
+    old, eng.TC_MERGE_ROWS = eng.TC_MERGE_ROWS, 64             # several passes over the scratch
+    try:
+        assert np.array_equal(eng.gmm_score(X, pm, tensor=True)["E"].cpu().numpy(), E)
+    finally:
+        eng.TC_MERGE_ROWS = old
+
+
 def test_gmm_score_tensor_core_unsupported_is_loud(eng):
     import torch
     from srb200 import lib as L
-    models, base = _models(5, W=3, S=4, M=8)                       # 8 Gaussians per state: not covered
-    pm, _ = eng.PackedModel.from_words(models)
-    assert not pm.scorer_tensor_core_ok()
+    models, base = _models(5, W=3, S=4, M=8)                       # the C entry takes 4 Gaussians per state only (the
+    pm, _ = eng.PackedModel.from_words(models)                     # engine scores 8 as 2 sub-states of 4, see below)
+    assert pm.scorer_tensor_core_ok()
+    big, _ = _models(5, W=6, S=5, M=8)                             # 240 Gaussians > 228 tensor-core columns
+    assert not eng.PackedModel.from_words(big)[0].scorer_tensor_core_ok()
     assert L.load().srb_gmm_score_tc_supported(39, 58, 4) == 0     # packed model + cost ring > 227 KB of shared memory
     assert L.load().srb_gmm_score_tc_supported(39, 57, 4) == 1
     X = torch.zeros((64, 39), device="cuda")
