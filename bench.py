@@ -441,19 +441,34 @@ def bench_stress(args, ctx):
     bs = torch.empty(N, dtype=torch.int32, device="cuda")
     L_ = ctx["lib"]
 
+    use_tc = not args.ffma
+    launches = 1
+    if use_tc:
+        J = pm.Mp // 4
+        nblocks = -(-R // (57 // J))
+        launches = 2 * nblocks * -(-N // engine.TC_BEST_ROWS)
+
     def step():
-        L_.check(L_.load().srb_gmm_score(L_.ptr(Xd), N, D_, L_.ptr(pm.ab), L_.ptr(pm.c), L_.ptr(pm.shift), R, pm.Mp,
-                                         None, R, L_.ptr(bc), L_.ptr(bs), None, L_.stream_ptr()))
+        if use_tc:
+            engine.gmm_best_tc(Xd, pm, bc, bs)
+        else:
+            L_.check(L_.load().srb_gmm_score(L_.ptr(Xd), N, D_, L_.ptr(pm.ab), L_.ptr(pm.c), L_.ptr(pm.shift), R, pm.Mp,
+                                             None, R, L_.ptr(bc), L_.ptr(bs), None, L_.stream_ptr()))
 
     sampler = ClockSampler(ctx["local"])
     sampler.start()
     total_ms, per = timed_steps(step, args.steps, args.warmup, torch, dist, ctx["world"])
     clocks = sampler.stop()
     ms = float(np.mean(per))
-    roof = _roof_fma(R * M * 2 * D_, N, ms, ctx["peak_fma"], "score_kernel<39>", "4.992 M FMA/frame = 64000 Gaussians x 2*39")
+    roof = _roof_fma(R * M * 2 * D_, N, ms, ctx["peak_fma"],
+                     "classify_tc_kernel<39> (scorer mode, 7 states = 56 sub-states per launch) + merge_best_kernel"
+                     if use_tc else "score_kernel<39>", "4.992 M FMA/frame = 64000 Gaussians x 2*39")
+    if use_tc:
+        roof["note"] = ("tcgen05 3xTF32: algorithmic FP32-equivalent rate over the measured FFMA peak, > 1 = above the "
+                        "CUDA-core roofline; --ffma runs the FP32-FMA scorer")
     return {"metric": "GMM-scored frames/s (2000 states x 32 Gaussians, best state per frame)",
             "value": ctx["world"] * N * args.steps / (total_ms * 1e-3), "unit": "frames/s",
-            "ms_per_step": total_ms / args.steps, "gpu_launches": args.steps, "roofline": roof, "clocks": clocks,
+            "ms_per_step": total_ms / args.steps, "gpu_launches": args.steps * launches, "roofline": roof, "clocks": clocks,
             "_workload": f"stress: 2000 states x 32 Gaussians, {N} frames per GPU", "_frames": N}
 
 

@@ -70,6 +70,12 @@ int srb_gmm_score_rows(const float *X, int64_t N, int64_t row0, int64_t nrows, i
  * With it srb_gmm_score_tc (4 Gaussians per column group) scores states of 4*J Gaussians: the packed model of R states
  * x 4*J Gaussians IS the packed model of R*J states x 4 (same ab / c memory), see BaumWelchTrainer.e_step. */
 int srb_neg_lse_groups(const float *P, int64_t N, int R, int J, float *E, int64_t ldE, void *stream);
+/* Running best state for models too large for one tensor-core launch (BASELINE config 5: 2 000 states x 32): the
+ * states are scored block by block as sub-states (srb_gmm_score_tc on the block's slice of ab / c) and each block's
+ * P[N, Rb*J] is folded into best_cost / best_state (first != 0 on the first block: starts from +inf / state 0;
+ * strict '<' keeps the first minimum like srb_gmm_score).  The cost matrix is never materialised. */
+int srb_merge_best(const float *P, int64_t N, int Rb, int J, int state0, int first, float *best_cost,
+                   int32_t *best_state, void *stream);
 
 /* ---- fused isolated-word classifier (core.py:79-87 over hmm.py:126-135 over decode.py:80-146) ----
  * W word models of S states each (packed model has R = W*S states, word-major); trans float[W,S,S] with

@@ -202,6 +202,32 @@ __global__ void neg_lse_groups_kernel(const float *__restrict__ P, int64_t N, in
     }
 }
 
+// Running best state over blocks of states scored as sub-states: P[n, s*J + j] are the sub-state costs of states
+// state0 .. state0+Rb-1; the state cost is merged as in neg_lse_groups_kernel and replaces best_cost[n] / best_state[n]
+// when strictly smaller (blocks arrive in ascending state order: the first minimum wins, as in score_kernel).
+__global__ void merge_best_kernel(const float *__restrict__ P, int64_t N, int Rb, int J, int state0, int first,
+                                  float *__restrict__ best_cost, int32_t *__restrict__ best_state) {
+    for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < N; n += (int64_t)gridDim.x * blockDim.x) {
+        const float *p = P + n * Rb * J;
+        float bc = first ? CUDART_INF_F : best_cost[n];
+        int bs = first ? 0 : best_state[n];
+        for (int r = 0; r < Rb; ++r, p += J) {
+            float m = CUDART_INF_F;
+            for (int j = 0; j < J; ++j) m = fminf(m, p[j]);
+            if (!(m < bc + 0.75f * (float)J)) continue;                  // -log sum >= m - log J: cannot win
+            float sum = 0.f;
+            for (int j = 0; j < J; ++j) sum += __expf(m - p[j]);
+            const float v = m - __logf(sum);
+            if (v < bc) {
+                bc = v;
+                bs = state0 + r;
+            }
+        }
+        best_cost[n] = bc;
+        best_state[n] = bs;
+    }
+}
+
 }  // namespace srb
 
 using namespace srb;
@@ -288,6 +314,19 @@ int srb_neg_lse_groups(const float *P, int64_t N, int R, int J, float *E, int64_
     const int64_t cap = (int64_t)sm_count() * 32;
     if (grid > cap) grid = cap;
     neg_lse_groups_kernel<<<(int)grid, 256, 0, (cudaStream_t)stream>>>(P, N, R, J, E, ldE);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+int srb_merge_best(const float *P, int64_t N, int Rb, int J, int state0, int first, float *best_cost,
+                   int32_t *best_state, void *stream) {
+    SRB_REQUIRE(N >= 0 && Rb > 0 && J > 0 && J <= 64 && state0 >= 0, SRB_EINVAL, "srb_merge_best: bad sizes");
+    if (N == 0) return SRB_OK;
+    SRB_REQUIRE(P && best_cost && best_state, SRB_EINVAL, "srb_merge_best: null pointer");
+    int64_t grid = (N + 127) / 128;
+    const int64_t cap = (int64_t)sm_count() * 32;
+    if (grid > cap) grid = cap;
+    merge_best_kernel<<<(int)grid, 128, 0, (cudaStream_t)stream>>>(P, N, Rb, J, state0, first, best_cost, best_state);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }

@@ -48,6 +48,7 @@ class PackedModel:
         self.repack()
 
     def repack(self):
+        self.version = getattr(self, "version", 0) + 1               # caches of derived packings key on it
         _l.check(_l.load().srb_pack_model(_l.ptr(self.mu), _l.ptr(self.var), _l.ptr(self.w), _l.ptr(self.shift64),
                                           self.R, self.M, self.D, _l.ptr(self.ab), _l.ptr(self.c),
                                           _l.ptr(self.shift), _l.stream_ptr()))
@@ -137,6 +138,47 @@ def gmm_score_tc(X, pm, E=None):
                                     co.numel() - 1, P.data_ptr(), RJ, _l.stream_ptr()))
         _l.check(L.srb_neg_lse_groups(P.data_ptr(), n, pm.R, J, E[r0:].data_ptr(), E.stride(0), _l.stream_ptr()))
     return E
+
+
+TC_BEST_ROWS = 1 << 18          # frames per pass of gmm_best_tc: the 57-column scratch (60 MB) stays in L2
+
+
+def gmm_best_tc(X, pm, best_cost=None, best_state=None):
+    """Per-frame best state and its cost (srb_gmm_score's best_cost / best_state) for a model of ANY number of states
+    on the tensor cores: blocks of 57 // J states are scored as sub-states of 4 Gaussians (srb_gmm_score_tc on the
+    block's slice of the packed model, split once per model update and cached on pm) and folded into the running
+    minimum by srb_merge_best.  -> (best_cost[N] float32, best_state[N] int32)"""
+    X = as_frames(X)
+    N, dev, L = X.shape[0], X.device, _l.load()
+    J = pm.Mp // 4
+    SB = 57 // J if J else 0
+    if pm.D != 39 or pm.Mp % 4 or SB < 1 or not L.srb_gmm_score_tc_supported(pm.D, min(SB, pm.R) * J, 4):
+        raise ValueError("gmm_best_tc: D = 39 and 4*J <= 228 Gaussians per state needed")
+    SB = min(SB, pm.R)
+    nb = (pm.R + SB - 1) // SB
+    nf = int(L.srb_tc_model_floats(SB * J, 4, pm.D))
+    cache = getattr(pm, "_tc_blocks", None)
+    if cache is None or cache[0] != pm.version:
+        tcb = torch.empty(nb * nf, dtype=torch.float32, device=dev)
+        for b in range(nb):
+            r0, rb = b * SB, min(SB, pm.R - b * SB)
+            _l.check(L.srb_pack_model_tc(pm.ab[r0 * J * pm.D * 8:].data_ptr(), pm.c[r0 * pm.Mp:].data_ptr(), rb * J, 4,
+                                         pm.D, tcb[b * nf:].data_ptr(), _l.stream_ptr()))
+        cache = pm._tc_blocks = (pm.version, tcb)
+    tcb = cache[1]
+    bc = torch.empty(N, dtype=torch.float32, device=dev) if best_cost is None else best_cost
+    bs = torch.empty(N, dtype=torch.int32, device=dev) if best_state is None else best_state
+    P = torch.empty((min(N, TC_BEST_ROWS), SB * J), dtype=torch.float32, device=dev)
+    st = _l.stream_ptr()
+    for f0 in range(0, N, TC_BEST_ROWS):
+        n = min(TC_BEST_ROWS, N - f0)
+        co = score_chunk_offsets(n, dev)
+        for b in range(nb):
+            r0, rb = b * SB, min(SB, pm.R - b * SB)
+            _l.check(L.srb_gmm_score_tc(X[f0:].data_ptr(), n, pm.D, tcb[b * nf:].data_ptr(), _l.ptr(pm.shift), rb * J, 4,
+                                        _l.ptr(co), co.numel() - 1, P.data_ptr(), rb * J, st))
+            _l.check(L.srb_merge_best(P.data_ptr(), n, rb, J, r0, int(b == 0), bc[f0:].data_ptr(), bs[f0:].data_ptr(), st))
+    return bc, bs
 
 
 def gmm_score(X, pm, want_E=True, want_best=False, want_comp=False, tensor=None):

@@ -102,6 +102,35 @@ def test_gmm_score_tensor_core_sub_states(eng, W, S, M, B, T):
         eng.TC_MERGE_ROWS = old
 
 
+@pytest.mark.parametrize("R,M,N", [(70, 8, 3000), (20, 32, 1500), (5, 4, 700), (130, 16, 2100)])
+def test_gmm_best_tensor_core_blocks(eng, R, M, N):
+    """engine.gmm_best_tc (blocks of 57 // J states on the tcgen05 scorer + srb_merge_best) against the FFMA scorer's
+    streaming best state: costs to FP32 noise, states equal wherever the two best costs differ by more than 1e-4."""
+    import torch
+    rng = np.random.default_rng(R + M)
+    mu = rng.normal(size=(R, 1, 39)) + 0.5 * rng.normal(size=(R, M, 39))
+    var = rng.uniform(0.5, 1.5, size=(R, M, 39))
+    w = rng.dirichlet(np.ones(M), size=R)
+    pm = eng.PackedModel(mu, var, w)
+    X = torch.randn((N, 39), dtype=torch.float32, device="cuda", generator=torch.Generator("cuda").manual_seed(5))
+    ref = eng.gmm_score(X, pm, want_E=True, want_best=True, tensor=False)
+    E = ref["E"].cpu().numpy()
+    old, eng.TC_BEST_ROWS = eng.TC_BEST_ROWS, 1024                 # several frame passes
+    try:
+        bc, bs = eng.gmm_best_tc(X, pm)
+    finally:
+        eng.TC_BEST_ROWS = old
+    bc, bs = bc.cpu().numpy(), bs.cpu().numpy()
+    np.testing.assert_allclose(bc, ref["best_cost"].cpu().numpy(), rtol=2e-5)
+    so = np.sort(E, axis=1)
+    decided = (so[:, 1] - so[:, 0]) > 1e-4 * np.abs(so[:, 0]) if R > 1 else np.ones(N, bool)
+    assert decided.mean() > 0.9
+    assert np.array_equal(bs[decided], ref["best_state"].cpu().numpy()[decided])
+    np.testing.assert_allclose(E[np.arange(N), bs], bc, rtol=2e-5)   # the state named carries the cost named
+    bc2, bs2 = eng.gmm_best_tc(X, pm)                                # cached block packing, one frame pass
+    assert np.array_equal(bc2.cpu().numpy(), bc) and np.array_equal(bs2.cpu().numpy(), bs)
+
+
 def test_gmm_score_tensor_core_unsupported_is_loud(eng):
     import torch
     from srb200 import lib as L
