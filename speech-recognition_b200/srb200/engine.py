@@ -1,4 +1,5 @@
 """Batched device-side operators over libsrb200 (torch is used for memory and streams only)."""
+import os
 import numpy as np
 import torch
 
@@ -140,7 +141,9 @@ def gmm_score_tc(X, pm, E=None):
     return E
 
 
-TC_BEST_ROWS = 1 << 18          # frames per pass of gmm_best_tc: the 57-column scratch (60 MB) stays in L2
+# frames per pass of gmm_best_tc.  Measured on config 5 (frames/s): 2^17 6.4e6, 2^18 6.9e6, 2^20 7.9e6, 2^22 8.4e6,
+# one pass 8.5e6 -- the per-launch cost of staging the block's model outweighs keeping the scratch in L2.
+TC_BEST_ROWS = int(os.environ.get("SRB_TC_BEST_ROWS", 1 << 22))
 
 
 def gmm_best_tc(X, pm, best_cost=None, best_state=None):
