@@ -184,10 +184,14 @@ def gmm_best_tc(X, pm, best_cost=None, best_state=None):
     return bc, bs
 
 
+TC_BEST_MIN_FRAMES = 1 << 16    # best-state-only requests of at least this many frames go to gmm_best_tc
+
+
 def gmm_score(X, pm, want_E=True, want_best=False, want_comp=False, tensor=None):
     """K1.  -> dict(E[N,R], best_cost[N], best_state[N], comp[N,R,Mp]) for the requested outputs.
     tensor: None = the tcgen05 (3xTF32) scorer for E-only requests of >= TC_SCORE_MIN_FRAMES frames when it covers
-    the model, else the FFMA scorer; True / False force one."""
+    the model and for best-state-only requests of >= TC_BEST_MIN_FRAMES frames (any number of states), else the FFMA
+    scorer; True / False force one."""
     X = as_frames(X)
     N = X.shape[0]
     assert X.shape[1] == pm.D
@@ -196,9 +200,14 @@ def gmm_score(X, pm, want_E=True, want_best=False, want_comp=False, tensor=None)
     e_only = want_E and not want_best and not want_comp
     if tensor is None:
         tensor = e_only and N >= TC_SCORE_MIN_FRAMES and pm.scorer_tensor_core_ok()
+    best_only = want_best and not want_E and not want_comp
+    if best_only and tensor is not False and pm.D == 39 and pm.Mp % 4 == 0 and 4 <= pm.Mp <= 228 and (
+            tensor or N >= TC_BEST_MIN_FRAMES):
+        bc, bs = gmm_best_tc(X, pm)                      # streaming best state, block by block on the tensor cores
+        return {"best_cost": bc, "best_state": bs}
     if tensor:
         if not e_only:
-            raise ValueError("the tensor-core scorer returns E only")
+            raise ValueError("the tensor-core scorer returns E only, or the best state only")
         return {"E": gmm_score_tc(X, pm)}
     E = torch.empty((N, pm.R), dtype=torch.float32, device=dev) if want_E else None
     bc = torch.empty(N, dtype=torch.float32, device=dev) if want_best else None

@@ -129,6 +129,8 @@ def test_gmm_best_tensor_core_blocks(eng, R, M, N):
     np.testing.assert_allclose(E[np.arange(N), bs], bc, rtol=2e-5)   # the state named carries the cost named
     bc2, bs2 = eng.gmm_best_tc(X, pm)                                # cached block packing, one frame pass
     assert np.array_equal(bc2.cpu().numpy(), bc) and np.array_equal(bs2.cpu().numpy(), bs)
+    out = eng.gmm_score(X, pm, want_E=False, want_best=True, tensor=True)       # the public route to the same path
+    assert np.array_equal(out["best_cost"].cpu().numpy(), bc) and np.array_equal(out["best_state"].cpu().numpy(), bs)
 
 
 def test_gmm_score_tensor_core_unsupported_is_loud(eng):
