@@ -205,6 +205,7 @@ __global__ void neg_lse_groups_kernel(const float *__restrict__ P, int64_t N, in
 // Running best state over blocks of states scored as sub-states: P[n, s*J + j] are the sub-state costs of states
 // state0 .. state0+Rb-1; the state cost is merged as in neg_lse_groups_kernel and replaces best_cost[n] / best_state[n]
 // when strictly smaller (blocks arrive in ascending state order: the first minimum wins, as in score_kernel).
+template <bool VEC4>   // VEC4: J % 4 == 0 and P 16-byte aligned -- whole 16-byte loads, every fetched sector used by one thread
 __global__ void merge_best_kernel(const float *__restrict__ P, int64_t N, int Rb, int J, int state0, int first,
                                   float *__restrict__ best_cost, int32_t *__restrict__ best_state) {
     for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < N; n += (int64_t)gridDim.x * blockDim.x) {
@@ -212,14 +213,28 @@ __global__ void merge_best_kernel(const float *__restrict__ P, int64_t N, int Rb
         float bc = first ? CUDART_INF_F : best_cost[n];
         int bs = first ? 0 : best_state[n];
         for (int r = 0; r < Rb; ++r, p += J) {
-            float m = CUDART_INF_F;
-            for (int j = 0; j < J; ++j) m = fminf(m, p[j]);
-            if (!(m < bc + 0.75f * (float)J)) continue;                  // -log sum >= m - log J: cannot win
-            float sum = 0.f;
-            for (int j = 0; j < J; ++j) sum += __expf(m - p[j]);
-            const float v = m - __logf(sum);
-            if (v < bc) {
-                bc = v;
+            float m = CUDART_INF_F, sum = 0.f;
+            if (VEC4) {
+                const float4 *q = reinterpret_cast<const float4 *>(p);
+                float4 v[16];                                            // J <= 64
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                    if (4 * j < J) {
+                        v[j] = q[j];
+                        m = fminf(m, fminf(fminf(v[j].x, v[j].y), fminf(v[j].z, v[j].w)));
+                    }
+                if (!(m < bc + 0.75f * (float)J)) continue;              // -log sum >= m - log J: cannot win
+#pragma unroll
+                for (int j = 0; j < 16; ++j)
+                    if (4 * j < J) sum += __expf(m - v[j].x) + __expf(m - v[j].y) + __expf(m - v[j].z) + __expf(m - v[j].w);
+            } else {
+                for (int j = 0; j < J; ++j) m = fminf(m, p[j]);
+                if (!(m < bc + 0.75f * (float)J)) continue;
+                for (int j = 0; j < J; ++j) sum += __expf(m - p[j]);
+            }
+            const float c = m - __logf(sum);
+            if (c < bc) {
+                bc = c;
                 bs = state0 + r;
             }
         }
@@ -326,7 +341,12 @@ int srb_merge_best(const float *P, int64_t N, int Rb, int J, int state0, int fir
     int64_t grid = (N + 127) / 128;
     const int64_t cap = (int64_t)sm_count() * 32;
     if (grid > cap) grid = cap;
-    merge_best_kernel<<<(int)grid, 128, 0, (cudaStream_t)stream>>>(P, N, Rb, J, state0, first, best_cost, best_state);
+    if (J % 4 == 0 && ((uintptr_t)P & 15) == 0)
+        merge_best_kernel<true><<<(int)grid, 128, 0, (cudaStream_t)stream>>>(P, N, Rb, J, state0, first, best_cost,
+                                                                             best_state);
+    else
+        merge_best_kernel<false><<<(int)grid, 128, 0, (cudaStream_t)stream>>>(P, N, Rb, J, state0, first, best_cost,
+                                                                              best_state);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }
