@@ -457,6 +457,25 @@ def path_to_words(path, emit, n_states_per_word):
     return words
 
 
+def pool_segments(path_forward, is_nes):
+    """The literal pooling loop of continuous_speech.py:91-106 on one forward path [[state, frame], ...]
+    -> list of (state_row, start_frame, end_frame) in flush order (quirk A12: the first frame after a state change is
+    skipped, the last open segment is never flushed)."""
+    out = []
+    start_idx = None
+    current_state = None
+    for r, c in path_forward:
+        r, c = int(r), int(c)
+        if start_idx is None and not is_nes[r]:                       # :97-99
+            start_idx = c
+            current_state = r
+        if r != current_state and start_idx is not None and start_idx < c:   # :100-106
+            out.append((current_state, start_idx, c))
+            start_idx = None
+            current_state = None
+    return out
+
+
 def continuous_pool(data, word_models, label_seqs):
     """continuous_speech.py:80-107: forced alignment + the reference's frame pooling (A12).
     -> ordered dict {flat_state: [frame arrays]} in first-flush order."""

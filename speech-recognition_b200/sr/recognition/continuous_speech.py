@@ -3,7 +3,8 @@
 `build_state_sequences` builds the same flat state list / dense transition matrix / end indices.
 `continuous_train` runs the embedded Viterbi training loop with ONE batched scoring launch and ONE batched
 graph-Viterbi launch per outer iteration for all utterances (one forced-alignment chain graph per distinct label
-sequence), then the per-state split / K-means / EM of the reference on device-resident pools.
+sequence), then the per-state split / K-means / EM of the reference on device-resident pools.  The tied-state lookup
+of the transition update follows the reference's `modelidx_state_map` semantics exactly (see continuous_train).
 """
 import copy
 import os
@@ -49,31 +50,53 @@ def build_state_sequences(hmms, label_matrix):
 def _pool_segments(path, is_nes):
     """The reference's pooling state machine (continuous_speech.py:90-106, quirks A12) on one forward path:
     -> list of (state_row, start_frame, end_frame).  A segment opens at the first point whose state emits, closes
-    at the first later point with a different row (that point's frame is excluded and does not open a segment
-    itself); the last open segment is never flushed."""
-    r, c = path[:, 0], path[:, 1]
+    at the first later point with a different row AND a later frame (that point's frame is excluded and the point
+    does not open a segment itself); the last open segment is never flushed.
+
+    The loop runs over RUNS of equal rows, not over points: inside a run the machine can only (1) close the segment
+    a previous run left open -- at the run's first point whose frame lies past the segment's start, which is the
+    second point when the open state began on this very frame (a one-frame state followed by the same-column hop
+    through a NES, decode.py:109-111) -- and then (2) reopen at the following point.  Frames never decrease along
+    a path, so (1) is a binary search."""
+    r, c = np.asarray(path[:, 0]), np.asarray(path[:, 1])
     n = len(r)
     if n == 0:
         return []
-    # only the first two points of every run of equal rows can change the machine's state
     run_first = np.flatnonzero(np.concatenate([[True], r[1:] != r[:-1]]))
-    cand = np.unique(np.concatenate([run_first, np.minimum(run_first + 1, n - 1)]))
+    run_end = np.concatenate([run_first[1:], [n]])
     out = []
     start = cur = None
-    for i in cand:
-        ri, ci = int(r[i]), int(c[i])
-        if start is None and not is_nes[ri]:
-            start, cur = ci, ri
-        if ri != cur and start is not None and start < ci:
-            out.append((cur, start, ci))
+    for p, e in zip(run_first.tolist(), run_end.tolist()):
+        ri = int(r[p])
+        if start is not None:
+            if ri == cur:
+                continue
+            q = p + int(np.searchsorted(c[p:e], start, side="right"))     # first point of the run with frame > start
+            if q >= e:
+                continue
+            out.append((cur, start, int(c[q])))
             start = cur = None
+            p = q + 1
+        if p < e and not is_nes[ri]:
+            start, cur = int(c[p]), ri
     return out
 
 
-def continuous_train(data, models, label_seqs, output_path, n_gaussians=4, n_segments=5, max_iteration=1000):
-    """Embedded training on connected utterances (continuous_speech.py:56-179)."""
+def continuous_train(data, models, label_seqs, output_path, n_gaussians=4, n_segments=5, max_iteration=1000, *,
+                     state_lookup="reference"):
+    """Embedded training on connected utterances (continuous_speech.py:56-179).
+
+    state_lookup="reference" (default) reproduces the reference's transition update exactly: `modelidx_state_map`
+    holds the state objects of the FIRST deep copy for the whole run (continuous_speech.py:66-71), and the pools are
+    a dict keyed by the CURRENT copy's state objects, which hash by `id` (kept by deepcopy) and compare by VALUE
+    (GMM.__eq__, np.allclose).  So from the second outer iteration on a state's transitions are re-estimated only
+    while its freshly trained mixture still equals the one the first iteration produced; otherwise the reference
+    warns "No MFCC data for state" and the arcs keep their previous costs.  state_lookup="current" looks the states
+    up in the current copy instead (every state with data gets its arcs re-estimated in every iteration)."""
+    assert state_lookup in ("reference", "current")
     old_models = models
     new_models = copy.deepcopy(models)
+    modelidx_state_map = {i: list(m.gmm_states) for i, m in enumerate(new_models)}     # :66-71, never refreshed
     X, off = _ops.cat_frames(data)
     Xd = _ops.to_device(X)
     off64 = off.astype(np.int64)
@@ -91,20 +114,20 @@ def continuous_train(data, models, label_seqs, output_path, n_gaussians=4, n_seg
             utt_graph.append(keys[k])
         res = decode_batch(data, graphs, utt_graph=utt_graph, want_path=True)
         paths = res.paths()
-        # ---- pooling per tied state (dict order = first appearance, it fixes the RNG stream of kmeans)
-        pools, order = {}, []
+        # ---- pooling per tied state: a dict keyed by the state objects like the reference's gmm_data (:76,101-104);
+        # its insertion order = first flush, which fixes the order kmeans consumes the global RNG stream in
+        gmm_data = {}
         for u, path in enumerate(paths):
             seq = graphs[utt_graph[u]][0]
             is_nes = np.array([type(s) is NES for s in seq])
             for row, a, b in _pool_segments(path[::-1], is_nes):
-                st = seq[row]
-                if id(st) not in pools:
-                    pools[id(st)] = (st, [])
-                    order.append(id(st))
-                pools[id(st)][1].append((int(off64[u]) + a, int(off64[u]) + b))
+                spans = gmm_data.get(seq[row])
+                if spans is None:
+                    gmm_data[seq[row]] = spans = []
+                spans.append((int(off64[u]) + a, int(off64[u]) + b))
         # ---- per-state split / K-means / EM (continuous_speech.py:110-142)
-        for sid in order:
-            state, spans = pools[sid]
+        for state in gmm_data.keys():
+            spans = gmm_data[state]
             assert type(state) is not NES
             idx = torch.from_numpy(np.concatenate([np.arange(a, b) for a, b in spans])).to(Xd.device)
             seg_d = Xd.index_select(0, idx)
@@ -123,13 +146,13 @@ def continuous_train(data, models, label_seqs, output_path, n_gaussians=4, n_seg
                 state.update_models(centroids, variance, weights[:k])
                 state._em_device(seg_d, k, 10000)
         # ---- transitions from segment counts (continuous_speech.py:144-164)
-        for m in new_models:
-            states = m.gmm_states
-            for si, st in enumerate(states):
-                if id(st) not in pools:
+        for mi, m in enumerate(new_models):
+            states = modelidx_state_map[mi] if state_lookup == "reference" else m.gmm_states
+            for si in range(len(states)):
+                spans = gmm_data.get(states[si])                # hash by id, then stored_key == states[si] by value
+                if spans is None:
                     warnings.warn("No MFCC data for state", UserWarning)
                     continue
-                spans = pools[id(st)][1]
                 p_jump = len(spans) / sum(b - a for a, b in spans)
                 if si < len(states) - 1:
                     m.transitions[si + 1, si] = -np.log(p_jump)

@@ -22,6 +22,26 @@ def close(a, b, rtol=RTOL, atol=0.0):
     np.testing.assert_allclose(np.asarray(a, np.float64), np.asarray(b, np.float64), rtol=rtol, atol=atol)
 
 
+def em_stops(fn, *a, **k):
+    """Runs fn with stdout captured -> (result, the k of every "EM converged at iteration: k" it printed)."""
+    import contextlib
+    import io
+    import re
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        out = fn(*a, **k)
+    return out, np.array([int(x) for x in re.findall(r"EM converged at iteration: (\d+)", buf.getvalue())])
+
+
+def check_stops(stops, ref):
+    """The 2e-3 tolerance of converged points must not hide an early stop: every EM loop has to stop within a few
+    iterations of the reference's (np.allclose on FP32-accumulated statistics may trip a little earlier or later,
+    SURVEY A14)."""
+    ref = np.asarray(ref)
+    assert len(stops) == len(ref), (stops.tolist(), ref.tolist())
+    assert np.all(np.abs(stops - ref) <= np.maximum(3, 0.1 * ref)), (stops.tolist(), ref.tolist())
+
+
 def load_models(rec, mu, cov, w, trans):
     """Rebuild mirror HMM objects from dumped parameters [W,S,M,D]."""
     models = []
@@ -158,7 +178,9 @@ def case_kmeans_em(rec, G):
         for iters, tag in ((1, "it1"), (3, "it3"), (10000, "conv")):
             g = rec.GMM(z[f"em{k}_mu_in"][0].copy(), z[f"em{k}_cov_in"][0].copy(), 4)
             g.update_models(z[f"em{k}_mu_in"].copy(), z[f"em{k}_cov_in"].copy(), z[f"em{k}_w_in"].copy())
-            g.em(data, k, iters)
+            _, stops = em_stops(g.em, data, k, iters)
+            if iters == 10000:
+                check_stops(stops, G["train_multi"][f"em{k}_conv_stop"])
             tol = RTOL if iters < 10000 else 2e-3        # the converged point depends on the stopping iteration
             close(g.w, z[f"em{k}_{tag}_w"], rtol=tol)
             close(np.array([d.mean for d in g.dists]), z[f"em{k}_{tag}_mu"], rtol=tol, atol=2e-5 if iters < 10000 else 1e-3)
@@ -207,7 +229,8 @@ def case_fit(rec, G):
     models = []
     for w in range(W):
         np.random.seed(1000 + w)
-        m = rec.HMM(5).fit(utts[w], n_gaussians=4, use_gmm=True, use_em=True)
+        m, stops = em_stops(rec.HMM(5).fit, utts[w], n_gaussians=4, use_gmm=True, use_em=True)
+        check_stops(stops, G["train_multi"][f"fit_em_stop{w}"])
         models.append(m)
         assert np.array_equal(np.cumsum([0] + [len(s) for s in m.segments]), z[f"fit_seg_off{w}"])
         assert np.array_equal(np.concatenate(m.segments), z[f"fit_seg_cat{w}"])
@@ -249,5 +272,48 @@ def case_continuous_train(rec, G):
     assert new[0].gmm_states[0].parent == 0
 
 
+def case_continuous_train_multi(rec, G):
+    """Three outer iterations (continuous_speech.py:73-179): from the second one on the reference looks the tied
+    states up through `modelidx_state_map`, which still holds the FIRST copy's objects, in a dict keyed by the
+    current copy's objects (hash by id, equality by value) -- so a state's arcs are re-estimated only while its
+    mixture still equals the first iteration's, and every other state raises "No MFCC data for state".  The models,
+    the number of those warnings, the outer iteration count and the EM stop iterations must follow the reference."""
+    import contextlib
+    import io
+    import re
+    import warnings
+    z, zm = G["train"], G["train_multi"]
+    data = unrag(z["ct_X"], z["ct_off"])
+    strings = [list(map(int, s)) for s in z["ct_strings"]]
+    for n_iter in (2, 3):
+        models = load_models(rec, z["fit_mu"], z["fit_cov"], z["fit_w"], z["fit_trans"])
+        for i, m in enumerate(models):
+            for s in m.gmm_states:
+                s.parent = i
+        buf = io.StringIO()
+        with tempfile.TemporaryDirectory() as td, warnings.catch_warnings(record=True) as wrn, \
+                contextlib.redirect_stdout(buf):
+            warnings.simplefilter("always")
+            np.random.seed(3000)
+            rec.continuous_train(data, models, strings, td, 4, 5, n_iter)
+            new = [pickle.load(open(os.path.join(td, f"{i}.pkl"), "rb")) for i in range(len(models))]
+        text = buf.getvalue()
+        assert len(re.findall(r"Continuous training iteration:", text)) == int(zm[f"it{n_iter}_outer"])
+        assert ("Continuous training converged" in text) == bool(zm[f"it{n_iter}_converged"])
+        n_warn = sum("No MFCC data" in str(x.message) for x in wrn)
+        assert n_warn == int(zm[f"it{n_iter}_no_data_warnings"]), (n_warn, int(zm[f"it{n_iter}_no_data_warnings"]))
+        mu, cov, wt, tr = _dump(new)
+        close(wt, zm[f"it{n_iter}_w"], rtol=2e-3)
+        close(mu, zm[f"it{n_iter}_mu"], rtol=2e-3, atol=1e-3)
+        close(cov, zm[f"it{n_iter}_cov"], rtol=2e-3)
+        _close_trans(tr, zm[f"it{n_iter}_trans"])
+        # the 2e-3 tolerance of the converged points must not hide an early stop: the EM loops have to stop within a
+        # few iterations of where the reference's did (SURVEY A14: np.allclose on float32-accumulated statistics)
+        stops = np.array([int(k) for k in re.findall(r"EM converged at iteration: (\d+)", text)])
+        ref = zm[f"it{n_iter}_em_stop"]
+        assert len(stops) == len(ref), (len(stops), len(ref))
+        assert np.all(np.abs(stops - ref) <= np.maximum(3, 0.1 * ref)), (stops.tolist(), ref.tolist())
+
+
 ALL = [case_emission, case_isolated_decode, case_graph_decode, case_dtw_helpers, case_kmeans_em, case_skmeans,
-       case_fit, case_continuous_train]
+       case_fit, case_continuous_train, case_continuous_train_multi]
