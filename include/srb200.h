@@ -121,8 +121,12 @@ int srb_classify_tc(const float *X, const int32_t *utt_off, int32_t B, int64_t N
  *   pred_ptr     CSR (absolute offsets) over the finite entries of transitions[r, :] in ascending origin order
  *                (decode.py:104-107), pred_idx = origin (graph local), pred_cost = transitions[r, origin]
  *   nes_idx      ascending local indices of the NES (they split a column into runs, see viterbi.cu)
- *   end_state    candidate end states in caller order; the end frame is always the last frame (callers pass
- *                -1 or T-1: main.py:60, continuous_speech.py:89, decode.py:126-127)
+ *   end_state    candidate end states in caller order; the end frame is the last frame (callers pass -1 or T-1:
+ *                main.py:60, continuous_speech.py:89, decode.py:126-127) unless end_frame is given
+ *   end_frame    (srb_viterbi_graph only, optional) frame of each end point, negative values count from the end like
+ *                the reference's Python indexing (decode.py:131-137 accepts any [state, frame]); needs costs_out,
+ *                from which the costs of end points off the last frame are read.  The path then starts at the best
+ *                end point's frame and frame_label is -1 past it.
  * At most 255 predecessors per state.  Start: only (state 0, frame 0) is seeded (decode.py:99-100).
  * Outputs: best_cost[B], best_end[B] (last minimum wins, decode.py:131-134; +inf / -1 when no path),
  *   bp[bp_off[u] + c*R + r] = position of the winning origin in r's predecessor list (first minimum wins),
@@ -136,9 +140,26 @@ int srb_classify_tc(const float *X, const int32_t *utt_off, int32_t B, int64_t N
 int srb_viterbi_graph(const float *E, int64_t ldE, const int32_t *utt_off, int32_t B, const int32_t *utt_graph,
                       const int32_t *g_state_off, const int32_t *g_nes_off, const int32_t *g_end_off,
                       const int32_t *emit, const int32_t *pred_ptr, const int32_t *pred_idx, const float *pred_cost,
-                      const int32_t *nes_idx, const int32_t *end_state, int32_t Rmax, const int64_t *bp_off,
-                      uint8_t *bp, float *costs_out, float *best_cost, int32_t *best_end, const int64_t *path_off,
-                      int32_t *path_state, int32_t *path_frame, int32_t *path_len, int32_t *frame_label, void *stream);
+                      const int32_t *nes_idx, const int32_t *end_state, const int32_t *end_frame, int32_t Rmax,
+                      const int64_t *bp_off, uint8_t *bp, float *costs_out, float *best_cost, int32_t *best_end,
+                      const int64_t *path_off, int32_t *path_state, int32_t *path_frame, int32_t *path_len,
+                      int32_t *frame_label, void *stream);
+
+/* ---- dtw with beam pruning (decode.py:7-77 incl. the beam of :42-48,62-68) -----------------------------------------
+ * Dl float[N, ldD] local distances of every frame to the S template rows (srb_local_dist); trans float[S,S] dense,
+ * trans[i*S + o] = cost o -> i, +inf entries stay candidates as in the reference (decode.py:44-51 does not skip them).
+ * After each column the reference sorts its costs and marks every FINITE cell of rank >= beam with -1; the next
+ * column's row 0 skips those origins, the other rows see them as +inf (row 0's scan has reset them), and the marks of
+ * the last column stay in the returned matrix.  beam < 0 = no pruning (np.inf).  Ranks are by (cost, row).
+ *   costs_out float[ws_off[u] + j*S + i] = costs[i, j] (pruned cells: +inf, -1 in the last column)
+ *   bp uint16 same indexing = winning origin row (the first candidate when every candidate is +inf, like np.argmin)
+ *   path_state/path_frame[path_off[u] ...] the reversed path of decode.py:71-77 from (S-1, T-1) down to (0, 0),
+ *   end cell excluded; path_len[u] = T-1, or -2 when row 0 of some column had no candidate left (the reference's
+ *   np.argmin raises ValueError), -3 when the walk reaches column 0 off row 0 (the reference then wraps to column -1
+ *   and does not terminate).  Utterances need >= 2 frames and S >= 2 (decode.py:22); S <= 4096. */
+int srb_dtw_beam(const float *Dl, int64_t ldD, const int32_t *utt_off, int32_t B, const float *trans, int32_t S,
+                 int32_t beam, const int64_t *ws_off, uint16_t *bp, float *costs_out, const int64_t *path_off,
+                 int32_t *path_state, int32_t *path_frame, int32_t *path_len, void *stream);
 
 /* Same contract and bit-identical outputs as srb_viterbi_graph, for graphs in BANDED FORM (what
  * build_state_sequences, continuous_speech.py:13-53, and plain left-to-right models produce): the emitting

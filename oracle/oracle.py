@@ -171,6 +171,45 @@ def dtw(X, Y, trans, var=None):
     return costs, path[:n].copy()
 
 
+def dtw_beam(Dl, trans, beam=np.inf):
+    """decode.py:19-77 WITH the beam (pure-Python loops, small cases only) on a precomputed local-distance matrix
+    Dl[T,S] -> (costs[S,T], path).  Follows the reference statement by statement: -1 marks cells excluded by the beam
+    (:62-68); the first row swept in the next column skips marked origins and resets the mark to inf (:44-51)."""
+    Dl = np.asarray(Dl, np.float64)
+    T, S = Dl.shape
+    assert T > 1 and S > 1                                                      # :22
+    costs = np.full((S, T), np.inf)
+    pm = np.zeros((S, T, 2), np.int64)
+    for j in range(T):
+        for i in range(S):
+            if i == 0 and j == 0:
+                costs[0, 0] = Dl[0, 0]                                          # :34-40
+                continue
+            prev_costs, from_pts = [], []
+            for origin in range(trans.shape[1]):                               # :44-51
+                if costs[origin, j - 1] == -1:
+                    costs[origin, j - 1] = np.inf
+                else:
+                    prev_costs.append(trans[i, origin] + costs[origin, j - 1])
+                    from_pts.append([origin, j - 1])
+            min_i = int(np.argmin(prev_costs))                                  # :53 (ValueError when empty)
+            pm[i, j] = from_pts[min_i]
+            costs[i, j] = min(costs[i, j], prev_costs[min_i] + Dl[j, i])        # :56-60
+        if not np.isinf(beam):                                                  # :62-68
+            sort_idx = np.argsort(costs[:, j].flatten(), kind="stable")
+            for i in sort_idx[beam:]:
+                if not np.isinf(costs[i, j]):
+                    costs[i, j] = -1
+    i, j = S - 1, T - 1
+    path = []
+    while i != 0 or j != 0:                                                     # :71-77
+        if j == 0:
+            raise RuntimeError("walk back left the first column (the reference wraps to column -1 here)")
+        i, j = pm[i, j]
+        path.append([i, j])
+    return costs, np.array(path, np.int64).reshape(-1, 2)
+
+
 def forward_backward(E, trans):
     """No reference counterpart (parity unpinned).  -> (neg_log_Z, alpha[T,R], beta[T,R], gamma[T,R])."""
     E, Ep = _d(E)

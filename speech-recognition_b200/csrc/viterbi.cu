@@ -24,6 +24,7 @@ struct GraphBatch {
     const float *pred_cost;       // transitions[target, origin]
     const int32_t *nes_idx;       // ascending local indices of the NES of each graph
     const int32_t *end_state;     // candidate end states (local), frame = last (main.py:60 passes -1)
+    const int32_t *end_frame;     // optional: frame of each end point (negative counts from the end, decode.py:131-137)
 };
 
 __device__ __forceinline__ void lexmin(float &v, int &p, float ov, int op) {
@@ -39,17 +40,25 @@ __device__ __forceinline__ void finish_utterance(const GraphBatch &G, int g, int
                                                  const float *prev, const int32_t *emit, const int32_t *pptr,
                                                  const uint8_t *bpu, int lane, float *best_cost, int32_t *best_end,
                                                  const int64_t *path_off, int32_t *path_state, int32_t *path_frame,
-                                                 int32_t *path_len, int32_t *frame_label) {
+                                                 int32_t *path_len, int32_t *frame_label, const float *cu = nullptr) {
     const float INF = CUDART_INF_F;
     // ---- best end point: '>=' -> the last listed minimum wins (decode.py:131-134); traceback :142-146
     if (lane == 0) {
         float bc = INF;
-        int bi = -1;
+        int bi = -1, bj = T - 1;
         for (int e = G.g_end_off[g]; e < G.g_end_off[g + 1]; ++e) {
             const int s = G.end_state[e];
-            if (bc >= prev[s]) {
-                bc = prev[s];
+            int c = T - 1;
+            if (G.end_frame) {                                   // any [state, frame] end point (decode.py:126-134)
+                c = G.end_frame[e];
+                if (c < 0) c += T;                               // Python indexing: -1 = the last frame
+                if (c < 0 || c >= T) continue;                   // the host layer rejects these (IndexError)
+            }
+            const float v = (c == T - 1 || !cu) ? prev[s] : cu[(size_t)c * R + s];
+            if (bc >= v) {
+                bc = v;
                 bi = s;
+                bj = c;
             }
         }
         best_cost[u] = bc;
@@ -59,8 +68,11 @@ __device__ __forceinline__ void finish_utterance(const GraphBatch &G, int g, int
             int32_t *ps = path_state ? path_state + path_off[u] : nullptr;
             int32_t *pf = path_state ? path_frame + path_off[u] : nullptr;
             const int cap = path_state ? (int)(path_off[u + 1] - path_off[u]) : 0x7fffffff;
-            int i = bi, j = T - 1;
-            if (frame_label && emit[i] >= 0) frame_label[f0 + j] = s0 + i;
+            int i = bi, j = bj;
+            if (frame_label) {
+                for (int c = bj + 1; c < T; ++c) frame_label[f0 + c] = -1;   // frames past an early end point
+                if (emit[i] >= 0) frame_label[f0 + j] = s0 + i;
+            }
             while (j > 0 && len < cap) {
                 const int code = bpu[(size_t)j * R + i];
                 const int o = G.pred_idx[pptr[i] + code];
@@ -180,8 +192,9 @@ viterbi_graph_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *__
             cur = t;
             __syncwarp();
         }
+        __syncwarp();                                              // costs_out rows written by other lanes are visible
         finish_utterance(G, g, s0, R, T, f0, u, prev, emit, pptr, bpu, lane, best_cost, best_end, path_off, path_state,
-                         path_frame, path_len, frame_label);
+                         path_frame, path_len, frame_label, cu);
         __syncwarp();
     }
 }
@@ -1155,7 +1168,7 @@ extern "C" {
 static GraphBatch make_graph(const int32_t *utt_graph, const int32_t *g_state_off, const int32_t *g_nes_off,
                              const int32_t *g_end_off, const int32_t *emit, const int32_t *pred_ptr,
                              const int32_t *pred_idx, const float *pred_cost, const int32_t *nes_idx,
-                             const int32_t *end_state) {
+                             const int32_t *end_state, const int32_t *end_frame = nullptr) {
     GraphBatch G;
     G.utt_graph = utt_graph;
     G.g_state_off = g_state_off;
@@ -1167,16 +1180,20 @@ static GraphBatch make_graph(const int32_t *utt_graph, const int32_t *g_state_of
     G.pred_cost = pred_cost;
     G.nes_idx = nes_idx;
     G.end_state = end_state;
+    G.end_frame = end_frame;
     return G;
 }
 
 int srb_viterbi_graph(const float *E, int64_t ldE, const int32_t *utt_off, int32_t B, const int32_t *utt_graph,
                       const int32_t *g_state_off, const int32_t *g_nes_off, const int32_t *g_end_off,
                       const int32_t *emit, const int32_t *pred_ptr, const int32_t *pred_idx, const float *pred_cost,
-                      const int32_t *nes_idx, const int32_t *end_state, int32_t Rmax, const int64_t *bp_off,
-                      uint8_t *bp, float *costs_out, float *best_cost, int32_t *best_end, const int64_t *path_off,
-                      int32_t *path_state, int32_t *path_frame, int32_t *path_len, int32_t *frame_label, void *stream) {
+                      const int32_t *nes_idx, const int32_t *end_state, const int32_t *end_frame, int32_t Rmax,
+                      const int64_t *bp_off, uint8_t *bp, float *costs_out, float *best_cost, int32_t *best_end,
+                      const int64_t *path_off, int32_t *path_state, int32_t *path_frame, int32_t *path_len,
+                      int32_t *frame_label, void *stream) {
     if (B == 0) return SRB_OK;
+    SRB_REQUIRE(!end_frame || costs_out, SRB_EINVAL,
+                "srb_viterbi_graph: end points off the last frame need costs_out (their costs are read from it)");
     SRB_REQUIRE(E && utt_off && g_state_off && g_nes_off && g_end_off && emit && pred_ptr && pred_idx && pred_cost &&
                     end_state && bp_off && bp && best_cost && best_end,
                 SRB_EINVAL, "srb_viterbi_graph: null pointer");
@@ -1193,7 +1210,7 @@ int srb_viterbi_graph(const float *E, int64_t ldE, const int32_t *utt_off, int32
     const int64_t cap = (int64_t)sms * 16;
     if (grid > cap) grid = cap;
     GraphBatch G = make_graph(utt_graph, g_state_off, g_nes_off, g_end_off, emit, pred_ptr, pred_idx, pred_cost, nes_idx,
-                              end_state);
+                              end_state, end_frame);
     viterbi_graph_kernel<<<(int)grid, VW * 32, bytes, (cudaStream_t)stream>>>(
         E, ldE, utt_off, B, G, Rmax, bp_off, bp, costs_out, best_cost, best_end, path_off, path_state, path_frame,
         path_len, frame_label);

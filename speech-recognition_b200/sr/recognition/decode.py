@@ -42,12 +42,18 @@ def dtw(x, y, dist_fun, transitions, variance=None, beam=np.inf):
     -> (costs [S, T] float64, path [T-1, 2] int64 reversed)."""
     col_count, row_count = len(x), len(y)
     assert col_count > 1 and row_count > 1
-    if not isinf(beam):
-        raise NotImplementedError("beam pruning is not built (no caller of the reference passes a finite beam)")
     Xd = _ops.to_device(np.asarray(x))
     dist = _local_distances(Xd, x, y, dist_fun, variance)
-    graph = StateGraph(transitions, np.arange(row_count), end_states=[row_count - 1], keep_inf=True)
     off = np.array([0, col_count], np.int32)
+    if not isinf(beam) or row_count > 255:
+        # beam pruning (decode.py:42-48,62-68: -1 sentinels, pruned origins skipped by row 0 and +inf for the other
+        # rows), and templates too long for the graph kernel's 8-bit back-pointer codes: srb_dtw_beam
+        if not isinf(beam) and int(beam) != beam:
+            raise TypeError("slice indices must be integers or None or have an __index__ method")   # sort_idx[beam:]
+        costs, _, paths = engine.dtw_beam(dist, off, transitions, None if isinf(beam) else int(beam))
+        costs = costs[:col_count * row_count].reshape(col_count, row_count).t().double().cpu().numpy()
+        return costs, paths[0]
+    graph = StateGraph(transitions, np.arange(row_count), end_states=[row_count - 1], keep_inf=True)
     res = _ops.viterbi_batch(dist, off, [graph], want_costs=True, want_path=True)
     costs = res.costs[:col_count * row_count].reshape(col_count, row_count).t().double().cpu().numpy()
     return costs, res.paths()[0]
@@ -103,7 +109,10 @@ def _emission_matrix(Xd, X_host, state_lists):
 
 def _graph_of(states, transitions, end_states, col):
     emit = np.array([-1 if type(s) == NES else col[id(s)] for s in states], np.int32)
-    g = StateGraph(transitions, emit, end_states=end_states)
+    end_frames = None
+    if isinstance(end_states, tuple):              # (states, frames): end points off the last frame
+        end_states, end_frames = end_states
+    g = StateGraph(transitions, emit, end_states=end_states, end_frames=end_frames)
     if g.has_nes_self_loop:
         raise NameError("a non-emitting state transits to itself in the same column (decode.py:120-121)")
     return g
@@ -115,7 +124,8 @@ def decode_batch(xs, graphs, utt_graph=None, want_costs=False, want_path=True, w
     X, off = _ops.cat_frames(xs)
     Xd = _ops.to_device(X)
     E, col = _emission_matrix(Xd, X, [g[0] for g in graphs])
-    sg = [_graph_of(st, tr, None if ends is None else list(ends), col) for st, tr, ends in graphs]
+    sg = [_graph_of(st, tr, None if ends is None else (ends if isinstance(ends, tuple) else list(ends)), col)
+          for st, tr, ends in graphs]
     ug = None if utt_graph is None else np.asarray(utt_graph, np.int32)
     res = _ops.viterbi_batch(E, off, sg, utt_graph=ug, want_costs=want_costs, want_path=want_path,
                              want_label=want_label)
@@ -130,10 +140,13 @@ def decode_hmm_states(x, states, transitions, end_points=None):
     T = len(x)
     ends = None
     if end_points is not None:
-        for e in end_points:
-            if e[1] not in (-1, T - 1):
-                raise NotImplementedError("end points must lie on the last frame (all reference callers pass -1)")
+        frames = [int(e[1]) for e in end_points]
+        for c in frames:
+            if not -T <= c < T:
+                raise IndexError(f"index {c} is out of bounds for axis 1 with size {T}")     # costs[end[0], end[1]]
         ends = [int(e[0]) for e in end_points]
+        if any(c not in (-1, T - 1) for c in frames):
+            ends = (ends, frames)                  # any [state, frame] (decode.py:126-134): srb_viterbi_graph end_frame
     res = decode_batch([np.asarray(x)], [(states, np.asarray(transitions), ends)], want_costs=True, want_path=True)
     if isinf(res.best_cost[0]):
         warnings.warn("decode_hmm_states: Cannot find a path when decoding sequence")

@@ -390,6 +390,11 @@ def viterbi_launch(gb, E, offd, B, ug, ws_d, bp, costs, bc, be, po_d, ps, pf, pl
     both give identical outputs), else srb_viterbi_graph."""
     p, L = _l.ptr, _l.load()
     use_banded = gb.banded if banded is None else (banded and gb.banded)
+    end_frame = gb.dev.get("end_frame")                   # end points off the last frame: generic kernel only
+    if end_frame is not None:
+        if banded:
+            raise ValueError("end points off the last frame run through srb_viterbi_graph (banded=False)")
+        use_banded = False
     head = (p(E), E.stride(0), p(offd), B, p(ug), p(gb["g_state_off"]), p(gb["g_nes_off"]), p(gb["g_end_off"]),
             p(gb["emit"]), p(gb["pred_ptr"]), p(gb["pred_idx"]), p(gb["pred_cost"]), p(gb["nes_idx"]), p(gb["end_state"]))
     tail = (gb.Rmax, p(ws_d), p(bp), p(costs), p(bc), p(be), p(po_d), p(ps), p(pf), p(pl), p(frame_label),
@@ -398,7 +403,7 @@ def viterbi_launch(gb, E, offd, B, ug, ws_d, bp, costs, bc, be, po_d, ps, pf, pl
         _l.check(L.srb_viterbi_banded(*head, p(gb["band"]), p(gb["codes"]), p(gb["entry_nes"]), p(gb["entry_cost"]),
                                       p(gb["g_entry_off"]), p(gb["entry_state"]), *tail))
     else:
-        _l.check(L.srb_viterbi_graph(*head, *tail))
+        _l.check(L.srb_viterbi_graph(*head, p(end_frame), *tail))
     return use_banded
 
 
@@ -423,6 +428,45 @@ def viterbi(E, off, gb, utt_graph=None, want_costs=False, want_path=True, frame_
     res.frame_label = frame_label
     res.path_off_dev, res.utt_graph_dev, res.gb = po_d, ug, gb
     return res
+
+
+def dtw_beam(dist, off, trans, beam=None):
+    """dtw with the reference's beam pruning (decode.py:7-77; srb_dtw_beam) for a ragged batch of utterances against
+    ONE template.  dist: [N, S] float32 CUDA local distances; trans: [S, S] (cost o -> i at [i, o], inf entries stay
+    candidates); beam: None / inf = no pruning.
+    -> (costs flat float32 [sum T*S] with costs[i, j] at ws[u] + j*S + i, ws int64[B+1], paths: list of [T-1, 2] int64)
+    Raises ValueError where the reference's np.argmin gets an empty list, RuntimeError where its walk back would leave
+    the first column (the reference does not terminate there)."""
+    dev = dist.device
+    S = int(dist.shape[1])
+    offd = as_offsets(off)
+    offn = offd.cpu().numpy().astype(np.int64)
+    B = len(offn) - 1
+    T = np.diff(offn)
+    ws = np.zeros(B + 1, np.int64)
+    np.cumsum(T * S, out=ws[1:])
+    po = np.zeros(B + 1, np.int64)
+    np.cumsum(np.maximum(T - 1, 0), out=po[1:])
+    tr = torch.as_tensor(np.ascontiguousarray(np.asarray(trans, np.float64))).to(dev, torch.float32).contiguous()
+    assert tuple(tr.shape) == (S, S)
+    bp = torch.empty(max(int(ws[-1]), 1), dtype=torch.int16, device=dev)
+    costs = torch.empty(max(int(ws[-1]), 1), dtype=torch.float32, device=dev)
+    ps = torch.empty(max(int(po[-1]), 1), dtype=torch.int32, device=dev)
+    pf = torch.empty(max(int(po[-1]), 1), dtype=torch.int32, device=dev)
+    pl = torch.zeros(max(B, 1), dtype=torch.int32, device=dev)
+    b = -1 if beam is None or beam == float("inf") else int(beam)
+    _l.check(_l.load().srb_dtw_beam(_l.ptr(dist), dist.stride(0), _l.ptr(offd), B, _l.ptr(tr), S, b,
+                                    _l.ptr(torch.from_numpy(ws).to(dev)), _l.ptr(bp), _l.ptr(costs),
+                                    _l.ptr(torch.from_numpy(po).to(dev)), _l.ptr(ps), _l.ptr(pf), _l.ptr(pl),
+                                    _l.stream_ptr()))
+    ln = pl.cpu().numpy()
+    if (ln[:B] == -2).any():
+        raise ValueError("attempt to get argmin of an empty sequence")          # what np.argmin([]) raises, decode.py:53
+    if (ln[:B] == -3).any():
+        raise RuntimeError("dtw: the walk back left the first column off row 0 (the reference does not terminate here)")
+    psn, pfn = ps.cpu().numpy(), pf.cpu().numpy()
+    paths = [np.stack([psn[po[u]:po[u] + ln[u]], pfn[po[u]:po[u] + ln[u]]], axis=1).astype(np.int64) for u in range(B)]
+    return costs, ws, paths
 
 
 def forward_backward(E, off, gb, utt_graph=None, want_xi=False, banded=None):

@@ -11,7 +11,7 @@ class StateGraph:
     """One graph: emit[r] (column of the emission matrix, -1 = NES), CSR predecessors in ascending origin order
     (decode.py:104-107 iterates origins ascending, so 'first minimum' is preserved), end states."""
 
-    def __init__(self, transitions, emit, end_states=None, keep_inf=False):
+    def __init__(self, transitions, emit, end_states=None, keep_inf=False, end_frames=None):
         tr = np.asarray(transitions, dtype=np.float64)
         R = tr.shape[0]
         assert tr.shape == (R, R)
@@ -31,6 +31,9 @@ class StateGraph:
         if end_states is None:
             end_states = [R - 1]                         # decode.py:126-127
         self.end_states = np.asarray(end_states, dtype=np.int32).reshape(-1)
+        # frames of the end points when some lie off the last frame (decode.py:126-134 takes any [state, frame])
+        self.end_frames = None if end_frames is None else np.asarray(end_frames, dtype=np.int32).reshape(-1)
+        assert self.end_frames is None or self.end_frames.shape == self.end_states.shape
         # successor CSR of the same edges (forward-backward's beta recursion)
         order = np.lexsort((tgt, org))
         self.succ_ptr = np.zeros(R + 1, np.int32)
@@ -120,6 +123,9 @@ class GraphBatch:
             "succ_idx": cat([g.succ_idx for g in graphs], np.int32),
             "succ_cost": cat([g.succ_cost for g in graphs], np.float32),
         }
+        if any(g.end_frames is not None for g in graphs):
+            host["end_frame"] = cat([g.end_frames if g.end_frames is not None else np.full(len(g.end_states), -1)
+                                     for g in graphs], np.int32)
         forms = [g.banded_form() for g in graphs]
         self.banded = all(f is not None for f in forms)
         if self.banded:

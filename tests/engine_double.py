@@ -124,14 +124,16 @@ def viterbi(E, off, gb, utt_graph=None, want_costs=False, want_path=True, frame_
         costs, bp = _viterbi_one(Eu, g, want_costs)
         ws[u + 1] = ws[u] + T * g.R
         costs_flat.append(costs.ravel())
-        best, bi = np.inf, -1
-        for s in g.end_states:
-            if best >= costs[T - 1, s]:
-                best, bi = costs[T - 1, s], int(s)
+        best, bi, bj = np.inf, -1, T - 1
+        frames = g.end_frames if getattr(g, "end_frames", None) is not None else [T - 1] * len(g.end_states)
+        for s, c in zip(g.end_states, frames):
+            c = int(c) + T if c < 0 else int(c)
+            if best >= costs[c, s]:
+                best, bi, bj = costs[c, s], int(s), c
         bc[u], be[u] = best, bi
         path = []
         if np.isfinite(best):
-            i, j = bi, T - 1
+            i, j = bi, bj
             if g.emit[i] >= 0:
                 fl[off[u] + j] = s0 + i
             while j > 0:
@@ -174,6 +176,58 @@ def viterbi(E, off, gb, utt_graph=None, want_costs=False, want_path=True, frame_
         frame_label[:len(fl)] = torch.from_numpy(fl)
         res.frame_label = frame_label
     return res
+
+
+def dtw_beam(dist, off, trans, beam=None):
+    """numpy stand-in of engine.dtw_beam: the column rules of decode.py:42-68 (marked origins skipped by row 0, +inf
+    for the other rows; finite cells of rank >= beam marked)."""
+    Dl = _np(dist, np.float64)
+    off = _np(off, np.int64)
+    tr = _np(trans, np.float64)
+    S = Dl.shape[1]
+    B = len(off) - 1
+    ws = np.zeros(B + 1, np.int64)
+    flat, paths = [], []
+    for u in range(B):
+        d = Dl[off[u]:off[u + 1]]
+        T = d.shape[0]
+        ws[u + 1] = ws[u] + T * S
+        costs = np.full((T, S), np.inf)
+        bp = np.zeros((T, S), np.int64)
+        mark = np.zeros(S, bool)
+        for j in range(T):
+            for i in range(S):
+                if j == 0:
+                    costs[0, i] = d[0, 0] if i == 0 else np.inf
+                    continue
+                cand = np.where(mark, np.inf, costs[j - 1]) + tr[i]
+                idx = np.flatnonzero(~mark) if i == 0 else np.arange(S)
+                if len(idx) == 0:
+                    raise ValueError("attempt to get argmin of an empty sequence")
+                bo = idx[np.argmin(cand[idx])]
+                bp[j, i] = bo
+                costs[j, i] = cand[bo] + d[j, i]
+            cj = costs[j]
+            fin = np.isfinite(cj)
+            if beam is not None:
+                rank = np.empty(S, np.int64)
+                rank[np.argsort(cj, kind="stable")] = np.arange(S)
+                mark = fin & (rank >= beam)
+            else:
+                mark = np.zeros(S, bool)
+            if j > 0:
+                costs[j - 1][prev_mark] = np.inf
+            prev_mark = mark
+        costs[T - 1][mark] = -1.0
+        i, j, path = S - 1, T - 1, []
+        while i != 0 or j != 0:
+            if j == 0:
+                raise RuntimeError("dtw: the walk back left the first column off row 0")
+            i, j = int(bp[j, i]), j - 1
+            path.append([i, j])
+        flat.append(costs.ravel())
+        paths.append(np.array(path, np.int64).reshape(-1, 2))
+    return torch.from_numpy(np.concatenate(flat).astype(np.float32)), ws, paths
 
 
 def classify(X, off, pm, trans, W, S, final=None, label=None):
@@ -275,5 +329,5 @@ def install(monkeypatch):
     """Replace the device entry points of srb200.engine for the duration of one test."""
     from srb200 import engine
     for name in ("device", "PackedModel", "as_frames", "as_offsets", "gmm_score", "viterbi", "classify",
-                 "group_stats", "moments_from_stats", "gmm_stats", "mstep", "local_dist"):
+                 "group_stats", "moments_from_stats", "gmm_stats", "mstep", "local_dist", "dtw_beam"):
         monkeypatch.setattr(engine, name, globals()[name])

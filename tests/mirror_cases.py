@@ -164,6 +164,67 @@ def case_dtw_helpers(rec, G):
     close(rec.calc_variance(temps[1].T), z["cv_out"])
 
 
+def case_dtw_beam(rec, G):
+    """dtw(..., beam=k) (decode.py:42-48,62-68): cost matrices incl. the -1 marks left in the last column, +inf at the
+    cells the beam removed, and the paths the reference walks through its back-pointers."""
+    z = G["beam"]
+    xs = unrag(z["bm_X"], z["bm_off"])
+    for k, (beam, maha, ti, u, plen) in enumerate(z["bm_cases"]):
+        trans = z["bm_trans2"] if ti else z["bm_trans"]
+        if maha:
+            costs, path = rec.dtw(xs[u], z["bm_y"], rec.mahalanobis, trans, z["bm_var"], beam=int(beam))
+        else:
+            costs, path = rec.dtw(xs[u], z["bm_y"], rec.euclidean, trans, beam=int(beam))
+        ref = z[f"bm_costs{k}"]
+        f = np.isfinite(ref)
+        assert np.array_equal(np.isfinite(costs), f), (k, beam)
+        assert np.array_equal(costs == -1, ref == -1), (k, beam)
+        close(costs[f], ref[f])
+        assert np.array_equal(path, z[f"bm_path{k}"]), (k, beam)
+    # no beam, long template (> 255 rows: past the graph kernel's 8-bit back-pointer codes) against a short one
+    # embedded in it: rows 0..5 of a 300-row template whose other rows are unreachable behave like the 6-row template
+    S, big = z["bm_y"].shape[0], 300
+    y = np.concatenate([z["bm_y"], np.zeros((big - S, z["bm_y"].shape[1]))])
+    tr = np.full((big, big), np.inf)
+    tr[:S, :S] = z["bm_trans"]
+    c_small, _ = rec.dtw(xs[1], z["bm_y"], rec.euclidean, z["bm_trans"])
+    c_big, _ = rec.dtw(xs[1], y, rec.euclidean, tr)
+    close(c_big[:S], c_small)
+    assert np.isinf(c_big[S:]).all()
+    try:
+        rec.dtw(xs[0], z["bm_y"], rec.euclidean, z["bm_trans"], beam=2.5)
+        raise AssertionError("a fractional beam must raise TypeError (sort_idx[beam:], decode.py:65)")
+    except TypeError:
+        pass
+
+
+def case_end_points(rec, G):
+    """decode_hmm_states with end points off the last frame, negative frames, a NES end (decode.py:126-146)."""
+    z = G["ends"]
+    models = load_models(rec, z["en_mu"], z["en_cov"], z["en_w"], z["en_wtrans"])
+    seq, trans, ends = rec.build_state_sequences(models, [[0, 1]] * 2)
+    assert list(ends) == list(z["en_ends"])
+    x = z["en_X"]
+    for k in range(int(z["en_n"])):
+        costs, path = rec.decode_hmm_states(x, seq, trans, end_points=z[f"en_list{k}"].tolist())
+        ref = z[f"en_costs{k}"]
+        f = np.isfinite(ref)
+        assert np.array_equal(np.isfinite(costs), f)
+        close(costs[f], ref[f])
+        assert np.array_equal(path.reshape(-1, 2), z[f"en_path{k}"]), k
+    S = len(models[1].gmm_states)
+    costs, path = rec.decode_hmm_states(x[:14], models[1].gmm_states, models[1].transitions,
+                                        end_points=[[S - 1, 9], [S - 2, -2]])
+    f = np.isfinite(z["en_iso_costs"])
+    close(costs[f], z["en_iso_costs"][f])
+    assert np.array_equal(path, z["en_iso_path"])
+    try:
+        rec.decode_hmm_states(x, seq, trans, end_points=[[0, len(x)]])
+        raise AssertionError("an end frame past the utterance must raise IndexError")
+    except IndexError:
+        pass
+
+
 # ------------------------------------------------------------------------------------------------ K-means / EM
 def case_kmeans_em(rec, G):
     z = G["kmeans_em"]
@@ -315,5 +376,5 @@ def case_continuous_train_multi(rec, G):
         assert np.all(np.abs(stops - ref) <= np.maximum(3, 0.1 * ref)), (stops.tolist(), ref.tolist())
 
 
-ALL = [case_emission, case_isolated_decode, case_graph_decode, case_dtw_helpers, case_kmeans_em, case_skmeans,
+ALL = [case_emission, case_isolated_decode, case_graph_decode, case_dtw_helpers, case_dtw_beam, case_end_points, case_kmeans_em, case_skmeans,
        case_fit, case_continuous_train, case_continuous_train_multi]

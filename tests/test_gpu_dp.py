@@ -297,3 +297,65 @@ def test_path_words_kernel_matches_main_py_postprocessing():
         k = min(len(want[u]), max_words)
         assert wn[u, :k].tolist() == want[u][:k]
         assert (wn[u, k:] == -5).all()
+
+
+def test_dtw_beam_batch_against_oracle(eng):
+    """srb_dtw_beam on a ragged batch against the literal restatement of decode.py:19-77 (oracle.dtw_beam): random
+    templates of 2..40 rows, dense transitions with +inf entries, beams from 1 to past the row count and none."""
+    import torch
+    rng = np.random.default_rng(5)
+    for S, beam in ((2, 1), (5, 2), (7, 3), (16, 4), (40, 6), (40, None), (9, 100), (300, 8)):
+        T = rng.integers(2, 40, size=12)
+        off = np.zeros(len(T) + 1, np.int32)
+        off[1:] = np.cumsum(T)
+        Dl = rng.uniform(0.5, 3.0, size=(off[-1], S)).astype(np.float32)
+        tr = np.full((S, S), np.inf)
+        for i in range(S):
+            tr[i, i] = rng.uniform(0.1, 1.0)
+            if i:
+                tr[i, i - 1] = rng.uniform(0.1, 2.0)
+            if i > 1 and rng.random() < 0.4:
+                tr[i, i - 2] = rng.uniform(1.0, 3.0)
+        tr = tr.astype(np.float32).astype(np.float64)
+        costs, ws, paths = eng.dtw_beam(torch.from_numpy(Dl).cuda(), off, tr, beam)
+        c = costs.cpu().numpy()
+        for u in range(len(T)):
+            try:
+                rc, rp = orc.dtw_beam(Dl[off[u]:off[u + 1]].astype(np.float64), tr, np.inf if beam is None else beam)
+            except RuntimeError:
+                continue
+            got = c[ws[u]:ws[u + 1]].reshape(-1, S).T
+            f = np.isfinite(rc)
+            assert np.array_equal(np.isfinite(got), f), (S, beam, u)
+            np.testing.assert_allclose(got[f], rc[f], rtol=RTOL)
+            assert np.array_equal(paths[u], rp), (S, beam, u)    # random uniform costs: no near-ties at these sizes
+
+
+def test_end_frames_through_the_abi(eng, golden):
+    """srb_viterbi_graph's end_frame: best end point over any [state, frame] list, path from that frame."""
+    from srb200.graph import GraphBatch, StateGraph
+    import torch
+    g = golden["ends"]
+    models = models_from(g["en_mu"], g["en_cov"], g["en_w"], g["en_wtrans"])
+    E = dev_E(eng, g["en_X"], models)
+    T = len(g["en_X"])
+    off = np.array([0, T], np.int32)
+    for k in range(int(g["en_n"])):
+        el = g[f"en_list{k}"]
+        gb = GraphBatch([StateGraph(g["en_trans"], g["en_emit"], end_states=el[:, 0], end_frames=el[:, 1])], E.device)
+        assert "end_frame" in gb.dev
+        fl = torch.full((T,), -7, dtype=torch.int32, device=E.device)
+        res = eng.viterbi(E, off, gb, want_costs=True, frame_label=fl)
+        ref = g[f"en_costs{k}"]
+        got = res.costs.cpu().numpy().reshape(T, -1).T
+        f = np.isfinite(ref)
+        np.testing.assert_allclose(got[f], ref[f], rtol=RTOL)
+        rp = g[f"en_path{k}"]
+        if np.isfinite(res.best_cost.cpu().numpy()[0]):
+            assert np.array_equal(res.paths()[0], rp)
+            lab = fl.cpu().numpy()
+            assert (lab[np.asarray(rp)[:, 1].max() + 2:] == -1).all()
+        else:
+            assert res.path_len.cpu().numpy()[0] == 0
+    with pytest.raises(Exception):
+        eng.viterbi(E, off, gb, want_costs=False)          # end frames need the cost matrix

@@ -112,6 +112,38 @@ def test_dtw_and_helpers(golden):
     np.testing.assert_allclose(orc.calc_variance(xs[1]), g["cv_out"], rtol=1e-11)
 
 
+def test_dtw_beam(golden):
+    """oracle.dtw_beam against dtw(..., beam=k) of the reference (decode.py:42-48,62-68): costs incl. -1 marks, paths."""
+    g = golden["beam"]
+    xs = unragged(g["bm_X"], g["bm_off"])
+    for k, (beam, maha, ti, u, plen) in enumerate(g["bm_cases"]):
+        Dl = orc.local_dist(xs[u], g["bm_y"], g["bm_var"] if maha else None)
+        costs, path = orc.dtw_beam(Dl, g["bm_trans2"] if ti else g["bm_trans"], int(beam))
+        ref = g[f"bm_costs{k}"]
+        f = np.isfinite(ref)
+        assert np.array_equal(np.isfinite(costs), f)
+        np.testing.assert_allclose(costs[f], ref[f], rtol=RT)
+        assert np.array_equal(path, g[f"bm_path{k}"])
+    # beam = inf is the C restatement's dtw
+    Dl = orc.local_dist(xs[2], g["bm_y"])
+    c0, p0 = orc.dtw(xs[2], g["bm_y"], g["bm_trans"])
+    c1, p1 = orc.dtw_beam(Dl, g["bm_trans"])
+    assert np.array_equal(c0, c1) and np.array_equal(p0, p1)
+
+
+def test_end_points_off_the_last_frame(golden):
+    """orc_decode with any [state, frame] end points (decode.py:126-146)."""
+    g = golden["ends"]
+    models = models_from(g["en_mu"], g["en_cov"], g["en_w"], g["en_wtrans"])
+    emit, trans = g["en_emit"], g["en_trans"]
+    E = orc.emissions(g["en_X"], models, emit)
+    for k in range(int(g["en_n"])):
+        costs, path, _ = orc.decode_hmm_states(E, trans, emit < 0, g[f"en_list{k}"])
+        f = np.isfinite(g[f"en_costs{k}"])
+        np.testing.assert_allclose(costs[f], g[f"en_costs{k}"][f], rtol=RT)
+        assert np.array_equal(path.reshape(-1, 2), g[f"en_path{k}"])
+
+
 def test_kmeans_and_em(golden):
     g = golden["kmeans_em"]
     data = g["km_data"]
