@@ -187,6 +187,30 @@ int srb_path_words(const int32_t *path_state, const int64_t *path_off, const int
                    const int32_t *utt_graph, const int32_t *g_state_off, const int32_t *state_word, int32_t max_words,
                    int32_t *words, int32_t *nwords, void *stream);
 
+/* ---- text_viterbi over a lexical tree (sr/langmodel/spellchecker.py:15-135) --------------------------
+ * The edit-distance dynamic programme of '*' + text against the flattened lextree with a loop back to the root.
+ * Tree (built by the host, sr/langmodel/lextree.py FlatTree): n_rows nodes in the depth-first order of
+ * spellchecker.py:7-12, the LAST row being the blank node the spell-checker appends (:37); node_val int32[n_rows]
+ * (character code), node_parent int32[n_rows] (spellchecker.py:52-63; -1 for the root and the blank node);
+ * level_nodes = node indices of depth >= 1 sorted by depth, level_off int32[n_levels+1] their ranges (a node's only
+ * same-column predecessor is its parent: a column is swept level by level); word_ends int32[n_ends] = blank node
+ * first, then the end-of-word nodes in index order (:54-59), n_ends >= 2.
+ * Strings: x int32[sum n_cols] character codes INCLUDING the leading '*' (:26), x_off int64[B+1]; n_cols >= 2.
+ * dist (optional) float[sum n_cols, n_rows] = dist_fun(x[c], node r) for a caller-supplied distance; NULL = the
+ * default int(a != b) (:15).  Costs: deletion 1, insertion 1, match 0, space 0, loop 1 (:28-32); first minimum of
+ * [deletion, match, insertion, loop] and of the word-end lists (np.argmin).
+ * Workspaces (caller-owned): col_ws float[B * 2 * n_rows]; bp uint8[bp_off[u] + c*n_rows + r] (bp_off[u] =
+ * x_off[u] * n_rows); bp_jump int32[sum n_cols, 2].
+ * Outputs: best_cost[B] (:123); out_nodes[out_off[u] ...] the node indices the walk back of :126-135 appends, END OF
+ * THE STRING FIRST (the caller maps them to characters and reverses, :135); out_len[u] their count, -1 when the
+ * capacity out_off[u+1]-out_off[u] was too small (n_cols * (n_levels + 2) always suffices), -2 for an empty text and
+ * -3 when the walk jumps past column 1 (in both cases the reference's `while 1` does not terminate). */
+int srb_text_viterbi(const int32_t *x, const int64_t *x_off, int32_t B, const int32_t *node_val,
+                     const int32_t *node_parent, const int32_t *level_nodes, const int32_t *level_off, int32_t n_levels,
+                     int32_t n_rows, const int32_t *word_ends, int32_t n_ends, const float *dist, float *col_ws,
+                     uint8_t *bp, const int64_t *bp_off, int32_t *bp_jump, float *best_cost, int32_t *out_nodes,
+                     const int64_t *out_off, int32_t *out_len, void *stream);
+
 /* ---- K4: batched forward-backward (Baum-Welch E-step) for NES-free graphs -------------------------
  * The reference has NO forward-backward; semantics are defined to be consistent with
  * srb_viterbi_graph: same graph packing, start in state 0 at frame 0, end in any end_state at the last frame;

@@ -597,3 +597,54 @@ def local_dist(X, Y, var=None, shared_var=False, want_dist=True, want_argmin=Fal
     _l.check(_l.load().srb_local_dist(_l.ptr(X), X.shape[0], D, _l.ptr(Y), _l.ptr(v), S, 0 if var is None else 1,
                                       0 if shared_var else D, _l.ptr(out), S, _l.ptr(am), _l.stream_ptr()))
     return out, am
+
+
+# ------------------------------------------------------------------------------------------------ lextree (f4)
+class DeviceLexTree:
+    """A flattened lextree (sr/langmodel/lextree.py FlatTree) resident on the device for srb_text_viterbi."""
+
+    def __init__(self, flat):
+        dev = device()
+        self.flat = flat
+        self.n_rows, self.n_levels, self.n_ends = int(flat.n_rows), int(flat.n_levels), int(len(flat.word_ends))
+        self.val = torch.from_numpy(flat.val).to(dev)
+        self.parent = torch.from_numpy(flat.parent).to(dev)
+        self.level_nodes = torch.from_numpy(flat.level_nodes if len(flat.level_nodes) else np.zeros(1, np.int32)).to(dev)
+        self.level_off = torch.from_numpy(flat.level_off).to(dev)
+        self.word_ends = torch.from_numpy(flat.word_ends).to(dev)
+
+
+def text_viterbi(codes, tree, dist=None):
+    """srb_text_viterbi for a batch of strings against one tree.
+    codes: list of int32 arrays = character codes of '*' + text (spellchecker.py:26); tree: DeviceLexTree;
+    dist: optional [sum n_cols, n_rows] float32 matrix of a caller-supplied dist_fun.
+    -> (best_cost float64 [B], list of node-index arrays in FORWARD order = the matched strings' nodes)."""
+    dev = tree.val.device
+    B = len(codes)
+    n_cols = np.array([len(c) for c in codes], np.int64)
+    if (n_cols < 2).any():
+        raise ValueError("text_viterbi needs a non-empty text (the reference's walk back does not terminate on '')")
+    x_off = np.zeros(B + 1, np.int64)
+    np.cumsum(n_cols, out=x_off[1:])
+    out_off = np.zeros(B + 1, np.int64)
+    np.cumsum(n_cols * (tree.n_levels + 2), out=out_off[1:])
+    x = torch.from_numpy(np.concatenate(codes).astype(np.int32)).to(dev)
+    col_ws = torch.empty(B * 2 * tree.n_rows, dtype=torch.float32, device=dev)
+    bp = torch.empty(int(x_off[-1]) * tree.n_rows, dtype=torch.uint8, device=dev)
+    jump = torch.empty((int(x_off[-1]), 2), dtype=torch.int32, device=dev)
+    best = torch.empty(B, dtype=torch.float32, device=dev)
+    out = torch.empty(int(out_off[-1]), dtype=torch.int32, device=dev)
+    out_len = torch.empty(B, dtype=torch.int32, device=dev)
+    d = None if dist is None else dist.to(dev, torch.float32).contiguous()
+    assert d is None or tuple(d.shape) == (int(x_off[-1]), tree.n_rows)
+    _l.check(_l.load().srb_text_viterbi(
+        _l.ptr(x), _l.ptr(torch.from_numpy(x_off).to(dev)), B, _l.ptr(tree.val), _l.ptr(tree.parent),
+        _l.ptr(tree.level_nodes), _l.ptr(tree.level_off), tree.n_levels, tree.n_rows, _l.ptr(tree.word_ends), tree.n_ends,
+        _l.ptr(d), _l.ptr(col_ws), _l.ptr(bp), _l.ptr(torch.from_numpy(x_off * tree.n_rows).to(dev)), _l.ptr(jump),
+        _l.ptr(best), _l.ptr(out), _l.ptr(torch.from_numpy(out_off).to(dev)), _l.ptr(out_len), _l.stream_ptr()))
+    ln, on = out_len.cpu().numpy(), out.cpu().numpy()
+    if (ln == -3).any() or (ln == -2).any():
+        raise RuntimeError("text_viterbi: the walk back does not reach column 1 (the reference loops forever here)")
+    if (ln < 0).any():
+        raise RuntimeError("text_viterbi: output capacity exhausted")
+    return best.double().cpu().numpy(), [on[out_off[u]:out_off[u] + ln[u]][::-1].copy() for u in range(B)]

@@ -35,6 +35,8 @@ SIGNATURES = {
     "srb_viterbi_graph": (c_int, [c_void_p, c_i64, c_void_p, c_i32] + [c_void_p] * 11 + [c_i32] + [c_void_p] * 11),
     "srb_dtw_beam": (c_int, [c_void_p, c_i64, c_void_p, c_i32, c_void_p, c_i32, c_i32] + [c_void_p] * 8),
     "srb_viterbi_banded": (c_int, [c_void_p, c_i64, c_void_p, c_i32] + [c_void_p] * 16 + [c_i32] + [c_void_p] * 11),
+    "srb_text_viterbi": (c_int, [c_void_p, c_void_p, c_i32] + [c_void_p] * 4 + [c_i32, c_i32, c_void_p, c_i32] +
+                         [c_void_p] * 10),
     "srb_mfcc_num_frames": (c_i64, [c_i64, c_int]),
     "srb_mfcc": (c_int, [c_void_p, c_void_p, c_void_p, c_i32, c_i64, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
                          c_void_p]),

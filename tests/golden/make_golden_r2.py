@@ -90,10 +90,67 @@ def case_ends(out):
     out["en_n"] = np.int64(len(lists))
 
 
+VOWELS = set("aeiou")
+
+
+def soft_dist(a, b):
+    """A caller-supplied dist_fun for text_viterbi: vowels are half as far from each other as other characters."""
+    if a == b:
+        return 0.0
+    return 0.5 if (a in VOWELS and b in VOWELS) else 1.0
+
+
+def case_lextree(out):
+    import random
+    import pandas as pd
+    import sr.langmodel as lm
+    assert lm.__file__.startswith("/root/reference")
+    sys.setrecursionlimit(20000)
+    words_all = [str(w) for w in pd.read_csv("/root/reference/tests/test_data/dict1.txt")["words"].values.tolist()]
+    rnd = random.Random(4242)
+    dicts = [
+        ["once", "upon", "a", "time", "on", "one", "up", "tim", "at", "an", "and", "ant"],
+        ["a", "a", "ab", "ab", "abc", "b", "ba", "bab", "c"],                       # duplicates: the skipped-element quirk
+        rnd.sample(words_all, 120),
+        rnd.sample(words_all, 400) + ["the", "a", "of", "to", "monkey", "crocodile", "said", "heart", "tree", "river"],
+    ]
+    texts = [
+        ["onse apon a tyme", "a", "at an ant", "xyz", "oneup on", "tim e", "uponn a a tme"],
+        ["abc ab a", "bab c", "cab", "aabbcc", "b"],
+        ["tha quick brwn fox", "helo wrld", "zzzz", "e"],
+        ["the munkey sed to the krocodile", "harte of the tre", "rever", "a", "onse upon a tyme the monkey said"],
+    ]
+
+    def flat(tree):
+        nodes = []
+        lm.get_nodes(nodes, tree)
+        idx = {id(n): i for i, n in enumerate(nodes)}
+        parent = np.full(len(nodes), -1, np.int64)
+        for n in nodes:
+            for c in n.children:
+                parent[idx[id(c)]] = idx[id(n)]
+        return np.array([n.val for n in nodes]), np.array([n.property for n in nodes], np.int64), parent
+
+    for d, (words, txts) in enumerate(zip(dicts, texts)):
+        out[f"lt{d}_words"] = np.array(words)
+        tree = lm.lextree_from_words(list(words))
+        v, pr, pa = flat(tree)
+        out[f"lt{d}_vals"], out[f"lt{d}_props"], out[f"lt{d}_parent"] = v, pr, pa
+        out[f"lt{d}_texts"] = np.array(txts)
+        res = [lm.text_viterbi(t, tree) for t in txts]
+        out[f"lt{d}_cost"] = np.array([r[0] for r in res], np.float64)
+        out[f"lt{d}_match"] = np.array([r[1] for r in res])
+        if d in (0, 2):
+            res = [lm.text_viterbi(t, tree, soft_dist) for t in txts]
+            out[f"lt{d}_soft_cost"] = np.array([r[0] for r in res], np.float64)
+            out[f"lt{d}_soft_match"] = np.array([r[1] for r in res])
+    out["lt_n"] = np.int64(len(dicts))
+
+
 def main():
     import time
     only = set(sys.argv[1:])
-    for name, fn in (("beam", case_beam), ("ends", case_ends)):
+    for name, fn in (("beam", case_beam), ("ends", case_ends), ("lextree", case_lextree)):
         if only and name not in only:
             continue
         t0 = time.time()
