@@ -217,25 +217,31 @@ int srb_text_viterbi(const int32_t *x, const int64_t *x_off, int32_t B, const in
  * min instead of log-sum-exp gives the Viterbi costs.  succ_* is the successor CSR of the same edges
  * (succ_ptr absolute, per origin), pred_tgt[j] the target of predecessor edge j.
  *   gamma[ws_off[u] + c*R + r]  state posterior (sums to 1 over r);  neg_log_z[u] = -log P(x) (double)
- *   xi_sum[j] += sum_c posterior of edge j (double, indexed like pred_idx; caller zeroes it; optional). */
+ *   xi_sum[j] += sum_c posterior of edge j (double, indexed like pred_idx; caller zeroes it; optional).  It is formed
+ *   WITHOUT atomics: every warp adds its utterances' edge posteriors to a private row of the caller-owned workspace
+ *   xi_part (srb_fb_xi_parts() rows of nnz_total doubles, nnz_total = number of edges of all packed graphs) and the
+ *   rows are summed in a fixed order, so xi_sum is bit-reproducible run to run (needed when xi_sum != NULL). */
+int srb_fb_xi_parts(void);
 int srb_forward_backward(const float *E, int64_t ldE, const int32_t *utt_off, int32_t B, const int32_t *utt_graph,
                          const int32_t *g_state_off, const int32_t *g_end_off, const int32_t *emit,
                          const int32_t *pred_ptr, const int32_t *pred_idx, const float *pred_cost,
                          const int32_t *pred_tgt, const int32_t *succ_ptr, const int32_t *succ_idx,
                          const float *succ_cost, const int32_t *end_state, int32_t Rmax, int32_t NNZmax,
-                         const int64_t *ws_off, float *gamma, double *neg_log_z, double *xi_sum, void *stream);
+                         const int64_t *ws_off, float *gamma, double *neg_log_z, double *xi_sum, double *xi_part,
+                         int32_t nnz_total, void *stream);
 
 /* The same E-step for left-to-right models: every graph NES-free with all predecessors of r inside {r-2, r-1, r}
  * (what HMM.fit / calc_transition_costs build, kmeans.py:53-95) and Rmax <= 32.  band / codes as in
  * srb_viterbi_banded (band[r] = costs from r-2, r-1, r; codes[r] = their positions in r's predecessor list, one
  * byte each); order: optional int32[B] permutation of the utterances (falling length balances the lane groups).
- * One lane per state, 32 / pow2(Rmax) utterances per warp; outputs as srb_forward_backward (xi_sum to 1e-6 relative:
- * the per-utterance sums are formed in registers before the atomic). */
+ * One lane per state, 32 / pow2(Rmax) utterances per warp; outputs and the xi_part workspace as srb_forward_backward
+ * (the per-utterance edge sums are formed in registers, then added to the warp's row). */
 int srb_forward_backward_banded(const float *E, int64_t ldE, const int32_t *utt_off, int32_t B, const int32_t *utt_graph,
                                 const int32_t *g_state_off, const int32_t *g_end_off, const int32_t *emit,
                                 const int32_t *pred_ptr, const int32_t *end_state, const float *band,
                                 const int32_t *codes, const int32_t *order, int32_t Rmax, const int64_t *ws_off,
-                                float *gamma, double *neg_log_z, double *xi_sum, void *stream);
+                                float *gamma, double *neg_log_z, double *xi_sum, double *xi_part, int32_t nnz_total,
+                                void *stream);
 
 
 /* ---- K5 / K6: sufficient statistics, K-means assignment, M-step ---------------------------------

@@ -210,17 +210,52 @@ def dtw_beam(Dl, trans, beam=np.inf):
     return costs, np.array(path, np.int64).reshape(-1, 2)
 
 
-def forward_backward(E, trans):
-    """No reference counterpart (parity unpinned).  -> (neg_log_Z, alpha[T,R], beta[T,R], gamma[T,R])."""
+def forward_backward(E, trans, semiring="sum"):
+    """No reference counterpart (parity unpinned).  -> (neg_log_Z, alpha[T,R], beta[T,R], gamma[T,R]).
+    semiring="min" runs the SAME recursion with min in place of -log-sum-exp: alpha is then decode_hmm_states' cost
+    matrix bit for bit, the identity that ties this restatement to the reference (decode.py:97-124)."""
     E, Ep = _d(E)
     T, R = E.shape
     trans, tp = _d(trans)
     a = np.empty((T, R))
     b = np.empty((T, R))
     g = np.empty((T, R))
-    nlz = lib().orc_forward_backward(Ep, ctypes.c_int64(T), R, tp, a.ctypes.data_as(c_dp), b.ctypes.data_as(c_dp),
-                                     g.ctypes.data_as(c_dp))
+    fn = lib().orc_forward_backward_sr
+    fn.restype = ctypes.c_double
+    nlz = fn(Ep, ctypes.c_int64(T), R, tp, a.ctypes.data_as(c_dp), b.ctypes.data_as(c_dp), g.ctypes.data_as(c_dp),
+             int(semiring == "min"))
     return float(nlz), a, b, g
+
+
+def forward_backward_bruteforce(E, trans, end_states=None):
+    """Forward-backward by ENUMERATING every state sequence (independent of any recursion; T <= 10, R <= 4 or so):
+    weight(path) = exp(-(sum_c E[c, s_c] + sum_c trans[s_c, s_{c-1}])), paths start in state 0 at frame 0
+    (decode.py:99-100) and end in one of end_states (default: the last state, decode.py:126-127) at the last frame.
+    -> (neg_log_Z, gamma[T,R], xi[R,R] summed over frames: xi[r, o] = posterior mass of the arcs o -> r)."""
+    import itertools
+    E = np.asarray(E, np.float64)
+    T, R = E.shape
+    trans = np.asarray(trans, np.float64)
+    ends = [R - 1] if end_states is None else list(end_states)
+    Z = 0.0
+    gamma = np.zeros((T, R))
+    xi = np.zeros((R, R))
+    for tail in itertools.product(range(R), repeat=T - 1):
+        path = (0,) + tail
+        if path[-1] not in ends:
+            continue
+        cost = E[0, 0]
+        for c in range(1, T):
+            cost += trans[path[c], path[c - 1]] + E[c, path[c]]
+        if not np.isfinite(cost):
+            continue
+        w = np.exp(-cost)
+        Z += w
+        for c in range(T):
+            gamma[c, path[c]] += w
+            if c:
+                xi[path[c], path[c - 1]] += w
+    return -np.log(Z), gamma / Z, xi / Z
 
 
 # ------------------------------------------------------------------------------------ kmeans.py helpers

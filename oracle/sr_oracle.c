@@ -393,8 +393,14 @@ static double neg_lse2(double a, double b) { /* -log(exp(-a)+exp(-b)) */
     return m - log(exp(-(a - m)) + exp(-(b - m)));
 }
 
-double orc_forward_backward(const double *E, int64_t T, int R, const double *trans, double *alpha, double *beta,
-                            double *gamma) {
+static double neg_min2(double a, double b) { return a < b ? a : b; }
+
+/* semiring != 0: (min, +) instead of (-log-sum-exp, +), i.e. the SAME recursion with every sum over paths replaced
+ * by the best path -- alpha then equals orc_decode's cost matrix bit for bit (same additions in the same order),
+ * which ties this restatement to decode_hmm_states (decode.py:97-124). */
+double orc_forward_backward_sr(const double *E, int64_t T, int R, const double *trans, double *alpha, double *beta,
+                               double *gamma, int semiring) {
+    double (*comb)(double, double) = semiring ? neg_min2 : neg_lse2;
     for (int64_t i = 0; i < T * R; ++i) alpha[i] = beta[i] = ORC_INF;
     alpha[0] = E[0];
     for (int64_t c = 1; c < T; ++c)
@@ -403,7 +409,7 @@ double orc_forward_backward(const double *E, int64_t T, int R, const double *tra
             for (int o = 0; o < R; ++o) {
                 double tr = trans[(int64_t)r * R + o];
                 if (isinf(tr)) continue;
-                a = neg_lse2(a, tr + alpha[(c - 1) * R + o]);
+                a = comb(a, tr + alpha[(c - 1) * R + o]);
             }
             alpha[c * R + r] = a + E[c * R + r];
         }
@@ -414,7 +420,7 @@ double orc_forward_backward(const double *E, int64_t T, int R, const double *tra
             for (int r = 0; r < R; ++r) {
                 double tr = trans[(int64_t)r * R + o];
                 if (isinf(tr)) continue;
-                b = neg_lse2(b, tr + E[(c + 1) * R + r] + beta[(c + 1) * R + r]);
+                b = comb(b, tr + E[(c + 1) * R + r] + beta[(c + 1) * R + r]);
             }
             beta[c * R + o] = b;
         }
@@ -422,6 +428,11 @@ double orc_forward_backward(const double *E, int64_t T, int R, const double *tra
     if (gamma)
         for (int64_t i = 0; i < T * R; ++i) gamma[i] = exp(-(alpha[i] + beta[i] - nlz));
     return nlz;
+}
+
+double orc_forward_backward(const double *E, int64_t T, int R, const double *trans, double *alpha, double *beta,
+                            double *gamma) {
+    return orc_forward_backward_sr(E, T, R, trans, alpha, beta, gamma, 0);
 }
 
 

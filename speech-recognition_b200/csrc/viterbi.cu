@@ -828,11 +828,20 @@ forward_backward_kernel(const float *__restrict__ E, int64_t ldE, const int32_t 
                         GraphBatch G, const int32_t *__restrict__ succ_ptr, const int32_t *__restrict__ succ_idx,
                         const float *__restrict__ succ_cost, const int32_t *__restrict__ pred_tgt, int Rmax,
                         int NNZmax, const int64_t *__restrict__ ws_off, float *__restrict__ gamma,
-                        double *__restrict__ neg_log_z, double *__restrict__ xi_sum) {
-    extern __shared__ float vsm[];
+                        double *__restrict__ neg_log_z, double *__restrict__ xi_part, int nnz_total) {
+    extern __shared__ __align__(8) float vsm[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    float *colA = vsm + (size_t)warp * (2 * Rmax + NNZmax), *colB = colA + Rmax, *xi = colB + Rmax;
+    double *xacc = reinterpret_cast<double *>(vsm) + (size_t)warp * NNZmax;   // this utterance's edge posteriors
+    float *colA = vsm + (size_t)VW * NNZmax * 2 + (size_t)warp * (2 * Rmax + NNZmax), *colB = colA + Rmax,
+          *xi = colB + Rmax;
     const float INF = CUDART_INF_F;
+    // edge posteriors without atomics: every warp owns one row of xi_part (zeroed here, summed over the utterances the
+    // warp walks, reduced over the rows in a fixed order by xi_reduce_kernel) -- the result does not depend on timing
+    double *wrow = xi_part ? xi_part + (size_t)(blockIdx.x * VW + warp) * nnz_total : nullptr;
+    if (wrow) {
+        for (int j = lane; j < nnz_total; j += 32) wrow[j] = 0.0;
+        __syncwarp();
+    }
 
     for (int u = blockIdx.x * VW + warp; u < B; u += gridDim.x * VW) {
         const int g = G.utt_graph ? G.utt_graph[u] : 0;
@@ -890,7 +899,10 @@ forward_backward_kernel(const float *__restrict__ E, int64_t ldE, const int32_t 
         if (lane == 0 && neg_log_z) neg_log_z[u] = (zl < INF) ? scale + (double)zl : (double)INF;
         // ---- backward; colA/colB now hold beta_hat columns
         float *bnext = colA, *bcur = colB;
-        for (int j = lane; j < nnz; j += 32) xi[j] = 0.f;
+        for (int j = lane; j < nnz; j += 32) {
+            xi[j] = 0.f;
+            xacc[j] = 0.0;
+        }
         for (int r = lane; r < R; r += 32) bnext[r] = INF;
         __syncwarp();
         for (int e = G.g_end_off[g] + lane; e < G.g_end_off[g + 1]; e += 32) bnext[G.end_state[e]] = 0.f;
@@ -927,8 +939,8 @@ forward_backward_kernel(const float *__restrict__ E, int64_t ldE, const int32_t 
                 }
                 xs = warp_sum(xs);
                 const float xinv = xs > 0.f ? 1.f / xs : 0.f;
-                if (xi_sum)
-                    for (int j = lane; j < nnz; j += 32) atomicAdd(xi_sum + e0 + j, (double)(xi[j] * xinv));
+                if (wrow)
+                    for (int j = lane; j < nnz; j += 32) xacc[j] += (double)(xi[j] * xinv);   // lane-private entries
             }
             for (int r = lane; r < R; r += 32) gu[(size_t)c * R + r] = bcur[r] * inv;
             __syncwarp();
@@ -955,8 +967,28 @@ forward_backward_kernel(const float *__restrict__ E, int64_t ldE, const int32_t 
             bnext = bcur;
             bcur = t;
         }
+        if (wrow)
+            for (int j = lane; j < nnz; j += 32) wrow[e0 + j] += xacc[j];
         __syncwarp();
     }
+}
+
+// xi_sum[j] += sum over the per-warp rows of xi_part, in a FIXED order: thread t of block j adds rows t, t + 256, ...
+// in ascending order, then the 256 partial sums are folded by a fixed-shape tree.
+__global__ void __launch_bounds__(256)
+xi_reduce_kernel(const double *__restrict__ part, int nparts, int nnz, double *__restrict__ xi_sum) {
+    __shared__ double red[256];
+    const int j = blockIdx.x, t = threadIdx.x;
+    double s = 0.0;
+    for (int p = t; p < nparts; p += 256) s += part[(size_t)p * nnz + j];
+    red[t] = s;
+    __syncthreads();
+#pragma unroll
+    for (int d = 128; d; d >>= 1) {
+        if (t < d) red[t] += red[t + d];
+        __syncthreads();
+    }
+    if (t == 0) xi_sum[j] += red[0];
 }
 
 // ------------------------------------------------------------------------------------------------ K4, banded
@@ -964,8 +996,9 @@ forward_backward_kernel(const float *__restrict__ E, int64_t ldE, const int32_t 
 // what HMM.fit / calc_transition_costs produce, kmeans.py:53-95).  A group of W = pow2 >= Rmax lanes owns one utterance
 // (32 / W utterances per warp), a lane owns one state: alpha / beta live in a register, the band costs and the CSR
 // positions of the three arcs are read once per utterance, predecessors / successors arrive by width-W shuffles, the
-// emission and alpha_hat loads run one column ahead, and the edge posteriors are summed in registers -- one atomic per
-// arc per UTTERANCE instead of one per frame.  `order` (optional) lists the utterances by falling length so that the
+// emission and alpha_hat loads run one column ahead, and the edge posteriors are summed in registers and added once per
+// UTTERANCE to the warp's private row of xi_part (no atomics: the groups of a warp take turns, rows are reduced in a
+// fixed order by xi_reduce_kernel).  `order` (optional) lists the utterances by falling length so that the
 // groups of a warp finish together.  Same boundary conditions, renormalisation and outputs as forward_backward_kernel.
 template <int W>
 __device__ __forceinline__ float group_min(float v) {
@@ -991,11 +1024,17 @@ __global__ void __launch_bounds__(VW * 32)
 forward_backward_banded_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *__restrict__ off, int B,
                                GraphBatch G, const float *__restrict__ band, const int32_t *__restrict__ codes,
                                const int32_t *__restrict__ order, const int64_t *__restrict__ ws_off,
-                               float *__restrict__ gamma, double *__restrict__ neg_log_z, double *__restrict__ xi_sum) {
+                               float *__restrict__ gamma, double *__restrict__ neg_log_z, double *__restrict__ xi_part,
+                               int nnz_total) {
     constexpr int GPW = 32 / W;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, sub = lane & (W - 1), grp = lane / W;
     const float INF = CUDART_INF_F;
     const int nslots = (B + GPW - 1) / GPW;
+    double *wrow = xi_part ? xi_part + (size_t)(blockIdx.x * VW + warp) * nnz_total : nullptr;
+    if (wrow) {
+        for (int j = lane; j < nnz_total; j += 32) wrow[j] = 0.0;
+        __syncwarp();
+    }
 
     for (int slot = blockIdx.x * VW + warp; slot < nslots; slot += gridDim.x * VW) {
         const int idx = slot * GPW + grp;
@@ -1103,10 +1142,18 @@ forward_backward_banded_kernel(const float *__restrict__ E, int64_t ldE, const i
             al_p = al_n;
             e_c = e_n;
         }
-        if (xi_sum && act && T > 0) {
-            if (a2 < INF) atomicAdd(xi_sum + arc2, x2);
-            if (a1 < INF) atomicAdd(xi_sum + arc1, x1);
-            if (a0 < INF) atomicAdd(xi_sum + arc0, x0);
+        if (wrow) {
+            // the groups of a warp may sit on the same word (same arcs): they add in turn; inside a group every lane
+            // owns its state's three arcs
+#pragma unroll
+            for (int gi = 0; gi < GPW; ++gi) {
+                if (grp == gi && act && T > 0) {
+                    if (a2 < INF) wrow[arc2] += x2;
+                    if (a1 < INF) wrow[arc1] += x1;
+                    if (a0 < INF) wrow[arc0] += x0;
+                }
+                __syncwarp();
+            }
         }
     }
 }
@@ -1152,14 +1199,19 @@ using namespace srb;
 template <int W>
 static int launch_fb_banded(const float *E, int64_t ldE, const int32_t *utt_off, int32_t B, const GraphBatch &G,
                             const float *band, const int32_t *codes, const int32_t *order, const int64_t *ws_off,
-                            float *gamma, double *neg_log_z, double *xi_sum, void *stream) {
+                            float *gamma, double *neg_log_z, double *xi_sum, double *xi_part, int nnz_total,
+                            void *stream) {
     const int64_t slots = ((int64_t)B * W + 31) / 32;
     int64_t grid = (slots + VW - 1) / VW;
     const int64_t cap = (int64_t)sm_count() * 16;
     if (grid > cap) grid = cap;
     forward_backward_banded_kernel<W><<<(int)grid, VW * 32, 0, (cudaStream_t)stream>>>(
-        E, ldE, utt_off, B, G, band, codes, order, ws_off, gamma, neg_log_z, xi_sum);
+        E, ldE, utt_off, B, G, band, codes, order, ws_off, gamma, neg_log_z, xi_sum ? xi_part : nullptr, nnz_total);
     SRB_CUDA(cudaGetLastError());
+    if (xi_sum) {
+        xi_reduce_kernel<<<nnz_total, 256, 0, (cudaStream_t)stream>>>(xi_part, (int)grid * VW, nnz_total, xi_sum);
+        SRB_CUDA(cudaGetLastError());
+    }
     return SRB_OK;
 }
 
@@ -1273,13 +1325,16 @@ int srb_forward_backward(const float *E, int64_t ldE, const int32_t *utt_off, in
                          const int32_t *pred_ptr, const int32_t *pred_idx, const float *pred_cost,
                          const int32_t *pred_tgt, const int32_t *succ_ptr, const int32_t *succ_idx,
                          const float *succ_cost, const int32_t *end_state, int32_t Rmax, int32_t NNZmax,
-                         const int64_t *ws_off, float *gamma, double *neg_log_z, double *xi_sum, void *stream) {
+                         const int64_t *ws_off, float *gamma, double *neg_log_z, double *xi_sum, double *xi_part,
+                         int32_t nnz_total, void *stream) {
     SRB_REQUIRE(E && utt_off && g_state_off && g_end_off && emit && pred_ptr && pred_idx && pred_cost && pred_tgt &&
                     succ_ptr && succ_idx && succ_cost && end_state && ws_off && gamma,
                 SRB_EINVAL, "srb_forward_backward: null pointer");
     SRB_REQUIRE(B >= 0 && Rmax > 0 && NNZmax >= 0 && ldE > 0, SRB_EINVAL, "srb_forward_backward: bad sizes");
+    SRB_REQUIRE(!xi_sum || (xi_part && nnz_total > 0), SRB_EINVAL,
+                "srb_forward_backward: xi_sum needs the xi_part workspace (srb_fb_xi_parts() * nnz_total doubles)");
     if (B == 0) return SRB_OK;
-    const size_t bytes = (size_t)VW * (2 * Rmax + NNZmax) * sizeof(float);
+    const size_t bytes = (size_t)VW * ((2 * Rmax + NNZmax) * sizeof(float) + NNZmax * sizeof(double));
     SRB_REQUIRE(bytes <= (size_t)smem_optin(), SRB_EUNSUPPORTED, "srb_forward_backward: graph too large for shared memory");
     SRB_CUDA(cudaFuncSetAttribute(forward_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     const int sms = sm_count();
@@ -1289,19 +1344,29 @@ int srb_forward_backward(const float *E, int64_t ldE, const int32_t *utt_off, in
     GraphBatch G = make_graph(utt_graph, g_state_off, g_state_off, g_end_off, emit, pred_ptr, pred_idx, pred_cost, nullptr,
                               end_state);
     forward_backward_kernel<<<(int)grid, VW * 32, bytes, (cudaStream_t)stream>>>(
-        E, ldE, utt_off, B, G, succ_ptr, succ_idx, succ_cost, pred_tgt, Rmax, NNZmax, ws_off, gamma, neg_log_z, xi_sum);
+        E, ldE, utt_off, B, G, succ_ptr, succ_idx, succ_cost, pred_tgt, Rmax, NNZmax, ws_off, gamma, neg_log_z,
+        xi_sum ? xi_part : nullptr, nnz_total);
     SRB_CUDA(cudaGetLastError());
+    if (xi_sum) {
+        xi_reduce_kernel<<<nnz_total, 256, 0, (cudaStream_t)stream>>>(xi_part, (int)grid * VW, nnz_total, xi_sum);
+        SRB_CUDA(cudaGetLastError());
+    }
     return SRB_OK;
 }
+
+int srb_fb_xi_parts(void) { return sm_count() * 16 * VW; }
 
 int srb_forward_backward_banded(const float *E, int64_t ldE, const int32_t *utt_off, int32_t B, const int32_t *utt_graph,
                                 const int32_t *g_state_off, const int32_t *g_end_off, const int32_t *emit,
                                 const int32_t *pred_ptr, const int32_t *end_state, const float *band,
                                 const int32_t *codes, const int32_t *order, int32_t Rmax, const int64_t *ws_off,
-                                float *gamma, double *neg_log_z, double *xi_sum, void *stream) {
+                                float *gamma, double *neg_log_z, double *xi_sum, double *xi_part, int32_t nnz_total,
+                                void *stream) {
     SRB_REQUIRE(E && utt_off && g_state_off && g_end_off && emit && pred_ptr && end_state && band && codes && ws_off &&
                     gamma,
                 SRB_EINVAL, "srb_forward_backward_banded: null pointer");
+    SRB_REQUIRE(!xi_sum || (xi_part && nnz_total > 0), SRB_EINVAL,
+                "srb_forward_backward_banded: xi_sum needs the xi_part workspace (srb_fb_xi_parts() * nnz_total doubles)");
     SRB_REQUIRE(B >= 0 && Rmax > 0 && ldE > 0, SRB_EINVAL, "srb_forward_backward_banded: bad sizes");
     SRB_REQUIRE(Rmax <= 32, SRB_EUNSUPPORTED, "srb_forward_backward_banded: %d states (at most 32: use srb_forward_backward)",
                 Rmax);
@@ -1309,12 +1374,16 @@ int srb_forward_backward_banded(const float *E, int64_t ldE, const int32_t *utt_
     GraphBatch G = make_graph(utt_graph, g_state_off, g_state_off, g_end_off, emit, pred_ptr, nullptr, nullptr, nullptr,
                               end_state);
     if (Rmax <= 4)
-        return launch_fb_banded<4>(E, ldE, utt_off, B, G, band, codes, order, ws_off, gamma, neg_log_z, xi_sum, stream);
+        return launch_fb_banded<4>(E, ldE, utt_off, B, G, band, codes, order, ws_off, gamma, neg_log_z, xi_sum, xi_part,
+                                   nnz_total, stream);
     if (Rmax <= 8)
-        return launch_fb_banded<8>(E, ldE, utt_off, B, G, band, codes, order, ws_off, gamma, neg_log_z, xi_sum, stream);
+        return launch_fb_banded<8>(E, ldE, utt_off, B, G, band, codes, order, ws_off, gamma, neg_log_z, xi_sum, xi_part,
+                                   nnz_total, stream);
     if (Rmax <= 16)
-        return launch_fb_banded<16>(E, ldE, utt_off, B, G, band, codes, order, ws_off, gamma, neg_log_z, xi_sum, stream);
-    return launch_fb_banded<32>(E, ldE, utt_off, B, G, band, codes, order, ws_off, gamma, neg_log_z, xi_sum, stream);
+        return launch_fb_banded<16>(E, ldE, utt_off, B, G, band, codes, order, ws_off, gamma, neg_log_z, xi_sum, xi_part,
+                                   nnz_total, stream);
+    return launch_fb_banded<32>(E, ldE, utt_off, B, G, band, codes, order, ws_off, gamma, neg_log_z, xi_sum, xi_part,
+                                nnz_total, stream);
 }
 
 int srb_path_words(const int32_t *path_state, const int64_t *path_off, const int32_t *path_len, int32_t B,

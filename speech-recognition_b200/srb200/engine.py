@@ -95,6 +95,8 @@ def as_offsets(off):
     return off.to(device(), torch.int32).contiguous()
 
 
+_scratch = {}                   # caller-owned workspaces of the kernels, grown on demand and reused (per device)
+
 TC_SCORE_MIN_FRAMES = 4096      # below this the FFMA scorer's launch is cheaper than staging the packed model per CTA
 _chunk_off_cache = {}
 
@@ -469,6 +471,17 @@ def dtw_beam(dist, off, trans, beam=None):
     return costs, ws, paths
 
 
+def _xi_part(nnz_total, dev):
+    """Caller-owned workspace of the forward-backward kernels: srb_fb_xi_parts() rows of nnz_total doubles."""
+    need = _l.load().srb_fb_xi_parts() * nnz_total
+    key = (dev.index, "xi_part")
+    buf = _scratch.get(key)
+    if buf is None or buf.numel() < need:
+        buf = torch.empty(need, dtype=torch.float64, device=dev)
+        _scratch[key] = buf
+    return buf
+
+
 def forward_backward(E, off, gb, utt_graph=None, want_xi=False, banded=None):
     """K4.  -> (gamma flat float32 [sum T*R], ws_off, neg_log_z[B] float64, xi_sum[nnz] float64 or None).
     Left-to-right models of at most 32 states (gb.banded) run srb_forward_backward_banded, one lane per state with the
@@ -483,7 +496,9 @@ def forward_backward(E, off, gb, utt_graph=None, want_xi=False, banded=None):
     ug = None if utt_graph is None else torch.as_tensor(np.asarray(utt_graph, np.int32)).to(dev)
     gamma = torch.empty(max(int(ws[-1]), 1), dtype=torch.float32, device=dev)
     nlz = torch.empty(B, dtype=torch.float64, device=dev)
-    xi = torch.zeros(max(int(gb.edge_off[-1]), 1), dtype=torch.float64, device=dev) if want_xi else None
+    nnz_total = max(int(gb.edge_off[-1]), 1)
+    xi = torch.zeros(nnz_total, dtype=torch.float64, device=dev) if want_xi else None
+    xi_part = _xi_part(nnz_total, dev) if want_xi else None          # per-warp rows: edge posteriors without atomics
     fits = gb.banded and gb.Rmax <= 32
     if banded and not fits:
         raise ValueError("forward_backward: banded=True needs left-to-right graphs of at most 32 states")
@@ -492,19 +507,19 @@ def forward_backward(E, off, gb, utt_graph=None, want_xi=False, banded=None):
         _l.check(_l.load().srb_forward_backward_banded(
             _l.ptr(E), E.stride(0), _l.ptr(offd), B, _l.ptr(ug), _l.ptr(gb["g_state_off"]), _l.ptr(gb["g_end_off"]),
             _l.ptr(gb["emit"]), _l.ptr(gb["pred_ptr"]), _l.ptr(gb["end_state"]), _l.ptr(gb["band"]), _l.ptr(gb["codes"]),
-            _l.ptr(order), gb.Rmax, _l.ptr(ws_d), _l.ptr(gamma), _l.ptr(nlz), _l.ptr(xi), _l.stream_ptr()))
+            _l.ptr(order), gb.Rmax, _l.ptr(ws_d), _l.ptr(gamma), _l.ptr(nlz), _l.ptr(xi), _l.ptr(xi_part), nnz_total,
+            _l.stream_ptr()))
         return gamma, ws, nlz, xi
     _l.check(_l.load().srb_forward_backward(
         _l.ptr(E), E.stride(0), _l.ptr(offd), B, _l.ptr(ug), _l.ptr(gb["g_state_off"]), _l.ptr(gb["g_end_off"]),
         _l.ptr(gb["emit"]), _l.ptr(gb["pred_ptr"]), _l.ptr(gb["pred_idx"]), _l.ptr(gb["pred_cost"]),
         _l.ptr(gb["pred_tgt"]), _l.ptr(gb["succ_ptr"]), _l.ptr(gb["succ_idx"]), _l.ptr(gb["succ_cost"]),
         _l.ptr(gb["end_state"]), gb.Rmax, gb.NNZmax, _l.ptr(ws_d), _l.ptr(gamma), _l.ptr(nlz), _l.ptr(xi),
-        _l.stream_ptr()))
+        _l.ptr(xi_part), nnz_total, _l.stream_ptr()))
     return gamma, ws, nlz, xi
 
 
 # ------------------------------------------------------------------------------------------------ K5 / K6
-_scratch = {}
 
 
 def _partial(groups, D, dev):

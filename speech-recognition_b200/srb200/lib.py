@@ -43,10 +43,11 @@ SIGNATURES = {
     "srb_delta_standardize": (c_int, [c_void_p, c_void_p, c_i32, c_void_p, c_int, c_void_p]),
     "srb_path_words": (c_int, [c_void_p, c_void_p, c_void_p, c_i32, c_void_p, c_void_p, c_void_p, c_i32, c_void_p,
                                c_void_p, c_void_p]),
+    "srb_fb_xi_parts": (c_int, []),
     "srb_forward_backward": (c_int, [c_void_p, c_i64, c_void_p, c_i32] + [c_void_p] * 12 + [c_i32, c_i32] +
-                             [c_void_p] * 5),
+                             [c_void_p] * 5 + [c_i32, c_void_p]),
     "srb_forward_backward_banded": (c_int, [c_void_p, c_i64, c_void_p, c_i32] + [c_void_p] * 9 + [c_i32] +
-                                    [c_void_p] * 5),
+                                    [c_void_p] * 5 + [c_i32, c_void_p]),
     "srb_stats_row": (c_int, [c_int]),
     "srb_stats_parts": (c_int, []),
     "srb_group_stats": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),

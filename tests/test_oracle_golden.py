@@ -229,11 +229,50 @@ def test_forward_backward_identities(golden):
             np.testing.assert_allclose(mn - np.log(np.exp(-(col - mn)).sum()), nlz, rtol=1e-12)
         costs, _, _ = orc.decode_hmm_states(E, m[3])
         assert nlz <= costs[-1, -1] + 1e-9                                    # sum over paths >= best path
-        # "hot" limit: scale costs up -> soft-min tends to min -> alpha/beta_scale tends to the Viterbi costs
+        # the SAME recursion in the (min, +) semiring is decode_hmm_states: bit for bit (SURVEY 8c asks "exactly")
+        nlz_m, a_m, b_m, _ = orc.forward_backward(E, m[3], semiring="min")
+        assert np.array_equal(a_m, costs.T)
+        assert nlz_m == costs[-1, -1]
+        # and its backward half: alpha + beta along the best path is the best cost
+        path = orc.decode_hmm_states(E, m[3])[1]
+        for s_, c_ in path:
+            assert abs(a_m[c_, s_] + b_m[c_, s_] - nlz_m) <= 1e-9 * abs(nlz_m)
+        # "hot" limit of the sum semiring: scaled costs -> soft-min tends to min
         s = 200.0
         nlz_s, a_s, _, _ = orc.forward_backward(E * s, np.where(np.isinf(m[3]), np.inf, m[3] * s))
         f = np.isfinite(costs.T)
-        np.testing.assert_allclose(a_s[f] / s, costs.T[f], rtol=2e-3)
+        np.testing.assert_allclose(a_s[f] / s, costs.T[f], rtol=1e-6, atol=np.log(5 * len(x)) / s)
+
+
+def test_forward_backward_against_path_enumeration():
+    """Independent pin of the forward-backward restatement (a21 has no reference): every state sequence of small
+    models enumerated explicitly -- log Z, state posteriors and summed edge posteriors to 1e-10."""
+    rng = np.random.default_rng(77)
+    for T, R in ((2, 2), (3, 3), (5, 2), (6, 3), (7, 4), (8, 4), (9, 3)):
+        for trial in range(3):
+            E = rng.uniform(0.5, 6.0, size=(T, R))
+            tr = np.full((R, R), np.inf)
+            for i in range(R):
+                tr[i, i] = rng.uniform(0.05, 2.0)
+                if i:
+                    tr[i, i - 1] = rng.uniform(0.05, 2.5)
+                if i > 1 and trial != 1:
+                    tr[i, i - 2] = rng.uniform(0.5, 3.0)                      # skip arcs (kmeans.py:72-84)
+            if trial == 2:
+                tr = rng.uniform(0.1, 3.0, size=(R, R))                       # ergodic
+            nlz_b, gam_b, xi_b = orc.forward_backward_bruteforce(E, tr)
+            nlz, a, b, gam = orc.forward_backward(E, tr)
+            if not np.isfinite(nlz_b):
+                assert not np.isfinite(nlz)
+                continue
+            np.testing.assert_allclose(nlz, nlz_b, rtol=1e-12)
+            np.testing.assert_allclose(gam, gam_b, rtol=1e-10, atol=1e-300)
+            xi = np.zeros((R, R))
+            for r in range(R):
+                for o in range(R):
+                    if np.isfinite(tr[r, o]):
+                        xi[r, o] = np.exp(-(a[:-1, o] + tr[r, o] + E[1:, r] + b[1:, r] - nlz)).sum()
+            np.testing.assert_allclose(xi, xi_b, rtol=1e-10, atol=1e-300)
 
 
 def test_feature_oracle_matches_reference_front_end():
