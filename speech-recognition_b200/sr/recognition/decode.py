@@ -50,7 +50,12 @@ def dtw(x, y, dist_fun, transitions, variance=None, beam=np.inf):
         # rows), and templates too long for the graph kernel's 8-bit back-pointer codes: srb_dtw_beam
         if not isinf(beam) and int(beam) != beam:
             raise TypeError("slice indices must be integers or None or have an __index__ method")   # sort_idx[beam:]
-        costs, _, paths = engine.dtw_beam(dist, off, transitions, None if isinf(beam) else int(beam))
+        costs, _, paths, status = engine.dtw_beam(dist, off, transitions, None if isinf(beam) else int(beam))
+        if status[0] == -2:
+            raise ValueError("attempt to get argmin of an empty sequence")        # np.argmin([]) at decode.py:53
+        if status[0] == -3:
+            raise RuntimeError("dtw: the walk back left the first column off row 0 (the reference indexes column -1 "
+                               "from there and does not terminate)")
         costs = costs[:col_count * row_count].reshape(col_count, row_count).t().double().cpu().numpy()
         return costs, paths[0]
     graph = StateGraph(transitions, np.arange(row_count), end_states=[row_count - 1], keep_inf=True)

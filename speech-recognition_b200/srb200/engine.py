@@ -436,9 +436,9 @@ def dtw_beam(dist, off, trans, beam=None):
     """dtw with the reference's beam pruning (decode.py:7-77; srb_dtw_beam) for a ragged batch of utterances against
     ONE template.  dist: [N, S] float32 CUDA local distances; trans: [S, S] (cost o -> i at [i, o], inf entries stay
     candidates); beam: None / inf = no pruning.
-    -> (costs flat float32 [sum T*S] with costs[i, j] at ws[u] + j*S + i, ws int64[B+1], paths: list of [T-1, 2] int64)
-    Raises ValueError where the reference's np.argmin gets an empty list, RuntimeError where its walk back would leave
-    the first column (the reference does not terminate there)."""
+    -> (costs flat float32 [sum T*S] with costs[i, j] at ws[u] + j*S + i, ws int64[B+1], paths: list of [T-1, 2] int64
+        or None, status int32[B]: path length, -2 where the reference's np.argmin gets an empty list (ValueError), -3
+        where its walk back would leave the first column off row 0 (the reference does not terminate there))."""
     dev = dist.device
     S = int(dist.shape[1])
     offd = as_offsets(off)
@@ -461,14 +461,11 @@ def dtw_beam(dist, off, trans, beam=None):
                                     _l.ptr(torch.from_numpy(ws).to(dev)), _l.ptr(bp), _l.ptr(costs),
                                     _l.ptr(torch.from_numpy(po).to(dev)), _l.ptr(ps), _l.ptr(pf), _l.ptr(pl),
                                     _l.stream_ptr()))
-    ln = pl.cpu().numpy()
-    if (ln[:B] == -2).any():
-        raise ValueError("attempt to get argmin of an empty sequence")          # what np.argmin([]) raises, decode.py:53
-    if (ln[:B] == -3).any():
-        raise RuntimeError("dtw: the walk back left the first column off row 0 (the reference does not terminate here)")
+    ln = pl.cpu().numpy()[:B]
     psn, pfn = ps.cpu().numpy(), pf.cpu().numpy()
-    paths = [np.stack([psn[po[u]:po[u] + ln[u]], pfn[po[u]:po[u] + ln[u]]], axis=1).astype(np.int64) for u in range(B)]
-    return costs, ws, paths
+    paths = [np.stack([psn[po[u]:po[u] + ln[u]], pfn[po[u]:po[u] + ln[u]]], axis=1).astype(np.int64) if ln[u] >= 0
+             else None for u in range(B)]
+    return costs, ws, paths, ln
 
 
 def _xi_part(nnz_total, dev):

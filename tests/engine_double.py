@@ -222,12 +222,14 @@ def dtw_beam(dist, off, trans, beam=None):
         i, j, path = S - 1, T - 1, []
         while i != 0 or j != 0:
             if j == 0:
-                raise RuntimeError("dtw: the walk back left the first column off row 0")
+                path = None
+                break
             i, j = int(bp[j, i]), j - 1
             path.append([i, j])
         flat.append(costs.ravel())
-        paths.append(np.array(path, np.int64).reshape(-1, 2))
-    return torch.from_numpy(np.concatenate(flat).astype(np.float32)), ws, paths
+        paths.append(None if path is None else np.array(path, np.int64).reshape(-1, 2))
+    status = np.array([-3 if p is None else len(p) for p in paths], np.int32)
+    return torch.from_numpy(np.concatenate(flat).astype(np.float32)), ws, paths, status
 
 
 def classify(X, off, pm, trans, W, S, final=None, label=None):

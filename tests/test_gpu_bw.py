@@ -1,6 +1,11 @@
 """GPU: one Baum-Welch iteration (srb200.trainer.BaumWelchTrainer: K1 + K4 + srb_gmm_stats_soft + M-step) against a
-float64 numpy restatement built on the oracle's forward-backward.  The reference has no Baum-Welch:
-parity is UNPINNED here; the oracle side is tied to the reference by the hard-count limit test below."""
+float64 numpy restatement built on the oracle's forward-backward.  The reference has no Baum-Welch, so
+parity cannot be pinned to reference outputs; it is pinned as far as it can be: the oracle's forward-backward is
+checked against explicit path enumeration and is bit-identical to decode_hmm_states in the (min,+) semiring
+(tests/test_oracle_golden.py), the kernels are checked against both (tests/test_gpu_dp.py), and the soft statistics
+reduce to the hard-count kernel (pinned to GMM.em) in the 0/1 limit (below).  Tolerance: BASELINE north_star's 1e-4
+relative on re-estimated weights / means / variances / transition probabilities (means: 1e-4 of max(|mu|, sigma), the
+scale a mean is known to)."""
 import numpy as np
 import pytest
 
@@ -62,15 +67,17 @@ def numpy_iteration(X, off, words, models, S, ncomp):
     return mu, var, w, np.stack(trans), nlz_sum / len(words)
 
 
+@pytest.mark.parametrize("base_scale", [1.0, 0.12])
 @pytest.mark.parametrize("S,M,ncomp,tensor", [(4, 4, 2, False), (8, 8, 4, False), (5, 4, 3, False), (3, 8, 8, False),
                                                (6, 2, 1, False), (8, 16, 4, True), (5, 4, 2, True), (4, 8, 4, True)])
-def test_baum_welch_iteration(S, M, ncomp, tensor):
+def test_baum_welch_iteration(S, M, ncomp, tensor, base_scale):
     """ncomp = 1, 2, 3 (padded lane group), 4, 8 cover every lane-group width of the soft-count kernel; S = 3 .. 8 the
     4- and 8-lane groups of the banded forward-backward kernel."""
     from srb200 import engine, synth
     from srb200.trainer import BaumWelchTrainer, sort_by_word
     W = 2
-    models, base = synth.make_models(81, W=W, S=S, M=M)
+    # base_scale 0.12: neighbouring states overlap, the posteriors are genuinely soft (synth.make_models)
+    models, base = synth.make_models(81, W=W, S=S, M=M, base_scale=base_scale, spread=0.5 * base_scale)
     X, off, words = synth.make_utterances(82, base, 24, ragged=(12, 40), noise=1.1)
     X, off, words, _ = sort_by_word(X, off, words)
     pm, _ = engine.PackedModel.from_words(models)
@@ -78,13 +85,14 @@ def test_baum_welch_iteration(S, M, ncomp, tensor):
     assert bool(tr.tensor) == tensor           # tensor: states scored as Mp/4 sub-states on the tcgen05 scorer
     tr.em_iteration()
     mu, var, w, trans, nlz = numpy_iteration(X.astype(np.float64), off.astype(np.int64), words, models, S, ncomp)
-    np.testing.assert_allclose(tr.mean_neg_log_z(), nlz, rtol=1e-5)
-    np.testing.assert_allclose(pm.w.cpu().numpy(), w, rtol=2e-4)
-    np.testing.assert_allclose(pm.mu.cpu().numpy(), mu, rtol=2e-4, atol=5e-5)
-    np.testing.assert_allclose(pm.var.cpu().numpy(), var, rtol=5e-4)
+    np.testing.assert_allclose(tr.mean_neg_log_z(), nlz, rtol=1e-6)
+    np.testing.assert_allclose(pm.w.cpu().numpy(), w, rtol=1e-4)
+    scale = np.maximum(np.abs(mu), np.sqrt(var))
+    assert np.max(np.abs(pm.mu.cpu().numpy() - mu) / scale) < 1e-4
+    np.testing.assert_allclose(pm.var.cpu().numpy(), var, rtol=1e-4)
     fin = np.isfinite(trans)
     assert np.array_equal(np.isfinite(tr.trans), fin)
-    np.testing.assert_allclose(tr.trans[fin], trans[fin], rtol=1e-3, atol=1e-4)
+    np.testing.assert_allclose(np.exp(-tr.trans[fin]), np.exp(-trans[fin]), rtol=1e-4)      # transition probabilities
     # EM monotonicity: the data log-likelihood does not decrease
     c1 = tr.mean_neg_log_z()
     tr.em_iteration()

@@ -17,9 +17,10 @@ from srb200 import engine, synth  # noqa: E402
 from srb200.graph import GraphBatch, StateGraph  # noqa: E402
 
 out = {}
-for S, M, banded in ((5, 4, True), (5, 4, False), (8, 16, True), (8, 16, False), (20, 2, True), (20, 2, False)):
-    models, base = synth.make_models(41, W=3, S=S, M=M)
-    X, off, words = synth.make_utterances(42, base, 40, ragged=(S + 3, 300))
+for S, M, banded, bs in ((5, 4, True, 1.0), (5, 4, True, 0.12), (5, 4, False, 0.12), (8, 16, True, 0.12), (8, 16, False, 0.12),
+                         (20, 2, True, 0.12), (20, 2, False, 0.12), (8, 16, True, 0.05)):
+    models, base = synth.make_models(41, W=3, S=S, M=M, base_scale=bs, spread=0.5 * bs)
+    X, off, words = synth.make_utterances(42, base, 40, ragged=(S + 3, 300), noise=1.0 if bs < 1 else 0.7)
     pm, _ = engine.PackedModel.from_words(models)
     E = engine.gmm_score(X.astype(np.float32), pm)["E"]
     Eh = E.double().cpu().numpy()
@@ -46,7 +47,9 @@ for S, M, banded in ((5, 4, True), (5, 4, False), (8, 16, True), (8, 16, False),
                     o, r = sg.pred_idx[j], sg.pred_tgt[j]
                     xi_ref[e0 + j] += np.exp(-(a[:-1, o] + m[3][r, o] + Em[1:, r] + b[1:, r] - z)).sum()
     big = xi_ref > 1e-2
-    out[f"S{S}_M{M}_{'banded' if banded else 'generic'}"] = {
+    key = f"S{S}_M{M}_{'banded' if banded else 'generic'}_scale{bs}"
+    out[key] = {
+        "gamma_entries_between_0.05_and_0.95": float(np.mean((gamma > 0.05) & (gamma < 0.95))),
         "gamma_rel_err_vs_f64_emissions(gamma>1e-3)": float(np.max(g_err)),
         "gamma_rel_err_same_emissions(gamma>1e-3)": float(np.max(g_err_same)),
         "nlz_rel_err_vs_f64_emissions": float(np.max(z_err)), "nlz_rel_err_same_emissions": float(np.max(z_err_same)),
@@ -54,15 +57,16 @@ for S, M, banded in ((5, 4, True), (5, 4, False), (8, 16, True), (8, 16, False),
     }
     # run-to-run reproducibility of the edge posteriors (no atomics)
     xi2 = engine.forward_backward(E, off, gb, utt_graph=words.astype(np.int32), want_xi=True, banded=banded)[3]
-    out[f"S{S}_M{M}_{'banded' if banded else 'generic'}"]["xi_bit_reproducible"] = bool(np.array_equal(xi2.cpu().numpy(), xi))
+    out[key]["xi_bit_reproducible"] = bool(np.array_equal(xi2.cpu().numpy(), xi))
 
 # ---- one Baum-Welch iteration: parameter errors
 import test_gpu_bw as tb  # noqa: E402
 from srb200.trainer import BaumWelchTrainer, sort_by_word  # noqa: E402
 
-for S, M, ncomp, tensor in ((8, 16, 4, True), (8, 16, 4, False), (5, 4, 2, False), (4, 8, 4, True)):
+for S, M, ncomp, tensor, bs in ((8, 16, 4, True, 1.0), (8, 16, 4, True, 0.12), (8, 16, 4, False, 0.12), (5, 4, 2, False, 0.12),
+                                (4, 8, 4, True, 0.12)):
     W = 2
-    models, base = synth.make_models(81, W=W, S=S, M=M)
+    models, base = synth.make_models(81, W=W, S=S, M=M, base_scale=bs, spread=0.5 * bs)
     X, off, words = synth.make_utterances(82, base, 48, ragged=(12, 80), noise=1.1)
     X, off, words, _ = sort_by_word(X, off, words)
     pm, _ = engine.PackedModel.from_words(models)
@@ -73,7 +77,7 @@ for S, M, ncomp, tensor in ((8, 16, 4, True), (8, 16, 4, False), (5, 4, 2, False
     sd = np.sqrt(var)
     sl = np.s_[:, :ncomp]
     fin = np.isfinite(trans)
-    out[f"bw_S{S}_M{M}_n{ncomp}_{'tc' if tensor else 'ffma'}"] = {
+    out[f"bw_S{S}_M{M}_n{ncomp}_{'tc' if tensor else 'ffma'}_scale{bs}"] = {
         "w_rel": float(np.max(np.abs(gw[sl] - w[sl]) / w[sl])),
         "mu_err_over_sd": float(np.max(np.abs(gm[sl] - mu[sl]) / sd[sl])),
         "mu_err_over_max(|mu|,sd)": float(np.max(np.abs(gm[sl] - mu[sl]) / np.maximum(np.abs(mu[sl]), sd[sl]))),
