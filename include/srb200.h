@@ -77,6 +77,21 @@ int srb_neg_lse_groups(const float *P, int64_t N, int R, int J, float *E, int64_
 int srb_merge_best(const float *P, int64_t N, int Rb, int J, int state0, int first, float *best_cost,
                    int32_t *best_state, void *stream);
 
+/* ---- the same reduction as ONE persistent GEMM (score_gemm.cu): a 128-frame tile's split [x'^2, x', 1] operand stays in
+ * tensor memory while ALL of the model's Gaussians stream past it in blocks of 160 columns (TMA bulk copies through a
+ * 2-stage shared-memory ring, two accumulators in tensor memory, 3xTF32), the per-state log-sum-exp and the running
+ * best state are kept in registers; X is read once, only best_cost / best_state are written.
+ *   srb_gmm_best_gemm_supported(D, R, Mp)  1 for D = 39 and Mp a multiple of 16 up to 160 (any number of states R)
+ *   srb_model_blocks_floats(R, Mp, D)      floats of the blocked split model
+ *   srb_pack_model_blocks(ab, c, ...)      ab, c (srb_pack_model) -> blocks[ceil(R / SB)][2][K/4][160][4], SB = 160 / Mp
+ *                                          states per block; once per model update
+ *   srb_gmm_best_gemm(...)                 best_cost / best_state as srb_gmm_score (first minimum) */
+int srb_gmm_best_gemm_supported(int D, int R, int Mp);
+int64_t srb_model_blocks_floats(int R, int Mp, int D);
+int srb_pack_model_blocks(const float *ab, const float *c, int R, int Mp, int D, float *blocks, void *stream);
+int srb_gmm_best_gemm(const float *X, int64_t N, int D, const float *blocks, const float *shift, int R, int Mp,
+                      float *best_cost, int32_t *best_state, void *stream);
+
 /* ---- fused isolated-word classifier (core.py:79-87 over hmm.py:126-135 over decode.py:80-146) ----
  * W word models of S states each (packed model has R = W*S states, word-major); trans float[W,S,S] with
  * trans[w,i,j] = cost j -> i, +inf = none (decode.py:86-87).  Start in state 0 at frame 0

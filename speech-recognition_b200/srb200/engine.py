@@ -186,6 +186,26 @@ def gmm_best_tc(X, pm, best_cost=None, best_state=None):
     return bc, bs
 
 
+def gmm_best_gemm(X, pm, best_cost=None, best_state=None):
+    """Per-frame best state and its cost for a model of ANY number of states as one persistent tensor-core GEMM
+    (srb_gmm_best_gemm: the frame tile's operand stays in tensor memory, the model streams past it, nothing but the
+    result leaves the SM).  Mp a multiple of 16.  -> (best_cost[N] float32, best_state[N] int32)"""
+    X = as_frames(X)
+    N, dev, L = X.shape[0], X.device, _l.load()
+    if not L.srb_gmm_best_gemm_supported(pm.D, pm.R, pm.Mp):
+        raise ValueError("gmm_best_gemm: D = 39 and a multiple of 16 Gaussians per state (at most 160) needed")
+    cache = getattr(pm, "_gemm_blocks", None)
+    if cache is None or cache[0] != pm.version:
+        blocks = torch.empty(int(L.srb_model_blocks_floats(pm.R, pm.Mp, pm.D)), dtype=torch.float32, device=dev)
+        _l.check(L.srb_pack_model_blocks(_l.ptr(pm.ab), _l.ptr(pm.c), pm.R, pm.Mp, pm.D, _l.ptr(blocks), _l.stream_ptr()))
+        cache = pm._gemm_blocks = (pm.version, blocks)
+    bc = torch.empty(N, dtype=torch.float32, device=dev) if best_cost is None else best_cost
+    bs = torch.empty(N, dtype=torch.int32, device=dev) if best_state is None else best_state
+    _l.check(L.srb_gmm_best_gemm(_l.ptr(X), N, pm.D, _l.ptr(cache[1]), _l.ptr(pm.shift), pm.R, pm.Mp, _l.ptr(bc),
+                                 _l.ptr(bs), _l.stream_ptr()))
+    return bc, bs
+
+
 TC_BEST_MIN_FRAMES = 1 << 16    # best-state-only requests of at least this many frames go to gmm_best_tc
 
 
@@ -205,7 +225,10 @@ def gmm_score(X, pm, want_E=True, want_best=False, want_comp=False, tensor=None)
     best_only = want_best and not want_E and not want_comp
     if best_only and tensor is not False and pm.D == 39 and pm.Mp % 4 == 0 and 4 <= pm.Mp <= 228 and (
             tensor or N >= TC_BEST_MIN_FRAMES):
-        bc, bs = gmm_best_tc(X, pm)                      # streaming best state, block by block on the tensor cores
+        if _l.load().srb_gmm_best_gemm_supported(pm.D, pm.R, pm.Mp):
+            bc, bs = gmm_best_gemm(X, pm)                # one persistent GEMM, the model streams past the frame tile
+        else:
+            bc, bs = gmm_best_tc(X, pm)                  # block by block through the classifier kernel's scorer mode
         return {"best_cost": bc, "best_state": bs}
     if tensor:
         if not e_only:
@@ -457,9 +480,9 @@ def dtw_beam(dist, off, trans, beam=None):
     pf = torch.empty(max(int(po[-1]), 1), dtype=torch.int32, device=dev)
     pl = torch.zeros(max(B, 1), dtype=torch.int32, device=dev)
     b = -1 if beam is None or beam == float("inf") else int(beam)
-    _l.check(_l.load().srb_dtw_beam(_l.ptr(dist), dist.stride(0), _l.ptr(offd), B, _l.ptr(tr), S, b,
-                                    _l.ptr(torch.from_numpy(ws).to(dev)), _l.ptr(bp), _l.ptr(costs),
-                                    _l.ptr(torch.from_numpy(po).to(dev)), _l.ptr(ps), _l.ptr(pf), _l.ptr(pl),
+    ws_d, po_d = torch.from_numpy(ws).to(dev), torch.from_numpy(po).to(dev)    # named: they must outlive the launch
+    _l.check(_l.load().srb_dtw_beam(_l.ptr(dist), dist.stride(0), _l.ptr(offd), B, _l.ptr(tr), S, b, _l.ptr(ws_d),
+                                    _l.ptr(bp), _l.ptr(costs), _l.ptr(po_d), _l.ptr(ps), _l.ptr(pf), _l.ptr(pl),
                                     _l.stream_ptr()))
     ln = pl.cpu().numpy()[:B]
     psn, pfn = ps.cpu().numpy(), pf.cpu().numpy()
@@ -649,11 +672,13 @@ def text_viterbi(codes, tree, dist=None):
     out_len = torch.empty(B, dtype=torch.int32, device=dev)
     d = None if dist is None else dist.to(dev, torch.float32).contiguous()
     assert d is None or tuple(d.shape) == (int(x_off[-1]), tree.n_rows)
+    x_off_d, bp_off_d = torch.from_numpy(x_off).to(dev), torch.from_numpy(x_off * tree.n_rows).to(dev)
+    out_off_d = torch.from_numpy(out_off).to(dev)                   # named: they must outlive the launch
     _l.check(_l.load().srb_text_viterbi(
-        _l.ptr(x), _l.ptr(torch.from_numpy(x_off).to(dev)), B, _l.ptr(tree.val), _l.ptr(tree.parent),
-        _l.ptr(tree.level_nodes), _l.ptr(tree.level_off), tree.n_levels, tree.n_rows, _l.ptr(tree.word_ends), tree.n_ends,
-        _l.ptr(d), _l.ptr(col_ws), _l.ptr(bp), _l.ptr(torch.from_numpy(x_off * tree.n_rows).to(dev)), _l.ptr(jump),
-        _l.ptr(best), _l.ptr(out), _l.ptr(torch.from_numpy(out_off).to(dev)), _l.ptr(out_len), _l.stream_ptr()))
+        _l.ptr(x), _l.ptr(x_off_d), B, _l.ptr(tree.val), _l.ptr(tree.parent), _l.ptr(tree.level_nodes),
+        _l.ptr(tree.level_off), tree.n_levels, tree.n_rows, _l.ptr(tree.word_ends), tree.n_ends, _l.ptr(d), _l.ptr(col_ws),
+        _l.ptr(bp), _l.ptr(bp_off_d), _l.ptr(jump), _l.ptr(best), _l.ptr(out), _l.ptr(out_off_d), _l.ptr(out_len),
+        _l.stream_ptr()))
     ln, on = out_len.cpu().numpy(), out.cpu().numpy()
     if (ln == -3).any() or (ln == -2).any():
         raise RuntimeError("text_viterbi: the walk back does not reach column 1 (the reference loops forever here)")

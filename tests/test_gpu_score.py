@@ -133,6 +133,70 @@ def test_gmm_best_tensor_core_blocks(eng, R, M, N):
     assert np.array_equal(out["best_cost"].cpu().numpy(), bc) and np.array_equal(out["best_state"].cpu().numpy(), bs)
 
 
+@pytest.mark.parametrize("R,M,N", [(20, 32, 1500), (130, 16, 2100), (1, 16, 130), (7, 48, 300), (2, 64, 129), (3, 160, 64),
+                                   (2000, 32, 777), (401, 16, 20000)])
+def test_gmm_best_gemm(eng, R, M, N):
+    """engine.gmm_best_gemm (srb_gmm_best_gemm: one persistent tcgen05 GEMM, the frame tile's operand resident in tensor
+    memory, the model streamed past it in 160-column blocks by TMA bulk copies, running best state in registers) against
+    the float64 oracle's GMM.evaluate (hmm_state.py:114-120, log domain) and against the FFMA scorer: costs to 1e-4
+    (FP32 rule), states equal wherever the two best costs differ by more than that.  Shapes: one block / many blocks,
+    partial last block, a state per block (M = 160), partial last frame tile, more tiles than SMs (several tiles per
+    CTA), and BASELINE config 5's 2 000 x 32."""
+    import torch
+    rng = np.random.default_rng(R + M)
+    mu = rng.normal(size=(R, 1, 39)) + 0.5 * rng.normal(size=(R, M, 39))
+    var = rng.uniform(0.5, 1.5, size=(R, M, 39))
+    w = rng.dirichlet(np.ones(M), size=R)
+    pm = eng.PackedModel(mu, var, w)
+    X = torch.randn((N, 39), dtype=torch.float32, device="cuda", generator=torch.Generator("cuda").manual_seed(5))
+    bc, bs = eng.gmm_best_gemm(X, pm)
+    bc, bs = bc.cpu().numpy(), bs.cpu().numpy()
+    n_or = min(N, 200)                                     # oracle sample (the scalar C restatement: R*M*39 per frame)
+    idx = np.sort(rng.choice(N, size=n_or, replace=False))
+    Xo = X.cpu().numpy()[idx].astype(np.float64)
+    Eo = np.stack([orc.gmm_evaluate(Xo, mu[r], var[r], w[r], log_domain=True)[0] for r in range(R)], axis=1)
+    np.testing.assert_allclose(bc[idx], Eo.min(axis=1), rtol=RTOL)
+    so = np.sort(Eo, axis=1)
+    decided = (so[:, 1] - so[:, 0]) > RTOL * np.abs(so[:, 0]) if R > 1 else np.ones(n_or, bool)
+    assert decided.mean() > 0.9
+    assert np.array_equal(bs[idx][decided], Eo.argmin(axis=1)[decided])
+    np.testing.assert_allclose(Eo[np.arange(n_or), bs[idx]], bc[idx], rtol=RTOL)   # the state named carries the cost named
+    if R * M <= 8192:
+        ref = eng.gmm_score(X, pm, want_E=True, want_best=True, tensor=False)       # FFMA scorer, every frame
+        E = ref["E"].cpu().numpy()
+        np.testing.assert_allclose(bc, ref["best_cost"].cpu().numpy(), rtol=2e-5)
+        s2 = np.sort(E, axis=1)
+        dec = (s2[:, 1] - s2[:, 0]) > 1e-4 * np.abs(s2[:, 0]) if R > 1 else np.ones(N, bool)
+        assert np.array_equal(bs[dec], ref["best_state"].cpu().numpy()[dec])
+    bc2, bs2 = eng.gmm_best_gemm(X, pm)                    # cached blocks; bit-reproducible
+    assert np.array_equal(bc2.cpu().numpy(), bc) and np.array_equal(bs2.cpu().numpy(), bs)
+    out = eng.gmm_score(X, pm, want_E=False, want_best=True, tensor=True)           # the public route to the same path
+    assert np.array_equal(out["best_cost"].cpu().numpy(), bc) and np.array_equal(out["best_state"].cpu().numpy(), bs)
+
+
+def test_gmm_best_gemm_zero_weight_and_unsupported(eng):
+    """Components of weight 0 (C = -inf) contribute nothing; a state whose components all have weight 0 never wins;
+    shapes the kernel is not built for are refused loudly."""
+    import torch
+    rng = np.random.default_rng(3)
+    R, M = 6, 16
+    mu = rng.normal(size=(R, M, 39))
+    var = rng.uniform(0.5, 1.5, size=(R, M, 39))
+    w = rng.dirichlet(np.ones(M), size=R)
+    w[:, 5:] = 0.0
+    w[2, :] = 0.0
+    pm = eng.PackedModel(mu, var, w)
+    X = torch.randn((300, 39), dtype=torch.float32, device="cuda", generator=torch.Generator("cuda").manual_seed(6))
+    bc, bs = eng.gmm_best_gemm(X, pm)
+    ref = eng.gmm_score(X, pm, want_E=True, want_best=True, tensor=False)
+    np.testing.assert_allclose(bc.cpu().numpy(), ref["best_cost"].cpu().numpy(), rtol=2e-5)
+    assert (bs.cpu().numpy() != 2).all()
+    assert np.isinf(ref["E"].cpu().numpy()[:, 2]).all()
+    small = eng.PackedModel(mu[:, :4], var[:, :4], np.full((R, 4), 0.25))
+    with pytest.raises(ValueError):
+        eng.gmm_best_gemm(X, small)
+
+
 def test_gmm_score_tensor_core_unsupported_is_loud(eng):
     import torch
     from srb200 import lib as L
