@@ -443,14 +443,10 @@ def bench_stress(args, ctx):
 
     use_tc = not args.ffma
     launches = 1
-    if use_tc:
-        J = pm.Mp // 4
-        nblocks = -(-R // (57 // J))
-        launches = 2 * nblocks * -(-N // engine.TC_BEST_ROWS)
 
     def step():
         if use_tc:
-            engine.gmm_best_tc(Xd, pm, bc, bs)
+            engine.gmm_best_gemm(Xd, pm, bc, bs)
         else:
             L_.check(L_.load().srb_gmm_score(L_.ptr(Xd), N, D_, L_.ptr(pm.ab), L_.ptr(pm.c), L_.ptr(pm.shift), R, pm.Mp,
                                              None, R, L_.ptr(bc), L_.ptr(bs), None, L_.stream_ptr()))
@@ -461,7 +457,7 @@ def bench_stress(args, ctx):
     clocks = sampler.stop()
     ms = float(np.mean(per))
     roof = _roof_fma(R * M * 2 * D_, N, ms, ctx["peak_fma"],
-                     "classify_tc_kernel<39> (scorer mode, 7 states = 56 sub-states per launch) + merge_best_kernel"
+                     "gmm_best_gemm_kernel<39> (persistent tcgen05 3xTF32 GEMM, model streamed by TMA bulk copies)"
                      if use_tc else "score_kernel<39>", "4.992 M FMA/frame = 64000 Gaussians x 2*39")
     if use_tc:
         roof["note"] = ("tcgen05 3xTF32: algorithmic FP32-equivalent rate over the measured FFMA peak, > 1 = above the "

@@ -82,6 +82,7 @@ def gmm_evaluate(X, mu, cov, w, log_domain=False):
     w, wp = _d(w)
     N, D = X.shape
     M = mu.shape[0]
+    assert M <= 1024, "orc_gmm_evaluate keeps the component log-densities of a frame in a 1024-entry array"
     cost = np.empty(N)
     comps = np.empty((N, M))
     lib().orc_gmm_evaluate(Xp, ctypes.c_int64(N), D, mup, covp, wp, M, int(log_domain), cost.ctypes.data_as(c_dp),

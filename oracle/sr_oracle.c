@@ -65,7 +65,7 @@ void orc_gmm_evaluate(const double *X, int64_t N, int D, const double *mu, const
             }
             if (cost_out) cost_out[i] = -log(s);                                               /* :118 */
         } else {
-            double l[64], mx = -ORC_INF;
+            double l[1024], mx = -ORC_INF;                       /* oracle.py checks M <= 1024 */
             for (int m = 0; m < M; ++m) {
                 l[m] = log(w[m]) + pdf_log(x, mu + (size_t)m * D, cov + (size_t)m * D, D);
                 if (l[m] > mx) mx = l[m];

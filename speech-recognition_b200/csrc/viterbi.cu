@@ -823,6 +823,14 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
+// smallest emission cost of a column over the graph's states (0 when every state is impossible)
+__device__ __forceinline__ float column_emin(const float *Erow, const int32_t *emit, int R, int lane) {
+    float m = CUDART_INF_F;
+    for (int r = lane; r < R; r += 32) m = fminf(m, Erow[emit[r]]);
+    m = warp_min(m);
+    return m < CUDART_INF_F ? m : 0.f;
+}
+
 __global__ void __launch_bounds__(VW * 32)
 forward_backward_kernel(const float *__restrict__ E, int64_t ldE, const int32_t *__restrict__ off, int B,
                         GraphBatch G, const int32_t *__restrict__ succ_ptr, const int32_t *__restrict__ succ_idx,
@@ -860,22 +868,26 @@ forward_backward_kernel(const float *__restrict__ E, int64_t ldE, const int32_t 
         double scale = 0.0;
         for (int c = 0; c < T; ++c) {
             const float *Erow = E + (f0 + c) * ldE;
+            // the column's smallest emission cost is taken out BEFORE the costs are added: emission costs are tens of
+            // nats, adding one to a renormalised alpha (a few nats) and subtracting the minimum afterwards would round
+            // at the emission's magnitude in every column (measured: 7e-5 relative on gamma after 300 frames)
+            const float emin = column_emin(Erow, emit, R, lane);
             float mymin = INF;
             for (int r = lane; r < R; r += 32) {
                 float a;
                 if (c == 0) {
-                    a = (r == 0) ? Erow[emit[0]] : INF;
+                    a = (r == 0) ? Erow[emit[0]] - emin : INF;
                 } else {
                     OnlineNegLse acc; acc.reset();
                     for (int j = pptr[r]; j < pptr[r + 1]; ++j) acc.add(G.pred_cost[j] + prev[G.pred_idx[j]]);
-                    a = acc.value() + Erow[emit[r]];
+                    a = acc.value() + (Erow[emit[r]] - emin);
                 }
                 cur[r] = a;
                 mymin = fminf(mymin, a);
             }
             const float m = warp_min(mymin);
             const float sub = (m < INF) ? m : 0.f;
-            scale += (double)sub;
+            scale += (double)sub + (double)emin;
             __syncwarp();
             for (int r = lane; r < R; r += 32) {
                 const float a = cur[r] - sub;
@@ -922,11 +934,12 @@ forward_backward_kernel(const float *__restrict__ E, int64_t ldE, const int32_t 
             if (c > 0) {
                 // xi of the transitions into column c (needs alpha_hat_{c-1}, still in global)
                 const float *Erow = E + (f0 + c) * ldE;
+                const float emin = column_emin(Erow, emit, R, lane);
                 float xs = 0.f, vmin = INF;
                 for (int j = lane; j < nnz; j += 32) {
                     const int r = pred_tgt[e0 + j];
                     const int o = G.pred_idx[e0 + j];
-                    const float v = gu[(size_t)(c - 1) * R + o] + G.pred_cost[e0 + j] + Erow[emit[r]] + bnext[r];
+                    const float v = gu[(size_t)(c - 1) * R + o] + G.pred_cost[e0 + j] + (Erow[emit[r]] - emin) + bnext[r];
                     xi[j] = v;
                     vmin = fminf(vmin, v);
                 }
@@ -947,12 +960,13 @@ forward_backward_kernel(const float *__restrict__ E, int64_t ldE, const int32_t 
             if (c == 0) break;
             // beta_hat_{c-1}(o) = -lse over successors r of (tr + E_c(r) + beta_hat_c(r)), renormalised
             const float *Erow = E + (f0 + c) * ldE;
+            const float emin = column_emin(Erow, emit, R, lane);
             float mymin = INF;
             for (int o = lane; o < R; o += 32) {
                 OnlineNegLse acc; acc.reset();
                 for (int j = sptr[o]; j < sptr[o + 1]; ++j) {
                     const int r = succ_idx[j];
-                    acc.add(succ_cost[j] + Erow[emit[r]] + bnext[r]);
+                    acc.add(succ_cost[j] + (Erow[emit[r]] - emin) + bnext[r]);
                 }
                 const float b = acc.value();
                 bcur[o] = b;
@@ -1071,22 +1085,28 @@ forward_backward_banded_kernel(const float *__restrict__ E, int64_t ldE, const i
         float *gu = gamma + (valid ? ws_off[u] : 0) + sub;
 
         // ---- forward: alpha_hat columns to gamma
+        // Emission costs are tens of nats while the renormalised alpha / beta are a few: the column's smallest emission
+        // cost is taken out BEFORE the costs are added, so no sum ever rounds at the emission's magnitude (measured:
+        // gamma 7e-5 relative after 300 frames without this, 3e-6 with it; profiles/r02_fb_error.json).
         float alpha = INF;
         double scale = 0.0;
-        float e_c = (act && 0 < T) ? Eu[0] : 0.f;
+        float e_c = (act && 0 < T) ? Eu[0] : INF;
         for (int c = 0; c < Tmax; ++c) {
             const bool live = c < T;
-            float e_n = 0.f;
+            float e_n = INF;
             if (act && c + 1 < T) e_n = Eu[(int64_t)(c + 1) * ldE];
+            float emin = group_min<W>(e_c);
+            if (!(emin < INF)) emin = 0.f;
+            const float eh = e_c - emin;
             const float p1 = __shfl_up_sync(0xffffffffu, alpha, 1, W), p2 = __shfl_up_sync(0xffffffffu, alpha, 2, W);
             float a;
-            if (c == 0) a = (sub == 0) ? e_c : INF;
-            else a = neg_lse3(p2 + a2, p1 + a1, alpha + a0) + e_c;
+            if (c == 0) a = (sub == 0) ? eh : INF;
+            else a = neg_lse3(p2 + a2, p1 + a1, alpha + a0) + eh;
             if (!act) a = INF;
             const float m = group_min<W>(a);
             const float sh = (m < INF) ? m : 0.f;
             if (live) {
-                scale += (double)sh;
+                scale += (double)sh + (double)emin;
                 alpha = a - sh;
                 if (act) gu[(size_t)c * R] = alpha;
             }
@@ -1105,10 +1125,10 @@ forward_backward_banded_kernel(const float *__restrict__ E, int64_t ldE, const i
         int c = Tmax - 1;
         float al_c = (act && c < T) ? gu[(size_t)c * R] : INF;
         float al_p = (act && c >= 1 && c - 1 < T) ? gu[(size_t)(c - 1) * R] : INF;
-        e_c = (act && c < T) ? Eu[(int64_t)c * ldE] : 0.f;
+        e_c = (act && c < T) ? Eu[(int64_t)c * ldE] : INF;
         for (; c >= 0; --c) {
             const bool live = c < T;
-            float al_n = INF, e_n = 0.f;                             // alpha_hat_{c-2}, E_{c-1}
+            float al_n = INF, e_n = INF;                             // alpha_hat_{c-2}, E_{c-1}
             if (act && c >= 2 && c - 2 < T) al_n = gu[(size_t)(c - 2) * R];
             if (act && c >= 1 && c - 1 < T) e_n = Eu[(int64_t)(c - 1) * ldE];
             // gamma_c
@@ -1117,7 +1137,9 @@ forward_backward_banded_kernel(const float *__restrict__ E, int64_t ldE, const i
             const float gs = group_sum<W>(p);
             if (live && act) gu[(size_t)c * R] = p * (gs > 0.f ? 1.f / gs : 0.f);
             // xi of the arcs into column c, beta_hat_{c-1}
-            const float w = e_c + beta;                              // E_c(r) + beta_hat_c(r)
+            float emin = group_min<W>(e_c);
+            if (!(emin < INF)) emin = 0.f;
+            const float w = (e_c - emin) + beta;                     // E_hat_c(r) + beta_hat_c(r)
             const float q1 = __shfl_up_sync(0xffffffffu, al_p, 1, W), q2 = __shfl_up_sync(0xffffffffu, al_p, 2, W);
             const float y2 = a2 + w, y1 = a1 + w, y0 = a0 + w;
             const float v2 = q2 + y2, v1 = q1 + y1, v0 = al_p + y0;
