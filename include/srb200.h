@@ -304,6 +304,15 @@ int srb_local_dist(const float *X, int64_t N, int D, const double *Y, const doub
 int srb_mstep(const double *stats, int R, int M, int ncomp, int D, double *mu, double *var, double *w,
               double var_floor, void *stream);
 
+/* Baum-Welch transition re-estimation on the device (no reference counterpart): for every origin state o
+ * of the packed graphs, a[o -> r] = xi[o -> r] / sum_r' xi[o -> r'] and cost = -log a is written IN PLACE into the arc's
+ * cost in the predecessor CSR (pred_cost, indexed like xi), the successor CSR (succ_cost) and the band array of
+ * srb_forward_backward_banded (band_slot[e] = index into band of edge e, -1 = none).  succ_ptr int32[n_states+1] is the
+ * successor CSR over ALL packed states (absolute offsets), succ_edge[j] = predecessor-CSR index of successor entry j.
+ * Arcs with xi == 0 and origins without mass keep their cost.  Deterministic (one thread per origin, fixed order). */
+int srb_update_transitions(const double *xi, const int32_t *succ_ptr, const int32_t *succ_edge, const int32_t *band_slot,
+                           int32_t n_states, float *pred_cost, float *succ_cost, float *band, void *stream);
+
 /* lc[g] = log w_g - 0.5*(D log 2pi + sum_d log var[g,d])  (natural log) */
 int srb_gauss_consts(const double *var, const double *w, int G, int D, double *lc, void *stream);
 

@@ -405,6 +405,31 @@ __global__ void gauss_consts_kernel(const double *__restrict__ var, const double
     lc[g] = (w[g] > 0.0 ? log(w[g]) : -CUDART_INF) - 0.5 * ((double)D * 1.8378770664093454836 + ld);
 }
 
+// Baum-Welch transition update on the device: a[o -> r] = xi[o -> r] / sum_r' xi[o -> r'], cost = -log a, written in
+// place into every copy of the arc's cost the kernels read (predecessor CSR, successor CSR, band array).  One thread per
+// origin state walks its successor list in a fixed order: deterministic, no host round trip.  Arcs never taken (xi == 0)
+// and origins without mass keep their cost, like the host form this replaces.
+__global__ void update_transitions_kernel(const double *__restrict__ xi, const int32_t *__restrict__ succ_ptr,
+                                          const int32_t *__restrict__ succ_edge, const int32_t *__restrict__ band_slot,
+                                          int n_states, float *__restrict__ pred_cost, float *__restrict__ succ_cost,
+                                          float *__restrict__ band) {
+    const int o = blockIdx.x * blockDim.x + threadIdx.x;
+    if (o >= n_states) return;
+    const int j0 = succ_ptr[o], j1 = succ_ptr[o + 1];
+    double out = 0.0;
+    for (int j = j0; j < j1; ++j) out += xi[succ_edge[j]];
+    if (!(out > 0.0)) return;
+    for (int j = j0; j < j1; ++j) {
+        const int e = succ_edge[j];
+        const double x = xi[e];
+        if (!(x > 0.0)) continue;
+        const float c = (float)(-log(x / out));
+        pred_cost[e] = c;
+        if (succ_cost) succ_cost[j] = c;
+        if (band && band_slot && band_slot[e] >= 0) band[band_slot[e]] = c;
+    }
+}
+
 }  // namespace srb
 
 using namespace srb;
@@ -507,6 +532,17 @@ int srb_mstep(const double *stats, int R, int M, int ncomp, int D, double *mu, d
     SRB_REQUIRE(R > 0 && M > 0 && ncomp >= 1 && ncomp <= M && D > 0, SRB_EINVAL, "srb_mstep: bad sizes");
     const int n = R * ncomp * D;
     mstep_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(stats, R, M, ncomp, D, mu, var, w, var_floor);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+int srb_update_transitions(const double *xi, const int32_t *succ_ptr, const int32_t *succ_edge, const int32_t *band_slot,
+                           int32_t n_states, float *pred_cost, float *succ_cost, float *band, void *stream) {
+    SRB_REQUIRE(n_states >= 0, SRB_EINVAL, "srb_update_transitions: bad sizes");
+    if (n_states == 0) return SRB_OK;
+    SRB_REQUIRE(xi && succ_ptr && succ_edge && pred_cost, SRB_EINVAL, "srb_update_transitions: null pointer");
+    update_transitions_kernel<<<(n_states + 127) / 128, 128, 0, (cudaStream_t)stream>>>(xi, succ_ptr, succ_edge, band_slot,
+                                                                                          n_states, pred_cost, succ_cost, band);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }

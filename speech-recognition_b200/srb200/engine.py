@@ -306,8 +306,10 @@ class HostClassifier:
             yield u, ue
             u = ue
 
-    def run(self, X, off, labels_out=None, final_out=None):
-        """X: [N, D] float32 host tensor/array (pinned for full speed); off: [B+1] int32 -> labels [B] int32 (host)."""
+    def run(self, X, off, labels_out=None, final_out=None, sync=True):
+        """X: [N, D] float32 host tensor/array (pinned for full speed); off: [B+1] int32 -> labels [B] int32 (host).
+        The labels are valid on return (sync=True); with sync=False the caller must synchronise the current stream
+        before reading them."""
         Xt = X if torch.is_tensor(X) else torch.from_numpy(np.ascontiguousarray(X, dtype=np.float32))
         offn = off.numpy() if torch.is_tensor(off) else np.asarray(off)
         B = len(offn) - 1
@@ -347,7 +349,49 @@ class HostClassifier:
         for s in range(2):
             if self.done[s] is not None:
                 cur.wait_event(self.done[s])
+        if sync:
+            for s in range(2):                      # the D2H copies are asynchronous: the HOST must wait as well before
+                if self.done[s] is not None:        # it reads labels_out (sync=False: the caller synchronises the stream)
+                    self.done[s].synchronize()
         return labels_out
+
+
+class HostBestState:
+    """Host-facing likelihood sweep (BASELINE config 5): pinned host frames in, per-frame best state and cost out.
+    The frames are cut into chunks; chunk k+1 is copied host->device on one stream while srb_gmm_best_gemm runs on
+    chunk k on the other, results come back with one D2H copy per chunk."""
+
+    def __init__(self, pm, chunk_frames=1 << 20):
+        dev = device()
+        self.pm, self.chunk = pm, int(chunk_frames) // 4 * 4            # chunk starts stay 16-byte aligned
+        self.streams = [torch.cuda.Stream(dev) for _ in range(2)]
+        self.xbuf = [torch.empty((self.chunk, pm.D), dtype=torch.float32, device=dev) for _ in range(2)]
+        self.bc = [torch.empty(self.chunk, dtype=torch.float32, device=dev) for _ in range(2)]
+        self.bs = [torch.empty(self.chunk, dtype=torch.int32, device=dev) for _ in range(2)]
+        gmm_best_gemm(self.xbuf[0][:4], pm)                             # packs the model's blocks once
+
+    def run(self, Xh, cost_out, state_out):
+        """Xh [N, D] float32 pinned host tensor; cost_out [N] float32 / state_out [N] int32 pinned host tensors."""
+        N = Xh.shape[0]
+        cur = torch.cuda.current_stream()
+        start = torch.cuda.Event()
+        start.record(cur)
+        done = [None, None]
+        for k, f0 in enumerate(range(0, N, self.chunk)):
+            s, n = k & 1, min(self.chunk, N - f0)
+            st = self.streams[s]
+            with torch.cuda.stream(st):
+                st.wait_event(start)
+                self.xbuf[s][:n].copy_(Xh[f0:f0 + n], non_blocking=True)
+                gmm_best_gemm(self.xbuf[s][:n], self.pm, self.bc[s][:n], self.bs[s][:n])
+                cost_out[f0:f0 + n].copy_(self.bc[s][:n], non_blocking=True)
+                state_out[f0:f0 + n].copy_(self.bs[s][:n], non_blocking=True)
+                done[s] = torch.cuda.Event()
+                done[s].record(st)
+        for ev in done:
+            if ev is not None:
+                cur.wait_event(ev)
+        return cost_out, state_out
 
 
 # ------------------------------------------------------------------------------------------------ K2 / K4

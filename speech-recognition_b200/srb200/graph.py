@@ -40,6 +40,7 @@ class StateGraph:
         np.cumsum(np.bincount(org, minlength=R), out=self.succ_ptr[1:])
         self.succ_idx = tgt[order].astype(np.int32)
         self.succ_cost = self.pred_cost[order]
+        self.succ_edge = order.astype(np.int32)          # predecessor-CSR index of every successor entry
         self.has_nes_self_loop = bool(any(np.isfinite(tr[n, n]) for n in self.nes_idx))
 
     @property
@@ -122,6 +123,7 @@ class GraphBatch:
             "succ_ptr": succ_ptr,
             "succ_idx": cat([g.succ_idx for g in graphs], np.int32),
             "succ_cost": cat([g.succ_cost for g in graphs], np.float32),
+            "succ_edge": cat([g.succ_edge.astype(np.int64) + edge_off[i] for i, g in enumerate(graphs)], np.int32),
         }
         if any(g.end_frames is not None for g in graphs):
             host["end_frame"] = cat([g.end_frames if g.end_frames is not None else np.full(len(g.end_states), -1)
@@ -137,6 +139,14 @@ class GraphBatch:
                 "g_entry_off": offs([len(f["entry_state"]) for f in forms]),
                 "entry_state": cat([f["entry_state"] for f in forms], np.int32),
             })
+            # index into `band` of every predecessor-CSR edge (-1: the arc from a non-emitting entry state), so that
+            # srb_update_transitions can rewrite a re-estimated cost wherever the kernels read it
+            slots = []
+            for i, g in enumerate(graphs):
+                k = g.pred_tgt.astype(np.int64) - g.pred_idx
+                sl = (int(self.state_off[i]) + g.pred_tgt.astype(np.int64)) * 3 + (2 - k)
+                slots.append(np.where((k >= 0) & (k <= 2) & (g.emit[g.pred_idx] >= 0), sl, -1))
+            host["band_slot"] = cat(slots, np.int32)
         self.host = host
         self.dev = {}
         for k, v in host.items():

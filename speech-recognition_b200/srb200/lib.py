@@ -63,6 +63,7 @@ SIGNATURES = {
                                c_void_p, c_void_p]),
     "srb_mstep": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, ctypes.c_double,
                           c_void_p]),
+    "srb_update_transitions": (c_int, [c_void_p] * 4 + [c_i32] + [c_void_p] * 4),
     "srb_gauss_consts": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "srb_em_tile_frames": (c_int, []),
     "srb_em_parts": (c_int, []),

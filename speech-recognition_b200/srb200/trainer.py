@@ -27,12 +27,15 @@ def shard_range(n_items, rank, world):
 
 
 def sort_by_word(X, off, words):
-    """Reorder utterances so that each word's frames are contiguous.  -> (X, off, words, order)"""
+    """Reorder utterances so that each word's frames are contiguous.  -> (X, off, words, order)
+    X may be a CUDA tensor when the corpus is already word-sorted (it is then passed through untouched)."""
     words = np.asarray(words)
     order = np.argsort(words, kind="stable")
     lens = np.diff(off)
     if np.array_equal(order, np.arange(len(order))):
         return X, np.asarray(off), words, order
+    if torch.is_tensor(X):
+        X = X.cpu().numpy()
     new_off = np.zeros(len(off), np.int64)
     np.cumsum(lens[order], out=new_off[1:])
     idx = np.concatenate([np.arange(off[u], off[u + 1]) for u in order]) if len(order) else np.zeros(0, np.int64)
@@ -77,7 +80,7 @@ class IsolatedTrainer:
     def __init__(self, X, off, words, pm, trans, S, ncomp, group=None, var_floor=1e-6, fused=None):
         """X [N,D] float32, off [B+1], words [B] (numpy, this rank's shard); pm: PackedModel with W*S states;
         trans: [W,S,S] float64 numpy (decode.py:86-87 convention)."""
-        X, off, words, self.order = sort_by_word(np.asarray(X), np.asarray(off), words)
+        X, off, words, self.order = sort_by_word(X if torch.is_tensor(X) else np.asarray(X), np.asarray(off), words)
         self.dev = engine.device()
         self.X = engine.as_frames(X)
         self.pm, self.S, self.ncomp, self.group, self.var_floor = pm, S, ncomp, group, var_floor
@@ -247,7 +250,7 @@ class BaumWelchTrainer:
 
     def __init__(self, X, off, words, pm, trans, S, ncomp, group=None, var_floor=1e-6, gmin=1e-7,
                  update_transitions=True, tensor=None):
-        X, off, words, self.order = sort_by_word(np.asarray(X), np.asarray(off), words)
+        X, off, words, self.order = sort_by_word(X if torch.is_tensor(X) else np.asarray(X), np.asarray(off), words)
         self.dev = engine.device()
         self.X = engine.as_frames(X)
         self.pm, self.S, self.ncomp, self.group = pm, S, ncomp, group
@@ -259,7 +262,7 @@ class BaumWelchTrainer:
         self.N, self.B = int(off[-1]), len(off) - 1
         uptr = np.searchsorted(words, np.arange(self.W + 1), side="left")
         self.word_rows = [(int(off[uptr[w]]), int(off[uptr[w + 1]])) for w in range(self.W)]
-        self.trans = np.array(trans, dtype=np.float64)
+        self._trans0 = np.array(trans, dtype=np.float64)
         self._build_graphs()
         self.E = torch.empty((max(self.N, 1), S), dtype=torch.float32, device=self.dev)
         L = _l.load()
@@ -285,15 +288,50 @@ class BaumWelchTrainer:
         self.lc = torch.empty(self.G, dtype=torch.float64, device=self.dev)
 
     def _build_graphs(self):
-        self.graphs = [StateGraph(self.trans[w], np.arange(self.S)) for w in range(self.W)]
+        self.graphs = [StateGraph(self._trans0[w], np.arange(self.S)) for w in range(self.W)]
         self.gb = GraphBatch(self.graphs, self.dev)
 
-    def e_step(self):
+    @property
+    def trans(self):
+        """[W, S, S] float64 transition costs (decode.py:86-87 convention) read back from the device graphs, where
+        srb_update_transitions re-estimates them in place."""
+        pc = self.gb["pred_cost"].cpu().numpy().astype(np.float64)
+        out = np.full((self.W, self.S, self.S), np.inf)
+        for w, g in enumerate(self.graphs):
+            e0 = int(self.gb.edge_off[w])
+            out[w][g.pred_tgt, g.pred_idx] = pc[e0:e0 + g.nnz]
+        return out
+
+    def em_iteration_from_host(self, Xh):
+        """One iteration with the shard coming from PINNED host memory (the end-to-end path bench.py times): every
+        word's block of frames is copied host->device on a copy stream while the blocks before it are scored."""
+        cur = torch.cuda.current_stream()
+        if not hasattr(self, "_copy_stream"):
+            self._copy_stream = torch.cuda.Stream(self.dev)
+        cp = self._copy_stream
+        cp.wait_stream(cur)                                   # the previous iteration is done reading self.X
+        ready = []
+        for r0, r1 in self.word_rows:
+            with torch.cuda.stream(cp):
+                if r1 > r0:
+                    self.X[r0:r1].copy_(Xh[r0:r1], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(cp)
+            ready.append(ev)
+        self.e_step(ready=ready)
+        self.accumulate()
+        self.reduce()
+        self.update()
+        return self.stats
+
+    def e_step(self, ready=None):
         pm, S, L, p = self.pm, self.S, _l.load(), _l.ptr
         st = _l.stream_ptr()
         blk = S * pm.Mp * pm.D * 2
         RJ = S * self.J if self.tensor else 0
         for w, (r0, r1) in enumerate(self.word_rows):
+            if ready is not None:
+                torch.cuda.current_stream().wait_event(ready[w])
             if r1 <= r0:
                 continue
             ab_w, c_w = pm.ab[w * blk:].data_ptr(), pm.c[w * S * pm.Mp:].data_ptr()
@@ -346,17 +384,13 @@ class BaumWelchTrainer:
                                      _l.ptr(pm.w), float(self.var_floor), _l.stream_ptr()))
         pm.repack()
         if self.update_transitions:
-            o = self.G * self.row
-            xi = self.stats[o:o + self.nnz].cpu().numpy()
-            for w, g in enumerate(self.graphs):
-                e0 = int(self.gb.edge_off[w])
-                x = xi[e0:e0 + g.nnz]
-                out = np.bincount(g.pred_idx, weights=x, minlength=self.S)      # total mass leaving each origin
-                with np.errstate(divide="ignore", invalid="ignore"):
-                    cost = -np.log(x / out[g.pred_idx])
-                keep = (out[g.pred_idx] > 0) & (x > 0)          # arcs never taken keep their cost (and the CSR its shape)
-                self.trans[w][g.pred_tgt[keep], g.pred_idx[keep]] = cost[keep]
-            self._build_graphs()
+            # a[o -> r] = xi[o -> r] / sum_r' xi[o -> r'], rewritten in place in the device graphs (no host round trip)
+            o, gb, p = self.G * self.row, self.gb, _l.ptr
+            xi = self.stats[o:o + self.nnz]
+            _l.check(_l.load().srb_update_transitions(
+                xi.data_ptr(), p(gb["succ_ptr"]), p(gb["succ_edge"]), p(gb["band_slot"]) if gb.banded else None,
+                int(gb.state_off[-1]), p(gb["pred_cost"]), p(gb["succ_cost"]), p(gb["band"]) if gb.banded else None,
+                _l.stream_ptr()))
 
     def em_iteration(self):
         self.e_step()

@@ -129,8 +129,12 @@ def test_gmm_best_tensor_core_blocks(eng, R, M, N):
     np.testing.assert_allclose(E[np.arange(N), bs], bc, rtol=2e-5)   # the state named carries the cost named
     bc2, bs2 = eng.gmm_best_tc(X, pm)                                # cached block packing, one frame pass
     assert np.array_equal(bc2.cpu().numpy(), bc) and np.array_equal(bs2.cpu().numpy(), bs)
-    out = eng.gmm_score(X, pm, want_E=False, want_best=True, tensor=True)       # the public route to the same path
-    assert np.array_equal(out["best_cost"].cpu().numpy(), bc) and np.array_equal(out["best_state"].cpu().numpy(), bs)
+    out = eng.gmm_score(X, pm, want_E=False, want_best=True, tensor=True)       # the public route: this path for states
+    if M % 16:                                                                  # of 4, 8, 12 Gaussians, else the GEMM kernel
+        assert np.array_equal(out["best_cost"].cpu().numpy(), bc) and np.array_equal(out["best_state"].cpu().numpy(), bs)
+    else:
+        np.testing.assert_allclose(out["best_cost"].cpu().numpy(), bc, rtol=2e-5)
+        assert np.array_equal(out["best_state"].cpu().numpy()[decided], bs[decided])
 
 
 @pytest.mark.parametrize("R,M,N", [(20, 32, 1500), (130, 16, 2100), (1, 16, 130), (7, 48, 300), (2, 64, 129), (3, 160, 64),
