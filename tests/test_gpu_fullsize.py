@@ -1,0 +1,153 @@
+"""GPU parity at BASELINE shapes and sizes (configs 3, 4, 5): the kernels run on >= 1 M frames at the full model shape
+and a random sample of their outputs is compared with the float64 oracle -- costs at 1e-4 relative, states / paths /
+strings exact wherever the oracle's decision margin exceeds that; inside the margin either choice is accepted when its
+own float64 cost matches the optimum within the tolerance.  bench.py repeats the config-5 check on the
+10 M-frame run itself (cpu_baseline.best_state_agreement_outside_margin)."""
+import os
+from concurrent.futures import ThreadPoolExecutor
+
+import numpy as np
+import pytest
+
+from oracle import oracle as orc
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-4
+
+
+def test_config5_2000x32_sampled_oracle():
+    """2 000 states x 32 Gaussians, 1 M frames through srb_gmm_best_gemm; 1 024 sampled frames against orc_gmm_evaluate."""
+    import torch
+    from srb200 import engine
+    R, M, N, D = 2000, 32, 1 << 20, 39
+    rng = np.random.default_rng(7)
+    mu = rng.normal(size=(R, 1, D)) + 0.5 * rng.normal(size=(R, M, D))
+    var = rng.uniform(0.5, 1.5, size=(R, M, D))
+    w = rng.dirichlet(np.ones(M), size=R)
+    pm = engine.PackedModel(mu, var, w)
+    X = torch.randn((N, D), dtype=torch.float32, device="cuda", generator=torch.Generator("cuda").manual_seed(9))
+    bc, bs = engine.gmm_best_gemm(X, pm)
+    idx = np.sort(rng.choice(N, 1024, replace=False))
+    Xs = X[torch.from_numpy(idx).cuda()].cpu().numpy().astype(np.float64)
+    cost = np.stack([orc.gmm_evaluate(Xs, mu[r], var[r], w[r], log_domain=True)[0] for r in range(R)], axis=1)
+    bc, bs = bc.cpu().numpy()[idx], bs.cpu().numpy()[idx]
+    np.testing.assert_allclose(bc, cost.min(axis=1), rtol=RTOL)
+    so = np.sort(cost, axis=1)
+    decided = (so[:, 1] - so[:, 0]) > RTOL * np.abs(so[:, 0])
+    assert decided.mean() > 0.95
+    assert np.array_equal(bs[decided], cost.argmin(axis=1)[decided])
+    np.testing.assert_allclose(cost[np.arange(len(idx)), bs], bc, rtol=RTOL)      # inside the margin: the named state's cost
+
+
+def path_cost(path, end_state, T, E, trans):
+    """float64 cost of a decoded path (reversed [[state, frame], ...], end cell excluded) under decode.py's rules."""
+    pts = [(int(s), int(f)) for s, f in path[::-1]] + [(int(end_state), T - 1)]
+    c = E[pts[0][1], pts[0][0]]
+    for (s0, f0), (s1, f1) in zip(pts[:-1], pts[1:]):
+        c += trans[s1, s0] + E[f1, s1]
+    return c
+
+
+def test_config4_connected_digits_sampled_oracle():
+    """4 096 utterances x 500 frames on the 393-state digit-loop graph (2 M frames): tcgen05 scoring + one-graph banded
+    Viterbi + word strings; 96 sampled utterances against orc_decode (decode.py:80-146)."""
+    from srb200 import engine, synth
+    from srb200.decoder import StringDecoder
+    W, S, L, T, B = 11, 5, 7, 500, 4096
+    models, base = synth.make_models(1, W=W, S=S, M=4)
+    X, off, strings = synth.make_strings(300, base, B, L, T)
+    pm, _ = engine.PackedModel.from_words(models)
+    dec = StringDecoder(pm, np.stack([m[3] for m in models]), L, off)
+    words, nwords = dec.run(engine.as_frames(X))
+    words, nwords = words.cpu().numpy(), nwords.cpu().numpy()
+    assert (nwords == L).all() and (words == strings).all()
+    p = dec.plan
+    ps, pf, pl = p.ps.cpu().numpy(), p.pf.cpu().numpy(), p.pl.cpu().numpy()
+    bcost, bend = p.best_cost.cpu().numpy(), p.best_end.cpu().numpy()
+    emit, trans, ends = orc.build_state_sequences(S, [m[3] for m in models], [list(range(W))] * L)
+    sample = np.sort(np.random.default_rng(3).choice(B, 96, replace=False))
+    orc.set_num_threads(1)
+
+    def one(u):
+        x = X[off[u]:off[u + 1]].astype(np.float64)
+        E = orc.emissions(x, models, emit, log_domain=True)
+        costs, path, best = orc.decode_hmm_states(E, trans, emit < 0, [[e, -1] for e in ends])
+        return E, costs, path, best
+
+    with ThreadPoolExecutor(os.cpu_count() or 8) as ex:
+        res = list(ex.map(one, sample))
+    orc.set_num_threads()
+    same = 0
+    for u, (E, costs, path, best) in zip(sample, res):
+        ref_cost = costs[best[0], best[1]]
+        np.testing.assert_allclose(bcost[u], ref_cost, rtol=RTOL)
+        got = np.stack([ps[p.po[u]:p.po[u] + pl[u]], pf[p.po[u]:p.po[u] + pl[u]]], axis=1)
+        if np.array_equal(got, path) and bend[u] == best[0]:
+            same += 1
+        else:   # a near-tie resolved the other way in FP32: the path taken must cost the optimum within the tolerance
+            np.testing.assert_allclose(path_cost(got, bend[u], T, E, trans), ref_cost, rtol=RTOL)
+        assert orc.path_to_words(got, emit, S) == list(strings[u])
+    assert same >= 0.9 * len(sample)
+
+
+def test_config3_baum_welch_iteration_full_shape():
+    """11 words x 8 states x 16 Gaussians (4 trained), 6 000 ragged utterances of 50-300 frames (> 1 M frames): one
+    BaumWelchTrainer iteration (tcgen05 scoring + banded forward-backward + soft statistics + M-step + transition update)
+    against a float64 restatement on the oracle's forward-backward over the WHOLE corpus."""
+    from srb200 import engine, synth
+    from srb200.trainer import BaumWelchTrainer, sort_by_word
+    W, S, M, D = 11, 8, 16, 39
+    ncomp = 2 ** int(np.log(M))
+    models, base = synth.make_models(11, W=W, S=S, M=M)
+    X, off, words = synth.make_utterances(400, base, 6000, ragged=(50, 300))
+    X, off, words, _ = sort_by_word(X, off, words)
+    assert X.shape[0] > 1_000_000
+    pm, _ = engine.PackedModel.from_words(models)
+    tr = BaumWelchTrainer(X, off, words, pm, np.stack([m[3] for m in models]), S, ncomp)
+    assert tr.tensor
+    tr.em_iteration()
+    # ---- float64 restatement
+    X64 = X.astype(np.float64)
+    G = W * S
+    S0, S1, S2, cnt = np.zeros((G, ncomp)), np.zeros((G, ncomp, D)), np.zeros((G, ncomp, D)), np.zeros(G)
+    xi = np.zeros((W, S, S))
+    nlz_sum = 0.0
+    mu0 = np.concatenate([m[0] for m in models])
+    for u in range(len(words)):
+        m = models[words[u]]
+        x = X64[off[u]:off[u + 1]]
+        comps = np.stack([orc.gmm_evaluate(x, m[0][s], m[1][s], m[2][s], log_domain=True)[1] for s in range(S)], axis=1)
+        mx = comps.max(axis=2, keepdims=True)
+        E = -(mx[:, :, 0] + np.log(np.exp(comps - mx).sum(axis=2)))
+        nlz, al, be, gam = orc.forward_backward(E, m[3])
+        nlz_sum += nlz
+        for k in range(3):                                               # arcs r-k -> r of the left-to-right band
+            for r in range(k, S):
+                if np.isfinite(m[3][r, r - k]):
+                    xi[words[u], r, r - k] += np.exp(-(al[:-1, r - k] + m[3][r, r - k] + E[1:, r] + be[1:, r] - nlz)).sum()
+        lc = comps[:, :, :ncomp]
+        p = np.exp(lc - lc.max(axis=2, keepdims=True))
+        p = p / p.sum(axis=2, keepdims=True) * gam[:, :, None]
+        g0 = words[u] * S
+        cnt[g0:g0 + S] += gam.sum(axis=0)
+        S0[g0:g0 + S] += p.sum(axis=0)
+        for s in range(S):
+            e = x[:, None, :] - mu0[g0 + s, None, :ncomp]                # moments about the current means [T, ncomp, D]
+            S1[g0 + s] += np.einsum("tm,tmd->md", p[:, s], e)
+            S2[g0 + s] += np.einsum("tm,tmd->md", p[:, s], e * e)
+    m1 = S1 / S0[:, :, None]
+    mu = mu0[:, :ncomp] + m1
+    var = S2 / S0[:, :, None] - m1 * m1
+    wgt = S0 / cnt[:, None]
+    np.testing.assert_allclose(tr.mean_neg_log_z(), nlz_sum / len(words), rtol=1e-6)
+    np.testing.assert_allclose(pm.w.cpu().numpy()[:, :ncomp], wgt, rtol=RTOL)
+    got_mu = pm.mu.cpu().numpy()[:, :ncomp]
+    assert np.max(np.abs(got_mu - mu) / np.maximum(np.abs(mu), np.sqrt(var))) < RTOL
+    np.testing.assert_allclose(pm.var.cpu().numpy()[:, :ncomp], var, rtol=RTOL)
+    got_tr = tr.trans
+    for wd in range(W):
+        out = xi[wd].sum(axis=0)
+        for r in range(S):
+            for o in range(S):
+                if np.isfinite(models[wd][3][r, o]) and xi[wd][r, o] > 0:
+                    np.testing.assert_allclose(np.exp(-got_tr[wd][r, o]), xi[wd][r, o] / out[o], rtol=RTOL)
