@@ -329,7 +329,8 @@ int srb_gauss_consts(const double *var, const double *w, int G, int D, double *l
  *                 utt_word must be non-decreasing; an utterance longer than a tile gives SRB_EUNSUPPORTED (use
  *                 srb_gmm_score_rows + srb_viterbi_graph + srb_gmm_stats instead).
  *   srb_em_isolated  partial: caller scratch of srb_em_parts() * W*S*M * srb_stats_row(D) floats, or NULL for an
- *                 alignment-only call; stats_out double[W*S*M, row] as srb_gmm_stats; optional outputs
+ *                 alignment-only call; stats_out double[W*S*M, row] as srb_gmm_stats (accumulate < 0: the per-CTA
+ *                 slices stay in `partial` for srb_em_push, stats_out may be NULL); optional outputs
  *                 best_cost[B] (costs[-1,-1] of hmm.py:135, +inf when no path), seg_start int32[B,S] (segment start
  *                 frames = seg_starts of kmeans.py:200-204), frame_label int32[N] (w*S+s, -1 without a path). */
 int srb_em_tile_frames(void);
@@ -341,6 +342,33 @@ int srb_em_isolated(const float *X, int64_t N, int D, const int32_t *utt_off, in
                     int W, int S, int M, int Mp, const float *trans, int ncomp, const double *mu, float *partial,
                     double *stats_out, int accumulate, float *best_cost, int32_t *seg_start, int32_t *frame_label,
                     void *stream);
+
+/* ---- multi-GPU tail of the fused training pass: statistics exchange over NVLink peer memory + replicated M-step -------
+ * One process per GPU; the only coupling of the ranks is the sum of the sufficient statistics (kmeans.py:41-50 pools the
+ * frames of ALL utterances per state).  Instead of reduce + ncclAllReduce + M-step + two packing launches:
+ *   srb_peer_alloc / _export / _open / _close / _free   a device buffer other processes of the box can map (CUDA IPC):
+ *                   the owner exports a 64-byte handle, the peers open it (the host layer ships the handles)
+ *   srb_em_sync_bytes(world, len)   size of a rank's exchange buffer for statistics of `len` doubles (W*S*M*(2D+3))
+ *   srb_em_push     sums the per-CTA slices srb_em_isolated left in `partial` (call it with accumulate = -1) in a fixed
+ *                   order, adds the summed best_cost and the utterance count, and stores the len+2 doubles into slot
+ *                   [epoch & 1][rank] of EVERY rank's buffer (peer_bufs: HOST array of `world` device pointers, entry
+ *                   `rank` the own buffer), then releases flag[rank] = epoch on every peer.  epoch = 1, 2, 3, ...
+ *   srb_em_update   waits until all `world` flags of the own buffer reach `epoch`, adds the slots IN RANK ORDER (all
+ *                   ranks get bit-identical totals) into stats_out[len+2], applies the M-step of GMM.em
+ *                   (hmm_state.py:138-148, as srb_mstep) to mu / var / w and re-packs ab / c (srb_pack_model) and, when
+ *                   tcb != NULL, the tensor-core operand (srb_pack_model_tc) -- one CTA per Gaussian, D = 39.
+ * world <= 8.  With world == 1 the pair is the single-GPU tail (no peers involved). */
+int srb_peer_alloc(int64_t bytes, void **ptr);
+int srb_peer_free(void *ptr);
+int srb_peer_export(void *ptr, uint8_t *handle64);
+int srb_peer_open(const uint8_t *handle64, void **ptr);
+int srb_peer_close(void *ptr);
+int64_t srb_em_sync_bytes(int world, int64_t len);
+int srb_em_push(const float *partial, int32_t nparts, int64_t len, const float *best_cost, int32_t B, void *const *peer_bufs,
+                int world, int rank, uint64_t epoch, void *stream);
+int srb_em_update(void *own_buf, int world, uint64_t epoch, int R, int M, int Mp, int ncomp, int D, double *mu, double *var,
+                  double *w, const double *shift, double var_floor, float *ab, float *c, float *tcb, double *stats_out,
+                  void *stream);
 
 /* ---- FP32 FMA peak probe (roofline denominator for K1; not part of the reference path) ----------
  * Runs `iters` dependent-chain-free FMA rounds per thread on every SM and returns elapsed ms through

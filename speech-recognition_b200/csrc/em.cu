@@ -459,7 +459,8 @@ int srb_em_isolated(const float *X, int64_t N, int D, const int32_t *utt_off, in
                     void *stream) {
     SRB_REQUIRE(X && utt_off && tile_desc && ab && c && shift && trans && ((uintptr_t)tile_desc & 15) == 0, SRB_EINVAL,
                 "srb_em_isolated: null pointer");
-    SRB_REQUIRE(!partial || (stats_out && mu), SRB_EINVAL, "srb_em_isolated: statistics need stats_out and mu");
+    SRB_REQUIRE(!partial || ((stats_out || accumulate < 0) && mu), SRB_EINVAL,
+                "srb_em_isolated: statistics need stats_out and mu");
     SRB_REQUIRE(W > 0 && S > 0 && S <= ESMAX && M > 0 && Mp >= M && (Mp & 3) == 0, SRB_EUNSUPPORTED,
                 "srb_em_isolated: S=%d (max %d), M=%d, Mp=%d", S, ESMAX, M, Mp);
     SRB_REQUIRE(ncomp >= 1 && ncomp <= M && ncomp <= EMAXC, SRB_EUNSUPPORTED, "srb_em_isolated: ncomp=%d", ncomp);
@@ -505,7 +506,7 @@ int srb_em_isolated(const float *X, int64_t N, int D, const int32_t *utt_off, in
 #undef SRB_EM_LAUNCH
 #undef SRB_EM_LAUNCH_T
     }
-    if (partial) {
+    if (partial && accumulate >= 0) {                        // accumulate < 0: the slices are left for srb_em_push
         const int64_t len = (int64_t)G * row;
         reduce_slices_kernel<<<(int)((len + 255) / 256), 256, 0, st>>>(partial, nparts, len, stats_out, accumulate);
     }

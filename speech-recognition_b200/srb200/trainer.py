@@ -42,6 +42,63 @@ def sort_by_word(X, off, words):
     return X[idx], new_off.astype(off.dtype), words[order], order
 
 
+class PeerExchange:
+    """Exchange buffers of the fused training tail (srb_em_push / srb_em_update): one device buffer per rank that every
+    other process of the box maps through CUDA IPC, so that a rank's statistics are STORED into its peers' memory over
+    NVLink by the kernel that forms them -- no collective call, no host in the loop."""
+
+    def __init__(self, length, group=None):
+        import ctypes
+        import torch.distributed as dist
+        L = _l.load()
+        multi = dist.is_initialized() and dist.get_world_size(group) > 1
+        self.world = dist.get_world_size(group) if multi else 1
+        self.rank = dist.get_rank(group) if multi else 0
+        self.length, self.epoch, self.opened = int(length), 0, []
+        nbytes = int(L.srb_em_sync_bytes(self.world, self.length))
+        if nbytes <= 0:
+            raise _l.SrbError(-2, f"no exchange buffer layout for {self.world} ranks")
+        own = ctypes.c_void_p()
+        _l.check(L.srb_peer_alloc(nbytes, ctypes.byref(own)))
+        self.own = own.value
+        ptrs = [None] * self.world
+        ptrs[self.rank] = self.own
+        if multi:
+            dev = engine.device()
+            handle = (ctypes.c_uint8 * 64)()
+            ok = L.srb_peer_export(self.own, handle) == 0
+            mine = torch.tensor(list(handle) + [int(ok)], dtype=torch.uint8, device=dev)
+            allh = [torch.empty_like(mine) for _ in range(self.world)]
+            dist.all_gather(allh, mine, group=group)
+            allh = [h.cpu().numpy() for h in allh]
+            ok = all(int(h[64]) for h in allh)
+            for r in range(self.world):
+                if ok and r != self.rank:
+                    p = ctypes.c_void_p()
+                    hb = (ctypes.c_uint8 * 64)(*[int(v) for v in allh[r][:64]])
+                    if L.srb_peer_open(hb, ctypes.byref(p)) == 0:
+                        ptrs[r] = p.value
+                        self.opened.append(p.value)
+                    else:
+                        ok = False
+            flag = torch.tensor([int(ok)], dtype=torch.int32, device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)          # every rank mapped every peer, or nobody
+            if not int(flag.item()):
+                self.close()
+                raise _l.SrbError(-3, "CUDA IPC mapping of the peers' exchange buffers failed: " +
+                                  L.srb_last_error_string().decode())
+        self.ptr_array = (ctypes.c_void_p * self.world)(*ptrs)
+
+    def close(self):
+        L = _l.load()
+        for p in self.opened:
+            L.srb_peer_close(p)
+        self.opened = []
+        if getattr(self, "own", None):
+            L.srb_peer_free(self.own)
+            self.own = None
+
+
 class ViterbiPlan:
     """Pre-planned K2 launch for a fixed batch (offsets, graphs): all buffers allocated once."""
 
@@ -77,9 +134,11 @@ class ViterbiPlan:
 class IsolatedTrainer:
     """All W word models trained together on this rank's shard of a word-sorted corpus."""
 
-    def __init__(self, X, off, words, pm, trans, S, ncomp, group=None, var_floor=1e-6, fused=None):
+    def __init__(self, X, off, words, pm, trans, S, ncomp, group=None, var_floor=1e-6, fused=None, peer=None):
         """X [N,D] float32, off [B+1], words [B] (numpy, this rank's shard); pm: PackedModel with W*S states;
-        trans: [W,S,S] float64 numpy (decode.py:86-87 convention)."""
+        trans: [W,S,S] float64 numpy (decode.py:86-87 convention).
+        peer: None = the two-launch tail over NVLink peer memory (srb_em_push / srb_em_update) when the fused pass runs
+        and the peers' buffers can be mapped, else reduce + NCCL allreduce + M-step + packing; True / False force one."""
         X, off, words, self.order = sort_by_word(X if torch.is_tensor(X) else np.asarray(X), np.asarray(off), words)
         self.dev = engine.device()
         self.X = engine.as_frames(X)
@@ -110,6 +169,16 @@ class IsolatedTrainer:
                 raise ValueError("fused training pass not applicable: " + self.fused_why)
         if self.fused:
             self.launches_per_iteration = 1 + 1 + 1 + 2 + 1 + 1   # memset+em+reduce, cost sum (2), mstep, pack
+        self.peer = None
+        if self.fused and peer is not False and pm.D == 39:
+            try:
+                self.peer = PeerExchange(self.G * self.row, group)
+                self.launches_per_iteration = 2 + 1 + 1            # memset + em kernel, push, update
+            except _l.SrbError:
+                if peer:
+                    raise
+        elif peer:
+            raise ValueError("the peer-memory tail needs the fused pass and D = 39")
 
     def _plan_fused(self, off32, words32, trans):
         import ctypes
@@ -164,20 +233,21 @@ class IsolatedTrainer:
                 p(self.em_partial), p(body), int(k > 0), p(self.best_cost), None, None, cur.cuda_stream))
         self.stats[self.G * self.row] = self.best_cost[:self.B].sum(dtype=torch.float64)
         self.stats[self.G * self.row + 1] = float(self.B)
-        self.reduce()
-        self.update()
+        self._allreduce()                                      # the chunks accumulate through stats_out: collective tail
+        self._mstep()
         return self.stats
 
     def fused_pass(self, seg_start=None, frame_label=None, stats=True):
         """srb_em_isolated over the shard: statistics body of self.stats (+ best_cost, optional boundaries/labels)."""
         pm, p = self.pm, _l.ptr
         body = self.stats[:self.G * self.row]
+        keep = stats and self.peer is not None                 # the slices stay for srb_em_push (reduce())
         _l.check(_l.load().srb_em_isolated(
             p(self.X), self.N, pm.D, p(self.off_d), self.B, p(self.tiles), self.ntiles, self.tile_frames, p(pm.ab),
             p(pm.c), p(pm.shift), self.W, self.S, pm.M, pm.Mp, p(self.trans_d), self.ncomp, p(pm.mu),
-            p(self.em_partial) if stats else None, p(body) if stats else None, 0, p(self.best_cost), p(seg_start),
-            p(frame_label), _l.stream_ptr()))
-        if stats:
+            p(self.em_partial) if stats else None, p(body) if stats else None, -1 if keep else 0, p(self.best_cost),
+            p(seg_start), p(frame_label), _l.stream_ptr()))
+        if stats and not keep:
             self.stats[self.G * self.row] = self.best_cost[:self.B].sum(dtype=torch.float64)
             self.stats[self.G * self.row + 1] = float(self.B)
         return self.stats
@@ -212,12 +282,34 @@ class IsolatedTrainer:
         return self.stats
 
     def reduce(self):
-        """The one collective of an iteration: sum of the statistics buffer over ranks (NCCL over NVLink)."""
+        """The one exchange of an iteration: the sum of the statistics over the ranks.  Peer tail: srb_em_push folds
+        the per-CTA slices and stores the result into every rank's exchange buffer over NVLink; else NCCL allreduce."""
+        if self.peer is not None:
+            pe = self.peer
+            pe.epoch += 1
+            _l.check(_l.load().srb_em_push(_l.ptr(self.em_partial), _l.load().srb_em_parts(), self.G * self.row,
+                                           _l.ptr(self.best_cost), self.B, pe.ptr_array, pe.world, pe.rank, pe.epoch,
+                                           _l.stream_ptr()))
+            return self.stats
+        return self._allreduce()
+
+    def _allreduce(self):
         if self.group is not None or (torch.distributed.is_initialized() and torch.distributed.get_world_size() > 1):
             torch.distributed.all_reduce(self.stats, group=self.group)
         return self.stats
 
     def update(self):
+        """Replicated M-step + repacking.  Peer tail: srb_em_update (waits for the peers' flags, sums the slots in rank
+        order, M-step and both packings, one CTA per Gaussian)."""
+        if self.peer is None:
+            return self._mstep()
+        pm, pe, p = self.pm, self.peer, _l.ptr
+        _l.check(_l.load().srb_em_update(pe.own, pe.world, pe.epoch, pm.R, pm.M, pm.Mp, self.ncomp, pm.D, p(pm.mu),
+                                         p(pm.var), p(pm.w), p(pm.shift64), float(self.var_floor), p(pm.ab), p(pm.c),
+                                         p(pm.tcb), p(self.stats), _l.stream_ptr()))
+        pm.version += 1                                        # caches of derived packings key on it
+
+    def _mstep(self):
         pm = self.pm
         _l.check(_l.load().srb_mstep(_l.ptr(self.stats), pm.R, pm.M, self.ncomp, pm.D, _l.ptr(pm.mu), _l.ptr(pm.var),
                                      _l.ptr(pm.w), float(self.var_floor), _l.stream_ptr()))
