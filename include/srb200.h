@@ -328,13 +328,16 @@ int srb_gauss_consts(const double *var, const double *w, int G, int D, double *l
  *                 word << 8 | utterances} (capacity 4*B ints; copy it to 16-byte aligned device memory).
  *                 utt_word must be non-decreasing; an utterance longer than a tile gives SRB_EUNSUPPORTED (use
  *                 srb_gmm_score_rows + srb_viterbi_graph + srb_gmm_stats instead).
- *   srb_em_isolated  partial: caller scratch of srb_em_parts() * W*S*M * srb_stats_row(D) floats, or NULL for an
+ *   srb_em_isolated  partial: caller scratch of srb_em_partial_floats(W, S, M, D) floats (srb_em_parts() private slices of
+ *                 W*S*M * srb_stats_row(D) floats, one per CTA, followed by one 64-bit word mask per slice: a CTA WRITES
+ *                 the rows of the words it saw and sets their bits, nothing is zero-filled; W <= 64), or NULL for an
  *                 alignment-only call; stats_out double[W*S*M, row] as srb_gmm_stats (accumulate < 0: the per-CTA
  *                 slices stay in `partial` for srb_em_push, stats_out may be NULL); optional outputs
  *                 best_cost[B] (costs[-1,-1] of hmm.py:135, +inf when no path), seg_start int32[B,S] (segment start
  *                 frames = seg_starts of kmeans.py:200-204), frame_label int32[N] (w*S+s, -1 without a path). */
 int srb_em_tile_frames(void);
 int srb_em_parts(void);
+int64_t srb_em_partial_floats(int W, int S, int M, int D);
 int srb_em_plan(const int32_t *utt_off_host, const int32_t *utt_word_host, int32_t B, int32_t *tile_desc_host,
                 int32_t *ntiles, int32_t *tile_frames);
 int srb_em_isolated(const float *X, int64_t N, int D, const int32_t *utt_off, int32_t B, const int32_t *tile_desc,
@@ -364,8 +367,8 @@ int srb_peer_export(void *ptr, uint8_t *handle64);
 int srb_peer_open(const uint8_t *handle64, void **ptr);
 int srb_peer_close(void *ptr);
 int64_t srb_em_sync_bytes(int world, int64_t len);
-int srb_em_push(const float *partial, int32_t nparts, int64_t len, const float *best_cost, int32_t B, void *const *peer_bufs,
-                int world, int rank, uint64_t epoch, void *stream);
+int srb_em_push(const float *partial, int32_t nparts, int W, int S, int M, int ncomp, int D, const float *best_cost,
+                int32_t B, void *const *peer_bufs, int world, int rank, uint64_t epoch, void *stream);
 int srb_em_update(void *own_buf, int world, uint64_t epoch, int R, int M, int Mp, int ncomp, int D, double *mu, double *var,
                   double *w, const double *shift, double var_floor, float *ab, float *c, float *tcb, double *stats_out,
                   void *stream);

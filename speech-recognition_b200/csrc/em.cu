@@ -65,8 +65,8 @@ em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__rest
                    const int4 *__restrict__ tile_desc, int ntiles,
                    const float *__restrict__ ab, const float *__restrict__ c, const float *__restrict__ shift, int S_rt,
                    int M, int Mp, const float *__restrict__ trans, int ncomp_rt, const double *__restrict__ mu,
-                   float *__restrict__ partial, int G, float *__restrict__ best_cost, int32_t *__restrict__ seg_start,
-                   int32_t *__restrict__ frame_label) {
+                   float *__restrict__ partial, unsigned long long *__restrict__ slice_mask, int G,
+                   float *__restrict__ best_cost, int32_t *__restrict__ seg_start, int32_t *__restrict__ frame_label) {
     extern __shared__ __align__(16) float smem[];
     const int S = ST ? ST : S_rt;
     const int ncomp = NC ? NC : ncomp_rt;
@@ -86,7 +86,11 @@ em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__rest
     // contiguous range of tiles per CTA: a CTA sees one or two words, so parameters are (re)loaded rarely
     const int t_lo = (int)((int64_t)ntiles * blockIdx.x / gridDim.x);
     const int t_hi = (int)((int64_t)ntiles * (blockIdx.x + 1) / gridDim.x);
+    // The CTA's private slice holds one block of rows per word.  Words arrive in ascending order, so a word is flushed
+    // exactly once per launch: the flush WRITES its rows and sets the word's bit in the slice's mask; rows of other
+    // words are never read by the reducers (no 42 MB memset and no 42 MB of zeros to add per iteration).
     float *slice = stats ? partial + (size_t)blockIdx.x * G * row : nullptr;
+    unsigned long long wmask = 0ull;
     int cur_w = -1;
 
     int4 desc = t_lo < t_hi ? __ldg(tile_desc + t_lo) : make_int4(0, 0, 0, 0);
@@ -103,8 +107,9 @@ em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__rest
 #pragma unroll
                     for (int q = 0; q < EWARPS; ++q) s += part[q * GW * row + i];
                     const int g = i / row, j = i - g * row;
-                    slice[((size_t)(cur_w * S + g / ncomp) * M + g % ncomp) * row + j] += s;
+                    slice[((size_t)(cur_w * S + g / ncomp) * M + g % ncomp) * row + j] = s;
                 }
+                wmask |= 1ull << (cur_w & 63);
             }
             __syncthreads();
             if (stats)
@@ -396,17 +401,27 @@ em_isolated_kernel(const float *__restrict__ X, int64_t N, const int32_t *__rest
 #pragma unroll
             for (int q = 0; q < EWARPS; ++q) s += part[q * GW * row + i];
             const int g = i / row, j = i - g * row;
-            slice[((size_t)(cur_w * S + g / ncomp) * M + g % ncomp) * row + j] += s;
+            slice[((size_t)(cur_w * S + g / ncomp) * M + g % ncomp) * row + j] = s;
         }
+        wmask |= 1ull << (cur_w & 63);
     }
+    if (stats && tid == 0) slice_mask[blockIdx.x] = wmask;
 }
 
-__global__ void reduce_slices_kernel(const float *__restrict__ partial, int64_t nparts, int64_t len,
+// Fixed-order fp64 sum of the per-CTA slices.  Only the rows a slice's CTA has written are read: word w of slice p when
+// bit w of mask[p] is set, and of those the rows of the first ncomp components (the others were never touched: 0).
+__global__ void reduce_slices_kernel(const float *__restrict__ partial, const unsigned long long *__restrict__ mask,
+                                     int64_t nparts, int64_t len, int word_len, int M, int ncomp, int row,
                                      double *__restrict__ out, int accumulate) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= len) return;
     double s = accumulate ? out[i] : 0.0;
-    for (int64_t p = 0; p < nparts; ++p) s += (double)partial[p * len + i];
+    const int w = (int)(i / word_len);
+    if ((int)((i / row) % M) < ncomp) {
+        const unsigned long long bit = 1ull << (w & 63);
+        for (int64_t p = 0; p < nparts; ++p)
+            if (mask[p] & bit) s += (double)partial[p * len + i];
+    }
     out[i] = s;
 }
 
@@ -419,6 +434,11 @@ extern "C" {
 int srb_em_tile_frames(void) { return ETILE_MAX; }
 
 int srb_em_parts(void) { return sm_count() * EPARTS; }
+
+int64_t srb_em_partial_floats(int W, int S, int M, int D) {
+    const int64_t nparts = (int64_t)sm_count() * EPARTS;
+    return nparts * W * S * M * (2 * D + 3) + 2 * nparts;      // the slices + one 64-bit word mask per slice
+}
 
 int srb_em_plan(const int32_t *utt_off, const int32_t *utt_word, int32_t B, int32_t *tile_desc, int32_t *ntiles,
                 int32_t *tile_frames) {
@@ -472,7 +492,12 @@ int srb_em_isolated(const float *X, int64_t N, int D, const int32_t *utt_off, in
                 "srb_em_isolated: tile_frames must come from srb_em_plan");
     const int nparts = sms * EPARTS;
     cudaStream_t st = (cudaStream_t)stream;
-    if (partial) SRB_CUDA(cudaMemsetAsync(partial, 0, sizeof(float) * (size_t)nparts * G * row, st));
+    SRB_REQUIRE(!partial || W <= 64, SRB_EUNSUPPORTED, "srb_em_isolated: statistics for at most 64 word models per call");
+    // the masks of ALL slices are cleared (a launch may use fewer CTAs than there are slices); the slices themselves
+    // are not: a CTA writes the rows of the words it saw, the reducers read nothing else
+    unsigned long long *slice_mask = partial ? reinterpret_cast<unsigned long long *>(partial + (size_t)nparts * G * row)
+                                             : nullptr;
+    if (partial) SRB_CUDA(cudaMemsetAsync(slice_mask, 0, sizeof(unsigned long long) * (size_t)nparts, st));
     if (B > 0 && ntiles > 0) {
         const EmSmem L = em_layout(S, Mp, ncomp, D, partial != nullptr, tile_frames);
         const size_t bytes = sizeof(float) * (size_t)L.total;
@@ -485,7 +510,7 @@ int srb_em_isolated(const float *X, int64_t N, int D, const int32_t *utt_off, in
                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));                   \
         em_isolated_kernel<kD, kS, kC, kT><<<grid, kT, bytes, st>>>(                                               \
             X, N, utt_off, reinterpret_cast<const int4 *>(tile_desc), ntiles, ab, c, shift, S, M, Mp, trans, ncomp, mu, \
-            partial, G, best_cost, seg_start, frame_label);                                                        \
+            partial, slice_mask, G, best_cost, seg_start, frame_label);                                                        \
     }
 #define SRB_EM_LAUNCH(kD, kS, kC)                                                                                  \
     {                                                                                                              \
@@ -508,7 +533,8 @@ int srb_em_isolated(const float *X, int64_t N, int D, const int32_t *utt_off, in
     }
     if (partial && accumulate >= 0) {                        // accumulate < 0: the slices are left for srb_em_push
         const int64_t len = (int64_t)G * row;
-        reduce_slices_kernel<<<(int)((len + 255) / 256), 256, 0, st>>>(partial, nparts, len, stats_out, accumulate);
+        reduce_slices_kernel<<<(int)((len + 255) / 256), 256, 0, st>>>(partial, slice_mask, nparts, len, S * M * row, M, ncomp,
+                                                                       row, stats_out, accumulate);
     }
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;

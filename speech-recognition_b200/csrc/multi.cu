@@ -40,30 +40,25 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
 }
 
 __global__ void __launch_bounds__(256)
-em_push_kernel(const float *__restrict__ partial, int nparts, int64_t len, const float *__restrict__ best_cost, int B,
-               PeerBufs P, int world, int rank, unsigned long long epoch) {
+em_push_kernel(const float *__restrict__ partial, const unsigned long long *__restrict__ mask, int nparts, int64_t len,
+               int word_len, int M, int ncomp, int row, const float *__restrict__ best_cost, int B, PeerBufs P, int world,
+               int rank, unsigned long long epoch) {
     __shared__ double red[256];
     const int64_t slot_len = len + 2;
     const int64_t base = ((int64_t)(epoch & 1) * world + rank) * slot_len;
     if (blockIdx.x + 1 < gridDim.x) {
-        // 32 elements x 8 part groups per CTA: group q adds parts q*chunk .. in ascending order (4 loads in flight), then
-        // the 8 group sums are added in group order -- a fixed order whatever the timing, 8x shorter dependent chains
+        // 32 elements x 8 part groups per CTA: group q adds its parts in ascending order, then the 8 group sums are added
+        // in group order -- a fixed order whatever the timing.  Only slices whose CTA saw the element's word are read
+        // (mask bit), and only rows of trained components (the others were never written: 0).
         const int e = threadIdx.x & 31, q = threadIdx.x >> 5;
         const int64_t i = (int64_t)blockIdx.x * 32 + e;
         const int chunk = (nparts + 7) >> 3;
         const int p0 = q * chunk, p1 = min(nparts, p0 + chunk);
         double s = 0.0;
-        if (i < len) {
-            int p = p0;
-            for (; p + 4 <= p1; p += 4) {
-                const float a = partial[(int64_t)p * len + i], b = partial[(int64_t)(p + 1) * len + i];
-                const float c = partial[(int64_t)(p + 2) * len + i], d = partial[(int64_t)(p + 3) * len + i];
-                s += (double)a;
-                s += (double)b;
-                s += (double)c;
-                s += (double)d;
-            }
-            for (; p < p1; ++p) s += (double)partial[(int64_t)p * len + i];
+        if (i < len && (int)((i / row) % M) < ncomp) {
+            const unsigned long long bit = 1ull << ((int)(i / word_len) & 63);
+            for (int p = p0; p < p1; ++p)
+                if (mask[p] & bit) s += (double)partial[(int64_t)p * len + i];
         }
         red[threadIdx.x] = s;
         __syncthreads();
@@ -249,8 +244,10 @@ int64_t srb_em_sync_bytes(int world, int64_t len) {
     return SYNC_HEADER + (int64_t)sizeof(double) * 2 * world * (len + 2);
 }
 
-int srb_em_push(const float *partial, int32_t nparts, int64_t len, const float *best_cost, int32_t B, void *const *peer_bufs,
-                int world, int rank, uint64_t epoch, void *stream) {
+int srb_em_push(const float *partial, int32_t nparts, int W, int S, int M, int ncomp, int D, const float *best_cost,
+                int32_t B, void *const *peer_bufs, int world, int rank, uint64_t epoch, void *stream) {
+    const int row = 2 * D + 3;
+    const int64_t len = (int64_t)W * S * M * row;
     SRB_REQUIRE(partial && peer_bufs && (best_cost || B == 0), SRB_EINVAL, "srb_em_push: null pointer");
     SRB_REQUIRE(world >= 1 && world <= MAX_RANKS && rank >= 0 && rank < world && len > 0 && nparts > 0 && epoch > 0,
                 SRB_EINVAL, "srb_em_push: bad sizes (at most %d ranks)", MAX_RANKS);
@@ -258,8 +255,9 @@ int srb_em_push(const float *partial, int32_t nparts, int64_t len, const float *
     for (int r = 0; r < MAX_RANKS; ++r) P.buf[r] = r < world ? static_cast<uint8_t *>(peer_bufs[r]) : nullptr;
     for (int r = 0; r < world; ++r) SRB_REQUIRE(P.buf[r], SRB_EINVAL, "srb_em_push: peer buffer %d is null", r);
     const int grid = (int)((len + 31) / 32) + 1;
-    em_push_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(partial, nparts, len, best_cost, B, P, world, rank,
-                                                            (unsigned long long)epoch);
+    const unsigned long long *mask = reinterpret_cast<const unsigned long long *>(partial + (size_t)nparts * len);
+    em_push_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(partial, mask, nparts, len, S * M * row, M, ncomp, row, best_cost,
+                                                            B, P, world, rank, (unsigned long long)epoch);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }

@@ -77,7 +77,9 @@ SIGNATURES = {
     "srb_peer_open": (c_int, [c_void_p, ctypes.POINTER(c_void_p)]),
     "srb_peer_close": (c_int, [c_void_p]),
     "srb_em_sync_bytes": (c_i64, [c_int, c_i64]),
-    "srb_em_push": (c_int, [c_void_p, c_i32, c_i64, c_void_p, c_i32, c_void_p, c_int, c_int, ctypes.c_uint64, c_void_p]),
+    "srb_em_push": (c_int, [c_void_p, c_i32, c_int, c_int, c_int, c_int, c_int, c_void_p, c_i32, c_void_p, c_int, c_int,
+                            ctypes.c_uint64, c_void_p]),
+    "srb_em_partial_floats": (c_i64, [c_int, c_int, c_int, c_int]),
     "srb_em_update": (c_int, [c_void_p, c_int, ctypes.c_uint64, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
                               c_void_p, c_void_p, ctypes.c_double, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "srb_fma_peak": (c_int, [c_int, c_int, ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_double), c_void_p]),

@@ -202,7 +202,8 @@ class IsolatedTrainer:
         self._copy_stream = torch.cuda.Stream(self.dev)
         self.off_d = torch.from_numpy(off32).to(self.dev)
         self.trans_d = torch.from_numpy(trans.astype(np.float32)).to(self.dev).contiguous()
-        self.em_partial = torch.empty(L.srb_em_parts() * self.G * self.row, dtype=torch.float32, device=self.dev)
+        self.em_partial = torch.empty(int(L.srb_em_partial_floats(W, S, self.pm.M, self.pm.D)), dtype=torch.float32,
+                                      device=self.dev)
         self.best_cost = torch.empty(max(self.B, 1), dtype=torch.float32, device=self.dev)
         return True
 
@@ -287,9 +288,10 @@ class IsolatedTrainer:
         if self.peer is not None:
             pe = self.peer
             pe.epoch += 1
-            _l.check(_l.load().srb_em_push(_l.ptr(self.em_partial), _l.load().srb_em_parts(), self.G * self.row,
-                                           _l.ptr(self.best_cost), self.B, pe.ptr_array, pe.world, pe.rank, pe.epoch,
-                                           _l.stream_ptr()))
+            pm = self.pm
+            _l.check(_l.load().srb_em_push(_l.ptr(self.em_partial), _l.load().srb_em_parts(), self.W, self.S, pm.M,
+                                           self.ncomp, pm.D, _l.ptr(self.best_cost), self.B, pe.ptr_array, pe.world,
+                                           pe.rank, pe.epoch, _l.stream_ptr()))
             return self.stats
         return self._allreduce()
 
