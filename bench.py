@@ -349,7 +349,7 @@ def bench_em(args, ctx):
         for _ in range(reps):
             ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
             ev[0].record()
-            tr.fused_pass()
+            tr.fused_pass(keep_slices=True)
             ev[1].record()
             tr.reduce()
             ev[2].record()

@@ -22,6 +22,7 @@ namespace srb {
 
 constexpr int MAX_RANKS = 8;
 constexpr int SYNC_HEADER = 256;          // bytes: 16 flags + the CTA counter
+constexpr int PUSH_MAX_PARTS = 1024;      // per-CTA slices srb_em_push can list (srb_em_parts() = 4 per SM)
 
 struct PeerBufs {
     uint8_t *buf[MAX_RANKS];
@@ -47,22 +48,46 @@ em_push_kernel(const float *__restrict__ partial, const unsigned long long *__re
     const int64_t slot_len = len + 2;
     const int64_t base = ((int64_t)(epoch & 1) * world + rank) * slot_len;
     if (blockIdx.x + 1 < gridDim.x) {
-        // 32 elements x 8 part groups per CTA: group q adds its parts in ascending order, then the 8 group sums are added
-        // in group order -- a fixed order whatever the timing.  Only slices whose CTA saw the element's word are read
-        // (mask bit), and only rows of trained components (the others were never written: 0).
+        // A CTA = 32 elements of ONE word x 8 part groups.  Warp 0 lists, in ascending order, the slices whose CTA saw the
+        // word (mask bit); group q then adds its eighth of the list in that order (4 loads in flight) and the 8 group sums
+        // are added in group order -- a fixed order whatever the timing.  Rows of untrained components were never
+        // written by anybody: 0.
+        __shared__ int list[PUSH_MAX_PARTS];
+        __shared__ int nlist;
         const int e = threadIdx.x & 31, q = threadIdx.x >> 5;
-        const int64_t i = (int64_t)blockIdx.x * 32 + e;
-        const int chunk = (nparts + 7) >> 3;
-        const int p0 = q * chunk, p1 = min(nparts, p0 + chunk);
+        const int bpw = (word_len + 31) >> 5;
+        const int w = blockIdx.x / bpw, j = (blockIdx.x - w * bpw) * 32 + e;
+        const int64_t i = (int64_t)w * word_len + j;
+        if (q == 0) {
+            int n = 0;
+            for (int p0 = 0; p0 < nparts; p0 += 32) {
+                const int p = p0 + e;
+                const bool on = p < nparts && ((mask[p] >> (w & 63)) & 1ull);
+                const unsigned b = __ballot_sync(0xffffffffu, on);
+                if (on) list[n + __popc(b & ((1u << e) - 1))] = p;
+                n += __popc(b);
+            }
+            if (e == 0) nlist = n;
+        }
+        __syncthreads();
+        const int n = nlist;
         double s = 0.0;
-        if (i < len && (int)((i / row) % M) < ncomp) {
-            const unsigned long long bit = 1ull << ((int)(i / word_len) & 63);
-            for (int p = p0; p < p1; ++p)
-                if (mask[p] & bit) s += (double)partial[(int64_t)p * len + i];
+        if (j < word_len && (int)((j / row) % M) < ncomp) {
+            int k = (int)((int64_t)n * q / 8);
+            const int k1 = (int)((int64_t)n * (q + 1) / 8);
+            for (; k + 4 <= k1; k += 4) {
+                const float a = partial[(int64_t)list[k] * len + i], b = partial[(int64_t)list[k + 1] * len + i];
+                const float c = partial[(int64_t)list[k + 2] * len + i], d = partial[(int64_t)list[k + 3] * len + i];
+                s += (double)a;
+                s += (double)b;
+                s += (double)c;
+                s += (double)d;
+            }
+            for (; k < k1; ++k) s += (double)partial[(int64_t)list[k] * len + i];
         }
         red[threadIdx.x] = s;
         __syncthreads();
-        if (q == 0 && i < len) {
+        if (q == 0 && j < word_len) {
             double t = red[e];
 #pragma unroll
             for (int k = 1; k < 8; ++k) t += red[k * 32 + e];
@@ -254,7 +279,8 @@ int srb_em_push(const float *partial, int32_t nparts, int W, int S, int M, int n
     PeerBufs P;
     for (int r = 0; r < MAX_RANKS; ++r) P.buf[r] = r < world ? static_cast<uint8_t *>(peer_bufs[r]) : nullptr;
     for (int r = 0; r < world; ++r) SRB_REQUIRE(P.buf[r], SRB_EINVAL, "srb_em_push: peer buffer %d is null", r);
-    const int grid = (int)((len + 31) / 32) + 1;
+    SRB_REQUIRE(nparts <= PUSH_MAX_PARTS, SRB_EUNSUPPORTED, "srb_em_push: more than %d slices", PUSH_MAX_PARTS);
+    const int grid = W * ((S * M * row + 31) / 32) + 1;
     const unsigned long long *mask = reinterpret_cast<const unsigned long long *>(partial + (size_t)nparts * len);
     em_push_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(partial, mask, nparts, len, S * M * row, M, ncomp, row, best_cost,
                                                             B, P, world, rank, (unsigned long long)epoch);

@@ -238,11 +238,13 @@ class IsolatedTrainer:
         self._mstep()
         return self.stats
 
-    def fused_pass(self, seg_start=None, frame_label=None, stats=True):
-        """srb_em_isolated over the shard: statistics body of self.stats (+ best_cost, optional boundaries/labels)."""
+    def fused_pass(self, seg_start=None, frame_label=None, stats=True, keep_slices=False):
+        """srb_em_isolated over the shard: statistics body of self.stats (+ best_cost, optional boundaries/labels).
+        keep_slices: leave the per-CTA slices for reduce() = srb_em_push (what em_iteration does with the peer tail)
+        instead of folding them into self.stats here."""
         pm, p = self.pm, _l.ptr
         body = self.stats[:self.G * self.row]
-        keep = stats and self.peer is not None                 # the slices stay for srb_em_push (reduce())
+        keep = stats and keep_slices and self.peer is not None
         _l.check(_l.load().srb_em_isolated(
             p(self.X), self.N, pm.D, p(self.off_d), self.B, p(self.tiles), self.ntiles, self.tile_frames, p(pm.ab),
             p(pm.c), p(pm.shift), self.W, self.S, pm.M, pm.Mp, p(self.trans_d), self.ncomp, p(pm.mu),
@@ -321,7 +323,7 @@ class IsolatedTrainer:
         """One segmental-K-means + EM pass.  Returns the device statistics buffer (last two entries: summed
         Viterbi cost and utterance count over all ranks) without synchronising."""
         if self.fused:
-            self.fused_pass()
+            self.fused_pass(keep_slices=True)
         else:
             self.align()
             self.accumulate()
