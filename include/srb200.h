@@ -353,7 +353,7 @@ int srb_em_isolated(const float *X, int64_t N, int D, const int32_t *utt_off, in
  *                   the owner exports a 64-byte handle, the peers open it (the host layer ships the handles)
  *   srb_em_sync_bytes(world, len)   size of a rank's exchange buffer for statistics of `len` doubles (W*S*M*(2D+3))
  *   srb_em_push     sums the per-CTA slices srb_em_isolated left in `partial` (call it with accumulate = -1) in a fixed
- *                   order, adds the summed best_cost and the utterance count, and stores the len+2 doubles into slot
+ *                   order, adds 16 partial sums of best_cost and the utterance count, and stores these doubles into slot
  *                   [epoch & 1][rank] of EVERY rank's buffer (peer_bufs: HOST array of `world` device pointers, entry
  *                   `rank` the own buffer), then releases flag[rank] = epoch on every peer.  epoch = 1, 2, 3, ...
  *   srb_em_update   waits until all `world` flags of the own buffer reach `epoch`, adds the slots IN RANK ORDER (all

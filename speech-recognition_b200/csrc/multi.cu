@@ -12,7 +12,7 @@
 // This replaces reduce_slices + 2 torch reductions + ncclAllReduce (143 kB: pure latency, 0.22 ms at 8 GPUs in round 1) +
 // mstep + pack + pack_tc.  With one rank it is the same two launches without peers.
 //
-// Exchange buffer of a rank (srb_em_sync_bytes): flags uint64[16] | CTA counter | slots double[2][world][len + 2].
+// Exchange buffer of a rank (srb_em_sync_bytes): flags uint64[16] | CTA counter | slots double[2][world][len + 17].
 // Flags carry the epoch (monotone), the slot halves alternate with its parity: a rank can only be one epoch ahead of a
 // peer that still reads, and then it writes the other half.
 #include "common.cuh"
@@ -22,6 +22,8 @@ namespace srb {
 
 constexpr int MAX_RANKS = 8;
 constexpr int SYNC_HEADER = 256;          // bytes: 16 flags + the CTA counter
+constexpr int COST_BLOCKS = 16;           // CTAs of srb_em_push that sum the shard's Viterbi costs (one partial each)
+constexpr int SLOT_TAIL = COST_BLOCKS + 1; // doubles after the statistics in a slot: the cost partials and the count
 constexpr int PUSH_MAX_PARTS = 1024;      // per-CTA slices srb_em_push can list (srb_em_parts() = 4 per SM)
 
 struct PeerBufs {
@@ -45,9 +47,9 @@ em_push_kernel(const float *__restrict__ partial, const unsigned long long *__re
                int word_len, int M, int ncomp, int row, const float *__restrict__ best_cost, int B, PeerBufs P, int world,
                int rank, unsigned long long epoch) {
     __shared__ double red[256];
-    const int64_t slot_len = len + 2;
+    const int64_t slot_len = len + SLOT_TAIL;
     const int64_t base = ((int64_t)(epoch & 1) * world + rank) * slot_len;
-    if (blockIdx.x + 1 < gridDim.x) {
+    if (blockIdx.x + COST_BLOCKS < gridDim.x) {
         // A CTA = 32 elements of ONE word x 8 part groups.  Warp 0 lists, in ascending order, the slices whose CTA saw the
         // word (mask bit); group q then adds its eighth of the list in that order (4 loads in flight) and the 8 group sums
         // are added in group order -- a fixed order whatever the timing.  Rows of untrained components were never
@@ -94,12 +96,12 @@ em_push_kernel(const float *__restrict__ partial, const unsigned long long *__re
             for (int r = 0; r < world; ++r) slots_of(P.buf[r])[base + i] = t;
         }
     } else {
-        // last CTA: summed Viterbi cost of the shard (fixed-shape reduction) and its utterance count
+        // the last COST_BLOCKS CTAs: Viterbi costs of a sixteenth of the shard's utterances each (fixed-shape reduction);
+        // srb_em_update adds the partials in order.  The first of them also writes the utterance count.
+        const int cb = blockIdx.x - (gridDim.x - COST_BLOCKS);
+        const int u0 = (int)((int64_t)B * cb / COST_BLOCKS), u1 = (int)((int64_t)B * (cb + 1) / COST_BLOCKS);
         double s = 0.0;
-        for (int u = threadIdx.x; u < B; u += 256) {
-            const float c = best_cost[u];
-            s += (double)c;
-        }
+        for (int u = u0 + threadIdx.x; u < u1; u += 256) s += (double)best_cost[u];
         red[threadIdx.x] = s;
         __syncthreads();
 #pragma unroll
@@ -109,8 +111,8 @@ em_push_kernel(const float *__restrict__ partial, const unsigned long long *__re
         }
         if (threadIdx.x == 0)
             for (int r = 0; r < world; ++r) {
-                slots_of(P.buf[r])[base + len] = red[0];
-                slots_of(P.buf[r])[base + len + 1] = (double)B;
+                slots_of(P.buf[r])[base + len + cb] = red[0];
+                if (cb == 0) slots_of(P.buf[r])[base + len + COST_BLOCKS] = (double)B;
             }
     }
     // every store of this CTA is visible system-wide before the CTA counts itself done; the last one raises the flags
@@ -138,7 +140,7 @@ em_update_kernel(uint8_t *__restrict__ buf, int world, unsigned long long epoch,
     __shared__ double red[4];
     __shared__ float col_s[2 * D + 8];
     const int tid = threadIdx.x;
-    const int64_t slot_len = len + 2;
+    const int64_t slot_len = len + SLOT_TAIL;
     const double *slots = slots_of(buf) + (int64_t)(epoch & 1) * world * slot_len;
     if (tid < world) {
         const unsigned long long *f = flags_of(buf) + tid;
@@ -148,10 +150,15 @@ em_update_kernel(uint8_t *__restrict__ buf, int world, unsigned long long epoch,
     __syncthreads();
     const int g = blockIdx.x;                                 // real Gaussian index, or R*M for the scalar block
     if (g == R * M) {
-        if (tid < 2) {
+        if (tid == 0) {                                       // summed Viterbi cost: ranks in order, partials in order
             double s = 0.0;
-            for (int r = 0; r < world; ++r) s += __ldcg(slots + r * slot_len + len + tid);
-            stats_out[len + tid] = s;
+            for (int r = 0; r < world; ++r)
+                for (int k = 0; k < COST_BLOCKS; ++k) s += __ldcg(slots + r * slot_len + len + k);
+            stats_out[len] = s;
+        } else if (tid == 1) {                                // utterances
+            double s = 0.0;
+            for (int r = 0; r < world; ++r) s += __ldcg(slots + r * slot_len + len + COST_BLOCKS);
+            stats_out[len + 1] = s;
         }
         return;
     }
@@ -266,7 +273,7 @@ int srb_peer_close(void *ptr) {
 
 int64_t srb_em_sync_bytes(int world, int64_t len) {
     if (world < 1 || world > MAX_RANKS || len < 0) return 0;
-    return SYNC_HEADER + (int64_t)sizeof(double) * 2 * world * (len + 2);
+    return SYNC_HEADER + (int64_t)sizeof(double) * 2 * world * (len + SLOT_TAIL);
 }
 
 int srb_em_push(const float *partial, int32_t nparts, int W, int S, int M, int ncomp, int D, const float *best_cost,
@@ -280,7 +287,7 @@ int srb_em_push(const float *partial, int32_t nparts, int W, int S, int M, int n
     for (int r = 0; r < MAX_RANKS; ++r) P.buf[r] = r < world ? static_cast<uint8_t *>(peer_bufs[r]) : nullptr;
     for (int r = 0; r < world; ++r) SRB_REQUIRE(P.buf[r], SRB_EINVAL, "srb_em_push: peer buffer %d is null", r);
     SRB_REQUIRE(nparts <= PUSH_MAX_PARTS, SRB_EUNSUPPORTED, "srb_em_push: more than %d slices", PUSH_MAX_PARTS);
-    const int grid = W * ((S * M * row + 31) / 32) + 1;
+    const int grid = W * ((S * M * row + 31) / 32) + COST_BLOCKS;
     const unsigned long long *mask = reinterpret_cast<const unsigned long long *>(partial + (size_t)nparts * len);
     em_push_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(partial, mask, nparts, len, S * M * row, M, ncomp, row, best_cost,
                                                             B, P, world, rank, (unsigned long long)epoch);
