@@ -806,6 +806,8 @@ def run_ours(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: there is no CPU path for the product arm")
     torch.cuda.set_device(local)
+    from srb200 import numa
+    cpus = numa.bind_to_gpu(local) if world > 1 else None      # pinned buffers then live on the GPU's NUMA node
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     from srb200 import engine, synth
@@ -818,6 +820,9 @@ def run_ours(args):
     ctx = {"torch": torch, "dist": dist, "engine": engine, "pm": pm, "trans": trans, "models": models, "base": base,
            "world": world, "local": local, "rank": rank, "peak_fma": peak_fma, "lib": lib_}
     common = {"n_gpus": world, "higher_is_better": True, "vs_baseline": None, "dtype": "f32", "data": "synthetic"}
+    if world > 1:
+        common["host_binding"] = (f"rank 0 bound to {len(cpus)} CPUs local to its GPU (NVML cpu affinity); every rank "
+                                  "binds likewise before it allocates pinned buffers") if cpus else "unbound"
     sub_fns = {"connected": bench_connected, "stress": bench_stress, "fb": bench_fb, "frontend": bench_frontend}
     if args.workload in sub_fns:
         line = sub_fns[args.workload](args, ctx, args.steps, max(args.warmup, 3))

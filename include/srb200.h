@@ -112,9 +112,9 @@ int srb_classify(const float *X, const int32_t *utt_off, int32_t B, int64_t N, i
  * Costs agree with srb_classify within FP32 accumulation noise (~1e-6 relative); labels are equal wherever the two
  * best words differ by more than that. */
 int64_t srb_tc_model_floats(int R, int Mp, int D);
-/* diagnostics: with a device buffer of int64[64][10] set, CTA 0 of every following srb_classify_tc launch stamps
- * clock64 at its pipeline events (score_tc.cu, TC_STAMP) for its first 64 tiles; NULL (the default) turns it off. */
-int srb_tc_set_timeline(int64_t *device_buf);
+/* diagnostics: srb_classify_tc with a caller-owned device buffer timeline int64[64][10] (or NULL): CTA 0 stamps clock64
+ * at its pipeline events (score_tc.cu, TC_STAMP) for its first 64 tiles.  An argument, not library state: the library
+ * keeps no hidden global state and every entry point is re-entrant per stream. */
 int srb_pack_model_tc(const float *ab, const float *c, int R, int Mp, int D, float *tcb, void *stream);
 int srb_classify_tc_supported(int D, int W, int S, int Mp);
 /* The scorer alone on the same kernel: E[n, r] = states[r].evaluate(X[n]) like srb_gmm_score (E only).  chunk_off
@@ -126,6 +126,9 @@ int srb_gmm_score_tc(const float *X, int64_t N, int D, const float *tcb, const f
 int srb_classify_tc(const float *X, const int32_t *utt_off, int32_t B, int64_t N, int D, const float *tcb,
                     const float *shift, int W, int S, int Mp, const float *trans, float *final,
                     int32_t *label, void *stream);
+int srb_classify_tc_timeline(const float *X, const int32_t *utt_off, int32_t B, int64_t N, int D, const float *tcb,
+                             const float *shift, int W, int S, int Mp, const float *trans, float *final,
+                             int32_t *label, int64_t *timeline, void *stream);
 
 
 /* ---- K2: batched Viterbi over state graphs with non-emitting states ------------------------------

@@ -35,7 +35,7 @@ constexpr int TC_BAR_FULL = 1, TC_BAR_FREE_A = 3, TC_BAR_FREE_B = 5;   // named 
 constexpr int TC_NMAX = 256;           // Gaussian columns of one MMA
 constexpr int TC_COL_A = 256;          // TMEM column of the A operand (accumulators sit in [0, NP))
 constexpr int TC_MP = 4;               // Gaussians per state handled by the epilogue
-constexpr int TC_TL_TILES = 64, TC_TL_EVENTS = 10;   // srb_tc_set_timeline buffer: int64[TC_TL_TILES][TC_TL_EVENTS]
+constexpr int TC_TL_TILES = 64, TC_TL_EVENTS = 10;   // srb_classify_tc_timeline buffer: int64[TC_TL_TILES][TC_TL_EVENTS]
 constexpr float TC_CMIN = -1e30f;      // stands in for log2(0) inside the MMA
 
 __host__ __device__ constexpr int tc_kp(int D) { return (2 * D + 7) & ~7; }
@@ -112,7 +112,7 @@ classify_tc_kernel(const float *__restrict__ X, const int32_t *__restrict__ off,
     float *fin_s = xs + TC_SUB * TC_XSQ;                     // TC_SUB * TC_FIN * W
     float *Es = fin_s + TC_SUB * TC_FIN * Wc;                // TC_CHUNK * ES
     const int tid = threadIdx.x, wq = tid >> 5;
-    // diagnostics (srb_tc_set_timeline): CTA 0 stamps clock64 at its pipeline events of the first TC_TL_TILES tiles
+    // diagnostics (srb_classify_tc_timeline): CTA 0 stamps clock64 at its pipeline events of the first TC_TL_TILES tiles
     const bool tl_on = timeline != nullptr && blockIdx.x == 0 && (tid & 31) == 0;
 #define TC_STAMP(j, k) do { if (tl_on && (j) < TC_TL_TILES) timeline[(j) * TC_TL_EVENTS + (k)] = clock64(); } while (0)
 
@@ -365,14 +365,7 @@ static size_t classify_tc_smem_bytes(int W, int S, int NP, int D, bool scorer = 
 
 using namespace srb;
 
-static long long *g_tc_timeline = nullptr;
-
 extern "C" {
-
-int srb_tc_set_timeline(int64_t *device_buf) {
-    g_tc_timeline = reinterpret_cast<long long *>(device_buf);
-    return SRB_OK;
-}
 
 int64_t srb_tc_model_floats(int R, int Mp, int D) {
     if (R <= 0 || Mp <= 0 || (Mp & 3) || D <= 0 || tc_np(R, Mp) > TC_NMAX) return 0;
@@ -402,6 +395,12 @@ int srb_classify_tc_supported(int D, int W, int S, int Mp) {
 int srb_classify_tc(const float *X, const int32_t *utt_off, int32_t B, int64_t N, int D, const float *tcb,
                     const float *shift, int W, int S, int Mp, const float *trans, float *final_cost, int32_t *label,
                     void *stream) {
+    return srb_classify_tc_timeline(X, utt_off, B, N, D, tcb, shift, W, S, Mp, trans, final_cost, label, nullptr, stream);
+}
+
+int srb_classify_tc_timeline(const float *X, const int32_t *utt_off, int32_t B, int64_t N, int D, const float *tcb,
+                             const float *shift, int W, int S, int Mp, const float *trans, float *final_cost,
+                             int32_t *label, int64_t *timeline, void *stream) {
     SRB_REQUIRE(((X && final_cost) || B == 0 || N == 0) && utt_off && tcb && shift && trans, SRB_EINVAL,
                 "srb_classify_tc: null pointer");
     SRB_REQUIRE(B >= 0 && N >= 0, SRB_EINVAL, "srb_classify_tc: bad sizes");
@@ -419,7 +418,8 @@ int srb_classify_tc(const float *X, const int32_t *utt_off, int32_t B, int64_t N
     const int grid = (int)(want < sms ? want : sms);
     SRB_CUDA(cudaFuncSetAttribute(classify_tc_kernel<39>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
     classify_tc_kernel<39><<<grid, TC_NT, bytes, (cudaStream_t)stream>>>(
-        X, utt_off, B, N, reinterpret_cast<const uint32_t *>(tcb), shift, W, S, NP, trans, final_cost, label, nullptr, 0, g_tc_timeline);
+        X, utt_off, B, N, reinterpret_cast<const uint32_t *>(tcb), shift, W, S, NP, trans, final_cost, label, nullptr, 0,
+        reinterpret_cast<long long *>(timeline));
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }

@@ -22,7 +22,6 @@ SIGNATURES = {
     "srb_classify": (c_int, [c_void_p, c_void_p, c_i32, c_i64, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int,
                              c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "srb_tc_model_floats": (c_i64, [c_int, c_int, c_int]),
-    "srb_tc_set_timeline": (c_int, [c_void_p]),
     "srb_pack_model_tc": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "srb_gmm_score_tc_supported": (c_int, [c_int, c_int, c_int]),
     "srb_gmm_score_tc": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_void_p, c_int, c_int, c_void_p, c_i32, c_void_p,
@@ -36,6 +35,8 @@ SIGNATURES = {
     "srb_classify_tc_supported": (c_int, [c_int, c_int, c_int, c_int]),
     "srb_classify_tc": (c_int, [c_void_p, c_void_p, c_i32, c_i64, c_int, c_void_p, c_void_p, c_int, c_int,
                                 c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "srb_classify_tc_timeline": (c_int, [c_void_p, c_void_p, c_i32, c_i64, c_int, c_void_p, c_void_p, c_int, c_int,
+                                         c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "srb_viterbi_graph": (c_int, [c_void_p, c_i64, c_void_p, c_i32] + [c_void_p] * 11 + [c_i32] + [c_void_p] * 11),
     "srb_dtw_beam": (c_int, [c_void_p, c_i64, c_void_p, c_i32, c_void_p, c_i32, c_i32] + [c_void_p] * 8),
     "srb_viterbi_banded": (c_int, [c_void_p, c_i64, c_void_p, c_i32] + [c_void_p] * 16 + [c_i32] + [c_void_p] * 11),

@@ -1,4 +1,4 @@
-"""Pipeline timeline of the tensor-core classifier (srb_tc_set_timeline): per tile, cycles of CTA 0's events relative to
+"""Pipeline timeline of the tensor-core classifier (srb_classify_tc_timeline): per tile, cycles of CTA 0's events relative to
 the MMA issue of that tile.  Run on a B200:  python tools/tc_timeline.py"""
 import os
 import sys
@@ -18,10 +18,13 @@ Xd, offd = engine.as_frames(X), engine.as_offsets(off)
 buf = torch.zeros((64, 10), dtype=torch.int64, device="cuda")
 for _ in range(3):
     engine.classify(Xd, offd, pm, trans, W, S, tensor=True)
-_l.check(_l.load().srb_tc_set_timeline(buf.data_ptr()))
-engine.classify(Xd, offd, pm, trans, W, S, tensor=True)
+B = offd.numel() - 1
+final = torch.empty((B, W), dtype=torch.float32, device="cuda")
+label = torch.empty(B, dtype=torch.int32, device="cuda")
+_l.check(_l.load().srb_classify_tc_timeline(_l.ptr(Xd), _l.ptr(offd), B, Xd.shape[0], pm.D, _l.ptr(pm.tcb), _l.ptr(pm.shift),
+                                            W, S, pm.Mp, _l.ptr(trans), _l.ptr(final), _l.ptr(label), _l.ptr(buf),
+                                            _l.stream_ptr()))
 torch.cuda.synchronize()
-_l.check(_l.load().srb_tc_set_timeline(None))
 t = buf.cpu().numpy()
 names = ["mma:AR", "mma:DF", "mma:commit", "scoreA:HB", "scoreA:end", "vit:prep0", "vit:prep1", "vit:dp0", "vit:dp1", "scoreB:end"]
 print("tile  period | " + "  ".join(f"{n:>10}" for n in names))
