@@ -12,6 +12,8 @@
 // that  var = S2/S0 - (S1/S0)^2  does not cancel in FP32:  S0 = sum g, S1 = sum g (x - shift), S2 = sum g (x - shift)^2.
 // Row layout of one group in every buffer:  [S0, S1[0..D), S2[0..D), count, loglik]  = 2*D + 3 values
 // (count / loglik: frames and summed log-likelihood of the state, kept on its component 0 only).
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace srb {
@@ -295,6 +297,161 @@ gmm_stats_soft_kernel(const float *__restrict__ X, int64_t row0, int64_t nrows, 
     }
 }
 
+// Register form of the same kernel for models of at most SS states (everything HMM.fit builds): the lane that owns
+// component m and dimensions dl, dl + LPC, ... keeps the moments of ALL states in registers (SS x (2 * KD + 2) of them),
+// and the loop over the states with gamma > gmin is unrolled with warp-uniform predicates, so the per-frame read-modify-
+// write of a private shared-memory block (two thirds of the old kernel's instructions, and the 11 KB per warp that capped
+// it at 16 latency-bound warps per SM) is gone.  The registers are folded into ONE shared block per CTA, warp after warp
+// in a fixed order, every SOFT_FLUSH chunks (bounds the FP32 accumulation length) and at the end; the block goes to the
+// CTA's private global slice as before.  Same arithmetic per (frame, state, component) as gmm_stats_soft_kernel.
+constexpr int SOFT_FLUSH = 128;    // chunks of SCH_SOFT frames a warp accumulates in registers between two folds
+
+template <int NCP, int SS, int KD, int OCC>
+__global__ void __launch_bounds__(SW * 32, OCC)
+gmm_stats_soft_reg_kernel(const float *__restrict__ X, int64_t row0, int64_t nrows, int D, const float *__restrict__ gamma,
+                          int S, int M, int ncomp, const double *__restrict__ mu, const double *__restrict__ var,
+                          const double *__restrict__ lc, float gmin, float *__restrict__ partial) {
+    constexpr int LPC = 32 / NCP;
+    extern __shared__ float ssm[];
+    const int row = 2 * D + 3, GW = S * ncomp, Dp = soft_stride(D, LPC);
+    float *mean_s = ssm, *hiv_s = mean_s + GW * Dp, *lc_s = hiv_s + GW * Dp, *blk = lc_s + ((GW + 3) & ~3);   // blk[GW][row]
+    const int lane = threadIdx.x & 31, wq = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < GW * Dp; i += blockDim.x) {
+        const int gi = i / Dp, d = i - gi * Dp;
+        const size_t g = (size_t)(gi / ncomp) * M + gi % ncomp;
+        mean_s[i] = d < D ? (float)mu[g * D + d] : 0.f;
+        hiv_s[i] = d < D ? (float)(-0.5 / var[g * D + d]) : 0.f;
+    }
+    for (int i = threadIdx.x; i < GW; i += blockDim.x) lc_s[i] = (float)lc[(size_t)(i / ncomp) * M + i % ncomp];
+    for (int i = threadIdx.x; i < GW * row; i += blockDim.x) blk[i] = 0.f;
+    __syncthreads();
+    const int m = lane / LPC, dl = lane % LPC, mm = min(m, ncomp - 1);
+    const bool has = m < ncomp;
+    float a0[SS], ag[SS], a1[SS][KD], a2[SS][KD];
+#pragma unroll
+    for (int s = 0; s < SS; ++s) {
+        a0[s] = ag[s] = 0.f;
+#pragma unroll
+        for (int k = 0; k < KD; ++k) a1[s][k] = a2[s][k] = 0.f;
+    }
+    const int64_t wg = (int64_t)blockIdx.x * SW + wq, nw = (int64_t)gridDim.x * SW;
+    const int64_t nchunks = (nrows + SCH_SOFT - 1) / SCH_SOFT;
+    const int64_t iters = (nchunks + nw - 1) / nw;                          // the same for every warp of the grid
+    for (int64_t it = 0; it < iters; ++it) {
+        const int64_t c0 = (wg + it * nw) * SCH_SOFT;
+        if (c0 < nrows) {
+            const int64_t nb = row0 + c0, ne = row0 + min(nrows, c0 + SCH_SOFT);
+            float xn[KD], gn = 0.f;
+#pragma unroll
+            for (int k = 0; k < KD; ++k) xn[k] = (k * LPC + dl < D) ? X[nb * D + k * LPC + dl] : 0.f;
+            if (lane < S) gn = gamma[nb * S + lane];
+            for (int64_t n = nb; n < ne; ++n) {
+                float x[KD];
+                const float gl = gn;
+#pragma unroll
+                for (int k = 0; k < KD; ++k) x[k] = xn[k];
+                if (n + 1 < ne) {
+#pragma unroll
+                    for (int k = 0; k < KD; ++k)
+                        if (k * LPC + dl < D) xn[k] = X[(n + 1) * D + k * LPC + dl];
+                    if (lane < S) gn = gamma[(n + 1) * S + lane];
+                }
+                const unsigned todo = __ballot_sync(0xffffffffu, lane < S && gl > gmin);
+#pragma unroll
+                for (int s = 0; s < SS; ++s) {
+                    if (!((todo >> s) & 1u)) continue;                      // warp uniform
+                    const float g = __shfl_sync(0xffffffffu, gl, s);
+                    const float *mp = mean_s + (size_t)(s * ncomp + mm) * Dp + dl;
+                    const float *hp = hiv_s + (size_t)(s * ncomp + mm) * Dp + dl;
+                    float e[KD], acc = 0.f;
+#pragma unroll
+                    for (int k = 0; k < KD; ++k) {
+                        e[k] = x[k] - mp[k * LPC];                          // 0 - 0 beyond D
+                        acc = fmaf(e[k] * e[k], hp[k * LPC], acc);
+                    }
+#pragma unroll
+                    for (int d = LPC >> 1; d; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+                    const float ll = has ? acc + lc_s[s * ncomp + mm] : -CUDART_INF_F;
+                    float mx = ll;
+#pragma unroll
+                    for (int d = LPC; d < 32; d <<= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+                    const float pe = (mx > -CUDART_INF_F) ? __expf(ll - mx) : 0.f;
+                    float den = pe;
+#pragma unroll
+                    for (int d = LPC; d < 32; d <<= 1) den += __shfl_xor_sync(0xffffffffu, den, d);
+                    const float p = pe * (den > 0.f ? g / den : 0.f);
+                    a0[s] += p;
+                    ag[s] += g;
+#pragma unroll
+                    for (int k = 0; k < KD; ++k) {
+                        a1[s][k] = fmaf(p, e[k], a1[s][k]);
+                        a2[s][k] = fmaf(p * e[k], e[k], a2[s][k]);
+                    }
+                }
+            }
+        }
+        if ((it % SOFT_FLUSH) == SOFT_FLUSH - 1 || it + 1 == iters) {
+            // fold the registers into the CTA's block, warp after warp (fixed order), and start again from zero
+            for (int q = 0; q < SW; ++q) {
+                if (wq == q && has) {
+#pragma unroll
+                    for (int s = 0; s < SS; ++s) {
+                        if (s < S) {
+                            float *r = blk + (size_t)(s * ncomp + m) * row;
+                            if (dl == 0) {
+                                r[0] += a0[s];
+                                if (m == 0) r[2 * D + 1] += ag[s];
+                            }
+#pragma unroll
+                            for (int k = 0; k < KD; ++k)
+                                if (k * LPC + dl < D) {
+                                    r[1 + k * LPC + dl] += a1[s][k];
+                                    r[1 + D + k * LPC + dl] += a2[s][k];
+                                }
+                        }
+                    }
+                }
+                __syncthreads();
+            }
+#pragma unroll
+            for (int s = 0; s < SS; ++s) {
+                a0[s] = ag[s] = 0.f;
+#pragma unroll
+                for (int k = 0; k < KD; ++k) a1[s][k] = a2[s][k] = 0.f;
+            }
+        }
+    }
+    float *slice = partial + (size_t)blockIdx.x * S * M * row;
+    for (int i = threadIdx.x; i < GW * row; i += blockDim.x) {
+        const int gi = i / row, j = i - gi * row;
+        slice[(size_t)((gi / ncomp) * M + gi % ncomp) * row + j] = blk[i];
+    }
+}
+
+template <int NCP>
+static cudaError_t launch_stats_soft_reg(int grid, cudaStream_t st, const float *X, int64_t row0, int64_t nrows, int D,
+                                         const float *gamma, int S, int M, int ncomp, const double *mu, const double *var,
+                                         const double *lc, float gmin, float *partial) {
+    constexpr int LPC = 32 / NCP, KD = (39 + LPC - 1) / LPC;                 // D <= 39 + what the padding of KD*LPC allows
+    const int row = 2 * D + 3, GW = S * ncomp;
+    const size_t bytes = sizeof(float) * ((size_t)2 * GW * soft_stride(D, LPC) + ((GW + 3) & ~3) + (size_t)GW * row);
+    static const int occ = getenv("SRB_SOFT_OCC") ? atoi(getenv("SRB_SOFT_OCC")) : 1;   // CTAs per SM the registers allow
+    if (occ >= 2) {
+        cudaError_t rc = cudaFuncSetAttribute(gmm_stats_soft_reg_kernel<NCP, 8, KD, 2>,
+                                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+        if (rc != cudaSuccess) return rc;
+        gmm_stats_soft_reg_kernel<NCP, 8, KD, 2><<<grid, SW * 32, bytes, st>>>(X, row0, nrows, D, gamma, S, M, ncomp, mu, var,
+                                                                               lc, gmin, partial);
+        return cudaGetLastError();
+    }
+    cudaError_t rc = cudaFuncSetAttribute(gmm_stats_soft_reg_kernel<NCP, 8, KD, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)bytes);
+    if (rc != cudaSuccess) return rc;
+    gmm_stats_soft_reg_kernel<NCP, 8, KD, 1><<<grid, SW * 32, bytes, st>>>(X, row0, nrows, D, gamma, S, M, ncomp, mu, var, lc,
+                                                                           gmin, partial);
+    return cudaGetLastError();
+}
+
 template <int NCP>
 static cudaError_t launch_stats_soft(int grid, size_t bytes, cudaStream_t st, const float *X, int64_t row0, int64_t nrows,
                                      int D, const float *gamma, int S, int M, int ncomp, const double *mu,
@@ -495,7 +652,15 @@ int srb_gmm_stats_soft(const float *X, int64_t N, int64_t row0, int64_t nrows, i
     cudaStream_t st = (cudaStream_t)stream;
     SRB_CUDA(cudaMemsetAsync(partial, 0, sizeof(float) * len * grid, st));
     const float gm = (float)gmin;
-    if (ncp == 1)
+    if (S <= 8 && D <= (39 + lpc - 1) / lpc * lpc && ncp >= 2 && !getenv("SRB_SOFT_SMEM")) {
+        // register form: the moments of all states stay in the lanes' registers (see gmm_stats_soft_reg_kernel)
+        if (ncp == 2)
+            SRB_CUDA(launch_stats_soft_reg<2>(grid, st, X, row0, nrows, D, gamma, S, M, ncomp, mu, var, lc, gm, partial));
+        else if (ncp == 4)
+            SRB_CUDA(launch_stats_soft_reg<4>(grid, st, X, row0, nrows, D, gamma, S, M, ncomp, mu, var, lc, gm, partial));
+        else
+            SRB_CUDA(launch_stats_soft_reg<8>(grid, st, X, row0, nrows, D, gamma, S, M, ncomp, mu, var, lc, gm, partial));
+    } else if (ncp == 1)
         SRB_CUDA(launch_stats_soft<1>(grid, bytes, st, X, row0, nrows, D, gamma, S, M, ncomp, mu, var, lc, gm, partial));
     else if (ncp == 2)
         SRB_CUDA(launch_stats_soft<2>(grid, bytes, st, X, row0, nrows, D, gamma, S, M, ncomp, mu, var, lc, gm, partial));
