@@ -91,6 +91,15 @@ int64_t srb_model_blocks_floats(int R, int Mp, int D);
 int srb_pack_model_blocks(const float *ab, const float *c, int R, int Mp, int D, float *blocks, void *stream);
 int srb_gmm_best_gemm(const float *X, int64_t N, int D, const float *blocks, const float *shift, int R, int Mp,
                       float *best_cost, int32_t *best_state, void *stream);
+/* The same kernel in ROWS mode, for word-sorted corpora (HMM.fit scores each word's frames against that word's states,
+ * hmm.py:57): blocks packed with SB = the states of one word (srb_pack_model_blocks_sb; SB * Mp <= 160), tile_desc
+ * int32[ntiles][4] (device, 16-byte aligned) = {first frame, frames <= 128, block = word, 0}; every tile is scored
+ * against ITS block only and E[frame, s] = states[block * SB + s].evaluate(X[frame]) for s < SB (ldE >= SB).  One launch
+ * for all words, no sub-state scratch (the round-1 path wrote and re-read 256 B/frame of it). */
+int64_t srb_model_blocks_floats_sb(int R, int Mp, int D, int SB);
+int srb_pack_model_blocks_sb(const float *ab, const float *c, int R, int Mp, int D, int SB, float *blocks, void *stream);
+int srb_gmm_score_gemm(const float *X, int64_t N, int D, const float *blocks, const float *shift, int R, int Mp, int SB,
+                       const int32_t *tile_desc, int64_t ntiles, float *E, int64_t ldE, void *stream);
 
 /* ---- fused isolated-word classifier (core.py:79-87 over hmm.py:126-135 over decode.py:80-146) ----
  * W word models of S states each (packed model has R = W*S states, word-major); trans float[W,S,S] with

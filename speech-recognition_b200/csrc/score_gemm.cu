@@ -88,7 +88,12 @@ template <int D>
 __global__ void __launch_bounds__(GB_NT, 1)
 gmm_best_gemm_kernel(const float *__restrict__ X, int64_t N, const uint32_t *__restrict__ blocks,
                      const float *__restrict__ shift, int R, int Mp, int SB, int nblocks,
-                     float *__restrict__ best_cost, int32_t *__restrict__ best_state) {
+                     float *__restrict__ best_cost, int32_t *__restrict__ best_state,
+                     const int4 *__restrict__ tile_desc, int64_t ntiles_rows, float *__restrict__ E_out, int64_t ldE) {
+    // Two modes.  Sweep (tile_desc == NULL): tile t = frames [128 t, 128 t + 128), ALL blocks of the model stream past it,
+    // the running best state is kept.  Rows (tile_desc != NULL): tile t = {first frame, frames <= 128, block, -} scores
+    // its frames against ONE block (the states of the tile's word) and writes their costs to E_out[frame, state].
+    const bool rows = tile_desc != nullptr;
     constexpr int KP = gb_kp(D);
     constexpr uint32_t BLOCK_BYTES = 2u * KP * GB_NB * 4u;
     extern __shared__ __align__(128) uint8_t gsm[];
@@ -98,8 +103,9 @@ gmm_best_gemm_kernel(const float *__restrict__ X, int64_t N, const uint32_t *__r
     __shared__ float comb_v[GB_M];
     __shared__ int comb_s[GB_M];
     const int tid = threadIdx.x, wq = tid >> 5, lane = tid & 31;
-    const int64_t ntiles = (N + GB_M - 1) / GB_M;
+    const int64_t ntiles = rows ? ntiles_rows : (N + GB_M - 1) / GB_M;
     if ((int64_t)blockIdx.x >= ntiles) return;                // uniform: before any allocation
+    const int nb_t = rows ? 1 : nblocks;                      // blocks per tile
 
     if (wq == 0) tc::tmem_alloc<512>(&tslot);
     if (tid == 32) {
@@ -125,12 +131,13 @@ gmm_best_gemm_kernel(const float *__restrict__ X, int64_t N, const uint32_t *__r
         if (lane == 0) {
             uint32_t g = 0;
             for (int64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
-                for (int jb = 0; jb < nblocks; ++jb, ++g) {
+                const int b0 = rows ? __ldg(tile_desc + t).z : 0;
+                for (int jb = 0; jb < nb_t; ++jb, ++g) {
                     const int s = g % GB_STAGES;
                     tc::mbar_wait(&bar_empty[s], ((g / GB_STAGES) & 1) ^ 1);
                     mbar_expect_tx(&bar_full[s], BLOCK_BYTES);
                     uint8_t *dst = gsm + (size_t)s * BLOCK_BYTES;
-                    const uint8_t *src = reinterpret_cast<const uint8_t *>(blocks) + (size_t)jb * BLOCK_BYTES;
+                    const uint8_t *src = reinterpret_cast<const uint8_t *>(blocks) + (size_t)(b0 + jb) * BLOCK_BYTES;
                     bulk_g2s(dst, src, BLOCK_BYTES / 2, &bar_full[s]);
                     bulk_g2s(dst + BLOCK_BYTES / 2, src + BLOCK_BYTES / 2, BLOCK_BYTES / 2, &bar_full[s]);
                 }
@@ -144,7 +151,7 @@ gmm_best_gemm_kernel(const float *__restrict__ X, int64_t N, const uint32_t *__r
             for (int64_t t = blockIdx.x; t < ntiles; t += gridDim.x, ++lt) {
                 tc::mbar_wait(&bar_a_ready, lt & 1);
                 tc::fence_after_sync();
-                for (int jb = 0; jb < nblocks; ++jb, ++g) {
+                for (int jb = 0; jb < nb_t; ++jb, ++g) {
                     const int s = g % GB_STAGES, b = g & 1;
                     tc::mbar_wait(&bar_acc_free[b], ((g >> 1) & 1) ^ 1);   // the epilogue has drained this accumulator
                     tc::mbar_wait(&bar_full[s], (g / GB_STAGES) & 1);      // the block's bytes have landed
@@ -173,42 +180,78 @@ gmm_best_gemm_kernel(const float *__restrict__ X, int64_t N, const uint32_t *__r
         const int fl = q * 32 + lane;                         // frame of the tile = TMEM lane
         const int C = Mp >> 4;                                // 16-column loads per state
         uint32_t g = 0;
-        for (int64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
-            const int64_t f = t * GB_M + fl;
-            if (half == 0) {
-                // ---- A operand of this tile: thread = frame.  Every MMA of the previous tile has completed (this warp
-                //      saw its last accumulator full), so the operand columns are free.
-                const bool live = f < N;
-                const float *row = X + (live ? f : 0) * D;
-#pragma unroll
-                for (int k0 = 0; k0 < KP; k0 += 8) {
-                    uint32_t h[8], l[8];
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const int d = (k0 >> 1) + i;
-                        if (d < D) {
-                            const float v = live ? __ldg(row + d) - shift_s[d] : 0.f;
-                            tc::split_tf32(v * v, h[2 * i], l[2 * i]);
-                            tc::split_tf32(v, h[2 * i + 1], l[2 * i + 1]);
-                        } else {                              // k = 2*D: the constant feature, then zero padding
-                            h[2 * i] = d == D ? 0x3f800000u : 0u;
-                            h[2 * i + 1] = l[2 * i] = l[2 * i + 1] = 0u;
-                        }
-                    }
-                    tc::tmem_st8(lane_base + GB_COL_A + k0, h);
-                    tc::tmem_st8(lane_base + GB_COL_A + KP + k0, l);
-                }
-                tc::tmem_st_wait();
-                tc::fence_before_sync();
-                tc::mbar_arrive(&bar_a_ready);
+        // The frames of a tile are fetched into registers ONE TILE AHEAD (half 0: thread = frame), so that the A operand
+        // of tile t+1 is written to TMEM as soon as the last MMA of tile t has completed -- before this warp starts on
+        // tile t's last accumulator -- and the tensor core only idles for the split + tcgen05.st of one tile.
+        float xr[D];
+        auto tile_of = [&](int64_t tt, int64_t &f0, int &nf, int &blk) {
+            if (rows) {
+                const int4 d = __ldg(tile_desc + tt);
+                f0 = d.x;
+                nf = d.y;
+                blk = d.z;
+            } else {
+                f0 = tt * GB_M;
+                nf = (int)min((int64_t)GB_M, N - f0);
+                blk = 0;
             }
+        };
+        auto load_x = [&](int64_t tt) {
+            int64_t f0;
+            int nf, blk;
+            tile_of(tt, f0, nf, blk);
+            const bool live = fl < nf;
+            const float *row = X + (live ? f0 + fl : 0) * D;
+#pragma unroll
+            for (int d = 0; d < D; ++d) xr[d] = live ? __ldg(row + d) : 0.f;
+        };
+        auto build_a = [&]() {
+#pragma unroll
+            for (int k0 = 0; k0 < KP; k0 += 8) {
+                uint32_t h[8], l[8];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int d = (k0 >> 1) + i;
+                    if (d < D) {
+                        const float v = xr[d] - shift_s[d];
+                        tc::split_tf32(v * v, h[2 * i], l[2 * i]);
+                        tc::split_tf32(v, h[2 * i + 1], l[2 * i + 1]);
+                    } else {                                  // k = 2*D: the constant feature, then zero padding
+                        h[2 * i] = d == D ? 0x3f800000u : 0u;
+                        h[2 * i + 1] = l[2 * i] = l[2 * i + 1] = 0u;
+                    }
+                }
+                tc::tmem_st8(lane_base + GB_COL_A + k0, h);
+                tc::tmem_st8(lane_base + GB_COL_A + KP + k0, l);
+            }
+            tc::tmem_st_wait();
+            tc::fence_before_sync();
+            tc::mbar_arrive(&bar_a_ready);
+        };
+        if (half == 0) {
+            load_x(blockIdx.x);
+            build_a();
+            if ((int64_t)blockIdx.x + gridDim.x < ntiles) load_x((int64_t)blockIdx.x + gridDim.x);
+        }
+        for (int64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+            int64_t f0;
+            int nf, blk0;
+            tile_of(t, f0, nf, blk0);
+            const int64_t f = f0 + fl;
+            const bool live = fl < nf;
             float best = -CUDART_INF_F;                       // largest log2 sum_m w_m N_m(x) so far = smallest cost
             int bstate = 0;
-            for (int jb = 0; jb < nblocks; ++jb, ++g) {
+            for (int jb = 0; jb < nb_t; ++jb, ++g) {
                 const int b = g & 1;
-                const int nst = min(SB, R - jb * SB);
+                const int state0 = (blk0 + jb) * SB;          // first state of the block (global index)
+                const int nst = min(SB, R - state0);
                 tc::mbar_wait(&bar_acc_full[b], (g >> 1) & 1);
                 tc::fence_after_sync();
+                if (half == 0 && jb == nb_t - 1 && t + gridDim.x < ntiles) {
+                    // every MMA of this tile is done: the operand columns are free for the next tile's frames
+                    build_a();
+                    if (t + 2 * (int64_t)gridDim.x < ntiles) load_x(t + 2 * (int64_t)gridDim.x);
+                }
                 const uint32_t acc = lane_base + b * GB_NB;
                 // states s = s0, s0 + 2, ...: two 16-column loads in flight
                 const int s0 = (half ^ jb) & 1;
@@ -216,6 +259,18 @@ gmm_best_gemm_kernel(const float *__restrict__ X, int64_t N, const uint32_t *__r
                 int s = s0, ch = 0;                           // (state, chunk) of the load in va
                 if (s < nst) tc::tmem_ld16_issue(acc + s * Mp, va);
                 float M = -3e38f, S = 0.f;
+                auto finish_state = [&](int st) {
+                    const float lse = M + lg2(S);
+                    const bool ok = M > 0.5f * GB_CMIN;       // else: every Gaussian of the state has zero weight
+                    if (rows) {
+                        if (live) E_out[f * ldE + st] = ok ? -LN2_F * lse : CUDART_INF_F;
+                    } else if (ok && lse > best) {            // strict: the first (lowest) state keeps a tie
+                        best = lse;
+                        bstate = state0 + st;
+                    }
+                    M = -3e38f;
+                    S = 0.f;
+                };
                 while (s < nst) {
                     // next (state, chunk)
                     int sn = s, chn = ch + 1;
@@ -226,15 +281,7 @@ gmm_best_gemm_kernel(const float *__restrict__ X, int64_t N, const uint32_t *__r
                     tc::tmem_ld16_fence(va);
                     if (sn < nst) tc::tmem_ld16_issue(acc + sn * Mp + chn * 16, vb);
                     gb_fold16(va, M, S);
-                    if (ch == C - 1) {
-                        const float lse = M + lg2(S);
-                        if (M > 0.5f * GB_CMIN && lse > best) {          // strict: the first (lowest) state keeps a tie
-                            best = lse;
-                            bstate = jb * SB + s;
-                        }
-                        M = -3e38f;
-                        S = 0.f;
-                    }
+                    if (ch == C - 1) finish_state(s);
                     s = sn;
                     ch = chn;
                     if (s >= nst) break;
@@ -248,15 +295,7 @@ gmm_best_gemm_kernel(const float *__restrict__ X, int64_t N, const uint32_t *__r
                     tc::tmem_ld16_fence(vb);
                     if (sn < nst) tc::tmem_ld16_issue(acc + sn * Mp + chn * 16, va);
                     gb_fold16(vb, M, S);
-                    if (ch == C - 1) {
-                        const float lse = M + lg2(S);
-                        if (M > 0.5f * GB_CMIN && lse > best) {
-                            best = lse;
-                            bstate = jb * SB + s;
-                        }
-                        M = -3e38f;
-                        S = 0.f;
-                    }
+                    if (ch == C - 1) finish_state(s);
                     s = sn;
                     ch = chn;
                 }
@@ -264,6 +303,7 @@ gmm_best_gemm_kernel(const float *__restrict__ X, int64_t N, const uint32_t *__r
                 __syncwarp();
                 if (lane == 0) tc::mbar_arrive(&bar_acc_free[b]);
             }
+            if (rows) continue;
             // ---- merge the two halves of the lane quarter (ties: the lower state index, i.e. the first minimum)
             if (half == 1) {
                 comb_v[fl] = best;
@@ -277,7 +317,7 @@ gmm_best_gemm_kernel(const float *__restrict__ X, int64_t N, const uint32_t *__r
                     best = ov;
                     bstate = os;
                 }
-                if (f < N) {
+                if (live) {
                     if (best_cost) best_cost[f] = best > -CUDART_INF_F ? -LN2_F * best : CUDART_INF_F;
                     if (best_state) best_state[f] = bstate;
                 }
@@ -310,15 +350,45 @@ int64_t srb_model_blocks_floats(int R, int Mp, int D) {
     return (int64_t)((R + SB - 1) / SB) * 2 * gb_kp(D) * GB_NB;
 }
 
-int srb_pack_model_blocks(const float *ab, const float *c, int R, int Mp, int D, float *blocks, void *stream) {
+int64_t srb_model_blocks_floats_sb(int R, int Mp, int D, int SB) {
+    if (!srb_gmm_best_gemm_supported(D, R, Mp) || SB < 1 || SB * Mp > GB_NB) return 0;
+    return (int64_t)((R + SB - 1) / SB) * 2 * gb_kp(D) * GB_NB;
+}
+
+static int pack_blocks(const float *ab, const float *c, int R, int Mp, int D, int SB, float *blocks, void *stream) {
     SRB_REQUIRE(ab && c && blocks, SRB_EINVAL, "srb_pack_model_blocks: null pointer");
-    SRB_REQUIRE(srb_gmm_best_gemm_supported(D, R, Mp), SRB_EUNSUPPORTED,
-                "srb_pack_model_blocks: D=%d, %d Gaussians per state not covered (D = 39, Mp a multiple of 16 up to %d)", D,
-                Mp, GB_NB);
+    SRB_REQUIRE(srb_gmm_best_gemm_supported(D, R, Mp) && SB >= 1 && SB * Mp <= GB_NB, SRB_EUNSUPPORTED,
+                "srb_pack_model_blocks: D=%d, %d Gaussians per state, %d states per block not covered (D = 39, Mp a multiple "
+                "of 16, at most %d columns per block)", D, Mp, SB, GB_NB);
     SRB_REQUIRE(((uintptr_t)blocks & 15) == 0, SRB_EINVAL, "srb_pack_model_blocks: blocks must be 16-byte aligned");
-    const int SB = gb_states_per_block(Mp), nb = (R + SB - 1) / SB, KP = gb_kp(D);
+    const int nb = (R + SB - 1) / SB, KP = gb_kp(D);
     dim3 grid((KP * GB_NB + 255) / 256, nb);
     pack_blocks_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(ab, c, R, Mp, D, SB, KP, reinterpret_cast<uint32_t *>(blocks));
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+int srb_pack_model_blocks(const float *ab, const float *c, int R, int Mp, int D, float *blocks, void *stream) {
+    return pack_blocks(ab, c, R, Mp, D, gb_states_per_block(Mp > 0 ? Mp : 16), blocks, stream);
+}
+
+int srb_pack_model_blocks_sb(const float *ab, const float *c, int R, int Mp, int D, int SB, float *blocks, void *stream) {
+    return pack_blocks(ab, c, R, Mp, D, SB, blocks, stream);
+}
+
+static int gemm_launch(const float *X, int64_t N, int D, const float *blocks, const float *shift, int R, int Mp, int SB,
+                       float *best_cost, int32_t *best_state, const int32_t *tile_desc, int64_t ntiles_rows, float *E,
+                       int64_t ldE, void *stream) {
+    const int sms = sm_count();
+    SRB_REQUIRE(sms > 0, SRB_ENODEVICE, "no CUDA device");
+    const int nb = (R + SB - 1) / SB;
+    const size_t bytes = (size_t)GB_STAGES * 2 * gb_kp(D) * GB_NB * 4;
+    const int64_t ntiles = tile_desc ? ntiles_rows : (N + GB_M - 1) / GB_M;
+    const int grid = (int)(ntiles < sms ? ntiles : sms);
+    SRB_CUDA(cudaFuncSetAttribute(gmm_best_gemm_kernel<39>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    gmm_best_gemm_kernel<39><<<grid, GB_NT, bytes, (cudaStream_t)stream>>>(
+        X, N, reinterpret_cast<const uint32_t *>(blocks), shift, R, Mp, SB, nb, best_cost, best_state,
+        reinterpret_cast<const int4 *>(tile_desc), ntiles_rows, E, ldE);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }
@@ -332,17 +402,20 @@ int srb_gmm_best_gemm(const float *X, int64_t N, int D, const float *blocks, con
                 "srb_gmm_best_gemm: D=%d, %d Gaussians per state not covered (D = 39, Mp a multiple of 16 up to %d); use "
                 "srb_gmm_score", D, Mp, GB_NB);
     SRB_REQUIRE(((uintptr_t)blocks & 15) == 0, SRB_EINVAL, "srb_gmm_best_gemm: blocks must be 16-byte aligned");
-    const int sms = sm_count();
-    SRB_REQUIRE(sms > 0, SRB_ENODEVICE, "no CUDA device");
-    const int SB = gb_states_per_block(Mp), nb = (R + SB - 1) / SB;
-    const size_t bytes = (size_t)GB_STAGES * 2 * gb_kp(D) * GB_NB * 4;
-    const int64_t ntiles = (N + GB_M - 1) / GB_M;
-    const int grid = (int)(ntiles < sms ? ntiles : sms);
-    SRB_CUDA(cudaFuncSetAttribute(gmm_best_gemm_kernel<39>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-    gmm_best_gemm_kernel<39><<<grid, GB_NT, bytes, (cudaStream_t)stream>>>(
-        X, N, reinterpret_cast<const uint32_t *>(blocks), shift, R, Mp, SB, nb, best_cost, best_state);
-    SRB_CUDA(cudaGetLastError());
-    return SRB_OK;
+    return gemm_launch(X, N, D, blocks, shift, R, Mp, gb_states_per_block(Mp), best_cost, best_state, nullptr, 0, nullptr, 0,
+                       stream);
+}
+
+int srb_gmm_score_gemm(const float *X, int64_t N, int D, const float *blocks, const float *shift, int R, int Mp, int SB,
+                       const int32_t *tile_desc, int64_t ntiles, float *E, int64_t ldE, void *stream) {
+    SRB_REQUIRE(N >= 0 && ntiles >= 0, SRB_EINVAL, "srb_gmm_score_gemm: bad sizes");
+    if (N == 0 || ntiles == 0) return SRB_OK;
+    SRB_REQUIRE(X && blocks && shift && tile_desc && E, SRB_EINVAL, "srb_gmm_score_gemm: null pointer");
+    SRB_REQUIRE(srb_gmm_best_gemm_supported(D, R, Mp) && SB >= 1 && SB * Mp <= GB_NB && ldE >= SB, SRB_EUNSUPPORTED,
+                "srb_gmm_score_gemm: D=%d, %d Gaussians per state, %d states per block not covered", D, Mp, SB);
+    SRB_REQUIRE(((uintptr_t)blocks & 15) == 0 && ((uintptr_t)tile_desc & 15) == 0, SRB_EINVAL,
+                "srb_gmm_score_gemm: blocks and tile_desc must be 16-byte aligned");
+    return gemm_launch(X, N, D, blocks, shift, R, Mp, SB, nullptr, nullptr, tile_desc, ntiles, E, ldE, stream);
 }
 
 }  // extern "C"

@@ -31,6 +31,10 @@ SIGNATURES = {
     "srb_model_blocks_floats": (c_i64, [c_int, c_int, c_int]),
     "srb_pack_model_blocks": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "srb_gmm_best_gemm": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "srb_model_blocks_floats_sb": (c_i64, [c_int, c_int, c_int, c_int]),
+    "srb_pack_model_blocks_sb": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "srb_gmm_score_gemm": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_i64,
+                                   c_void_p, c_i64, c_void_p]),
     "srb_neg_lse_groups": (c_int, [c_void_p, c_i64, c_int, c_int, c_void_p, c_i64, c_void_p]),
     "srb_classify_tc_supported": (c_int, [c_int, c_int, c_int, c_int]),
     "srb_classify_tc": (c_int, [c_void_p, c_void_p, c_i32, c_i64, c_int, c_void_p, c_void_p, c_int, c_int,

@@ -11,6 +11,8 @@ HBM; one `em_iteration()` is
 Utterances are sharded over ranks; the only collective is one allreduce of the float64 statistics buffer
 (`[W*S*M, 2D+3]` + total cost) per iteration, after which every rank applies the same M-step.
 """
+import os
+
 import numpy as np
 import torch
 
@@ -373,11 +375,30 @@ class BaumWelchTrainer:
         if tensor and not ok:
             raise ValueError("BaumWelchTrainer: the tensor-core scorer does not cover this model")
         self.tensor = bool(ok and (tensor or (tensor is None and self.N >= 8 * engine.TC_SCORE_MIN_FRAMES)))
-        if self.tensor:
+        use_gemm = bool(self.tensor and pm.Mp % 16 == 0 and S * pm.Mp <= 160 and
+                        L.srb_gmm_best_gemm_supported(pm.D, pm.R, pm.Mp) and not os.environ.get("SRB_BW_NO_GEMM"))
+        if self.tensor and not use_gemm:
             self.tc_floats = int(L.srb_tc_model_floats(S * self.J, 4, pm.D))
             self.tcb = torch.empty(self.W * self.tc_floats, dtype=torch.float32, device=self.dev)
             self.P = self.E if self.J == 1 else torch.empty((max(self.N, 1), S * self.J), dtype=torch.float32,
                                                             device=self.dev)
+        # one-launch tensor-core scoring (srb_gmm_score_gemm, rows mode): a word's states are one 160-column block of
+        # the persistent GEMM kernel, tiles of 128 frames never straddle words; E is written directly (no sub-state
+        # scratch, no merge pass).  Needs Mp a multiple of 16 and S * Mp <= 160.
+        self.gemm = use_gemm
+        if self.gemm:
+            self.blocks = torch.empty(int(L.srb_model_blocks_floats_sb(pm.R, pm.Mp, pm.D, S)), dtype=torch.float32,
+                                      device=self.dev)
+            descs, self.word_tiles = [], [0]
+            for w, (r0, r1) in enumerate(self.word_rows):
+                f0 = np.arange(r0, r1, 128, dtype=np.int64)
+                d = np.zeros((len(f0), 4), np.int32)
+                d[:, 0], d[:, 1], d[:, 2] = f0, np.minimum(128, r1 - f0), w
+                descs.append(d)
+                self.word_tiles.append(self.word_tiles[-1] + len(f0))
+            tiles = np.concatenate(descs) if descs else np.zeros((0, 4), np.int32)
+            self.score_tiles = torch.from_numpy(np.ascontiguousarray(tiles if len(tiles) else np.zeros((1, 4), np.int32))
+                                                ).to(self.dev)
         # [statistics | xi per edge | sum of -log Z, utterances]
         self.stats = torch.zeros(self.G * self.row + self.nnz + 2, dtype=torch.float64, device=self.dev)
         self.partial = torch.empty(L.srb_stats_parts() * S * pm.M * self.row, dtype=torch.float32, device=self.dev)
@@ -425,7 +446,18 @@ class BaumWelchTrainer:
         st = _l.stream_ptr()
         blk = S * pm.Mp * pm.D * 2
         RJ = S * self.J if self.tensor else 0
+        if self.gemm:
+            _l.check(L.srb_pack_model_blocks_sb(p(pm.ab), p(pm.c), pm.R, pm.Mp, pm.D, S, p(self.blocks), st))
+            spans = [(0, self.word_tiles[-1])] if ready is None else list(zip(self.word_tiles[:-1], self.word_tiles[1:]))
+            for k, (t0, t1) in enumerate(spans):
+                if ready is not None:
+                    torch.cuda.current_stream().wait_event(ready[k])      # this word's frames have arrived
+                if t1 > t0:
+                    _l.check(L.srb_gmm_score_gemm(p(self.X), self.N, pm.D, p(self.blocks), p(pm.shift), pm.R, pm.Mp, S,
+                                                  self.score_tiles[t0:].data_ptr(), t1 - t0, p(self.E), S, st))
         for w, (r0, r1) in enumerate(self.word_rows):
+            if self.gemm:
+                break
             if ready is not None:
                 torch.cuda.current_stream().wait_event(ready[w])
             if r1 <= r0:

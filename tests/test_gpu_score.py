@@ -178,6 +178,51 @@ def test_gmm_best_gemm(eng, R, M, N):
     assert np.array_equal(out["best_cost"].cpu().numpy(), bc) and np.array_equal(out["best_state"].cpu().numpy(), bs)
 
 
+@pytest.mark.parametrize("W,S,M", [(3, 8, 16), (11, 5, 32), (2, 3, 48), (4, 10, 16), (1, 1, 160)])
+def test_gmm_score_gemm_rows_mode(eng, W, S, M):
+    """srb_gmm_score_gemm: every word's frames against that word's states in ONE launch of the persistent GEMM kernel
+    (a word = one 160-column block, tiles of <= 128 frames that never straddle words), against the oracle's
+    GMM.evaluate and the FFMA scorer.  Ragged word blocks incl. an empty word and blocks shorter than a tile."""
+    import torch
+    from srb200 import lib as L
+    rng = np.random.default_rng(W * 100 + S)
+    R = W * S
+    mu = rng.normal(size=(R, 1, 39)) + 0.5 * rng.normal(size=(R, M, 39))
+    var = rng.uniform(0.5, 1.5, size=(R, M, 39))
+    w = rng.dirichlet(np.ones(M), size=R)
+    pm = eng.PackedModel(mu, var, w)
+    rows = [int(v) for v in rng.integers(1, 700, size=W)]
+    if W > 2:
+        rows[1] = 0                                                       # a word without utterances
+        rows[-1] = 37
+    off = np.concatenate([[0], np.cumsum(rows)])
+    N = int(off[-1])
+    X = torch.randn((N, 39), dtype=torch.float32, device="cuda", generator=torch.Generator("cuda").manual_seed(11))
+    lib = L.load()
+    blocks = torch.empty(int(lib.srb_model_blocks_floats_sb(R, pm.Mp, 39, S)), dtype=torch.float32, device="cuda")
+    L.check(lib.srb_pack_model_blocks_sb(L.ptr(pm.ab), L.ptr(pm.c), R, pm.Mp, 39, S, L.ptr(blocks), L.stream_ptr()))
+    descs = []
+    for wd in range(W):
+        for f0 in range(int(off[wd]), int(off[wd + 1]), 128):
+            descs.append([f0, min(128, int(off[wd + 1]) - f0), wd, 0])
+    tiles = torch.tensor(descs, dtype=torch.int32, device="cuda")
+    E = torch.full((N, S), -1.0, dtype=torch.float32, device="cuda")
+    L.check(lib.srb_gmm_score_gemm(L.ptr(X), N, 39, L.ptr(blocks), L.ptr(pm.shift), R, pm.Mp, S, L.ptr(tiles), len(descs),
+                                   L.ptr(E), S, L.stream_ptr()))
+    E = E.cpu().numpy()
+    ref = eng.gmm_score(X, pm, want_E=True, tensor=False)["E"].cpu().numpy()          # all states, FFMA
+    Xh = X.cpu().numpy().astype(np.float64)
+    for wd in range(W):
+        a, b = int(off[wd]), int(off[wd + 1])
+        if b == a:
+            continue
+        np.testing.assert_allclose(E[a:b], ref[a:b, wd * S:(wd + 1) * S], rtol=2e-5)
+        k = min(b - a, 40)
+        for s_ in range(S):
+            co = orc.gmm_evaluate(Xh[a:a + k], mu[wd * S + s_], var[wd * S + s_], w[wd * S + s_], log_domain=True)[0]
+            np.testing.assert_allclose(E[a:a + k, s_], co, rtol=RTOL)
+
+
 def test_gmm_best_gemm_zero_weight_and_unsupported(eng):
     """Components of weight 0 (C = -inf) contribute nothing; a state whose components all have weight 0 never wins;
     shapes the kernel is not built for are refused loudly."""
