@@ -797,19 +797,22 @@ static size_t banded1_smem_bytes(int Rmax) {
 // accuracy for paths whose cumulative cost reaches 1e4:
 //     gamma_c(r) = exp(-(alpha_hat_c(r) + beta_hat_c(r))) / sum_r(...)
 //     xi_c(o->r) = exp(-(alpha_hat_{c-1}(o) + tr + E_c(r) + beta_hat_c(r))) / sum_edges(...)
+// exp / log are the fast intrinsics (ex2.approx / lg2.approx): measured on the B200, the IEEE-accurate functions changed
+// no digit of gamma / xi (the error that mattered came from adding un-renormalised emission costs, fixed above) and
+// made the banded kernel three times slower.
 struct OnlineNegLse {   // accumulates -log(sum exp(-x_i))
     float m, s;
     __device__ __forceinline__ void reset() { m = __int_as_float(0x7f800000); s = 0.f; }
     __device__ __forceinline__ void add(float x) {
         if (x == CUDART_INF_F) return;
         if (x < m) {
-            s = s * expf(x - m) + 1.f;   // m == inf: s == 0 and exp(-inf) == 0
+            s = s * __expf(x - m) + 1.f;   // m == inf: s == 0 and exp(-inf) == 0
             m = x;
         } else {
-            s += expf(m - x);
+            s += __expf(m - x);
         }
     }
-    __device__ __forceinline__ float value() const { return s > 0.f ? m - logf(s) : CUDART_INF_F; }
+    __device__ __forceinline__ float value() const { return s > 0.f ? m - __logf(s) : CUDART_INF_F; }
 };
 
 __device__ __forceinline__ float warp_min(float v) {
@@ -905,8 +908,8 @@ forward_backward_kernel(const float *__restrict__ E, int64_t ldE, const int32_t 
         float zl = zacc.value();
         {   // merge the per-lane partial sums: -lse over lanes
             const float zm = warp_min(zl);
-            const float zs = warp_sum(zl < INF ? expf(zm - zl) : 0.f);
-            zl = (zm < INF) ? zm - logf(zs) : INF;
+            const float zs = warp_sum(zl < INF ? __expf(zm - zl) : 0.f);
+            zl = (zm < INF) ? zm - __logf(zs) : INF;
         }
         if (lane == 0 && neg_log_z) neg_log_z[u] = (zl < INF) ? scale + (double)zl : (double)INF;
         // ---- backward; colA/colB now hold beta_hat columns
@@ -924,7 +927,7 @@ forward_backward_kernel(const float *__restrict__ E, int64_t ldE, const int32_t 
             float gs = 0.f;
             for (int r = lane; r < R; r += 32) {
                 const float v = gu[(size_t)c * R + r] + bnext[r];
-                const float p = (v < INF) ? expf(-v) : 0.f;
+                const float p = (v < INF) ? __expf(-v) : 0.f;
                 bcur[r] = p;                          // scratch
                 gs += p;
             }
@@ -946,7 +949,7 @@ forward_backward_kernel(const float *__restrict__ E, int64_t ldE, const int32_t 
                 vmin = warp_min(vmin);                 // E_c is not renormalised: exp(-v) alone would underflow
                 for (int j = lane; j < nnz; j += 32) {
                     const float v = xi[j];
-                    const float p = (v < INF) ? expf(vmin - v) : 0.f;
+                    const float p = (v < INF) ? __expf(vmin - v) : 0.f;
                     xs += p;
                     xi[j] = p;                         // unnormalised, this column only (added below)
                 }
@@ -1030,7 +1033,7 @@ __device__ __forceinline__ float group_sum(float v) {
 __device__ __forceinline__ float neg_lse3(float a, float b, float c) {
     const float m = fminf(a, fminf(b, c));
     if (!(m < CUDART_INF_F)) return CUDART_INF_F;
-    return m - logf(expf(m - a) + expf(m - b) + expf(m - c));
+    return m - __logf(__expf(m - a) + __expf(m - b) + __expf(m - c));
 }
 
 template <int W>
@@ -1115,8 +1118,8 @@ forward_backward_banded_kernel(const float *__restrict__ E, int64_t ldE, const i
         {   // log Z over the end states of the last column
             const float v = (is_end && T > 0) ? alpha : INF;
             const float zm = group_min<W>(v);
-            const float zs = group_sum<W>(v < INF ? expf(zm - v) : 0.f);
-            const float zl = (zm < INF) ? zm - logf(zs) : INF;
+            const float zs = group_sum<W>(v < INF ? __expf(zm - v) : 0.f);
+            const float zl = (zm < INF) ? zm - __logf(zs) : INF;
             if (valid && T > 0 && sub == 0 && neg_log_z) neg_log_z[u] = (zl < INF) ? scale + (double)zl : (double)INF;
         }
         // ---- backward: gamma over alpha_hat, edge posteriors into registers
@@ -1133,7 +1136,7 @@ forward_backward_banded_kernel(const float *__restrict__ E, int64_t ldE, const i
             if (act && c >= 1 && c - 1 < T) e_n = Eu[(int64_t)(c - 1) * ldE];
             // gamma_c
             const float v = al_c + beta;
-            const float p = (v < INF) ? expf(-v) : 0.f;
+            const float p = (v < INF) ? __expf(-v) : 0.f;
             const float gs = group_sum<W>(p);
             if (live && act) gu[(size_t)c * R] = p * (gs > 0.f ? 1.f / gs : 0.f);
             // xi of the arcs into column c, beta_hat_{c-1}
@@ -1144,9 +1147,9 @@ forward_backward_banded_kernel(const float *__restrict__ E, int64_t ldE, const i
             const float y2 = a2 + w, y1 = a1 + w, y0 = a0 + w;
             const float v2 = q2 + y2, v1 = q1 + y1, v0 = al_p + y0;
             const float vmin = group_min<W>(fminf(v2, fminf(v1, v0)));
-            const float r2 = (v2 < INF) ? expf(vmin - v2) : 0.f;
-            const float r1 = (v1 < INF) ? expf(vmin - v1) : 0.f;
-            const float r0 = (v0 < INF) ? expf(vmin - v0) : 0.f;
+            const float r2 = (v2 < INF) ? __expf(vmin - v2) : 0.f;
+            const float r1 = (v1 < INF) ? __expf(vmin - v1) : 0.f;
+            const float r0 = (v0 < INF) ? __expf(vmin - v0) : 0.f;
             const float xs = group_sum<W>(r2 + r1 + r0);
             const float xinv = xs > 0.f ? 1.f / xs : 0.f;
             float s1 = __shfl_down_sync(0xffffffffu, y1, 1, W), s2 = __shfl_down_sync(0xffffffffu, y2, 2, W);
