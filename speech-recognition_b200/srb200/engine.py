@@ -583,6 +583,51 @@ def forward_backward(E, off, gb, utt_graph=None, want_xi=False, banded=None):
     return gamma, ws, nlz, xi
 
 
+class ForwardBackwardPlan:
+    """Pre-planned K4 launch for a fixed batch (offsets, graphs): offsets, workspace layout, the length-sorted utterance
+    order and every output buffer live on the device and are built once -- an iteration of BaumWelchTrainer then
+    enqueues the kernel without touching the host (forward_backward() re-derives all of this per call, which for 1 M
+    utterances is tens of milliseconds of host time per iteration)."""
+
+    def __init__(self, off, gb, utt_graph=None, want_xi=True):
+        if gb.n_nes_max:
+            raise ValueError("forward_backward is defined for NES-free graphs only")
+        dev = gb["emit"].device
+        self.gb = gb
+        self.off = as_offsets(off)
+        self.B = self.off.numel() - 1
+        ws, _ = _utt_layout(off, gb, utt_graph)
+        self.ws = ws
+        self.ws_d = torch.from_numpy(ws).to(dev)
+        self.ug = None if utt_graph is None else torch.as_tensor(np.asarray(utt_graph, np.int32)).to(dev)
+        self.gamma = torch.empty(max(int(ws[-1]), 1), dtype=torch.float32, device=dev)
+        self.nlz = torch.empty(max(self.B, 1), dtype=torch.float64, device=dev)
+        self.nnz_total = max(int(gb.edge_off[-1]), 1)
+        self.xi = torch.zeros(self.nnz_total, dtype=torch.float64, device=dev) if want_xi else None
+        self.xi_part = _xi_part(self.nnz_total, dev) if want_xi else None
+        self.banded = bool(gb.banded and gb.Rmax <= 32)
+        self.order = None
+        if self.banded and self.B > 1:
+            self.order = torch.argsort(self.off[1:] - self.off[:-1], descending=True, stable=True).to(torch.int32)
+
+    def run(self, E):
+        gb, L, p = self.gb, _l.load(), _l.ptr
+        if self.xi is not None:
+            self.xi.zero_()
+        if self.banded:
+            _l.check(L.srb_forward_backward_banded(
+                p(E), E.stride(0), p(self.off), self.B, p(self.ug), p(gb["g_state_off"]), p(gb["g_end_off"]), p(gb["emit"]),
+                p(gb["pred_ptr"]), p(gb["end_state"]), p(gb["band"]), p(gb["codes"]), p(self.order), gb.Rmax, p(self.ws_d),
+                p(self.gamma), p(self.nlz), p(self.xi), p(self.xi_part), self.nnz_total, _l.stream_ptr()))
+        else:
+            _l.check(L.srb_forward_backward(
+                p(E), E.stride(0), p(self.off), self.B, p(self.ug), p(gb["g_state_off"]), p(gb["g_end_off"]), p(gb["emit"]),
+                p(gb["pred_ptr"]), p(gb["pred_idx"]), p(gb["pred_cost"]), p(gb["pred_tgt"]), p(gb["succ_ptr"]),
+                p(gb["succ_idx"]), p(gb["succ_cost"]), p(gb["end_state"]), gb.Rmax, gb.NNZmax, p(self.ws_d), p(self.gamma),
+                p(self.nlz), p(self.xi), p(self.xi_part), self.nnz_total, _l.stream_ptr()))
+        return self.gamma, self.ws, self.nlz, self.xi
+
+
 # ------------------------------------------------------------------------------------------------ K5 / K6
 
 

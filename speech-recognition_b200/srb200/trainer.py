@@ -361,6 +361,7 @@ class BaumWelchTrainer:
         uptr = np.searchsorted(words, np.arange(self.W + 1), side="left")
         self.word_rows = [(int(off[uptr[w]]), int(off[uptr[w + 1]])) for w in range(self.W)]
         self._trans0 = np.array(trans, dtype=np.float64)
+        self.fb_plan = None
         self._build_graphs()
         self.E = torch.empty((max(self.N, 1), S), dtype=torch.float32, device=self.dev)
         L = _l.load()
@@ -476,8 +477,9 @@ class BaumWelchTrainer:
                 if self.J > 1:
                     _l.check(L.srb_neg_lse_groups(self.P[ra:].data_ptr(), r1 - ra, S, self.J, self.E[ra:].data_ptr(), S,
                                                   st))
-        self.gamma, _, self.nlz, self.xi = engine.forward_backward(self.E, self.off, self.gb, utt_graph=self.words,
-                                                                   want_xi=True)
+        if self.fb_plan is None:                               # offsets, layout, order and buffers: once
+            self.fb_plan = engine.ForwardBackwardPlan(self.off, self.gb, utt_graph=self.words, want_xi=True)
+        self.gamma, _, self.nlz, self.xi = self.fb_plan.run(self.E)
         return self.gamma
 
     def accumulate(self):

@@ -24,3 +24,11 @@ def score():
 def fb():
     engine.forward_backward(tr.E, tr.off, tr.gb, utt_graph=tr.words, want_xi=True)
 print('score ms', t(score), 'fb ms', t(fb), 'e_step', t(tr.e_step), 'acc', t(tr.accumulate), file=sys.stderr)
+def fb_noxi():
+    engine.forward_backward(tr.E, tr.off, tr.gb, utt_graph=tr.words, want_xi=False)
+print('fb without xi ms', t(fb_noxi), file=sys.stderr)
+import torch
+offd = engine.as_offsets(tr.off)
+def sort_only():
+    torch.argsort(offd[1:] - offd[:-1], descending=True, stable=True).to(torch.int32)
+print('argsort ms', t(sort_only), file=sys.stderr)
