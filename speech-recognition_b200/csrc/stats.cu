@@ -341,51 +341,90 @@ gmm_stats_soft_reg_kernel(const float *__restrict__ X, int64_t row0, int64_t nro
         const int64_t c0 = (wg + it * nw) * SCH_SOFT;
         if (c0 < nrows) {
             const int64_t nb = row0 + c0, ne = row0 + min(nrows, c0 + SCH_SOFT);
-            float xn[KD], gn = 0.f;
+            float xn[KD], xm[KD], gn = 0.f, gm_ = 0.f;                       // the next pair of frames, fetched one step ahead
 #pragma unroll
-            for (int k = 0; k < KD; ++k) xn[k] = (k * LPC + dl < D) ? X[nb * D + k * LPC + dl] : 0.f;
-            if (lane < S) gn = gamma[nb * S + lane];
-            for (int64_t n = nb; n < ne; ++n) {
-                float x[KD];
-                const float gl = gn;
+            for (int k = 0; k < KD; ++k) {
+                xn[k] = (k * LPC + dl < D) ? X[nb * D + k * LPC + dl] : 0.f;
+                xm[k] = (nb + 1 < ne && k * LPC + dl < D) ? X[(nb + 1) * D + k * LPC + dl] : 0.f;
+            }
+            if (lane < S) {
+                gn = gamma[nb * S + lane];
+                if (nb + 1 < ne) gm_ = gamma[(nb + 1) * S + lane];
+            }
+            // TWO frames per step: neighbouring frames put their mass on (nearly) the same states, so the unrolled state
+            // loop runs over the union of their active states once, with two independent chains per lane (a state that
+            // is inactive for one of the frames contributes exact zeros: its gamma is passed as 0)
+            for (int64_t n = nb; n < ne; n += 2) {
+                float xa[KD], xb[KD];
+                const float gla = gn, glb = gm_;
 #pragma unroll
-                for (int k = 0; k < KD; ++k) x[k] = xn[k];
-                if (n + 1 < ne) {
-#pragma unroll
-                    for (int k = 0; k < KD; ++k)
-                        if (k * LPC + dl < D) xn[k] = X[(n + 1) * D + k * LPC + dl];
-                    if (lane < S) gn = gamma[(n + 1) * S + lane];
+                for (int k = 0; k < KD; ++k) {
+                    xa[k] = xn[k];
+                    xb[k] = xm[k];
                 }
-                const unsigned todo = __ballot_sync(0xffffffffu, lane < S && gl > gmin);
+                gm_ = 0.f;
+#pragma unroll
+                for (int k = 0; k < KD; ++k) {
+                    xm[k] = 0.f;
+                    if (k * LPC + dl < D) {
+                        if (n + 2 < ne) xn[k] = X[(n + 2) * D + k * LPC + dl];
+                        if (n + 3 < ne) xm[k] = X[(n + 3) * D + k * LPC + dl];
+                    }
+                }
+                if (lane < S) {
+                    if (n + 2 < ne) gn = gamma[(n + 2) * S + lane];
+                    if (n + 3 < ne) gm_ = gamma[(n + 3) * S + lane];
+                }
+                const float ga_ = gla > gmin ? gla : 0.f, gb_ = glb > gmin ? glb : 0.f;
+                const unsigned todo = __ballot_sync(0xffffffffu, lane < S && (ga_ > 0.f || gb_ > 0.f));
 #pragma unroll
                 for (int s = 0; s < SS; ++s) {
                     if (!((todo >> s) & 1u)) continue;                      // warp uniform
-                    const float g = __shfl_sync(0xffffffffu, gl, s);
+                    const float g_a = __shfl_sync(0xffffffffu, ga_, s), g_b = __shfl_sync(0xffffffffu, gb_, s);
                     const float *mp = mean_s + (size_t)(s * ncomp + mm) * Dp + dl;
                     const float *hp = hiv_s + (size_t)(s * ncomp + mm) * Dp + dl;
-                    float e[KD], acc = 0.f;
+                    float ea[KD], eb[KD], acca = 0.f, accb = 0.f;
 #pragma unroll
                     for (int k = 0; k < KD; ++k) {
-                        e[k] = x[k] - mp[k * LPC];                          // 0 - 0 beyond D
-                        acc = fmaf(e[k] * e[k], hp[k * LPC], acc);
+                        const float mk = mp[k * LPC], hk = hp[k * LPC];
+                        ea[k] = xa[k] - mk;                                 // 0 - 0 beyond D
+                        eb[k] = xb[k] - mk;
+                        acca = fmaf(ea[k] * ea[k], hk, acca);
+                        accb = fmaf(eb[k] * eb[k], hk, accb);
                     }
 #pragma unroll
-                    for (int d = LPC >> 1; d; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
-                    const float ll = has ? acc + lc_s[s * ncomp + mm] : -CUDART_INF_F;
-                    float mx = ll;
+                    for (int d = LPC >> 1; d; d >>= 1) {
+                        acca += __shfl_xor_sync(0xffffffffu, acca, d);
+                        accb += __shfl_xor_sync(0xffffffffu, accb, d);
+                    }
+                    const float lcv = lc_s[s * ncomp + mm];
+                    const float lla = has ? acca + lcv : -CUDART_INF_F, llb = has ? accb + lcv : -CUDART_INF_F;
+                    float mxa = lla, mxb = llb;
 #pragma unroll
-                    for (int d = LPC; d < 32; d <<= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, d));
-                    const float pe = (mx > -CUDART_INF_F) ? __expf(ll - mx) : 0.f;
-                    float den = pe;
+                    for (int d = LPC; d < 32; d <<= 1) {
+                        mxa = fmaxf(mxa, __shfl_xor_sync(0xffffffffu, mxa, d));
+                        mxb = fmaxf(mxb, __shfl_xor_sync(0xffffffffu, mxb, d));
+                    }
+                    const float pea = (mxa > -CUDART_INF_F) ? __expf(lla - mxa) : 0.f;
+                    const float peb = (mxb > -CUDART_INF_F) ? __expf(llb - mxb) : 0.f;
+                    float dena = pea, denb = peb;
 #pragma unroll
-                    for (int d = LPC; d < 32; d <<= 1) den += __shfl_xor_sync(0xffffffffu, den, d);
-                    const float p = pe * (den > 0.f ? g / den : 0.f);
-                    a0[s] += p;
-                    ag[s] += g;
+                    for (int d = LPC; d < 32; d <<= 1) {
+                        dena += __shfl_xor_sync(0xffffffffu, dena, d);
+                        denb += __shfl_xor_sync(0xffffffffu, denb, d);
+                    }
+                    const float pa = pea * (dena > 0.f ? g_a / dena : 0.f);
+                    const float pb = peb * (denb > 0.f ? g_b / denb : 0.f);
+                    a0[s] += pa;
+                    a0[s] += pb;
+                    ag[s] += g_a;
+                    ag[s] += g_b;
 #pragma unroll
                     for (int k = 0; k < KD; ++k) {
-                        a1[s][k] = fmaf(p, e[k], a1[s][k]);
-                        a2[s][k] = fmaf(p * e[k], e[k], a2[s][k]);
+                        a1[s][k] = fmaf(pa, ea[k], a1[s][k]);
+                        a2[s][k] = fmaf(pa * ea[k], ea[k], a2[s][k]);
+                        a1[s][k] = fmaf(pb, eb[k], a1[s][k]);
+                        a2[s][k] = fmaf(pb * eb[k], eb[k], a2[s][k]);
                     }
                 }
             }
