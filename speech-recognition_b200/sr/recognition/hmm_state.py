@@ -47,6 +47,18 @@ class MultivariateNormal:
     def diag_cov(self):
         return _as_diag(self._cov)
 
+    def __getstate__(self):
+        """Pickles carry the dense `inv_cov` the reference's `pdf` reads (hmm_state.py:42), so a model written here can
+        be loaded AND evaluated by the reference; it is derived data and is dropped again on load."""
+        state = dict(self.__dict__)
+        state["inv_cov"] = self.inv_cov
+        return state
+
+    def __setstate__(self, state):
+        state = dict(state)
+        state.pop("inv_cov", None)
+        self.__dict__.update(state)
+
     def pdf(self, x):
         """N(x; mean, diag cov), hmm_state.py:36-45.  x: [D] (or [N, D] -> [N])."""
         x = np.asarray(x)
