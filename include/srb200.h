@@ -311,6 +311,13 @@ int srb_gmm_stats_soft(const float *X, int64_t N, int64_t row0, int64_t nrows, i
 int srb_local_dist(const float *X, int64_t N, int D, const double *Y, const double *var, int S, int kind,
                    int var_stride, float *out, int64_t ldo, int32_t *argmin_out, void *stream);
 
+/* K-means assignment for many pools in one launch (kmeans.py:180-185 for every state of every word at once): frame n
+ * belongs to pool group[n] in [0, G) (< 0: skipped, argmin -1); Y double[G*k, D] the pools' centroids, var double[G, D] the
+ * ONE variance row each pool uses for all its centroids (kmeans.py:183 passes cov[0]).  argmin_out[n] = first minimum of
+ * mahalanobis(centroid, x, var) over the pool's k centroids. */
+int srb_kmeans_assign(const float *X, int64_t N, int D, const int32_t *group, const double *Y, const double *var, int G,
+                      int k, int32_t *argmin_out, void *stream);
+
 /* M-step of GMM.em (hmm_state.py:138-148) in place on mu/var/w double (first ncomp components per state):
  * mu += S1/S0, var = S2/S0 - (S1/S0)^2 (floored at var_floor), w = S0/count. */
 int srb_mstep(const double *stats, int R, int M, int ncomp, int D, double *mu, double *var, double *w,

@@ -567,6 +567,53 @@ local_dist_kernel(const float *__restrict__ X, int64_t N, int D, const double *_
     }
 }
 
+// ---- K-means assignment for MANY pools at once (kmeans.py:180-185 for every state of every word in one launch): frame n
+// belongs to pool group[n] (< 0: skipped), whose k centroids are Y[group*k .. +k) and whose distance uses ONE variance
+// row var[group] for all centroids (kmeans.py:183 passes cov[0]).  argmin_out[n] = first minimum of
+// mahalanobis(centroid_c, x_n, var) over c (hmm_state.py:48-58); the constant term is the same for all c and dropped.
+__global__ void __launch_bounds__(SW * 32)
+kmeans_assign_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t *__restrict__ group,
+                     const double *__restrict__ Y, const double *__restrict__ var, int G, int k,
+                     int32_t *__restrict__ argmin_out) {
+    extern __shared__ float lsm[];
+    float *ys = lsm, *iv = ys + (size_t)G * k * D;                         // G*k*D centroids, G*D half inverse variances
+    for (int i = threadIdx.x; i < G * k * D; i += blockDim.x) ys[i] = (float)Y[i];
+    for (int i = threadIdx.x; i < G * D; i += blockDim.x) iv[i] = (float)(0.5 / var[i]);
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const int64_t wg = (int64_t)blockIdx.x * SW + (threadIdx.x >> 5), nw = (int64_t)gridDim.x * SW;
+    const int d0 = lane, d1 = lane + 32;
+    const bool h0 = d0 < D, h1 = d1 < D;
+    for (int64_t n = wg; n < N; n += nw) {
+        const int g = group[n];
+        if (g < 0 || g >= G) {
+            if (lane == 0) argmin_out[n] = -1;
+            continue;
+        }
+        const float xa = h0 ? X[n * D + d0] : 0.f, xb = h1 ? X[n * D + d1] : 0.f;
+        float best = CUDART_INF_F;
+        int bi = 0;
+        for (int c = 0; c < k; ++c) {
+            const float *y = ys + (size_t)(g * k + c) * D;
+            float p = 0.f;
+            if (h0) {
+                const float e = xa - y[d0];
+                p = e * e * iv[g * D + d0];
+            }
+            if (h1) {
+                const float e = xb - y[d1];
+                p = fmaf(e * e, iv[g * D + d1], p);
+            }
+            p = wsum(p);
+            if (p < best) {                // np.argmin: first minimum (kmeans.py:185); NaN centroids never win
+                best = p;
+                bi = c;
+            }
+        }
+        if (lane == 0) argmin_out[n] = bi;
+    }
+}
+
 // ---- M-step of GMM.em (hmm_state.py:138-148) from the reduced moments, for the first ncomp components of
 // every state:  mu' = mu + S1/S0;  var' = S2/S0 - (S1/S0)^2  (== sum p (x-mu')^2 / sum p);  w' = S0 / count.
 // Components with S0 == 0 are left untouched (the reference would divide by zero there).
@@ -726,6 +773,23 @@ int srb_local_dist(const float *X, int64_t N, int D, const double *Y, const doub
     if (grid > cap) grid = cap;
     local_dist_kernel<<<(int)grid, SW * 32, bytes, (cudaStream_t)stream>>>(X, N, D, Y, var, S, kind, var_stride, out,
                                                                           ldo, argmin_out);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+int srb_kmeans_assign(const float *X, int64_t N, int D, const int32_t *group, const double *Y, const double *var, int G,
+                      int k, int32_t *argmin_out, void *stream) {
+    SRB_REQUIRE(N >= 0 && D > 0 && D <= 64 && G > 0 && k > 0, SRB_EINVAL, "srb_kmeans_assign: bad sizes");
+    if (N == 0) return SRB_OK;
+    SRB_REQUIRE(X && group && Y && var && argmin_out, SRB_EINVAL, "srb_kmeans_assign: null pointer");
+    const size_t bytes = sizeof(float) * ((size_t)G * k * D + (size_t)G * D);
+    SRB_REQUIRE(bytes <= (size_t)smem_optin(), SRB_EUNSUPPORTED,
+                "srb_kmeans_assign: %d pools x %d centroids do not fit shared memory", G, k);
+    SRB_CUDA(cudaFuncSetAttribute(kmeans_assign_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    int64_t grid = (N + SW - 1) / SW;
+    const int64_t cap = (int64_t)sm_count() * 8;
+    if (grid > cap) grid = cap;
+    kmeans_assign_kernel<<<(int)grid, SW * 32, bytes, (cudaStream_t)stream>>>(X, N, D, group, Y, var, G, k, argmin_out);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }

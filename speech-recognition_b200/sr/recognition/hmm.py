@@ -124,4 +124,38 @@ def classify(models, xs):
     return costs, np.argmin(costs, axis=1)
 
 
-__all__ = ["HMM", "classify"]
+def fit_words(ys_per_word, n_segments, n_gaussians, use_em=True, seeds=None, group=None, fused_align=True):
+    """`HMM(n_segments).fit(ys, n_gaussians)` for EVERY word at once (hmm.py:57-124 per word): all words' utterances are
+    one device-resident corpus and every phase -- skmeans, binary-split K-means, per-state EM, re-alignment -- runs for
+    all states of all words together (srb200.fit.WordFitter; with torch.distributed initialised the utterances of this
+    process are its shard and the statistics are summed over the ranks).
+    ys_per_word: list (one entry per word) of lists of [T, D] utterances; seeds: optional per-word seeds of the global
+    numpy RNG, applied where a caller of the reference would seed before each word's fit.  -> list of HMM"""
+    from srb200.fit import WordFitter
+    from .hmm_state import GMM
+    from .kmeans import segment_data
+    utts = [u for ys in ys_per_word for u in ys]
+    words = np.repeat(np.arange(len(ys_per_word)), [len(ys) for ys in ys_per_word])
+    X, off = _ops.cat_frames(utts)
+    ft = WordFitter(X, off, words, len(ys_per_word), n_segments, n_gaussians, use_em=use_em, seeds=seeds, group=group,
+                    fused_align=fused_align)
+    models = ft.fit()
+    out, S = [], n_segments
+    for w, (mu, var, wt, trans) in enumerate(models):
+        m = HMM(S)
+        m.use_gmm, m.use_em = True, use_em
+        m.mu, m.sigma, m.transitions = ft.hmm_mu[w].copy(), ft.hmm_sigma[w].copy(), trans.copy()
+        m.gmm_states = []
+        for s in range(S):
+            g = GMM(m.mu[s], m.sigma[s], n_gaussians)
+            g.update_models(mu[s].copy(), var[s].copy(), wt[s].copy())
+            g.mu_old, g.sigma_old, g.w_old = ft.mu_old[w * S + s].copy(), ft.var_old[w * S + s].copy(), ft.w_old[w * S + s].copy()
+            m.gmm_states.append(g)
+        a, b = ft.word_utts[w]
+        m.segments = segment_data(ys_per_word[w], b - a, S, ft.final_starts[a:b]) if b > a else []
+        out.append(m)
+    fit_words.last = ft
+    return out
+
+
+__all__ = ["HMM", "classify", "fit_words"]

@@ -702,6 +702,20 @@ def gmm_stats(X, label, pm, ncomp, out=None, accumulate=False):
     return out
 
 
+def kmeans_assign(X, group, centroids, var0):
+    """K-means assignment of many pools at once (srb_kmeans_assign): group int32[N] (pool of every frame, < 0 = none),
+    centroids [G, k, D], var0 [G, D] (the one variance row a pool uses, kmeans.py:183).  -> int32[N] cluster (-1 = none)"""
+    X = as_frames(X)
+    dev = X.device
+    c, v = _f64(centroids, dev), _f64(var0, dev)
+    G, k, D = (int(t) for t in c.shape)
+    g = _i32(group, dev)
+    out = torch.empty(X.shape[0], dtype=torch.int32, device=dev)
+    _l.check(_l.load().srb_kmeans_assign(_l.ptr(X), X.shape[0], D, _l.ptr(g), _l.ptr(c), _l.ptr(v), G, k, _l.ptr(out),
+                                         _l.stream_ptr()))
+    return out
+
+
 def mstep(stats, pm, ncomp, var_floor=0.0):
     """In-place M-step on pm.mu / pm.var / pm.w (double), then refresh the packed fp32 copy."""
     _l.check(_l.load().srb_mstep(_l.ptr(stats), pm.R, pm.M, ncomp, pm.D, _l.ptr(pm.mu), _l.ptr(pm.var), _l.ptr(pm.w),

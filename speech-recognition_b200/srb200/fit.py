@@ -1,0 +1,323 @@
+"""Batched `HMM.fit` for ALL words of a labelled corpus (BASELINE config 2 in full: segmental K-means -> binary-split
+K-means -> per-state EM -> Viterbi re-alignment), device resident and sharded by utterance.
+
+The reference trains one word at a time and one state at a time (hmm.py:57-124): `skmeans` (kmeans.py:111-155), then per
+state `kmeans` on the x0.9 / x1.1 split centroids (kmeans.py:166-193) and `GMM.em` (hmm_state.py:122-159), then
+`align_gmm_states` (kmeans.py:196-205).  The mirror's `HMM.fit` follows it call by call (a Python loop of small launches per
+state).  Here every phase runs for all W*S states at once:
+
+    phase                      per iteration                                               exchange (N GPUs)
+    skmeans                    W x srb_local_dist + one srb_viterbi_graph + srb_group_stats  fp64 allreduce of [W*S, 2D+3]
+    K-means (per split)        srb_kmeans_assign + srb_group_stats                           fp64 allreduce of [W*S*k, 2D+3]
+    EM (per split)             srb_gmm_stats (all states, label = state)                     fp64 allreduce of [W*S*M, 2D+3]
+    re-alignment               srb_em_isolated (alignment only)                              none
+
+The statistics are summed over the ranks (`torch.distributed.all_reduce`), every rank applies the same update: the
+"local partials -> one fp64 allreduce -> replicated update" pattern of SURVEY 8e for the two phases the round-1 trainer
+left single-GPU.  What stays on the host is O(states) bookkeeping in float64: the convergence tests of the reference
+(np.allclose / np.array_equal per word or per state, with converged words / states frozen at the iteration where the
+reference's own loop would have stopped), the M-step on the 200-odd reduced rows, and the global numpy RNG stream of
+kmeans.py:171, drawn state by state in the reference's order and indexed by a frame's rank in its state's pool.
+"""
+import numpy as np
+import torch
+
+from . import engine
+from .graph import GraphBatch, StateGraph
+from .trainer import sort_by_word
+
+
+def _dist_on(group):
+    return group is not None or (torch.distributed.is_initialized() and torch.distributed.get_world_size() > 1)
+
+
+def _allreduce(t, group):
+    if _dist_on(group):
+        torch.distributed.all_reduce(t, group=group)
+    return t
+
+
+def transition_costs(n_temps, n_all, S):
+    """calc_transition_costs (kmeans.py:53-95) for uniform segment lengths without empty segments: stay / advance costs
+    from the pooled segment lengths n_all[S] of n_temps utterances; the last state stays with probability 1."""
+    tr = np.full((S, S), np.inf)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        for i in range(S):
+            n_jump = 0 if i == S - 1 else n_temps
+            if n_jump:
+                tr[i + 1, i] = -np.log(n_jump / n_all[i])
+            tr[i, i] = -np.log((n_all[i] - n_jump) / n_all[i])
+    return tr
+
+
+class WordFitter:
+    """All W word models of this rank's shard of a labelled corpus, trained together.  X [N, D] float32 (numpy or CUDA,
+    word-sorted when on the device), off [B+1], words [B]."""
+
+    def __init__(self, X, off, words, W, n_segments, n_gaussians, use_em=True, group=None, seeds=None, verbose=False,
+                 fused_align=True):
+        X, off, words, self.order = sort_by_word(X if torch.is_tensor(X) else np.asarray(X), np.asarray(off), words)
+        self.dev = engine.device()
+        self.X = engine.as_frames(X)
+        self.W, self.S, self.M, self.D = int(W), int(n_segments), int(n_gaussians), int(self.X.shape[1])
+        self.use_em, self.group, self.seeds, self.verbose = use_em, group, seeds, verbose
+        self.fused_align = fused_align
+        self.words = np.asarray(words, np.int64)
+        self.off = np.asarray(off, np.int64)
+        self.B, self.N = len(self.off) - 1, int(self.off[-1])
+        self.T = np.diff(self.off)
+        uptr = np.searchsorted(self.words, np.arange(self.W + 1), side="left")
+        self.word_utts = [(int(uptr[w]), int(uptr[w + 1])) for w in range(self.W)]
+        self.word_rows = [(int(self.off[a]), int(self.off[b])) for a, b in self.word_utts]
+        self.off_d = torch.from_numpy(self.off).to(self.dev)
+        self.T_d = torch.from_numpy(self.T).to(self.dev)
+        self.utt_of = torch.repeat_interleave(torch.arange(self.B, device=self.dev), self.T_d)        # [N]
+        self.t_in = torch.arange(self.N, device=self.dev) - self.off_d[self.utt_of]
+        self.word_of_frame = torch.from_numpy(self.words).to(self.dev)[self.utt_of]
+        self.iterations = {}
+        world = torch.distributed.get_world_size(group) if _dist_on(group) else 1
+        self.rank = torch.distributed.get_rank(group) if _dist_on(group) else 0
+        self.world = world
+
+    # ------------------------------------------------------------------------------------------ helpers
+    def _labels_from_starts(self, starts):
+        """frame -> w*S + segment for seg_starts [B, S] (segment_data's slicing, kmeans.py:41-50)."""
+        st = torch.from_numpy(np.ascontiguousarray(starts[:, 1:], dtype=np.int64)).to(self.dev)       # [B, S-1]
+        seg = (self.t_in[:, None] >= st[self.utt_of]).sum(dim=1)
+        return (self.word_of_frame * self.S + seg).to(torch.int32)
+
+    def _moments(self, label, K, shift=None, unbiased=True):
+        """(count[K], mean[K, D], var[K, D]) of the frames of every group over ALL ranks; two passes (mean, then moments
+        about it) unless a shift is given."""
+        D = self.D
+        if shift is None:
+            z = torch.zeros((K, D), dtype=torch.float64, device=self.dev)
+            st = _allreduce(engine.group_stats(self.X, label, K, z), self.group)
+            shift_t = st[:, 1:1 + D] / st[:, :1]
+            shift_t = torch.where(torch.isfinite(shift_t), shift_t, torch.zeros_like(shift_t))
+        else:
+            shift_t = torch.as_tensor(shift, dtype=torch.float64).to(self.dev).reshape(K, D)
+        st = _allreduce(engine.group_stats(self.X, label, K, shift_t), self.group)
+        with np.errstate(all="ignore"):
+            cnt, mean, var = engine.moments_from_stats(st, shift_t, D, unbiased=unbiased)
+        return cnt.cpu().numpy(), mean.cpu().numpy(), var.cpu().numpy()
+
+    def _global_sum(self, a):
+        t = torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(self.dev)
+        return _allreduce(t, self.group).cpu().numpy()
+
+    # ------------------------------------------------------------------------------------------ phase 1: skmeans
+    def skmeans(self, max_iteration=1000):
+        """kmeans.py:111-155 for every word at once -> (mu [W,S,D], var [W,S,D], trans [W,S,S], seg_starts [B,S])."""
+        W, S = self.W, self.S
+        if (self.T < 5).any():
+            raise NameError('template is too small, cannot do dtw on it')                 # kmeans.py:142-143
+        seg_len = self.T // S
+        starts = np.concatenate([np.zeros((self.B, 1), np.int64),
+                                 np.cumsum(np.repeat(seg_len[:, None], S, axis=1), axis=1)[:, :-1]], axis=1)
+        _, res, var = self._moments(self._labels_from_starts(starts), W * S)
+        res, var = res.reshape(W, S, -1), var.reshape(W, S, -1)
+        # transition costs come from the UNIFORM lengths in every iteration (A5): computed once
+        n_temps = self._global_sum(np.bincount(self.words, minlength=W).astype(np.float64))
+        n_all = self._global_sum(np.bincount(self.words, weights=seg_len.astype(np.float64), minlength=W))
+        trans = np.stack([transition_costs(n_temps[w], np.full(S, n_all[w]), S) for w in range(W)])
+        graphs = [StateGraph(trans[w], np.arange(S), end_states=[S - 1], keep_inf=True) for w in range(W)]
+        gb = GraphBatch(graphs, self.dev)
+        fl = torch.empty(max(self.N, 1), dtype=torch.int32, device=self.dev)
+        dist = torch.empty((max(self.N, 1), S), dtype=torch.float32, device=self.dev)
+        state_off = torch.from_numpy(np.arange(W, dtype=np.int64) * S).to(self.dev)
+        active = np.ones(W, bool)
+        its = np.zeros(W, np.int64)
+        for it in range(max_iteration):
+            for w, (r0, r1) in enumerate(self.word_rows):                     # Euclidean distances to the word's means
+                if r1 > r0 and active[w]:
+                    dist[r0:r1] = engine.local_dist(self.X[r0:r1], res[w])[0]
+            engine.viterbi(dist, self.off.astype(np.int32), gb, utt_graph=self.words.astype(np.int32), want_path=False,
+                           frame_label=fl)
+            lab = fl[:self.N]                                                 # graph offset + state = w*S + s
+            cnt = torch.bincount((self.utt_of * S + (lab.long() - state_off[self.word_of_frame])).clamp_(min=0),
+                                 weights=(lab >= 0).double(), minlength=self.B * S).reshape(self.B, S)
+            new_starts = np.zeros((self.B, S), np.int64)
+            new_starts[:, 1:] = np.cumsum(cnt.cpu().numpy().astype(np.int64), axis=1)[:, :-1]
+            _, new_res, new_var = self._moments(self._labels_from_starts(new_starts), W * S)
+            new_res, new_var = new_res.reshape(W, S, -1), new_var.reshape(W, S, -1)
+            for w in np.flatnonzero(active):
+                a, b = self.word_utts[w]
+                starts[a:b] = new_starts[a:b]
+                var[w] = new_var[w]
+                its[w] = it
+                if np.allclose(res[w], new_res[w]):
+                    active[w] = False                                         # `break` before res = new_res (:148-150)
+                else:
+                    res[w] = new_res[w]
+            if not active.any():
+                break
+        self.iterations["skmeans"] = its
+        self.hmm_mu, self.hmm_sigma, self.trans, self.seg_starts = res, var, trans, starts
+        return res, var, trans, starts
+
+    # ------------------------------------------------------------------------------------------ phase 2: per-state GMMs
+    def _pool_ranks(self, state):
+        """Rank of every frame inside its state's pool (segment_data order: utterance by utterance), offset by the frames
+        the lower ranks contribute to the pool.  -> (rank_in_pool int64[N], n_local[G], n_global[G], offset[G])"""
+        G = self.W * self.S
+        order = torch.argsort(state, stable=True)
+        sorted_state = state[order].long()
+        n_local = torch.bincount(sorted_state, minlength=G)
+        start = torch.cumsum(n_local, 0) - n_local
+        rank = torch.empty(self.N, dtype=torch.int64, device=self.dev)
+        rank[order] = torch.arange(self.N, device=self.dev) - start[sorted_state]
+        n_loc = n_local.cpu().numpy().astype(np.int64)
+        if self.world > 1:
+            allc = [torch.empty_like(n_local) for _ in range(self.world)]
+            torch.distributed.all_gather(allc, n_local, group=self.group)
+            allc = np.stack([c.cpu().numpy() for c in allc]).astype(np.int64)
+            offset, n_glob = allc[:self.rank].sum(axis=0), allc.sum(axis=0)
+        else:
+            offset, n_glob = np.zeros(G, np.int64), n_loc
+        return rank, n_loc, n_glob, offset
+
+    def fit_states(self, kmeans_max_iteration=1000, em_max_iteration=10000):
+        """hmm.py:97-124 for every state of every word at once (after skmeans)."""
+        W, S, M, D = self.W, self.S, self.M, self.D
+        G = W * S
+        n_splits = int(np.log(M))
+        assert n_splits > 0
+        state = self._labels_from_starts(self.seg_starts)                      # pool of every frame
+        rank, n_loc, n_glob, offset = self._pool_ranks(state)
+        mu = np.repeat(self.hmm_mu.reshape(G, 1, D), M, axis=1).copy()          # GMM.__init__: M copies (hmm_state.py:105-112)
+        var = np.repeat(self.hmm_sigma.reshape(G, 1, D), M, axis=1).copy()
+        wgt = np.full((G, M), 1.0 / M)
+        mu_old, var_old, w_old = mu.copy(), var.copy(), wgt.copy()
+        pm = engine.PackedModel(mu, var, wgt)
+        centroids = self.hmm_mu.reshape(G, 1, D).copy()
+        weights = np.repeat((1.0 / np.maximum(n_glob, 1))[:, None], M, axis=1)  # np.full(n_gaussians, 1 / n) (hmm.py:108)
+        self.iterations["kmeans"], self.iterations["em"] = [], []
+        # the global numpy RNG stream of kmeans.py:171 in the reference's order: word by word (optionally re-seeded per
+        # word, like a caller who seeds before each HMM.fit), state by state, split by split
+        draws = [[None] * G for _ in range(n_splits)]
+        for w in range(W):
+            if self.seeds is not None:
+                np.random.seed(self.seeds[w])
+            for s_ in range(S):
+                for i in range(n_splits):
+                    draws[i][w * S + s_] = np.random.randint(0, 2 ** (i + 1), int(n_glob[w * S + s_]))
+        for i in range(n_splits):
+            k = 2 ** (i + 1)
+            centroids = np.concatenate([centroids * 0.9, centroids * 1.1], axis=1)            # [G, k, D]  (hmm.py:110-112)
+            # ---- K-means: the random initial partition (kmeans.py:171) only gives the variances (A3)
+            parts = draws[i]
+            part_off = np.concatenate([[0], np.cumsum([len(p) for p in parts])])
+            flat = torch.from_numpy(np.concatenate(parts) if parts else np.zeros(0, np.int64)).to(self.dev)
+            gidx = torch.from_numpy(part_off[:-1] + offset).to(self.dev)[state.long()] + rank
+            part = flat[gidx]
+            _, _, cov = self._moments((state.long() * k + part).to(torch.int32), G * k)
+            cov = cov.reshape(G, k, D)
+            shift = centroids.copy()
+            active = n_glob > 0
+            km_its = np.zeros(G, np.int64)
+            cnt = np.zeros((G, k))
+            for it in range(max(kmeans_max_iteration, 1)):
+                am = engine.kmeans_assign(self.X, state, centroids, cov[:, 0])
+                c, new_c, _ = self._moments((state.long() * k + am.long()).to(torch.int32), G * k, shift=shift.reshape(G * k, D))
+                c, new_c = c.reshape(G, k), new_c.reshape(G, k, D)
+                for g in np.flatnonzero(active):
+                    km_its[g] = it
+                    cnt[g] = c[g]
+                    if np.array_equal(new_c[g], centroids[g]):
+                        active[g] = False
+                    else:
+                        centroids[g] = new_c[g]
+                if not active.any():
+                    break
+            self.iterations["kmeans"].append(km_its)
+            for g in range(G):                                                   # weights from cluster counts (A4, sic)
+                if n_glob[g] == 0:
+                    continue
+                present = np.flatnonzero(cnt[g] > 0)
+                c_counts = cnt[g][present]
+                for cl in present:
+                    weights[g, cl] = c_counts[cl] / n_glob[g]                    # IndexError like hmm.py:116-118 if a cluster is empty
+            mu[:, :k], var[:, :k], wgt[:, :k] = centroids, cov, weights[:, :k]
+            self._upload(pm, mu, var, wgt)
+            if self.use_em:
+                self.iterations["em"].append(self._em(pm, state, k, mu, var, wgt, mu_old, var_old, w_old, n_glob,
+                                                      em_max_iteration))
+        self.pm, self.mu, self.var, self.w = pm, mu, var, wgt
+        self.mu_old, self.var_old, self.w_old = mu_old, var_old, w_old
+        return mu, var, wgt
+
+    def _upload(self, pm, mu, var, w):
+        pm.mu.copy_(torch.from_numpy(mu))
+        pm.var.copy_(torch.from_numpy(var))
+        pm.w.copy_(torch.from_numpy(w))
+        pm.repack()
+
+    def _em(self, pm, state, k, mu, var, wgt, mu_old, var_old, w_old, n_glob, max_iteration):
+        """GMM.em (hmm_state.py:122-159) over the first k components of every state at once; a state stops at the
+        iteration where the reference's loop would (np.allclose of the new parameters with the previous ones)."""
+        G, M, D = mu.shape
+        active = n_glob > 0
+        its = np.zeros(G, np.int64)
+        row = 2 * D + 3
+        for it in range(max_iteration):
+            st = _allreduce(engine.gmm_stats(self.X, state, pm, k), self.group).cpu().numpy().reshape(G, M, row)
+            S0 = st[:, :k, 0]
+            cntg = st[:, 0, 2 * D + 1]
+            with np.errstate(all="ignore"):
+                m1 = st[:, :k, 1:1 + D] / S0[:, :, None]
+                nmu = mu[:, :k] + m1
+                nvar = st[:, :k, 1 + D:1 + 2 * D] / S0[:, :, None] - m1 * m1
+                nw = S0 / cntg[:, None]
+            ok = S0 > 0                                                           # empty components stay (DESIGN 5 ii)
+            for g in np.flatnonzero(active):
+                its[g] = it
+                o = ok[g]
+                mu[g, :k][o], var[g, :k][o] = nmu[g][o], nvar[g][o]
+                if cntg[g] > 0:
+                    wgt[g, :k][o] = nw[g][o]
+                if np.allclose(mu[g, :k], mu_old[g, :k]) and np.allclose(var[g, :k], var_old[g, :k]) and \
+                        np.allclose(wgt[g, :k], w_old[g, :k]):
+                    active[g] = False
+                    if self.verbose:
+                        print("EM converged at iteration:", it)
+                else:
+                    mu_old[g, :k], var_old[g, :k], w_old[g, :k] = mu[g, :k], var[g, :k], wgt[g, :k]
+            self._upload(pm, mu, var, wgt)
+            if not active.any():
+                break
+        return its
+
+    # ------------------------------------------------------------------------------------------ phase 3: re-alignment
+    def align(self):
+        """align_gmm_states (kmeans.py:196-205): Viterbi re-alignment with the trained states -> seg_starts [B, S]."""
+        if self.fused_align:
+            from .trainer import IsolatedTrainer
+            tr = IsolatedTrainer(self.X, self.off.astype(np.int32), self.words, self.pm, self.trans, self.S, 1, fused=None,
+                                 peer=False)
+        if self.fused_align and tr.fused:
+            seg = torch.zeros((self.B, self.S), dtype=torch.int32, device=self.dev)
+            tr.fused_pass(seg_start=seg, stats=False)
+            starts = seg.cpu().numpy().astype(np.int64)
+        else:                                                  # K1 on all states + K2 per word graph
+            E = engine.gmm_score(self.X, self.pm, want_E=True)["E"]
+            graphs = [StateGraph(self.trans[w], np.arange(self.S) + w * self.S) for w in range(self.W)]
+            fl = torch.empty(max(self.N, 1), dtype=torch.int32, device=self.dev)
+            engine.viterbi(E, self.off.astype(np.int32), GraphBatch(graphs, self.dev), utt_graph=self.words.astype(np.int32),
+                           want_path=False, frame_label=fl)
+            lab = fl[:self.N].long() - (self.word_of_frame * self.S)
+            cnt = torch.bincount((self.utt_of * self.S + lab).clamp_(min=0), weights=(lab >= 0).double(),
+                                 minlength=self.B * self.S).reshape(self.B, self.S).cpu().numpy().astype(np.int64)
+            starts = np.zeros((self.B, self.S), np.int64)
+            starts[:, 1:] = np.cumsum(cnt, axis=1)[:, :-1]
+        self.final_starts = starts
+        return starts
+
+    def fit(self):
+        """-> list of W word models (mu[S,M,D], var[S,M,D], w[S,M], trans[S,S])."""
+        self.skmeans()
+        self.fit_states()
+        self.align()
+        S = self.S
+        return [(self.mu[w * S:(w + 1) * S], self.var[w * S:(w + 1) * S], self.w[w * S:(w + 1) * S], self.trans[w])
+                for w in range(self.W)]

@@ -66,6 +66,7 @@ SIGNATURES = {
                                    c_void_p, ctypes.c_double, c_void_p, c_void_p, c_int, c_void_p]),
     "srb_local_dist": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_i64,
                                c_void_p, c_void_p]),
+    "srb_kmeans_assign": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "srb_mstep": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, ctypes.c_double,
                           c_void_p]),
     "srb_update_transitions": (c_int, [c_void_p] * 4 + [c_i32] + [c_void_p] * 4),

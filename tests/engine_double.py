@@ -327,9 +327,21 @@ def local_dist(X, Y, var=None, shared_var=False, want_dist=True, want_argmin=Fal
             torch.from_numpy(d.argmin(1).astype(np.int32)) if want_argmin else None)
 
 
+def kmeans_assign(X, group, centroids, var0):
+    X, g = _np(X, np.float64), _np(group, np.int64)
+    c, v = _np(centroids, np.float64), _np(var0, np.float64)
+    out = np.full(X.shape[0], -1, np.int32)
+    ok = (g >= 0) & (g < c.shape[0])
+    e = X[ok, None, :] - c[g[ok]]                                        # [n, k, D]
+    d = (0.5 * e * e / v[g[ok]][:, None, :]).sum(-1)
+    d = np.where(np.isnan(d), np.inf, d)
+    out[ok] = d.argmin(1)
+    return torch.from_numpy(out)
+
+
 def install(monkeypatch):
     """Replace the device entry points of srb200.engine for the duration of one test."""
     from srb200 import engine
     for name in ("device", "PackedModel", "as_frames", "as_offsets", "gmm_score", "viterbi", "classify",
-                 "group_stats", "moments_from_stats", "gmm_stats", "mstep", "local_dist", "dtw_beam"):
+                 "group_stats", "moments_from_stats", "gmm_stats", "mstep", "local_dist", "dtw_beam", "kmeans_assign"):
         monkeypatch.setattr(engine, name, globals()[name])

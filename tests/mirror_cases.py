@@ -313,6 +313,35 @@ def case_fit(rec, G):
     close(w1, z["fitk_w"])
 
 
+def case_fit_words(rec, G, fused_align=True):
+    """fit_words: the three golden words trained TOGETHER (one corpus, every phase batched over all states) must give
+    what the reference's per-word HMM.fit gave -- same pooled segments, parameters, transitions and EM stop iterations."""
+    z, zm = G["train"], G["train_multi"]
+    W = 3
+    utts = [unrag(z[f"tr_X{w}"], z[f"tr_off{w}"]) for w in range(W)]
+    models = rec.fit_words(utts, 5, 4, use_em=True, seeds=[1000 + w for w in range(W)], fused_align=fused_align)
+    ft = rec.fit_words.last
+    for w, m in enumerate(models):
+        assert np.array_equal(np.cumsum([0] + [len(s) for s in m.segments]), z[f"fit_seg_off{w}"])
+        assert np.array_equal(np.concatenate(m.segments), z[f"fit_seg_cat{w}"])
+        check_stops(ft.iterations["em"][0][w * 5:(w + 1) * 5], zm[f"fit_em_stop{w}"])
+    mu, cov, wt, tr = _dump(models)
+    close(wt, z["fit_w"], rtol=2e-3)
+    close(mu, z["fit_mu"], rtol=2e-3, atol=1e-3)
+    close(cov, z["fit_cov"], rtol=2e-3)
+    _close_trans(tr, z["fit_trans"])
+    close(np.array([m.mu for m in models]), z["fit_hmm_mu"], atol=1e-6)
+    close(np.array([m.sigma for m in models]), z["fit_hmm_sigma"])
+    ev = np.array([[models[w].evaluate(utts[v][i]) for w in range(W)] for v in range(W) for i in range(2)])
+    close(ev, z["fit_eval"], rtol=1e-3)
+    # k-means only (use_em=False): word 0 alone, the golden fitk_* run
+    mk = rec.fit_words([utts[0]], 5, 4, use_em=False, seeds=[2000], fused_align=fused_align)
+    mu1, cov1, w1, _ = _dump(mk)
+    close(mu1, z["fitk_mu"], atol=1e-6)
+    close(cov1, z["fitk_cov"])
+    close(w1, z["fitk_w"])
+
+
 def case_continuous_train(rec, G):
     z = G["train"]
     models = load_models(rec, z["fit_mu"], z["fit_cov"], z["fit_w"], z["fit_trans"])
@@ -399,4 +428,4 @@ def case_continuous_train_multi(rec, G):
 
 
 ALL = [case_emission, case_isolated_decode, case_graph_decode, case_dtw_helpers, case_dtw_beam, case_end_points, case_kmeans_em, case_skmeans,
-       case_fit, case_continuous_train, case_continuous_train_multi]
+       case_fit, case_fit_words, case_continuous_train, case_continuous_train_multi]
