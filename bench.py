@@ -84,7 +84,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--workload", default=os.environ.get("SRB_WORKLOAD", "em"),
-                    choices=["decode", "em", "connected", "stress", "fb", "frontend"])
+                    choices=["decode", "em", "connected", "stress", "fb", "fit", "frontend"])
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--scaling", default=os.environ.get("SRB_SCALING", "strong"), choices=["strong", "weak"],
                     help="em at N > 1: split 100 k utterances over the ranks (strong) or 100 k per rank (weak)")
@@ -572,6 +572,102 @@ def bench_fb(args, ctx, steps, warmup):
     return out
 
 
+# ------------------------------------------------------------------------------------------ config 2 in full: HMM.fit
+def cpu_fit(base, n_per_word, frames):
+    """oracle.hmm_fit (skmeans -> split K-means -> EM -> re-alignment, the reference's HMM.fit word by word) on a bounded
+    sample: n_per_word utterances of each of the 11 words.  One thread (the per-state loops are numpy)."""
+    from oracle import oracle as orc
+    from srb200 import synth
+    X, off, words = synth.make_utterances(2, base, n_per_word * W_, T=frames)
+    X64 = X.astype(np.float64)
+    ys = [[X64[off[u]:off[u + 1]] for u in np.flatnonzero(words == w)] for w in range(W_)]
+
+    def run():
+        for w in range(W_):
+            np.random.seed(1000 + w)
+            orc.hmm_fit(ys[w], S_, M_, use_em=True)
+
+    dt = _timed_cpu(run)
+    return X.shape[0] / dt, dt * 1e3, int(X.shape[0])
+
+
+def bench_fit(args, ctx, steps, warmup):
+    """BASELINE config 2 in full: `HMM(5).fit(ys, 4)` for the 11 words of the 100 k-utterance corpus (hmm.py:57-124:
+    skmeans to convergence, binary-split K-means, per-state EM to convergence, Viterbi re-alignment), every phase batched
+    over all 55 states (srb200.fit.WordFitter) and, at N > 1, the corpus split over the ranks with one fp64 allreduce of
+    the statistics per iteration (strong scaling).  A step is one complete fit from the raw corpus."""
+    torch, dist, engine = ctx["torch"], ctx["dist"], ctx["engine"]
+    from srb200 import synth
+    from srb200.fit import WordFitter
+    from srb200.trainer import shard_range, sort_by_word
+    rank, world = ctx["rank"], ctx["world"]
+    X, off, words = synth.make_utterances(100, ctx["base"], args.utts, T=args.frames)
+    lo, hi = shard_range(args.utts, rank, world)
+    X, words = X[int(off[lo]):int(off[hi])], words[lo:hi]
+    off = (off[lo:hi + 1] - off[lo]).astype(np.int64)
+    Xs, offs, wordss, _ = sort_by_word(X, off, words)
+    Xd = engine.as_frames(Xs)
+    N_total = args.utts * args.frames
+    seeds = [1000 + w for w in range(W_)]
+    last = {}
+
+    def step():
+        ft = WordFitter(Xd, offs, wordss, W_, S_, M_, use_em=True, seeds=seeds)
+        ft.fit()
+        last["ft"] = ft
+
+    steps, warmup = max(1, min(steps, 3)), 1
+    sampler = ClockSampler(ctx["local"]).start()
+    total_ms, per = timed_steps(step, steps, warmup, torch, dist, world)
+    clocks = sampler.stop()
+    ft = last["ft"]
+    its = {"skmeans": int(ft.iterations["skmeans"].max()) + 1,
+           "kmeans": [int(a.max()) + 1 for a in ft.iterations["kmeans"]],
+           "em": [int(a.max()) + 1 for a in ft.iterations["em"]]}
+    # phase split of one more fit, wall clock around synchronised phases
+    ph = {}
+    ft = WordFitter(Xd, offs, wordss, W_, S_, M_, use_em=True, seeds=seeds)
+    for name, fn in (("skmeans", ft.skmeans), ("kmeans+em", ft.fit_states), ("align", ft.align)):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        fn()
+        torch.cuda.synchronize()
+        ph[name] = (time.perf_counter() - t0) * 1e3
+    out = {"metric": "full-training frames/s (HMM.fit of all 11 words: skmeans + split K-means + EM + re-alignment)",
+           "value": N_total * steps / (total_ms * 1e-3), "unit": "frames/s", "ms_per_step": total_ms / steps,
+           "steps": steps, "warmup": warmup, "scaling": "strong", "iterations_to_convergence": its, "phase_ms": ph,
+           "clocks": clocks,
+           "config": {"workload": f"fit: {W_} words x {S_} states x {M_} Gaussians, D={D_}, {args.utts} utterances x "
+                                  f"{args.frames} frames in all, split over {world} GPU(s); data-dependent iteration "
+                                  "counts (np.allclose stops of the reference), listed in iterations_to_convergence",
+                      "l2": "corpus larger than L2"}}
+    if not args.no_e2e:
+        # the drop-in call: sr.recognition.fit_words on HOST lists of utterances (concatenation, H2D, training, models out)
+        import sr.recognition as rec
+        ys = [[X[off[u]:off[u + 1]] for u in np.flatnonzero(words == w)] for w in range(W_)]
+        t0 = time.perf_counter()
+        if world > 1:
+            dist.barrier()
+        models = rec.fit_words(ys, S_, M_, use_em=True, seeds=seeds)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        dt = time.perf_counter() - t0
+        out["e2e"] = {"value": N_total / dt, "unit": "frames/s", "h2d_bytes_per_step": int(X.nbytes),
+                      "d2h_bytes_per_step": int(sum((2 * D_ + 1) * M_ * 8 for m in models for _ in m.gmm_states)),
+                      "steps": 1, "seconds": dt,
+                      "api": "sr.recognition.fit_words(ys_per_word, 5, 4): host lists of [T, D] utterances in, trained HMM "
+                             "objects (GMM states, transitions, segments) out; wall clock, barrier on both sides"}
+    if rank == 0 and not args.no_cpu:
+        npw = args.cpu_utts or 40
+        v, cms, nfr = cpu_fit(ctx["base"], npw, args.frames)
+        out["cpu_baseline"] = {"value": v, "unit": "frames/s", "cores": 1, "kind": "port",
+                               "sample": f"{npw} utterances of each word ({nfr} frames), oracle.hmm_fit word by word "
+                                         f"(numpy float64 restatement of hmm.py:57-124), {cms:.0f} ms; iteration counts "
+                                         "differ with the corpus size"}
+    return out
+
+
 # ------------------------------------------------------------------------------------------ config 4: connected
 def cpu_connected(models, base, n_utts, L, T):
     """orc_decode on the 393-state word-loop graph (decode.py:80-146: T*R*R candidate scans per utterance), one utterance
@@ -823,14 +919,15 @@ def run_ours(args):
     if world > 1:
         common["host_binding"] = (f"rank 0 bound to {len(cpus)} CPUs local to its GPU (NVML cpu affinity); every rank "
                                   "binds likewise before it allocates pinned buffers") if cpus else "unbound"
-    sub_fns = {"connected": bench_connected, "stress": bench_stress, "fb": bench_fb, "frontend": bench_frontend}
+    sub_fns = {"connected": bench_connected, "stress": bench_stress, "fb": bench_fb, "frontend": bench_frontend,
+               "fit": bench_fit}
     if args.workload in sub_fns:
         line = sub_fns[args.workload](args, ctx, args.steps, max(args.warmup, 3))
         line.update(common)
-        line["scaling"] = "weak"
+        line.setdefault("scaling", "weak")
         line["config"].update({"l2": "inputs larger than L2",
                                "parallelism": f"utterance-sharded x{world}, " + (
-                                   "one fp64 allreduce of the statistics per step" if args.workload == "fb"
+                                   "one fp64 allreduce of the statistics per iteration" if args.workload in ("fb", "fit")
                                    else "no collective")})
         if rank == 0:
             emit(line)
@@ -877,7 +974,7 @@ def run_ours(args):
         t0 = time.time()
         line["decode"] = bench_decode(args, ctx, steps, warmup)
         log(f"decode sub-line {time.time() - t0:.1f} s")
-        for name in ("connected", "stress", "fb"):
+        for name in ("connected", "stress", "fb", "fit"):
             t0 = time.time()
             try:
                 line[name] = sub_fns[name](args, ctx, steps, warmup)

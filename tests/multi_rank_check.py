@@ -44,6 +44,23 @@ def run(peer, rank, world):
     return out
 
 
+def run_fit(rank, world):
+    """The complete HMM.fit of 5 words (WordFitter: skmeans, split K-means, EM, re-alignment) on this rank's shard."""
+    from srb200.fit import WordFitter
+    Wf, Bf = 5, 1500
+    _, base = synth.make_models(3, W=Wf, S=S, M=M)
+    X, off, words = synth.make_utterances(101, base, Bf, ragged=(60, 110))
+    lo, hi = shard_range(Bf, rank, world)
+    ft = WordFitter(X[int(off[lo]):int(off[hi])], off[lo:hi + 1] - off[lo], words[lo:hi], Wf, S, M, use_em=True,
+                    seeds=[50 + w for w in range(Wf)])
+    models = ft.fit()
+    starts = np.empty_like(ft.final_starts)
+    starts[ft.order] = ft.final_starts
+    return {"mu": np.stack([m[0] for m in models]), "var": np.stack([m[1] for m in models]),
+            "w": np.stack([m[2] for m in models]), "trans": np.stack([m[3] for m in models]), "starts": starts,
+            "lo": lo, "hi": hi}
+
+
 def close(a, b, tol):
     a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
     scale = np.maximum(np.abs(b).max(axis=-1, keepdims=True), 1e-30) if b.ndim > 1 else np.maximum(np.abs(b), 1e-30)
@@ -65,7 +82,9 @@ def main():
             np.testing.assert_allclose(a[4], b[4], rtol=1e-6, atol=1e-30)         # the FFMA packing
             ta, tb = a[5].reshape(2, -1).sum(axis=0), b[5].reshape(2, -1).sum(axis=0)   # tensor-core operand: hi + lo
             np.testing.assert_allclose(ta, tb, rtol=1e-6, atol=1e-30)             # (the constant's fp64 sum order differs)
-        np.savez(path, **{f"it{i}_{k}": v for i, r in enumerate(res) for k, v in zip(("stats", "mu", "var", "w"), r)})
+        fit = run_fit(0, 1)
+        np.savez(path, **{f"it{i}_{k}": v for i, r in enumerate(res) for k, v in zip(("stats", "mu", "var", "w"), r)},
+                 **{f"fit_{k}": v for k, v in fit.items()})
         print("single-rank reference written")
         return
     dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ.get("LOCAL_RANK", 0))))
@@ -86,9 +105,22 @@ def main():
             close(mu, ref[f"it{i}_mu"], 1e-5)
             close(var, ref[f"it{i}_var"], 1e-5)
             close(w, ref[f"it{i}_w"], 1e-5)
+    # (4) the sharded full fit: same models (every stop test of the reference is taken on allreduced statistics, so the
+    # ranks agree on it; against one rank the fp32 in-kernel partials may move a borderline stop by an iteration)
+    fit = run_fit(rank, world)
+    for k in ("mu", "var", "w"):
+        t = torch.from_numpy(fit[k]).cuda().view(torch.uint8).to(torch.int32)
+        lo_, hi_ = t.clone(), t.clone()
+        dist.all_reduce(lo_, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi_, op=dist.ReduceOp.MAX)
+        assert torch.equal(lo_, hi_), f"fit: replicas differ in {k}"
+        close(fit[k], ref[f"fit_{k}"], 1e-3)
+    np.testing.assert_array_equal(fit["trans"], ref["fit_trans"])
+    same = (fit["starts"] == ref["fit_starts"][fit["lo"]:fit["hi"]]).all(axis=1).mean()
+    assert same > 0.995, same
     dist.barrier()
     if rank == 0:
-        print(f"{world} ranks == 1 rank (peer-memory tail and NCCL tail)")
+        print(f"{world} ranks == 1 rank (peer-memory tail, NCCL tail, sharded HMM.fit)")
     dist.destroy_process_group()
 
 

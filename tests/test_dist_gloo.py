@@ -89,3 +89,70 @@ def test_shard_range_partitions():
             assert all(parts[i][1] == parts[i + 1][0] for i in range(world - 1))
             sizes = [b - a for a, b in parts]
             assert max(sizes) - min(sizes) <= 1
+
+
+# ---------------------------------------------------------------------------------------------- sharded HMM.fit
+class _Patch:
+    """monkeypatch stand-in for engine_double.install inside a spawned worker."""
+
+    @staticmethod
+    def setattr(obj, name, value):
+        setattr(obj, name, value)
+
+
+def _fit_corpus():
+    from srb200 import synth
+    _, base = synth.make_models(7, W=3, S=5, M=4)
+    return synth.make_utterances(8, base, 46, ragged=(30, 70))
+
+
+def _fit(X, off, words, group=None):
+    from srb200.fit import WordFitter
+    ft = WordFitter(X, off, words, 3, 5, 4, use_em=True, seeds=[11, 12, 13], fused_align=False, group=group)
+    models = ft.fit()
+    return ft, models
+
+
+def _fit_worker(rank, world, port, out):
+    sys.path[:0] = [HERE, os.path.dirname(HERE), os.path.join(os.path.dirname(HERE), "speech-recognition_b200")]
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import engine_double as ed
+    ed.install(_Patch)
+    from srb200.trainer import shard_range
+    X, off, words = _fit_corpus()
+    lo, hi = shard_range(len(words), rank, world)
+    ft, models = _fit(X[off[lo]:off[hi]], off[lo:hi + 1] - off[lo], words[lo:hi])
+    # final segment starts back in the shard's original utterance order
+    starts = np.empty_like(ft.final_starts)
+    starts[ft.order] = ft.final_starts
+    torch.save({"models": models, "starts": starts, "range": (lo, hi), "its": ft.iterations}, os.path.join(out, f"fit{rank}.pt"))
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(600)
+def test_two_rank_fit_equals_single_process(tmp_path, monkeypatch):
+    """WordFitter on two gloo ranks (each its contiguous shard of the utterances) = WordFitter on the whole corpus: same
+    pools in the same order (rank offsets into the reference's RNG draws), same stop iterations, same models."""
+    world = 2
+    mp.spawn(_fit_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    r = [torch.load(tmp_path / f"fit{k}.pt", weights_only=False) for k in range(world)]
+    import engine_double as ed
+    ed.install(monkeypatch)
+    X, off, words = _fit_corpus()
+    ft, models = _fit(X, off, words)
+    starts = np.empty_like(ft.final_starts)
+    starts[ft.order] = ft.final_starts
+    assert np.array_equal(np.concatenate([r[0]["starts"], r[1]["starts"]]), starts)
+    for k in range(world):
+        assert np.array_equal(r[k]["its"]["skmeans"], ft.iterations["skmeans"])
+        for a, b in zip(r[k]["its"]["kmeans"] + r[k]["its"]["em"], ft.iterations["kmeans"] + ft.iterations["em"]):
+            assert np.array_equal(a, b)
+        for (mu, var, w, tr), (mu1, var1, w1, tr1) in zip(r[k]["models"], models):
+            np.testing.assert_allclose(mu, mu1, rtol=1e-9, atol=1e-11)
+            np.testing.assert_allclose(var, var1, rtol=1e-8)
+            np.testing.assert_allclose(w, w1, rtol=1e-9)
+            np.testing.assert_array_equal(tr, tr1)
+    for a, b in zip(r[0]["models"], r[1]["models"]):
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y)                      # replicated updates: identical on every rank
