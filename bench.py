@@ -612,7 +612,8 @@ def bench_fit(args, ctx, steps, warmup):
     last = {}
 
     def step():
-        ft = WordFitter(Xd, offs, wordss, W_, S_, M_, use_em=True, seeds=seeds)
+        ft = WordFitter(Xd, offs, wordss, W_, S_, M_, use_em=True, seeds=seeds,
+                        verbose=bool(os.environ.get("SRB_FIT_VERBOSE")) and rank == 0)
         ft.fit()
         last["ft"] = ft
 

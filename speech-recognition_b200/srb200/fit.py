@@ -19,6 +19,8 @@ left single-GPU.  What stays on the host is O(states) bookkeeping in float64: th
 reference's own loop would have stopped), the M-step on the 200-odd reduced rows, and the global numpy RNG stream of
 kmeans.py:171, drawn state by state in the reference's order and indexed by a frame's rank in its state's pool.
 """
+import sys
+
 import numpy as np
 import torch
 
@@ -178,7 +180,9 @@ class WordFitter:
         return rank, n_loc, n_glob, offset
 
     def fit_states(self, kmeans_max_iteration=1000, em_max_iteration=10000):
-        """hmm.py:97-124 for every state of every word at once (after skmeans)."""
+        """hmm.py:97-124 for every state of every word at once (after skmeans).  The parameters, the stop tests and the
+        iteration counters live on the device (float64 torch tensors, same IEEE operations as the reference's numpy);
+        the host only learns, every few iterations, how many states are still running."""
         W, S, M, D = self.W, self.S, self.M, self.D
         G = W * S
         n_splits = int(np.log(M))
@@ -188,11 +192,12 @@ class WordFitter:
         mu = np.repeat(self.hmm_mu.reshape(G, 1, D), M, axis=1).copy()          # GMM.__init__: M copies (hmm_state.py:105-112)
         var = np.repeat(self.hmm_sigma.reshape(G, 1, D), M, axis=1).copy()
         wgt = np.full((G, M), 1.0 / M)
-        mu_old, var_old, w_old = mu.copy(), var.copy(), wgt.copy()
         pm = engine.PackedModel(mu, var, wgt)
-        centroids = self.hmm_mu.reshape(G, 1, D).copy()
+        self._old = [pm.mu.clone(), pm.var.clone(), pm.w.clone()]
+        centroids = self._t(self.hmm_mu.reshape(G, 1, D))
         weights = np.repeat((1.0 / np.maximum(n_glob, 1))[:, None], M, axis=1)  # np.full(n_gaussians, 1 / n) (hmm.py:108)
         self.iterations["kmeans"], self.iterations["em"] = [], []
+        self._n_loc = torch.from_numpy(n_loc).to(self.dev)
         # the global numpy RNG stream of kmeans.py:171 in the reference's order: word by word (optionally re-seeded per
         # word, like a caller who seeds before each HMM.fit), state by state, split by split
         draws = [[None] * G for _ in range(n_splits)]
@@ -202,9 +207,10 @@ class WordFitter:
             for s_ in range(S):
                 for i in range(n_splits):
                     draws[i][w * S + s_] = np.random.randint(0, 2 ** (i + 1), int(n_glob[w * S + s_]))
+        has = torch.from_numpy(n_glob > 0).to(self.dev)
         for i in range(n_splits):
             k = 2 ** (i + 1)
-            centroids = np.concatenate([centroids * 0.9, centroids * 1.1], axis=1)            # [G, k, D]  (hmm.py:110-112)
+            centroids = torch.cat([centroids * 0.9, centroids * 1.1], dim=1)                  # [G, k, D]  (hmm.py:110-112)
             # ---- K-means: the random initial partition (kmeans.py:171) only gives the variances (A3)
             parts = draws[i]
             part_off = np.concatenate([[0], np.cumsum([len(p) for p in parts])])
@@ -213,23 +219,7 @@ class WordFitter:
             part = flat[gidx]
             _, _, cov = self._moments((state.long() * k + part).to(torch.int32), G * k)
             cov = cov.reshape(G, k, D)
-            shift = centroids.copy()
-            active = n_glob > 0
-            km_its = np.zeros(G, np.int64)
-            cnt = np.zeros((G, k))
-            for it in range(max(kmeans_max_iteration, 1)):
-                am = engine.kmeans_assign(self.X, state, centroids, cov[:, 0])
-                c, new_c, _ = self._moments((state.long() * k + am.long()).to(torch.int32), G * k, shift=shift.reshape(G * k, D))
-                c, new_c = c.reshape(G, k), new_c.reshape(G, k, D)
-                for g in np.flatnonzero(active):
-                    km_its[g] = it
-                    cnt[g] = c[g]
-                    if np.array_equal(new_c[g], centroids[g]):
-                        active[g] = False
-                    else:
-                        centroids[g] = new_c[g]
-                if not active.any():
-                    break
+            centroids, cnt, km_its = self._kmeans(state, k, centroids, self._t(cov[:, 0]), has.clone(), kmeans_max_iteration)
             self.iterations["kmeans"].append(km_its)
             for g in range(G):                                                   # weights from cluster counts (A4, sic)
                 if n_glob[g] == 0:
@@ -238,55 +228,110 @@ class WordFitter:
                 c_counts = cnt[g][present]
                 for cl in present:
                     weights[g, cl] = c_counts[cl] / n_glob[g]                    # IndexError like hmm.py:116-118 if a cluster is empty
-            mu[:, :k], var[:, :k], wgt[:, :k] = centroids, cov, weights[:, :k]
-            self._upload(pm, mu, var, wgt)
+            pm.mu[:, :k], pm.var[:, :k], pm.w[:, :k] = centroids, self._t(cov), self._t(weights[:, :k])
+            pm.repack()
             if self.use_em:
-                self.iterations["em"].append(self._em(pm, state, k, mu, var, wgt, mu_old, var_old, w_old, n_glob,
-                                                      em_max_iteration))
-        self.pm, self.mu, self.var, self.w = pm, mu, var, wgt
-        self.mu_old, self.var_old, self.w_old = mu_old, var_old, w_old
-        return mu, var, wgt
+                self.iterations["em"].append(self._em(pm, state, k, has.clone(), em_max_iteration))
+        self.pm = pm
+        self.mu, self.var, self.w = (t.cpu().numpy().copy() for t in (pm.mu, pm.var, pm.w))
+        self.mu_old, self.var_old, self.w_old = (t.cpu().numpy().copy() for t in self._old)
+        return self.mu, self.var, self.w
 
-    def _upload(self, pm, mu, var, w):
-        pm.mu.copy_(torch.from_numpy(mu))
-        pm.var.copy_(torch.from_numpy(var))
-        pm.w.copy_(torch.from_numpy(w))
-        pm.repack()
+    def _t(self, a):
+        return torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(self.dev)
 
-    def _em(self, pm, state, k, mu, var, wgt, mu_old, var_old, w_old, n_glob, max_iteration):
+    class _WorkingSet:
+        """The frames of the states that are still iterating.  Once fewer than half of the frames in hand belong to
+        running states the set is compacted (one gather), so the tail of the slowest states does not re-read the corpus."""
+
+        def __init__(self, fitter, state):
+            self.f, self.X, self.state = fitter, fitter.X, state
+            self.n = int(state.shape[0])
+
+        def maybe_compact(self, active):
+            need = int(self.f._n_loc[active].sum().item())
+            if need * 2 < self.n:
+                idx = torch.nonzero(active[self.state.long()]).squeeze(1)
+                self.X, self.state, self.n = self.X[idx].contiguous(), self.state[idx].contiguous(), int(idx.numel())
+
+    CHECK_EVERY = 4          # iterations between two host reads of the running-state count
+
+    def _kmeans(self, state, k, cen, cov0, active, max_iteration):
+        """kmeans.py:178-193 for every pool at once: a pool stops at the iteration where its new centroids equal the
+        previous ones (np.array_equal, :190) and keeps those.  -> (centroids [G,k,D] device, counts [G,k] numpy, its[G])"""
+        G, D = cen.shape[0], self.D
+        shift = cen.clone().reshape(G * k, D)
+        ws = self._WorkingSet(self, state)
+        its = torch.zeros(G, dtype=torch.int64, device=self.dev)
+        cnt = torch.zeros((G, k), dtype=torch.float64, device=self.dev)
+        zero = torch.zeros((G * k, 2 * D + 3), dtype=torch.float64, device=self.dev)
+        for it in range(max(max_iteration, 1)):
+            if ws.n:
+                am = engine.kmeans_assign(ws.X, ws.state, cen, cov0)
+                st = engine.group_stats(ws.X, (ws.state.long() * k + am.long()).to(torch.int32), G * k, shift)
+            else:
+                st = zero.clone()
+            st = _allreduce(st, self.group)
+            c = st[:, 0].reshape(G, k)
+            new_c = (shift + st[:, 1:1 + D] / st[:, :1]).reshape(G, k, D)
+            same = (new_c == cen).flatten(1).all(dim=1)                           # NaN never equal, like np.array_equal
+            its = torch.where(active, it, its)
+            cnt = torch.where(active[:, None], c, cnt)
+            active = active & ~same
+            cen = torch.where(active[:, None, None], new_c, cen)
+            if it % self.CHECK_EVERY == self.CHECK_EVERY - 1:
+                n_run = int(active.sum().item())
+                if self.verbose:
+                    print(f"[fit] k-means k={k} iteration {it}: {n_run} pools running, {ws.n} frames in hand", file=sys.stderr)
+                if not n_run:
+                    break
+                ws.maybe_compact(active)
+        return cen, cnt.cpu().numpy(), its.cpu().numpy()
+
+    @staticmethod
+    def _allclose(a, b):
+        """np.allclose(a, b) per leading index: |a - b| <= 1e-8 + 1e-5 |b| everywhere (NaN -> False)."""
+        return ((a - b).abs() <= 1e-8 + 1e-5 * b.abs()).flatten(1).all(dim=1)
+
+    def _em(self, pm, state, k, active, max_iteration):
         """GMM.em (hmm_state.py:122-159) over the first k components of every state at once; a state stops at the
-        iteration where the reference's loop would (np.allclose of the new parameters with the previous ones)."""
-        G, M, D = mu.shape
-        active = n_glob > 0
-        its = np.zeros(G, np.int64)
+        iteration where the reference's loop would (np.allclose of the new parameters with the previous ones) and is
+        frozen from then on.  Updates pm.mu / pm.var / pm.w in place.  -> its[G] (last iteration index of every state)"""
+        G, M, D = pm.mu.shape
+        mu, var, w = pm.mu[:, :k], pm.var[:, :k], pm.w[:, :k]                    # views
+        mu_old, var_old, w_old = (t[:, :k] for t in self._old)
+        ws = self._WorkingSet(self, state)
+        its = torch.zeros(G, dtype=torch.int64, device=self.dev)
         row = 2 * D + 3
+        zero = torch.zeros((G * M, row), dtype=torch.float64, device=self.dev)
         for it in range(max_iteration):
-            st = _allreduce(engine.gmm_stats(self.X, state, pm, k), self.group).cpu().numpy().reshape(G, M, row)
+            st = engine.gmm_stats(ws.X, ws.state, pm, k) if ws.n else zero.clone()
+            st = _allreduce(st, self.group).reshape(G, M, row)
             S0 = st[:, :k, 0]
             cntg = st[:, 0, 2 * D + 1]
-            with np.errstate(all="ignore"):
-                m1 = st[:, :k, 1:1 + D] / S0[:, :, None]
-                nmu = mu[:, :k] + m1
-                nvar = st[:, :k, 1 + D:1 + 2 * D] / S0[:, :, None] - m1 * m1
-                nw = S0 / cntg[:, None]
-            ok = S0 > 0                                                           # empty components stay (DESIGN 5 ii)
-            for g in np.flatnonzero(active):
-                its[g] = it
-                o = ok[g]
-                mu[g, :k][o], var[g, :k][o] = nmu[g][o], nvar[g][o]
-                if cntg[g] > 0:
-                    wgt[g, :k][o] = nw[g][o]
-                if np.allclose(mu[g, :k], mu_old[g, :k]) and np.allclose(var[g, :k], var_old[g, :k]) and \
-                        np.allclose(wgt[g, :k], w_old[g, :k]):
-                    active[g] = False
-                    if self.verbose:
-                        print("EM converged at iteration:", it)
-                else:
-                    mu_old[g, :k], var_old[g, :k], w_old[g, :k] = mu[g, :k], var[g, :k], wgt[g, :k]
-            self._upload(pm, mu, var, wgt)
-            if not active.any():
-                break
-        return its
+            m1 = st[:, :k, 1:1 + D] / S0[:, :, None]
+            nmu = mu + m1
+            nvar = st[:, :k, 1 + D:1 + 2 * D] / S0[:, :, None] - m1 * m1
+            nw = S0 / cntg[:, None]
+            ok = (S0 > 0) & active[:, None]                                       # empty components stay (DESIGN 5 ii)
+            mu.copy_(torch.where(ok[:, :, None], nmu, mu))
+            var.copy_(torch.where(ok[:, :, None], nvar, var))
+            w.copy_(torch.where(ok & (cntg > 0)[:, None], nw, w))
+            conv = self._allclose(mu, mu_old) & self._allclose(var, var_old) & self._allclose(w, w_old)
+            its = torch.where(active, it, its)
+            active = active & ~conv
+            mu_old.copy_(torch.where(active[:, None, None], mu, mu_old))
+            var_old.copy_(torch.where(active[:, None, None], var, var_old))
+            w_old.copy_(torch.where(active[:, None], w, w_old))
+            pm.repack()
+            if it % self.CHECK_EVERY == self.CHECK_EVERY - 1:
+                n_run = int(active.sum().item())
+                if self.verbose and (it < 64 or it % 256 == 255 or not n_run):
+                    print(f"[fit] EM k={k} iteration {it}: {n_run} states running, {ws.n} frames in hand", file=sys.stderr)
+                if not n_run:
+                    break
+                ws.maybe_compact(active)
+        return its.cpu().numpy()
 
     # ------------------------------------------------------------------------------------------ phase 3: re-alignment
     def align(self):
