@@ -286,6 +286,19 @@ int srb_stats_parts(void);
 int srb_group_stats(const float *X, int64_t N, int D, const int32_t *label, int K, const double *shift,
                     float *partial, double *out, int accumulate, void *stream);
 
+/* srb_group_stats without caller scratch and without any allocation: the private slices live in a file-scope
+ * `static __device__` array of SRB_STATIC_SCRATCH_FLOATS floats (48 MiB, held by every GPU that loads the library until
+ * the process exits).  No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (CUDA graph capture, tight serving loops).  Same arguments and results as srb_group_stats minus
+ * `partial`.  Limit: srb_stats_parts() * K * srb_stats_row(D) <= srb_static_scratch_floats() (K <= 65 groups at D = 39
+ * on a 148-SM B200), else SRB_EUNSUPPORTED.  Calls cudaMemsetAsync + two kernels only: no cudaMalloc / cudaFree.
+ * All calls on one device share the array (it is cleared at the start of each call): calls that overlap on the GPU,
+ * e.g. on two streams, race -- serialise them. */
+#define SRB_STATIC_SCRATCH_FLOATS (12 * 1024 * 1024)
+int64_t srb_static_scratch_floats(void);
+int srb_group_stats_static(const float *X, int64_t N, int D, const int32_t *label, int K, const double *shift,
+                           double *out, int accumulate, void *stream);
+
 /* E-step of GMM.em (hmm_state.py:122-136) for frames hard-aligned to tied states: label[n] = state in [0,R)
  * (< 0: skip); posteriors over the FIRST ncomp components of the state (hmm.py:104-124 trains 2^i of them),
  * computed in the log domain (no underflow rows); shift = the component's current mean.

@@ -13,6 +13,7 @@
 // Row layout of one group in every buffer:  [S0, S1[0..D), S2[0..D), count, loglik]  = 2*D + 3 values
 // (count / loglik: frames and summed log-likelihood of the state, kept on its component 0 only).
 #include <cstdlib>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -694,6 +695,55 @@ int srb_group_stats(const float *X, int64_t N, int D, const int32_t *label, int 
     const int64_t len = (int64_t)K * (2 * D + 3), parts = (int64_t)grid * SW;
     cudaStream_t st = (cudaStream_t)stream;
     SRB_CUDA(cudaMemsetAsync(partial, 0, sizeof(float) * len * parts, st));
+    if (N > 0) group_stats_kernel<<<grid, SW * 32, 0, st>>>(X, N, D, label, K, shift, partial);
+    reduce_partials_kernel<<<(int)((len + 255) / 256), 256, 0, st>>>(partial, parts, len, out, accumulate);
+    SRB_CUDA(cudaGetLastError());
+    return SRB_OK;
+}
+
+// ---- srb_group_stats_static: srb_group_stats for callers that may not allocate (CUDA graph capture, serving loops).
+// The private slices live in this file-scope device array instead of caller scratch.  Host code only ever uses the
+// DEVICE address of the array, fetched once per device with cudaGetSymbolAddress (the bare symbol is a host shadow).
+// Every call on a device shares the array: two calls that overlap on the GPU (different streams) race.
+static __device__ __align__(256) float g_static_partial[SRB_STATIC_SCRATCH_FLOATS];
+
+int64_t srb_static_scratch_floats(void) { return (int64_t)SRB_STATIC_SCRATCH_FLOATS; }
+
+static int static_partial_ptr(float **out) {
+    constexpr int MAXDEV = 64;
+    static float *ptrs[MAXDEV] = {};
+    static std::mutex mu;
+    int dev = -1;
+    SRB_CUDA(cudaGetDevice(&dev));
+    SRB_REQUIRE(dev >= 0 && dev < MAXDEV, SRB_EUNSUPPORTED, "srb_group_stats_static: device ordinal %d", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ptrs[dev]) {
+        float *p = nullptr;
+        SRB_CUDA(cudaGetSymbolAddress((void **)&p, g_static_partial));       // with device `dev` current
+        SRB_REQUIRE(p != nullptr, SRB_ECUDA, "srb_group_stats_static: no device address for the scratch array");
+        ptrs[dev] = p;
+    }
+    *out = ptrs[dev];
+    return SRB_OK;
+}
+
+int srb_group_stats_static(const float *X, int64_t N, int D, const int32_t *label, int K, const double *shift,
+                           double *out, int accumulate, void *stream) {
+    SRB_REQUIRE((X || N == 0) && label && shift && out, SRB_EINVAL, "srb_group_stats_static: null pointer");
+    SRB_REQUIRE(N >= 0 && D > 0 && D <= 64 && K > 0, SRB_EINVAL, "srb_group_stats_static: bad N/D/K");
+    const int grid = stats_grid();
+    SRB_REQUIRE(grid > 0, SRB_ENODEVICE, "no CUDA device");
+    const int64_t len = (int64_t)K * (2 * D + 3), parts = (int64_t)grid * SW;
+    SRB_REQUIRE(len * parts <= (int64_t)SRB_STATIC_SCRATCH_FLOATS, SRB_EUNSUPPORTED,
+                "srb_group_stats_static: K=%d groups x %d floats x %lld slices = %lld floats exceed the static scratch of "
+                "%lld floats (at most %lld groups at this D); use srb_group_stats with caller scratch",
+                K, 2 * D + 3, (long long)parts, (long long)(len * parts), (long long)SRB_STATIC_SCRATCH_FLOATS,
+                (long long)(SRB_STATIC_SCRATCH_FLOATS / (parts * (2 * D + 3))));
+    float *partial = nullptr;
+    const int rc = static_partial_ptr(&partial);
+    if (rc != SRB_OK) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    SRB_CUDA(cudaMemsetAsync(partial, 0, sizeof(float) * len * parts, st));    // the array keeps the last call's sums
     if (N > 0) group_stats_kernel<<<grid, SW * 32, 0, st>>>(X, N, D, label, K, shift, partial);
     reduce_partials_kernel<<<(int)((len + 255) / 256), 256, 0, st>>>(partial, parts, len, out, accumulate);
     SRB_CUDA(cudaGetLastError());
