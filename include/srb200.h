@@ -331,6 +331,24 @@ int srb_local_dist(const float *X, int64_t N, int D, const double *Y, const doub
 int srb_kmeans_assign(const float *X, int64_t N, int D, const int32_t *group, const double *Y, const double *var, int G,
                       int k, int32_t *argmin_out, void *stream);
 
+/* The statistics of ONE K-means or ONE EM iteration for many pools (HMM states) at once, X read once: frame n belongs to
+ * pool state[n] in [0, G) (< 0 or >= G: skipped) and is weighed over the pool's first k components, then the weighted
+ * moments of every (pool, component) are accumulated (rows [G*M, srb_stats_row(D)] like srb_gmm_stats; k in {1,2,4,8}).
+ *   mode 0  GMM.em E-step (hmm_state.py:122-136): weights = posteriors under center/var double[G*M, D] and
+ *           lc double[G*M] (srb_gauss_consts), moments about the component's own mean; `shift` unused.
+ *           Same results as srb_gmm_stats.
+ *   mode 1  kmeans.py:180-187: weights = one-hot first minimum of mahalanobis(center_c, x, var[pool]) with the ONE
+ *           variance row var double[G, D] per pool (kmeans.py:183), moments about shift double[G*M, D]; M must equal
+ *           k.  Same results as srb_kmeans_assign followed by srb_group_stats; argmin_out int32[N] optional (-1 = skipped).
+ * partial: caller scratch of srb_pool_stats_parts() * G*M * srb_stats_row(D) floats.  The parameter tables live in
+ * shared memory: srb_pool_stats_supported(G, k, D) says whether they fit (55 pools x 4 x 39 do), else SRB_EUNSUPPORTED.
+ * Deterministic: private slices, fixed-order double reduction. */
+int srb_pool_stats_parts(void);
+int srb_pool_stats_supported(int G, int k, int D);
+int srb_pool_stats(const float *X, int64_t N, int D, const int32_t *state, int G, int M, int k, int mode,
+                   const double *center, const double *var, const double *lc, const double *shift, float *partial,
+                   double *out, int32_t *argmin_out, int accumulate, void *stream);
+
 /* M-step of GMM.em (hmm_state.py:138-148) in place on mu/var/w double (first ncomp components per state):
  * mu += S1/S0, var = S2/S0 - (S1/S0)^2 (floored at var_floor), w = S0/count. */
 int srb_mstep(const double *stats, int R, int M, int ncomp, int D, double *mu, double *var, double *w,

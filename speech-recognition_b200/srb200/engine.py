@@ -716,6 +716,53 @@ def kmeans_assign(X, group, centroids, var0):
     return out
 
 
+def pool_stats_supported(G, k, D):
+    return k in (1, 2, 4, 8) and bool(_l.load().srb_pool_stats_supported(int(G), int(k), int(D)))
+
+
+def _pool_partial(groups, D, dev):
+    L = _l.load()
+    need = L.srb_pool_stats_parts() * groups * L.srb_stats_row(D)
+    key = (dev.index, "pool_partial")
+    buf = _scratch.get(key)
+    if buf is None or buf.numel() < need:
+        buf = torch.empty(need, dtype=torch.float32, device=dev)
+        _scratch[key] = buf
+    return buf
+
+
+def pool_em_stats(X, state, pm, k):
+    """srb_pool_stats mode 0: E-step statistics of GMM.em for every state at once, frames hard-assigned to states
+    (same rows as gmm_stats: double [R*M, 2D+3])."""
+    X = as_frames(X)
+    dev = X.device
+    state = _i32(state, dev)
+    L = _l.load()
+    lc = gauss_consts(pm.var, pm.w)
+    out = torch.empty((pm.R * pm.M, L.srb_stats_row(pm.D)), dtype=torch.float64, device=dev)
+    _l.check(L.srb_pool_stats(_l.ptr(X), X.shape[0], pm.D, _l.ptr(state), pm.R, pm.M, int(k), 0, _l.ptr(pm.mu),
+                              _l.ptr(pm.var), _l.ptr(lc), None, _l.ptr(_pool_partial(pm.R * pm.M, pm.D, dev)), _l.ptr(out),
+                              None, 0, _l.stream_ptr()))
+    return out
+
+
+def pool_kmeans_stats(X, state, centroids, var0, shift, want_argmin=False):
+    """srb_pool_stats mode 1: one K-means iteration for every pool at once -- assignment to the nearest of the pool's k
+    centroids [G, k, D] under the pool's variance row var0 [G, D], moments of every cluster about shift [G*k, D].
+    -> double [G*k, 2D+3] (and the int32[N] assignment)"""
+    X = as_frames(X)
+    dev = X.device
+    state = _i32(state, dev)
+    c, v, sh = _f64(centroids, dev), _f64(var0, dev), _f64(shift, dev)
+    G, k, D = (int(t) for t in c.shape)
+    L = _l.load()
+    out = torch.empty((G * k, L.srb_stats_row(D)), dtype=torch.float64, device=dev)
+    am = torch.empty(X.shape[0], dtype=torch.int32, device=dev) if want_argmin else None
+    _l.check(L.srb_pool_stats(_l.ptr(X), X.shape[0], D, _l.ptr(state), G, k, k, 1, _l.ptr(c), _l.ptr(v), None, _l.ptr(sh),
+                              _l.ptr(_pool_partial(G * k, D, dev)), _l.ptr(out), _l.ptr(am), 0, _l.stream_ptr()))
+    return (out, am) if want_argmin else out
+
+
 def mstep(stats, pm, ncomp, var_floor=0.0):
     """In-place M-step on pm.mu / pm.var / pm.w (double), then refresh the packed fp32 copy."""
     _l.check(_l.load().srb_mstep(_l.ptr(stats), pm.R, pm.M, ncomp, pm.D, _l.ptr(pm.mu), _l.ptr(pm.var), _l.ptr(pm.w),

@@ -261,12 +261,15 @@ class WordFitter:
         previous ones (np.array_equal, :190) and keeps those.  -> (centroids [G,k,D] device, counts [G,k] numpy, its[G])"""
         G, D = cen.shape[0], self.D
         shift = cen.clone().reshape(G * k, D)
+        fused = engine.pool_stats_supported(G, k, D)          # one pass over X per iteration instead of two
         ws = self._WorkingSet(self, state)
         its = torch.zeros(G, dtype=torch.int64, device=self.dev)
         cnt = torch.zeros((G, k), dtype=torch.float64, device=self.dev)
         zero = torch.zeros((G * k, 2 * D + 3), dtype=torch.float64, device=self.dev)
         for it in range(max(max_iteration, 1)):
-            if ws.n:
+            if ws.n and fused:
+                st = engine.pool_kmeans_stats(ws.X, ws.state, cen, cov0, shift)
+            elif ws.n:
                 am = engine.kmeans_assign(ws.X, ws.state, cen, cov0)
                 st = engine.group_stats(ws.X, (ws.state.long() * k + am.long()).to(torch.int32), G * k, shift)
             else:
@@ -303,9 +306,10 @@ class WordFitter:
         ws = self._WorkingSet(self, state)
         its = torch.zeros(G, dtype=torch.int64, device=self.dev)
         row = 2 * D + 3
+        fused = engine.pool_stats_supported(G, k, D)
         zero = torch.zeros((G * M, row), dtype=torch.float64, device=self.dev)
         for it in range(max_iteration):
-            st = engine.gmm_stats(ws.X, ws.state, pm, k) if ws.n else zero.clone()
+            st = (engine.pool_em_stats if fused else engine.gmm_stats)(ws.X, ws.state, pm, k) if ws.n else zero.clone()
             st = _allreduce(st, self.group).reshape(G, M, row)
             S0 = st[:, :k, 0]
             cntg = st[:, 0, 2 * D + 1]

@@ -60,6 +60,10 @@ SIGNATURES = {
     "srb_stats_row": (c_int, [c_int]),
     "srb_stats_parts": (c_int, []),
     "srb_group_stats": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "srb_pool_stats_parts": (c_int, []),
+    "srb_pool_stats_supported": (c_int, [c_int, c_int, c_int]),
+    "srb_pool_stats": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                               c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "srb_static_scratch_floats": (c_i64, []),
     "srb_group_stats_static": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_int, c_void_p, c_void_p, c_int, c_void_p]),
     "srb_gmm_stats": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,

@@ -339,9 +339,28 @@ def kmeans_assign(X, group, centroids, var0):
     return torch.from_numpy(out)
 
 
+def pool_stats_supported(G, k, D):
+    return k in (1, 2, 4, 8)
+
+
+def pool_em_stats(X, state, pm, k):
+    return gmm_stats(X, state, pm, k)
+
+
+def pool_kmeans_stats(X, state, centroids, var0, shift, want_argmin=False):
+    c = _np(centroids, np.float64)
+    G, k, D = c.shape
+    am = kmeans_assign(X, state, c, var0)
+    st_ = _np(state, np.int64)
+    lab = np.where(st_ >= 0, st_ * k + am.numpy(), -1)
+    out = group_stats(X, lab, G * k, _np(shift, np.float64).reshape(G * k, D))
+    return (out, am) if want_argmin else out
+
+
 def install(monkeypatch):
     """Replace the device entry points of srb200.engine for the duration of one test."""
     from srb200 import engine
     for name in ("device", "PackedModel", "as_frames", "as_offsets", "gmm_score", "viterbi", "classify",
-                 "group_stats", "moments_from_stats", "gmm_stats", "mstep", "local_dist", "dtw_beam", "kmeans_assign"):
+                 "group_stats", "moments_from_stats", "gmm_stats", "mstep", "local_dist", "dtw_beam", "kmeans_assign",
+                 "pool_stats_supported", "pool_em_stats", "pool_kmeans_stats"):
         monkeypatch.setattr(engine, name, globals()[name])

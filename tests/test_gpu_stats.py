@@ -124,3 +124,74 @@ def test_gmm_stats_multi_state_vs_oracle(eng):
         np.testing.assert_allclose(mu[s], gs.mu, rtol=RTOL, atol=1e-5)
         np.testing.assert_allclose(var[s], gs.cov, rtol=RTOL)
         np.testing.assert_allclose(w[s], gs.w, rtol=RTOL)
+
+
+def _pool_case(seed=52, B=300, T=60, ragged=None):
+    from srb200 import synth
+    models, base = synth.make_models(51, W=11, S=5, M=4)
+    X, off, words = synth.make_utterances(seed, base, B, T=T) if ragged is None else \
+        synth.make_utterances(seed, base, B, ragged=ragged)
+    rng = np.random.default_rng(3)
+    N = X.shape[0]
+    t_in = np.arange(N) - np.repeat(off[:-1], np.diff(off))
+    Tn = np.repeat(np.diff(off), np.diff(off))
+    lab = (np.repeat(words, np.diff(off)) * 5 + np.minimum(t_in * 5 // Tn, 4)).astype(np.int32)
+    lab[rng.random(N) < 0.05] = -1
+    return models, X, lab
+
+
+@pytest.mark.parametrize("k", [1, 2, 4])
+def test_pool_em_stats_equals_gmm_stats(eng, k):
+    """srb_pool_stats mode 0 == srb_gmm_stats (same arithmetic, other summation order), ragged tail chunk included, and
+    two runs are bit-identical (private slices, program-order reductions)."""
+    models, X, lab = _pool_case(ragged=(37, 81))
+    pm, _ = eng.PackedModel.from_words(models)
+    assert eng.pool_stats_supported(55, k, 39)
+    ref = eng.gmm_stats(X, lab, pm, k).cpu().numpy()
+    got = eng.pool_em_stats(X, lab, pm, k).cpu().numpy()
+    again = eng.pool_em_stats(X, lab, pm, k).cpu().numpy()
+    assert np.array_equal(got, again)
+    D = 39
+    scale = np.abs(ref[:, 1 + D:1 + 2 * D]).max(axis=1, keepdims=True) + 1e-30     # a row's second moments set its scale
+    assert np.max(np.abs(got - ref)[:, :1 + 2 * D] / np.maximum(scale, np.abs(ref[:, :1]))) < 2e-5
+    np.testing.assert_array_equal(got[:, 2 * D + 1], ref[:, 2 * D + 1])            # frame counts
+    np.testing.assert_allclose(got[:, 2 * D + 2], ref[:, 2 * D + 2], rtol=1e-5)    # summed log-likelihood
+    assert not got.reshape(55, 4, -1)[:, k:].any()                                 # untrained components untouched
+
+
+@pytest.mark.parametrize("k", [2, 4])
+def test_pool_kmeans_stats_equals_assign_plus_group_stats(eng, k):
+    """srb_pool_stats mode 1 == srb_kmeans_assign + srb_group_stats; assignments equal except where the two nearest
+    centroids are closer than FP32 resolves (other summation order of the 39 terms)."""
+    models, X, lab = _pool_case()
+    rng = np.random.default_rng(9)
+    G, D = 55, 39
+    mu = np.concatenate([m[0] for m in models])[:, :k]                              # [G, k, D]
+    var0 = np.concatenate([m[1] for m in models])[:, 0]
+    shift = (mu + rng.normal(scale=0.05, size=mu.shape)).reshape(G * k, D)
+    am_ref = eng.kmeans_assign(X, lab, mu, var0)
+    st, am = eng.pool_kmeans_stats(X, lab, mu, var0, shift, want_argmin=True)
+    am_ref, am = am_ref.cpu().numpy(), am.cpu().numpy()
+    assert np.array_equal(am < 0, lab < 0) and np.array_equal(am_ref < 0, lab < 0)
+    diff = np.flatnonzero(am != am_ref)
+    assert len(diff) <= 2, len(diff)
+    for n in diff:                                                                  # only near-ties may differ
+        d = (0.5 * (X[n].astype(np.float64) - mu[lab[n]]) ** 2 / var0[lab[n]]).sum(axis=1)
+        assert abs(d[am[n]] - d[am_ref[n]]) <= 1e-5 * d.min()
+    ref = eng.group_stats(X, np.where(lab >= 0, lab * k + am, -1).astype(np.int32), G * k, shift).cpu().numpy()
+    got = st.cpu().numpy()
+    np.testing.assert_array_equal(got[:, 0], ref[:, 0])
+    scale = np.abs(ref[:, 1 + D:1 + 2 * D]).max(axis=1, keepdims=True) + 1e-30
+    assert np.max(np.abs(got - ref)[:, :1 + 2 * D] / scale) < 2e-5
+    st2 = eng.pool_kmeans_stats(X, lab, mu, var0, shift).cpu().numpy()
+    assert np.array_equal(got, st2)                                                 # the K-means stop test needs this
+
+
+def test_pool_stats_rejects_tables_beyond_shared_memory(eng):
+    from srb200 import lib as _l
+    assert not eng.pool_stats_supported(400, 8, 39)
+    assert not eng.pool_stats_supported(55, 3, 39)
+    models, X, lab = _pool_case(B=20)
+    big = np.zeros((400, 8, 39))
+    with pytest.raises(_l.SrbError):
+        eng.pool_kmeans_stats(X, lab, big, np.ones((400, 39)), big.reshape(-1, 39))
