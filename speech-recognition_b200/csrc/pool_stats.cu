@@ -6,10 +6,13 @@
 // then weighted moments": here one kernel does either for all W*S pools at once, and the K-means assignment is fused
 // with the moments (X is read once per iteration instead of twice).
 //
-// A warp owns chunks of 32 consecutive frames.  The chunk is staged in shared memory by coalesced loads (the next chunk
-// is already in flight in registers).  Phase A: lane = frame, scores its k components against the parameter tables in
-// shared memory (frames of one state broadcast).  Phase B: lanes = dimensions, a loop over the 32 frames adds the
-// weighted first and second moments about the component's shift to register accumulators; when the state changes (the
+// A warp owns chunks of 32 consecutive frames = 128*D contiguous bytes, brought into the warp's own shared-memory ring
+// (two stages when they fit) by ONE bulk copy of the TMA engine per chunk (cp.async.bulk + mbarrier complete_tx; plain
+// loads for the ragged last chunk, an even D or a misaligned X).  Phase A: lane = frame, scores its k components against
+// the parameter table in shared memory ({-centre, scale} interleaved over the components: one 128-bit broadcast load and
+// three packed fma.rn.f32x2 per dimension and component pair).  Phase B: lanes = dimensions (d, d+32 packed in a float2),
+// a loop over the 32 frames reads the frame's {state, weights} record (one broadcast load) and adds the weighted first
+// and second moments about the component's shift to register accumulators; when the state changes (the
 // frames of an utterance come in runs of one state) the accumulators are added to the warp's PRIVATE slice of `partial`
 // with fire-and-forget reductions -- one thread per address, program order, so the sums do not depend on scheduling.
 // The slices are then summed in a fixed order in double.  HBM traffic: 4*D bytes of X + 4 bytes of label per frame.
@@ -24,99 +27,151 @@ namespace {
 constexpr int PW = 16;                 // warps per CTA, one CTA per SM
 constexpr int MAX_SMEM = 227 * 1024;
 
-template <int KC, int MODE, int DMAX>   // MODE 0: EM posteriors (hmm_state.py:122-136)  1: K-means one-hot (kmeans.py:180-187)
+__device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void bar_init(uint64_t *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count));
+}
+__device__ __forceinline__ void bar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_addr(bar)), "r"(parity) : "memory");
+}
+// TMA engine, bulk (1-D) form: global -> shared, completion counted in bytes on the mbarrier
+__device__ __forceinline__ void bulk_load(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_addr(dst)), "l"(src), "r"(bytes), "r"(smem_addr(bar)) : "memory");
+}
+
+__host__ __device__ constexpr int rec_floats(int KC) { return KC <= 2 ? 4 : KC == 4 ? 8 : 12; }   // {state, loglik, w[KC]}
+__host__ __device__ inline int up4(int n) { return (n + 3) & ~3; }
+
+// shared memory, in floats: tab [G, D, 2*KC] = {-centre[KC], scale[KC]} per (pool, dim); shf: K-means [G, KC, D] negated
+// shifts, EM [G, KC] constants log w - 0.5 log|2 pi var| (EM shifts by the centre); rec [PW, 32, rec_floats]; xs [PW, nst, 32*ld]; then PW*nst mbarriers.
+struct PoolLayout {
+    int tab, shf, rec, xs, bar_bytes_off, ld, stage;
+    size_t bytes;
+};
+__host__ __device__ inline PoolLayout pool_layout(int G, int KC, int D, int mode, int nst) {
+    PoolLayout L;
+    L.ld = D | 1;
+    L.stage = 32 * L.ld;
+    L.tab = 0;
+    L.shf = up4(G * D * 2 * KC);
+    L.rec = L.shf + (mode == 1 ? up4(G * KC * D) : up4(G * KC));
+    L.xs = L.rec + PW * 32 * rec_floats(KC);
+    L.bar_bytes_off = (L.xs + PW * nst * L.stage) * 4;
+    L.bytes = (size_t)L.bar_bytes_off + (size_t)PW * nst * 8;
+    return L;
+}
+
+template <int KC, int MODE>   // MODE 0: EM posteriors (hmm_state.py:122-136)  1: K-means one-hot (kmeans.py:180-187)
 __global__ void __launch_bounds__(PW * 32, 1)
 pool_stats_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t *__restrict__ state, int G, int M,
                   const double *__restrict__ center, const double *__restrict__ var, const double *__restrict__ lc,
-                  const double *__restrict__ shift, float *__restrict__ partial, int32_t *__restrict__ argmin_out) {
-    extern __shared__ float sm[];
-    const int Dp = D | 1;                                  // odd row stride: lane = frame reads are conflict-free
-    const int GKD = G * KC * D;
-    float *cen = sm;                                       // [G, KC, D] centres the frames are scored against
-    float *vv = cen + GKD;                                 // EM: [G, KC, D] -0.5/var     K-means: [G, D] 0.5/var0
-    float *aux = vv + (MODE == 0 ? GKD : G * D);           // EM: [G, KC] log w - 0.5 log|2 pi var|   K-means: [G, KC, D] shift
-    float *xs_all = aux + (MODE == 0 ? G * KC : GKD);
-    for (int i = threadIdx.x; i < GKD; i += blockDim.x) {
-        const int g = i / (KC * D), r = i - g * (KC * D), m = r / D, d = r - m * D;
+                  const double *__restrict__ shift, float *__restrict__ partial, int32_t *__restrict__ argmin_out,
+                  int nst, int bulk) {
+    extern __shared__ __align__(128) float sm[];
+    constexpr int RW = rec_floats(KC), K2 = (KC + 1) / 2;
+    const PoolLayout L = pool_layout(G, KC, D, MODE, nst);
+    float *tab = sm + L.tab, *shf = sm + L.shf;
+    const int ld = L.ld;
+    // scale: EM -0.5/var of the component, K-means 0.5/var0 of the pool (kmeans.py:183: one variance row for all centroids)
+    for (int i = threadIdx.x; i < G * D * KC; i += blockDim.x) {
+        const int g = i / (D * KC), r = i - g * (D * KC), d = r / KC, m = r - d * KC;
         const size_t src = ((size_t)g * M + m) * D + d;
-        cen[i] = (float)center[src];
-        if (MODE == 0) vv[i] = (float)(-0.5 / var[src]);
-        else aux[i] = (float)shift[src];
+        float *t = tab + ((size_t)g * D + d) * 2 * KC;
+        t[m] = -(float)center[src];
+        t[KC + m] = (MODE == 0) ? (float)(-0.5 / var[src]) : (float)(0.5 / var[(size_t)g * D + d]);
+        if (MODE == 1) shf[((size_t)g * KC + m) * D + d] = -(float)shift[src];
     }
-    if (MODE == 0) {
-        for (int i = threadIdx.x; i < G * KC; i += blockDim.x) aux[i] = (float)lc[(size_t)(i / KC) * M + (i % KC)];
-    } else {
-        for (int i = threadIdx.x; i < G * D; i += blockDim.x) vv[i] = (float)(0.5 / var[i]);
-    }
+    if (MODE == 0)
+        for (int i = threadIdx.x; i < G * KC; i += blockDim.x) shf[i] = (float)lc[(size_t)(i / KC) * M + (i % KC)];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float *rec = sm + L.rec + warp * 32 * RW;
+    float *xs0 = sm + L.xs + (size_t)warp * nst * L.stage;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(reinterpret_cast<char *>(sm) + L.bar_bytes_off) + warp * nst;
+    if (lane == 0)
+        for (int i = 0; i < nst; ++i) bar_init(&bars[i], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     __syncthreads();
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    float *xs = xs_all + (size_t)warp * 32 * Dp;
     const int64_t wg = (int64_t)blockIdx.x * PW + warp, nw = (int64_t)gridDim.x * PW;
     const int row = 2 * D + 3;
-    float *mine = partial + (size_t)wg * G * M * row;
-    const int64_t nchunks = (N + 31) >> 5, total = N * D;
+    float *mine = partial + (size_t)wg * G * KC * row;          // private slice: the KC scored components of every pool
+    const int64_t nchunks = (N + 31) >> 5, nfull = N >> 5;      // chunks [0, nfull) hold 32 frames
+    // a warp works on a CONTIGUOUS range of chunks: runs of one state continue across chunks, and the few pools a warp
+    // meets keep its slice rows in L2
+    const int64_t cpw = (nchunks + nw - 1) / nw, c_begin = wg * cpw, c_end = min(nchunks, c_begin + cpw);
     const int d0 = lane, d1 = lane + 32;
     const bool h0 = d0 < D, h1 = d1 < D;
-
-    float pre[DMAX];
-    auto fetch = [&](int64_t c) {
-        const int64_t base = c * 32 * D + lane;
-#pragma unroll
-        for (int i = 0; i < DMAX; ++i) {
-            const int64_t idx = base + (int64_t)i * 32;
-            pre[i] = (i < D && idx < total) ? X[idx] : 0.f;
-        }
-    };
+    const uint32_t chunk_bytes = 32u * (uint32_t)D * 4u;
 
     int cur = -1;
-    float s0[KC], a0[KC], a1[KC], q0[KC], q1[KC], sh0[KC], sh1[KC];
-    float cnt = 0.f, llsum = 0.f;
+    float s0[KC];
+    float2 a2[KC], q2[KC], nsh[KC];
+    float llsum = 0.f;
+    int run_frames = 0;                                     // frames of the current run (the count column)
 #pragma unroll
-    for (int m = 0; m < KC; ++m) s0[m] = a0[m] = a1[m] = q0[m] = q1[m] = sh0[m] = sh1[m] = 0.f;
+    for (int m = 0; m < KC; ++m) {
+        s0[m] = 0.f;
+        a2[m] = q2[m] = nsh[m] = make_float2(0.f, 0.f);
+    }
 
     auto flush = [&]() {
         if (cur < 0) return;
 #pragma unroll
         for (int m = 0; m < KC; ++m) {
-            float *r = mine + ((size_t)cur * M + m) * row;
+            float *r = mine + ((size_t)cur * KC + m) * row;
             if (lane == 0) {
                 atomicAdd(r, s0[m]);
                 if (MODE == 0 && m == 0) {
-                    atomicAdd(r + 2 * D + 1, cnt);
+                    atomicAdd(r + 2 * D + 1, (float)run_frames);
                     atomicAdd(r + 2 * D + 2, llsum);
                 }
             }
             if (h0) {
-                atomicAdd(r + 1 + d0, a0[m]);
-                atomicAdd(r + 1 + D + d0, q0[m]);
+                atomicAdd(r + 1 + d0, a2[m].x);
+                atomicAdd(r + 1 + D + d0, q2[m].x);
             }
             if (h1) {
-                atomicAdd(r + 1 + d1, a1[m]);
-                atomicAdd(r + 1 + D + d1, q1[m]);
+                atomicAdd(r + 1 + d1, a2[m].y);
+                atomicAdd(r + 1 + D + d1, q2[m].y);
             }
         }
     };
 
-    if (wg < nchunks) fetch(wg);
-    for (int64_t c = wg; c < nchunks; c += nw) {
-        // ---- stage the chunk: element e = i*32 + lane of the [32, D] block goes to row e / D, column e % D
-        {
-            int rr = lane / D, cc = lane - rr * D;
-#pragma unroll
-            for (int i = 0; i < DMAX; ++i) {
-                if (i < D) xs[rr * Dp + cc] = pre[i];
-                cc += 32;
-                while (cc >= D) {
-                    cc -= D;
-                    ++rr;
-                }
+    // ---- prologue: the first nst chunks of this warp
+    if (bulk && lane == 0)
+        for (int i = 0; i < nst; ++i) {
+            const int64_t c = c_begin + i;
+            if (c < c_end && c < nfull) {
+                bar_expect_tx(&bars[i], chunk_bytes);
+                bulk_load(xs0 + (size_t)i * L.stage, X + c * 32 * D, chunk_bytes, &bars[i]);
             }
         }
-        __syncwarp();
-        if (c + nw < nchunks) fetch(c + nw);               // in flight while this chunk is worked on
+    // lanes without a dimension (d >= D) read column 0 and feed accumulators that are never flushed
+    const int o0 = h0 ? d0 : 0, o1 = h1 ? d1 : 0;
+    int it = 0;
+    for (int64_t c = c_begin; c < c_end; ++c, ++it) {
+        const int stg = (nst == 2) ? (it & 1) : 0;
+        float *xs = xs0 + (size_t)stg * L.stage;
+        if (bulk && c < nfull) {
+            bar_wait(&bars[stg], (uint32_t)((nst == 2 ? (it >> 1) : it) & 1));
+        } else {                                            // tail chunk, or X / D not fit for the bulk copy
+            const int64_t base = c * 32 * D;
+            const int nel = (int)min((int64_t)32 * D, N * D - base);
+            for (int e = lane; e < nel; e += 32) xs[(e / D) * ld + (e % D)] = X[base + e];
+            __syncwarp();
+        }
 
-        // ---- phase A: lane = frame
+        // ---- phase A: lane = frame, scores the k components of its own pool
         const int64_t n = c * 32 + lane;
         int s = (n < N) ? state[n] : -1;
         if (s >= G) s = -1;
@@ -124,26 +179,53 @@ pool_stats_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t *
 #pragma unroll
         for (int m = 0; m < KC; ++m) w[m] = 0.f;
         if (s >= 0) {
-            const float *xr = xs + lane * Dp;
-            const float *cg = cen + (size_t)s * KC * D;
-            const float *vg = (MODE == 0) ? vv + (size_t)s * KC * D : vv + (size_t)s * D;
+            const float *xr = xs + lane * ld;
+            const float *tg = tab + (size_t)s * D * 2 * KC;
             float ll[KC];
+            if constexpr (KC == 1) {
+                float acc = 0.f;
+#pragma unroll 13
+                for (int d = 0; d < D; ++d) {
+                    const float2 t = *reinterpret_cast<const float2 *>(tg + 2 * d);
+                    const float e = xr[d] + t.x;
+                    acc = fmaf(e * e, t.y, acc);
+                }
+                ll[0] = acc;
+            } else {
+                float2 acc[K2];
 #pragma unroll
-            for (int m = 0; m < KC; ++m) ll[m] = 0.f;
-#pragma unroll 3
-            for (int d = 0; d < D; ++d) {
-                const float x = xr[d];
+                for (int h = 0; h < K2; ++h) acc[h] = make_float2(0.f, 0.f);
+#pragma unroll 13
+                for (int d = 0; d < D; ++d) {
+                    const float x = xr[d];
+                    const float2 x2 = make_float2(x, x);
+                    const float4 *t4 = reinterpret_cast<const float4 *>(tg + (size_t)d * 2 * KC);
+                    if constexpr (KC == 2) {
+                        const float4 t = t4[0];                                   // {-c0, -c1, v0, v1}
+                        const float2 e = __fadd2_rn(x2, make_float2(t.x, t.y));
+                        acc[0] = __ffma2_rn(__fmul2_rn(e, e), make_float2(t.z, t.w), acc[0]);
+                    } else {
 #pragma unroll
-                for (int m = 0; m < KC; ++m) {
-                    const float e = x - cg[m * D + d];
-                    ll[m] = fmaf(e * e, (MODE == 0) ? vg[m * D + d] : vg[d], ll[m]);
+                        for (int h = 0; h < KC / 4; ++h) {
+                            const float4 tc = t4[h], tv = t4[KC / 4 + h];         // {-c[4h..4h+4)}, {v[4h..4h+4)}
+                            const float2 ea = __fadd2_rn(x2, make_float2(tc.x, tc.y));
+                            const float2 eb = __fadd2_rn(x2, make_float2(tc.z, tc.w));
+                            acc[2 * h] = __ffma2_rn(__fmul2_rn(ea, ea), make_float2(tv.x, tv.y), acc[2 * h]);
+                            acc[2 * h + 1] = __ffma2_rn(__fmul2_rn(eb, eb), make_float2(tv.z, tv.w), acc[2 * h + 1]);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int h = 0; h < K2; ++h) {
+                    ll[2 * h] = acc[h].x;
+                    ll[2 * h + 1] = acc[h].y;
                 }
             }
             if (MODE == 0) {
                 float mx = -CUDART_INF_F;
 #pragma unroll
                 for (int m = 0; m < KC; ++m) {
-                    ll[m] += aux[s * KC + m];
+                    ll[m] += shf[s * KC + m];                                     // log w - 0.5 log|2 pi var|
                     mx = fmaxf(mx, ll[m]);
                 }
                 float den = 0.f;
@@ -172,72 +254,136 @@ pool_stats_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t *
         } else if (MODE == 1 && argmin_out && n < N) {
             argmin_out[n] = -1;
         }
-
-        // ---- phase B: lanes = dimensions, loop over the frames of the chunk
-#pragma unroll 4
-        for (int j = 0; j < 32; ++j) {
-            const int sj = __shfl_sync(0xffffffffu, s, j);
-            if (sj != cur) {
-                flush();
-                cur = sj;
-                cnt = llsum = 0.f;
+        {   // the frame's record for phase B: {state, loglik, w[KC]}
+            float *r = rec + lane * RW;
+            if constexpr (KC == 1) {
+                *reinterpret_cast<float4 *>(r) = make_float4(__int_as_float(s), llf, w[0], 0.f);
+            } else {
+                *reinterpret_cast<float4 *>(r) = make_float4(__int_as_float(s), llf, w[0], w[1]);
 #pragma unroll
-                for (int m = 0; m < KC; ++m) {
-                    s0[m] = a0[m] = a1[m] = q0[m] = q1[m] = 0.f;
-                    if (sj >= 0) {
-                        const float *t = (MODE == 0 ? cen : aux) + ((size_t)sj * KC + m) * D;
-                        sh0[m] = h0 ? t[d0] : 0.f;
-                        sh1[m] = h1 ? t[d1] : 0.f;
-                    }
+                for (int h = 1; h < RW / 4; ++h) {
+                    const int b = 4 * h - 2;
+                    *reinterpret_cast<float4 *>(r + 4 * h) = make_float4(b < KC ? w[b] : 0.f, b + 1 < KC ? w[b + 1] : 0.f,
+                                                                         b + 2 < KC ? w[b + 2] : 0.f, b + 3 < KC ? w[b + 3] : 0.f);
                 }
-            }
-            float wj[KC];
-#pragma unroll
-            for (int m = 0; m < KC; ++m) wj[m] = __shfl_sync(0xffffffffu, w[m], j);
-            const float lj = (MODE == 0) ? __shfl_sync(0xffffffffu, llf, j) : 0.f;
-            if (sj < 0) continue;
-            const float x0 = h0 ? xs[j * Dp + d0] : 0.f, x1 = h1 ? xs[j * Dp + d1] : 0.f;
-            cnt += 1.f;
-            llsum += lj;
-#pragma unroll
-            for (int m = 0; m < KC; ++m) {
-                const float e0 = x0 - sh0[m], e1 = x1 - sh1[m];
-                s0[m] += wj[m];
-                a0[m] = fmaf(wj[m], e0, a0[m]);
-                a1[m] = fmaf(wj[m], e1, a1[m]);
-                q0[m] = fmaf(wj[m] * e0, e0, q0[m]);
-                q1[m] = fmaf(wj[m] * e1, e1, q1[m]);
             }
         }
         __syncwarp();
+
+        // ---- phase B: lanes = dimensions (d0, d1 packed in one float2).  The chunk is cut into runs of one state (a
+        // ballot of the state changes); a run's frames go through a branch-free loop, the accumulators are flushed
+        // between runs of different states and carried across chunks.  Runs of skipped frames (state < 0) cost nothing.
+        {
+            const int s_up = __shfl_up_sync(0xffffffffu, s, 1);
+            const unsigned starts = __ballot_sync(0xffffffffu, lane == 0 || s != s_up);
+            int j0 = 0;
+            while (j0 < 32) {
+                const unsigned rest = starts & ~((2u << j0) - 1u);
+                const int j1 = rest ? __ffs(rest) - 1 : 32;
+                const int sj = __shfl_sync(0xffffffffu, s, j0);
+                if (sj != cur) {
+                    flush();
+                    cur = sj;
+                    llsum = 0.f;
+                    run_frames = 0;
+#pragma unroll
+                    for (int m = 0; m < KC; ++m) {
+                        s0[m] = 0.f;
+                        a2[m] = q2[m] = make_float2(0.f, 0.f);
+                        if (sj >= 0) {
+                            if (MODE == 0) {
+                                const float *t = tab + (size_t)sj * D * 2 * KC + m;
+                                nsh[m] = make_float2(t[o0 * 2 * KC], t[o1 * 2 * KC]);
+                            } else {
+                                const float *t = shf + ((size_t)sj * KC + m) * D;
+                                nsh[m] = make_float2(t[o0], t[o1]);
+                            }
+                        }
+                    }
+                }
+                if (sj >= 0) {
+                    run_frames += j1 - j0;
+                    const float *xp0 = xs + j0 * ld + o0, *xp1 = xs + j0 * ld + o1;
+                    const float *rp = rec + j0 * RW;
+#pragma unroll 4
+                    for (int j = j0; j < j1; ++j, xp0 += ld, xp1 += ld, rp += RW) {
+                        const float4 r0 = *reinterpret_cast<const float4 *>(rp);  // broadcast {state, loglik, w0, w1}
+                        float wj[KC];
+                        if constexpr (KC == 1) {
+                            wj[0] = r0.z;
+                        } else {
+                            wj[0] = r0.z;
+                            wj[1] = r0.w;
+#pragma unroll
+                            for (int h = 1; h < RW / 4; ++h) {
+                                const float4 rh = *reinterpret_cast<const float4 *>(rp + 4 * h);
+                                const int b = 4 * h - 2;
+                                if (b < KC) wj[b] = rh.x;
+                                if (b + 1 < KC) wj[b + 1] = rh.y;
+                                if (b + 2 < KC) wj[b + 2] = rh.z;
+                                if (b + 3 < KC) wj[b + 3] = rh.w;
+                            }
+                        }
+                        const float2 x2 = make_float2(*xp0, *xp1);
+                        if (MODE == 0) llsum += r0.y;
+#pragma unroll
+                        for (int m = 0; m < KC; ++m) {
+                            const float2 w2 = make_float2(wj[m], wj[m]);
+                            const float2 e = __fadd2_rn(x2, nsh[m]);
+                            s0[m] += wj[m];
+                            a2[m] = __ffma2_rn(w2, e, a2[m]);
+                            q2[m] = __ffma2_rn(__fmul2_rn(w2, e), e, q2[m]);
+                        }
+                    }
+                }
+                j0 = j1;
+            }
+        }
+        __syncwarp();                                       // every lane is done with xs[stg] and rec
+
+        // ---- refill this stage with the chunk nst rounds ahead
+        if (bulk && lane == 0) {
+            const int64_t cn = c + nst;
+            if (cn < c_end && cn < nfull) {
+                bar_expect_tx(&bars[stg], chunk_bytes);
+                bulk_load(xs, X + cn * 32 * D, chunk_bytes, &bars[stg]);
+            }
+        }
     }
     flush();
 }
 
-// out[i] (+)= sum_p partial[p][i] in double, fixed order: 8 lanes of slices per element, slice p goes to lane p % 8,
-// the 8 partial sums are added in lane order.
+// out[G*M rows] (+)= sum over the slices [G*k rows] in double, fixed order: 8 lanes of slices per element, slice p goes
+// to lane p % 8, the 8 partial sums are added in lane order.  Rows of the untrained components (m >= k) get zero.
 __global__ void __launch_bounds__(256)
-reduce_slices8_kernel(const float *__restrict__ partial, int64_t nparts, int64_t len, double *__restrict__ out,
-                      int accumulate) {
+reduce_slices8_kernel(const float *__restrict__ partial, int64_t nparts, int M, int k, int row, int64_t len_out,
+                      double *__restrict__ out, int accumulate) {
     __shared__ double part[8][32];
     const int e = threadIdx.x & 31, j = threadIdx.x >> 5;
     const int64_t i = (int64_t)blockIdx.x * 32 + e;
     double s = 0.0;
-    if (i < len) {
-        int64_t p = j;
-        for (; p + 24 < nparts; p += 32) {
-            const float v0 = partial[p * len + i], v1 = partial[(p + 8) * len + i], v2 = partial[(p + 16) * len + i],
-                        v3 = partial[(p + 24) * len + i];
-            s += (double)v0;
-            s += (double)v1;
-            s += (double)v2;
-            s += (double)v3;
+    bool live = false;
+    if (i < len_out) {
+        const int64_t g = i / ((int64_t)M * row);
+        const int r = (int)(i - g * M * row), m = r / row, col = r - m * row;
+        live = m < k;
+        if (live) {
+            const int64_t len = len_out / M * k, src = (g * k + m) * row + col;
+            int64_t p = j;
+            for (; p + 24 < nparts; p += 32) {
+                const float v0 = partial[p * len + src], v1 = partial[(p + 8) * len + src],
+                            v2 = partial[(p + 16) * len + src], v3 = partial[(p + 24) * len + src];
+                s += (double)v0;
+                s += (double)v1;
+                s += (double)v2;
+                s += (double)v3;
+            }
+            for (; p < nparts; p += 8) s += (double)partial[p * len + src];
         }
-        for (; p < nparts; p += 8) s += (double)partial[p * len + i];
     }
     part[j][e] = s;
     __syncthreads();
-    if (j == 0 && i < len) {
+    if (j == 0 && i < len_out) {
         double t = accumulate ? out[i] : 0.0;
 #pragma unroll
         for (int q = 0; q < 8; ++q) t += part[q][e];
@@ -245,27 +391,19 @@ reduce_slices8_kernel(const float *__restrict__ partial, int64_t nparts, int64_t
     }
 }
 
-size_t smem_bytes(int G, int k, int D, int mode) {
-    const size_t gkd = (size_t)G * k * D;
-    const size_t tables = mode == 0 ? 2 * gkd + (size_t)G * k : 2 * gkd + (size_t)G * D;
-    return (tables + (size_t)PW * 32 * (D | 1)) * sizeof(float);
-}
+size_t smem_bytes(int G, int k, int D, int mode, int nst = 1) { return pool_layout(G, k, D, mode, nst).bytes; }
 
 int pow2_at_least(int k) { return k <= 1 ? 1 : k <= 2 ? 2 : k <= 4 ? 4 : 8; }
 
 template <int KC, int MODE>
 int launch(const float *X, int64_t N, int D, const int32_t *state, int G, int M, const double *center, const double *var,
-           const double *lc, const double *shift, float *partial, int32_t *argmin_out, int grid, size_t smem,
-           cudaStream_t st) {
-    if (D <= 40) {
-        auto kfn = pool_stats_kernel<KC, MODE, 40>;
-        SRB_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        kfn<<<grid, PW * 32, smem, st>>>(X, N, D, state, G, M, center, var, lc, shift, partial, argmin_out);
-    } else {
-        auto kfn = pool_stats_kernel<KC, MODE, 64>;
-        SRB_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        kfn<<<grid, PW * 32, smem, st>>>(X, N, D, state, G, M, center, var, lc, shift, partial, argmin_out);
-    }
+           const double *lc, const double *shift, float *partial, int32_t *argmin_out, int grid, cudaStream_t st) {
+    const int nst = smem_bytes(G, KC, D, MODE, 2) <= (size_t)MAX_SMEM ? 2 : 1;
+    const size_t smem = smem_bytes(G, KC, D, MODE, nst);
+    const int bulk = (D & 1) && (reinterpret_cast<uintptr_t>(X) & 15) == 0;     // dense odd rows, 16-byte aligned source
+    auto kfn = pool_stats_kernel<KC, MODE>;
+    SRB_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kfn<<<grid, PW * 32, smem, st>>>(X, N, D, state, G, M, center, var, lc, shift, partial, argmin_out, nst, bulk);
     return SRB_OK;
 }
 
@@ -276,7 +414,7 @@ using namespace srb;
 
 extern "C" {
 
-int srb_pool_stats_parts(void) { return sm_count() * PW; }
+int srb_pool_stats_parts(void) { return sm_count() * PW; }   // private slices of G*k rows (G*M rows of scratch always suffice)
 
 int srb_pool_stats_supported(int G, int k, int D) {
     return G > 0 && k >= 1 && k <= 8 && D > 0 && D <= 64 && smem_bytes(G, pow2_at_least(k), D, 1) <= (size_t)MAX_SMEM &&
@@ -298,15 +436,16 @@ int srb_pool_stats(const float *X, int64_t N, int D, const int32_t *state, int G
                 "memory (limit %d); use srb_kmeans_assign + srb_group_stats / srb_gmm_stats", G, k, D, smem, MAX_SMEM);
     const int grid = sm_count();
     SRB_REQUIRE(grid > 0, SRB_ENODEVICE, "no CUDA device");
-    const int64_t len = (int64_t)G * M * (2 * D + 3), parts = (int64_t)grid * PW;
+    const int row = 2 * D + 3;
+    const int64_t len_out = (int64_t)G * M * row, len = (int64_t)G * k * row, parts = (int64_t)grid * PW;
     cudaStream_t st = (cudaStream_t)stream;
     SRB_CUDA(cudaMemsetAsync(partial, 0, sizeof(float) * len * parts, st));
     if (N > 0) {
         int rc = SRB_OK;
 #define SRB_POOL_CASE(KC)                                                                                              \
     case KC:                                                                                                           \
-        rc = mode == 0 ? launch<KC, 0>(X, N, D, state, G, M, center, var, lc, shift, partial, argmin_out, grid, smem, st) \
-                       : launch<KC, 1>(X, N, D, state, G, M, center, var, lc, shift, partial, argmin_out, grid, smem, st); \
+        rc = mode == 0 ? launch<KC, 0>(X, N, D, state, G, M, center, var, lc, shift, partial, argmin_out, grid, st) \
+                       : launch<KC, 1>(X, N, D, state, G, M, center, var, lc, shift, partial, argmin_out, grid, st); \
         break;
         switch (k) {
             SRB_POOL_CASE(1)
@@ -317,7 +456,7 @@ int srb_pool_stats(const float *X, int64_t N, int D, const int32_t *state, int G
 #undef SRB_POOL_CASE
         if (rc != SRB_OK) return rc;
     }
-    reduce_slices8_kernel<<<(int)((len + 31) / 32), 256, 0, st>>>(partial, parts, len, out, accumulate);
+    reduce_slices8_kernel<<<(int)((len_out + 31) / 32), 256, 0, st>>>(partial, parts, M, k, row, len_out, out, accumulate);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }

@@ -157,6 +157,26 @@ def test_pool_em_stats_equals_gmm_stats(eng, k):
     np.testing.assert_array_equal(got[:, 2 * D + 1], ref[:, 2 * D + 1])            # frame counts
     np.testing.assert_allclose(got[:, 2 * D + 2], ref[:, 2 * D + 2], rtol=1e-5)    # summed log-likelihood
     assert not got.reshape(55, 4, -1)[:, k:].any()                                 # untrained components untouched
+    # a source that is not 16-byte aligned (row 1 of the device tensor) takes the plain-load path: same numbers as the
+    # TMA path on the same frames
+    import torch
+    Xd, labd = torch.from_numpy(X).cuda(), torch.from_numpy(lab).cuda()
+    a = eng.pool_em_stats(Xd[1:], labd[1:], pm, k).cpu().numpy()
+    b = eng.pool_em_stats(Xd[1:].clone(), labd[1:].clone(), pm, k).cpu().numpy()
+    assert Xd[1:].data_ptr() % 16 != 0 and np.array_equal(a, b)
+
+
+def test_pool_stats_even_dimension(eng):
+    """D = 24 (even: padded rows, no bulk copy) and k = 8 against srb_gmm_stats."""
+    rng = np.random.default_rng(4)
+    G, M, D, N = 7, 8, 24, 5000
+    X = rng.normal(size=(N, D)).astype(np.float32)
+    lab = np.sort(rng.integers(-1, G, N)).astype(np.int32)
+    pm = eng.PackedModel(rng.normal(size=(G, M, D)), rng.uniform(0.5, 2.0, size=(G, M, D)), np.full((G, M), 1.0 / M))
+    ref = eng.gmm_stats(X, lab, pm, 8).cpu().numpy()
+    got = eng.pool_em_stats(X, lab, pm, 8).cpu().numpy()
+    scale = np.abs(ref[:, 1 + D:1 + 2 * D]).max(axis=1, keepdims=True) + 1e-30
+    assert np.max(np.abs(got - ref)[:, :1 + 2 * D] / np.maximum(scale, np.abs(ref[:, :1]))) < 2e-5
 
 
 @pytest.mark.parametrize("k", [2, 4])
