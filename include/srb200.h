@@ -349,6 +349,22 @@ int srb_pool_stats(const float *X, int64_t N, int D, const int32_t *state, int G
                    const double *center, const double *var, const double *lc, const double *shift, float *partial,
                    double *out, int32_t *argmin_out, int accumulate, void *stream);
 
+/* Per-iteration updates of the batched HMM.fit, one CTA per pool, float64 without fused multiply-adds (the reference's
+ * numpy arithmetic operation by operation, so a pool stops at the iteration the reference's loop would):
+ *   srb_fit_em_update      GMM.em's M-step + stop test (hmm_state.py:138-159) on the first k components of every ACTIVE
+ *                          state from stats double[G*M, row]: mu += S1/S0, var = S2/S0 - (S1/S0)^2, w = S0/count
+ *                          (components with S0 == 0 stay); a state whose new parameters satisfy np.allclose (atol 1e-8,
+ *                          rtol 1e-5) against *_old is frozen (active[g] = 0), else *_old <- new.  its[g] = it for the
+ *                          states that were active.  lc double[G*M] <- srb_gauss_consts of the updated model.
+ *   srb_fit_kmeans_update  kmeans.py:187-192 from stats double[G*k, row]: new centroid = shift + S1/S0; an active pool
+ *                          whose new centroids equal cen exactly (np.array_equal) is frozen, else cen <- new;
+ *                          cnt double[G*k] <- cluster sizes of the pools that were active. */
+int srb_fit_em_update(const double *stats, int G, int M, int k, int D, double *mu, double *var, double *w, double *mu_old,
+                      double *var_old, double *w_old, uint8_t *active, int64_t *its, int64_t it, double *lc,
+                      void *stream);
+int srb_fit_kmeans_update(const double *stats, int G, int k, int D, const double *shift, double *cen, uint8_t *active,
+                          int64_t *its, int64_t it, double *cnt, void *stream);
+
 /* M-step of GMM.em (hmm_state.py:138-148) in place on mu/var/w double (first ncomp components per state):
  * mu += S1/S0, var = S2/S0 - (S1/S0)^2 (floored at var_floor), w = S0/count. */
 int srb_mstep(const double *stats, int R, int M, int ncomp, int D, double *mu, double *var, double *w,

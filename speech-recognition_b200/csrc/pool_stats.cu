@@ -353,12 +353,12 @@ pool_stats_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t *
     flush();
 }
 
-// out[G*M rows] (+)= sum over the slices [G*k rows] in double, fixed order: 8 lanes of slices per element, slice p goes
-// to lane p % 8, the 8 partial sums are added in lane order.  Rows of the untrained components (m >= k) get zero.
-__global__ void __launch_bounds__(256)
-reduce_slices8_kernel(const float *__restrict__ partial, int64_t nparts, int M, int k, int row, int64_t len_out,
+// out[G*M rows] (+)= sum over the slices [G*k rows] in double, fixed order: 32 lanes of slices per element, slice p
+// goes to lane p % 32, the 32 partial sums are added in lane order.  Rows of the untrained components (m >= k) get zero.
+__global__ void __launch_bounds__(1024)
+reduce_slices32_kernel(const float *__restrict__ partial, int64_t nparts, int M, int k, int row, int64_t len_out,
                       double *__restrict__ out, int accumulate) {
-    __shared__ double part[8][32];
+    __shared__ double part[32][33];
     const int e = threadIdx.x & 31, j = threadIdx.x >> 5;
     const int64_t i = (int64_t)blockIdx.x * 32 + e;
     double s = 0.0;
@@ -370,15 +370,15 @@ reduce_slices8_kernel(const float *__restrict__ partial, int64_t nparts, int M, 
         if (live) {
             const int64_t len = len_out / M * k, src = (g * k + m) * row + col;
             int64_t p = j;
-            for (; p + 24 < nparts; p += 32) {
-                const float v0 = partial[p * len + src], v1 = partial[(p + 8) * len + src],
-                            v2 = partial[(p + 16) * len + src], v3 = partial[(p + 24) * len + src];
+            for (; p + 96 < nparts; p += 128) {
+                const float v0 = partial[p * len + src], v1 = partial[(p + 32) * len + src],
+                            v2 = partial[(p + 64) * len + src], v3 = partial[(p + 96) * len + src];
                 s += (double)v0;
                 s += (double)v1;
                 s += (double)v2;
                 s += (double)v3;
             }
-            for (; p < nparts; p += 8) s += (double)partial[p * len + src];
+            for (; p < nparts; p += 32) s += (double)partial[p * len + src];
         }
     }
     part[j][e] = s;
@@ -386,7 +386,7 @@ reduce_slices8_kernel(const float *__restrict__ partial, int64_t nparts, int M, 
     if (j == 0 && i < len_out) {
         double t = accumulate ? out[i] : 0.0;
 #pragma unroll
-        for (int q = 0; q < 8; ++q) t += part[q][e];
+        for (int q = 0; q < 32; ++q) t += part[q][e];
         out[i] = t;
     }
 }
@@ -456,7 +456,7 @@ int srb_pool_stats(const float *X, int64_t N, int D, const int32_t *state, int G
 #undef SRB_POOL_CASE
         if (rc != SRB_OK) return rc;
     }
-    reduce_slices8_kernel<<<(int)((len_out + 31) / 32), 256, 0, st>>>(partial, parts, M, k, row, len_out, out, accumulate);
+    reduce_slices32_kernel<<<(int)((len_out + 31) / 32), 1024, 0, st>>>(partial, parts, M, k, row, len_out, out, accumulate);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }

@@ -731,14 +731,15 @@ def _pool_partial(groups, D, dev):
     return buf
 
 
-def pool_em_stats(X, state, pm, k):
+def pool_em_stats(X, state, pm, k, lc=None):
     """srb_pool_stats mode 0: E-step statistics of GMM.em for every state at once, frames hard-assigned to states
-    (same rows as gmm_stats: double [R*M, 2D+3])."""
+    (same rows as gmm_stats: double [R*M, 2D+3]).  lc: the model's constants when the caller keeps them current."""
     X = as_frames(X)
     dev = X.device
     state = _i32(state, dev)
     L = _l.load()
-    lc = gauss_consts(pm.var, pm.w)
+    if lc is None:
+        lc = gauss_consts(pm.var, pm.w)
     out = torch.empty((pm.R * pm.M, L.srb_stats_row(pm.D)), dtype=torch.float64, device=dev)
     _l.check(L.srb_pool_stats(_l.ptr(X), X.shape[0], pm.D, _l.ptr(state), pm.R, pm.M, int(k), 0, _l.ptr(pm.mu),
                               _l.ptr(pm.var), _l.ptr(lc), None, _l.ptr(_pool_partial(pm.R * pm.M, pm.D, dev)), _l.ptr(out),
@@ -761,6 +762,21 @@ def pool_kmeans_stats(X, state, centroids, var0, shift, want_argmin=False):
     _l.check(L.srb_pool_stats(_l.ptr(X), X.shape[0], D, _l.ptr(state), G, k, k, 1, _l.ptr(c), _l.ptr(v), None, _l.ptr(sh),
                               _l.ptr(_pool_partial(G * k, D, dev)), _l.ptr(out), _l.ptr(am), 0, _l.stream_ptr()))
     return (out, am) if want_argmin else out
+
+
+def fit_em_update(stats, pm, k, old, active, its, it, lc):
+    """srb_fit_em_update: M-step + np.allclose stop test of GMM.em for every active state, in place on pm.mu / pm.var /
+    pm.w (double), old = [mu_old, var_old, w_old], active bool[G], its int64[G], lc double[G*M]."""
+    _l.check(_l.load().srb_fit_em_update(_l.ptr(stats), pm.R, pm.M, int(k), pm.D, _l.ptr(pm.mu), _l.ptr(pm.var), _l.ptr(pm.w),
+                                         _l.ptr(old[0]), _l.ptr(old[1]), _l.ptr(old[2]), _l.ptr(active), _l.ptr(its), int(it),
+                                         _l.ptr(lc), _l.stream_ptr()))
+
+
+def fit_kmeans_update(stats, shift, cen, active, its, it, cnt):
+    """srb_fit_kmeans_update: centroid update + np.array_equal stop test for every active pool, in place on cen [G,k,D]."""
+    G, k, D = (int(t) for t in cen.shape)
+    _l.check(_l.load().srb_fit_kmeans_update(_l.ptr(stats), G, k, D, _l.ptr(shift), _l.ptr(cen), _l.ptr(active), _l.ptr(its),
+                                             int(it), _l.ptr(cnt), _l.stream_ptr()))
 
 
 def mstep(stats, pm, ncomp, var_floor=0.0):

@@ -254,12 +254,13 @@ class WordFitter:
                 idx = torch.nonzero(active[self.state.long()]).squeeze(1)
                 self.X, self.state, self.n = self.X[idx].contiguous(), self.state[idx].contiguous(), int(idx.numel())
 
-    CHECK_EVERY = 4          # iterations between two host reads of the running-state count
+    CHECK_EVERY = 8          # iterations between two host reads of the running-state count
 
     def _kmeans(self, state, k, cen, cov0, active, max_iteration):
         """kmeans.py:178-193 for every pool at once: a pool stops at the iteration where its new centroids equal the
         previous ones (np.array_equal, :190) and keeps those.  -> (centroids [G,k,D] device, counts [G,k] numpy, its[G])"""
         G, D = cen.shape[0], self.D
+        cen = cen.contiguous().clone()
         shift = cen.clone().reshape(G * k, D)
         fused = engine.pool_stats_supported(G, k, D)          # one pass over X per iteration instead of two
         ws = self._WorkingSet(self, state)
@@ -275,13 +276,7 @@ class WordFitter:
             else:
                 st = zero.clone()
             st = _allreduce(st, self.group)
-            c = st[:, 0].reshape(G, k)
-            new_c = (shift + st[:, 1:1 + D] / st[:, :1]).reshape(G, k, D)
-            same = (new_c == cen).flatten(1).all(dim=1)                           # NaN never equal, like np.array_equal
-            its = torch.where(active, it, its)
-            cnt = torch.where(active[:, None], c, cnt)
-            active = active & ~same
-            cen = torch.where(active[:, None, None], new_c, cen)
+            engine.fit_kmeans_update(st, shift, cen, active, its, it, cnt)
             if it % self.CHECK_EVERY == self.CHECK_EVERY - 1:
                 n_run = int(active.sum().item())
                 if self.verbose:
@@ -291,43 +286,26 @@ class WordFitter:
                 ws.maybe_compact(active)
         return cen, cnt.cpu().numpy(), its.cpu().numpy()
 
-    @staticmethod
-    def _allclose(a, b):
-        """np.allclose(a, b) per leading index: |a - b| <= 1e-8 + 1e-5 |b| everywhere (NaN -> False)."""
-        return ((a - b).abs() <= 1e-8 + 1e-5 * b.abs()).flatten(1).all(dim=1)
-
     def _em(self, pm, state, k, active, max_iteration):
         """GMM.em (hmm_state.py:122-159) over the first k components of every state at once; a state stops at the
         iteration where the reference's loop would (np.allclose of the new parameters with the previous ones) and is
         frozen from then on.  Updates pm.mu / pm.var / pm.w in place.  -> its[G] (last iteration index of every state)"""
         G, M, D = pm.mu.shape
-        mu, var, w = pm.mu[:, :k], pm.var[:, :k], pm.w[:, :k]                    # views
-        mu_old, var_old, w_old = (t[:, :k] for t in self._old)
         ws = self._WorkingSet(self, state)
         its = torch.zeros(G, dtype=torch.int64, device=self.dev)
         row = 2 * D + 3
         fused = engine.pool_stats_supported(G, k, D)
         zero = torch.zeros((G * M, row), dtype=torch.float64, device=self.dev)
+        lc = engine.gauss_consts(pm.var, pm.w)
         for it in range(max_iteration):
-            st = (engine.pool_em_stats if fused else engine.gmm_stats)(ws.X, ws.state, pm, k) if ws.n else zero.clone()
-            st = _allreduce(st, self.group).reshape(G, M, row)
-            S0 = st[:, :k, 0]
-            cntg = st[:, 0, 2 * D + 1]
-            m1 = st[:, :k, 1:1 + D] / S0[:, :, None]
-            nmu = mu + m1
-            nvar = st[:, :k, 1 + D:1 + 2 * D] / S0[:, :, None] - m1 * m1
-            nw = S0 / cntg[:, None]
-            ok = (S0 > 0) & active[:, None]                                       # empty components stay (DESIGN 5 ii)
-            mu.copy_(torch.where(ok[:, :, None], nmu, mu))
-            var.copy_(torch.where(ok[:, :, None], nvar, var))
-            w.copy_(torch.where(ok & (cntg > 0)[:, None], nw, w))
-            conv = self._allclose(mu, mu_old) & self._allclose(var, var_old) & self._allclose(w, w_old)
-            its = torch.where(active, it, its)
-            active = active & ~conv
-            mu_old.copy_(torch.where(active[:, None, None], mu, mu_old))
-            var_old.copy_(torch.where(active[:, None, None], var, var_old))
-            w_old.copy_(torch.where(active[:, None], w, w_old))
-            pm.repack()
+            if not ws.n:
+                st = zero.clone()
+            elif fused:
+                st = engine.pool_em_stats(ws.X, ws.state, pm, k, lc=lc)
+            else:
+                st = engine.gmm_stats(ws.X, ws.state, pm, k)
+            st = _allreduce(st, self.group)
+            engine.fit_em_update(st, pm, k, self._old, active, its, it, lc)       # M-step, stop test, freeze, new lc
             if it % self.CHECK_EVERY == self.CHECK_EVERY - 1:
                 n_run = int(active.sum().item())
                 if self.verbose and (it < 64 or it % 256 == 255 or not n_run):
@@ -335,6 +313,7 @@ class WordFitter:
                 if not n_run:
                     break
                 ws.maybe_compact(active)
+        pm.repack()
         return its.cpu().numpy()
 
     # ------------------------------------------------------------------------------------------ phase 3: re-alignment

@@ -343,7 +343,7 @@ def pool_stats_supported(G, k, D):
     return k in (1, 2, 4, 8)
 
 
-def pool_em_stats(X, state, pm, k):
+def pool_em_stats(X, state, pm, k, lc=None):
     return gmm_stats(X, state, pm, k)
 
 
@@ -357,10 +357,59 @@ def pool_kmeans_stats(X, state, centroids, var0, shift, want_argmin=False):
     return (out, am) if want_argmin else out
 
 
+def gauss_consts(var, w):
+    v, ww = _np(var, np.float64), _np(w, np.float64)
+    G = ww.size
+    v = v.reshape(G, -1)
+    with np.errstate(divide="ignore"):
+        return torch.from_numpy(np.log(ww.reshape(G)) - 0.5 * (v.shape[1] * np.log(2 * np.pi) + np.log(v).sum(1)))
+
+
+def _allclose_rows(a, b):
+    return ((a - b).abs() <= 1e-8 + 1e-5 * b.abs()).flatten(1).all(dim=1)
+
+
+def fit_em_update(stats, pm, k, old, active, its, it, lc):
+    """numpy-semantics stand-in of srb_fit_em_update (float64 torch on the CPU), in place."""
+    G, M, D = pm.mu.shape
+    st = stats.reshape(G, M, 2 * D + 3)
+    mu, var, w = pm.mu[:, :k], pm.var[:, :k], pm.w[:, :k]
+    mu_old, var_old, w_old = (t[:, :k] for t in old)
+    S0 = st[:, :k, 0]
+    cntg = st[:, 0, 2 * D + 1]
+    m1 = st[:, :k, 1:1 + D] / S0[:, :, None]
+    nmu = mu + m1
+    nvar = st[:, :k, 1 + D:1 + 2 * D] / S0[:, :, None] - m1 * m1
+    nw = S0 / cntg[:, None]
+    ok = (S0 > 0) & active[:, None]
+    mu.copy_(torch.where(ok[:, :, None], nmu, mu))
+    var.copy_(torch.where(ok[:, :, None], nvar, var))
+    w.copy_(torch.where(ok & (cntg > 0)[:, None], nw, w))
+    conv = _allclose_rows(mu, mu_old) & _allclose_rows(var, var_old) & _allclose_rows(w, w_old)
+    its.copy_(torch.where(active, torch.full_like(its, it), its))
+    active.copy_(active & ~conv)
+    mu_old.copy_(torch.where(active[:, None, None], mu, mu_old))
+    var_old.copy_(torch.where(active[:, None, None], var, var_old))
+    w_old.copy_(torch.where(active[:, None], w, w_old))
+    lc.copy_(gauss_consts(pm.var, pm.w).reshape(lc.shape))
+
+
+def fit_kmeans_update(stats, shift, cen, active, its, it, cnt):
+    G, k, D = cen.shape
+    c = stats[:, 0].reshape(G, k)
+    new_c = (shift + stats[:, 1:1 + D] / stats[:, :1]).reshape(G, k, D)
+    same = (new_c == cen).flatten(1).all(dim=1)
+    its.copy_(torch.where(active, torch.full_like(its, it), its))
+    cnt.copy_(torch.where(active[:, None], c, cnt))
+    active.copy_(active & ~same)
+    cen.copy_(torch.where(active[:, None, None], new_c, cen))
+
+
 def install(monkeypatch):
     """Replace the device entry points of srb200.engine for the duration of one test."""
     from srb200 import engine
     for name in ("device", "PackedModel", "as_frames", "as_offsets", "gmm_score", "viterbi", "classify",
                  "group_stats", "moments_from_stats", "gmm_stats", "mstep", "local_dist", "dtw_beam", "kmeans_assign",
-                 "pool_stats_supported", "pool_em_stats", "pool_kmeans_stats"):
+                 "pool_stats_supported", "pool_em_stats", "pool_kmeans_stats",
+                 "gauss_consts", "fit_em_update", "fit_kmeans_update"):
         monkeypatch.setattr(engine, name, globals()[name])

@@ -215,3 +215,61 @@ def test_pool_stats_rejects_tables_beyond_shared_memory(eng):
     big = np.zeros((400, 8, 39))
     with pytest.raises(_l.SrbError):
         eng.pool_kmeans_stats(X, lab, big, np.ones((400, 39)), big.reshape(-1, 39))
+
+
+def test_fit_update_kernels_equal_numpy_semantics(eng):
+    """srb_fit_em_update / srb_fit_kmeans_update against the float64 torch-on-CPU statement of the same updates
+    (tests/engine_double.py): bit-identical parameters, same stop decisions, frozen states untouched."""
+    import torch
+    import engine_double as ed
+    rng = np.random.default_rng(12)
+    G, M, k, D = 9, 4, 2, 39
+    row = 2 * D + 3
+    mu, var = rng.normal(size=(G, M, D)), rng.uniform(0.5, 2.0, size=(G, M, D))
+    w = np.full((G, M), 0.25)
+    st = np.zeros((G, M, row))
+    st[:, :k, 0] = rng.uniform(50, 500, size=(G, k))
+    st[:, :k, 1:1 + D] = rng.normal(scale=1e-3, size=(G, k, D)) * st[:, :k, :1]
+    st[:, :k, 1 + D:1 + 2 * D] = rng.uniform(0.5, 2.0, size=(G, k, D)) * st[:, :k, :1]
+    st[:, 0, 2 * D + 1] = st[:, :k, 0].sum(axis=1)
+    st[3, 1, 0] = 0.0                                                   # an empty component stays
+    st[5, :k, 1:1 + D] = 0.0                                            # state 5: nothing moves -> converges when old == new
+    active = np.ones(G, bool)
+    active[7] = False                                                   # frozen before
+    pm_d, pm_h = eng.PackedModel(mu, var, w), ed.PackedModel(mu, var, w)
+    old_d = [pm_d.mu.clone(), pm_d.var.clone(), pm_d.w.clone()]
+    old_h = [pm_h.mu.clone(), pm_h.var.clone(), pm_h.w.clone()]
+    var5 = st[5, :k, 1 + D:1 + 2 * D] / st[5, :k, :1]                   # make state 5's old variances/weights the new ones
+    for o in (old_d, old_h):
+        o[1][5, :k] = torch.from_numpy(var5).to(o[1].device)
+        o[2][5, :k] = torch.from_numpy(st[5, :k, 0] / st[5, 0, 2 * D + 1]).to(o[2].device)
+    a_d, a_h = torch.from_numpy(active.copy()).cuda(), torch.from_numpy(active.copy())
+    its_d, its_h = torch.zeros(G, dtype=torch.int64).cuda(), torch.zeros(G, dtype=torch.int64)
+    lc_d, lc_h = torch.zeros(G * M, dtype=torch.float64).cuda(), torch.zeros(G * M, dtype=torch.float64)
+    st_t = torch.from_numpy(st.reshape(G * M, row))
+    eng.fit_em_update(st_t.cuda(), pm_d, k, old_d, a_d, its_d, 17, lc_d)
+    ed.fit_em_update(st_t, pm_h, k, old_h, a_h, its_h, 17, lc_h)
+    for x, y in zip([pm_d.mu, pm_d.var, pm_d.w] + old_d, [pm_h.mu, pm_h.var, pm_h.w] + old_h):
+        assert np.array_equal(x.cpu().numpy(), y.numpy())
+    assert np.array_equal(a_d.cpu().numpy(), a_h.numpy()) and not a_h[5] and not a_h[7] and a_h[0]
+    assert np.array_equal(its_d.cpu().numpy(), its_h.numpy()) and its_h[7] == 0 and its_h[5] == 17
+    np.testing.assert_allclose(lc_d.cpu().numpy(), lc_h.numpy(), rtol=1e-13)
+    # K-means update
+    cen = rng.normal(size=(G, k, D))
+    shift = cen + rng.normal(scale=0.01, size=cen.shape)
+    sk = np.zeros((G * k, row))
+    sk[:, 0] = rng.integers(10, 90, G * k)
+    sk[:, 1:1 + D] = rng.normal(size=(G * k, D))
+    nc = shift.reshape(G * k, D) + sk[:, 1:1 + D] / sk[:, :1]
+    cen[2] = nc.reshape(G, k, D)[2]                                     # pool 2 is at its fixed point
+    outs = []
+    for dev, mod in (("cuda", eng), ("cpu", ed)):
+        c = torch.from_numpy(cen.copy()).to(dev)
+        a = torch.from_numpy(active.copy()).to(dev)
+        i_ = torch.zeros(G, dtype=torch.int64, device=dev)
+        n_ = torch.zeros((G, k), dtype=torch.float64, device=dev)
+        mod.fit_kmeans_update(torch.from_numpy(sk).to(dev), torch.from_numpy(shift.reshape(G * k, D)).to(dev), c, a, i_, 4, n_)
+        outs.append([t.cpu().numpy() for t in (c, a, i_, n_)])
+    for x, y in zip(*outs):
+        assert np.array_equal(x, y)
+    assert not outs[0][1][2] and not outs[0][1][7] and outs[0][1][0] and outs[0][3][7].sum() == 0
