@@ -159,6 +159,7 @@ pool_stats_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t *
     // lanes without a dimension (d >= D) read column 0 and feed accumulators that are never flushed
     const int o0 = h0 ? d0 : 0, o1 = h1 ? d1 : 0;
     int it = 0;
+    int s_next = (c_begin < c_end && c_begin * 32 + lane < N) ? state[c_begin * 32 + lane] : -1;
     for (int64_t c = c_begin; c < c_end; ++c, ++it) {
         const int stg = (nst == 2) ? (it & 1) : 0;
         float *xs = xs0 + (size_t)stg * L.stage;
@@ -171,9 +172,13 @@ pool_stats_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t *
             __syncwarp();
         }
 
-        // ---- phase A: lane = frame, scores the k components of its own pool
+        // ---- phase A: lane = frame, scores the k components of its own pool (its label was fetched a chunk ahead)
         const int64_t n = c * 32 + lane;
-        int s = (n < N) ? state[n] : -1;
+        int s = s_next;
+        {
+            const int64_t nn = n + 32;
+            s_next = (c + 1 < c_end && nn < N) ? state[nn] : -1;
+        }
         if (s >= G) s = -1;
         float w[KC], llf = 0.f;
 #pragma unroll
