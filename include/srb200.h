@@ -340,10 +340,13 @@ int srb_kmeans_assign(const float *X, int64_t N, int D, const int32_t *group, co
  *   mode 1  kmeans.py:180-187: weights = one-hot first minimum of mahalanobis(center_c, x, var[pool]) with the ONE
  *           variance row var double[G, D] per pool (kmeans.py:183), moments about shift double[G*M, D]; M must equal
  *           k.  Same results as srb_kmeans_assign followed by srb_group_stats; argmin_out int32[N] optional (-1 = skipped).
- * partial: caller scratch of srb_pool_stats_parts() * G*M * srb_stats_row(D) floats.  The parameter tables live in
- * shared memory: srb_pool_stats_supported(G, k, D) says whether they fit (55 pools x 4 x 39 do), else SRB_EUNSUPPORTED.
+ * partial: caller scratch of srb_pool_stats_partial_floats(G, k, D) floats, 8-byte aligned (srb_pool_stats_parts() private
+ * slices of G*k rows, one per warp, and one 64-bit pool mask per slice: with G <= 64 the slices are write-once and the
+ * reduction skips the pools a warp never met).  The parameter tables live in shared memory:
+ * srb_pool_stats_supported(G, k, D) says whether they fit (55 pools x 4 x 39 do), else SRB_EUNSUPPORTED.
  * Deterministic: private slices, fixed-order double reduction. */
 int srb_pool_stats_parts(void);
+int64_t srb_pool_stats_partial_floats(int G, int k, int D);
 int srb_pool_stats_supported(int G, int k, int D);
 int srb_pool_stats(const float *X, int64_t N, int D, const int32_t *state, int G, int M, int k, int mode,
                    const double *center, const double *var, const double *lc, const double *shift, float *partial,

@@ -75,8 +75,8 @@ template <int KC, int MODE>   // MODE 0: EM posteriors (hmm_state.py:122-136)  1
 __global__ void __launch_bounds__(PW * 32, 1)
 pool_stats_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t *__restrict__ state, int G, int M,
                   const double *__restrict__ center, const double *__restrict__ var, const double *__restrict__ lc,
-                  const double *__restrict__ shift, float *__restrict__ partial, int32_t *__restrict__ argmin_out,
-                  int nst, int bulk) {
+                  const double *__restrict__ shift, float *__restrict__ partial, unsigned long long *__restrict__ masks,
+                  int32_t *__restrict__ argmin_out, int nst, int bulk) {
     extern __shared__ __align__(128) float sm[];
     constexpr int RW = rec_floats(KC), K2 = (KC + 1) / 2;
     const PoolLayout L = pool_layout(G, KC, D, MODE, nst);
@@ -124,25 +124,47 @@ pool_stats_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t *
         a2[m] = q2[m] = nsh[m] = make_float2(0.f, 0.f);
     }
 
+    // masks != nullptr (G <= 64): the slice is NOT zeroed beforehand; the first flush of a pool STORES its rows and sets
+    // the pool's bit in the warp's mask, later ones add; the reduction reads a slice's rows of pool g only if bit g is set.
+    unsigned long long touched = 0ull;
     auto flush = [&]() {
         if (cur < 0) return;
+        const bool first = masks != nullptr && !((touched >> cur) & 1ull);
+        touched |= 1ull << (cur & 63);
 #pragma unroll
         for (int m = 0; m < KC; ++m) {
             float *r = mine + ((size_t)cur * KC + m) * row;
-            if (lane == 0) {
-                atomicAdd(r, s0[m]);
-                if (MODE == 0 && m == 0) {
-                    atomicAdd(r + 2 * D + 1, (float)run_frames);
-                    atomicAdd(r + 2 * D + 2, llsum);
+            const float c1 = (MODE == 0 && m == 0) ? (float)run_frames : 0.f, c2 = (MODE == 0 && m == 0) ? llsum : 0.f;
+            if (first) {
+                if (lane == 0) {
+                    r[0] = s0[m];
+                    r[2 * D + 1] = c1;
+                    r[2 * D + 2] = c2;
                 }
-            }
-            if (h0) {
-                atomicAdd(r + 1 + d0, a2[m].x);
-                atomicAdd(r + 1 + D + d0, q2[m].x);
-            }
-            if (h1) {
-                atomicAdd(r + 1 + d1, a2[m].y);
-                atomicAdd(r + 1 + D + d1, q2[m].y);
+                if (h0) {
+                    r[1 + d0] = a2[m].x;
+                    r[1 + D + d0] = q2[m].x;
+                }
+                if (h1) {
+                    r[1 + d1] = a2[m].y;
+                    r[1 + D + d1] = q2[m].y;
+                }
+            } else {
+                if (lane == 0) {
+                    atomicAdd(r, s0[m]);
+                    if (MODE == 0 && m == 0) {
+                        atomicAdd(r + 2 * D + 1, c1);
+                        atomicAdd(r + 2 * D + 2, c2);
+                    }
+                }
+                if (h0) {
+                    atomicAdd(r + 1 + d0, a2[m].x);
+                    atomicAdd(r + 1 + D + d0, q2[m].x);
+                }
+                if (h1) {
+                    atomicAdd(r + 1 + d1, a2[m].y);
+                    atomicAdd(r + 1 + D + d1, q2[m].y);
+                }
             }
         }
     };
@@ -356,13 +378,14 @@ pool_stats_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t *
         }
     }
     flush();
+    if (masks != nullptr && lane == 0) masks[wg] = touched;
 }
 
 // out[G*M rows] (+)= sum over the slices [G*k rows] in double, fixed order: 32 lanes of slices per element, slice p
 // goes to lane p % 32, the 32 partial sums are added in lane order.  Rows of the untrained components (m >= k) get zero.
 __global__ void __launch_bounds__(1024)
-reduce_slices32_kernel(const float *__restrict__ partial, int64_t nparts, int M, int k, int row, int64_t len_out,
-                      double *__restrict__ out, int accumulate) {
+reduce_slices32_kernel(const float *__restrict__ partial, const unsigned long long *__restrict__ masks, int64_t nparts,
+                       int M, int k, int row, int64_t len_out, double *__restrict__ out, int accumulate) {
     __shared__ double part[32][33];
     const int e = threadIdx.x & 31, j = threadIdx.x >> 5;
     const int64_t i = (int64_t)blockIdx.x * 32 + e;
@@ -375,6 +398,11 @@ reduce_slices32_kernel(const float *__restrict__ partial, int64_t nparts, int M,
         if (live) {
             const int64_t len = len_out / M * k, src = (g * k + m) * row + col;
             int64_t p = j;
+            if (masks != nullptr) {                         // only the slices whose warp met pool g
+                for (; p < nparts; p += 32)
+                    if ((masks[p] >> g) & 1ull) s += (double)partial[p * len + src];
+                p = nparts;
+            }
             for (; p + 96 < nparts; p += 128) {
                 const float v0 = partial[p * len + src], v1 = partial[(p + 32) * len + src],
                             v2 = partial[(p + 64) * len + src], v3 = partial[(p + 96) * len + src];
@@ -402,13 +430,14 @@ int pow2_at_least(int k) { return k <= 1 ? 1 : k <= 2 ? 2 : k <= 4 ? 4 : 8; }
 
 template <int KC, int MODE>
 int launch(const float *X, int64_t N, int D, const int32_t *state, int G, int M, const double *center, const double *var,
-           const double *lc, const double *shift, float *partial, int32_t *argmin_out, int grid, cudaStream_t st) {
+           const double *lc, const double *shift, float *partial, unsigned long long *masks, int32_t *argmin_out, int grid,
+           cudaStream_t st) {
     const int nst = smem_bytes(G, KC, D, MODE, 2) <= (size_t)MAX_SMEM ? 2 : 1;
     const size_t smem = smem_bytes(G, KC, D, MODE, nst);
     const int bulk = (D & 1) && (reinterpret_cast<uintptr_t>(X) & 15) == 0;     // dense odd rows, 16-byte aligned source
     auto kfn = pool_stats_kernel<KC, MODE>;
     SRB_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kfn<<<grid, PW * 32, smem, st>>>(X, N, D, state, G, M, center, var, lc, shift, partial, argmin_out, nst, bulk);
+    kfn<<<grid, PW * 32, smem, st>>>(X, N, D, state, G, M, center, var, lc, shift, partial, masks, argmin_out, nst, bulk);
     return SRB_OK;
 }
 
@@ -419,7 +448,12 @@ using namespace srb;
 
 extern "C" {
 
-int srb_pool_stats_parts(void) { return sm_count() * PW; }   // private slices of G*k rows (G*M rows of scratch always suffice)
+int srb_pool_stats_parts(void) { return sm_count() * PW; }   // private slices of G*k rows
+
+int64_t srb_pool_stats_partial_floats(int G, int k, int D) {    // slices + one 64-bit pool mask per slice
+    const int64_t parts = srb_pool_stats_parts();
+    return ((parts * G * k * (2 * D + 3) + 1) & ~(int64_t)1) + 2 * parts;
+}
 
 int srb_pool_stats_supported(int G, int k, int D) {
     return G > 0 && k >= 1 && k <= 8 && D > 0 && D <= 64 && smem_bytes(G, pow2_at_least(k), D, 1) <= (size_t)MAX_SMEM &&
@@ -444,13 +478,18 @@ int srb_pool_stats(const float *X, int64_t N, int D, const int32_t *state, int G
     const int row = 2 * D + 3;
     const int64_t len_out = (int64_t)G * M * row, len = (int64_t)G * k * row, parts = (int64_t)grid * PW;
     cudaStream_t st = (cudaStream_t)stream;
-    SRB_CUDA(cudaMemsetAsync(partial, 0, sizeof(float) * len * parts, st));
+    // G <= 64: write-once slices with one 64-bit pool mask per warp behind them (no memset of the slices, the reduction
+    // skips what a warp never met); else zeroed slices
+    unsigned long long *masks = G <= 64 ? reinterpret_cast<unsigned long long *>(partial + ((len * parts + 1) & ~(int64_t)1))
+                                        : nullptr;
+    if (masks) SRB_CUDA(cudaMemsetAsync(masks, 0, sizeof(unsigned long long) * parts, st));
+    else SRB_CUDA(cudaMemsetAsync(partial, 0, sizeof(float) * len * parts, st));
     if (N > 0) {
         int rc = SRB_OK;
 #define SRB_POOL_CASE(KC)                                                                                              \
     case KC:                                                                                                           \
-        rc = mode == 0 ? launch<KC, 0>(X, N, D, state, G, M, center, var, lc, shift, partial, argmin_out, grid, st) \
-                       : launch<KC, 1>(X, N, D, state, G, M, center, var, lc, shift, partial, argmin_out, grid, st); \
+        rc = mode == 0 ? launch<KC, 0>(X, N, D, state, G, M, center, var, lc, shift, partial, masks, argmin_out, grid, st) \
+                       : launch<KC, 1>(X, N, D, state, G, M, center, var, lc, shift, partial, masks, argmin_out, grid, st); \
         break;
         switch (k) {
             SRB_POOL_CASE(1)
@@ -461,7 +500,7 @@ int srb_pool_stats(const float *X, int64_t N, int D, const int32_t *state, int G
 #undef SRB_POOL_CASE
         if (rc != SRB_OK) return rc;
     }
-    reduce_slices32_kernel<<<(int)((len_out + 31) / 32), 1024, 0, st>>>(partial, parts, M, k, row, len_out, out, accumulate);
+    reduce_slices32_kernel<<<(int)((len_out + 31) / 32), 1024, 0, st>>>(partial, masks, parts, M, k, row, len_out, out, accumulate);
     SRB_CUDA(cudaGetLastError());
     return SRB_OK;
 }

@@ -720,9 +720,8 @@ def pool_stats_supported(G, k, D):
     return k in (1, 2, 4, 8) and bool(_l.load().srb_pool_stats_supported(int(G), int(k), int(D)))
 
 
-def _pool_partial(groups, D, dev):
-    L = _l.load()
-    need = L.srb_pool_stats_parts() * groups * L.srb_stats_row(D)
+def _pool_partial(G, k, D, dev):
+    need = _l.load().srb_pool_stats_partial_floats(int(G), int(k), int(D))
     key = (dev.index, "pool_partial")
     buf = _scratch.get(key)
     if buf is None or buf.numel() < need:
@@ -742,7 +741,7 @@ def pool_em_stats(X, state, pm, k, lc=None):
         lc = gauss_consts(pm.var, pm.w)
     out = torch.empty((pm.R * pm.M, L.srb_stats_row(pm.D)), dtype=torch.float64, device=dev)
     _l.check(L.srb_pool_stats(_l.ptr(X), X.shape[0], pm.D, _l.ptr(state), pm.R, pm.M, int(k), 0, _l.ptr(pm.mu),
-                              _l.ptr(pm.var), _l.ptr(lc), None, _l.ptr(_pool_partial(pm.R * pm.M, pm.D, dev)), _l.ptr(out),
+                              _l.ptr(pm.var), _l.ptr(lc), None, _l.ptr(_pool_partial(pm.R, k, pm.D, dev)), _l.ptr(out),
                               None, 0, _l.stream_ptr()))
     return out
 
@@ -760,7 +759,7 @@ def pool_kmeans_stats(X, state, centroids, var0, shift, want_argmin=False):
     out = torch.empty((G * k, L.srb_stats_row(D)), dtype=torch.float64, device=dev)
     am = torch.empty(X.shape[0], dtype=torch.int32, device=dev) if want_argmin else None
     _l.check(L.srb_pool_stats(_l.ptr(X), X.shape[0], D, _l.ptr(state), G, k, k, 1, _l.ptr(c), _l.ptr(v), None, _l.ptr(sh),
-                              _l.ptr(_pool_partial(G * k, D, dev)), _l.ptr(out), _l.ptr(am), 0, _l.stream_ptr()))
+                              _l.ptr(_pool_partial(G, k, D, dev)), _l.ptr(out), _l.ptr(am), 0, _l.stream_ptr()))
     return (out, am) if want_argmin else out
 
 

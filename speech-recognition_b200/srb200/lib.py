@@ -61,6 +61,7 @@ SIGNATURES = {
     "srb_stats_parts": (c_int, []),
     "srb_group_stats": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "srb_pool_stats_parts": (c_int, []),
+    "srb_pool_stats_partial_floats": (c_i64, [c_int, c_int, c_int]),
     "srb_pool_stats_supported": (c_int, [c_int, c_int, c_int]),
     "srb_pool_stats": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),

@@ -273,3 +273,25 @@ def test_fit_update_kernels_equal_numpy_semantics(eng):
     for x, y in zip(*outs):
         assert np.array_equal(x, y)
     assert not outs[0][1][2] and not outs[0][1][7] and outs[0][1][0] and outs[0][3][7].sum() == 0
+
+
+def test_pool_stats_more_than_64_pools(eng):
+    """G = 70 pools: zeroed slices instead of the write-once slices with a 64-bit pool mask; short runs and every run
+    length / alignment a chunk can hold (labels in random runs of 1..9 frames)."""
+    rng = np.random.default_rng(8)
+    G, M, D, N = 70, 2, 39, 20011
+    X = rng.normal(size=(N, D)).astype(np.float32)
+    runs = rng.integers(1, 10, N)
+    lab = np.repeat(rng.integers(-1, G, N), runs)[:N].astype(np.int32)
+    pm = eng.PackedModel(rng.normal(size=(G, M, D)), rng.uniform(0.5, 2.0, size=(G, M, D)), np.full((G, M), 0.5))
+    for labels in (lab, np.minimum(lab, 40).astype(np.int32)):          # second pass: 41 pools in use -> mask path of G = 64
+        Gx = G if labels is lab else 64
+        pmx = pm if labels is lab else eng.PackedModel(pm.mu[:64].cpu().numpy(), pm.var[:64].cpu().numpy(),
+                                                       pm.w[:64].cpu().numpy())
+        ref = eng.gmm_stats(X, labels, pmx, 2).cpu().numpy()
+        got = eng.pool_em_stats(X, labels, pmx, 2).cpu().numpy()
+        assert got.shape == (Gx * M, 2 * D + 3)
+        scale = np.abs(ref[:, 1 + D:1 + 2 * D]).max(axis=1, keepdims=True) + 1e-30
+        assert np.max(np.abs(got - ref)[:, :1 + 2 * D] / np.maximum(scale, np.abs(ref[:, :1]))) < 2e-5
+        np.testing.assert_array_equal(got[:, 2 * D + 1], ref[:, 2 * D + 1])
+        np.testing.assert_allclose(got[:, 2 * D + 2], ref[:, 2 * D + 2], rtol=1e-5, atol=1e-3)
