@@ -634,10 +634,39 @@ def bench_fit(args, ctx, steps, warmup):
         fn()
         torch.cuda.synchronize()
         ph[name] = (time.perf_counter() - t0) * 1e3
+    # dominant kernel: srb_pool_stats, one launch per K-means / EM iteration over the rank's whole shard (X read once);
+    # timed alone here with CUDA events on the launching stream, the call = pool-mask memset + kernel + slice reduction
+    state = ft._labels_from_starts(ft.seg_starts)
+    lc = engine.gauss_consts(ft.pm.var, ft.pm.w)
+    n_loc = int(Xd.shape[0])
+    calls = 20
+    engine.pool_em_stats(Xd, state, ft.pm, 2, lc=lc)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(calls):
+        engine.pool_em_stats(Xd, state, ft.pm, 2, lc=lc)
+    ev1.record()
+    torch.cuda.synchronize()
+    k_ms = ev0.elapsed_time(ev1) / calls
+    pk = peaks()
+    bytes_pf = 4 * D_ + 4
+    gbs = n_loc * bytes_pf / (k_ms * 1e-3) / 1e9
+    fma_pf = 2 * (2 * D_ + 2 * D_)                                   # 2 components x (scoring + moments), 2 FMA per dim each
+    roof = {"bound": "hbm", "achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": gbs / pk["hbm_gbs"],
+            "kernel": "pool_stats_kernel<2, 0> (srb_pool_stats: pool-mask memset + kernel + slice reduction in one call)",
+            "kernel_ms": k_ms,
+            "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "source" not in pk else "fallback 6650 GB/s",
+            "algorithmic": f"{bytes_pf} B/frame = {D_} float32 features + one int32 label, read once per iteration; "
+                           f"{fma_pf} FMA/frame",
+            "fp32_fma_frac": fma_pf * n_loc / (k_ms * 1e-3) / ctx["peak_fma"],
+            "share_of_step": f"{sum(its['kmeans']) + sum(its['em'])} launches x {k_ms:.3f} ms of the {total_ms / steps:.0f} ms "
+                             "step (the working set shrinks as states converge)"}
+    roof.update(ncu_traffic("pool_stats_kernel", n_loc))
     out = {"metric": "full-training frames/s (HMM.fit of all 11 words: skmeans + split K-means + EM + re-alignment)",
            "value": N_total * steps / (total_ms * 1e-3), "unit": "frames/s", "ms_per_step": total_ms / steps,
            "steps": steps, "warmup": warmup, "scaling": "strong", "iterations_to_convergence": its, "phase_ms": ph,
-           "clocks": clocks,
+           "clocks": clocks, "roofline": roof,
+           "gpu_launches": (3 * its["skmeans"] + 4 * (sum(its["kmeans"]) + sum(its["em"])) + 2) * steps,
            "config": {"workload": f"fit: {W_} words x {S_} states x {M_} Gaussians, D={D_}, {args.utts} utterances x "
                                   f"{args.frames} frames in all, split over {world} GPU(s); data-dependent iteration "
                                   "counts (np.allclose stops of the reference), listed in iterations_to_convergence",

@@ -398,9 +398,17 @@ reduce_slices32_kernel(const float *__restrict__ partial, const unsigned long lo
         if (live) {
             const int64_t len = len_out / M * k, src = (g * k + m) * row + col;
             int64_t p = j;
-            if (masks != nullptr) {                         // only the slices whose warp met pool g
-                for (; p < nparts; p += 32)
-                    if ((masks[p] >> g) & 1ull) s += (double)partial[p * len + src];
+            if (masks != nullptr) {                         // only the slices whose warp met pool g; 8 loads in flight
+                for (; p < nparts; p += 256) {
+                    float v[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
+                        const int64_t q = p + 32 * u;
+                        v[u] = (q < nparts && ((masks[q] >> g) & 1ull)) ? partial[q * len + src] : 0.f;
+                    }
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) s += (double)v[u];
+                }
                 p = nparts;
             }
             for (; p + 96 < nparts; p += 128) {
