@@ -617,7 +617,7 @@ def bench_fit(args, ctx, steps, warmup):
         ft.fit()
         last["ft"] = ft
 
-    steps, warmup = max(1, min(steps, 3)), 1
+    steps, warmup = max(1, min(steps, 2)), 1
     sampler = ClockSampler(ctx["local"]).start()
     total_ms, per = timed_steps(step, steps, warmup, torch, dist, world)
     clocks = sampler.stop()
@@ -640,32 +640,48 @@ def bench_fit(args, ctx, steps, warmup):
     lc = engine.gauss_consts(ft.pm.var, ft.pm.w)
     n_loc = int(Xd.shape[0])
     calls = 20
-    engine.pool_em_stats(Xd, state, ft.pm, 2, lc=lc)
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    ev0.record()
-    for _ in range(calls):
-        engine.pool_em_stats(Xd, state, ft.pm, 2, lc=lc)
-    ev1.record()
-    torch.cuda.synchronize()
-    k_ms = ev0.elapsed_time(ev1) / calls
+    def call_ms(f64):
+        engine.pool_em_stats(Xd, state, ft.pm, 2, lc=lc, f64=f64)
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        for _ in range(calls):
+            engine.pool_em_stats(Xd, state, ft.pm, 2, lc=lc, f64=f64)
+        ev1.record()
+        torch.cuda.synchronize()
+        return ev0.elapsed_time(ev1) / calls
+
+    k_ms, k32_ms = call_ms(True), call_ms(False)
     pk = peaks()
     bytes_pf = 4 * D_ + 4
     gbs = n_loc * bytes_pf / (k_ms * 1e-3) / 1e9
     fma_pf = 2 * (2 * D_ + 2 * D_)                                   # 2 components x (scoring + moments), 2 FMA per dim each
     roof = {"bound": "hbm", "achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": gbs / pk["hbm_gbs"],
-            "kernel": "pool_stats_kernel<2, 0> (srb_pool_stats: pool-mask memset + kernel + slice reduction in one call)",
+            "kernel": "pool_stats64_kernel<2, 0> (srb_pool_stats_f64: pool-mask memset + kernel + slice reduction in one call)",
             "kernel_ms": k_ms,
             "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "source" not in pk else "fallback 6650 GB/s",
             "algorithmic": f"{bytes_pf} B/frame = {D_} float32 features + one int32 label, read once per iteration; "
                            f"{fma_pf} FMA/frame",
-            "fp32_fma_frac": fma_pf * n_loc / (k_ms * 1e-3) / ctx["peak_fma"],
+            "fp64_pipe": {"ops_per_frame": 7 * D_ * 2, "frac": 7 * D_ * 2 * n_loc / (k_ms * 1e-3) / (148 * 64 * 1.965e9),
+                          "note": "3 (scoring) + 4 (moments) double operations per dimension and component over the nominal "
+                                  "148 SM x 64 FP64 lanes x 1.965 GHz; no measured FP64 peak in MEASURED_PEAKS.json"},
+            "f32_kernel": {"kernel": "pool_stats_kernel<2, 0> (srb_pool_stats, precision='f32')", "kernel_ms": k32_ms,
+                           "achieved": n_loc * bytes_pf / (k32_ms * 1e-3) / 1e9,
+                           "frac": n_loc * bytes_pf / (k32_ms * 1e-3) / 1e9 / pk["hbm_gbs"],
+                           "fp32_fma_frac": fma_pf * n_loc / (k32_ms * 1e-3) / ctx["peak_fma"]},
             "share_of_step": f"{sum(its['kmeans']) + sum(its['em'])} launches x {k_ms:.3f} ms of the {total_ms / steps:.0f} ms "
                              "step (the working set shrinks as states converge)"}
-    roof.update(ncu_traffic("pool_stats_kernel", n_loc))
+    roof.update(ncu_traffic("pool_stats64_kernel", n_loc))
+    # the FP32 variant of the whole fit (precision="f32": faster passes, K-means may settle in a neighbouring fixed point)
+    t32 = {}
+    if not args.no_sub:
+        def step32():
+            WordFitter(Xd, offs, wordss, W_, S_, M_, use_em=True, seeds=seeds, precision="f32").fit()
+        ms32, _ = timed_steps(step32, 1, 1, torch, dist, world)
+        t32 = {"value": N_total / (ms32 * 1e-3), "unit": "frames/s", "ms_per_step": ms32, "steps": 1}
     out = {"metric": "full-training frames/s (HMM.fit of all 11 words: skmeans + split K-means + EM + re-alignment)",
            "value": N_total * steps / (total_ms * 1e-3), "unit": "frames/s", "ms_per_step": total_ms / steps,
            "steps": steps, "warmup": warmup, "scaling": "strong", "iterations_to_convergence": its, "phase_ms": ph,
-           "clocks": clocks, "roofline": roof,
+           "clocks": clocks, "roofline": roof, "precision": "f64 passes (default)", "f32_variant": t32,
            "gpu_launches": (3 * its["skmeans"] + 4 * (sum(its["kmeans"]) + sum(its["em"])) + 2) * steps,
            "config": {"workload": f"fit: {W_} words x {S_} states x {M_} Gaussians, D={D_}, {args.utts} utterances x "
                                   f"{args.frames} frames in all, split over {world} GPU(s); data-dependent iteration "

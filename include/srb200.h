@@ -352,6 +352,18 @@ int srb_pool_stats(const float *X, int64_t N, int D, const int32_t *state, int G
                    const double *center, const double *var, const double *lc, const double *shift, float *partial,
                    double *out, int32_t *argmin_out, int accumulate, void *stream);
 
+/* srb_pool_stats in float64 (scoring, weights, moments, slices): same arguments and rows, `partial` is caller scratch of
+ * srb_pool_stats_f64_partial_doubles(G, k, D) doubles; k in {1, 2, 4}; the double parameter tables must fit shared memory
+ * (srb_pool_stats_f64_supported; 55 x 2 x 39 and 55 x 4 x 39 do).  For the iterated loops of the batched HMM.fit:
+ * kmeans.py:178-193 is a discrete map run to bitwise equality and GMM.em stops on np.allclose at 1e-8 / 1e-5; with the
+ * reference's own precision the trajectories, fixed points and stop iterations are the reference's (X is float32 and
+ * converts exactly), where FP32 rounding sends K-means on 10^4..10^5-frame pools to a different nearby fixed point. */
+int srb_pool_stats_f64_supported(int G, int k, int D);
+int64_t srb_pool_stats_f64_partial_doubles(int G, int k, int D);
+int srb_pool_stats_f64(const float *X, int64_t N, int D, const int32_t *state, int G, int M, int k, int mode,
+                       const double *center, const double *var, const double *lc, const double *shift, double *partial,
+                       double *out, int32_t *argmin_out, int accumulate, void *stream);
+
 /* Per-iteration updates of the batched HMM.fit, one CTA per pool, float64 without fused multiply-adds (the reference's
  * numpy arithmetic operation by operation, so a pool stops at the iteration the reference's loop would):
  *   srb_fit_em_update      GMM.em's M-step + stop test (hmm_state.py:138-159) on the first k components of every ACTIVE

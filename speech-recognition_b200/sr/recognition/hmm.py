@@ -124,7 +124,8 @@ def classify(models, xs):
     return costs, np.argmin(costs, axis=1)
 
 
-def fit_words(ys_per_word, n_segments, n_gaussians, use_em=True, seeds=None, group=None, fused_align=True):
+def fit_words(ys_per_word, n_segments, n_gaussians, use_em=True, seeds=None, group=None, fused_align=True,
+              precision="f64"):
     """`HMM(n_segments).fit(ys, n_gaussians)` for EVERY word at once (hmm.py:57-124 per word): all words' utterances are
     one device-resident corpus and every phase -- skmeans, binary-split K-means, per-state EM, re-alignment -- runs for
     all states of all words together (srb200.fit.WordFitter; with torch.distributed initialised the utterances of this
@@ -138,7 +139,7 @@ def fit_words(ys_per_word, n_segments, n_gaussians, use_em=True, seeds=None, gro
     words = np.repeat(np.arange(len(ys_per_word)), [len(ys) for ys in ys_per_word])
     X, off = _ops.cat_frames(utts)
     ft = WordFitter(X, off, words, len(ys_per_word), n_segments, n_gaussians, use_em=use_em, seeds=seeds, group=group,
-                    fused_align=fused_align)
+                    fused_align=fused_align, precision=precision)
     models = ft.fit()
     out, S = [], n_segments
     for w, (mu, var, wt, trans) in enumerate(models):

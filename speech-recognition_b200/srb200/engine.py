@@ -730,7 +730,21 @@ def _pool_partial(G, k, D, dev):
     return buf
 
 
-def pool_em_stats(X, state, pm, k, lc=None):
+def pool_stats_supported_f64(G, k, D):
+    return k in (1, 2, 4) and bool(_l.load().srb_pool_stats_f64_supported(int(G), int(k), int(D)))
+
+
+def _pool_partial64(G, k, D, dev):
+    need = _l.load().srb_pool_stats_f64_partial_doubles(int(G), int(k), int(D))
+    key = (dev.index, "pool_partial64")
+    buf = _scratch.get(key)
+    if buf is None or buf.numel() < need:
+        buf = torch.empty(need, dtype=torch.float64, device=dev)
+        _scratch[key] = buf
+    return buf
+
+
+def pool_em_stats(X, state, pm, k, lc=None, f64=False):
     """srb_pool_stats mode 0: E-step statistics of GMM.em for every state at once, frames hard-assigned to states
     (same rows as gmm_stats: double [R*M, 2D+3]).  lc: the model's constants when the caller keeps them current."""
     X = as_frames(X)
@@ -740,13 +754,18 @@ def pool_em_stats(X, state, pm, k, lc=None):
     if lc is None:
         lc = gauss_consts(pm.var, pm.w)
     out = torch.empty((pm.R * pm.M, L.srb_stats_row(pm.D)), dtype=torch.float64, device=dev)
+    if f64:
+        _l.check(L.srb_pool_stats_f64(_l.ptr(X), X.shape[0], pm.D, _l.ptr(state), pm.R, pm.M, int(k), 0, _l.ptr(pm.mu),
+                                      _l.ptr(pm.var), _l.ptr(lc), None, _l.ptr(_pool_partial64(pm.R, k, pm.D, dev)),
+                                      _l.ptr(out), None, 0, _l.stream_ptr()))
+        return out
     _l.check(L.srb_pool_stats(_l.ptr(X), X.shape[0], pm.D, _l.ptr(state), pm.R, pm.M, int(k), 0, _l.ptr(pm.mu),
                               _l.ptr(pm.var), _l.ptr(lc), None, _l.ptr(_pool_partial(pm.R, k, pm.D, dev)), _l.ptr(out),
                               None, 0, _l.stream_ptr()))
     return out
 
 
-def pool_kmeans_stats(X, state, centroids, var0, shift, want_argmin=False):
+def pool_kmeans_stats(X, state, centroids, var0, shift, want_argmin=False, f64=False):
     """srb_pool_stats mode 1: one K-means iteration for every pool at once -- assignment to the nearest of the pool's k
     centroids [G, k, D] under the pool's variance row var0 [G, D], moments of every cluster about shift [G*k, D].
     -> double [G*k, 2D+3] (and the int32[N] assignment)"""
@@ -758,8 +777,13 @@ def pool_kmeans_stats(X, state, centroids, var0, shift, want_argmin=False):
     L = _l.load()
     out = torch.empty((G * k, L.srb_stats_row(D)), dtype=torch.float64, device=dev)
     am = torch.empty(X.shape[0], dtype=torch.int32, device=dev) if want_argmin else None
-    _l.check(L.srb_pool_stats(_l.ptr(X), X.shape[0], D, _l.ptr(state), G, k, k, 1, _l.ptr(c), _l.ptr(v), None, _l.ptr(sh),
-                              _l.ptr(_pool_partial(G, k, D, dev)), _l.ptr(out), _l.ptr(am), 0, _l.stream_ptr()))
+    if f64:
+        _l.check(L.srb_pool_stats_f64(_l.ptr(X), X.shape[0], D, _l.ptr(state), G, k, k, 1, _l.ptr(c), _l.ptr(v), None,
+                                      _l.ptr(sh), _l.ptr(_pool_partial64(G, k, D, dev)), _l.ptr(out), _l.ptr(am), 0,
+                                      _l.stream_ptr()))
+    else:
+        _l.check(L.srb_pool_stats(_l.ptr(X), X.shape[0], D, _l.ptr(state), G, k, k, 1, _l.ptr(c), _l.ptr(v), None, _l.ptr(sh),
+                                  _l.ptr(_pool_partial(G, k, D, dev)), _l.ptr(out), _l.ptr(am), 0, _l.stream_ptr()))
     return (out, am) if want_argmin else out
 
 

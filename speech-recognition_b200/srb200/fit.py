@@ -57,13 +57,17 @@ class WordFitter:
     word-sorted when on the device), off [B+1], words [B]."""
 
     def __init__(self, X, off, words, W, n_segments, n_gaussians, use_em=True, group=None, seeds=None, verbose=False,
-                 fused_align=True):
+                 fused_align=True, precision="f64"):
         X, off, words, self.order = sort_by_word(X if torch.is_tensor(X) else np.asarray(X), np.asarray(off), words)
         self.dev = engine.device()
         self.X = engine.as_frames(X)
         self.W, self.S, self.M, self.D = int(W), int(n_segments), int(n_gaussians), int(self.X.shape[1])
         self.use_em, self.group, self.seeds, self.verbose = use_em, group, seeds, verbose
         self.fused_align = fused_align
+        # "f64": the K-means / EM passes score and accumulate in float64 (srb_pool_stats_f64) so that the iterated loops
+        # follow the reference's float64 trajectories to its fixed points and stop iterations; "f32": srb_pool_stats
+        assert precision in ("f64", "f32")
+        self.f64 = precision == "f64"
         self.words = np.asarray(words, np.int64)
         self.off = np.asarray(off, np.int64)
         self.B, self.N = len(self.off) - 1, int(self.off[-1])
@@ -263,13 +267,14 @@ class WordFitter:
         cen = cen.contiguous().clone()
         shift = cen.clone().reshape(G * k, D)
         fused = engine.pool_stats_supported(G, k, D)          # one pass over X per iteration instead of two
+        f64 = self.f64 and engine.pool_stats_supported_f64(G, k, D)
         ws = self._WorkingSet(self, state)
         its = torch.zeros(G, dtype=torch.int64, device=self.dev)
         cnt = torch.zeros((G, k), dtype=torch.float64, device=self.dev)
         zero = torch.zeros((G * k, 2 * D + 3), dtype=torch.float64, device=self.dev)
         for it in range(max(max_iteration, 1)):
             if ws.n and fused:
-                st = engine.pool_kmeans_stats(ws.X, ws.state, cen, cov0, shift)
+                st = engine.pool_kmeans_stats(ws.X, ws.state, cen, cov0, shift, f64=f64)
             elif ws.n:
                 am = engine.kmeans_assign(ws.X, ws.state, cen, cov0)
                 st = engine.group_stats(ws.X, (ws.state.long() * k + am.long()).to(torch.int32), G * k, shift)
@@ -295,13 +300,14 @@ class WordFitter:
         its = torch.zeros(G, dtype=torch.int64, device=self.dev)
         row = 2 * D + 3
         fused = engine.pool_stats_supported(G, k, D)
+        f64 = self.f64 and engine.pool_stats_supported_f64(G, k, D)
         zero = torch.zeros((G * M, row), dtype=torch.float64, device=self.dev)
         lc = engine.gauss_consts(pm.var, pm.w)
         for it in range(max_iteration):
             if not ws.n:
                 st = zero.clone()
             elif fused:
-                st = engine.pool_em_stats(ws.X, ws.state, pm, k, lc=lc)
+                st = engine.pool_em_stats(ws.X, ws.state, pm, k, lc=lc, f64=f64)
             else:
                 st = engine.gmm_stats(ws.X, ws.state, pm, k)
             st = _allreduce(st, self.group)

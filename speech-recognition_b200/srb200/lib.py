@@ -65,6 +65,10 @@ SIGNATURES = {
     "srb_pool_stats_supported": (c_int, [c_int, c_int, c_int]),
     "srb_pool_stats": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
+    "srb_pool_stats_f64_supported": (c_int, [c_int, c_int, c_int]),
+    "srb_pool_stats_f64_partial_doubles": (c_i64, [c_int, c_int, c_int]),
+    "srb_pool_stats_f64": (c_int, [c_void_p, c_i64, c_int, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                   c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p]),
     "srb_fit_em_update": (c_int, [c_void_p, c_int, c_int, c_int, c_int] + [c_void_p] * 8 + [c_i64, c_void_p, c_void_p]),
     "srb_fit_kmeans_update": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_i64,
                                       c_void_p, c_void_p]),

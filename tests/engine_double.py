@@ -343,11 +343,15 @@ def pool_stats_supported(G, k, D):
     return k in (1, 2, 4, 8)
 
 
-def pool_em_stats(X, state, pm, k, lc=None):
+def pool_stats_supported_f64(G, k, D):
+    return k in (1, 2, 4)
+
+
+def pool_em_stats(X, state, pm, k, lc=None, f64=False):
     return gmm_stats(X, state, pm, k)
 
 
-def pool_kmeans_stats(X, state, centroids, var0, shift, want_argmin=False):
+def pool_kmeans_stats(X, state, centroids, var0, shift, want_argmin=False, f64=False):
     c = _np(centroids, np.float64)
     G, k, D = c.shape
     am = kmeans_assign(X, state, c, var0)
@@ -410,6 +414,6 @@ def install(monkeypatch):
     from srb200 import engine
     for name in ("device", "PackedModel", "as_frames", "as_offsets", "gmm_score", "viterbi", "classify",
                  "group_stats", "moments_from_stats", "gmm_stats", "mstep", "local_dist", "dtw_beam", "kmeans_assign",
-                 "pool_stats_supported", "pool_em_stats", "pool_kmeans_stats",
+                 "pool_stats_supported", "pool_stats_supported_f64", "pool_em_stats", "pool_kmeans_stats",
                  "gauss_consts", "fit_em_update", "fit_kmeans_update"):
         monkeypatch.setattr(engine, name, globals()[name])

@@ -151,3 +151,66 @@ def test_config3_baum_welch_iteration_full_shape():
             for o in range(S):
                 if np.isfinite(models[wd][3][r, o]) and xi[wd][r, o] > 0:
                     np.testing.assert_allclose(np.exp(-got_tr[wd][r, o]), xi[wd][r, o] / out[o], rtol=RTOL)
+
+
+def test_config2_full_fit_sampled_oracle():
+    """BASELINE config 2 through the batched HMM.fit (srb200.fit.WordFitter: skmeans, split K-means, EM, re-alignment for
+    all 55 states at once) on 22 000 utterances (2.2 M frames); K-means runs to its own stop, EM is capped at 30 iterations
+    so that the float64 oracle can follow (a capped K-means would be compared in mid-transient, where the split direction
+    still turns and FP32 / FP64 trajectories drift apart):
+    two sampled words fitted by the oracle word by word, state by state (oracle.skmeans / kmeans / GMMState.em with the same
+    caps and the same draws of the global numpy RNG) must give the same segment means, GMM parameters and final
+    segmentation of the sampled utterances."""
+    from srb200 import synth
+    from srb200.fit import WordFitter
+    W, S, M, KM, EMI = 11, 5, 4, 1000, 30
+    _, base = synth.make_models(1, W=W, S=S, M=M)
+    X, off, words = synth.make_utterances(77, base, 22_000, ragged=(80, 120))
+    assert X.shape[0] >= 2_000_000
+    seeds = [300 + w for w in range(W)]
+    ft = WordFitter(X, off, words, W, S, M, use_em=True, seeds=seeds)
+    ft.skmeans()
+    ft.fit_states(kmeans_max_iteration=KM, em_max_iteration=EMI)
+    ft.align()
+    starts = np.empty_like(ft.final_starts)
+    starts[ft.order] = ft.final_starts                                            # back in corpus order
+    X64 = X.astype(np.float64)
+    for w in (2, 9):
+        us = np.flatnonzero(words == w)
+        ys = [X64[off[u]:off[u + 1]] for u in us]
+        hmu, hsig, trans, segments = orc.skmeans(ys, S)
+        np.testing.assert_allclose(ft.hmm_mu[w], hmu, rtol=RTOL, atol=1e-5)
+        np.testing.assert_allclose(ft.hmm_sigma[w], hsig, rtol=1e-3)
+        np.testing.assert_allclose(ft.trans[w], trans, rtol=1e-12)
+        np.random.seed(seeds[w])
+        mu, cov, wt = [], [], []
+        for i in range(S):
+            data = segments[i]
+            assert len(data) == int(ft._n_loc[w * S + i])
+            st = orc.GMMState(hmu[i], hsig[i], M)
+            part = np.random.randint(0, 2, len(data))
+            cl, cents, cv = orc.kmeans(data, 2, np.stack([hmu[i] * 0.9, hmu[i] * 1.1]), max_iteration=KM, rng_randint=part)
+            weights = np.full(M, 1 / len(data))
+            cs, cc = np.unique(cl, return_counts=True)
+            weights[cs] = cc / len(data)
+            st.update_models(cents, cv, weights[:2])
+            st.em(data, 2, max_iteration=EMI)
+            mu.append(st.mu), cov.append(st.cov), wt.append(st.w)
+        sl = slice(w * S, (w + 1) * S)
+        # float64 passes (srb_pool_stats_f64): same K-means fixed point, same EM trajectory
+        # (measured: weights 1e-7, means 2e-8 absolute -- what the FP32-accumulated segment means of skmeans leave)
+        np.testing.assert_allclose(ft.w[sl], np.array(wt), rtol=1e-5)
+        np.testing.assert_allclose(ft.mu[sl], np.array(mu), rtol=1e-5, atol=1e-7)
+        np.testing.assert_allclose(ft.var[sl], np.array(cov), rtol=1e-5)
+        # final segmentation of 200 sampled utterances against the oracle's alignment under the ORACLE's model
+        # (kmeans.py:196-205); near-ties may fall the other way under models that differ by 2e-3
+        model = (np.array(mu), np.array(cov), np.array(wt), trans)
+        pick = np.random.default_rng(w).choice(len(us), 200, replace=False)
+        same = 0
+        for r in pick:
+            E = orc.emissions(ys[r], [model], np.arange(S))
+            _, path, _ = orc.decode_hmm_states(E, trans)
+            o = np.zeros(S, np.int64)
+            o[1:] = orc.get_segments_from_path(path, S)
+            same += np.array_equal(o, starts[us[r]])
+        assert same >= 198, same

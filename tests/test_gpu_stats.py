@@ -295,3 +295,36 @@ def test_pool_stats_more_than_64_pools(eng):
         assert np.max(np.abs(got - ref)[:, :1 + 2 * D] / np.maximum(scale, np.abs(ref[:, :1]))) < 2e-5
         np.testing.assert_array_equal(got[:, 2 * D + 1], ref[:, 2 * D + 1])
         np.testing.assert_allclose(got[:, 2 * D + 2], ref[:, 2 * D + 2], rtol=1e-5, atol=1e-3)
+
+
+@pytest.mark.parametrize("k", [1, 2, 4])
+def test_pool_stats_f64_equals_float64_statement(eng, k):
+    """srb_pool_stats_f64 against the numpy float64 statement of the same statistics (tests/engine_double.py): 1e-11 of a
+    row's scale for EM, identical assignments and 1e-12 for K-means; run-to-run bit-identical."""
+    import engine_double as ed
+    models, X, lab = _pool_case(ragged=(37, 81))
+    G, D = (55, 39) if k < 4 else (25, 39)                 # the double tables of 55 x 4 x 39 exceed shared memory
+    assert not eng.pool_stats_supported_f64(55, 4, 39)
+    models, lab = models[:G // 5], np.where(lab < G, lab, -1).astype(np.int32)
+    pm, _ = eng.PackedModel.from_words(models)
+    pm_h = ed.PackedModel(pm.mu.cpu().numpy(), pm.var.cpu().numpy(), pm.w.cpu().numpy())
+    assert eng.pool_stats_supported_f64(G, k, D)
+    got = eng.pool_em_stats(X, lab, pm, k, f64=True).cpu().numpy()
+    assert np.array_equal(got, eng.pool_em_stats(X, lab, pm, k, f64=True).cpu().numpy())
+    ref = ed.gmm_stats(X, lab, pm_h, k).numpy()
+    scale = np.abs(ref[:, 1 + D:1 + 2 * D]).max(axis=1, keepdims=True) + 1e-30
+    assert np.max(np.abs(got - ref)[:, :1 + 2 * D] / np.maximum(scale, np.abs(ref[:, :1]))) < 1e-11
+    np.testing.assert_array_equal(got[:, 2 * D + 1], ref[:, 2 * D + 1])
+    np.testing.assert_allclose(got[:, 2 * D + 2], ref[:, 2 * D + 2], rtol=1e-11)
+    if k > 1:
+        rng = np.random.default_rng(9)
+        mu = pm.mu.cpu().numpy()[:, :k].copy()
+        var0 = pm.var.cpu().numpy()[:, 0].copy()
+        shift = (mu + rng.normal(scale=0.05, size=mu.shape)).reshape(G * k, D)
+        st, am = eng.pool_kmeans_stats(X, lab, mu, var0, shift, want_argmin=True, f64=True)
+        st_h, am_h = ed.pool_kmeans_stats(X, lab, mu, var0, shift, want_argmin=True)
+        assert np.array_equal(am.cpu().numpy(), am_h.numpy())
+        st, st_h = st.cpu().numpy(), st_h.numpy()
+        np.testing.assert_array_equal(st[:, 0], st_h[:, 0])
+        scale = np.abs(st_h[:, 1 + D:1 + 2 * D]).max(axis=1, keepdims=True) + 1e-30
+        assert np.max(np.abs(st - st_h)[:, :1 + 2 * D] / scale) < 1e-12

@@ -21,5 +21,6 @@ pm, _ = engine.PackedModel.from_words(models)
 cen = pm.mu[:, :k].contiguous()
 for _ in range(3):
     engine.pool_em_stats(Xd, state, pm, k)
+    engine.pool_em_stats(Xd, state, pm, k, f64=True)
     engine.pool_kmeans_stats(Xd, state, cen, pm.var[:, 0].contiguous(), cen.reshape(-1, 39))
 torch.cuda.synchronize()

@@ -63,3 +63,5 @@ timed("pool_kmeans_stats", lambda: engine.pool_kmeans_stats(ft.X, state, cen, co
 pm4 = engine.PackedModel(np.repeat(ft.hmm_mu.reshape(G, 1, D), M, axis=1) * np.array([0.9, 1.1, 0.95, 1.05])[None, :, None],
                          var, np.full((G, M), 0.25))
 timed("pool_em_stats k=4", lambda: engine.pool_em_stats(ft.X, state, pm4, 4))
+timed("pool_em_stats f64", lambda: engine.pool_em_stats(ft.X, state, pm, k, f64=True))
+timed("pool_kmeans_stats f64", lambda: engine.pool_kmeans_stats(ft.X, state, cen, cov0, shift, f64=True))
