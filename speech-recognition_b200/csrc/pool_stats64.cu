@@ -104,51 +104,69 @@ pool_stats64_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t
     const uint32_t chunk_bytes = 32u * (uint32_t)D * 4u;
 
     int cur = -1, run_frames = 0;
-    double s0[KC], a0[KC], a1[KC], q0[KC], q1[KC], n0[KC], n1[KC], llsum = 0.0;
+    // moments are accumulated about ONE shift per state (component 0's) and moved to each component's own shift when
+    // the run is flushed (exact in float64 to ~1e-16 of the moment): y and y^2 are formed once per frame, not per
+    // component.  Occupancies and log-likelihoods are summed by the lane that owns the frame and reduced at the flush.
+    double ps0[KC], a0[KC], a1[KC], q0[KC], q1[KC], n0[KC], n1[KC], pll = 0.0;
 #pragma unroll
-    for (int m = 0; m < KC; ++m) s0[m] = a0[m] = a1[m] = q0[m] = q1[m] = n0[m] = n1[m] = 0.0;
+    for (int m = 0; m < KC; ++m) ps0[m] = a0[m] = a1[m] = q0[m] = q1[m] = n0[m] = n1[m] = 0.0;
 
     unsigned long long touched = 0ull;
     auto flush = [&]() {
         if (cur < 0) return;
         const bool first = masks != nullptr && !((touched >> cur) & 1ull);
         touched |= 1ull << (cur & 63);
+        double ll = pll;
+        if (MODE == 0) {
+#pragma unroll
+            for (int o = 16; o; o >>= 1) ll += __shfl_xor_sync(0xffffffffu, ll, o);
+        }
 #pragma unroll
         for (int m = 0; m < KC; ++m) {
+            double S = ps0[m];
+#pragma unroll
+            for (int o = 16; o; o >>= 1) S += __shfl_xor_sync(0xffffffffu, S, o);
+            // from the state's shift (component 0's) to this component's: e = y - dlt
+            const double dl0 = n0[0] - n0[m], dl1 = n1[0] - n1[m];
+            const double A0 = a0[m] - dl0 * S, A1 = a1[m] - dl1 * S;
+            const double Q0 = q0[m] - 2.0 * dl0 * a0[m] + dl0 * dl0 * S, Q1 = q1[m] - 2.0 * dl1 * a1[m] + dl1 * dl1 * S;
             double *r = mine + ((size_t)cur * KC + m) * row;
-            const double c1 = (MODE == 0 && m == 0) ? (double)run_frames : 0.0, c2 = (MODE == 0 && m == 0) ? llsum : 0.0;
+            const double c1 = (MODE == 0 && m == 0) ? (double)run_frames : 0.0, c2 = (MODE == 0 && m == 0) ? ll : 0.0;
             if (first) {
                 if (lane == 0) {
-                    r[0] = s0[m];
+                    r[0] = S;
                     r[2 * D + 1] = c1;
                     r[2 * D + 2] = c2;
                 }
                 if (h0) {
-                    r[1 + d0] = a0[m];
-                    r[1 + D + d0] = q0[m];
+                    r[1 + d0] = A0;
+                    r[1 + D + d0] = Q0;
                 }
                 if (h1) {
-                    r[1 + d1] = a1[m];
-                    r[1 + D + d1] = q1[m];
+                    r[1 + d1] = A1;
+                    r[1 + D + d1] = Q1;
                 }
             } else {
                 if (lane == 0) {
-                    atomicAdd(r, s0[m]);
+                    atomicAdd(r, S);
                     if (MODE == 0 && m == 0) {
                         atomicAdd(r + 2 * D + 1, c1);
                         atomicAdd(r + 2 * D + 2, c2);
                     }
                 }
                 if (h0) {
-                    atomicAdd(r + 1 + d0, a0[m]);
-                    atomicAdd(r + 1 + D + d0, q0[m]);
+                    atomicAdd(r + 1 + d0, A0);
+                    atomicAdd(r + 1 + D + d0, Q0);
                 }
                 if (h1) {
-                    atomicAdd(r + 1 + d1, a1[m]);
-                    atomicAdd(r + 1 + D + d1, q1[m]);
+                    atomicAdd(r + 1 + d1, A1);
+                    atomicAdd(r + 1 + D + d1, Q1);
                 }
             }
+            ps0[m] = a0[m] = a1[m] = q0[m] = q1[m] = 0.0;
         }
+        pll = 0.0;
+        run_frames = 0;
     };
 
     if (bulk && lane == 0 && c_begin < c_end && c_begin < nfull) {
@@ -245,12 +263,9 @@ pool_stats64_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t
                 if (sj != cur) {
                     flush();
                     cur = sj;
-                    llsum = 0.0;
-                    run_frames = 0;
+                    if (sj >= 0) {
 #pragma unroll
-                    for (int m = 0; m < KC; ++m) {
-                        s0[m] = a0[m] = a1[m] = q0[m] = q1[m] = 0.0;
-                        if (sj >= 0) {
+                        for (int m = 0; m < KC; ++m) {
                             if (MODE == 0) {
                                 const double *t = tab + (size_t)sj * D * 2 * KC + m;
                                 n0[m] = t[o0 * 2 * KC];
@@ -265,21 +280,24 @@ pool_stats64_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t
                 }
                 if (sj >= 0) {
                     run_frames += j1 - j0;
+                    const bool own = lane >= j0 && lane < j1;
+#pragma unroll
+                    for (int m = 0; m < KC; ++m) ps0[m] += own ? w[m] : 0.0;
+                    if (MODE == 0) pll += own ? llf : 0.0;
                     const float *xp0 = xs + j0 * ld + o0, *xp1 = xs + j0 * ld + o1;
-                    const double *rp = rec + j0 * RW;
+                    const double *rp = rec + j0 * RW + 2;
+                    const double c0 = n0[0], c1 = n1[0];
 #pragma unroll 2
                     for (int j = j0; j < j1; ++j, xp0 += ld, xp1 += ld, rp += RW) {
-                        const double x0 = (double)*xp0, x1 = (double)*xp1;
-                        if (MODE == 0) llsum += rp[1];
+                        const double y0 = (double)*xp0 + c0, y1 = (double)*xp1 + c1;
+                        const double z0 = y0 * y0, z1 = y1 * y1;
 #pragma unroll
                         for (int m = 0; m < KC; ++m) {
-                            const double wm = rp[2 + m];
-                            const double e0 = x0 + n0[m], e1 = x1 + n1[m];
-                            s0[m] += wm;
-                            a0[m] = fma(wm, e0, a0[m]);
-                            a1[m] = fma(wm, e1, a1[m]);
-                            q0[m] = fma(wm * e0, e0, q0[m]);
-                            q1[m] = fma(wm * e1, e1, q1[m]);
+                            const double wm = rp[m];
+                            a0[m] = fma(wm, y0, a0[m]);
+                            a1[m] = fma(wm, y1, a1[m]);
+                            q0[m] = fma(wm, z0, q0[m]);
+                            q1[m] = fma(wm, z1, q1[m]);
                         }
                     }
                 }
