@@ -13,7 +13,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SO = os.path.join(ROOT, "speech-recognition_b200", "srb200", "libsrb200.so")
 WANT = ["UTCHMMA", "LDTM", "STTM", "UTCBAR", "UBLKCP", "UTMALDG", "UTMASTG", "SYNCS", "FFMA2", "FFMA", "LDGSTS", "DFMA", "DADD",
-        "MUFU", "ATOM", "RED"]
+        "MUFU", "ATOM", "RED", "REDG"]
 
 
 def main():
@@ -22,7 +22,7 @@ def main():
     for line in out.splitlines():
         m = re.search(r"Function : (\S+)", line)
         if m:
-            name = subprocess.run(["c++filt", m.group(1)], capture_output=True, text=True).stdout.strip().split("(")[0]
+            name = subprocess.run(["c++filt", m.group(1)], capture_output=True, text=True).stdout.strip().replace("(anonymous namespace)", "anon").split("(")[0]
             counts[name] = collections.Counter()
             continue
         m = re.match(r"\s+/\*[0-9a-f]+\*/\s+(?:@!?U?P\d+\s+)?([A-Z][A-Z0-9_]*)", line)
