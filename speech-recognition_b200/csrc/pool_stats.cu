@@ -55,7 +55,7 @@ __host__ __device__ inline int up4(int n) { return (n + 3) & ~3; }
 // shared memory, in floats: tab [G, D, 2*KC] = {-centre[KC], scale[KC]} per (pool, dim); shf: K-means [G, KC, D] negated
 // shifts, EM [G, KC] constants log w - 0.5 log|2 pi var| (EM shifts by the centre); rec [PW, 32, rec_floats]; xs [PW, nst, 32*ld]; then PW*nst mbarriers.
 struct PoolLayout {
-    int tab, shf, rec, xs, bar_bytes_off, ld, stage;
+    int tab, shf, rec, xs, lab, bar_bytes_off, ld, stage;
     size_t bytes;
 };
 __host__ __device__ inline PoolLayout pool_layout(int G, int KC, int D, int mode, int nst) {
@@ -66,7 +66,8 @@ __host__ __device__ inline PoolLayout pool_layout(int G, int KC, int D, int mode
     L.shf = up4(G * D * 2 * KC);
     L.rec = L.shf + (mode == 1 ? up4(G * KC * D) : up4(G * KC));
     L.xs = L.rec + PW * 32 * rec_floats(KC);
-    L.bar_bytes_off = (L.xs + PW * nst * L.stage) * 4;
+    L.lab = L.xs + PW * nst * L.stage;                     // the chunk's 32 labels per stage (same bulk-copy transaction)
+    L.bar_bytes_off = (L.lab + PW * nst * 32) * 4;
     L.bytes = (size_t)L.bar_bytes_off + (size_t)PW * nst * 8;
     return L;
 }
@@ -96,6 +97,7 @@ pool_stats_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t *
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     float *rec = sm + L.rec + warp * 32 * RW;
     float *xs0 = sm + L.xs + (size_t)warp * nst * L.stage;
+    int *lab0 = reinterpret_cast<int *>(sm + L.lab) + warp * nst * 32;
     uint64_t *bars = reinterpret_cast<uint64_t *>(reinterpret_cast<char *>(sm) + L.bar_bytes_off) + warp * nst;
     if (lane == 0)
         for (int i = 0; i < nst; ++i) bar_init(&bars[i], 1);
@@ -174,14 +176,14 @@ pool_stats_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t *
         for (int i = 0; i < nst; ++i) {
             const int64_t c = c_begin + i;
             if (c < c_end && c < nfull) {
-                bar_expect_tx(&bars[i], chunk_bytes);
+                bar_expect_tx(&bars[i], chunk_bytes + 128u);
                 bulk_load(xs0 + (size_t)i * L.stage, X + c * 32 * D, chunk_bytes, &bars[i]);
+                bulk_load(lab0 + i * 32, state + c * 32, 128u, &bars[i]);
             }
         }
     // lanes without a dimension (d >= D) read column 0 and feed accumulators that are never flushed
     const int o0 = h0 ? d0 : 0, o1 = h1 ? d1 : 0;
     int it = 0;
-    int s_next = (c_begin < c_end && c_begin * 32 + lane < N) ? state[c_begin * 32 + lane] : -1;
     for (int64_t c = c_begin; c < c_end; ++c, ++it) {
         const int stg = (nst == 2) ? (it & 1) : 0;
         float *xs = xs0 + (size_t)stg * L.stage;
@@ -196,11 +198,9 @@ pool_stats_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t *
 
         // ---- phase A: lane = frame, scores the k components of its own pool (its label was fetched a chunk ahead)
         const int64_t n = c * 32 + lane;
-        int s = s_next;
-        {
-            const int64_t nn = n + 32;
-            s_next = (c + 1 < c_end && nn < N) ? state[nn] : -1;
-        }
+        // (labels: with the bulk copy they arrived in shared memory beside the features -- a global load here would share
+        // a scoreboard with everything else in flight and stall the chunk's first instructions)
+        int s = (bulk && c < nfull) ? lab0[stg * 32 + lane] : ((n < N) ? state[n] : -1);
         if (s >= G) s = -1;
         float w[KC], llf = 0.f;
 #pragma unroll
@@ -372,8 +372,9 @@ pool_stats_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t *
         if (bulk && lane == 0) {
             const int64_t cn = c + nst;
             if (cn < c_end && cn < nfull) {
-                bar_expect_tx(&bars[stg], chunk_bytes);
+                bar_expect_tx(&bars[stg], chunk_bytes + 128u);
                 bulk_load(xs, X + cn * 32 * D, chunk_bytes, &bars[stg]);
+                bulk_load(lab0 + stg * 32, state + cn * 32, 128u, &bars[stg]);
             }
         }
     }
@@ -442,7 +443,7 @@ int launch(const float *X, int64_t N, int D, const int32_t *state, int G, int M,
            cudaStream_t st) {
     const int nst = smem_bytes(G, KC, D, MODE, 2) <= (size_t)MAX_SMEM ? 2 : 1;
     const size_t smem = smem_bytes(G, KC, D, MODE, nst);
-    const int bulk = (D & 1) && (reinterpret_cast<uintptr_t>(X) & 15) == 0;     // dense odd rows, 16-byte aligned source
+    const int bulk = (D & 1) && ((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(state)) & 15) == 0;   // dense odd rows, 16-byte aligned sources
     auto kfn = pool_stats_kernel<KC, MODE>;
     SRB_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kfn<<<grid, PW * 32, smem, st>>>(X, N, D, state, G, M, center, var, lc, shift, partial, masks, argmin_out, nst, bulk);

@@ -47,7 +47,7 @@ __device__ __forceinline__ void bulk_load(void *dst, const void *src, uint32_t b
 // shared memory, in bytes: tab double[G, D, 2*KC] = {-centre[KC], scale[KC]}; aux double: K-means [G, KC, D] negated shifts,
 // EM [G, KC] constants; rec double[PW, 32, 2 + KC] = {state, loglik, w[KC]}; xs float[PW, 32*ld]; PW mbarriers.
 struct Layout64 {
-    size_t tab, aux, rec, xs, bar, bytes;
+    size_t tab, aux, rec, xs, lab, bar, bytes;
     int ld;
 };
 __host__ __device__ inline Layout64 layout64(int G, int KC, int D, int mode) {
@@ -58,8 +58,9 @@ __host__ __device__ inline Layout64 layout64(int G, int KC, int D, int mode) {
     L.rec = L.aux + (size_t)(mode == 1 ? G * KC * D : G * KC) * 8;
     L.xs = L.rec + (size_t)PW * 32 * (2 + KC) * 8;
     L.xs = (L.xs + 15) & ~(size_t)15;
-    L.bar = L.xs + (size_t)PW * 32 * L.ld * 4;
-    L.bar = (L.bar + 7) & ~(size_t)7;
+    L.lab = L.xs + (size_t)PW * 32 * L.ld * 4;
+    L.lab = (L.lab + 15) & ~(size_t)15;
+    L.bar = L.lab + (size_t)PW * 32 * 4;
     L.bytes = L.bar + (size_t)PW * 8;
     return L;
 }
@@ -88,6 +89,7 @@ pool_stats64_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     double *rec = reinterpret_cast<double *>(smraw + L.rec) + warp * 32 * RW;
     float *xs = reinterpret_cast<float *>(smraw + L.xs) + (size_t)warp * 32 * ld;
+    int *lab = reinterpret_cast<int *>(smraw + L.lab) + warp * 32;
     uint64_t *bar = reinterpret_cast<uint64_t *>(smraw + L.bar) + warp;
     if (lane == 0) bar_init(bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -170,11 +172,11 @@ pool_stats64_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t
     };
 
     if (bulk && lane == 0 && c_begin < c_end && c_begin < nfull) {
-        bar_expect_tx(bar, chunk_bytes);
+        bar_expect_tx(bar, chunk_bytes + 128u);
         bulk_load(xs, X + c_begin * 32 * D, chunk_bytes, bar);
+        bulk_load(lab, state + c_begin * 32, 128u, bar);
     }
     int it = 0;
-    int s_next = (c_begin < c_end && c_begin * 32 + lane < N) ? state[c_begin * 32 + lane] : -1;
     for (int64_t c = c_begin; c < c_end; ++c, ++it) {
         if (bulk && c < nfull) {
             bar_wait(bar, (uint32_t)(it & 1));
@@ -186,11 +188,7 @@ pool_stats64_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t
         }
         // ---- phase A: lane = frame
         const int64_t n = c * 32 + lane;
-        int s = s_next;
-        {
-            const int64_t nn = n + 32;
-            s_next = (c + 1 < c_end && nn < N) ? state[nn] : -1;
-        }
+        int s = (bulk && c < nfull) ? lab[lane] : ((n < N) ? state[n] : -1);   // labels ride in the same bulk transaction
         if (s >= G) s = -1;
         double w[KC], llf = 0.0;
 #pragma unroll
@@ -306,8 +304,9 @@ pool_stats64_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t
         }
         __syncwarp();
         if (bulk && lane == 0 && c + 1 < c_end && c + 1 < nfull) {
-            bar_expect_tx(bar, chunk_bytes);
+            bar_expect_tx(bar, chunk_bytes + 128u);
             bulk_load(xs, X + (c + 1) * 32 * D, chunk_bytes, bar);
+            bulk_load(lab, state + (c + 1) * 32, 128u, bar);
         }
     }
     flush();
@@ -346,7 +345,7 @@ int launch64(const float *X, int64_t N, int D, const int32_t *state, int G, int 
              const double *lc, const double *shift, double *partial, unsigned long long *masks, int32_t *argmin_out,
              int grid, cudaStream_t st) {
     const size_t smem = layout64(G, KC, D, MODE).bytes;
-    const int bulk = (D & 1) && (reinterpret_cast<uintptr_t>(X) & 15) == 0;
+    const int bulk = (D & 1) && ((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(state)) & 15) == 0;
     auto kfn = pool_stats64_kernel<KC, MODE>;
     SRB_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kfn<<<grid, PW * 32, smem, st>>>(X, N, D, state, G, M, center, var, lc, shift, partial, masks, argmin_out, bulk);
