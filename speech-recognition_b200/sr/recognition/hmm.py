@@ -60,7 +60,20 @@ class HMM:
         self.gmm_states = [GMM(self.mu[i, :], self.sigma[i, :], n_gaussians) for i in range(self.n_segments)]
 
     def fit_GMM(self, ys, n_gaussians):
-        """skmeans -> per-state split / K-means / EM -> Viterbi re-alignment (hmm.py:83-95)."""
+        """skmeans -> per-state split / K-means / EM -> Viterbi re-alignment (hmm.py:83-95), all states of the word at
+        once on the device (fit_words with one word: same draws of the global numpy RNG, same "EM converged" lines)."""
+        m = fit_words([ys], self.n_segments, n_gaussians, use_em=self.use_em)[0]
+        self.mu, self.sigma, self.transitions = m.mu, m.sigma, m.transitions
+        self.gmm_states, self.segments = m.gmm_states, m.segments
+        ft = fit_words.last
+        for g in range(self.n_segments):                       # the reference prints this per state and split (hmm_state.py:153)
+            for its, conv in zip(ft.iterations.get("em", []), ft.converged.get("em", [])):
+                if conv[g]:
+                    print("EM converged at iteration:", int(its[g]))
+
+    def fit_GMM_per_state(self, ys, n_gaussians):
+        """The same fit one state at a time (the reference's own loop order, one launch per K-means / EM iteration and
+        state): kept for callers that hook `_fit_GMM`."""
         self.mu, self.sigma, self.transitions, self.segments = skmeans(ys, self.n_segments,
                                                                        return_segmented_data=True)
         self._init_gmm(n_gaussians)

@@ -81,6 +81,7 @@ class WordFitter:
         self.t_in = torch.arange(self.N, device=self.dev) - self.off_d[self.utt_of]
         self.word_of_frame = torch.from_numpy(self.words).to(self.dev)[self.utt_of]
         self.iterations = {}
+        self.converged = {}                                   # per EM pass: which states met the stop test (not the cap)
         world = torch.distributed.get_world_size(group) if _dist_on(group) else 1
         self.rank = torch.distributed.get_rank(group) if _dist_on(group) else 0
         self.world = world
@@ -320,11 +321,14 @@ class WordFitter:
                     break
                 ws.maybe_compact(active)
         pm.repack()
+        self.converged.setdefault("em", []).append(~active.cpu().numpy())
         return its.cpu().numpy()
 
     # ------------------------------------------------------------------------------------------ phase 3: re-alignment
     def align(self):
         """align_gmm_states (kmeans.py:196-205): Viterbi re-alignment with the trained states -> seg_starts [B, S]."""
+        if self.fused_align and self.dev.type != "cuda":
+            self.fused_align = False                           # host-logic runs on the numpy stand-in: K1 + K2 path
         if self.fused_align:
             from .trainer import IsolatedTrainer
             tr = IsolatedTrainer(self.X, self.off.astype(np.int32), self.words, self.pm, self.trans, self.S, 1, fused=None,
