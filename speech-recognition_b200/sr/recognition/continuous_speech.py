@@ -16,8 +16,7 @@ import torch
 
 from . import _ops
 from .decode import decode_batch
-from .hmm_state import NES, mahalanobis
-from .kmeans import _kmeans_device
+from .hmm_state import NES
 
 
 def build_state_sequences(hmms, label_matrix):
@@ -125,26 +124,34 @@ def continuous_train(data, models, label_seqs, output_path, n_gaussians=4, n_seg
                 if spans is None:
                     gmm_data[seq[row]] = spans = []
                 spans.append((int(off64[u]) + a, int(off64[u]) + b))
-        # ---- per-state split / K-means / EM (continuous_speech.py:110-142)
-        for state in gmm_data.keys():
-            spans = gmm_data[state]
-            assert type(state) is not NES
-            idx = torch.from_numpy(np.concatenate([np.arange(a, b) for a, b in spans])).to(Xd.device)
-            seg_d = Xd.index_select(0, idx)
-            seg_h = X[idx.cpu().numpy()]
-            n_splits = int(np.log(n_gaussians))
-            assert n_splits > 0
-            centroids = seg_d.double().mean(dim=0).cpu().numpy().reshape(1, -1)
-            weights = np.full(n_gaussians, 1 / n_segments)
-            for i in range(n_splits):
-                k = 2 ** (i + 1)
-                centroids = np.concatenate([centroids * 0.9, centroids * 1.1], axis=0)
-                clusters, centroids, variance = _kmeans_device(seg_d, seg_h, k, centroids, mahalanobis, 1000)
-                cs, c_counts = np.unique(clusters, return_counts=True)
-                for c in cs:
-                    weights[c] = c_counts[c] / n_segments       # continuous_speech.py:135-137 (sic)
-                state.update_models(centroids, variance, weights[:k])
-                state._em_device(seg_d, k, 10000)
+        # ---- per-state split / K-means / EM (continuous_speech.py:110-142), all pooled states at once: the pools are
+        # gathered in the dict's order (= the order the reference's loop consumes the global RNG stream in) and go through
+        # the batched loops of srb200.fit (one pass over the pooled frames per K-means / EM iteration)
+        states = list(gmm_data.keys())
+        assert all(type(st) is not NES for st in states)
+        if states:
+            from srb200.fit import WordFitter
+            rows = [np.concatenate([np.arange(a, b) for a, b in gmm_data[st]]) for st in states]
+            idx = torch.from_numpy(np.concatenate(rows)).to(Xd.device)
+            Xp = Xd.index_select(0, idx)
+            lab = torch.from_numpy(np.repeat(np.arange(len(states)), [len(r) for r in rows])).to(Xd.device)
+            Gp, Dp = len(states), Xp.shape[1]
+            cnt = torch.bincount(lab, minlength=Gp).double()
+            mean = torch.zeros((Gp, Dp), dtype=torch.float64, device=Xd.device).index_add_(0, lab, Xp.double()) / cnt[:, None]
+            ft = WordFitter.from_pools(Xp, lab, Gp, n_gaussians, use_em=True)
+            init = (np.stack([np.stack([d.mean for d in st.dists]) for st in states]),
+                    np.stack([np.stack([np.asarray(d.cov, np.float64) for d in st.dists]) for st in states]),
+                    np.stack([st.w for st in states]))
+            old = (np.stack([st.mu_old for st in states]), np.stack([st.sigma_old for st in states]),
+                   np.stack([st.w_old for st in states]))
+            mu, var, wgt = ft.fit_states(state=lab.to(torch.int32), init=init, old=old, centroid0=mean.cpu().numpy(),
+                                         weight_fill=1 / n_segments, weight_den=n_segments)   # continuous_speech.py:135-137 (sic)
+            for g, st in enumerate(states):
+                st.update_models(mu[g].copy(), var[g].copy(), wgt[g].copy())
+                st.mu_old, st.sigma_old, st.w_old = ft.mu_old[g].copy(), ft.var_old[g].copy(), ft.w_old[g].copy()
+                for its, conv in zip(ft.iterations.get("em", []), ft.converged.get("em", [])):
+                    if conv[g]:
+                        print("EM converged at iteration:", int(its[g]))
         # ---- transitions from segment counts (continuous_speech.py:144-164)
         for mi, m in enumerate(new_models):
             states = modelidx_state_map[mi] if state_lookup == "reference" else m.gmm_states

@@ -184,23 +184,53 @@ class WordFitter:
             offset, n_glob = np.zeros(G, np.int64), n_loc
         return rank, n_loc, n_glob, offset
 
-    def fit_states(self, kmeans_max_iteration=1000, em_max_iteration=10000):
+    @classmethod
+    def from_pools(cls, X, state, G, n_gaussians, use_em=True, group=None, seeds=None, verbose=False, precision="f64"):
+        """A fitter over ready-made pools instead of a labelled corpus: X [N, D] frames (numpy or CUDA), state int[N] the
+        pool of every frame (frames of a pool in the order the reference would concatenate them).  For callers that pool
+        themselves (continuous_train, continuous_speech.py:101-142); use fit_states(state=..., init=..., ...)."""
+        self = cls.__new__(cls)
+        self.dev = engine.device()
+        self.X = engine.as_frames(X)
+        self.W, self.S, self.M, self.D = 1, int(G), int(n_gaussians), int(self.X.shape[1])
+        self.use_em, self.group, self.seeds, self.verbose = use_em, group, seeds, verbose
+        self.fused_align, self.f64 = False, precision == "f64"
+        self.N = int(self.X.shape[0])
+        self.iterations, self.converged = {}, {}
+        self.world = torch.distributed.get_world_size(group) if _dist_on(group) else 1
+        self.rank = torch.distributed.get_rank(group) if _dist_on(group) else 0
+        self.pool_state = torch.as_tensor(state).to(self.dev, torch.int32)
+        return self
+
+    def fit_states(self, kmeans_max_iteration=1000, em_max_iteration=10000, *, state=None, init=None, old=None,
+                   centroid0=None, weight_fill=None, weight_den=None):
         """hmm.py:97-124 for every state of every word at once (after skmeans).  The parameters, the stop tests and the
         iteration counters live on the device (float64 torch tensors, same IEEE operations as the reference's numpy);
-        the host only learns, every few iterations, how many states are still running."""
+        the host only learns, every few iterations, how many states are still running.
+        Keyword arguments for pools that do not come from skmeans (continuous_speech.py:121-142): state int[N] labels,
+        init = (mu, var, w) [G, M, ...] the states' current mixtures, old = (mu_old, var_old, w_old) what their first EM
+        stop test compares with, centroid0 [G, D] the first centroid (the pool mean there), weight_fill / weight_den [G]
+        the value the weight vector starts from and the denominator of the cluster counts."""
         W, S, M, D = self.W, self.S, self.M, self.D
         G = W * S
         n_splits = int(np.log(M))
         assert n_splits > 0
-        state = self._labels_from_starts(self.seg_starts)                      # pool of every frame
+        if state is None:
+            state = self._labels_from_starts(self.seg_starts)                  # pool of every frame
         rank, n_loc, n_glob, offset = self._pool_ranks(state)
-        mu = np.repeat(self.hmm_mu.reshape(G, 1, D), M, axis=1).copy()          # GMM.__init__: M copies (hmm_state.py:105-112)
-        var = np.repeat(self.hmm_sigma.reshape(G, 1, D), M, axis=1).copy()
-        wgt = np.full((G, M), 1.0 / M)
+        if init is None:
+            mu = np.repeat(self.hmm_mu.reshape(G, 1, D), M, axis=1).copy()      # GMM.__init__: M copies (hmm_state.py:105-112)
+            var = np.repeat(self.hmm_sigma.reshape(G, 1, D), M, axis=1).copy()
+            wgt = np.full((G, M), 1.0 / M)
+        else:
+            mu, var, wgt = (np.array(a, dtype=np.float64) for a in init)
         pm = engine.PackedModel(mu, var, wgt)
-        self._old = [pm.mu.clone(), pm.var.clone(), pm.w.clone()]
-        centroids = self._t(self.hmm_mu.reshape(G, 1, D))
-        weights = np.repeat((1.0 / np.maximum(n_glob, 1))[:, None], M, axis=1)  # np.full(n_gaussians, 1 / n) (hmm.py:108)
+        self._old = [pm.mu.clone(), pm.var.clone(), pm.w.clone()] if old is None else [self._t(a) for a in old]
+        centroids = self._t((self.hmm_mu if centroid0 is None else np.asarray(centroid0)).reshape(G, 1, D))
+        weight_den = n_glob if weight_den is None else np.broadcast_to(np.asarray(weight_den, np.float64), (G,))
+        if weight_fill is None:
+            weight_fill = 1.0 / np.maximum(n_glob, 1)                           # np.full(n_gaussians, 1 / n) (hmm.py:108)
+        weights = np.repeat(np.broadcast_to(np.asarray(weight_fill, np.float64), (G,)).reshape(G, 1), M, axis=1)
         self.iterations["kmeans"], self.iterations["em"] = [], []
         self._n_loc = torch.from_numpy(n_loc).to(self.dev)
         # the global numpy RNG stream of kmeans.py:171 in the reference's order: word by word (optionally re-seeded per
@@ -232,7 +262,7 @@ class WordFitter:
                 present = np.flatnonzero(cnt[g] > 0)
                 c_counts = cnt[g][present]
                 for cl in present:
-                    weights[g, cl] = c_counts[cl] / n_glob[g]                    # IndexError like hmm.py:116-118 if a cluster is empty
+                    weights[g, cl] = c_counts[cl] / weight_den[g]                # IndexError like hmm.py:116-118 if a cluster is empty
             pm.mu[:, :k], pm.var[:, :k], pm.w[:, :k] = centroids, self._t(cov), self._t(weights[:, :k])
             pm.repack()
             if self.use_em:
