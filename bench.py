@@ -1,12 +1,12 @@
 #!/usr/bin/env python
 """bench.py -- throughput of the B200 GMM-HMM hot path (BASELINE.json metric), one JSON line on rank 0.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload em|decode|fb|connected|stress|frontend]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload em|decode|fb|connected|stress|fit|frontend]
                     [--scaling strong|weak] [--impl ours|reference] [--no-sub]
 
 The default line is BASELINE config 2 (`configs[1]`, the configuration the EM metric is quoted on): one segmental-K-means
 + EM iteration over 100 k labelled 100-frame utterances (Viterbi alignment -> posteriors -> sufficient statistics ->
-allreduce -> M-step).  At N = 1 the other four configurations ride along as sub-lines, each a complete record of its
+allreduce -> M-step).  At N = 1 the other four configurations and the full fit ride along as sub-lines, each a complete record of its
 own (value, roofline with ncu traffic, cpu_baseline, e2e):
   decode     config 1 shape at benchmark scale: every 100-frame utterance scored against all 11 word models (11 x 5 x 4,
              D = 39) and Viterbi-decoded (core.py:79-87)
@@ -14,6 +14,8 @@ own (value, roofline with ncu traffic, cpu_baseline, e2e):
   connected  config 4: connected digit strings, 7 layers x 11 words (393 states), 4 096 utterances x 500 frames, graph
              Viterbi with back-pointers, traceback and word strings
   stress     config 5: 2 000 states x 32 Gaussians x 39 dims on 10 M frames, best state per frame
+  fit        config 2 in full: HMM.fit of all 11 words on the 100 k utterances (skmeans, split K-means and EM to the
+             reference's own stop tests, re-alignment), float64 passes; strong scaling at N > 1
 At N > 1 the EM line is STRONG scaling by default (BASELINE config 2: "100k synthetic utterances, sharded across
 1/2/4/8"): the corpus is split over the ranks; `--scaling weak` gives every rank its own 100 k utterances.
 
