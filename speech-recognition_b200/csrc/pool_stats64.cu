@@ -199,7 +199,7 @@ pool_stats64_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t
             double ll[KC];
 #pragma unroll
             for (int m = 0; m < KC; ++m) ll[m] = 0.0;
-#pragma unroll 13
+#pragma unroll 39
             for (int d = 0; d < D; ++d) {
                 const double x = (double)xr[d];
 #pragma unroll
@@ -285,7 +285,7 @@ pool_stats64_kernel(const float *__restrict__ X, int64_t N, int D, const int32_t
                     const float *xp0 = xs + j0 * ld + o0, *xp1 = xs + j0 * ld + o1;
                     const double *rp = rec + j0 * RW + 2;
                     const double c0 = n0[0], c1 = n1[0];
-#pragma unroll 4
+#pragma unroll 8
                     for (int j = j0; j < j1; ++j, xp0 += ld, xp1 += ld, rp += RW) {
                         const double y0 = (double)*xp0 + c0, y1 = (double)*xp1 + c1;
                         const double z0 = y0 * y0, z1 = y1 * y1;
